@@ -1,0 +1,580 @@
+/*
+ * pllb200.h — C ABI of the B200-native phylogenetic-likelihood library (libpll_b200.so).
+ *
+ * This header is the drop-in boundary for ONE hot path of ddarriba/pll-modules + libpll-2:
+ * P-matrix construction, CLV ("partials") updates over operation lists, edge/root log-likelihood,
+ * sumtable + first/second derivatives, and the pllmod_treeinfo_* / pllmod_opt_* host drivers on top.
+ *
+ * Every symbol below that starts with pll_ / pllmod_ keeps the NAME, ARGUMENT MEANING, RETURN
+ * CONVENTION and STRUCT LAYOUT of the reference declaration it replaces, cited as (file:line)
+ * relative to the reference tree:
+ *     L = libs/libpll/src/pll.h      T = src/tree/pll_tree.h
+ *     O = src/optimize/pll_optimize.h   C = src/pllmod_common.h
+ * so that a caller compiled against the reference headers can be re-linked against
+ * libpll_b200.so unchanged for this path.  Symbols that start with pllb200_ are additive.
+ *
+ * Residency contract (differs from the CPU library):
+ *   - partition->clv[i] (allocated ones), partition->scale_buffer[i] and partition->pmatrix[i] are
+ *     DEVICE pointers into HBM arenas.  The host must not dereference them; use
+ *     pllb200_download_clv / _scaler / _pmatrix.
+ *   - tipchars, pattern_weights, invariant, model arrays (rates, weights, frequencies, subst_params,
+ *     eigen*, prop_invar) are ordinary host memory exactly as in the reference; the library mirrors
+ *     them to the device when an entry point consumes them.
+ *   - sumtable buffers passed to pll_update_sumtable / pll_compute_likelihood_derivatives are used
+ *     as KEYS for device-resident shadow buffers; their host bytes are never touched.
+ *
+ * Plain C, no C++ and no CUDA/torch types in any signature.
+ */
+#ifndef PLLB200_H_
+#define PLLB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PLL_EXPORT
+
+/* ---- return codes / constants (L:82-110) ------------------------------------------------- */
+#define PLL_FAILURE 0
+#define PLL_SUCCESS 1
+#define PLL_FALSE 0
+#define PLL_TRUE 1
+
+#define PLL_ALIGNMENT_CPU 8
+#define PLL_ALIGNMENT_SSE 16
+#define PLL_ALIGNMENT_AVX 32
+
+#define PLL_ASCII_SIZE 256
+
+/* 2^256 and 2^-256: the underflow rescaling constants (L:96-100) */
+#define PLL_SCALE_FACTOR 115792089237316195423570985008687907853269984665640564039457584007913129639936.0
+#define PLL_SCALE_THRESHOLD (1.0 / PLL_SCALE_FACTOR)
+#define PLL_SCALE_BUFFER_NONE -1
+#define PLL_SCALE_RATE_MAXDIFF 4 /* L:104 */
+
+#define PLL_MISC_EPSILON 1e-8
+#define PLL_EIGEN_MINFREQ 1e-6
+
+/* ---- attribute flags (L:114-137).  ARCH bits are accepted and ignored: the arithmetic always
+ *      runs on the device. ------------------------------------------------------------------ */
+#define PLL_ATTRIB_ARCH_CPU 0
+#define PLL_ATTRIB_ARCH_SSE (1 << 0)
+#define PLL_ATTRIB_ARCH_AVX (1 << 1)
+#define PLL_ATTRIB_ARCH_AVX2 (1 << 2)
+#define PLL_ATTRIB_ARCH_AVX512 (1 << 3)
+#define PLL_ATTRIB_ARCH_MASK 0xF
+#define PLL_ATTRIB_PATTERN_TIP (1 << 4)
+#define PLL_ATTRIB_AB_LEWIS (1 << 5)
+#define PLL_ATTRIB_AB_FELSENSTEIN (2 << 5)
+#define PLL_ATTRIB_AB_STAMATAKIS (3 << 5)
+#define PLL_ATTRIB_AB_MASK (7 << 5)
+#define PLL_ATTRIB_AB_FLAG (1 << 8)
+#define PLL_ATTRIB_RATE_SCALERS (1 << 9)
+#define PLL_ATTRIB_SITE_REPEATS (1 << 10) /* rejected: PLL_ERROR_PARAM_INVALID */
+#define PLL_ATTRIB_MASK ((1 << 11) - 1)
+
+#define PLL_TREE_TRAVERSE_POSTORDER 1
+#define PLL_TREE_TRAVERSE_PREORDER 2
+
+#define PLL_GAMMA_RATES_MEAN 0
+#define PLL_GAMMA_RATES_MEDIAN 1
+
+/* ---- error codes (L:162-196) -------------------------------------------------------------- */
+#define PLL_ERROR_MEM_ALLOC 112
+#define PLL_ERROR_PARAM_INVALID 113
+#define PLL_ERROR_TIPDATA_ILLEGALSTATE 114
+#define PLL_ERROR_TIPDATA_ILLEGALFUNCTION 115
+#define PLL_ERROR_INVAR_INCOMPAT 117
+#define PLL_ERROR_INVAR_PROPORTION 118
+#define PLL_ERROR_INVAR_PARAMINDEX 119
+#define PLL_ERROR_INVAR_NONEFOUND 120
+#define PLL_ERROR_AB_INVALIDMETHOD 121
+#define PLL_ERROR_AB_NOSUPPORT 122
+#define PLL_ERROR_EINVAL 130
+#define PLL_ERROR_TREE_INVALID 133
+/* additive: a CUDA runtime / device failure, message carries cudaGetErrorString */
+#define PLLB200_ERROR_DEVICE 9001
+
+typedef unsigned long long pll_state_t;
+typedef int pll_bool_t;
+
+struct pll_repeats; /* site repeats are out of scope; the pointer slot is kept for layout */
+
+/* L:241-288 — layout identical (35 fields, same order and types). */
+typedef struct pll_partition
+{
+  unsigned int tips;
+  unsigned int clv_buffers;
+  unsigned int nodes;
+  unsigned int states;
+  unsigned int sites;
+  unsigned int pattern_weight_sum;
+  unsigned int rate_matrices;
+  unsigned int prob_matrices;
+  unsigned int rate_cats;
+  unsigned int scale_buffers;
+  unsigned int attributes;
+
+  size_t alignment;
+  unsigned int states_padded;
+
+  double ** clv;               /* DEVICE pointers (NULL for tips under PATTERN_TIP) */
+  double ** pmatrix;           /* DEVICE pointers */
+  double * rates;
+  double * rate_weights;
+  double ** subst_params;
+  unsigned int ** scale_buffer; /* DEVICE pointers */
+  double ** frequencies;
+  double * prop_invar;
+  int * invariant;
+  unsigned int * pattern_weights;
+
+  int * eigen_decomp_valid;
+  double ** eigenvecs;
+  double ** inv_eigenvecs;
+  double ** eigenvals;
+
+  unsigned int maxstates;
+  unsigned char ** tipchars;
+  unsigned char * charmap;
+  double * ttlookup;           /* unused on the device path (always NULL) */
+  pll_state_t * tipmap;
+
+  int asc_bias_alloc;
+  int asc_additional_sites;
+
+  struct pll_repeats * repeats; /* always NULL */
+} pll_partition_t;
+
+/* L:325-335 */
+typedef struct pll_operation
+{
+  unsigned int parent_clv_index;
+  int parent_scaler_index;
+  unsigned int child1_clv_index;
+  unsigned int child1_matrix_index;
+  int child1_scaler_index;
+  unsigned int child2_clv_index;
+  unsigned int child2_matrix_index;
+  int child2_scaler_index;
+} pll_operation_t;
+
+/* L:388-400 */
+typedef struct pll_unode_s
+{
+  char * label;
+  double length;
+  unsigned int node_index;
+  unsigned int clv_index;
+  int scaler_index;
+  unsigned int pmatrix_index;
+  struct pll_unode_s * next;
+  struct pll_unode_s * back;
+  void * data;
+} pll_unode_t;
+
+/* L:402-411 */
+typedef struct pll_utree_s
+{
+  unsigned int tip_count;
+  unsigned int inner_count;
+  unsigned int edge_count;
+  int binary;
+  pll_unode_t ** nodes;
+  pll_unode_t * vroot;
+} pll_utree_t;
+
+/* L:553-554 */
+extern __thread int pll_errno;
+extern __thread char pll_errmsg[200];
+
+/* L:556-559 — state maps for tip encoding (bitmask per ASCII character) */
+extern const pll_state_t pll_map_bin[256];
+extern const pll_state_t pll_map_nt[256];
+extern const pll_state_t pll_map_aa[256];
+
+/* ---- libpll partition API --------------------------------------------------------------- */
+
+/* L:638-646 (pll.c:424). Allocates the HBM arenas. Fails (NULL, pll_errno=PLLB200_ERROR_DEVICE)
+ * when no CUDA device is usable: there is no CPU fallback. */
+pll_partition_t * pll_partition_create(unsigned int tips,
+                                       unsigned int clv_buffers,
+                                       unsigned int states,
+                                       unsigned int sites,
+                                       unsigned int rate_matrices,
+                                       unsigned int prob_matrices,
+                                       unsigned int rate_cats,
+                                       unsigned int scale_buffers,
+                                       unsigned int attributes);
+/* L:648 (pll.c:870) */
+void pll_partition_destroy(pll_partition_t * partition);
+/* L:650-653 (pll.c:1026) */
+int pll_set_tip_states(pll_partition_t * partition, unsigned int tip_index,
+                       const pll_state_t * map, const char * sequence);
+/* L:655-658 (pll.c:1066) */
+int pll_set_tip_clv(pll_partition_t * partition, unsigned int tip_index,
+                    const double * clv, int padding);
+/* L:660-661 (pll.c:1131) */
+void pll_set_pattern_weights(pll_partition_t * partition, const unsigned int * pattern_weights);
+/* L:674-675 (pll.c:133,148) */
+void * pll_aligned_alloc(size_t size, size_t alignment);
+void pll_aligned_free(void * ptr);
+/* pll.c:1202 */
+void pll_fill_parent_scaler(unsigned int scaler_size, unsigned int * parent_scaler,
+                            const unsigned int * left_scaler, const unsigned int * right_scaler);
+
+/* L:746-748 (models.c:546) */
+void pll_set_subst_params(pll_partition_t * partition, unsigned int params_index,
+                          const double * params);
+/* L:750-752 (models.c:445) */
+void pll_set_frequencies(pll_partition_t * partition, unsigned int params_index,
+                         const double * frequencies);
+/* L:754-755 (models.c:478) */
+void pll_set_category_rates(pll_partition_t * partition, const double * rates);
+/* L:757-758 (models.c:485) */
+void pll_set_category_weights(pll_partition_t * partition, const double * rate_weights);
+/* L:760-761 (models.c:293) host-side symmetric eigensolver */
+int pll_update_eigen(pll_partition_t * partition, unsigned int params_index);
+/* L:763-767 (models.c:412) */
+int pll_update_prob_matrices(pll_partition_t * partition,
+                             const unsigned int * params_indices,
+                             const unsigned int * matrix_indices,
+                             const double * branch_lengths,
+                             unsigned int count);
+/* L:769-770 (models.c:651) */
+unsigned int pll_count_invariant_sites(pll_partition_t * partition, unsigned int * state_inv_count);
+/* L:772 (models.c:651..) */
+int pll_update_invariant_sites(pll_partition_t * partition);
+/* L:774-776 (models.c:495) */
+int pll_update_invariant_sites_proportion(pll_partition_t * partition,
+                                          unsigned int params_index, double prop_invar);
+
+/* L:784-787 (likelihood.c:122) */
+double pll_compute_root_loglikelihood(pll_partition_t * partition, unsigned int clv_index,
+                                      int scaler_index, const unsigned int * freqs_indices,
+                                      double * persite_lnl);
+/* L:789-797 (likelihood.c:586) */
+double pll_compute_edge_loglikelihood(pll_partition_t * partition,
+                                      unsigned int parent_clv_index, int parent_scaler_index,
+                                      unsigned int child_clv_index, int child_scaler_index,
+                                      unsigned int matrix_index,
+                                      const unsigned int * freqs_indices,
+                                      double * persite_lnl);
+/* L:823-825 (partials.c:237) — asynchronous on the partition's stream */
+void pll_update_partials(pll_partition_t * partition, const pll_operation_t * operations,
+                         unsigned int count);
+/* L:834-840 (derivatives.c:239) */
+int pll_update_sumtable(pll_partition_t * partition,
+                        unsigned int parent_clv_index, unsigned int child_clv_index,
+                        int parent_scaler_index, int child_scaler_index,
+                        const unsigned int * params_indices, double * sumtable);
+/* L:842-849 (derivatives.c:333) */
+int pll_compute_likelihood_derivatives(pll_partition_t * partition,
+                                       int parent_scaler_index, int child_scaler_index,
+                                       double branch_length,
+                                       const unsigned int * params_indices,
+                                       const double * sumtable,
+                                       double * d_f, double * dd_f);
+/* L:856-858 (gamma.c:220) */
+int pll_compute_gamma_cats(double alpha, unsigned int categories, double * output_rates,
+                           int rates_mode);
+
+/* ---- libpll utree subset the treeinfo/optimize drivers need -------------------------------- */
+/* L:1010-1011 (parse_utree.y:99-145) */
+void pll_utree_destroy(pll_utree_t * tree, void (*cb_destroy)(void *));
+/* L:1020-1021 (parse_utree.y:522) */
+pll_utree_t * pll_utree_wraptree(pll_unode_t * root, unsigned int tip_count);
+/* L:929-933 (utree.c:427) */
+int pll_utree_traverse(pll_unode_t * root, int traversal, int (*cbtrav)(pll_unode_t *),
+                       pll_unode_t ** outbuffer, unsigned int * trav_size);
+/* L:921-927 (utree.c:317) */
+void pll_utree_create_operations(pll_unode_t * const * trav_buffer, unsigned int trav_buffer_size,
+                                 double * branches, unsigned int * pmatrix_indices,
+                                 pll_operation_t * ops, unsigned int * matrix_count,
+                                 unsigned int * ops_count);
+
+/* ---- pll-modules common (C:24-47) --------------------------------------------------------- */
+#define PLLMOD_COMMON_BRLEN_LINKED 0
+#define PLLMOD_COMMON_BRLEN_SCALED 1
+#define PLLMOD_COMMON_BRLEN_UNLINKED 2
+#define PLLMOD_COMMON_REDUCE_SUM 0
+#define PLLMOD_COMMON_REDUCE_MAX 1
+#define PLLMOD_COMMON_REDUCE_MIN 2
+#define PLLMOD_ERROR_INVALID_RANGE 1001
+#define PLLMOD_ERROR_INVALID_NODE_TYPE 1002
+#define PLLMOD_ERROR_INVALID_INDEX 1003
+#define PLLMOD_ERROR_NOT_IMPLEMENTED 1004
+void pllmod_set_error(int errno_, const char * errmsg_fmt, ...);
+void pllmod_reset_error(void);
+
+/* ---- pll-modules tree subset (T:35,63,219-277) -------------------------------------------- */
+#define PLLMOD_TREE_DEFAULT_BRANCH_LENGTH 0.1
+#define PLLMOD_TREE_ERROR_INVALID_TREE_SIZE 3456
+#define PLLMOD_TREE_ERROR_INVALID_TREE 3584
+#define PLLMOD_TREEINFO_PARTITION_ALL -1
+
+typedef struct pllb200_split_set_opaque pll_split_set_t; /* constraint checks: out of scope */
+
+/* T:202-208 */
+typedef struct treeinfo_edge
+{
+  unsigned int left_index;
+  unsigned int right_index;
+  unsigned int pmatrix_index;
+  double brlen;
+} pllmod_treeinfo_edge_t;
+
+/* T:210-217 */
+typedef struct treeinfo_topology
+{
+  unsigned int edge_count;
+  unsigned int brlen_set_count;
+  unsigned int root_index;
+  pllmod_treeinfo_edge_t * edges;
+  double ** branch_lengths;
+} pllmod_treeinfo_topology_t;
+
+/* T:219-277 — layout identical. */
+typedef struct treeinfo
+{
+  unsigned int tip_count;
+  unsigned int partition_count;
+  int brlen_linkage;
+  double * linked_branch_lengths;
+  pll_unode_t * root;
+  pll_utree_t * tree;
+  unsigned int subnode_count;
+  pll_unode_t ** subnodes;
+  pll_partition_t ** partitions;
+  double * alphas;
+  int * gamma_mode;
+  unsigned int ** param_indices;
+  int ** subst_matrix_symmetries;
+  double ** branch_lengths;
+  double * brlen_scalers;
+  double * partition_loglh;
+  int * params_to_optimize;
+  unsigned int init_partition_count;
+  unsigned int * init_partition_idx;
+  pll_partition_t ** init_partitions;
+  unsigned int * constraint;
+  pll_split_set_t * cons_splits;
+  pll_split_set_t * tree_splits;
+  double ** deriv_precomp;
+  char ** clv_valid;
+  char ** pmatrix_valid;
+  pll_unode_t ** travbuffer;
+  unsigned int * matrix_indices;
+  pll_operation_t * operations;
+  int active_partition;
+  unsigned int counter;
+  void * parallel_context;
+  void (*parallel_reduce_cb)(void *, double *, size_t, int);
+} pllmod_treeinfo_t;
+
+/* pll_tree.c:903 — random topology, default branch lengths (RNG differs from the reference's
+ * glibc-style generator: topologies are valid but not identical for equal seeds) */
+pll_utree_t * pllmod_utree_create_random(unsigned int taxa_count, const char * const * names,
+                                         unsigned int random_seed);
+/* utree_operations.c */
+int pllmod_utree_is_tip(const pll_unode_t * node);
+void pllmod_utree_set_length(pll_unode_t * edge, double length);
+int pllmod_utree_connect_nodes(pll_unode_t * parent, pll_unode_t * child, double length);
+
+/* T:616-790 (treeinfo.c) */
+pllmod_treeinfo_t * pllmod_treeinfo_create(pll_unode_t * root, unsigned int tips,
+                                           unsigned int partitions, int brlen_linkage);
+int pllmod_treeinfo_set_parallel_context(pllmod_treeinfo_t * treeinfo, void * parallel_context,
+                                         void (*parallel_reduce_cb)(void *, double *, size_t, int op));
+int pllmod_treeinfo_init_partition(pllmod_treeinfo_t * treeinfo, unsigned int partition_index,
+                                   pll_partition_t * partition, int params_to_optimize,
+                                   int gamma_mode, double alpha,
+                                   const unsigned int * param_indices,
+                                   const int * subst_matrix_symmetries);
+int pllmod_treeinfo_set_active_partition(pllmod_treeinfo_t * treeinfo, int partition_index);
+int pllmod_treeinfo_set_root(pllmod_treeinfo_t * treeinfo, pll_unode_t * root);
+int pllmod_treeinfo_get_branch_length_all(const pllmod_treeinfo_t * treeinfo,
+                                          const pll_unode_t * edge, double * lengths);
+int pllmod_treeinfo_set_branch_length(pllmod_treeinfo_t * treeinfo, pll_unode_t * edge, double length);
+int pllmod_treeinfo_set_branch_length_all(pllmod_treeinfo_t * treeinfo, pll_unode_t * edge,
+                                          const double * lengths);
+int pllmod_treeinfo_set_branch_length_partition(pllmod_treeinfo_t * treeinfo, pll_unode_t * edge,
+                                                int partition_index, double length);
+pllmod_treeinfo_topology_t * pllmod_treeinfo_get_topology(const pllmod_treeinfo_t * treeinfo,
+                                                          pllmod_treeinfo_topology_t * topol);
+int pllmod_treeinfo_set_topology(pllmod_treeinfo_t * treeinfo, const pllmod_treeinfo_topology_t * topol);
+int pllmod_treeinfo_destroy_topology(pllmod_treeinfo_topology_t * topol);
+int pllmod_treeinfo_destroy_partition(pllmod_treeinfo_t * treeinfo, unsigned int partition_index);
+void pllmod_treeinfo_destroy(pllmod_treeinfo_t * treeinfo);
+int pllmod_treeinfo_update_prob_matrices(pllmod_treeinfo_t * treeinfo, int update_all);
+void pllmod_treeinfo_invalidate_all(pllmod_treeinfo_t * treeinfo);
+int pllmod_treeinfo_validate_clvs(pllmod_treeinfo_t * treeinfo, pll_unode_t ** travbuffer,
+                                  unsigned int travbuffer_size);
+void pllmod_treeinfo_invalidate_pmatrix(pllmod_treeinfo_t * treeinfo, const pll_unode_t * edge);
+void pllmod_treeinfo_invalidate_clv(pllmod_treeinfo_t * treeinfo, const pll_unode_t * edge);
+double pllmod_treeinfo_compute_loglh(pllmod_treeinfo_t * treeinfo, int incremental);
+double pllmod_treeinfo_compute_loglh_flex(pllmod_treeinfo_t * treeinfo, int incremental,
+                                          int update_pmatrices);
+double pllmod_treeinfo_compute_loglh_persite(pllmod_treeinfo_t * treeinfo, int incremental,
+                                             double ** persite_lnl);
+int pllmod_treeinfo_scale_branches_all(pllmod_treeinfo_t * treeinfo, double scaler);
+int pllmod_treeinfo_scale_branches_partition(pllmod_treeinfo_t * treeinfo,
+                                             unsigned int partition_idx, double scaler);
+int pllmod_treeinfo_normalize_brlen_scalers(pllmod_treeinfo_t * treeinfo);
+int pllmod_treeinfo_set_tree(pllmod_treeinfo_t * treeinfo, pll_utree_t * tree);
+/* ADDITIVE (BASELINE.json north_star): traversal + P-matrix refresh + CLV update, no logL
+ * evaluation and no host synchronisation; the work that treeinfo.c:973-1041 does inline. */
+int pllmod_treeinfo_update_partials(pllmod_treeinfo_t * treeinfo, int incremental);
+
+/* ---- pll-modules optimize subset (O:60-62,71-76,88-102,158-187,194-354) --------------------- */
+#define PLLMOD_OPT_DEFAULT_BRANCH_LEN 0.1
+#define PLLMOD_OPT_MIN_BRANCH_LEN 1.0e-4
+#define PLLMOD_OPT_MAX_BRANCH_LEN 100.
+#define PLLMOD_OPT_TOL_BRANCH_LEN 1.0e-4
+#define PLLMOD_OPT_BLO_NEWTON_FAST 0
+#define PLLMOD_OPT_BLO_NEWTON_SAFE 1
+#define PLLMOD_OPT_BLO_NEWTON_FALLBACK 2
+#define PLLMOD_OPT_BLO_NEWTON_GLOBAL 3
+#define PLLMOD_OPT_BLO_NEWTON_OLDFAST 10
+#define PLLMOD_OPT_BLO_NEWTON_OLDSAFE 11
+#define PLLMOD_OPT_ERROR_NEWTON_DERIV 2210
+#define PLLMOD_OPT_ERROR_NEWTON_LIMIT 2220
+#define PLLMOD_OPT_ERROR_NEWTON_UNKNOWN 2230
+#define PLLMOD_OPT_ERROR_NEWTON_WORSE_LK 2240
+#define PLLMOD_OPT_ERROR_NEWTON_BAD_RADIUS 2250
+#define PLLMOD_OPT_BRLEN_OPTIMIZE_ALL -1
+
+/* O:158-169 */
+typedef struct
+{
+  pll_partition_t * partition;
+  pll_unode_t * tree;
+  const unsigned int * params_indices;
+  double * sumtable;
+  double branch_length_min;
+  double branch_length_max;
+  double tolerance;
+  int max_newton_iters;
+  int opt_method;
+} pll_newton_tree_params_t;
+
+/* O:171-193 */
+typedef struct
+{
+  pll_unode_t * tree;
+  unsigned int partition_count;
+  pll_partition_t ** partitions;
+  unsigned int ** params_indices;
+  double ** precomp_buffers;
+  double ** brlen_buffers;
+  double * brlen_orig;
+  double * brlen_guess;
+  int * converged;
+  double * brlen_scalers;
+  double branch_length_min;
+  double branch_length_max;
+  double tolerance;
+  int max_newton_iters;
+  int opt_method;
+  int brlen_linkage;
+  void * parallel_context;
+  void (*parallel_reduce_cb)(void *, double *, size_t, int);
+} pll_newton_tree_params_multi_t;
+
+/* O:198-207 (opt_algorithms.c:133) */
+int pllmod_opt_minimize_newton_multi(unsigned int xnum, double xmin, double * xguess, double xmax,
+                                     double tolerance, unsigned int max_iters, int * converged,
+                                     void * params,
+                                     void (*deriv_func)(void *, double *, double *, double *));
+/* O:210-218 (opt_algorithms.c:86) */
+double pllmod_opt_minimize_newton(double xmin, double xguess, double xmax, double tolerance,
+                                  unsigned int max_iters, void * params,
+                                  void (*deriv_func)(void *, double, double *, double *));
+/* O:221-229 (opt_algorithms.c:281) */
+double pllmod_opt_minimize_newton_old(double x1, double xguess, double x2, double tolerance,
+                                      unsigned int max_iters, void * params,
+                                      void (*deriv_func)(void *, double, double *, double *));
+/* O:283-291 (pll_optimize.c:1115) */
+double pllmod_opt_optimize_branch_lengths_iterative(pll_partition_t * partition, pll_unode_t * tree,
+                                                    const unsigned int * params_indices,
+                                                    double branch_length_min,
+                                                    double branch_length_max, double tolerance,
+                                                    int smoothings, int keep_update);
+/* O:293-302 (pll_optimize.c:961) */
+double pllmod_opt_optimize_branch_lengths_local(pll_partition_t * partition, pll_unode_t * tree,
+                                                const unsigned int * params_indices,
+                                                double branch_length_min, double branch_length_max,
+                                                double tolerance, int smoothings, int radius,
+                                                int keep_update);
+/* O:304-322 (pll_optimize.c:1739) */
+double pllmod_opt_optimize_branch_lengths_local_multi(
+    pll_partition_t ** partitions, size_t partition_count, pll_unode_t * tree,
+    unsigned int ** params_indices, double ** sumtable_buffers, double ** brlen_buffers,
+    double * brlen_scalers, double branch_length_min, double branch_length_max,
+    double lh_epsilon, int max_iters, int radius, int keep_update, int opt_method,
+    int brlen_linkage, void * parallel_context,
+    void (*parallel_reduce_cb)(void *, double *, size_t, int));
+/* pll_optimize.c:1182 */
+double pllmod_opt_compute_edge_loglikelihood_multi(
+    pll_partition_t ** partitions, size_t partition_count, unsigned int parent_clv_index,
+    int parent_scaler_index, unsigned int child_clv_index, int child_scaler_index,
+    unsigned int matrix_index, unsigned int ** const params_indices, double * persite_lnl,
+    void * parallel_context, void (*parallel_reduce_cb)(void *, double *, size_t, int));
+
+/* ---- additive device-side API (pllb200_*) ------------------------------------------------- */
+
+/* Number of usable CUDA devices (0 when the driver/GPU is absent). Never fails. */
+int pllb200_device_count(void);
+/* Device that subsequently created partitions of THIS THREAD live on (default: current device). */
+int pllb200_set_device(int device);
+/* Library build info string: "pllb200 <version> sm_100a". */
+const char * pllb200_version(void);
+
+/* Blocking copies of device-resident buffers back to host memory (sizes in elements as laid out by
+ * the reference: clv = sites_alloc*rate_cats*states_padded doubles, scaler = sites_alloc (or
+ * sites_alloc*rate_cats with PLL_ATTRIB_RATE_SCALERS) unsigned ints, pmatrix =
+ * rate_cats*states*states_padded doubles). Return PLL_SUCCESS / PLL_FAILURE. */
+int pllb200_download_clv(pll_partition_t * partition, unsigned int clv_index, double * dst);
+int pllb200_upload_clv(pll_partition_t * partition, unsigned int clv_index, const double * src);
+int pllb200_download_scaler(pll_partition_t * partition, unsigned int scaler_index, unsigned int * dst);
+int pllb200_download_pmatrix(pll_partition_t * partition, unsigned int matrix_index, double * dst);
+int pllb200_download_sumtable(pll_partition_t * partition, const double * sumtable_key, double * dst);
+/* Re-mirror host arrays a caller modified in place (pattern_weights / invariant / tipchars). */
+int pllb200_sync_host_arrays(pll_partition_t * partition);
+/* Wait for all queued device work of the partition. */
+int pllb200_partition_synchronize(pll_partition_t * partition);
+/* Run the partition's kernels on a caller-provided CUDA stream (cudaStream_t passed as void*),
+ * e.g. torch.cuda.current_stream().cuda_stream.  NULL restores the partition's own stream. */
+int pllb200_partition_set_stream(pll_partition_t * partition, void * cuda_stream);
+
+/* Asynchronous log-likelihood: queues traversal-independent edge logL evaluation; the value is
+ * delivered to *result (host memory owned by the caller) by pllb200_partition_synchronize or any
+ * later blocking call on the partition. */
+int pllb200_edge_loglikelihood_async(pll_partition_t * partition,
+                                     unsigned int parent_clv_index, int parent_scaler_index,
+                                     unsigned int child_clv_index, int child_scaler_index,
+                                     unsigned int matrix_index,
+                                     const unsigned int * freqs_indices, double * result);
+/* Device address (as integer) of the partition's most recent reduction results
+ * {logL, d_f, dd_f}: lets a caller run an NCCL all-reduce on them without a host round trip. */
+uint64_t pllb200_result_device_ptr(pll_partition_t * partition);
+
+/* Kernel tuning knobs and counters (per process). */
+typedef struct
+{
+  unsigned long long kernel_launches;   /* kernels launched by this library so far */
+  unsigned long long h2d_bytes;         /* bytes staged host->device */
+  unsigned long long d2h_bytes;         /* bytes copied device->host */
+} pllb200_stats_t;
+void pllb200_get_stats(pllb200_stats_t * out);
+void pllb200_reset_stats(void);
+/* name in {"trav_ctas_per_sm","trav_reorder","fuse_root"}; returns previous value, -1 if unknown */
+int pllb200_set_option(const char * name, int value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PLLB200_H_ */

@@ -1,0 +1,584 @@
+/*
+ * harness.c — TEST INFRASTRUCTURE.  One source, two builds:
+ *   oracle/_ref/libharness_ref.so            gcc -DHARNESS_REFERENCE against the reference headers
+ *                                            + oracle/_ref/libpll_ref.so (the unmodified reference)
+ *   pll-modules_b200/lib/libharness_b200.so  against include/ + libpll_b200.so (the product)
+ * It only uses the public C API both libraries share (pll_partition_*, pll_update_*,
+ * pll_compute_*, pllmod_treeinfo_*, pllmod_opt_*), so every parity test drives the reference and
+ * the product through literally the same caller code — the way the reference's own tests
+ * (test/src/optimize/blopt-minimal.c, libs/libpll/test/src/derivatives.c) drive libpll.
+ * The only #ifdef is how a CLV / scaler / P-matrix is read back (host memory vs device download).
+ *
+ * Synthetic inputs follow SURVEY.md §8d: random-insertion topology, Exp(mean) branch lengths
+ * clipped to [1e-4, 1] * scale, iid alignment with 5 % gaps from a counter-based hash (so any site
+ * slice of the same alignment can be generated independently: multi-GPU site sharding).
+ */
+#include "pll.h"
+#include "pll_tree.h"
+#include "pll_optimize.h"
+
+#include <math.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#include <time.h>
+
+typedef struct
+{
+  unsigned int tips;
+  unsigned int nparts;
+  pll_utree_t * tree;
+  pllmod_treeinfo_t * ti;
+  pll_partition_t ** parts;
+  unsigned int ** param_idx;
+  unsigned int * site_begin; /* slice of the global alignment this handle owns */
+  unsigned int * sites;      /* local sites per partition */
+  double ** sumtables;
+  int brlen_linkage;
+} harness_t;
+
+/* ---- deterministic generators -------------------------------------------------------------- */
+
+static unsigned long long xs64(unsigned long long * s)
+{
+  unsigned long long x = *s;
+  x ^= x << 13;
+  x ^= x >> 7;
+  x ^= x << 17;
+  return *s = x;
+}
+static double u01(unsigned long long * s) { return (double)(xs64(s) >> 11) / 9007199254740992.0; }
+
+static unsigned long long mix64(unsigned long long z)
+{
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+
+static const char * ALPHABET_NT = "ACGT";
+static const char * ALPHABET_AA = "ARNDCQEGHILKMFPSTWYV";
+
+/* character of (partition, tip, global site): 5 % gap, else uniform over the states */
+static char cell_char(unsigned long long seed, unsigned int part, unsigned int tip,
+                      unsigned long long site, unsigned int states)
+{
+  const unsigned long long h =
+      mix64(seed ^ mix64(((unsigned long long)part << 48) ^ ((unsigned long long)tip << 32) ^ site));
+  const unsigned int r = (unsigned int)(h % 10000u);
+  if (r < 500u) return '-';
+  const unsigned int st = (unsigned int)((h >> 20) % states);
+  if (states == 4) return ALPHABET_NT[st];
+  if (states == 20) return ALPHABET_AA[st];
+  return (char)('0' + st); /* generic alphabets use a custom map built in make_partition */
+}
+
+static pll_unode_t * new_tip(unsigned int idx)
+{
+  pll_unode_t * t = (pll_unode_t *)calloc(1, sizeof(pll_unode_t));
+  t->clv_index = t->node_index = t->pmatrix_index = idx;
+  t->scaler_index = PLL_SCALE_BUFFER_NONE;
+  return t;
+}
+
+static pll_unode_t * new_inner(unsigned int clv, int scaler, unsigned int * node_id)
+{
+  pll_unode_t * n[3];
+  for (int i = 0; i < 3; ++i)
+  {
+    n[i] = (pll_unode_t *)calloc(1, sizeof(pll_unode_t));
+    n[i]->clv_index = clv;
+    n[i]->scaler_index = scaler;
+    n[i]->node_index = (*node_id)++;
+  }
+  n[0]->next = n[1];
+  n[1]->next = n[2];
+  n[2]->next = n[0];
+  return n[0];
+}
+
+static void join(pll_unode_t * a, pll_unode_t * b, double len, unsigned int pm)
+{
+  a->back = b;
+  b->back = a;
+  a->length = b->length = len;
+  a->pmatrix_index = b->pmatrix_index = pm;
+}
+
+/* random-insertion topology; branch e of the growing tree is remembered by one of its ends */
+static pll_unode_t * build_tree(unsigned int tips, unsigned long long seed, double brlen_mean,
+                                double brlen_scale)
+{
+  unsigned long long s = seed ? seed : 88172645463325252ull;
+  unsigned int node_id = tips;
+  pll_unode_t ** ends = (pll_unode_t **)malloc(sizeof(pll_unode_t *) * (2 * tips - 3));
+  unsigned int nb = 0;
+  pll_unode_t * c0 = new_inner(tips, 0, &node_id);
+  pll_unode_t * t0 = new_tip(0), *t1 = new_tip(1), *t2 = new_tip(2);
+  join(t0, c0, 0.1, 0);
+  join(t1, c0->next, 0.1, 1);
+  join(t2, c0->next->next, 0.1, 2);
+  ends[nb++] = t0;
+  ends[nb++] = t1;
+  ends[nb++] = t2;
+  for (unsigned int t = 3; t < tips; ++t)
+  {
+    pll_unode_t * in = new_inner(tips + t - 2, (int)(t - 2), &node_id);
+    pll_unode_t * tip = new_tip(t);
+    pll_unode_t * e = ends[xs64(&s) % nb];
+    pll_unode_t * eb = e->back;
+    const unsigned int pm = e->pmatrix_index;
+    join(e, in, 0.1, pm);
+    join(eb, in->next, 0.1, nb);
+    join(tip, in->next->next, 0.1, nb + 1);
+    ends[nb++] = in->next;
+    ends[nb++] = tip;
+  }
+  for (unsigned int i = 0; i < nb; ++i)
+  {
+    double l = -brlen_mean * log(1.0 - u01(&s));
+    if (l < 1e-4) l = 1e-4;
+    if (l > 1.0) l = 1.0;
+    l *= brlen_scale;
+    ends[i]->length = ends[i]->back->length = l;
+  }
+  free(ends);
+  return c0;
+}
+
+/* ---- construction -------------------------------------------------------------------------- */
+
+static pll_partition_t * make_partition(unsigned int part, unsigned int tips, unsigned int states,
+                                        unsigned int site_begin, unsigned int sites,
+                                        unsigned int rate_cats, unsigned int attributes,
+                                        unsigned long long seed, double alpha, double pinv,
+                                        const double * subst, const double * freqs)
+{
+  pll_partition_t * p = pll_partition_create(tips, tips - 2, states, sites, 1, 2 * tips - 3,
+                                             rate_cats, tips - 2, attributes);
+  if (!p) return NULL;
+  double rates[64];
+  if (!pll_compute_gamma_cats(alpha, rate_cats, rates, PLL_GAMMA_RATES_MEAN)) return NULL;
+  pll_set_category_rates(p, rates);
+  pll_set_frequencies(p, 0, freqs);
+  pll_set_subst_params(p, 0, subst);
+
+  pll_state_t gmap[256];
+  const pll_state_t * map = states == 4 ? pll_map_nt : (states == 20 ? pll_map_aa : gmap);
+  if (map == gmap)
+  {
+    memset(gmap, 0, sizeof(gmap));
+    for (unsigned int i = 0; i < states; ++i) gmap['0' + i] = 1ull << i;
+    gmap['-'] = (states >= 64) ? ~0ull : ((1ull << states) - 1);
+  }
+  char * seq = (char *)malloc((size_t)sites + 1);
+  for (unsigned int t = 0; t < tips; ++t)
+  {
+    for (unsigned int i = 0; i < sites; ++i)
+      seq[i] = cell_char(seed, part, t, (unsigned long long)site_begin + i, states);
+    seq[sites] = 0;
+    if (!pll_set_tip_states(p, t, map, seq))
+    {
+      free(seq);
+      return NULL;
+    }
+  }
+  free(seq);
+  if (pinv > 0.0)
+    if (!pll_update_invariant_sites_proportion(p, 0, pinv)) return NULL;
+  return p;
+}
+
+/* Create tree + nparts partitions + treeinfo.
+ * states[p], sites_total[p] describe the GLOBAL alignment; this handle owns the site slice
+ * [floor(rank*S/nranks), floor((rank+1)*S/nranks)) of every partition.
+ * subst/freqs: concatenated per partition (states*(states-1)/2 and states doubles). */
+void * h_create(unsigned int tips, unsigned int nparts, const unsigned int * states,
+                const unsigned int * sites_total, unsigned int rate_cats, unsigned int attributes,
+                unsigned long long seed, double brlen_mean, double brlen_scale,
+                const double * alphas, const double * pinvs, const double * subst,
+                const double * freqs, int brlen_linkage, unsigned int rank, unsigned int nranks)
+{
+  harness_t * h = (harness_t *)calloc(1, sizeof(harness_t));
+  h->tips = tips;
+  h->nparts = nparts;
+  h->brlen_linkage = brlen_linkage;
+  h->parts = (pll_partition_t **)calloc(nparts, sizeof(pll_partition_t *));
+  h->param_idx = (unsigned int **)calloc(nparts, sizeof(unsigned int *));
+  h->site_begin = (unsigned int *)calloc(nparts, sizeof(unsigned int));
+  h->sites = (unsigned int *)calloc(nparts, sizeof(unsigned int));
+  h->sumtables = (double **)calloc(nparts, sizeof(double *));
+  pll_unode_t * root = build_tree(tips, seed, brlen_mean, brlen_scale);
+  h->ti = pllmod_treeinfo_create(root, tips, nparts, brlen_linkage);
+  if (!h->ti)
+  {
+    fprintf(stderr, "harness: treeinfo_create failed: %s\n", pll_errmsg);
+    return NULL;
+  }
+  h->tree = h->ti->tree;
+  for (unsigned int p = 0; p < nparts; ++p)
+  {
+    const unsigned long long S = sites_total[p];
+    const unsigned int b = (unsigned int)(S * rank / nranks), e = (unsigned int)(S * (rank + 1) / nranks);
+    h->site_begin[p] = b;
+    h->sites[p] = e - b;
+    h->parts[p] = make_partition(p, tips, states[p], b, e - b, rate_cats, attributes, seed,
+                                 alphas[p], pinvs ? pinvs[p] : 0.0, subst, freqs);
+    if (!h->parts[p])
+    {
+      fprintf(stderr, "harness: partition %u failed: %s\n", p, pll_errmsg);
+      return NULL;
+    }
+    subst += states[p] * (states[p] - 1) / 2;
+    freqs += states[p];
+    h->param_idx[p] = (unsigned int *)calloc(rate_cats, sizeof(unsigned int));
+    if (!pllmod_treeinfo_init_partition(h->ti, p, h->parts[p], 0, PLL_GAMMA_RATES_MEAN, alphas[p],
+                                        h->param_idx[p], NULL))
+    {
+      fprintf(stderr, "harness: init_partition failed: %s\n", pll_errmsg);
+      return NULL;
+    }
+    h->sumtables[p] = h->ti->deriv_precomp[p];
+  }
+  return h;
+}
+
+void h_destroy(void * hv)
+{
+  harness_t * h = (harness_t *)hv;
+  if (!h) return;
+  pll_utree_t * tree = h->ti->tree;
+  /* treeinfo frees its wrapper but not the nodes: collect them first */
+  const unsigned int n = tree->tip_count + tree->inner_count;
+  pll_unode_t ** nodes = (pll_unode_t **)malloc(sizeof(pll_unode_t *) * n);
+  memcpy(nodes, tree->nodes, sizeof(pll_unode_t *) * n);
+  const unsigned int tipc = tree->tip_count;
+  for (unsigned int p = 0; p < h->nparts; ++p) pll_partition_destroy(h->parts[p]);
+  pllmod_treeinfo_destroy(h->ti);
+  for (unsigned int i = 0; i < n; ++i)
+  {
+    if (i < tipc)
+      free(nodes[i]);
+    else
+    {
+      pll_unode_t * a = nodes[i], *b = a->next, *c = b->next;
+      free(a);
+      free(b);
+      free(c);
+    }
+  }
+  free(nodes);
+  for (unsigned int p = 0; p < h->nparts; ++p) free(h->param_idx[p]);
+  free(h->parts);
+  free(h->param_idx);
+  free(h->site_begin);
+  free(h->sites);
+  free(h->sumtables);
+  free(h);
+}
+
+/* ---- accessors ----------------------------------------------------------------------------- */
+
+unsigned int h_local_sites(void * hv, unsigned int p) { return ((harness_t *)hv)->sites[p]; }
+unsigned int h_states_padded(void * hv, unsigned int p) { return ((harness_t *)hv)->parts[p]->states_padded; }
+void * h_partition(void * hv, unsigned int p) { return ((harness_t *)hv)->parts[p]; }
+void * h_treeinfo(void * hv) { return ((harness_t *)hv)->ti; }
+int h_errno(void) { return pll_errno; }
+const char * h_errmsg(void) { return pll_errmsg; }
+
+void h_set_reduce_cb(void * hv, void * ctx, void (*cb)(void *, double *, size_t, int))
+{
+  pllmod_treeinfo_set_parallel_context(((harness_t *)hv)->ti, ctx, cb);
+}
+
+/* out: sites * rate_cats * states (UNPADDED, so the two libraries compare independent of padding) */
+int h_get_clv(void * hv, unsigned int p, unsigned int clv_index, double * out)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_partition_t * part = h->parts[p];
+  const unsigned int sp = part->states_padded, s = part->states, K = part->rate_cats;
+  const size_t n = (size_t)part->sites * K;
+  double * buf;
+#ifdef HARNESS_REFERENCE
+  buf = part->clv[clv_index];
+  if (!buf) return 0;
+#else
+  buf = (double *)malloc(sizeof(double) * ((size_t)part->sites + part->asc_additional_sites) * K * sp);
+  if (!pllb200_download_clv(part, clv_index, buf))
+  {
+    free(buf);
+    return 0;
+  }
+#endif
+  for (size_t e = 0; e < n; ++e) memcpy(out + e * s, buf + e * sp, sizeof(double) * s);
+#ifndef HARNESS_REFERENCE
+  free(buf);
+#endif
+  return 1;
+}
+
+int h_get_scaler(void * hv, unsigned int p, unsigned int scaler_index, unsigned int * out)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_partition_t * part = h->parts[p];
+  const size_t n = (size_t)part->sites * ((part->attributes & PLL_ATTRIB_RATE_SCALERS) ? part->rate_cats : 1);
+#ifdef HARNESS_REFERENCE
+  memcpy(out, part->scale_buffer[scaler_index], sizeof(unsigned int) * n);
+  return 1;
+#else
+  const size_t na = ((size_t)part->sites + part->asc_additional_sites) *
+                    ((part->attributes & PLL_ATTRIB_RATE_SCALERS) ? part->rate_cats : 1);
+  unsigned int * buf = (unsigned int *)malloc(sizeof(unsigned int) * na);
+  const int rc = pllb200_download_scaler(part, scaler_index, buf);
+  if (rc) memcpy(out, buf, sizeof(unsigned int) * n);
+  free(buf);
+  return rc;
+#endif
+}
+
+/* out: rate_cats * states * states (unpadded) */
+int h_get_pmatrix(void * hv, unsigned int p, unsigned int matrix_index, double * out)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_partition_t * part = h->parts[p];
+  const unsigned int sp = part->states_padded, s = part->states, K = part->rate_cats;
+  double * buf;
+#ifdef HARNESS_REFERENCE
+  buf = part->pmatrix[matrix_index];
+#else
+  buf = (double *)malloc(sizeof(double) * K * s * sp);
+  if (!pllb200_download_pmatrix(part, matrix_index, buf))
+  {
+    free(buf);
+    return 0;
+  }
+#endif
+  for (unsigned int r = 0; r < K * s; ++r) memcpy(out + (size_t)r * s, buf + (size_t)r * sp, sizeof(double) * s);
+#ifndef HARNESS_REFERENCE
+  free(buf);
+#endif
+  return 1;
+}
+
+void h_get_rates(void * hv, unsigned int p, double * out)
+{
+  pll_partition_t * part = ((harness_t *)hv)->parts[p];
+  memcpy(out, part->rates, sizeof(double) * part->rate_cats);
+}
+
+/* branch lengths by pmatrix index (2*tips-3 doubles) */
+void h_get_branch_lengths(void * hv, double * out)
+{
+  harness_t * h = (harness_t *)hv;
+  for (unsigned int i = 0; i < h->ti->subnode_count; ++i)
+    out[h->ti->subnodes[i]->pmatrix_index] = h->ti->subnodes[i]->length;
+}
+
+void h_set_branch_lengths(void * hv, const double * in)
+{
+  harness_t * h = (harness_t *)hv;
+  for (unsigned int i = 0; i < h->ti->subnode_count; ++i)
+    h->ti->subnodes[i]->length = in[h->ti->subnodes[i]->pmatrix_index];
+  pllmod_treeinfo_invalidate_all(h->ti);
+}
+
+unsigned int h_root_node_index(void * hv) { return ((harness_t *)hv)->ti->root->node_index; }
+int h_set_root(void * hv, unsigned int node_index)
+{
+  harness_t * h = (harness_t *)hv;
+  return pllmod_treeinfo_set_root(h->ti, h->ti->subnodes[node_index]);
+}
+/* describe subnode i: {clv_index, scaler_index, pmatrix_index, back node_index, is_tip} */
+void h_node_info(void * hv, unsigned int node_index, int * out)
+{
+  pll_unode_t * n = ((harness_t *)hv)->ti->subnodes[node_index];
+  out[0] = (int)n->clv_index;
+  out[1] = n->scaler_index;
+  out[2] = (int)n->pmatrix_index;
+  out[3] = (int)n->back->node_index;
+  out[4] = n->next == NULL;
+}
+
+/* ---- the hot path ---------------------------------------------------------------------------- */
+
+double h_compute_loglh(void * hv, int incremental)
+{
+  return pllmod_treeinfo_compute_loglh(((harness_t *)hv)->ti, incremental);
+}
+
+void h_partition_loglh(void * hv, double * out)
+{
+  harness_t * h = (harness_t *)hv;
+  memcpy(out, h->ti->partition_loglh, sizeof(double) * h->nparts);
+}
+
+double h_compute_loglh_persite(void * hv, double * persite_p0)
+{
+  harness_t * h = (harness_t *)hv;
+  double ** ps = (double **)calloc(h->nparts, sizeof(double *));
+  ps[0] = persite_p0;
+  const double r = pllmod_treeinfo_compute_loglh_persite(h->ti, 0, ps);
+  free(ps);
+  return r;
+}
+
+/* only the CLV updates of a full/partial traversal (what BASELINE's "CLV site-updates/s" times):
+ * the op list is built once, then pll_update_partials is called reps times. Returns seconds/rep. */
+double h_time_update_partials(void * hv, int reps)
+{
+  harness_t * h = (harness_t *)hv;
+  pllmod_treeinfo_t * ti = h->ti;
+  (void)pllmod_treeinfo_compute_loglh(ti, 0); /* P-matrices + op list in ti->operations */
+  const unsigned int ops = ti->tip_count - 2;
+  struct timespec t0, t1;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  for (int r = 0; r < reps; ++r)
+    for (unsigned int p = 0; p < h->nparts; ++p) pll_update_partials(h->parts[p], ti->operations, ops);
+#ifndef HARNESS_REFERENCE
+  for (unsigned int p = 0; p < h->nparts; ++p) pllb200_partition_synchronize(h->parts[p]);
+#endif
+  clock_gettime(CLOCK_MONOTONIC, &t1);
+  return ((t1.tv_sec - t0.tv_sec) + 1e-9 * (t1.tv_nsec - t0.tv_nsec)) / reps;
+}
+
+/* queue ONE full-traversal CLV update per partition without waiting (device timing is done by the
+ * caller with CUDA events on the partition stream) */
+void h_queue_update_partials(void * hv)
+{
+  harness_t * h = (harness_t *)hv;
+  const unsigned int ops = h->ti->tip_count - 2;
+  for (unsigned int p = 0; p < h->nparts; ++p) pll_update_partials(h->parts[p], h->ti->operations, ops);
+}
+
+int h_update_partials_only(void * hv, int incremental)
+{
+#ifdef HARNESS_REFERENCE
+  (void)hv;
+  (void)incremental;
+  return 0; /* additive symbol, absent from the reference */
+#else
+  return pllmod_treeinfo_update_partials(((harness_t *)hv)->ti, incremental);
+#endif
+}
+
+double h_edge_loglh(void * hv, unsigned int p, unsigned int node_index)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_unode_t * n = h->ti->subnodes[node_index];
+  return pll_compute_edge_loglikelihood(h->parts[p], n->clv_index, n->scaler_index,
+                                        n->back->clv_index, n->back->scaler_index,
+                                        n->pmatrix_index, h->param_idx[p], NULL);
+}
+
+double h_root_loglh(void * hv, unsigned int p, unsigned int node_index)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_unode_t * n = h->ti->subnodes[node_index];
+  return pll_compute_root_loglikelihood(h->parts[p], n->clv_index, n->scaler_index,
+                                        h->param_idx[p], NULL);
+}
+
+/* sumtable on the edge at subnode `node_index` (CLVs must be oriented towards it, e.g. the root
+ * edge after h_compute_loglh), then derivatives at each of the n branch lengths */
+int h_derivatives(void * hv, unsigned int p, unsigned int node_index, const double * brlens, int n,
+                  double * df, double * ddf)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_unode_t * e = h->ti->subnodes[node_index];
+  if (!pll_update_sumtable(h->parts[p], e->clv_index, e->back->clv_index, e->scaler_index,
+                           e->back->scaler_index, h->param_idx[p], h->sumtables[p]))
+    return 0;
+  for (int i = 0; i < n; ++i)
+    if (!pll_compute_likelihood_derivatives(h->parts[p], e->scaler_index, e->back->scaler_index,
+                                            brlens[i], h->param_idx[p], h->sumtables[p], &df[i], &ddf[i]))
+      return 0;
+  return 1;
+}
+
+/* out: sites*rate_cats*states (unpadded) */
+int h_get_sumtable(void * hv, unsigned int p, double * out)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_partition_t * part = h->parts[p];
+  const unsigned int sp = part->states_padded, s = part->states, K = part->rate_cats;
+  const size_t n = (size_t)part->sites * K;
+#ifdef HARNESS_REFERENCE
+  const double * buf = h->sumtables[p];
+#else
+  double * buf = (double *)malloc(sizeof(double) * ((size_t)part->sites + part->asc_additional_sites) * K * sp);
+  if (!pllb200_download_sumtable(part, h->sumtables[p], buf))
+  {
+    free(buf);
+    return 0;
+  }
+#endif
+  for (size_t e = 0; e < n; ++e) memcpy(out + e * s, buf + e * sp, sizeof(double) * s);
+#ifndef HARNESS_REFERENCE
+  free((void *)buf);
+#endif
+  return 1;
+}
+
+/* Newton-Raphson branch-length optimisation around the current root (all branches if radius -1) */
+double h_optimize_branch_lengths(void * hv, int method, int radius, int max_iters, double lh_epsilon,
+                                 double brlen_min, double brlen_max)
+{
+  harness_t * h = (harness_t *)hv;
+  pllmod_treeinfo_t * ti = h->ti;
+  return pllmod_opt_optimize_branch_lengths_local_multi(
+      ti->partitions, ti->partition_count, ti->root, ti->param_indices, ti->deriv_precomp,
+      ti->branch_lengths, ti->brlen_scalers, brlen_min, brlen_max, lh_epsilon, max_iters, radius, 1,
+      method, ti->brlen_linkage, ti->parallel_context, ti->parallel_reduce_cb);
+}
+
+/* legacy single-partition driver (pllmod_opt_optimize_branch_lengths_local) on partition 0 */
+double h_optimize_branch_lengths_single(void * hv, int radius, int smoothings, double tolerance)
+{
+  harness_t * h = (harness_t *)hv;
+  return pllmod_opt_optimize_branch_lengths_local(h->parts[0], h->ti->root, h->param_idx[0], 0, 0,
+                                                  tolerance, smoothings, radius, 1);
+}
+
+/* change the Gamma shape of partition p (model-parameter optimisers do this between evaluations) */
+int h_set_alpha(void * hv, unsigned int p, double alpha)
+{
+  harness_t * h = (harness_t *)hv;
+  double rates[64];
+  if (!pll_compute_gamma_cats(alpha, h->parts[p]->rate_cats, rates, PLL_GAMMA_RATES_MEAN)) return 0;
+  pll_set_category_rates(h->parts[p], rates);
+  const int old = h->ti->active_partition;
+  pllmod_treeinfo_set_active_partition(h->ti, (int)p);
+  pllmod_treeinfo_invalidate_all(h->ti);
+  pllmod_treeinfo_set_active_partition(h->ti, old);
+  return 1;
+}
+
+int h_gamma_cats(double alpha, unsigned int cats, int mode, double * out)
+{
+  return pll_compute_gamma_cats(alpha, cats, out, mode);
+}
+
+/* invalidate the CLVs/P-matrix around an edge as an SPR regraft evaluation would (algo_search.c:
+ * 753-790), then change its length: exercises small partial traversals */
+void h_perturb_edge(void * hv, unsigned int node_index, double new_length)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_unode_t * e = h->ti->subnodes[node_index];
+  pllmod_treeinfo_set_branch_length(h->ti, e, new_length);
+  pllmod_treeinfo_invalidate_pmatrix(h->ti, e);
+  /* every CLV that "sees" this edge from the root side is stale: walk towards the root is not
+   * needed — the reference's callers invalidate the two end nodes' other orientations */
+  if (e->next)
+  {
+    pllmod_treeinfo_invalidate_clv(h->ti, e->next);
+    pllmod_treeinfo_invalidate_clv(h->ti, e->next->next);
+  }
+  if (e->back->next)
+  {
+    pllmod_treeinfo_invalidate_clv(h->ti, e->back->next);
+    pllmod_treeinfo_invalidate_clv(h->ti, e->back->next->next);
+  }
+}
+
+unsigned int h_ops_counter(void * hv) { return ((harness_t *)hv)->ti->counter; }

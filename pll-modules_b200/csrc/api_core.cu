@@ -1,0 +1,223 @@
+/*
+ * api_core.cu — the six libpll entry points of the hot path, as thin dispatchers onto the kernels.
+ *
+ *   pll_update_prob_matrices            models.c:412      -> k_pmatrix.cu
+ *   pll_update_partials                 partials.c:237    -> k_partials.cu
+ *   pll_compute_edge_loglikelihood      likelihood.c:586  -> k_likelihood.cu
+ *   pll_compute_root_loglikelihood      likelihood.c:122  -> k_likelihood.cu
+ *   pll_update_sumtable                 derivatives.c:239 -> k_derivatives.cu
+ *   pll_compute_likelihood_derivatives  derivatives.c:333 -> k_derivatives.cu
+ *
+ * Calls that return no scalar are queued on the partition's stream and return immediately; calls
+ * that return a scalar wait for the stream and read the value from mapped pinned memory.
+ * Error convention as the reference: PLL_FAILURE / -INFINITY plus pll_errno + pll_errmsg.
+ */
+#include "internal.h"
+
+#include <cmath>
+#include <mutex>
+
+static bool enter(pll_partition_t * p)
+{
+  if (!p || ctx_of(p)->magic != PLLB200_MAGIC)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Not a libpll_b200 partition.");
+    return false;
+  }
+  return pllb200_cuda_ok(cudaSetDevice(ctx_of(p)->device), "cudaSetDevice");
+}
+
+extern "C" int pll_update_prob_matrices(pll_partition_t * partition,
+                                        const unsigned int * params_indices,
+                                        const unsigned int * matrix_indices,
+                                        const double * branch_lengths, unsigned int count)
+{
+  if (!enter(partition)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(partition);
+  if (!count) return PLL_SUCCESS;
+  if (!dev_sync_eigen(c, params_indices)) return PLL_FAILURE;
+  return launch_pmatrix(c, params_indices, matrix_indices, branch_lengths, count) ? PLL_SUCCESS
+                                                                                  : PLL_FAILURE;
+}
+
+extern "C" void pll_update_partials(pll_partition_t * partition,
+                                    const pll_operation_t * operations, unsigned int count)
+{
+  if (!enter(partition)) return;
+  launch_partials(ctx_of(partition), operations, count);
+}
+
+static double * persite_buffer(PartCtx * c)
+{
+  if (!c->d_persite)
+    if (!pllb200_cuda_ok(cudaMalloc(&c->d_persite, sizeof(double) * c->pub.sites), "persite alloc"))
+      return nullptr;
+  return c->d_persite;
+}
+
+static double finish_scalar(PartCtx * c, int slot, double * persite_lnl, double * d_persite)
+{
+  if (persite_lnl)
+  {
+    if (!pllb200_cuda_ok(cudaMemcpyAsync(persite_lnl, d_persite, sizeof(double) * c->pub.sites,
+                                         cudaMemcpyDeviceToHost, c->stream), "persite copy"))
+      return -INFINITY;
+    g_d2h_bytes += sizeof(double) * c->pub.sites;
+  }
+  if (!dev_flush(c)) return -INFINITY;
+  g_d2h_bytes += sizeof(double);
+  return c->h_result[slot * 4];
+}
+
+extern "C" double pll_compute_edge_loglikelihood(pll_partition_t * partition,
+                                                 unsigned int parent_clv_index,
+                                                 int parent_scaler_index,
+                                                 unsigned int child_clv_index,
+                                                 int child_scaler_index,
+                                                 unsigned int matrix_index,
+                                                 const unsigned int * freqs_indices,
+                                                 double * persite_lnl)
+{
+  if (!enter(partition)) return -INFINITY;
+  PartCtx * c = ctx_of(partition);
+  double * d_ps = nullptr;
+  if (persite_lnl && !(d_ps = persite_buffer(c))) return -INFINITY;
+  const int slot = dev_alloc_slot(c);
+  if (!launch_edge_logl(c, parent_clv_index, parent_scaler_index, child_clv_index,
+                        child_scaler_index, matrix_index, freqs_indices, d_ps, slot))
+    return -INFINITY;
+  return finish_scalar(c, slot, persite_lnl, d_ps);
+}
+
+extern "C" int pllb200_edge_loglikelihood_async(pll_partition_t * partition,
+                                                unsigned int parent_clv_index,
+                                                int parent_scaler_index,
+                                                unsigned int child_clv_index,
+                                                int child_scaler_index, unsigned int matrix_index,
+                                                const unsigned int * freqs_indices, double * result)
+{
+  if (!enter(partition)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(partition);
+  const int slot = dev_alloc_slot(c);
+  if (!launch_edge_logl(c, parent_clv_index, parent_scaler_index, child_clv_index,
+                        child_scaler_index, matrix_index, freqs_indices, nullptr, slot))
+    return PLL_FAILURE;
+  c->pending.push_back(PendingResult{result, slot, 0});
+  return PLL_SUCCESS;
+}
+
+extern "C" double pll_compute_root_loglikelihood(pll_partition_t * partition,
+                                                 unsigned int clv_index, int scaler_index,
+                                                 const unsigned int * freqs_indices,
+                                                 double * persite_lnl)
+{
+  if (!enter(partition)) return -INFINITY;
+  PartCtx * c = ctx_of(partition);
+  double * d_ps = nullptr;
+  if (persite_lnl && !(d_ps = persite_buffer(c))) return -INFINITY;
+  const int slot = dev_alloc_slot(c);
+  if (!launch_root_logl(c, clv_index, scaler_index, freqs_indices, d_ps, slot)) return -INFINITY;
+  return finish_scalar(c, slot, persite_lnl, d_ps);
+}
+
+/* device shadow of a caller-owned sumtable buffer.  Keys are also kept in a
+ * process-wide registry so that pll_aligned_free(key) gives the HBM back. */
+static std::mutex g_key_mutex;
+static std::unordered_map<const void *, PartCtx *> g_key_owner;
+
+void sumtable_forget_key(const void * key)
+{
+  std::lock_guard<std::mutex> lock(g_key_mutex);
+  if (g_key_owner.empty()) return;
+  auto it = g_key_owner.find(key);
+  if (it == g_key_owner.end()) return;
+  PartCtx * c = it->second;
+  g_key_owner.erase(it);
+  auto sh = c->sumtables.find(key);
+  if (sh != c->sumtables.end())
+  {
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    cudaFree(sh->second);
+    c->sumtables.erase(sh);
+  }
+}
+
+void sumtable_forget_partition(PartCtx * c)
+{
+  std::lock_guard<std::mutex> lock(g_key_mutex);
+  for (auto & kv : c->sumtables) g_key_owner.erase(kv.first);
+}
+
+static double * sumtable_shadow(PartCtx * c, const double * key, bool create)
+{
+  auto it = c->sumtables.find(key);
+  if (it != c->sumtables.end()) return it->second;
+  if (!create)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID,
+                      "pll_compute_likelihood_derivatives: sumtable was never built.");
+    return nullptr;
+  }
+  double * d = nullptr;
+  if (!pllb200_cuda_ok(cudaMalloc(&d, sizeof(double) * c->clv_stride), "sumtable alloc")) return nullptr;
+  {
+    std::lock_guard<std::mutex> lock(g_key_mutex);
+    auto own = g_key_owner.find(key);
+    if (own != g_key_owner.end() && own->second != c)
+    {
+      /* the same host buffer was used with another partition before: drop that shadow */
+      PartCtx * o = own->second;
+      auto sh = o->sumtables.find(key);
+      if (sh != o->sumtables.end())
+      {
+        cudaStreamSynchronize(o->stream);
+        cudaFree(sh->second);
+        o->sumtables.erase(sh);
+      }
+    }
+    g_key_owner[key] = c;
+  }
+  c->sumtables[key] = d;
+  return d;
+}
+
+extern "C" int pll_update_sumtable(pll_partition_t * partition, unsigned int parent_clv_index,
+                                   unsigned int child_clv_index, int parent_scaler_index,
+                                   int child_scaler_index, const unsigned int * params_indices,
+                                   double * sumtable)
+{
+  if (!enter(partition)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(partition);
+  if (!sumtable)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "NULL sumtable buffer.");
+    return PLL_FAILURE;
+  }
+  double * d = sumtable_shadow(c, sumtable, true);
+  if (!d) return PLL_FAILURE;
+  return launch_sumtable(c, parent_clv_index, child_clv_index, parent_scaler_index,
+                         child_scaler_index, params_indices, d) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pll_compute_likelihood_derivatives(pll_partition_t * partition,
+                                                  int parent_scaler_index, int child_scaler_index,
+                                                  double branch_length,
+                                                  const unsigned int * params_indices,
+                                                  const double * sumtable, double * d_f,
+                                                  double * dd_f)
+{
+  if (!enter(partition)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(partition);
+  double * d = sumtable_shadow(c, sumtable, false);
+  if (!d) return PLL_FAILURE;
+  const int slot = dev_alloc_slot(c);
+  if (!launch_derivatives(c, parent_scaler_index, child_scaler_index, branch_length,
+                          params_indices, d, slot))
+    return PLL_FAILURE;
+  if (!dev_flush(c)) return PLL_FAILURE;
+  g_d2h_bytes += 2 * sizeof(double);
+  *d_f = c->h_result[slot * 4 + 0];
+  *dd_f = c->h_result[slot * 4 + 1];
+  return PLL_SUCCESS;
+}

@@ -1,0 +1,462 @@
+/*
+ * device_ctx.cu — HBM residency for a partition: arenas, stream, staging ring, host->device
+ * mirroring of the small host-visible arrays, result delivery.
+ *
+ * Layout in HBM (one cudaMalloc per arena, sized once at pll_partition_create; nothing is
+ * allocated on the hot path):
+ *   d_clv      [clv buffers][sites_alloc][rate_cats][states_padded] double   site-major, rate
+ *              interleaved, state fastest — the reference's own order (pll.c:546-581) so a
+ *              downloaded CLV is byte-compatible
+ *   d_scaler   [scale_buffers][sites_alloc (x rate_cats)] u32
+ *   d_pmat     [prob_matrices][rate_cats][states][states_padded] double (pll.c:593-617)
+ *   d_pmat_il  4-state only: [prob_matrices][row i][cat k][col j], the shared-memory image the DNA
+ *              traversal kernel stages with one bulk copy per matrix (bank-conflict free)
+ *   d_tipchars [tips][tip_stride] u8, d_weights u32, d_invariant i32, d_eigen model block
+ */
+#include "internal.h"
+
+#include <algorithm>
+
+unsigned long long g_kernel_launches = 0;
+unsigned long long g_h2d_bytes = 0;
+unsigned long long g_d2h_bytes = 0;
+int g_opt_trav_ctas_per_sm = 0; /* 0 = occupancy query */
+int g_opt_trav_reorder = 1;
+int g_opt_fuse_root = 1;
+
+static __thread int t_device = -1;
+
+extern "C" int pllb200_device_count(void)
+{
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess)
+  {
+    cudaGetLastError();
+    return 0;
+  }
+  return n;
+}
+
+extern "C" int pllb200_set_device(int device)
+{
+  int n = pllb200_device_count();
+  if (device < 0 || device >= n)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid device %d (have %d).", device, n);
+    return PLL_FAILURE;
+  }
+  t_device = device;
+  return PLL_SUCCESS;
+}
+
+extern "C" const char * pllb200_version(void) { return "pllb200 0.1 sm_100a"; }
+
+extern "C" void pllb200_get_stats(pllb200_stats_t * out)
+{
+  out->kernel_launches = g_kernel_launches;
+  out->h2d_bytes = g_h2d_bytes;
+  out->d2h_bytes = g_d2h_bytes;
+}
+
+extern "C" void pllb200_reset_stats(void) { g_kernel_launches = g_h2d_bytes = g_d2h_bytes = 0; }
+
+extern "C" int pllb200_set_option(const char * name, int value)
+{
+  int * slot = nullptr;
+  if (!strcmp(name, "trav_ctas_per_sm")) slot = &g_opt_trav_ctas_per_sm;
+  else if (!strcmp(name, "trav_reorder")) slot = &g_opt_trav_reorder;
+  else if (!strcmp(name, "fuse_root")) slot = &g_opt_fuse_root;
+  if (!slot) return -1;
+  int old = *slot;
+  *slot = value;
+  return old;
+}
+
+static size_t round_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+bool dev_ctx_init(PartCtx * c)
+{
+  pll_partition_t * p = &c->pub;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+  {
+    cudaGetLastError();
+    pllb200_set_error(PLLB200_ERROR_DEVICE,
+                      "No usable CUDA device (%s): libpll_b200 has no CPU fallback.",
+                      e == cudaSuccess ? "device count is 0" : cudaGetErrorString(e));
+    return false;
+  }
+  int dev = t_device;
+  if (dev < 0) CUDA_TRY(cudaGetDevice(&dev), false);
+  c->device = dev;
+  CUDA_TRY(cudaSetDevice(dev), false);
+  CUDA_TRY(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, dev), false);
+
+  const unsigned int K = p->rate_cats, s = p->states, sp = p->states_padded;
+  const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
+  const bool rate_scalers = (p->attributes & PLL_ATTRIB_RATE_SCALERS) != 0;
+
+  c->clv_first = pattern_tip ? p->tips : 0;
+  c->clv_elems = (size_t)c->sites_alloc * K * sp;
+  c->clv_stride = round_up(c->clv_elems, 32);           /* 256 B */
+  c->scaler_elems = (size_t)c->sites_alloc * (rate_scalers ? K : 1);
+  c->scaler_stride = round_up(c->scaler_elems, 64);     /* 256 B */
+  c->pmat_elems = (size_t)K * s * sp;
+  c->tip_stride = round_up(c->sites_alloc, 256);
+  c->eigen_stride = (size_t)2 * s * sp + 2 * sp;
+
+  c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr;
+  c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
+  c->d_tipmap = nullptr; c->d_persite = nullptr; c->h_stage = nullptr; c->d_stage = nullptr;
+  c->d_partials = nullptr; c->d_ticket = nullptr; c->d_result = nullptr; c->h_result = nullptr;
+  c->own_stream = nullptr;
+
+  CUDA_TRY(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking), false);
+  c->stream = c->own_stream;
+
+  const unsigned int nclv = p->nodes - c->clv_first;
+  if (nclv)
+  {
+    const size_t bytes = (size_t)nclv * c->clv_stride * sizeof(double);
+    e = cudaMalloc(&c->d_clv, bytes);
+    if (e != cudaSuccess)
+    {
+      cudaGetLastError();
+      pllb200_set_error(PLL_ERROR_MEM_ALLOC, "Unable to allocate %.2f GB of HBM for CLVs (%s).",
+                        bytes / 1e9, cudaGetErrorString(e));
+      dev_ctx_destroy(c);
+      return false;
+    }
+    /* padded state columns must read as 0 forever; inner CLVs are fully overwritten otherwise */
+    if (sp != s || !pattern_tip) CUDA_TRY(cudaMemsetAsync(c->d_clv, 0, bytes, c->stream), false);
+    for (unsigned int i = c->clv_first; i < p->nodes; ++i) p->clv[i] = clv_dev(c, i);
+  }
+  if (p->scale_buffers)
+  {
+    const size_t bytes = (size_t)p->scale_buffers * c->scaler_stride * sizeof(unsigned int);
+    CUDA_TRY(cudaMalloc(&c->d_scaler, bytes), false);
+    CUDA_TRY(cudaMemsetAsync(c->d_scaler, 0, bytes, c->stream), false);
+    for (unsigned int i = 0; i < p->scale_buffers; ++i) p->scale_buffer[i] = scaler_dev(c, (int)i);
+  }
+  if (p->prob_matrices)
+  {
+    const size_t bytes = (size_t)p->prob_matrices * c->pmat_elems * sizeof(double);
+    CUDA_TRY(cudaMalloc(&c->d_pmat, bytes), false);
+    CUDA_TRY(cudaMemsetAsync(c->d_pmat, 0, bytes, c->stream), false);
+    for (unsigned int i = 0; i < p->prob_matrices; ++i) p->pmatrix[i] = c->d_pmat + i * c->pmat_elems;
+    if (s == 4)
+    {
+      CUDA_TRY(cudaMalloc(&c->d_pmat_il, bytes), false);
+      CUDA_TRY(cudaMemsetAsync(c->d_pmat_il, 0, bytes, c->stream), false);
+    }
+  }
+  if (pattern_tip && p->tips)
+  {
+    CUDA_TRY(cudaMalloc(&c->d_tipchars, (size_t)p->tips * c->tip_stride), false);
+    CUDA_TRY(cudaMemsetAsync(c->d_tipchars, s == 4 ? 15 : 0, (size_t)p->tips * c->tip_stride,
+                             c->stream), false);
+    CUDA_TRY(cudaMalloc(&c->d_tipmap, 256 * sizeof(unsigned long long)), false);
+    CUDA_TRY(cudaMemsetAsync(c->d_tipmap, 0, 256 * sizeof(unsigned long long), c->stream), false);
+  }
+  CUDA_TRY(cudaMalloc(&c->d_weights, sizeof(unsigned int) * c->sites_alloc), false);
+  CUDA_TRY(cudaMalloc(&c->d_eigen, sizeof(double) * c->eigen_stride * p->rate_matrices), false);
+  CUDA_TRY(cudaMemsetAsync(c->d_eigen, 0, sizeof(double) * c->eigen_stride * p->rate_matrices,
+                           c->stream), false);
+
+  c->stage_size = 4u << 20;
+  c->stage_head = 0;
+  CUDA_TRY(cudaHostAlloc(&c->h_stage, c->stage_size, cudaHostAllocDefault), false);
+  CUDA_TRY(cudaMalloc(&c->d_stage, c->stage_size), false);
+
+  CUDA_TRY(cudaMalloc(&c->d_partials, sizeof(double) * 4 * PLLB200_MAX_RED_BLOCKS), false);
+  CUDA_TRY(cudaMalloc(&c->d_ticket, sizeof(unsigned int) * 4), false);
+  CUDA_TRY(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned int) * 4, c->stream), false);
+  CUDA_TRY(cudaMalloc(&c->d_result, sizeof(double) * 4 * PLLB200_RESULT_SLOTS), false);
+  CUDA_TRY(cudaMemsetAsync(c->d_result, 0, sizeof(double) * 4 * PLLB200_RESULT_SLOTS, c->stream), false);
+  CUDA_TRY(cudaHostAlloc(&c->h_result, sizeof(double) * 4 * PLLB200_RESULT_SLOTS,
+                         cudaHostAllocMapped), false);
+  CUDA_TRY(cudaHostGetDevicePointer(&c->h_result_dev, c->h_result, 0), false);
+  c->next_slot = 0;
+  CUDA_TRY(cudaStreamSynchronize(c->stream), false);
+  return true;
+}
+
+void dev_ctx_destroy(PartCtx * c)
+{
+  if (c->device >= 0) cudaSetDevice(c->device);
+  if (c->own_stream) cudaStreamSynchronize(c->own_stream);
+  if (c->stream && c->stream != c->own_stream) cudaStreamSynchronize(c->stream);
+  for (auto & kv : c->sumtables) cudaFree(kv.second);
+  c->sumtables.clear();
+  cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il);
+  cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
+  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_stage); cudaFree(c->d_partials);
+  cudaFree(c->d_ticket); cudaFree(c->d_result);
+  if (c->h_stage) cudaFreeHost(c->h_stage);
+  if (c->h_result) cudaFreeHost(c->h_result);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
+  cudaGetLastError();
+  c->d_clv = nullptr;
+  c->own_stream = nullptr;
+}
+
+/* Copy `bytes` of host data into the stream-ordered staging ring and return the device address the
+ * kernels queued after this call may read.  The pinned half is reused lap by lap; a lap boundary
+ * waits for the stream so earlier async copies have consumed their source. */
+void * dev_stage(PartCtx * c, const void * src, size_t bytes)
+{
+  const size_t need = round_up(bytes, 256);
+  if (need > c->stage_size)
+  {
+    /* grow: rare (op lists beyond 128k ops) */
+    if (!pllb200_cuda_ok(cudaStreamSynchronize(c->stream), "stage grow sync")) return nullptr;
+    cudaFreeHost(c->h_stage);
+    cudaFree(c->d_stage);
+    c->stage_size = round_up(need * 2, 1 << 20);
+    if (!pllb200_cuda_ok(cudaHostAlloc(&c->h_stage, c->stage_size, cudaHostAllocDefault), "stage grow") ||
+        !pllb200_cuda_ok(cudaMalloc(&c->d_stage, c->stage_size), "stage grow"))
+      return nullptr;
+    c->stage_head = 0;
+  }
+  if (c->stage_head + need > c->stage_size)
+  {
+    if (!pllb200_cuda_ok(cudaStreamSynchronize(c->stream), "stage lap sync")) return nullptr;
+    c->stage_head = 0;
+  }
+  char * h = c->h_stage + c->stage_head;
+  char * d = c->d_stage + c->stage_head;
+  memcpy(h, src, bytes);
+  if (!pllb200_cuda_ok(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, c->stream), "stage copy"))
+    return nullptr;
+  c->stage_head += need;
+  g_h2d_bytes += bytes;
+  return d;
+}
+
+/* big host arrays: chunk through the staging ring (pageable sources, async-safe) */
+static bool upload_big(PartCtx * c, void * dst, const void * src, size_t bytes)
+{
+  const size_t chunk = c->stage_size / 2;
+  const char * s = (const char *)src;
+  char * d = (char *)dst;
+  while (bytes)
+  {
+    const size_t n = std::min(bytes, chunk);
+    void * st = dev_stage(c, s, n);
+    if (!st) return false;
+    if (!pllb200_cuda_ok(cudaMemcpyAsync(d, st, n, cudaMemcpyDeviceToDevice, c->stream), "upload_big"))
+      return false;
+    s += n; d += n; bytes -= n;
+  }
+  return true;
+}
+
+bool dev_sync_inputs(PartCtx * c)
+{
+  pll_partition_t * p = &c->pub;
+  if (c->any_tip_dirty && c->d_tipchars && p->tipchars)
+  {
+    for (unsigned int t = 0; t < p->tips; ++t)
+      if (c->tip_dirty[t])
+      {
+        if (!upload_big(c, c->d_tipchars + (size_t)t * c->tip_stride, p->tipchars[t], c->sites_alloc))
+          return false;
+        c->tip_dirty[t] = 0;
+      }
+    c->any_tip_dirty = false;
+  }
+  if (c->tipmap_dirty && c->d_tipmap && p->tipmap)
+  {
+    void * st = dev_stage(c, p->tipmap, 256 * sizeof(unsigned long long));
+    if (!st) return false;
+    CUDA_TRY(cudaMemcpyAsync(c->d_tipmap, st, 256 * sizeof(unsigned long long),
+                             cudaMemcpyDeviceToDevice, c->stream), false);
+    c->tipmap_dirty = false;
+  }
+  if (c->weights_dirty)
+  {
+    if (!upload_big(c, c->d_weights, p->pattern_weights, sizeof(unsigned int) * c->sites_alloc))
+      return false;
+    c->weights_dirty = false;
+  }
+  if (c->invariant_dirty && p->invariant)
+  {
+    if (!c->d_invariant) CUDA_TRY(cudaMalloc(&c->d_invariant, sizeof(int) * p->sites), false);
+    if (!upload_big(c, c->d_invariant, p->invariant, sizeof(int) * p->sites)) return false;
+    c->invariant_dirty = false;
+  }
+  return true;
+}
+
+/* Model block of every rate matrix referenced by params_indices: recompute the decomposition if
+ * the caller invalidated it (models.c:421-428) and mirror it when its version moved. */
+bool dev_sync_eigen(PartCtx * c, const unsigned int * params_indices)
+{
+  pll_partition_t * p = &c->pub;
+  const unsigned int s = p->states, sp = p->states_padded;
+  for (unsigned int k = 0; k < p->rate_cats; ++k)
+  {
+    const unsigned int m = params_indices[k];
+    if (m >= p->rate_matrices)
+    {
+      pllb200_set_error(PLL_ERROR_PARAM_INVALID, "params index %u out of range", m);
+      return false;
+    }
+    if (!p->eigen_decomp_valid[m] && !pll_update_eigen(p, m)) return false;
+    if (c->eigen_version_dev[m] == c->eigen_version[m]) continue;
+    std::vector<double> blk(c->eigen_stride, 0.0);
+    memcpy(blk.data(), p->eigenvecs[m], sizeof(double) * s * sp);
+    memcpy(blk.data() + s * sp, p->inv_eigenvecs[m], sizeof(double) * s * sp);
+    memcpy(blk.data() + 2 * s * sp, p->eigenvals[m], sizeof(double) * s);
+    memcpy(blk.data() + 2 * s * sp + sp, p->frequencies[m], sizeof(double) * s);
+    void * st = dev_stage(c, blk.data(), sizeof(double) * c->eigen_stride);
+    if (!st) return false;
+    CUDA_TRY(cudaMemcpyAsync(c->d_eigen + (size_t)m * c->eigen_stride, st,
+                             sizeof(double) * c->eigen_stride, cudaMemcpyDeviceToDevice, c->stream),
+             false);
+    c->eigen_version_dev[m] = c->eigen_version[m];
+  }
+  return true;
+}
+
+int dev_alloc_slot(PartCtx * c)
+{
+  /* all slots in flight -> drain */
+  if (c->pending.size() >= PLLB200_RESULT_SLOTS - 2) dev_flush(c);
+  int s = c->next_slot;
+  c->next_slot = (c->next_slot + 1) % PLLB200_RESULT_SLOTS;
+  return s;
+}
+
+bool dev_flush(PartCtx * c)
+{
+  CUDA_TRY(cudaStreamSynchronize(c->stream), false);
+  for (const PendingResult & r : c->pending) *r.host_dst = c->h_result[r.slot * 4 + r.comp];
+  c->pending.clear();
+  return true;
+}
+
+/* ---- additive C ABI: transfers, stream control ------------------------------------------- */
+
+static bool check_ctx(pll_partition_t * p)
+{
+  if (!p || ctx_of(p)->magic != PLLB200_MAGIC)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Not a libpll_b200 partition.");
+    return false;
+  }
+  cudaSetDevice(ctx_of(p)->device);
+  return true;
+}
+
+extern "C" int pllb200_download_clv(pll_partition_t * p, unsigned int clv_index, double * dst)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (clv_index >= p->nodes || clv_index < c->clv_first)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "CLV %u has no device buffer.", clv_index);
+    return PLL_FAILURE;
+  }
+  CUDA_TRY(cudaMemcpyAsync(dst, clv_dev(c, clv_index), sizeof(double) * c->clv_elems,
+                           cudaMemcpyDeviceToHost, c->stream), PLL_FAILURE);
+  g_d2h_bytes += sizeof(double) * c->clv_elems;
+  return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_upload_clv(pll_partition_t * p, unsigned int clv_index, const double * src)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (clv_index >= p->nodes || clv_index < c->clv_first)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "CLV %u has no device buffer.", clv_index);
+    return PLL_FAILURE;
+  }
+  return upload_big(c, clv_dev(c, clv_index), src, sizeof(double) * c->clv_elems) ? PLL_SUCCESS
+                                                                                  : PLL_FAILURE;
+}
+
+extern "C" int pllb200_download_scaler(pll_partition_t * p, unsigned int scaler_index,
+                                       unsigned int * dst)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (scaler_index >= p->scale_buffers)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid scaler index %u.", scaler_index);
+    return PLL_FAILURE;
+  }
+  CUDA_TRY(cudaMemcpyAsync(dst, scaler_dev(c, (int)scaler_index),
+                           sizeof(unsigned int) * c->scaler_elems, cudaMemcpyDeviceToHost,
+                           c->stream), PLL_FAILURE);
+  g_d2h_bytes += sizeof(unsigned int) * c->scaler_elems;
+  return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_download_pmatrix(pll_partition_t * p, unsigned int matrix_index, double * dst)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (matrix_index >= p->prob_matrices)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid matrix index %u.", matrix_index);
+    return PLL_FAILURE;
+  }
+  CUDA_TRY(cudaMemcpyAsync(dst, c->d_pmat + (size_t)matrix_index * c->pmat_elems,
+                           sizeof(double) * c->pmat_elems, cudaMemcpyDeviceToHost, c->stream),
+           PLL_FAILURE);
+  g_d2h_bytes += sizeof(double) * c->pmat_elems;
+  return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_download_sumtable(pll_partition_t * p, const double * key, double * dst)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  auto it = c->sumtables.find(key);
+  if (it == c->sumtables.end())
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Unknown sumtable buffer.");
+    return PLL_FAILURE;
+  }
+  CUDA_TRY(cudaMemcpyAsync(dst, it->second, sizeof(double) * c->clv_elems, cudaMemcpyDeviceToHost,
+                           c->stream), PLL_FAILURE);
+  g_d2h_bytes += sizeof(double) * c->clv_elems;
+  return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_sync_host_arrays(pll_partition_t * p)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  std::fill(c->tip_dirty.begin(), c->tip_dirty.end(), 1);
+  c->any_tip_dirty = c->weights_dirty = c->tipmap_dirty = true;
+  c->invariant_dirty = p->invariant != nullptr;
+  unsigned int sum = 0;
+  for (unsigned int i = 0; i < p->sites; ++i) sum += p->pattern_weights[i];
+  p->pattern_weight_sum = sum;
+  return dev_sync_inputs(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_partition_synchronize(pll_partition_t * p)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  return dev_flush(ctx_of(p)) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_partition_set_stream(pll_partition_t * p, void * cuda_stream)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (!dev_flush(c)) return PLL_FAILURE;
+  c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
+  return PLL_SUCCESS;
+}
+
+extern "C" uint64_t pllb200_result_device_ptr(pll_partition_t * p)
+{
+  if (!check_ctx(p)) return 0;
+  return (uint64_t)(uintptr_t)ctx_of(p)->d_result;
+}

@@ -1,0 +1,160 @@
+/*
+ * internal.h — private state behind pll_partition_t for the B200 library.
+ *
+ * A partition handed out by pll_partition_create is the first member of a PartCtx, so the public
+ * pointer doubles as the handle to its HBM arenas, stream and staging buffers
+ * (SURVEY.md §8b "Device-state attachment": over-allocation instead of a side registry).
+ */
+#ifndef PLLB200_INTERNAL_H_
+#define PLLB200_INTERNAL_H_
+
+#include "../../include/pllb200.h"
+
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstring>
+#include <unordered_map>
+#include <vector>
+
+#define PLLB200_MAGIC 0xB200C1F5u
+#define PLLB200_RESULT_SLOTS 64   /* async reduction results in flight per partition */
+#define PLLB200_MAX_RED_BLOCKS 2048 /* upper bound on reduction grid size */
+
+struct PendingResult
+{
+  double * host_dst;
+  int slot;
+  int comp; /* component inside the slot */
+};
+
+struct PartCtx
+{
+  pll_partition_t pub; /* MUST stay first */
+  unsigned int magic;
+  int device;
+  int sm_count;
+
+  cudaStream_t own_stream;
+  cudaStream_t stream;
+
+  /* geometry */
+  unsigned int sites_alloc;   /* sites + asc_additional_sites */
+  unsigned int clv_first;     /* first node index that owns a CLV buffer */
+  size_t clv_elems;           /* doubles per CLV: sites_alloc*K*sp */
+  size_t clv_stride;          /* doubles between consecutive CLVs (padded to 256 B) */
+  size_t scaler_elems;        /* u32 per scale buffer */
+  size_t scaler_stride;
+  size_t pmat_elems;          /* doubles per P-matrix: K*s*sp */
+  size_t tip_stride;          /* bytes between tipchar rows */
+  size_t eigen_stride;        /* doubles per rate matrix in the eigen block */
+
+  /* HBM arenas */
+  double * d_clv;
+  unsigned int * d_scaler;
+  double * d_pmat;
+  double * d_pmat_il;         /* 4-state interleaved copy [i][k][j] for the DNA traversal kernel */
+  unsigned char * d_tipchars;
+  unsigned int * d_weights;
+  int * d_invariant;
+  double * d_eigen;           /* [rate_matrix][ evecs s*sp | inv_evecs s*sp | evals sp | freqs sp ] */
+  unsigned long long * d_tipmap;
+  double * d_persite;         /* lazily allocated, sites doubles */
+
+  /* staging ring: pinned host + device mirror, stream-ordered */
+  char * h_stage;
+  char * d_stage;
+  size_t stage_size;
+  size_t stage_head;
+
+  /* reductions */
+  double * d_partials;        /* PLLB200_MAX_RED_BLOCKS*3 doubles */
+  unsigned int * d_ticket;
+  double * d_result;          /* PLLB200_RESULT_SLOTS*4 doubles on device */
+  double * h_result;          /* same, pinned + mapped: kernels write results straight to the host */
+  double * h_result_dev;      /* device alias of h_result */
+  int next_slot;
+  std::vector<PendingResult> pending;
+
+  /* sumtable shadows keyed by the caller's host pointer */
+  std::unordered_map<const void *, double *> sumtables;
+
+  /* host->device mirroring state */
+  std::vector<unsigned char> tip_dirty;
+  bool any_tip_dirty;
+  bool weights_dirty;
+  bool invariant_dirty;
+  bool tipmap_dirty;
+  std::vector<unsigned int> eigen_version;     /* bumped by pll_update_eigen */
+  std::vector<unsigned int> eigen_version_dev; /* version mirrored on the device */
+
+  /* scratch for op-list scheduling */
+  std::vector<pll_operation_t> op_scratch;
+  std::vector<int> idx_scratch;
+};
+
+static inline PartCtx * ctx_of(pll_partition_t * p) { return reinterpret_cast<PartCtx *>(p); }
+static inline const PartCtx * ctx_of(const pll_partition_t * p)
+{
+  return reinterpret_cast<const PartCtx *>(p);
+}
+
+/* error plumbing (errors.cpp) */
+void pllb200_set_error(int code, const char * fmt, ...);
+bool pllb200_cuda_ok(cudaError_t e, const char * what);
+#define CUDA_TRY(expr, failret)                        \
+  do                                                   \
+  {                                                    \
+    if (!pllb200_cuda_ok((expr), #expr)) return failret; \
+  } while (0)
+
+/* global counters (device_ctx.cu) */
+extern unsigned long long g_kernel_launches;
+extern unsigned long long g_h2d_bytes;
+extern unsigned long long g_d2h_bytes;
+extern int g_opt_trav_ctas_per_sm;
+extern int g_opt_trav_reorder;
+extern int g_opt_fuse_root;
+
+/* device context (device_ctx.cu) */
+bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */
+void dev_ctx_destroy(PartCtx * c);
+void * dev_stage(PartCtx * c, const void * src, size_t bytes); /* returns device ptr, stream ordered */
+bool dev_sync_inputs(PartCtx * c);   /* push dirty tipchars / weights / invariant / tipmap */
+bool dev_sync_eigen(PartCtx * c, const unsigned int * params_indices); /* ensure eigen block current */
+bool dev_flush(PartCtx * c);         /* stream sync + deliver pending async results */
+int dev_alloc_slot(PartCtx * c);
+/* sumtable shadows: global key registry so pll_aligned_free(key) releases the device buffer */
+void sumtable_forget_key(const void * key);
+void sumtable_forget_partition(PartCtx * c);
+
+static inline double * clv_dev(const PartCtx * c, unsigned int clv_index)
+{
+  return c->d_clv + (size_t)(clv_index - c->clv_first) * c->clv_stride;
+}
+static inline unsigned int * scaler_dev(const PartCtx * c, int scaler_index)
+{
+  return scaler_index < 0 ? nullptr : c->d_scaler + (size_t)scaler_index * c->scaler_stride;
+}
+static inline bool is_tip_pattern(const PartCtx * c, unsigned int clv_index)
+{
+  return (c->pub.attributes & PLL_ATTRIB_PATTERN_TIP) && clv_index < c->pub.tips;
+}
+
+/* kernel launchers (k_*.cu). All are asynchronous on c->stream and return false on launch error. */
+bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
+                    const unsigned int * matrix_indices, const double * branch_lengths,
+                    unsigned int count);
+bool launch_partials(PartCtx * c, const pll_operation_t * ops, unsigned int count);
+bool launch_edge_logl(PartCtx * c, unsigned int parent_clv, int parent_scaler,
+                      unsigned int child_clv, int child_scaler, unsigned int matrix_index,
+                      const unsigned int * freqs_indices, double * d_persite, int slot);
+bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
+                      const unsigned int * freqs_indices, double * d_persite, int slot);
+bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_clv,
+                     int parent_scaler, int child_scaler, const unsigned int * params_indices,
+                     double * d_sumtable);
+bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double branch_length,
+                        const unsigned int * params_indices, const double * d_sumtable, int slot);
+
+#endif

@@ -1,0 +1,535 @@
+/*
+ * k_derivatives.cu — sumtable construction and first/second derivatives of -logL w.r.t. one
+ * branch length, the inner loop of Newton-Raphson branch-length optimisation.
+ *
+ * Replaces pll_core_update_sumtable_ii / _ti and pll_core_likelihood_derivatives
+ * (libs/libpll/src/core_derivatives.c:116-640, 643-929 and SIMD twins), driven like
+ * derivatives.c:24-324 and :333-418.
+ *
+ *   sum[n,k,j] = (sum_i P[n,k,i] pi_k[i] Vinv_k[i][j]) * (sum_i V_k[j][i] C[n,k,i])          (A.6)
+ *     tip end: P[n,k,i] := bit i of the tip state, and the tip is always the "P" side
+ *     (derivatives.c:66-78); per-rate scalers: min-normalised, capped at 4 (core_derivatives.c:418-440)
+ *   diag[k,j]  = ( e^{l_j r_k t/(1-pinv_k)}, l r e, (l r)^2 e ) computed on the host per call (K*s exps)
+ *   (L,L',L'')_n = sum_k w_k [ sum_j sum[n,k,j] diag[k,j] ] (+ invariant term on L)              (A.7)
+ *   d_f  = sum_n wgt_n (-L'/L),  dd_f = sum_n wgt_n ((L'/L)^2 - L''/L)
+ *
+ * The sumtable (one CLV-sized buffer) never leaves HBM: the caller's host pointer is only a key.
+ * Sumtable: 384 B/site (ii) / 257 (ti); derivative pass: 132 B/site (DNA Gamma4) -> a 1 M-site pass
+ * is ~20 us of HBM time, so the kernel returns its two scalars through mapped pinned memory.
+ */
+#include "internal.h"
+#include "devutil.cuh"
+#include "reduce.cuh"
+
+#include <cmath>
+#include <utility>
+
+#define DV_MAXK 32
+#define DV_THREADS 256
+#define DVG_THREADS 128
+
+struct SumArgs
+{
+  const double * pclv;         /* "parent" side (pi * Vinv); null if tip */
+  const unsigned char * ptip;
+  const double * cclv;         /* child side (V) — always an inner CLV */
+  const unsigned int * pscaler;
+  const unsigned int * cscaler;
+  const double * eigen;
+  const unsigned long long * tipmap;
+  double * sum;
+  unsigned long long eigen_stride;
+  unsigned int sites, states, sp, K;
+  int rate_scalers;
+  int is4;
+  unsigned int model_idx[DV_MAXK];
+};
+
+template <int K>
+__global__ void __launch_bounds__(DV_THREADS) sumtable_dna_kernel(SumArgs a)
+{
+  __shared__ double s_w[K][16];  /* pi_i * Vinv[i][j] */
+  __shared__ double s_v[K][16];  /* V[j][i] */
+  for (int t = threadIdx.x; t < 16 * K; t += blockDim.x)
+  {
+    const int k = t / 16, q = t % 16;
+    const double * blk = a.eigen + (unsigned long long)a.model_idx[k] * a.eigen_stride;
+    s_v[k][q] = blk[q];
+    s_w[k][q] = blk[36 + q / 4] * blk[16 + q];
+  }
+  __syncthreads();
+  const int lane = threadIdx.x & 31;
+  const int k = lane % K;
+  const unsigned long long E = (unsigned long long)a.sites * K;
+  const unsigned long long Eround = (E + 31) / 32 * 32;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < Eround;
+       e += stride)
+  {
+    const bool act = e < E;
+    d4 out = {0, 0, 0, 0};
+    unsigned int sc = 0;
+    if (act)
+    {
+      const unsigned long long site = e / K;
+      d4 p;
+      if (a.ptip)
+      {
+        const unsigned int code = a.ptip[site];
+        p.x = (code & 1) ? 1.0 : 0.0;
+        p.y = (code & 2) ? 1.0 : 0.0;
+        p.z = (code & 4) ? 1.0 : 0.0;
+        p.w = (code & 8) ? 1.0 : 0.0;
+      }
+      else
+        p = ldg256(a.pclv + e * 4);
+      const d4 c = ldg256(a.cclv + e * 4);
+      const double * w = s_w[k];
+      const double * v = s_v[k];
+      const double l0 = p.x * w[0] + p.y * w[4] + p.z * w[8] + p.w * w[12];
+      const double l1 = p.x * w[1] + p.y * w[5] + p.z * w[9] + p.w * w[13];
+      const double l2 = p.x * w[2] + p.y * w[6] + p.z * w[10] + p.w * w[14];
+      const double l3 = p.x * w[3] + p.y * w[7] + p.z * w[11] + p.w * w[15];
+      const double r0 = v[0] * c.x + v[1] * c.y + v[2] * c.z + v[3] * c.w;
+      const double r1 = v[4] * c.x + v[5] * c.y + v[6] * c.z + v[7] * c.w;
+      const double r2 = v[8] * c.x + v[9] * c.y + v[10] * c.z + v[11] * c.w;
+      const double r3 = v[12] * c.x + v[13] * c.y + v[14] * c.z + v[15] * c.w;
+      out.x = l0 * r0;
+      out.y = l1 * r1;
+      out.z = l2 * r2;
+      out.w = l3 * r3;
+      if (a.rate_scalers)
+      {
+        if (a.pscaler) sc += a.pscaler[e];
+        if (a.cscaler) sc += a.cscaler[e];
+      }
+    }
+    if (a.rate_scalers)
+    {
+      unsigned int mn = sc;
+#pragma unroll
+      for (int off = 1; off < K; off <<= 1)
+      {
+        const unsigned int o = __shfl_xor_sync(0xffffffffu, mn, off);
+        mn = o < mn ? o : mn;
+      }
+      unsigned int diff = sc - mn;
+      if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
+      double f = 1.0;
+      for (unsigned int q = 0; q < diff; ++q) f *= SCALE_THRESHOLD_D;
+      if (diff)
+      {
+        out.x *= f;
+        out.y *= f;
+        out.z *= f;
+        out.w *= f;
+      }
+    }
+    if (act) stg256(a.sum + e * 4, out);
+  }
+}
+
+__global__ void __launch_bounds__(DVG_THREADS) sumtable_generic_kernel(SumArgs a)
+{
+  __shared__ unsigned int s_sc[DVG_THREADS];
+  const unsigned int K = a.K, s = a.states, sp = a.sp;
+  const unsigned int spb = DVG_THREADS / K;
+  const unsigned int lsite = threadIdx.x / K, k = threadIdx.x % K;
+  const unsigned long long site = (unsigned long long)blockIdx.x * spb + lsite;
+  const bool act = lsite < spb && site < a.sites;
+  const unsigned long long e = site * K + k;
+  unsigned int sc = 0;
+  if (act && a.rate_scalers)
+  {
+    if (a.pscaler) sc += a.pscaler[e];
+    if (a.cscaler) sc += a.cscaler[e];
+  }
+  double f = 1.0;
+  if (a.rate_scalers)
+  {
+    s_sc[threadIdx.x] = sc;
+    __syncthreads();
+    if (act)
+    {
+      unsigned int mn = sc;
+      for (unsigned int q = 0; q < K; ++q)
+        if (s_sc[lsite * K + q] < mn) mn = s_sc[lsite * K + q];
+      unsigned int diff = sc - mn;
+      if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
+      for (unsigned int q = 0; q < diff; ++q) f *= SCALE_THRESHOLD_D;
+    }
+  }
+  if (!act) return;
+  const double * blk = a.eigen + (unsigned long long)a.model_idx[k] * a.eigen_stride;
+  const double * ev = blk;
+  const double * iev = blk + s * sp;
+  const double * fr = blk + 2 * s * sp + sp;
+  unsigned long long mask = 0;
+  if (a.ptip)
+  {
+    const unsigned int code = a.ptip[site];
+    mask = a.is4 ? (unsigned long long)code : a.tipmap[code];
+  }
+  const double * pv = a.pclv ? a.pclv + e * sp : nullptr;
+  const double * cv = a.cclv + e * sp;
+  double * dst = a.sum + e * sp;
+  for (unsigned int j = 0; j < s; ++j)
+  {
+    double l = 0.0, r = 0.0;
+    for (unsigned int i = 0; i < s; ++i)
+    {
+      const double pi = pv ? pv[i] : (double)((mask >> i) & 1ull);
+      l += pi * fr[i] * iev[i * sp + j];
+      r += ev[j * sp + i] * cv[i];
+    }
+    dst[j] = l * r * f;
+  }
+  for (unsigned int j = s; j < sp; ++j) dst[j] = 0.0;
+}
+
+/* ---- derivatives ----------------------------------------------------------------------------- */
+
+struct DerivArgs
+{
+  const double * sum;
+  const unsigned int * weights;
+  const int * invariant;
+  const double * eigen;
+  const double * diag; /* generic path: staged [K][s][3] */
+  unsigned long long eigen_stride;
+  unsigned int sites, states, sp, K;
+  unsigned int model_idx[DV_MAXK];
+  double w[DV_MAXK];
+  double pinv[DV_MAXK];
+  ReduceOut red;
+};
+
+struct DiagDna
+{
+  double d[8][4][3];
+};
+
+template <int K>
+__global__ void __launch_bounds__(DV_THREADS) deriv_dna_kernel(DerivArgs a, DiagDna dg)
+{
+  const int lane = threadIdx.x & 31;
+  const int k = lane % K;
+  const double wk = a.w[k], pinv = a.pinv[k];
+  double d0[4], d1[4], d2[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+  {
+    d0[j] = dg.d[k][j][0];
+    d1[j] = dg.d[k][j][1];
+    d2[j] = dg.d[k][j][2];
+  }
+  const double * fr = a.eigen + (unsigned long long)a.model_idx[k] * a.eigen_stride + 36;
+  const unsigned long long E = (unsigned long long)a.sites * K;
+  const unsigned long long Eround = (E + 31) / 32 * 32;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  double acc1 = 0.0, acc2 = 0.0;
+  for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < Eround;
+       e += stride)
+  {
+    const bool act = e < E;
+    const unsigned long long site = e / K;
+    double L0 = 0.0, L1 = 0.0, L2 = 0.0;
+    if (act)
+    {
+      const d4 s = ldg256(a.sum + e * 4);
+      L0 = s.x * d0[0] + s.y * d0[1] + s.z * d0[2] + s.w * d0[3];
+      L1 = s.x * d1[0] + s.y * d1[1] + s.z * d1[2] + s.w * d1[3];
+      L2 = s.x * d2[0] + s.y * d2[1] + s.z * d2[2] + s.w * d2[3];
+      if (pinv > 0.0)
+      {
+        double inv_lk = 0.0;
+        if (a.invariant)
+        {
+          const int inv = a.invariant[site];
+          if (inv >= 0) inv_lk = fr[inv] * pinv;
+        }
+        L0 = L0 * (1.0 - pinv) + inv_lk;
+        L1 = L1 * (1.0 - pinv);
+        L2 = L2 * (1.0 - pinv);
+      }
+      L0 *= wk;
+      L1 *= wk;
+      L2 *= wk;
+    }
+#pragma unroll
+    for (int off = 1; off < K; off <<= 1)
+    {
+      L0 += __shfl_xor_sync(0xffffffffu, L0, off);
+      L1 += __shfl_xor_sync(0xffffffffu, L1, off);
+      L2 += __shfl_xor_sync(0xffffffffu, L2, off);
+    }
+    if (act && k == 0)
+    {
+      const double wgt = (double)a.weights[site];
+      const double r1 = -L1 / L0;
+      const double r2 = r1 * r1 - L2 / L0;
+      acc1 += wgt * r1;
+      acc2 += wgt * r2;
+    }
+  }
+  double v[2] = {acc1, acc2};
+  grid_reduce_finish<2>(v, a.red);
+}
+
+__global__ void __launch_bounds__(DVG_THREADS) deriv_generic_kernel(DerivArgs a)
+{
+  __shared__ double s_l[3][DVG_THREADS];
+  const unsigned int K = a.K, s = a.states, sp = a.sp;
+  const unsigned int spb = DVG_THREADS / K;
+  const unsigned int lsite = threadIdx.x / K, k = threadIdx.x % K;
+  const unsigned long long nblk = ((unsigned long long)a.sites + spb - 1) / spb;
+  double acc1 = 0.0, acc2 = 0.0;
+  for (unsigned long long blk = blockIdx.x; blk < nblk; blk += gridDim.x)
+  {
+    const unsigned long long site = blk * spb + lsite;
+    const bool act = lsite < spb && site < a.sites;
+    double L0 = 0.0, L1 = 0.0, L2 = 0.0;
+    if (act)
+    {
+      const double * sm = a.sum + (site * K + k) * sp;
+      const double * dg = a.diag + (size_t)k * s * 3;
+      for (unsigned int j = 0; j < s; ++j)
+      {
+        const double v = sm[j];
+        L0 += v * dg[j * 3 + 0];
+        L1 += v * dg[j * 3 + 1];
+        L2 += v * dg[j * 3 + 2];
+      }
+      const double pinv = a.pinv[k];
+      if (pinv > 0.0)
+      {
+        double inv_lk = 0.0;
+        const int inv = a.invariant ? a.invariant[site] : -1;
+        if (inv >= 0)
+          inv_lk = a.eigen[(unsigned long long)a.model_idx[k] * a.eigen_stride + 2 * s * sp + sp + inv] * pinv;
+        L0 = L0 * (1.0 - pinv) + inv_lk;
+        L1 = L1 * (1.0 - pinv);
+        L2 = L2 * (1.0 - pinv);
+      }
+      L0 *= a.w[k];
+      L1 *= a.w[k];
+      L2 *= a.w[k];
+    }
+    s_l[0][threadIdx.x] = L0;
+    s_l[1][threadIdx.x] = L1;
+    s_l[2][threadIdx.x] = L2;
+    __syncthreads();
+    if (act && k == 0)
+    {
+      double t0 = 0, t1 = 0, t2 = 0;
+      for (unsigned int q = 0; q < K; ++q)
+      {
+        t0 += s_l[0][threadIdx.x + q];
+        t1 += s_l[1][threadIdx.x + q];
+        t2 += s_l[2][threadIdx.x + q];
+      }
+      const double wgt = (double)a.weights[site];
+      const double r1 = -t1 / t0;
+      const double r2 = r1 * r1 - t2 / t0;
+      acc1 += wgt * r1;
+      acc2 += wgt * r2;
+    }
+    __syncthreads();
+  }
+  double v[2] = {acc1, acc2};
+  grid_reduce_finish<2>(v, a.red);
+}
+
+/* ---- host ------------------------------------------------------------------------------------ */
+
+bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_clv,
+                     int parent_scaler, int child_scaler, const unsigned int * params_indices,
+                     double * d_sumtable)
+{
+  pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats;
+  if (K > DV_MAXK)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats > %d is not supported.", DV_MAXK);
+    return false;
+  }
+  if (parent_clv >= p->nodes || child_clv >= p->nodes || parent_scaler >= (int)p->scale_buffers ||
+      child_scaler >= (int)p->scale_buffers)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid index in pll_update_sumtable.");
+    return false;
+  }
+  const bool ptip = is_tip_pattern(c, parent_clv), ctip = is_tip_pattern(c, child_clv);
+  if (ptip && ctip)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "pll_update_sumtable() was called for the tip-tip case!");
+    return false;
+  }
+  if (!dev_sync_inputs(c) || !dev_sync_eigen(c, params_indices)) return false;
+  SumArgs a;
+  memset(&a, 0, sizeof(a));
+  if (ptip || ctip)
+  {
+    /* the tip takes the "parent" role, the inner node's scaler is the only one (derivatives.c:66-78) */
+    const unsigned int tip = ptip ? parent_clv : child_clv;
+    const unsigned int inner = ptip ? child_clv : parent_clv;
+    a.ptip = c->d_tipchars + (size_t)tip * c->tip_stride;
+    a.cclv = clv_dev(c, inner);
+    a.pscaler = scaler_dev(c, ptip ? child_scaler : parent_scaler);
+  }
+  else
+  {
+    a.pclv = clv_dev(c, parent_clv);
+    a.cclv = clv_dev(c, child_clv);
+    a.pscaler = scaler_dev(c, parent_scaler);
+    a.cscaler = scaler_dev(c, child_scaler);
+  }
+  a.eigen = c->d_eigen;
+  a.eigen_stride = c->eigen_stride;
+  a.tipmap = c->d_tipmap;
+  a.sum = d_sumtable;
+  a.sites = c->sites_alloc;
+  a.states = p->states;
+  a.sp = p->states_padded;
+  a.K = K;
+  a.rate_scalers = (p->attributes & PLL_ATTRIB_RATE_SCALERS) != 0;
+  a.is4 = p->states == 4;
+  for (unsigned int k = 0; k < K; ++k) a.model_idx[k] = params_indices[k];
+
+  if (p->states == 4 && (K == 1 || K == 2 || K == 4 || K == 8))
+  {
+    const unsigned long long E = (unsigned long long)a.sites * K;
+    unsigned long long blocks = (E + DV_THREADS - 1) / DV_THREADS;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    switch (K)
+    {
+      case 1: sumtable_dna_kernel<1><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
+      case 2: sumtable_dna_kernel<2><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
+      case 4: sumtable_dna_kernel<4><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
+      default: sumtable_dna_kernel<8><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
+    }
+  }
+  else
+  {
+    const unsigned int spb = DVG_THREADS / K;
+    const unsigned int blocks = (a.sites + spb - 1) / spb;
+    sumtable_generic_kernel<<<blocks, DVG_THREADS, 0, c->stream>>>(a);
+  }
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "sumtable kernel launch");
+}
+
+bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double branch_length,
+                        const unsigned int * params_indices, const double * d_sumtable, int slot)
+{
+  (void)parent_scaler;
+  (void)child_scaler; /* ratios L'/L cancel the scaling; only asc-bias would need them */
+  pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats, s = p->states, sp = p->states_padded;
+  if (K > DV_MAXK)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats > %d is not supported.", DV_MAXK);
+    return false;
+  }
+  if (p->attributes & PLL_ATTRIB_AB_MASK)
+  {
+    pllb200_set_error(PLL_ERROR_AB_NOSUPPORT,
+                      "Ascertainment bias correction is not implemented on the device path yet.");
+    return false;
+  }
+  if (!dev_sync_inputs(c) || !dev_sync_eigen(c, params_indices)) return false;
+  DerivArgs a;
+  memset(&a, 0, sizeof(a));
+  a.sum = d_sumtable;
+  a.weights = c->d_weights;
+  a.eigen = c->d_eigen;
+  a.eigen_stride = c->eigen_stride;
+  a.sites = p->sites;
+  a.states = s;
+  a.sp = sp;
+  a.K = K;
+  bool any_pinv = false;
+  for (unsigned int k = 0; k < K; ++k)
+  {
+    a.model_idx[k] = params_indices[k];
+    a.w[k] = p->rate_weights[k];
+    a.pinv[k] = p->prop_invar[params_indices[k]];
+    any_pinv |= a.pinv[k] > 0.0;
+  }
+  if (any_pinv)
+  {
+    if (!p->invariant)
+    {
+      pllb200_set_error(PLL_ERROR_INVAR_NONEFOUND, "prop_invar > 0 but no invariant site array.");
+      return false;
+    }
+    if (!c->d_invariant)
+    {
+      c->invariant_dirty = true;
+      if (!dev_sync_inputs(c)) return false;
+    }
+    a.invariant = c->d_invariant;
+  }
+  a.red.partials = c->d_partials;
+  a.red.ticket = c->d_ticket;
+  a.red.result_dev = c->d_result + slot * 4;
+  a.red.result_host = c->h_result_dev + slot * 4;
+
+  /* diagonal table on the host: K*s exponentials (core_derivatives.c:757-772) */
+  const bool dna = s == 4 && (K == 1 || K == 2 || K == 4 || K == 8);
+  DiagDna dg;
+  std::vector<double> diag;
+  if (!dna) diag.resize((size_t)K * s * 3);
+  for (unsigned int k = 0; k < K; ++k)
+  {
+    const double * evals = p->eigenvals[params_indices[k]];
+    const double ki = p->rates[k] / (1.0 - a.pinv[k]);
+    for (unsigned int j = 0; j < s; ++j)
+    {
+      const double e0 = exp(evals[j] * ki * branch_length);
+      const double e1 = evals[j] * ki * e0;
+      const double e2 = evals[j] * ki * evals[j] * ki * e0;
+      if (dna)
+      {
+        dg.d[k][j][0] = e0;
+        dg.d[k][j][1] = e1;
+        dg.d[k][j][2] = e2;
+      }
+      else
+      {
+        diag[((size_t)k * s + j) * 3 + 0] = e0;
+        diag[((size_t)k * s + j) * 3 + 1] = e1;
+        diag[((size_t)k * s + j) * 3 + 2] = e2;
+      }
+    }
+  }
+  if (dna)
+  {
+    const unsigned long long E = (unsigned long long)a.sites * K;
+    unsigned long long blocks = (E + DV_THREADS - 1) / DV_THREADS;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+    switch (K)
+    {
+      case 1: deriv_dna_kernel<1><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
+      case 2: deriv_dna_kernel<2><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
+      case 4: deriv_dna_kernel<4><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
+      default: deriv_dna_kernel<8><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
+    }
+  }
+  else
+  {
+    a.diag = (const double *)dev_stage(c, diag.data(), sizeof(double) * diag.size());
+    if (!a.diag) return false;
+    const unsigned int spb = DVG_THREADS / K;
+    unsigned long long blocks = ((unsigned long long)a.sites + spb - 1) / spb;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+    deriv_generic_kernel<<<(unsigned)blocks, DVG_THREADS, 0, c->stream>>>(a);
+  }
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "derivative kernel launch");
+}

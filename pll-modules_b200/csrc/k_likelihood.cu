@@ -1,0 +1,426 @@
+/*
+ * k_likelihood.cu — edge and root log-likelihood with on-device reduction.
+ *
+ * Replaces pll_core_edge_loglikelihood_ii / _ti{,_4x4} and pll_core_root_loglikelihood
+ * (libs/libpll/src/core_likelihood.c:25-190, 352-610, 1192-1497 and SIMD twins), driven like
+ * likelihood.c:122-189 and :586-636.
+ *
+ * Per site n:
+ *   terma   = sum_k w_k (1-pinv_k) sum_i P[n,k,i] pi_k[i] sum_j M_k[i][j] C[n,k,j]
+ *   terminv = sum_k w_k pinv_k pi_k[inv[n]]            (inv[n] != -1, pinv_k > 0)
+ *   no scaling      : ln(terma + terminv)
+ *   c scalings > 0  : terminv > 0 ? ln(terma * 2^(-256 min(c,4)) + terminv) : ln(terma) + c ln 2^-256
+ *   per-rate scalers: c_k normalised to their minimum, differences capped at 4 (core_likelihood.c:1396-1414)
+ * times pattern_weights[n]; optional per-site output; deterministic grid sum (reduce.cuh).
+ *
+ * Thread = (site, rate category); the K lanes of a site combine with shuffles (4-state path) or
+ * shared memory (generic path).  HBM-bound: 268 B/site (ii), 137 B/site (ti) for DNA Gamma4.
+ */
+#include "internal.h"
+#include "devutil.cuh"
+#include "reduce.cuh"
+
+#include <utility>
+
+#define LK_MAXK 32
+
+struct LoglArgs
+{
+  const double * pclv;          /* inner ("parent") CLV */
+  const double * cclv;          /* child CLV, null if tip pattern / root */
+  const unsigned char * ctip;   /* child tip codes */
+  const double * pmat;          /* [K][s][sp]; null for root */
+  const unsigned int * pscaler;
+  const unsigned int * cscaler;
+  const unsigned int * weights;
+  const int * invariant;        /* may be null */
+  const double * eigen;         /* model block (frequencies live at +2*s*sp+sp) */
+  const unsigned long long * tipmap;
+  double * persite;             /* may be null */
+  unsigned long long eigen_stride;
+  unsigned int sites, states, sp, K;
+  int rate_scalers;
+  int is4;
+  unsigned int freq_idx[LK_MAXK];
+  double w[LK_MAXK];
+  double pinv[LK_MAXK];
+  ReduceOut red;
+};
+
+__device__ __forceinline__ double site_finish(double terma, double terminv, unsigned int scalings,
+                                              bool root)
+{
+  /* root: ln(term) + c ln 2^-256 irrespective of invariant sites (core_likelihood.c:172-176) */
+  if (root) return log(terma + terminv) + (double)scalings * LN_SCALE_THRESHOLD;
+  if (scalings)
+  {
+    if (terminv > 0.0)
+    {
+      const unsigned int capped = scalings < PLL_SCALE_RATE_MAXDIFF ? scalings : PLL_SCALE_RATE_MAXDIFF;
+      double f = SCALE_THRESHOLD_D;
+      for (unsigned int q = 1; q < capped; ++q) f *= SCALE_THRESHOLD_D;
+      return log(terma * f + terminv);
+    }
+    return log(terma) + (double)scalings * LN_SCALE_THRESHOLD;
+  }
+  return log(terma + terminv);
+}
+
+#define LK_THREADS 256
+
+/* ---- 4-state path: ROOT=false edge (ii or ti), ROOT=true root ----------------------------- */
+template <int K, bool ROOT>
+__global__ void __launch_bounds__(LK_THREADS) logl_dna_kernel(LoglArgs a)
+{
+  __shared__ double s_mat[16 * K];
+  __shared__ double s_freq[4 * K];
+  if (!ROOT)
+    for (int i = threadIdx.x; i < 16 * K; i += blockDim.x) s_mat[i] = a.pmat[i];
+  for (int i = threadIdx.x; i < 4 * K; i += blockDim.x)
+    s_freq[i] = a.eigen[(unsigned long long)a.freq_idx[i / 4] * a.eigen_stride + 2 * 4 * 4 + 4 + (i & 3)];
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const int k = lane % K;
+  const double wk = a.w[k], pinv = a.pinv[k];
+  const double f0 = s_freq[k * 4 + 0], f1 = s_freq[k * 4 + 1], f2 = s_freq[k * 4 + 2],
+               f3 = s_freq[k * 4 + 3];
+  const unsigned long long E = (unsigned long long)a.sites * K;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  const unsigned long long Eround = (E + 31) / 32 * 32;
+  double acc = 0.0;
+
+  for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < Eround;
+       e += stride)
+  {
+    const bool act = e < E;
+    const unsigned long long site = e / K;
+    double term = 0.0, tinv = 0.0;
+    unsigned int sc = 0;
+    if (act)
+    {
+      const d4 p = ldg256(a.pclv + e * 4);
+      double t0, t1, t2, t3;
+      if (ROOT)
+      {
+        t0 = t1 = t2 = t3 = 1.0;
+      }
+      else if (a.ctip)
+      {
+        const unsigned int code = a.ctip[site];
+        const double * m = s_mat + k * 16;
+        t0 = ((code & 1) ? m[0] : 0.0) + ((code & 2) ? m[1] : 0.0) + ((code & 4) ? m[2] : 0.0) + ((code & 8) ? m[3] : 0.0);
+        t1 = ((code & 1) ? m[4] : 0.0) + ((code & 2) ? m[5] : 0.0) + ((code & 4) ? m[6] : 0.0) + ((code & 8) ? m[7] : 0.0);
+        t2 = ((code & 1) ? m[8] : 0.0) + ((code & 2) ? m[9] : 0.0) + ((code & 4) ? m[10] : 0.0) + ((code & 8) ? m[11] : 0.0);
+        t3 = ((code & 1) ? m[12] : 0.0) + ((code & 2) ? m[13] : 0.0) + ((code & 4) ? m[14] : 0.0) + ((code & 8) ? m[15] : 0.0);
+      }
+      else
+      {
+        const d4 c = ldg256(a.cclv + e * 4);
+        const double * m = s_mat + k * 16;
+        t0 = m[0] * c.x + m[1] * c.y + m[2] * c.z + m[3] * c.w;
+        t1 = m[4] * c.x + m[5] * c.y + m[6] * c.z + m[7] * c.w;
+        t2 = m[8] * c.x + m[9] * c.y + m[10] * c.z + m[11] * c.w;
+        t3 = m[12] * c.x + m[13] * c.y + m[14] * c.z + m[15] * c.w;
+      }
+      term = p.x * f0 * t0 + p.y * f1 * t1 + p.z * f2 * t2 + p.w * f3 * t3;
+      if (a.rate_scalers)
+      {
+        if (a.pscaler) sc += a.pscaler[e];
+        if (a.cscaler) sc += a.cscaler[e];
+      }
+      else if (k == 0)
+      {
+        if (a.pscaler) sc += a.pscaler[site];
+        if (a.cscaler) sc += a.cscaler[site];
+      }
+    }
+    unsigned int site_sc = sc;
+    if (a.rate_scalers)
+    {
+      unsigned int mn = sc;
+#pragma unroll
+      for (int off = 1; off < K; off <<= 1)
+      {
+        const unsigned int o = __shfl_xor_sync(0xffffffffu, mn, off);
+        mn = o < mn ? o : mn;
+      }
+      unsigned int diff = sc - mn;
+      if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
+      for (unsigned int q = 0; q < diff; ++q) term *= SCALE_THRESHOLD_D;
+      site_sc = mn;
+    }
+    if (pinv > 0.0)
+    {
+      term = wk * term * (1.0 - pinv);
+      if (act && a.invariant)
+      {
+        const int inv = a.invariant[site];
+        if (inv >= 0) tinv = wk * s_freq[k * 4 + inv] * pinv;
+      }
+    }
+    else
+      term = term * wk;
+#pragma unroll
+    for (int off = 1; off < K; off <<= 1)
+    {
+      term += __shfl_xor_sync(0xffffffffu, term, off);
+      tinv += __shfl_xor_sync(0xffffffffu, tinv, off);
+    }
+    if (act && k == 0)
+    {
+      double lk = site_finish(term, tinv, site_sc, ROOT);
+      lk *= (double)a.weights[site];
+      if (a.persite) a.persite[site] = lk;
+      acc += lk;
+    }
+  }
+  double v[1] = {acc};
+  grid_reduce_finish<1>(v, a.red);
+}
+
+/* ---- generic path --------------------------------------------------------------------------- */
+#define LKG_THREADS 128
+
+__global__ void __launch_bounds__(LKG_THREADS) logl_generic_kernel(LoglArgs a, int root)
+{
+  __shared__ double s_term[LKG_THREADS];
+  __shared__ double s_inv[LKG_THREADS];
+  __shared__ unsigned int s_sc[LKG_THREADS];
+  const unsigned int K = a.K, s = a.states, sp = a.sp;
+  const unsigned int spb = LKG_THREADS / K;
+  const unsigned int lsite = threadIdx.x / K, k = threadIdx.x % K;
+  const unsigned long long nblk = ((unsigned long long)a.sites + spb - 1) / spb;
+  double acc = 0.0;
+
+  for (unsigned long long blk = blockIdx.x; blk < nblk; blk += gridDim.x)
+  {
+    const unsigned long long site = blk * spb + lsite;
+    const bool act = lsite < spb && site < a.sites;
+    double term = 0.0, tinv = 0.0;
+    unsigned int sc = 0;
+    if (act)
+    {
+      const unsigned long long e = site * K + k;
+      const double * freqs = a.eigen + (unsigned long long)a.freq_idx[k] * a.eigen_stride + 2 * s * sp + sp;
+      const double * pv = a.pclv + e * sp;
+      const double * mat = root ? nullptr : a.pmat + (size_t)k * s * sp;
+      const double * cv = a.cclv ? a.cclv + e * sp : nullptr;
+      unsigned long long cmask = 0;
+      if (a.ctip)
+      {
+        const unsigned int code = a.ctip[site];
+        cmask = a.is4 ? (unsigned long long)code : a.tipmap[code];
+      }
+      for (unsigned int i = 0; i < s; ++i)
+      {
+        double tb = 1.0;
+        if (!root)
+        {
+          tb = 0.0;
+          if (cv)
+            for (unsigned int j = 0; j < s; ++j) tb += __ldg(mat + i * sp + j) * cv[j];
+          else
+            for (unsigned int j = 0; j < s; ++j)
+              if ((cmask >> j) & 1ull) tb += __ldg(mat + i * sp + j);
+        }
+        term += pv[i] * freqs[i] * tb;
+      }
+      const unsigned long long si = a.rate_scalers ? e : site;
+      if (a.pscaler) sc += a.pscaler[si];
+      if (a.cscaler) sc += a.cscaler[si];
+      const double pinv = a.pinv[k];
+      if (pinv > 0.0)
+      {
+        const int inv = a.invariant ? a.invariant[site] : -1;
+        if (inv >= 0) tinv = a.w[k] * freqs[inv] * pinv;
+      }
+    }
+    s_term[threadIdx.x] = term;
+    s_inv[threadIdx.x] = tinv;
+    s_sc[threadIdx.x] = sc;
+    __syncthreads();
+    if (act && k == 0)
+    {
+      unsigned int site_sc = s_sc[threadIdx.x];
+      if (a.rate_scalers)
+        for (unsigned int q = 1; q < K; ++q)
+          if (s_sc[threadIdx.x + q] < site_sc) site_sc = s_sc[threadIdx.x + q];
+      double ta = 0.0, ti = 0.0;
+      for (unsigned int q = 0; q < K; ++q)
+      {
+        double t = s_term[threadIdx.x + q];
+        if (a.rate_scalers)
+        {
+          unsigned int diff = s_sc[threadIdx.x + q] - site_sc;
+          if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
+          for (unsigned int z = 0; z < diff; ++z) t *= SCALE_THRESHOLD_D;
+        }
+        const double pinv = a.pinv[q];
+        if (pinv > 0.0)
+          ta += a.w[q] * t * (1.0 - pinv);
+        else
+          ta += t * a.w[q];
+        ti += s_inv[threadIdx.x + q];
+      }
+      double lk = site_finish(ta, ti, site_sc, root != 0);
+      lk *= (double)a.weights[site];
+      if (a.persite) a.persite[site] = lk;
+      acc += lk;
+    }
+    __syncthreads();
+  }
+  double v[1] = {acc};
+  grid_reduce_finish<1>(v, a.red);
+}
+
+/* ---- host ------------------------------------------------------------------------------------ */
+
+static bool fill_common(PartCtx * c, LoglArgs & a, const unsigned int * freqs_indices,
+                        double * d_persite, int slot)
+{
+  pll_partition_t * p = &c->pub;
+  if (p->rate_cats > LK_MAXK)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats > %d is not supported.", LK_MAXK);
+    return false;
+  }
+  if (p->attributes & PLL_ATTRIB_AB_MASK)
+  {
+    pllb200_set_error(PLL_ERROR_AB_NOSUPPORT,
+                      "Ascertainment bias correction is not implemented on the device path yet.");
+    return false;
+  }
+  if (!dev_sync_inputs(c) || !dev_sync_eigen(c, freqs_indices)) return false;
+  memset(&a, 0, sizeof(a));
+  a.weights = c->d_weights;
+  a.eigen = c->d_eigen;
+  a.eigen_stride = c->eigen_stride;
+  a.tipmap = c->d_tipmap;
+  a.persite = d_persite;
+  a.sites = p->sites;
+  a.states = p->states;
+  a.sp = p->states_padded;
+  a.K = p->rate_cats;
+  a.rate_scalers = (p->attributes & PLL_ATTRIB_RATE_SCALERS) != 0;
+  a.is4 = p->states == 4;
+  bool any_pinv = false;
+  for (unsigned int k = 0; k < p->rate_cats; ++k)
+  {
+    a.freq_idx[k] = freqs_indices[k];
+    a.w[k] = p->rate_weights[k];
+    a.pinv[k] = p->prop_invar[freqs_indices[k]];
+    any_pinv |= a.pinv[k] > 0.0;
+  }
+  if (any_pinv)
+  {
+    if (!p->invariant)
+    {
+      pllb200_set_error(PLL_ERROR_INVAR_NONEFOUND, "prop_invar > 0 but no invariant site array.");
+      return false;
+    }
+    if (!c->d_invariant)
+    {
+      c->invariant_dirty = true;
+      if (!dev_sync_inputs(c)) return false;
+    }
+    a.invariant = c->d_invariant;
+  }
+  a.red.partials = c->d_partials;
+  a.red.ticket = c->d_ticket;
+  a.red.result_dev = c->d_result + slot * 4;
+  a.red.result_host = c->h_result_dev + slot * 4;
+  return true;
+}
+
+template <bool ROOT>
+static bool dispatch_logl(PartCtx * c, const LoglArgs & a)
+{
+  const unsigned int K = a.K;
+  if (a.states == 4 && (K == 1 || K == 2 || K == 4 || K == 8))
+  {
+    const unsigned long long E = (unsigned long long)a.sites * K;
+    unsigned long long blocks = (E + LK_THREADS - 1) / LK_THREADS;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+    if (blocks < 1) blocks = 1;
+    switch (K)
+    {
+      case 1: logl_dna_kernel<1, ROOT><<<(unsigned)blocks, LK_THREADS, 0, c->stream>>>(a); break;
+      case 2: logl_dna_kernel<2, ROOT><<<(unsigned)blocks, LK_THREADS, 0, c->stream>>>(a); break;
+      case 4: logl_dna_kernel<4, ROOT><<<(unsigned)blocks, LK_THREADS, 0, c->stream>>>(a); break;
+      default: logl_dna_kernel<8, ROOT><<<(unsigned)blocks, LK_THREADS, 0, c->stream>>>(a); break;
+    }
+  }
+  else
+  {
+    if (K > LKG_THREADS)
+    {
+      pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats too large.");
+      return false;
+    }
+    const unsigned int spb = LKG_THREADS / K;
+    unsigned long long blocks = ((unsigned long long)a.sites + spb - 1) / spb;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+    logl_generic_kernel<<<(unsigned)blocks, LKG_THREADS, 0, c->stream>>>(a, ROOT ? 1 : 0);
+  }
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "logl kernel launch");
+}
+
+bool launch_edge_logl(PartCtx * c, unsigned int parent_clv, int parent_scaler,
+                      unsigned int child_clv, int child_scaler, unsigned int matrix_index,
+                      const unsigned int * freqs_indices, double * d_persite, int slot)
+{
+  pll_partition_t * p = &c->pub;
+  if (parent_clv >= p->nodes || child_clv >= p->nodes || matrix_index >= p->prob_matrices ||
+      parent_scaler >= (int)p->scale_buffers || child_scaler >= (int)p->scale_buffers)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid index in edge log-likelihood call.");
+    return false;
+  }
+  /* the inner node plays "parent"; the matrix is applied to the other end (likelihood.c:612-624) */
+  const bool ptip = is_tip_pattern(c, parent_clv), ctip = is_tip_pattern(c, child_clv);
+  if (ptip && ctip)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Edge log-likelihood between two pattern tips.");
+    return false;
+  }
+  if (ptip)
+  {
+    std::swap(parent_clv, child_clv);
+    std::swap(parent_scaler, child_scaler);
+  }
+  LoglArgs a;
+  if (!fill_common(c, a, freqs_indices, d_persite, slot)) return false;
+  a.pclv = clv_dev(c, parent_clv);
+  a.pscaler = scaler_dev(c, parent_scaler);
+  if (ptip || ctip)
+    a.ctip = c->d_tipchars + (size_t)child_clv * c->tip_stride;
+  else
+  {
+    a.cclv = clv_dev(c, child_clv);
+    a.cscaler = scaler_dev(c, child_scaler);
+  }
+  a.pmat = c->d_pmat + (size_t)matrix_index * c->pmat_elems;
+  return dispatch_logl<false>(c, a);
+}
+
+bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
+                      const unsigned int * freqs_indices, double * d_persite, int slot)
+{
+  pll_partition_t * p = &c->pub;
+  if (clv_index >= p->nodes || clv_index < c->clv_first || scaler_index >= (int)p->scale_buffers)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid index in root log-likelihood call.");
+    return false;
+  }
+  LoglArgs a;
+  if (!fill_common(c, a, freqs_indices, d_persite, slot)) return false;
+  a.pclv = clv_dev(c, clv_index);
+  a.pscaler = scaler_dev(c, scaler_index);
+  return dispatch_logl<true>(c, a);
+}

@@ -1,0 +1,113 @@
+/*
+ * k_pmatrix.cu — batched transition-probability matrices.
+ *
+ * Replaces pll_core_update_pmatrix (libs/libpll/src/core_pmatrix.c:24-258 and its SSE/AVX/AVX2
+ * twins).  One CTA per (edge, rate category): P = I + V^-1 * diag(expm1(lambda_j * r_k * t / (1-pinv))) * V
+ * with the reference's conventions — the (1-pinv) divisor only when pinv > PLL_MISC_EPSILON
+ * (core_pmatrix.c:210), t == 0 gives the identity (:238-245), expm1 + identity for accuracy at
+ * small t (:201-206).  All `count` edges of a call go out in ONE launch (the reference's callers
+ * hand over one matrix per call, treeinfo.c:854 — our treeinfo batches them).
+ *
+ * Roofline: irrelevant (count*K*s*sp*8 bytes, ~1 MB for 2000 DNA edges); latency is what matters,
+ * hence one launch and kernel-parameter passing of the per-category model scalars.
+ */
+#include "internal.h"
+
+#define PM_MAXK 32
+
+struct PmatArgs
+{
+  unsigned int params_idx[PM_MAXK];
+  double rates[PM_MAXK];
+  double pinv[PM_MAXK];
+};
+
+__global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__ pmat_il,
+                               const double * __restrict__ eigen, size_t eigen_stride,
+                               const unsigned int * __restrict__ matrix_indices,
+                               const double * __restrict__ branch_lengths, unsigned int states,
+                               unsigned int sp, unsigned int K, PmatArgs a)
+{
+  extern __shared__ double sm[]; /* expd[sp] | inv[s*sp] | ev[s*sp] */
+  double * expd = sm;
+  double * s_inv = sm + sp;
+  double * s_ev = s_inv + states * sp;
+
+  const unsigned int e = blockIdx.x / K;
+  const unsigned int k = blockIdx.x % K;
+  const unsigned int m = matrix_indices[e];
+  const double t = branch_lengths[e];
+  const double * blk = eigen + (size_t)a.params_idx[k] * eigen_stride;
+  const double * g_ev = blk;
+  const double * g_inv = blk + states * sp;
+  const double * g_val = blk + 2 * states * sp;
+
+  for (unsigned int i = threadIdx.x; i < states * sp; i += blockDim.x)
+  {
+    s_inv[i] = g_inv[i];
+    s_ev[i] = g_ev[i];
+  }
+  if (threadIdx.x < states)
+  {
+    const double pinv = a.pinv[k];
+    double x = g_val[threadIdx.x] * a.rates[k] * t;
+    if (pinv > PLL_MISC_EPSILON) x = g_val[threadIdx.x] * a.rates[k] * t / (1.0 - pinv);
+    expd[threadIdx.x] = expm1(x);
+  }
+  __syncthreads();
+
+  double * out = pmat + ((size_t)m * K + k) * states * sp;
+  for (unsigned int idx = threadIdx.x; idx < states * sp; idx += blockDim.x)
+  {
+    const unsigned int i = idx / sp, j = idx % sp;
+    double v = 0.0;
+    if (j < states)
+    {
+      v = (i == j) ? 1.0 : 0.0;
+      if (t > 0.0)
+        for (unsigned int q = 0; q < states; ++q) v += (s_inv[i * sp + q] * expd[q]) * s_ev[q * sp + j];
+    }
+    out[idx] = v;
+    if (pmat_il) /* 4-state: [m][i][k][j] */
+      pmat_il[(size_t)m * K * 16 + (i * K + k) * 4 + j] = v;
+  }
+}
+
+bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
+                    const unsigned int * matrix_indices, const double * branch_lengths,
+                    unsigned int count)
+{
+  pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats, s = p->states, sp = p->states_padded;
+  if (K > PM_MAXK)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats > %d is not supported.", PM_MAXK);
+    return false;
+  }
+  PmatArgs a;
+  for (unsigned int k = 0; k < K; ++k)
+  {
+    a.params_idx[k] = params_indices[k];
+    a.rates[k] = p->rates[k];
+    a.pinv[k] = p->prop_invar[params_indices[k]];
+  }
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    if (matrix_indices[i] >= p->prob_matrices || !(branch_lengths[i] >= 0.0))
+    {
+      pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid matrix index %u or branch length %g.",
+                        matrix_indices[i], branch_lengths[i]);
+      return false;
+    }
+  }
+  const unsigned int * d_idx = (const unsigned int *)dev_stage(c, matrix_indices, sizeof(unsigned int) * count);
+  const double * d_len = (const double *)dev_stage(c, branch_lengths, sizeof(double) * count);
+  if (!d_idx || !d_len) return false;
+  unsigned int threads = ((s * sp + 31) / 32) * 32;
+  if (threads > 512) threads = 512;
+  const size_t smem = sizeof(double) * (sp + 2 * s * sp);
+  pmatrix_kernel<<<count * K, threads, smem, c->stream>>>(c->d_pmat, c->d_pmat_il, c->d_eigen,
+                                                          c->eigen_stride, d_idx, d_len, s, sp, K, a);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "pmatrix_kernel launch");
+}

@@ -1,0 +1,242 @@
+"""GPU parity tests: the CUDA path (through the C ABI, via the same-source harness) against
+(a) the committed golden fixtures produced by the unmodified reference (tests/golden/ref_cases.json),
+(b) the compiled reference itself (oracle/_ref) on the same seeded inputs, when it travelled.
+
+Tolerances (BASELINE.json north_star): logL 1e-8 relative, derivatives 1e-6 relative (absolute floor
+1e-9 where |value| < 1e-3), scaler counts exact away from the 2^-256 threshold.
+"""
+import json
+import os
+
+import numpy as np
+import pytest
+
+from pllharness import (ATTR_PATTERN_TIP, ATTR_RATE_SCALERS, BLO_NEWTON_FAST, BLO_NEWTON_OLDFAST,
+                        BLO_NEWTON_SAFE, Harness, have_reference, load_product_package)
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_cases.json")))
+
+
+def rel(a, b):
+    return abs(a - b) / max(abs(b), 1e-300)
+
+
+def assert_deriv_close(a, b):
+    a, b = np.asarray(a), np.asarray(b)
+    tol = np.where(np.abs(b) < 1e-3, 1e-9, 1e-6 * np.abs(b))
+    assert np.all(np.abs(a - b) <= tol), (a, b)
+
+
+def fix_args(kw):
+    kw = dict(kw)
+    return kw
+
+
+@pytest.mark.parametrize("name", sorted(GOLD.keys()))
+def test_against_golden(name):
+    case = GOLD[name]
+    ref = case["ref"]
+    kw = fix_args(case["args"])
+    with Harness("b200", **kw) as h:
+        ll = h.loglh()
+        assert rel(ll, ref["loglh"]) < 1e-8, (ll, ref["loglh"])
+        np.testing.assert_allclose(h.partition_loglh(), ref["partition_loglh"], rtol=1e-8)
+        r = h.root()
+        df, ddf = h.derivatives(r, ref["deriv_brlens"])
+        assert_deriv_close(df, ref["df"])
+        assert_deriv_close(ddf, ref["ddf"])
+        sc = [int(h.scaler(i).sum()) for i in range(kw["tips"] - 2)]
+        assert sc == ref["scaler_sums"]
+        info = h.node_info(r)
+        assert rel(float(h.clv(info["clv"]).sum()), ref["root_clv_sum"]) < 1e-9
+        np.testing.assert_allclose(h.rates(), ref["rates"], rtol=1e-13)
+        np.testing.assert_allclose(h.pmatrix(0).ravel()[:16], ref["pmatrix0"], rtol=1e-9, atol=1e-14)
+        blo = h.optimize_branch_lengths(method=0, radius=-1, max_iters=2, lh_epsilon=0.1)
+        assert rel(blo, ref["blo_fast"]) < 1e-8, (blo, ref["blo_fast"])
+        np.testing.assert_allclose(h.branch_lengths(), ref["blo_brlens"], atol=1e-5, rtol=1e-5)
+
+
+needs_ref = pytest.mark.skipif(not have_reference(), reason="oracle/_ref not built")
+
+
+def pair(**kw):
+    return Harness("ref", **kw), Harness("b200", **kw)
+
+
+@needs_ref
+@pytest.mark.parametrize("kw", [
+    dict(tips=16, sites=10000),                                  # BASELINE config 1
+    dict(tips=7, sites=33, rate_cats=2),                         # ragged: not a multiple of anything
+    dict(tips=5, sites=1, rate_cats=4),                          # single site
+    dict(tips=64, sites=4097, rate_cats=8),
+    dict(tips=30, sites=513, attributes=0),                      # tip CLVs instead of tip patterns
+    dict(tips=100, sites=2000, brlen_scale=10.0),                # deep tree: scaling active
+    dict(tips=100, sites=2000, brlen_scale=10.0, attributes=ATTR_PATTERN_TIP | ATTR_RATE_SCALERS),
+    dict(tips=24, sites=400, states=20),                         # protein LG+G4, generic kernels
+    dict(tips=12, sites=300, states=7, rate_cats=3),             # odd state count (padding)
+    dict(tips=16, sites=1000, pinv=0.3),
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_clvs_scalers_logl_match_reference(kw):
+    ref, dev = pair(**kw)
+    with ref, dev:
+        lr, ld = ref.loglh(), dev.loglh()
+        assert rel(ld, lr) < 1e-8, (ld, lr)
+        tips = kw["tips"]
+        thr = 2.0 ** -256
+        for i in range(tips - 2):
+            cr, cd = ref.clv(tips + i), dev.clv(tips + i)
+            sr, sd = ref.scaler(i), dev.scaler(i)
+            if not np.array_equal(sr, sd):
+                # only sites whose unscaled maximum sits at the threshold may differ
+                bad = np.nonzero(sr != sd)[0]
+                per_rate = bool(kw.get("attributes", ATTR_PATTERN_TIP) & ATTR_RATE_SCALERS)
+                K = kw.get("rate_cats", 4)
+                for b in bad:
+                    site = b // K if per_rate else b
+                    m = cr[site].max()
+                    assert abs(m / thr - 1) < 1e-8 or abs(m * thr - 1) < 1e-8 or abs(m / thr / thr - 1) < 1e-8, \
+                        (i, b, m)
+            else:
+                np.testing.assert_allclose(cd, cr, rtol=1e-10, atol=0)
+        for m in range(2 * tips - 3):
+            np.testing.assert_allclose(dev.pmatrix(m), ref.pmatrix(m), rtol=1e-9, atol=1e-15)
+
+
+@needs_ref
+@pytest.mark.parametrize("kw", [
+    dict(tips=16, sites=5000),
+    dict(tips=40, sites=1500, pinv=0.25),
+    dict(tips=12, sites=300, states=20),
+    dict(tips=60, sites=1000, brlen_scale=10.0, attributes=ATTR_PATTERN_TIP | ATTR_RATE_SCALERS),
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_sumtable_and_derivatives_every_edge(kw):
+    """Re-root on several edges (tip edges and inner edges), compare sumtable + d/dd at 6 lengths."""
+    ref, dev = pair(**kw)
+    brl = [1e-4, 1e-3, 0.01, 0.1, 1.0, 10.0]
+    with ref, dev:
+        nsub = kw["tips"] + 3 * (kw["tips"] - 2)
+        rng = np.random.RandomState(1)
+        for node in rng.choice(np.arange(kw["tips"], nsub), size=6, replace=False):
+            for h in (ref, dev):
+                h.set_root(int(node))
+            lr, ld = ref.loglh(), dev.loglh()
+            assert rel(ld, lr) < 1e-8
+            root = ref.root()
+            assert root == dev.root()
+            dfr, ddfr = ref.derivatives(root, brl)
+            dfd, ddfd = dev.derivatives(root, brl)
+            assert_deriv_close(dfd, dfr)
+            assert_deriv_close(ddfd, ddfr)
+            np.testing.assert_allclose(dev.sumtable(), ref.sumtable(), rtol=1e-9, atol=1e-300)
+
+
+@needs_ref
+@pytest.mark.parametrize("method", [BLO_NEWTON_FAST, BLO_NEWTON_SAFE, BLO_NEWTON_OLDFAST])
+def test_branch_length_optimisation_matches(method):
+    kw = dict(tips=24, sites=3000)
+    ref, dev = pair(**kw)
+    with ref, dev:
+        ref.loglh(), dev.loglh()
+        a = ref.optimize_branch_lengths(method=method, radius=-1, max_iters=3, lh_epsilon=0.01)
+        b = dev.optimize_branch_lengths(method=method, radius=-1, max_iters=3, lh_epsilon=0.01)
+        assert rel(b, a) < 1e-8, (b, a)
+        # every branch within the NR tolerance (bl_min/10, pll_optimize.c:1823-1825)
+        np.testing.assert_allclose(dev.branch_lengths(), ref.branch_lengths(), atol=1e-5, rtol=1e-6)
+        assert rel(dev.loglh(), ref.loglh()) < 1e-8
+
+
+@needs_ref
+def test_single_partition_legacy_blo_and_radius():
+    kw = dict(tips=20, sites=2000)
+    ref, dev = pair(**kw)
+    with ref, dev:
+        ref.loglh(), dev.loglh()
+        for radius in (0, 1, 3):
+            a = ref.optimize_branch_lengths_single(radius=radius, smoothings=1, tolerance=0.1)
+            b = dev.optimize_branch_lengths_single(radius=radius, smoothings=1, tolerance=0.1)
+            assert rel(b, a) < 1e-8, (radius, b, a)
+            np.testing.assert_allclose(dev.branch_lengths(), ref.branch_lengths(), atol=1e-5, rtol=1e-6)
+
+
+@needs_ref
+def test_partial_traversals_match_full_and_reference():
+    """SPR-like usage: perturb an edge, re-root there, evaluate incrementally (few ops)."""
+    kw = dict(tips=50, sites=1200)
+    ref, dev = pair(**kw)
+    with ref, dev:
+        ref.loglh(), dev.loglh()
+        nsub = kw["tips"] + 3 * (kw["tips"] - 2)
+        rng = np.random.RandomState(3)
+        for step in range(12):
+            node = int(rng.randint(kw["tips"], nsub))
+            newlen = float(rng.uniform(0.01, 0.5))
+            for h in (ref, dev):
+                h.perturb_edge(node, newlen)
+                h.set_root(node)
+            c0 = dev.ops_counter()
+            lr, ld = ref.loglh(1), dev.loglh(1)
+            assert rel(ld, lr) < 1e-8, (step, ld, lr)
+            assert dev.ops_counter() - c0 < kw["tips"] - 2   # really partial
+            assert rel(dev.loglh(0), ld) < 1e-10              # incremental == full
+
+
+@needs_ref
+def test_multi_partition_mixed_models_linked_and_unlinked():
+    for linkage in (0, 2):
+        kw = dict(tips=20, sites=[700, 300, 450, 64], states=[4, 20, 4, 20], alpha=[0.3, 0.6, 1.0, 2.0],
+                  linkage=linkage)
+        ref, dev = pair(**kw)
+        with ref, dev:
+            assert rel(dev.loglh(), ref.loglh()) < 1e-8
+            np.testing.assert_allclose(dev.partition_loglh(), ref.partition_loglh(), rtol=1e-8)
+            a = ref.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.1)
+            b = dev.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.1)
+            assert rel(b, a) < 1e-8, (linkage, b, a)
+
+
+@needs_ref
+def test_persite_root_and_alpha_change():
+    kw = dict(tips=16, sites=900)
+    ref, dev = pair(**kw)
+    with ref, dev:
+        vr, pr = ref.loglh_persite()
+        vd, pd = dev.loglh_persite()
+        assert rel(vd, vr) < 1e-8
+        np.testing.assert_allclose(pd, pr, rtol=1e-9)
+        root = ref.root()
+        back = ref.node_info(root)["back"]
+        node = root if not ref.node_info(root)["tip"] else back
+        assert rel(dev.root_loglh(node), ref.root_loglh(node)) < 1e-8
+        for alpha in (0.1, 2.5):
+            ref.set_alpha(alpha), dev.set_alpha(alpha)
+            assert rel(dev.loglh(), ref.loglh()) < 1e-8
+
+
+def test_update_partials_symbol_and_no_cpu_fallback():
+    pkg = load_product_package()
+    assert pkg.device_count() >= 1
+    with Harness("b200", tips=10, sites=500) as h:
+        pkg.reset_stats()
+        assert h.update_partials_only(0) == 1
+        s = pkg.stats()
+        assert s["kernel_launches"] >= 2          # P-matrix batch + traversal kernel
+        assert h.loglh(1) < 0
+
+
+def test_large_full_size_properties():
+    """Size-independent properties at a size the CPU oracle would need minutes for:
+    logL is additive over site slices and invariant under re-rooting."""
+    kw = dict(tips=64, sites=200000)
+    with Harness("b200", **kw) as h:
+        full = h.loglh()
+        parts = 0.0
+        for r in range(4):
+            with Harness("b200", rank=r, nranks=4, **kw) as s:
+                parts += s.loglh()
+        assert rel(parts, full) < 1e-10
+        nsub = kw["tips"] + 3 * (kw["tips"] - 2)
+        for node in (kw["tips"], kw["tips"] + 17, nsub - 1):
+            h.set_root(node)
+            assert rel(h.loglh(), full) < 1e-9
