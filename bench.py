@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""bench.py — CLV site-updates/s of the phylogenetic-likelihood hot path on B200 (BASELINE.json metric).
+
+Workload (config.workload): BASELINE.json configs[1] — DNA GTR+G4, 1000 taxa x 1 M sites, full
+post-order traversal (998 CLV updates per site) + P-matrix rebuild + edge log-likelihood, i.e. one
+`pllmod_treeinfo_compute_loglh(treeinfo, 0)` per step; synthetic alignment/tree per SURVEY.md §8d.
+With --gpus N (torchrun) every rank owns its own contiguous 1 M-site slice of an N M-site alignment
+(weak scaling); the only cross-GPU traffic is the all-reduce of the per-partition logL scalar.
+
+  value   = CLV site-updates/s (whole job), device-timed with CUDA events on the library's stream,
+            inputs resident in HBM (tip codes, P-matrix inputs staged before the events)
+  e2e     = the same metric through the public C-ABI call from host data: new branch lengths are set
+            on the host tree, pllmod_treeinfo_compute_loglh uploads op list + branch lengths and the
+            logL comes back to the host; wall-clock, max over ranks
+  roofline= the traversal kernel alone: algorithmic bytes (396/265/134 B per site for ii/ti/tt ops)
+            / CUDA-event launch duration vs MEASURED_PEAKS.json hbm_gbs
+  cpu_baseline / --impl reference = the UNMODIFIED reference (oracle/_ref, AVX2, one site slice per
+            host thread — the reference's own parallel_reduce_cb model) on a bounded site sample
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+BYTES = {"ii": 396, "ti": 265, "tt": 134}
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--tips", type=int, default=1000)
+    ap.add_argument("--sites", type=int, default=1000000)
+    ap.add_argument("--cpu-sites-per-core", type=int, default=4000)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--blo", action="store_true", help="also time one NR smoothing pass (extra keys)")
+    return ap.parse_args()
+
+
+def measured_peak():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = sorted(int(float(r[0])) for r in self.rows if r and r[0].replace(".", "").isdigit())
+        mx = [int(float(r[1])) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        reasons = set()
+        for r in self.rows:
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        # under load = upper half of the samples (the sampler also sees idle gaps)
+        load = sm[len(sm) // 2:] if sm else []
+        return {"sm_mhz": load[len(load) // 2] if load else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_run(tips, sites_per_core, reps, max_cores=None):
+    """Times the unmodified reference (AVX2) on a bounded sample: one site slice per host thread."""
+    from pllharness import Harness, have_reference
+    if not have_reference():
+        return None
+    cores = os.cpu_count() or 1
+    try:
+        cores = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
+    if max_cores:
+        cores = min(cores, max_cores)
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+        per_core = (tips - 2) * sites_per_core * 128 * 1.2
+        cores = max(1, min(cores, int(avail * 0.5 / per_core)))
+    except Exception:
+        pass
+    total_sites = sites_per_core * cores
+    hs = [None] * cores
+    times = [0.0] * cores
+
+    def setup(i):
+        hs[i] = Harness("ref", tips=tips, sites=total_sites, rank=i, nranks=cores)
+
+    def run(i):
+        times[i] = hs[i].time_update_partials(reps)
+
+    def fan(fn):
+        th = [threading.Thread(target=fn, args=(i,)) for i in range(cores)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+
+    fan(setup)
+    fan(run)            # warm-up (includes the first compute_loglh)
+    t0 = time.perf_counter()
+    fan(run)
+    wall = (time.perf_counter() - t0) / reps
+    for h in hs:
+        h.close()
+    updates = (tips - 2) * total_sites
+    return {"value": updates / wall, "unit": "CLV site-updates/s", "cores": cores, "kind": "reference",
+            "sample": "%d taxa x %d sites (%d sites/thread), full traversal via pll_update_partials, "
+                      "libpll AVX2 kernels, best-effort %d reps" % (tips, total_sites, sites_per_core, reps),
+            "seconds_per_traversal": wall}
+
+
+def main():
+    a = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if a.impl == "reference":
+        if rank != 0:
+            return 0
+        res = cpu_reference_run(a.tips, a.cpu_sites_per_core, max(1, a.steps))
+        if res is None:
+            print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built on this box"}))
+            return 0
+        line = {"impl": "reference", "metric": "CLV site-updates/sec", "value": res["value"],
+                "unit": "CLV site-updates/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+                "ms_per_step": res["seconds_per_traversal"] * 1e3, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "DNA GTR+G4, %d taxa, full traversal (CPU sample)" % a.tips,
+                           "l2": "inputs larger than L2"},
+                "cpu_baseline": res,
+                "e2e": {"value": res["value"], "unit": "CLV site-updates/s", "h2d_bytes_per_step": 0,
+                        "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from pllharness import Harness, load_product_package
+
+    pkg = load_product_package()
+    if not torch.cuda.is_available() or pkg.device_count() < 1:
+        raise SystemExit("bench.py needs a CUDA device: libpll_b200 has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    pkg.load().pllb200_set_device(local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    tips, S = a.tips, a.sites
+    t_setup = time.perf_counter()
+    # weak scaling: a global alignment of world*S sites, this rank owns slice `rank`
+    h = Harness("b200", tips=tips, sites=S * world, rank=rank, nranks=world)
+    stream = torch.cuda.Stream()
+    pkg.load().pllb200_partition_set_stream(h.partition_ptr(0), stream.cuda_stream)
+
+    red_buf = torch.zeros(8, dtype=torch.float64, device="cuda")
+
+    def reduce_cb(view, op):
+        n = len(view)
+        t = torch.from_numpy(np.array(view, copy=True)).to("cuda", non_blocking=False)
+        dist.all_reduce(t, op={0: dist.ReduceOp.SUM, 1: dist.ReduceOp.MAX, 2: dist.ReduceOp.MIN}[op])
+        view[:] = t.cpu().numpy()[:n]
+
+    if world > 1:
+        h.set_reduce_cb(reduce_cb)
+
+    ll0 = h.loglh(0)            # first full evaluation: uploads tips, builds everything
+    setup_s = time.perf_counter() - t_setup
+    counts = h.op_type_counts()
+    alg_bytes = sum(BYTES[k] * counts[k] for k in counts) * S
+    updates_per_step = (tips - 2) * S
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-timed value: K steps of compute_loglh(0) --------------------------------------
+    for _ in range(a.warmup):
+        h.loglh(0)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    barrier()
+    pkg.reset_stats()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record(stream)
+    for _ in range(a.steps):
+        ll = h.loglh(0)
+    ev1.record(stream)
+    barrier()
+    dev_ms = ev0.elapsed_time(ev1) / a.steps
+    st = pkg.stats()
+    launches = st["kernel_launches"]
+
+    # ---- traversal kernel alone (roofline) -------------------------------------------------------
+    kev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
+    for e0, e1 in kev:
+        e0.record(stream)
+        h.queue_update_partials()
+        e1.record(stream)
+    torch.cuda.synchronize()
+    kern_ms = sorted(e0.elapsed_time(e1) for e0, e1 in kev)
+    kern_avg = sum(kern_ms) / len(kern_ms)
+
+    # ---- e2e: host branch lengths -> public API -> logL on host, wall clock ----------------------
+    brl = h.branch_lengths()
+    rng = np.random.RandomState(1234)
+    pkg.reset_stats()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        h.set_branch_lengths(brl * rng.uniform(0.9, 1.1, size=brl.shape))
+        ll_e2e = h.loglh(0)
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / a.steps
+    st2 = pkg.stats()
+    clocks = sampler.stop()
+
+    extra = {}
+    if a.blo:
+        h.set_branch_lengths(brl)
+        h.loglh(0)
+        barrier()
+        t0 = time.perf_counter()
+        nll = h.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)
+        barrier()
+        extra["blo_one_smoothing_s"] = time.perf_counter() - t0
+        extra["blo_neg_loglh"] = nll
+
+    # max over ranks
+    if world > 1:
+        t = torch.tensor([dev_ms, e2e_s, kern_avg], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dev_ms, e2e_s, kern_avg = [float(x) for x in t.cpu()]
+    peak, peak_kind = measured_peak()
+    achieved = alg_bytes / (kern_avg * 1e-3) / 1e9
+
+    if rank == 0:
+        line = {
+            "metric": "CLV site-updates/sec", "value": updates_per_step * world / (dev_ms * 1e-3),
+            "unit": "CLV site-updates/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dev_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "DNA GTR+G4, %d taxa x %d sites per GPU, full traversal + P-matrices + edge logL "
+                                   "(pllmod_treeinfo_compute_loglh, BASELINE configs[1])" % (tips, S),
+                       "sites_per_gpu": S, "taxa": tips, "ops": counts, "parallelism": "site-sharded x%d" % world,
+                       "l2": "inputs larger than L2 (%.1f GB of CLVs per step)" % ((tips - 2) * S * 128 / 1e9),
+                       "setup_s": round(setup_s, 2)},
+            "e2e": {"value": updates_per_step * world / e2e_s, "unit": "CLV site-updates/s",
+                    "h2d_bytes_per_step": st2["h2d_bytes"] // a.steps, "d2h_bytes_per_step": st2["d2h_bytes"] // a.steps,
+                    "ms_per_step": e2e_s * 1e3,
+                    "what": "host tree with new branch lengths -> pllmod_treeinfo_compute_loglh -> logL on host"},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "peak_kind": peak_kind, "kernel": "trav_dna_kernel<4,false>",
+                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kern_avg,
+                         "kernel_share_of_step": kern_avg / dev_ms},
+            "clocks": clocks, "loglh": ll, "loglh_first": ll0,
+        }
+        line.update(extra)
+        if not a.no_cpu_baseline and world == 1:
+            cb = cpu_reference_run(tips, a.cpu_sites_per_core, 2)
+            if cb:
+                line["cpu_baseline"] = cb
+        print(json.dumps(line))
+    h.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -582,3 +582,20 @@ void h_perturb_edge(void * hv, unsigned int node_index, double new_length)
 }
 
 unsigned int h_ops_counter(void * hv) { return ((harness_t *)hv)->ti->counter; }
+
+/* {tip-tip, tip-inner, inner-inner} operation counts of the last traversal of partition p and the
+ * number of ops; used by bench.py to turn a launch into algorithmic bytes */
+void h_op_type_counts(void * hv, unsigned int p, unsigned int nops, unsigned int * out)
+{
+  harness_t * h = (harness_t *)hv;
+  const pll_partition_t * part = h->parts[p];
+  const int pattern = (part->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
+  out[0] = out[1] = out[2] = 0;
+  for (unsigned int i = 0; i < nops; ++i)
+  {
+    const pll_operation_t * o = &h->ti->operations[i];
+    const int t1 = pattern && o->child1_clv_index < part->tips;
+    const int t2 = pattern && o->child2_clv_index < part->tips;
+    out[t1 && t2 ? 0 : ((t1 || t2) ? 1 : 2)]++;
+  }
+}

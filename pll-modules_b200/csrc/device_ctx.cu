@@ -333,6 +333,7 @@ bool dev_flush(PartCtx * c)
 {
   CUDA_TRY(cudaStreamSynchronize(c->stream), false);
   for (const PendingResult & r : c->pending) *r.host_dst = c->h_result[r.slot * 4 + r.comp];
+  g_d2h_bytes += sizeof(double) * c->pending.size(); /* written by the kernel into mapped host memory */
   c->pending.clear();
   return true;
 }

@@ -108,6 +108,7 @@ def _lib(kind):
         lib.h_treeinfo.restype = C.c_void_p
         lib.h_treeinfo.argtypes = [C.c_void_p]
         lib.h_set_reduce_cb.argtypes = [C.c_void_p, C.c_void_p, REDUCE_CB]
+        lib.h_op_type_counts.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p]
         lib.h_ops_counter.restype = C.c_uint
         lib.h_ops_counter.argtypes = [C.c_void_p]
         _libs[kind] = lib
@@ -264,6 +265,11 @@ class Harness:
             fn(view, op)
         self._cb = REDUCE_CB(_cb)
         self.lib.h_set_reduce_cb(self.h, None, self._cb)
+
+    def op_type_counts(self, p=0):
+        out = np.zeros(3, dtype=np.uint32)
+        self.lib.h_op_type_counts(self.h, p, self.tips - 2, out.ctypes.data)
+        return dict(tt=int(out[0]), ti=int(out[1]), ii=int(out[2]))
 
     def ops_counter(self):
         return self.lib.h_ops_counter(self.h)

@@ -129,7 +129,10 @@ def test_sumtable_and_derivatives_every_edge(kw):
             dfd, ddfd = dev.derivatives(root, brl)
             assert_deriv_close(dfd, dfr)
             assert_deriv_close(ddfd, ddfr)
-            np.testing.assert_allclose(dev.sumtable(), ref.sumtable(), rtol=1e-9, atol=1e-300)
+            # the eigenbasis order/sign is solver-specific: compare basis-invariant views
+            sd, sr = np.sort(dev.sumtable(), axis=-1), np.sort(ref.sumtable(), axis=-1)
+            scale = np.abs(sr).max(axis=-1, keepdims=True) + 1e-300
+            assert np.max(np.abs(sd - sr) / scale) < 1e-9
 
 
 @needs_ref
