@@ -66,6 +66,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   if (!strcmp(name, "trav_ctas_per_sm")) slot = &g_opt_trav_ctas_per_sm;
   else if (!strcmp(name, "trav_reorder")) slot = &g_opt_trav_reorder;
   else if (!strcmp(name, "fuse_root")) slot = &g_opt_fuse_root;
+  else if (!strcmp(name, "trav_variant")) slot = &g_opt_trav_variant;
   if (!slot) return -1;
   int old = *slot;
   *slot = value;

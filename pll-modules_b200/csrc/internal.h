@@ -91,6 +91,7 @@ struct PartCtx
   /* scratch for op-list scheduling */
   std::vector<pll_operation_t> op_scratch;
   std::vector<int> idx_scratch;
+  std::vector<unsigned long long> devop_scratch; /* resolved ops for the 4-state traversal kernel */
 };
 
 static inline PartCtx * ctx_of(pll_partition_t * p) { return reinterpret_cast<PartCtx *>(p); }
@@ -115,6 +116,7 @@ extern unsigned long long g_d2h_bytes;
 extern int g_opt_trav_ctas_per_sm;
 extern int g_opt_trav_reorder;
 extern int g_opt_fuse_root;
+extern int g_opt_trav_variant;
 
 /* device context (device_ctx.cu) */
 bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */
@@ -146,6 +148,7 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
                     const unsigned int * matrix_indices, const double * branch_lengths,
                     unsigned int count);
 bool launch_partials(PartCtx * c, const pll_operation_t * ops, unsigned int count);
+bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int count); /* k_traversal_dna.cu */
 bool launch_edge_logl(PartCtx * c, unsigned int parent_clv, int parent_scaler,
                       unsigned int child_clv, int child_scaler, unsigned int matrix_index,
                       const unsigned int * freqs_indices, double * d_persite, int slot);

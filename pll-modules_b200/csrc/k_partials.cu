@@ -26,216 +26,12 @@
  * Algorithmic bytes per site and op (DNA, Gamma4, per-site scalers): ii 396, ti 265, tt 134.
  *
  * Generic path (any state count <= 64, any K <= 32): one launch per operation, thread = (site,cat).
+ * The 4-state site-column kernel itself lives in k_traversal_dna.cu.
  */
 #include "internal.h"
 #include "devutil.cuh"
 
 #include <algorithm>
-
-struct TravArgs
-{
-  const pll_operation_t * ops;
-  unsigned int nops;
-  double * clv;
-  unsigned long long clv_stride;
-  unsigned int clv_first;
-  unsigned int * scaler;
-  unsigned long long scaler_stride;
-  const double * pmat_il;
-  const unsigned char * tipchars;
-  unsigned long long tip_stride;
-  unsigned int tips_pattern; /* #tips when PATTERN_TIP, else 0 */
-  unsigned int sites;        /* sites_alloc */
-};
-
-/* one side of the product for one element: x[i] = sum_j M_k[i][j] * v[j]  (inner child) */
-template <int K>
-__device__ __forceinline__ void side_inner(const double * sM, int k, const d4 & v, double x[4])
-{
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-  {
-    const double2 a = *reinterpret_cast<const double2 *>(sM + (i * K + k) * 4);
-    const double2 b = *reinterpret_cast<const double2 *>(sM + (i * K + k) * 4 + 2);
-    x[i] = a.x * v.x + a.y * v.y + b.x * v.z + b.y * v.w;
-  }
-}
-/* tip child: x[i] = sum over the states set in the 4-bit code of M_k[i][j] */
-template <int K>
-__device__ __forceinline__ void side_tip(const double * sM, int k, unsigned int code, double x[4])
-{
-#pragma unroll
-  for (int i = 0; i < 4; ++i)
-  {
-    const double2 a = *reinterpret_cast<const double2 *>(sM + (i * K + k) * 4);
-    const double2 b = *reinterpret_cast<const double2 *>(sM + (i * K + k) * 4 + 2);
-    double t = 0.0;
-    if (code & 1u) t += a.x;
-    if (code & 2u) t += a.y;
-    if (code & 4u) t += b.x;
-    if (code & 8u) t += b.y;
-    x[i] = t;
-  }
-}
-
-#define TRAV_WARPS 8
-#define TRAV_R 1 /* elements per lane per chunk */
-#define TRAV_MIN_CTAS 4 /* 64 registers -> 32 resident warps per SM */
-
-template <int K, bool RATE_SCALERS>
-__global__ void __launch_bounds__(TRAV_WARPS * 32, TRAV_MIN_CTAS) trav_dna_kernel(TravArgs a)
-{
-  /* per warp: 2 stages x (L,R) x 16*K doubles */
-  __shared__ __align__(16) double s_mat[TRAV_WARPS][2][2][16 * K];
-
-  const int lane = threadIdx.x & 31;
-  const int warp = threadIdx.x >> 5;
-  const int k = lane % K;
-  const unsigned long long E = (unsigned long long)a.sites * K;
-  const unsigned long long chunk_elems = 32ull * TRAV_R;
-  const unsigned long long nchunks = (E + chunk_elems - 1) / chunk_elems;
-  const unsigned long long gwarp = (unsigned long long)blockIdx.x * TRAV_WARPS + warp;
-  const unsigned long long nwarps = (unsigned long long)gridDim.x * TRAV_WARPS;
-
-  for (unsigned long long chunk = gwarp; chunk < nchunks; chunk += nwarps)
-  {
-    unsigned long long e[TRAV_R];
-    bool act[TRAV_R];
-#pragma unroll
-    for (int r = 0; r < TRAV_R; ++r)
-    {
-      e[r] = chunk * chunk_elems + (unsigned long long)r * 32 + lane;
-      act[r] = e[r] < E;
-    }
-
-    for (unsigned int o = 0; o < a.nops; ++o)
-    {
-      const uint4 * op4 = reinterpret_cast<const uint4 *>(a.ops + o);
-      const uint4 oa = __ldg(op4);
-      const uint4 ob = __ldg(op4 + 1);
-      const unsigned int p_clv = oa.x;
-      const int p_sc = (int)oa.y;
-      const unsigned int c1_clv = oa.z, c1_mat = oa.w;
-      const int c1_sc = (int)ob.x;
-      const unsigned int c2_clv = ob.y, c2_mat = ob.z;
-      const int c2_sc = (int)ob.w;
-      const bool tip1 = c1_clv < a.tips_pattern;
-      const bool tip2 = c2_clv < a.tips_pattern;
-
-      /* ---- issue all global loads of this op ---- */
-      double * sL = s_mat[warp][o & 1][0];
-      double * sR = s_mat[warp][o & 1][1];
-      const double2 * gL = reinterpret_cast<const double2 *>(a.pmat_il + (unsigned long long)c1_mat * 16 * K);
-      const double2 * gR = reinterpret_cast<const double2 *>(a.pmat_il + (unsigned long long)c2_mat * 16 * K);
-      double2 mL[(8 * K + 31) / 32], mR[(8 * K + 31) / 32];
-#pragma unroll
-      for (int u = 0; u < (8 * K + 31) / 32; ++u)
-      {
-        const int idx = u * 32 + lane;
-        if (idx < 8 * K)
-        {
-          mL[u] = __ldg(gL + idx);
-          mR[u] = __ldg(gR + idx);
-        }
-      }
-
-      d4 vl[TRAV_R], vr[TRAV_R];
-      unsigned int cl[TRAV_R], cr[TRAV_R];
-      unsigned int sc[TRAV_R];
-#pragma unroll
-      for (int r = 0; r < TRAV_R; ++r)
-      {
-        cl[r] = cr[r] = 15u;
-        sc[r] = 0;
-        vl[r] = vr[r] = d4{0, 0, 0, 0};
-        if (act[r])
-        {
-          const unsigned long long site = e[r] / K;
-          if (tip1)
-            cl[r] = a.tipchars[(unsigned long long)c1_clv * a.tip_stride + site];
-          else
-            vl[r] = ldg256(a.clv + (unsigned long long)(c1_clv - a.clv_first) * a.clv_stride + e[r] * 4);
-          if (tip2)
-            cr[r] = a.tipchars[(unsigned long long)c2_clv * a.tip_stride + site];
-          else
-            vr[r] = ldg256(a.clv + (unsigned long long)(c2_clv - a.clv_first) * a.clv_stride + e[r] * 4);
-          if (p_sc >= 0)
-          {
-            const unsigned long long si = RATE_SCALERS ? e[r] : site;
-            if (RATE_SCALERS || k == 0)
-            {
-              if (c1_sc >= 0) sc[r] += a.scaler[(unsigned long long)c1_sc * a.scaler_stride + si];
-              if (c2_sc >= 0) sc[r] += a.scaler[(unsigned long long)c2_sc * a.scaler_stride + si];
-            }
-          }
-        }
-      }
-
-      /* ---- stage matrices for the warp ---- */
-#pragma unroll
-      for (int u = 0; u < (8 * K + 31) / 32; ++u)
-      {
-        const int idx = u * 32 + lane;
-        if (idx < 8 * K)
-        {
-          reinterpret_cast<double2 *>(sL)[idx] = mL[u];
-          reinterpret_cast<double2 *>(sR)[idx] = mR[u];
-        }
-      }
-      __syncwarp();
-
-      /* ---- compute ---- */
-      double * pdst = a.clv + (unsigned long long)(p_clv - a.clv_first) * a.clv_stride;
-#pragma unroll
-      for (int r = 0; r < TRAV_R; ++r)
-      {
-        double xl[4], xr[4];
-        if (tip1)
-          side_tip<K>(sL, k, cl[r], xl);
-        else
-          side_inner<K>(sL, k, vl[r], xl);
-        if (tip2)
-          side_tip<K>(sR, k, cr[r], xr);
-        else
-          side_inner<K>(sR, k, vr[r], xr);
-        d4 out;
-        out.x = xl[0] * xr[0];
-        out.y = xl[1] * xr[1];
-        out.z = xl[2] * xr[2];
-        out.w = xl[3] * xr[3];
-
-        if (p_sc >= 0)
-        {
-          int flag = 0;
-          if (!(tip1 && tip2))
-          {
-            flag = (out.x < SCALE_THRESHOLD_D) & (out.y < SCALE_THRESHOLD_D) &
-                   (out.z < SCALE_THRESHOLD_D) & (out.w < SCALE_THRESHOLD_D);
-            if (!RATE_SCALERS)
-            {
-#pragma unroll
-              for (int off = 1; off < K; off <<= 1) flag &= __shfl_xor_sync(0xffffffffu, flag, off);
-            }
-            if (flag)
-            {
-              out.x *= SCALE_FACTOR_D;
-              out.y *= SCALE_FACTOR_D;
-              out.z *= SCALE_FACTOR_D;
-              out.w *= SCALE_FACTOR_D;
-            }
-          }
-          if (act[r] && (RATE_SCALERS || k == 0))
-          {
-            const unsigned long long si = RATE_SCALERS ? e[r] : e[r] / K;
-            a.scaler[(unsigned long long)p_sc * a.scaler_stride + si] = sc[r] + (unsigned int)flag;
-          }
-        }
-        if (act[r]) stg256(pdst + e[r] * 4, out);
-      }
-    }
-    __syncwarp();
-  }
-}
 
 /* ------------------------------------------------------------------------------------------ */
 /* generic path: any states, any K; one operation per launch                                   */
@@ -405,36 +201,6 @@ static const pll_operation_t * schedule_ops(PartCtx * c, const pll_operation_t *
   return c->op_scratch.size() == count ? c->op_scratch.data() : ops;
 }
 
-template <int K>
-static bool launch_trav_dna(PartCtx * c, const TravArgs & a, bool rate_scalers)
-{
-  static int ctas_per_sm_cache[2] = {0, 0};
-  const int ri = rate_scalers ? 1 : 0;
-  if (!ctas_per_sm_cache[ri])
-  {
-    int nb = 0;
-    cudaError_t e = rate_scalers
-        ? cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, trav_dna_kernel<K, true>, TRAV_WARPS * 32, 0)
-        : cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, trav_dna_kernel<K, false>, TRAV_WARPS * 32, 0);
-    if (e != cudaSuccess || nb < 1) nb = 2;
-    ctas_per_sm_cache[ri] = nb;
-  }
-  int per_sm = g_opt_trav_ctas_per_sm > 0 ? std::min(g_opt_trav_ctas_per_sm, ctas_per_sm_cache[ri])
-                                          : ctas_per_sm_cache[ri];
-  const unsigned long long E = (unsigned long long)a.sites * K;
-  const unsigned long long nchunks = (E + 32 * TRAV_R - 1) / (32 * TRAV_R);
-  unsigned long long blocks = (nchunks + TRAV_WARPS - 1) / TRAV_WARPS;
-  const unsigned long long cap = (unsigned long long)c->sm_count * per_sm;
-  if (blocks > cap) blocks = cap;
-  if (blocks < 1) blocks = 1;
-  if (rate_scalers)
-    trav_dna_kernel<K, true><<<(unsigned int)blocks, TRAV_WARPS * 32, 0, c->stream>>>(a);
-  else
-    trav_dna_kernel<K, false><<<(unsigned int)blocks, TRAV_WARPS * 32, 0, c->stream>>>(a);
-  ++g_kernel_launches;
-  return pllb200_cuda_ok(cudaGetLastError(), "trav_dna_kernel launch");
-}
-
 bool launch_partials(PartCtx * c, const pll_operation_t * ops_in, unsigned int count)
 {
   pll_partition_t * p = &c->pub;
@@ -463,29 +229,7 @@ bool launch_partials(PartCtx * c, const pll_operation_t * ops_in, unsigned int c
   if (p->states == 4 && (K == 1 || K == 2 || K == 4 || K == 8))
   {
     const pll_operation_t * ops = schedule_ops(c, ops_in, count);
-    const pll_operation_t * d_ops =
-        (const pll_operation_t *)dev_stage(c, ops, sizeof(pll_operation_t) * count);
-    if (!d_ops) return false;
-    TravArgs a;
-    a.ops = d_ops;
-    a.nops = count;
-    a.clv = c->d_clv;
-    a.clv_stride = c->clv_stride;
-    a.clv_first = c->clv_first;
-    a.scaler = c->d_scaler;
-    a.scaler_stride = c->scaler_stride;
-    a.pmat_il = c->d_pmat_il;
-    a.tipchars = c->d_tipchars;
-    a.tip_stride = c->tip_stride;
-    a.tips_pattern = pattern_tip ? p->tips : 0;
-    a.sites = c->sites_alloc;
-    switch (K)
-    {
-      case 1: return launch_trav_dna<1>(c, a, rate_scalers);
-      case 2: return launch_trav_dna<2>(c, a, rate_scalers);
-      case 4: return launch_trav_dna<4>(c, a, rate_scalers);
-      default: return launch_trav_dna<8>(c, a, rate_scalers);
-    }
+    return launch_trav_dna(c, ops, count);
   }
 
   /* generic: one launch per op, caller's order */

@@ -1,0 +1,449 @@
+/*
+ * k_traversal_dna.cu — the 4-state "site-column" traversal kernel (see k_partials.cu header for the
+ * design rationale and the reference functions it replaces: core_partials.c:48-200,202-351,612-764,
+ * 1013-1210 and their AVX/AVX2 twins).
+ *
+ * One launch evaluates a whole operation list.  A warp owns a chunk of 32*R consecutive
+ * (site, rate-category) elements and walks the list for it; lane l handles elements
+ * e0+l, e0+l+32, ..., all of the same category k = l mod K, so one pass over the two staged
+ * P-matrices (16 broadcast LDS.128) serves R elements.  Per element and op: one 256-bit load per
+ * inner child (or one byte per tip child, expanded in registers to a 0/1 vector so that tip-tip,
+ * tip-inner and inner-inner share one arithmetic path: sum_j M[i][j]*{0,1} is bit-identical to the
+ * reference's masked row sums), 32 FP64 FMA/MUL, one 256-bit store.
+ *
+ * Latency structure (what ncu showed to matter — the kernel is not DRAM-bound because child CLVs
+ * are re-read from L1/L2, so dependent-load latency per op is the limiter):
+ *   - operations are pre-resolved on the host into 64-byte DevOp records (absolute offsets, flags)
+ *     and staged per CTA in shared memory, 256 ops per segment: reading op o+1 ahead costs nothing;
+ *   - the two P-matrices of op o+1 are fetched by TMA (cp.async.bulk global->shared, completion on a
+ *     per-warp mbarrier) while op o computes: no registers, no LSU instructions, no L1 pollution;
+ *   - the tip codes of op o+1 (the only loads that always come from DRAM) are issued during op o;
+ *   - full chunks run a predicate-free path; only the last partial chunk takes the guarded path.
+ */
+#include "internal.h"
+#include "devutil.cuh"
+
+#include <algorithm>
+
+struct __align__(16) DevOp
+{
+  unsigned long long p_off;  /* parent CLV: offset in doubles from the CLV arena */
+  unsigned long long c1_off; /* child 1: CLV offset in doubles, or byte offset into tipchars */
+  unsigned long long c2_off;
+  unsigned long long ps_off; /* scaler offsets in u32 elements from the scaler arena */
+  unsigned long long s1_off;
+  unsigned long long s2_off;
+  unsigned int m1_off;       /* P-matrix offsets in doubles into the interleaved image */
+  unsigned int m2_off;
+  unsigned int flags;
+  unsigned int pad;
+};
+#define OPF_TIP1 1u
+#define OPF_TIP2 2u
+#define OPF_PS 4u
+#define OPF_S1 8u
+#define OPF_S2 16u
+
+struct TravArgs
+{
+  const DevOp * ops;
+  unsigned int nops;
+  unsigned int sites; /* sites_alloc */
+  double * clv;
+  unsigned int * scaler;
+  const double * pmat_il;
+  const unsigned char * tipchars;
+};
+
+#define TRAV_WARPS 8
+#define TRAV_SEG(K) ((K) == 8 ? 128 : 256) /* DevOps staged per CTA at a time (<= 16 KB) */
+
+/* ---- mbarrier / TMA bulk copy (PTX ISA: cp.async.bulk, mbarrier) ------------------------------ */
+__device__ __forceinline__ unsigned int smem_u32(const void * p)
+{
+  return (unsigned int)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(unsigned long long * bar, unsigned int count)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long * bar, unsigned int bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long * bar, unsigned int parity)
+{
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gmem, unsigned int bytes,
+                                            unsigned long long * bar)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst_smem)),
+               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+/* 4-bit tip code -> 0.0/1.0 vector (hi word of 1.0 is 0x3FF00000) */
+__device__ __forceinline__ d4 tip_vector(unsigned int code)
+{
+  d4 v;
+  v.x = __hiloint2double((int)((code & 1u) * 0x3FF00000u), 0);
+  v.y = __hiloint2double((int)(((code >> 1) & 1u) * 0x3FF00000u), 0);
+  v.z = __hiloint2double((int)(((code >> 2) & 1u) * 0x3FF00000u), 0);
+  v.w = __hiloint2double((int)(((code >> 3) & 1u) * 0x3FF00000u), 0);
+  return v;
+}
+
+template <int K>
+struct TravSmem
+{
+  DevOp ops[TRAV_SEG(K)];
+  double mat[TRAV_WARPS][2][2][16 * K]; /* [warp][stage][L/R][row i][cat k][col j] */
+  unsigned long long bar[TRAV_WARPS][2];
+};
+
+/* One chunk (32*R elements = 32*R/K consecutive sites) through ops [0, nseg) of the staged segment.
+ * Lane l owns category k = l mod K of the R CONSECUTIVE sites s0 .. s0+R-1, s0 = chunk_site0 + (l/K)*R:
+ * a warp-level 256-bit access still covers whole 128-byte lines (K lanes x 32 B per site), the R tip
+ * codes of a lane are one packed load, and its R per-site scalers are contiguous.
+ * FULL: every site of the chunk exists (no guards).  ph: mbarrier phase bits of the two stages. */
+template <int K, int R, bool RATE_SCALERS, bool FULL>
+__device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm, unsigned int nseg,
+                                            unsigned long long s0, int lane, int warp,
+                                            unsigned int & ph)
+{
+  const int k = lane % K;
+  constexpr unsigned int MAT_BYTES = 16 * K * sizeof(double);
+  constexpr int ESTEP = K * 4;                               /* doubles between consecutive sites */
+  const unsigned long long eoff = (s0 * K + k) * 4;          /* doubles */
+  const unsigned long long sidx0 = RATE_SCALERS ? s0 * K + k : s0; /* scaler element of r = 0 */
+  constexpr int SC_STEP = RATE_SCALERS ? K : 1;
+  unsigned int actmask = 0;
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+    if (FULL || s0 + r < a.sites) actmask |= 1u << r;
+
+  /* R tip codes packed little-endian into one word (R = 4: one aligned 32-bit load) */
+  auto load_tips = [&](const unsigned char * base) -> unsigned int {
+    if (FULL && R == 4) return __ldg(reinterpret_cast<const unsigned int *>(base));
+    if (FULL && R == 2) return __ldg(reinterpret_cast<const unsigned short *>(base));
+    unsigned int t = 0;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      if ((actmask >> r) & 1u) t |= (unsigned int)__ldg(base + r) << (8 * r);
+    return t;
+  };
+
+  /* prologue: matrices + tip codes of op 0 */
+  __syncwarp();
+  if (lane == 0)
+  {
+    mbar_expect_tx(&sm.bar[warp][0], 2 * MAT_BYTES);
+    tma_load_1d(sm.mat[warp][0][0], a.pmat_il + sm.ops[0].m1_off, MAT_BYTES, &sm.bar[warp][0]);
+    tma_load_1d(sm.mat[warp][0][1], a.pmat_il + sm.ops[0].m2_off, MAT_BYTES, &sm.bar[warp][0]);
+  }
+  unsigned int t1 = 0, t2 = 0; /* packed tip codes of the CURRENT op */
+  {
+    const unsigned int f0 = sm.ops[0].flags;
+    if (f0 & OPF_TIP1) t1 = load_tips(a.tipchars + sm.ops[0].c1_off + s0);
+    if (f0 & OPF_TIP2) t2 = load_tips(a.tipchars + sm.ops[0].c2_off + s0);
+  }
+
+  for (unsigned int o = 0; o < nseg; ++o)
+  {
+    const DevOp & d = sm.ops[o];
+    const unsigned int flags = d.flags;
+    const bool tip1 = flags & OPF_TIP1, tip2 = flags & OPF_TIP2;
+    const unsigned int st = o & 1u;
+
+    /* all lanes are done with stage st^1 (op o-1): refill it with the matrices of op o+1 */
+    __syncwarp();
+    if (lane == 0 && o + 1 < nseg)
+    {
+      mbar_expect_tx(&sm.bar[warp][st ^ 1u], 2 * MAT_BYTES);
+      tma_load_1d(sm.mat[warp][st ^ 1u][0], a.pmat_il + sm.ops[o + 1].m1_off, MAT_BYTES, &sm.bar[warp][st ^ 1u]);
+      tma_load_1d(sm.mat[warp][st ^ 1u][1], a.pmat_il + sm.ops[o + 1].m2_off, MAT_BYTES, &sm.bar[warp][st ^ 1u]);
+    }
+
+    /* ---- loads of this op: inner children (mostly L1/L2 hits), child scalers ---- */
+    d4 v1[R], v2[R];
+    unsigned int sc[R];
+    const double * p1 = a.clv + d.c1_off + eoff;
+    const double * p2 = a.clv + d.c2_off + eoff;
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+    {
+      sc[r] = 0;
+      if (FULL || ((actmask >> r) & 1u))
+      {
+        if (!tip1) v1[r] = ldg256(p1 + ESTEP * r);
+        if (!tip2) v2[r] = ldg256(p2 + ESTEP * r);
+        if ((flags & OPF_PS) && (RATE_SCALERS || k == 0))
+        {
+          if (flags & OPF_S1) sc[r] += a.scaler[d.s1_off + sidx0 + SC_STEP * r];
+          if (flags & OPF_S2) sc[r] += a.scaler[d.s2_off + sidx0 + SC_STEP * r];
+        }
+      }
+      else
+        v1[r] = v2[r] = d4{0.0, 0.0, 0.0, 0.0};
+    }
+    /* ---- tip codes of the NEXT op (always a DRAM access: issue it a whole op early) ---- */
+    unsigned int n1 = 0, n2 = 0;
+    if (o + 1 < nseg)
+    {
+      const unsigned int fn = sm.ops[o + 1].flags;
+      if (fn & OPF_TIP1) n1 = load_tips(a.tipchars + sm.ops[o + 1].c1_off + s0);
+      if (fn & OPF_TIP2) n2 = load_tips(a.tipchars + sm.ops[o + 1].c2_off + s0);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+    {
+      if (tip1) v1[r] = tip_vector(t1 >> (8 * r));
+      if (tip2) v2[r] = tip_vector(t2 >> (8 * r));
+    }
+
+    /* ---- matrices of this op have landed? ---- */
+    mbar_wait(&sm.bar[warp][st], (ph >> st) & 1u);
+    ph ^= 1u << st;
+    const double * sL = sm.mat[warp][st][0];
+    const double * sR = sm.mat[warp][st][1];
+
+    /* ---- parent[i] = (L_k[i,:] . v1) * (R_k[i,:] . v2) ---- */
+    double out[R][4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+    {
+      const double2 la = *reinterpret_cast<const double2 *>(sL + (i * K + k) * 4);
+      const double2 lb = *reinterpret_cast<const double2 *>(sL + (i * K + k) * 4 + 2);
+      const double2 ra = *reinterpret_cast<const double2 *>(sR + (i * K + k) * 4);
+      const double2 rb = *reinterpret_cast<const double2 *>(sR + (i * K + k) * 4 + 2);
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+      {
+        const double xl = la.x * v1[r].x + la.y * v1[r].y + lb.x * v1[r].z + lb.y * v1[r].w;
+        const double xr = ra.x * v2[r].x + ra.y * v2[r].y + rb.x * v2[r].z + rb.y * v2[r].w;
+        out[r][i] = xl * xr;
+      }
+    }
+
+    /* ---- underflow scaling vote + scaler update ---- */
+    unsigned int scalemask = 0;
+    if ((flags & OPF_PS) && !(tip1 && tip2))
+    {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if ((out[r][0] < SCALE_THRESHOLD_D) & (out[r][1] < SCALE_THRESHOLD_D) &
+            (out[r][2] < SCALE_THRESHOLD_D) & (out[r][3] < SCALE_THRESHOLD_D))
+          scalemask |= 1u << r;
+      if (!RATE_SCALERS)
+      {
+#pragma unroll
+        for (int off = 1; off < K; off <<= 1) scalemask &= __shfl_xor_sync(0xffffffffu, scalemask, off);
+      }
+    }
+    if ((flags & OPF_PS) && (RATE_SCALERS || k == 0))
+    {
+      unsigned int * ps = a.scaler + d.ps_off + sidx0;
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (FULL || ((actmask >> r) & 1u)) ps[SC_STEP * r] = sc[r] + ((scalemask >> r) & 1u);
+    }
+
+    /* ---- store ---- */
+    double * pdst = a.clv + d.p_off + eoff;
+    if (scalemask)
+    {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if ((scalemask >> r) & 1u)
+        {
+          out[r][0] *= SCALE_FACTOR_D;
+          out[r][1] *= SCALE_FACTOR_D;
+          out[r][2] *= SCALE_FACTOR_D;
+          out[r][3] *= SCALE_FACTOR_D;
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+      if (FULL || ((actmask >> r) & 1u)) stg256(pdst + ESTEP * r, d4{out[r][0], out[r][1], out[r][2], out[r][3]});
+    t1 = n1;
+    t2 = n2;
+  }
+}
+
+/* the last, partial chunk: same code with guards, kept out of line so that it does not inflate the
+ * register allocation of the hot path.  MINB is a template parameter on purpose: one callee per kernel,
+ * so that ptxas sizes it under that kernel's register cap. */
+template <int K, int R, bool RATE_SCALERS, int MINB>
+__device__ __noinline__ void run_segment_tail(const TravArgs & a, TravSmem<K> & sm, unsigned int nseg,
+                                              unsigned long long s0, int lane, int warp,
+                                              unsigned int & ph)
+{
+  run_segment<K, R, RATE_SCALERS, false>(a, sm, nseg, s0, lane, warp, ph);
+}
+
+template <int K, int R, bool RATE_SCALERS, int MINB>
+__global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArgs a)
+{
+  __shared__ __align__(128) TravSmem<K> sm;
+
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  constexpr unsigned long long SPC = 32ull * R / K; /* sites per chunk */
+  const unsigned long long nchunks = ((unsigned long long)a.sites + SPC - 1) / SPC;
+  const unsigned long long gwarp = (unsigned long long)blockIdx.x * TRAV_WARPS + warp;
+  const unsigned long long nwarps = (unsigned long long)gridDim.x * TRAV_WARPS;
+
+  if (lane == 0)
+  {
+    mbar_init(&sm.bar[warp][0], 1);
+    mbar_init(&sm.bar[warp][1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  unsigned int ph = 0;
+
+  for (unsigned int seg = 0; seg < a.nops; seg += TRAV_SEG(K))
+  {
+    const unsigned int nseg = min(a.nops - seg, (unsigned int)TRAV_SEG(K));
+    __syncthreads(); /* previous segment fully consumed by every warp of the CTA */
+    {
+      const uint4 * src = reinterpret_cast<const uint4 *>(a.ops + seg);
+      uint4 * dst = reinterpret_cast<uint4 *>(sm.ops);
+      for (unsigned int i = threadIdx.x; i < nseg * 4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    for (unsigned long long chunk = gwarp; chunk < nchunks; chunk += nwarps)
+    {
+      const unsigned long long s0 = chunk * SPC + (unsigned long long)(lane / K) * R;
+      if ((chunk + 1) * SPC <= a.sites)
+        run_segment<K, R, RATE_SCALERS, true>(a, sm, nseg, s0, lane, warp, ph);
+      else
+        run_segment_tail<K, R, RATE_SCALERS, MINB>(a, sm, nseg, s0, lane, warp, ph);
+    }
+  }
+}
+
+/* ---- host ------------------------------------------------------------------------------------ */
+
+int g_opt_trav_variant = 0;
+
+template <int K, int R, bool RS, int MINB>
+static bool launch_variant(PartCtx * c, const TravArgs & a)
+{
+  static int per_sm_cache = 0;
+  if (!per_sm_cache)
+  {
+    int nb = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, trav_dna_kernel<K, R, RS, MINB>,
+                                                      TRAV_WARPS * 32, 0) != cudaSuccess || nb < 1)
+      nb = MINB;
+    per_sm_cache = nb;
+  }
+  int per_sm = per_sm_cache;
+  if (g_opt_trav_ctas_per_sm > 0) per_sm = std::min(per_sm, g_opt_trav_ctas_per_sm);
+  const unsigned long long spc = 32ull * R / K;
+  const unsigned long long nchunks = ((unsigned long long)a.sites + spc - 1) / spc;
+  unsigned long long blocks = (nchunks + TRAV_WARPS - 1) / TRAV_WARPS;
+  const unsigned long long cap = (unsigned long long)c->sm_count * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  trav_dna_kernel<K, R, RS, MINB><<<(unsigned int)blocks, TRAV_WARPS * 32, 0, c->stream>>>(a);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "trav_dna_kernel launch");
+}
+
+template <int K>
+static bool launch_k(PartCtx * c, const TravArgs & a, bool rate_scalers)
+{
+  if (rate_scalers) return launch_variant<K, 2, true, 3>(c, a);
+  if (K == 4)
+  {
+    switch (g_opt_trav_variant)
+    {
+      case 1: return launch_variant<K, 1, false, 4>(c, a);
+      case 2: return launch_variant<K, 2, false, 3>(c, a);
+      case 3: return launch_variant<K, 4, false, 2>(c, a);
+      case 4: return launch_variant<K, 2, false, 2>(c, a);
+      default: break;
+    }
+    return launch_variant<K, 4, false, 2>(c, a);
+  }
+  return launch_variant<K, 2, false, 3>(c, a);
+}
+
+bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int count)
+{
+  pll_partition_t * p = &c->pub;
+  const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
+  const bool rate_scalers = (p->attributes & PLL_ATTRIB_RATE_SCALERS) != 0;
+  const unsigned int K = p->rate_cats;
+
+  static_assert(sizeof(DevOp) == 64, "DevOp is 8 x u64");
+  c->devop_scratch.resize((size_t)count * 8);
+  DevOp * dops = reinterpret_cast<DevOp *>(c->devop_scratch.data());
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    const pll_operation_t & o = ops[i];
+    DevOp & d = dops[i];
+    memset(&d, 0, sizeof(d));
+    d.p_off = (unsigned long long)(o.parent_clv_index - c->clv_first) * c->clv_stride;
+    if (pattern_tip && o.child1_clv_index < p->tips)
+    {
+      d.flags |= OPF_TIP1;
+      d.c1_off = (unsigned long long)o.child1_clv_index * c->tip_stride;
+    }
+    else
+      d.c1_off = (unsigned long long)(o.child1_clv_index - c->clv_first) * c->clv_stride;
+    if (pattern_tip && o.child2_clv_index < p->tips)
+    {
+      d.flags |= OPF_TIP2;
+      d.c2_off = (unsigned long long)o.child2_clv_index * c->tip_stride;
+    }
+    else
+      d.c2_off = (unsigned long long)(o.child2_clv_index - c->clv_first) * c->clv_stride;
+    if (o.parent_scaler_index >= 0)
+    {
+      d.flags |= OPF_PS;
+      d.ps_off = (unsigned long long)o.parent_scaler_index * c->scaler_stride;
+    }
+    if (o.child1_scaler_index >= 0)
+    {
+      d.flags |= OPF_S1;
+      d.s1_off = (unsigned long long)o.child1_scaler_index * c->scaler_stride;
+    }
+    if (o.child2_scaler_index >= 0)
+    {
+      d.flags |= OPF_S2;
+      d.s2_off = (unsigned long long)o.child2_scaler_index * c->scaler_stride;
+    }
+    d.m1_off = o.child1_matrix_index * 16 * K;
+    d.m2_off = o.child2_matrix_index * 16 * K;
+  }
+  const DevOp * d_ops = (const DevOp *)dev_stage(c, dops, sizeof(DevOp) * count);
+  if (!d_ops) return false;
+  TravArgs a;
+  a.ops = d_ops;
+  a.nops = count;
+  a.sites = c->sites_alloc;
+  a.clv = c->d_clv;
+  a.scaler = c->d_scaler;
+  a.pmat_il = c->d_pmat_il;
+  a.tipchars = c->d_tipchars;
+  switch (K)
+  {
+    case 1: return launch_k<1>(c, a, rate_scalers);
+    case 2: return launch_k<2>(c, a, rate_scalers);
+    case 4: return launch_k<4>(c, a, rate_scalers);
+    default: return launch_k<8>(c, a, rate_scalers);
+  }
+}
