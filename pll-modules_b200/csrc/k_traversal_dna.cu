@@ -112,6 +112,55 @@ struct TravSmem
   unsigned long long bar[TRAV_WARPS][2];
 };
 
+/* hi word of a non-negative double: x < 2^-256  <=>  hi(x) < 0x2FF00000 (lo word of 2^-256 is 0) */
+__device__ __forceinline__ unsigned int hi_word(double x) { return (unsigned int)__double2hiint(x); }
+#define SCALE_THRESHOLD_HI 0x2FF00000u
+
+/* arithmetic of one op for the R elements of a lane; T1/T2: child is a pattern tip */
+template <int K, int R, bool T1, bool T2, bool FULL>
+__device__ __forceinline__ void op_body(const double * __restrict__ p1, const double * __restrict__ p2,
+                                        unsigned int t1, unsigned int t2, const double * sL,
+                                        const double * sR, int k, unsigned int actmask,
+                                        unsigned long long * bar, unsigned int parity,
+                                        double (&out)[R][4])
+{
+  constexpr int ESTEP = K * 4;
+  d4 v1[R], v2[R];
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+  {
+    if (FULL || ((actmask >> r) & 1u))
+    {
+      if (!T1) v1[r] = ldg256(p1 + ESTEP * r);
+      if (!T2) v2[r] = ldg256(p2 + ESTEP * r);
+    }
+    else
+      v1[r] = v2[r] = d4{0.0, 0.0, 0.0, 0.0};
+  }
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+  {
+    if (T1) v1[r] = tip_vector(t1 >> (8 * r));
+    if (T2) v2[r] = tip_vector(t2 >> (8 * r));
+  }
+  mbar_wait(bar, parity); /* matrices of this op have landed */
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+  {
+    const double2 la = *reinterpret_cast<const double2 *>(sL + (i * K + k) * 4);
+    const double2 lb = *reinterpret_cast<const double2 *>(sL + (i * K + k) * 4 + 2);
+    const double2 ra = *reinterpret_cast<const double2 *>(sR + (i * K + k) * 4);
+    const double2 rb = *reinterpret_cast<const double2 *>(sR + (i * K + k) * 4 + 2);
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+    {
+      const double xl = la.x * v1[r].x + la.y * v1[r].y + lb.x * v1[r].z + lb.y * v1[r].w;
+      const double xr = ra.x * v2[r].x + ra.y * v2[r].y + rb.x * v2[r].z + rb.y * v2[r].w;
+      out[r][i] = xl * xr;
+    }
+  }
+}
+
 /* One chunk (32*R elements = 32*R/K consecutive sites) through ops [0, nseg) of the staged segment.
  * Lane l owns category k = l mod K of the R CONSECUTIVE sites s0 .. s0+R-1, s0 = chunk_site0 + (l/K)*R:
  * a warp-level 256-bit access still covers whole 128-byte lines (K lanes x 32 B per site), the R tip
@@ -128,6 +177,7 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
   const unsigned long long eoff = (s0 * K + k) * 4;          /* doubles */
   const unsigned long long sidx0 = RATE_SCALERS ? s0 * K + k : s0; /* scaler element of r = 0 */
   constexpr int SC_STEP = RATE_SCALERS ? K : 1;
+  const bool sc_lane = RATE_SCALERS || k == 0;
   unsigned int actmask = 0;
 #pragma unroll
   for (int r = 0; r < R; ++r)
@@ -142,6 +192,23 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     for (int r = 0; r < R; ++r)
       if ((actmask >> r) & 1u) t |= (unsigned int)__ldg(base + r) << (8 * r);
     return t;
+  };
+  /* R scaler counts of one child (per-site mode with R = 4: one 128-bit load) */
+  auto add_scalers = [&](const unsigned int * base, unsigned int (&sc)[R]) {
+    if (FULL && R == 4 && !RATE_SCALERS)
+    {
+      const uint4 q = *reinterpret_cast<const uint4 *>(base);
+      sc[0] += q.x;
+      sc[1] += q.y;
+      sc[2] += q.z;
+      sc[3] += q.w;
+    }
+    else
+    {
+#pragma unroll
+      for (int r = 0; r < R; ++r)
+        if (FULL || ((actmask >> r) & 1u)) sc[r] += base[SC_STEP * r];
+    }
   };
 
   /* prologue: matrices + tip codes of op 0 */
@@ -163,7 +230,6 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
   {
     const DevOp & d = sm.ops[o];
     const unsigned int flags = d.flags;
-    const bool tip1 = flags & OPF_TIP1, tip2 = flags & OPF_TIP2;
     const unsigned int st = o & 1u;
 
     /* all lanes are done with stage st^1 (op o-1): refill it with the matrices of op o+1 */
@@ -174,30 +240,7 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
       tma_load_1d(sm.mat[warp][st ^ 1u][0], a.pmat_il + sm.ops[o + 1].m1_off, MAT_BYTES, &sm.bar[warp][st ^ 1u]);
       tma_load_1d(sm.mat[warp][st ^ 1u][1], a.pmat_il + sm.ops[o + 1].m2_off, MAT_BYTES, &sm.bar[warp][st ^ 1u]);
     }
-
-    /* ---- loads of this op: inner children (mostly L1/L2 hits), child scalers ---- */
-    d4 v1[R], v2[R];
-    unsigned int sc[R];
-    const double * p1 = a.clv + d.c1_off + eoff;
-    const double * p2 = a.clv + d.c2_off + eoff;
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-    {
-      sc[r] = 0;
-      if (FULL || ((actmask >> r) & 1u))
-      {
-        if (!tip1) v1[r] = ldg256(p1 + ESTEP * r);
-        if (!tip2) v2[r] = ldg256(p2 + ESTEP * r);
-        if ((flags & OPF_PS) && (RATE_SCALERS || k == 0))
-        {
-          if (flags & OPF_S1) sc[r] += a.scaler[d.s1_off + sidx0 + SC_STEP * r];
-          if (flags & OPF_S2) sc[r] += a.scaler[d.s2_off + sidx0 + SC_STEP * r];
-        }
-      }
-      else
-        v1[r] = v2[r] = d4{0.0, 0.0, 0.0, 0.0};
-    }
-    /* ---- tip codes of the NEXT op (always a DRAM access: issue it a whole op early) ---- */
+    /* tip codes of the NEXT op (always a DRAM access: issued a whole op early) */
     unsigned int n1 = 0, n2 = 0;
     if (o + 1 < nseg)
     {
@@ -205,74 +248,81 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
       if (fn & OPF_TIP1) n1 = load_tips(a.tipchars + sm.ops[o + 1].c1_off + s0);
       if (fn & OPF_TIP2) n2 = load_tips(a.tipchars + sm.ops[o + 1].c2_off + s0);
     }
+    /* child scaler counts (the lanes that own a scaler entry only) */
+    unsigned int sc[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r)
+    for (int r = 0; r < R; ++r) sc[r] = 0;
+    if ((flags & OPF_PS) && sc_lane)
     {
-      if (tip1) v1[r] = tip_vector(t1 >> (8 * r));
-      if (tip2) v2[r] = tip_vector(t2 >> (8 * r));
+      if (flags & OPF_S1) add_scalers(a.scaler + d.s1_off + sidx0, sc);
+      if (flags & OPF_S2) add_scalers(a.scaler + d.s2_off + sidx0, sc);
     }
 
-    /* ---- matrices of this op have landed? ---- */
-    mbar_wait(&sm.bar[warp][st], (ph >> st) & 1u);
-    ph ^= 1u << st;
+    /* ---- parent[i] = (L_k[i,:] . v1) * (R_k[i,:] . v2), one specialised body per tip pattern ---- */
+    const double * p1 = a.clv + d.c1_off + eoff;
+    const double * p2 = a.clv + d.c2_off + eoff;
     const double * sL = sm.mat[warp][st][0];
     const double * sR = sm.mat[warp][st][1];
-
-    /* ---- parent[i] = (L_k[i,:] . v1) * (R_k[i,:] . v2) ---- */
+    unsigned long long * bar = &sm.bar[warp][st];
+    const unsigned int parity = (ph >> st) & 1u;
+    ph ^= 1u << st;
     double out[R][4];
-#pragma unroll
-    for (int i = 0; i < 4; ++i)
+    switch (flags & (OPF_TIP1 | OPF_TIP2))
     {
-      const double2 la = *reinterpret_cast<const double2 *>(sL + (i * K + k) * 4);
-      const double2 lb = *reinterpret_cast<const double2 *>(sL + (i * K + k) * 4 + 2);
-      const double2 ra = *reinterpret_cast<const double2 *>(sR + (i * K + k) * 4);
-      const double2 rb = *reinterpret_cast<const double2 *>(sR + (i * K + k) * 4 + 2);
-#pragma unroll
-      for (int r = 0; r < R; ++r)
-      {
-        const double xl = la.x * v1[r].x + la.y * v1[r].y + lb.x * v1[r].z + lb.y * v1[r].w;
-        const double xr = ra.x * v2[r].x + ra.y * v2[r].y + rb.x * v2[r].z + rb.y * v2[r].w;
-        out[r][i] = xl * xr;
-      }
+      case 0: op_body<K, R, false, false, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
+      case OPF_TIP1: op_body<K, R, true, false, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
+      case OPF_TIP2: op_body<K, R, false, true, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
+      default: op_body<K, R, true, true, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
     }
 
     /* ---- underflow scaling vote + scaler update ---- */
     unsigned int scalemask = 0;
-    if ((flags & OPF_PS) && !(tip1 && tip2))
+    if (flags & OPF_PS)
     {
-#pragma unroll
-      for (int r = 0; r < R; ++r)
-        if ((out[r][0] < SCALE_THRESHOLD_D) & (out[r][1] < SCALE_THRESHOLD_D) &
-            (out[r][2] < SCALE_THRESHOLD_D) & (out[r][3] < SCALE_THRESHOLD_D))
-          scalemask |= 1u << r;
-      if (!RATE_SCALERS)
+      if ((flags & (OPF_TIP1 | OPF_TIP2)) != (OPF_TIP1 | OPF_TIP2))
       {
 #pragma unroll
-        for (int off = 1; off < K; off <<= 1) scalemask &= __shfl_xor_sync(0xffffffffu, scalemask, off);
-      }
-    }
-    if ((flags & OPF_PS) && (RATE_SCALERS || k == 0))
-    {
-      unsigned int * ps = a.scaler + d.ps_off + sidx0;
+        for (int r = 0; r < R; ++r)
+        {
+          const unsigned int m = max(max(hi_word(out[r][0]), hi_word(out[r][1])),
+                                     max(hi_word(out[r][2]), hi_word(out[r][3])));
+          if (m < SCALE_THRESHOLD_HI) scalemask |= 1u << r;
+        }
+        if (!RATE_SCALERS)
+        {
 #pragma unroll
-      for (int r = 0; r < R; ++r)
-        if (FULL || ((actmask >> r) & 1u)) ps[SC_STEP * r] = sc[r] + ((scalemask >> r) & 1u);
+          for (int off = 1; off < K; off <<= 1) scalemask &= __shfl_xor_sync(0xffffffffu, scalemask, off);
+        }
+      }
+      if (sc_lane)
+      {
+        unsigned int * ps = a.scaler + d.ps_off + sidx0;
+        if (FULL && R == 4 && !RATE_SCALERS)
+          *reinterpret_cast<uint4 *>(ps) = make_uint4(sc[0] + (scalemask & 1u), sc[1] + ((scalemask >> 1) & 1u),
+                                                      sc[2] + ((scalemask >> 2) & 1u), sc[3] + ((scalemask >> 3) & 1u));
+        else
+        {
+#pragma unroll
+          for (int r = 0; r < R; ++r)
+            if (FULL || ((actmask >> r) & 1u)) ps[SC_STEP * r] = sc[r] + ((scalemask >> r) & 1u);
+        }
+      }
+      if (scalemask)
+      {
+#pragma unroll
+        for (int r = 0; r < R; ++r)
+          if ((scalemask >> r) & 1u)
+          {
+            out[r][0] *= SCALE_FACTOR_D;
+            out[r][1] *= SCALE_FACTOR_D;
+            out[r][2] *= SCALE_FACTOR_D;
+            out[r][3] *= SCALE_FACTOR_D;
+          }
+      }
     }
 
     /* ---- store ---- */
     double * pdst = a.clv + d.p_off + eoff;
-    if (scalemask)
-    {
-#pragma unroll
-      for (int r = 0; r < R; ++r)
-        if ((scalemask >> r) & 1u)
-        {
-          out[r][0] *= SCALE_FACTOR_D;
-          out[r][1] *= SCALE_FACTOR_D;
-          out[r][2] *= SCALE_FACTOR_D;
-          out[r][3] *= SCALE_FACTOR_D;
-        }
-    }
 #pragma unroll
     for (int r = 0; r < R; ++r)
       if (FULL || ((actmask >> r) & 1u)) stg256(pdst + ESTEP * r, d4{out[r][0], out[r][1], out[r][2], out[r][3]});
