@@ -154,8 +154,9 @@ def main():
                 "unit": "CLV site-updates/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
                 "ms_per_step": res["seconds_per_traversal"] * 1e3, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-                "config": {"workload": "DNA GTR+G4, %d taxa, full traversal (CPU sample)" % a.tips,
-                           "l2": "inputs larger than L2"},
+                "config": {"workload": "DNA GTR+G4, %d taxa x %d sites per GPU, full traversal (BASELINE configs[1]); "
+                                       "reference CPU arm on a bounded site sample, throughput is per site" % (a.tips, a.sites),
+                           "taxa": a.tips, "l2": "inputs larger than L2"},
                 "cpu_baseline": res,
                 "e2e": {"value": res["value"], "unit": "CLV site-updates/s", "h2d_bytes_per_step": 0,
                         "d2h_bytes_per_step": 0}}
@@ -284,7 +285,11 @@ def main():
                     "what": "host tree with new branch lengths -> pllmod_treeinfo_compute_loglh -> logL on host"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_kind": peak_kind, "kernel": "trav_dna_kernel<4,false>",
+                         "traffic": 27.816e9 * S / 200000.0,
+                         "traffic_note": "dram__bytes_read+write of one ncu --set full capture at 200k sites "
+                                         "(profiles/r01_trav_dna_ncu_full_summary.csv), scaled linearly in sites "
+                                         "(a 400k-site capture agrees); a 1M-site launch cannot be replayed by ncu",
+                         "peak_kind": peak_kind, "kernel": "trav_dna_kernel<4,false>",
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kern_avg,
                          "kernel_share_of_step": kern_avg / dev_ms},
             "clocks": clocks, "loglh": ll, "loglh_first": ll0,
