@@ -250,6 +250,35 @@ def main():
     clocks = sampler.stop()
 
     extra = {}
+    # ---- logL and derivative evaluations/s at fixed S (second half of BASELINE's metric) -----------
+    root = h.root()
+    nrep = max(3, a.steps)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(nrep):
+        h.edge_loglh(root)
+    barrier()
+    logl_s = (time.perf_counter() - t0) / nrep
+    h.derivatives(root, [0.1])
+    barrier()
+    t0 = time.perf_counter()
+    h.derivatives(root, [0.1])
+    barrier()
+    t1 = time.perf_counter() - t0
+    nder = 8
+    t0 = time.perf_counter()
+    h.derivatives(root, list(np.linspace(0.01, 0.5, 1 + nder)))
+    barrier()
+    tn = time.perf_counter() - t0
+    deriv_s = max(1e-9, (tn - t1) / nder)
+    root_is_ti = h.node_info(root)["tip"] or h.node_info(h.node_info(root)["back"])["tip"]
+    extra["logl_evals_per_s"] = world / logl_s if world == 1 else 1.0 / logl_s
+    extra["logl_GBps_algorithmic"] = (137 if root_is_ti else 268) * S / logl_s / 1e9
+    extra["deriv_evals_per_s"] = 1.0 / deriv_s
+    extra["deriv_GBps_algorithmic"] = 132 * S / deriv_s / 1e9
+    extra["sumtable_builds_per_s"] = 1.0 / max(1e-9, t1 - deriv_s)
+    extra["evals_note"] = ("host wall clock through the C ABI incl. launch + sync, %d sites per GPU, root edge is %s"
+                           % (S, "tip-inner" if root_is_ti else "inner-inner"))
     if a.blo:
         h.set_branch_lengths(brl)
         h.loglh(0)
