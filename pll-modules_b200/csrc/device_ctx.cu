@@ -151,6 +151,13 @@ bool dev_ctx_init(PartCtx * c)
       CUDA_TRY(cudaMalloc(&c->d_pmat_il, bytes), false);
       CUDA_TRY(cudaMemsetAsync(c->d_pmat_il, 0, bytes, c->stream), false);
     }
+    else if (s == 20)
+    {
+      /* DMMA B-fragment image for the 20-state traversal kernel: [m][k][ntile 3][kstep 5][lane 32] */
+      const size_t fbytes = (size_t)p->prob_matrices * K * 480 * sizeof(double);
+      CUDA_TRY(cudaMalloc(&c->d_pmat_il, fbytes), false);
+      CUDA_TRY(cudaMemsetAsync(c->d_pmat_il, 0, fbytes, c->stream), false);
+    }
   }
   if (pattern_tip && p->tips)
   {

@@ -149,6 +149,7 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
                     unsigned int count);
 bool launch_partials(PartCtx * c, const pll_operation_t * ops, unsigned int count);
 bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int count); /* k_traversal_dna.cu */
+bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count);  /* k_traversal_aa.cu */
 bool launch_edge_logl(PartCtx * c, unsigned int parent_clv, int parent_scaler,
                       unsigned int child_clv, int child_scaler, unsigned int matrix_index,
                       const unsigned int * freqs_indices, double * d_persite, int slot);

@@ -232,6 +232,9 @@ bool launch_partials(PartCtx * c, const pll_operation_t * ops_in, unsigned int c
     return launch_trav_dna(c, ops, count);
   }
 
+  if (p->states == 20 && !rate_scalers && K <= 8 && c->d_pmat_il)
+    return launch_trav_aa(c, schedule_ops(c, ops_in, count), count); /* FP64 tensor-core path */
+
   /* generic: one launch per op, caller's order */
   if (K > GEN_THREADS)
   {

@@ -68,8 +68,15 @@ __global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__
         for (unsigned int q = 0; q < states; ++q) v += (s_inv[i * sp + q] * expd[q]) * s_ev[q * sp + j];
     }
     out[idx] = v;
-    if (pmat_il) /* 4-state: [m][i][k][j] */
+    if (pmat_il && states == 4) /* 4-state: [m][i][k][j] */
       pmat_il[(size_t)m * K * 16 + (i * K + k) * 4 + j] = v;
+    if (pmat_il && states == 20)
+    {
+      /* m8n8k4 B fragment (col-major 4x8): lane l holds B[row l%4][col l/4] = P[i = nt*8 + l/4][j = ks*4 + l%4];
+       * rows i >= 20 of the third n-tile stay zero from the allocation-time memset */
+      const unsigned int nt = i >> 3, ks = j >> 2, lane = ((i & 7u) << 2) | (j & 3u);
+      pmat_il[(((size_t)m * K + k) * 3 + nt) * 160 + ks * 32 + lane] = v;
+    }
   }
 }
 

@@ -1,0 +1,348 @@
+/*
+ * k_traversal_aa.cu — 20-state (protein) site-column traversal kernel on the FP64 tensor cores.
+ *
+ * Replaces pll_core_update_partial_{ii,ti,tt} for states == 20 (libs/libpll/src/core_partials.c:82-200,
+ * 354-610,612-764; AVX2 20x20 kernels core_partials_avx2.c:49-1009).  For one rate category the child
+ * contraction X[site][i] = sum_j V[site][j] * P[i][j] is a dense [sites x 20] x [20 x 20] product, so it
+ * runs as DMMA tiles (mma.sync.m8n8k4.f64): M = 8 sites, N = 8 parent states (3 tiles, 20 -> 24), K = 4
+ * child states (5 steps) -> 15 DMMA per side, tile and category.  The B operand (P^T) is pre-arranged by
+ * pmatrix_kernel as a fragment image [k][ntile][kstep][lane] so a lane fetches its fragment with one
+ * conflict-free LDS.64; both matrices of the NEXT operation (2 x K x 3840 B) arrive by TMA bulk copy into
+ * a double-buffered shared-memory stage while the current operation computes.
+ *
+ * Like the 4-state kernel, ONE launch walks the whole operation list for a chunk of sites (a CTA of 4
+ * warps owns 4 x 8T consecutive sites), so children written a few ops earlier come back from L1/L2.
+ * Here the lanes of a warp exchange data through global memory (D-fragment layout != A-fragment layout),
+ * which the per-operation __syncthreads orders.
+ *
+ * Tip children (PLL_ATTRIB_PATTERN_TIP): the A fragment is bit (j) of tipmap[code] as 0.0/1.0.
+ * Scaling (per-site mode): max high word over all K*20 entries of a site < 2^-256 -> the site is
+ * rescaled in a (rare) second pass and its scaler incremented (core_partials.c:729-763).
+ * Per-rate scalers with 20 states use the generic kernel (k_partials.cu).
+ * Algorithmic bytes per site (Gamma4): ii 1932, ti 1289, tt 646; 6480 flop -> 3.35 flop/B.
+ */
+#include "internal.h"
+#include "devutil.cuh"
+
+#include <algorithm>
+
+struct __align__(16) AaOp
+{
+  unsigned long long p_off, c1_off, c2_off; /* doubles into CLV arena / bytes into tipchars */
+  unsigned long long ps_off, s1_off, s2_off;
+  unsigned int m1_off, m2_off;              /* doubles into the fragment image */
+  unsigned int flags, pad;
+};
+#define AOPF_TIP1 1u
+#define AOPF_TIP2 2u
+#define AOPF_PS 4u
+#define AOPF_S1 8u
+#define AOPF_S2 16u
+
+struct AaArgs
+{
+  const AaOp * ops;
+  unsigned int nops, sites, K;
+  double * clv;
+  unsigned int * scaler;
+  const double * frag;
+  const unsigned char * tipchars;
+  const unsigned long long * tipmap;
+};
+
+#define AA_WARPS 4
+#define AA_T 4     /* 8-site tiles per warp and chunk */
+#define AA_SEG 128 /* ops staged per CTA */
+#define AA_FRAG 480 /* doubles per (matrix, category): 3 ntiles x 5 ksteps x 32 lanes */
+#define AA_THR_HI 0x2FF00000u
+
+__device__ __forceinline__ unsigned int aa_smem_u32(const void * p) { return (unsigned int)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void aa_mbar_init(unsigned long long * b, unsigned int n)
+{
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(aa_smem_u32(b)), "r"(n) : "memory");
+}
+__device__ __forceinline__ void aa_mbar_expect(unsigned long long * b, unsigned int bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(aa_smem_u32(b)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void aa_mbar_wait(unsigned long long * b, unsigned int parity)
+{
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tW_%=:\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t@p bra D_%=;\n\tbra W_%=;\n\tD_%=:\n\t}" ::"r"(
+          aa_smem_u32(b)),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void aa_tma(void * dst, const void * src, unsigned int bytes, unsigned long long * b)
+{
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   aa_smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(aa_smem_u32(b))
+               : "memory");
+}
+__device__ __forceinline__ void dmma(double & c0, double & c1, double a, double b)
+{
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+/* dynamic shared memory: AaOp ops[AA_SEG] | u64 tipmap[256] | u64 bar[2] | double mat[2 stages][2][K*480] */
+__global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
+{
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  AaOp * s_ops = reinterpret_cast<AaOp *>(smem_raw);
+  unsigned long long * s_tipmap = reinterpret_cast<unsigned long long *>(smem_raw + sizeof(AaOp) * AA_SEG);
+  unsigned long long * s_bar = s_tipmap + 256;
+  double * s_mat = reinterpret_cast<double *>(s_bar + 2);
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = lane >> 2, col = lane & 3; /* fragment coordinates */
+  const unsigned int K = a.K;
+  const unsigned int mat_doubles = K * AA_FRAG;
+  const unsigned int mat_bytes = mat_doubles * sizeof(double);
+  const unsigned long long span = (unsigned long long)K * 20; /* doubles per site */
+  const unsigned long long sites_per_cta = (unsigned long long)AA_WARPS * 8 * AA_T;
+  const unsigned long long nchunks = (a.sites + sites_per_cta - 1) / sites_per_cta;
+
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) s_tipmap[i] = a.tipmap ? a.tipmap[i] : 0ull;
+  if (threadIdx.x == 0)
+  {
+    aa_mbar_init(&s_bar[0], 1);
+    aa_mbar_init(&s_bar[1], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  unsigned int ph = 0;
+
+  for (unsigned int seg = 0; seg < a.nops; seg += AA_SEG)
+  {
+    const unsigned int nseg = min(a.nops - seg, (unsigned int)AA_SEG);
+    __syncthreads();
+    {
+      const uint4 * src = reinterpret_cast<const uint4 *>(a.ops + seg);
+      uint4 * dst = reinterpret_cast<uint4 *>(s_ops);
+      for (unsigned int i = threadIdx.x; i < nseg * 4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+
+    for (unsigned long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x)
+    {
+      const unsigned long long wsite0 = chunk * sites_per_cta + (unsigned long long)warp * 8 * AA_T;
+      __syncthreads(); /* both stages free */
+      if (threadIdx.x == 0)
+      {
+        aa_mbar_expect(&s_bar[0], 2 * mat_bytes);
+        aa_tma(s_mat, a.frag + s_ops[0].m1_off, mat_bytes, &s_bar[0]);
+        aa_tma(s_mat + mat_doubles, a.frag + s_ops[0].m2_off, mat_bytes, &s_bar[0]);
+      }
+      for (unsigned int o = 0; o < nseg; ++o)
+      {
+        const AaOp & d = s_ops[o];
+        const unsigned int flags = d.flags;
+        const bool tip1 = flags & AOPF_TIP1, tip2 = flags & AOPF_TIP2;
+        const unsigned int st = o & 1u;
+        __syncthreads(); /* op o-1 complete everywhere: its CLV is visible, stage st^1 is free */
+        if (threadIdx.x == 0 && o + 1 < nseg)
+        {
+          double * dstm = s_mat + (size_t)(st ^ 1u) * 2 * mat_doubles;
+          aa_mbar_expect(&s_bar[st ^ 1u], 2 * mat_bytes);
+          aa_tma(dstm, a.frag + s_ops[o + 1].m1_off, mat_bytes, &s_bar[st ^ 1u]);
+          aa_tma(dstm + mat_doubles, a.frag + s_ops[o + 1].m2_off, mat_bytes, &s_bar[st ^ 1u]);
+        }
+        aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
+        ph ^= 1u << st;
+        const double * sL = s_mat + (size_t)st * 2 * mat_doubles;
+        const double * sR = sL + mat_doubles;
+        const bool check = (flags & AOPF_PS) && !(tip1 && tip2);
+        unsigned int smax[AA_T]; /* per tile: max hi word of this lane's site (row) over k, i */
+#pragma unroll
+        for (int t = 0; t < AA_T; ++t) smax[t] = 0;
+
+        for (unsigned int k = 0; k < K; ++k)
+        {
+          double bL[15], bR[15];
+#pragma unroll
+          for (int f = 0; f < 15; ++f)
+          {
+            bL[f] = sL[(k * 15 + f) * 32 + lane];
+            bR[f] = sR[(k * 15 + f) * 32 + lane];
+          }
+#pragma unroll
+          for (int t = 0; t < AA_T; ++t)
+          {
+            const unsigned long long site = wsite0 + 8 * t + row;
+            const bool act = site < a.sites;
+            double aL[5], aR[5];
+            if (tip1)
+            {
+              const unsigned long long m = act ? s_tipmap[a.tipchars[d.c1_off + site]] : 0ull;
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks) aL[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+            }
+            else
+            {
+              const double * p = a.clv + d.c1_off + site * span + k * 20 + col;
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks) aL[ks] = act ? p[ks * 4] : 0.0;
+            }
+            if (tip2)
+            {
+              const unsigned long long m = act ? s_tipmap[a.tipchars[d.c2_off + site]] : 0ull;
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks) aR[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+            }
+            else
+            {
+              const double * p = a.clv + d.c2_off + site * span + k * 20 + col;
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks) aR[ks] = act ? p[ks * 4] : 0.0;
+            }
+            double xl[3][2], xr[3][2];
+#pragma unroll
+            for (int nt = 0; nt < 3; ++nt)
+            {
+              xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks)
+              {
+                dmma(xl[nt][0], xl[nt][1], aL[ks], bL[nt * 5 + ks]);
+                dmma(xr[nt][0], xr[nt][1], aR[ks], bR[nt * 5 + ks]);
+              }
+            }
+            /* D fragment: this lane holds parent[site][k][nt*8 + 2*col, +1] */
+            double * pd = a.clv + d.p_off + site * span + k * 20 + 2 * col;
+#pragma unroll
+            for (int nt = 0; nt < 3; ++nt)
+            {
+              const double o0 = xl[nt][0] * xr[nt][0], o1 = xl[nt][1] * xr[nt][1];
+              if (nt < 2 || col < 2)
+              {
+                if (check) smax[t] = max(smax[t], max((unsigned int)__double2hiint(o0), (unsigned int)__double2hiint(o1)));
+                if (act) *reinterpret_cast<double2 *>(pd + nt * 8) = make_double2(o0, o1);
+              }
+            }
+          }
+        }
+
+        /* ---- scalers + (rare) rescale pass ---- */
+        if (flags & AOPF_PS)
+        {
+#pragma unroll
+          for (int t = 0; t < AA_T; ++t)
+          {
+            unsigned int m = smax[t];
+            m = max(m, __shfl_xor_sync(0xffffffffu, m, 1));
+            m = max(m, __shfl_xor_sync(0xffffffffu, m, 2));
+            const bool scale = check && m < AA_THR_HI;
+            const unsigned long long site = wsite0 + 8 * t + row;
+            if (site < a.sites)
+            {
+              if (col == 0)
+              {
+                unsigned int v = scale ? 1u : 0u;
+                if (flags & AOPF_S1) v += a.scaler[d.s1_off + site];
+                if (flags & AOPF_S2) v += a.scaler[d.s2_off + site];
+                a.scaler[d.ps_off + site] = v;
+              }
+              if (scale)
+              {
+                /* each lane rescales exactly the entries it wrote: all k, cols 2*col(+1) of the n-tiles */
+                for (unsigned int k = 0; k < K; ++k)
+                {
+                  double * pd = a.clv + d.p_off + site * span + k * 20 + 2 * col;
+                  for (int nt = 0; nt < 3; ++nt)
+                    if (nt < 2 || col < 2)
+                    {
+                      pd[nt * 8] *= SCALE_FACTOR_D;
+                      pd[nt * 8 + 1] *= SCALE_FACTOR_D;
+                    }
+                }
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+/* ---- host ------------------------------------------------------------------------------------ */
+
+bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count)
+{
+  pll_partition_t * p = &c->pub;
+  const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
+  const unsigned int K = p->rate_cats;
+  static_assert(sizeof(AaOp) == 64, "AaOp is 8 x u64");
+  c->devop_scratch.resize((size_t)count * 8);
+  AaOp * dops = reinterpret_cast<AaOp *>(c->devop_scratch.data());
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    const pll_operation_t & o = ops[i];
+    AaOp & d = dops[i];
+    memset(&d, 0, sizeof(d));
+    d.p_off = (unsigned long long)(o.parent_clv_index - c->clv_first) * c->clv_stride;
+    if (pattern_tip && o.child1_clv_index < p->tips)
+    {
+      d.flags |= AOPF_TIP1;
+      d.c1_off = (unsigned long long)o.child1_clv_index * c->tip_stride;
+    }
+    else
+      d.c1_off = (unsigned long long)(o.child1_clv_index - c->clv_first) * c->clv_stride;
+    if (pattern_tip && o.child2_clv_index < p->tips)
+    {
+      d.flags |= AOPF_TIP2;
+      d.c2_off = (unsigned long long)o.child2_clv_index * c->tip_stride;
+    }
+    else
+      d.c2_off = (unsigned long long)(o.child2_clv_index - c->clv_first) * c->clv_stride;
+    if (o.parent_scaler_index >= 0)
+    {
+      d.flags |= AOPF_PS;
+      d.ps_off = (unsigned long long)o.parent_scaler_index * c->scaler_stride;
+    }
+    if (o.child1_scaler_index >= 0)
+    {
+      d.flags |= AOPF_S1;
+      d.s1_off = (unsigned long long)o.child1_scaler_index * c->scaler_stride;
+    }
+    if (o.child2_scaler_index >= 0)
+    {
+      d.flags |= AOPF_S2;
+      d.s2_off = (unsigned long long)o.child2_scaler_index * c->scaler_stride;
+    }
+    d.m1_off = o.child1_matrix_index * K * AA_FRAG;
+    d.m2_off = o.child2_matrix_index * K * AA_FRAG;
+  }
+  const AaOp * d_ops = (const AaOp *)dev_stage(c, dops, sizeof(AaOp) * count);
+  if (!d_ops) return false;
+  AaArgs a;
+  a.ops = d_ops;
+  a.nops = count;
+  a.sites = c->sites_alloc;
+  a.K = K;
+  a.clv = c->d_clv;
+  a.scaler = c->d_scaler;
+  a.frag = c->d_pmat_il;
+  a.tipchars = c->d_tipchars;
+  a.tipmap = c->d_tipmap;
+  const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 2 * 8 + (size_t)2 * 2 * K * AA_FRAG * sizeof(double);
+  static size_t smem_set = 0;
+  if (smem > smem_set)
+  {
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                         "trav_aa smem attribute"))
+      return false;
+    smem_set = smem;
+  }
+  int per_sm = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa_kernel, AA_WARPS * 32, smem) != cudaSuccess || per_sm < 1)
+    per_sm = 1;
+  const unsigned long long spc = (unsigned long long)AA_WARPS * 8 * AA_T;
+  unsigned long long blocks = (c->sites_alloc + spc - 1) / spc;
+  blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
+  if (blocks < 1) blocks = 1;
+  trav_aa_kernel<<<(unsigned int)blocks, AA_WARPS * 32, smem, c->stream>>>(a);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "trav_aa_kernel launch");
+}

@@ -1,0 +1,24 @@
+"""Protein (LG+G4) traversal timing: BASELINE configs[2] shape (500 taxa x 200k sites by default)."""
+import os, sys, time, json
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+import torch
+from pllharness import Harness, load_product_package
+tips = int(sys.argv[1]) if len(sys.argv) > 1 else 500
+sites = int(sys.argv[2]) if len(sys.argv) > 2 else 200000
+pkg = load_product_package()
+h = Harness("b200", tips=tips, sites=sites, states=20)
+stream = torch.cuda.Stream()
+pkg.load().pllb200_partition_set_stream(h.partition_ptr(0), stream.cuda_stream)
+ll = h.loglh(0)
+c = h.op_type_counts()
+alg = (c["ii"] * 1932 + c["ti"] * 1289 + c["tt"] * 646) * sites
+flops = (tips - 2) * sites * 6480.0
+ts = []
+for _ in range(4):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream); h.queue_update_partials(); e1.record(stream); torch.cuda.synchronize()
+    ts.append(e0.elapsed_time(e1))
+ms = sorted(ts)[1]
+print(json.dumps({"workload": "protein LG+G4 %d taxa x %d sites" % (tips, sites), "loglh": ll, "ops": c, "kernel_ms": ms,
+                  "site_updates_per_s": (tips - 2) * sites / ms * 1e3, "algorithmic_GBps": alg / ms / 1e6,
+                  "TFLOPs_fp64": flops / ms / 1e9}))
