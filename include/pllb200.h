@@ -447,6 +447,93 @@ int pllmod_treeinfo_update_partials(pllmod_treeinfo_t * treeinfo, int incrementa
 #define PLLMOD_OPT_ERROR_NEWTON_BAD_RADIUS 2250
 #define PLLMOD_OPT_BRLEN_OPTIMIZE_ALL -1
 
+/* parameter masks, O:30-43 */
+#define PLLMOD_OPT_PARAM_ALL (~0)
+#define PLLMOD_OPT_PARAM_SUBST_RATES (1 << 0)
+#define PLLMOD_OPT_PARAM_ALPHA (1 << 1)
+#define PLLMOD_OPT_PARAM_PINV (1 << 2)
+#define PLLMOD_OPT_PARAM_FREQUENCIES (1 << 3)
+#define PLLMOD_OPT_PARAM_BRANCHES_SINGLE (1 << 4)
+#define PLLMOD_OPT_PARAM_BRANCHES_ALL (1 << 5)
+#define PLLMOD_OPT_PARAM_BRANCHES_ITERATIVE (1 << 6)
+#define PLLMOD_OPT_PARAM_TOPOLOGY (1 << 7)
+#define PLLMOD_OPT_PARAM_FREE_RATES (1 << 8)
+#define PLLMOD_OPT_PARAM_RATE_WEIGHTS (1 << 9)
+#define PLLMOD_OPT_PARAM_BRANCH_LEN_SCALER (1 << 10)
+#define PLLMOD_OPT_PARAM_USER (1 << 16)
+/* L-BFGS-B bound types, O:46-49 */
+#define PLLMOD_OPT_LBFGSB_BOUND_NONE 0
+#define PLLMOD_OPT_LBFGSB_BOUND_LOWER 1
+#define PLLMOD_OPT_LBFGSB_BOUND_BOTH 2
+#define PLLMOD_OPT_LBFGSB_BOUND_UPPER 3
+/* defaults and limits, O:52-76 */
+#define PLLMOD_OPT_DEFAULT_RATE_RATIO 1
+#define PLLMOD_OPT_DEFAULT_FREQ_RATIO 1
+#define PLLMOD_OPT_DEFAULT_PINV 0.01
+#define PLLMOD_OPT_DEFAULT_ALPHA 0.5
+#define PLLMOD_OPT_MIN_SUBST_RATE 1.0e-3
+#define PLLMOD_OPT_MAX_SUBST_RATE 1000.
+#define PLLMOD_OPT_MIN_FREQ 1.0e-3
+#define PLLMOD_OPT_MAX_FREQ 100.
+#define PLLMOD_OPT_MIN_ALPHA 0.0201
+#define PLLMOD_OPT_MAX_ALPHA 100.
+#define PLLMOD_OPT_MIN_PINV 0
+#define PLLMOD_OPT_MAX_PINV 0.99
+#define PLLMOD_OPT_LNL_UNLIKELY -1e+80
+#define PLLMOD_OPT_MIN_RATE 0.02
+#define PLLMOD_OPT_MAX_RATE 100.
+#define PLLMOD_OPT_MIN_RATE_WEIGHT 1.0e-3
+#define PLLMOD_OPT_MAX_RATE_WEIGHT 100.
+#define PLLMOD_OPT_ERROR_PARAMETER 2000
+#define PLLMOD_OPT_ERROR_TAXA_MISMATCH 2010
+#define PLLMOD_OPT_ERROR_SEQLEN_MISMATCH 2020
+#define PLLMOD_OPT_ERROR_ALIGN_UNREADABLE 2030
+#define PLLMOD_OPT_ERROR_LBFGSB_UNKNOWN 2100
+#define PLLMOD_OPT_ERROR_BRENT_INIT 2310
+
+/* O:107-133: where and how the likelihood is evaluated for the Brent / L-BFGS-B drivers */
+typedef struct
+{
+  pll_partition_t * partition;
+  pll_operation_t * operations;
+  double * branch_lengths;
+  unsigned int * matrix_indices;
+  int rooted;
+  const unsigned int * params_indices;
+  union
+  {
+    struct
+    {
+      unsigned int root_clv_index;
+      int scaler_index;
+    } rooted_t;
+    struct
+    {
+      unsigned int parent_clv_index;
+      int parent_scaler_index;
+      unsigned int child_clv_index;
+      int child_scaler_index;
+      unsigned int edge_pmatrix_index;
+    } unrooted_t;
+  } where;
+  char __padding__[4];
+  double alpha_value;
+} pll_likelihood_info_t;
+
+/* O:135-149 */
+typedef struct
+{
+  pll_likelihood_info_t lk_params;
+  unsigned int highest_freq_state;
+  unsigned int highest_weight_state;
+  unsigned int params_index;
+  unsigned int which_parameters;
+  int * subst_params_symmetries;
+  double factr;
+  double pgtol;
+  double * sumtable;
+} pll_optimize_options_t;
+
 /* O:158-169 */
 typedef struct
 {
@@ -497,6 +584,34 @@ double pllmod_opt_minimize_newton(double xmin, double xguess, double xmax, doubl
 double pllmod_opt_minimize_newton_old(double x1, double xguess, double x2, double tolerance,
                                       unsigned int max_iters, void * params,
                                       void (*deriv_func)(void *, double, double *, double *));
+/* O:231-241 (opt_algorithms.c:418): L-BFGS-B with forward-difference gradients */
+double pllmod_opt_minimize_lbfgsb(double * x, double * xmin, double * xmax, int * bound,
+                                  unsigned int n, double factr, double pgtol, void * params,
+                                  double (*target_funk)(void *, double *));
+/* O:244-253 (opt_algorithms.c:1404): Brent within [xmin,xmax]; returns argmin, *fx = score */
+double pllmod_opt_minimize_brent(double xmin, double xguess, double xmax, double xtol, double * fx,
+                                 double * f2x, void * params, double (*target_funk)(void *, double));
+/* O:256-264 (opt_algorithms.c:1473): EM for mixture weights */
+void pllmod_opt_minimize_em(double * w, unsigned int w_count, double * sitecat_lh,
+                            unsigned int * site_w, unsigned int l, void * params,
+                            double (*update_sitecatlk_funk)(void *, double *));
+/* O:269-271 (pll_optimize.c:1146): derivative callback over pll_optimize_options_t */
+void pllmod_opt_derivative_func(void * parameters, double proposal, double * df, double * ddf);
+/* O:274-276 (pll_optimize.c:411): alpha / pinv / single branch by Brent; returns -logL */
+double pllmod_opt_optimize_onedim(pll_optimize_options_t * p, double min, double max);
+/* O:278-280 (pll_optimize.c:473): any parameter subset by L-BFGS-B; returns -logL */
+double pllmod_opt_optimize_multidim(pll_optimize_options_t * p, double * umin, double * umax);
+/* O:324-339 (opt_algorithms.c:1448): lock-step Brent over xnum variables */
+int pllmod_opt_minimize_brent_multi(unsigned int xnum, int * opt_mask, double * xmin,
+                                    double * xguess, double * xmax, double xtol, double * xopt,
+                                    double * fx, double * f2x, void * params,
+                                    double (*target_funk)(void *, double *, double *, int *),
+                                    int global_range);
+/* O:341-354 (opt_algorithms.c:628): lock-step L-BFGS-B over xnum partitions */
+double pllmod_opt_minimize_lbfgsb_multi(unsigned int xnum, double ** x, double ** xmin,
+                                        double ** xmax, int ** bound, unsigned int * n,
+                                        unsigned int nmax, double factr, double pgtol, void * params,
+                                        double (*target_funk)(void *, double **, double *, int *));
 /* O:283-291 (pll_optimize.c:1115) */
 double pllmod_opt_optimize_branch_lengths_iterative(pll_partition_t * partition, pll_unode_t * tree,
                                                     const unsigned int * params_indices,

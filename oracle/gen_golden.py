@@ -5,6 +5,8 @@ Run in the build container (needs /root/reference to have been compiled into ora
 Outputs (committed, small):
     tests/golden/lg_model.json      LG exchangeabilities + frequencies read from the reference library's
                                     exported tables pll_aa_rates_lg / pll_aa_freqs_lg (maps.c:288,1472)
+    tests/golden/ref_opt.json       Brent / L-BFGS-B / EM on analytic objectives and model-parameter optimisation
+                                    (pllmod_opt_optimize_onedim / _multidim) results of the reference
     tests/golden/ref_cases.json     logL / derivatives / scaler statistics / BLO results of the reference
                                     AVX2 path on the seeded synthetic inputs of oracle/harness.c
 """
@@ -65,7 +67,60 @@ def run_case(H, kw):
     return out
 
 
+# ---- optimiser goldens -> tests/golden/ref_opt.json ----------------------
+BRENT_CASES = [(fn, lo, g, hi, tol) for fn in range(4)
+               for (lo, g, hi, tol) in [(0.02, 0.5, 100.0, 1e-4), (1e-4, 2.0, 10.0, 1e-3), (0.02, 0.02, 5.0, 1e-2)]]
+LBFGSB_CASES = [
+    dict(fn=0, x0=[1.2, 1, 1.2, 1, 0.5], lo=[0.001] * 5, hi=[5] * 5, bound=[2] * 5),
+    dict(fn=1, x0=[1] * 6, lo=[0.001] * 6, hi=[2.5] * 6, bound=[2] * 6),
+    dict(fn=2, x0=[4, 3, 2, 1, 0.5], lo=[0.001] * 5, hi=[100] * 5, bound=[2, 2, 1, 1, 0]),
+    dict(fn=3, x0=[1] * 6, lo=[0.001] * 6, hi=[1000] * 6, bound=[2] * 6),
+    dict(fn=3, x0=[1] * 6, lo=[0.001] * 6, hi=[2.0] * 6, bound=[2] * 6),
+    dict(fn=2, x0=[1.2, 1, 1.2, 1, .5, .7], lo=[0.001] * 6, hi=[5] * 6, bound=[0] * 6),
+]
+# PLLMOD_OPT_PARAM_*: SUBST_RATES 1, ALPHA 2, PINV 4, FREQUENCIES 8, FREE_RATES 256, RATE_WEIGHTS 512
+MODEL_OPT_CASES = [
+    ("dna16_alpha_brent", dict(tips=16, sites=1000), dict(which=2, onedim=True, pgtol=1e-3, alpha_guess=0.7)),
+    ("dna16_pinv_brent", dict(tips=16, sites=1000, pinv=0.2), dict(which=4, onedim=True, pgtol=1e-3)),
+    ("dna16_rates_lbfgsb", dict(tips=16, sites=1000), dict(which=1, factr=1e7, pgtol=1e-4)),
+    ("dna16_rates_sym_lbfgsb", dict(tips=16, sites=1000),
+     dict(which=1, factr=1e7, pgtol=1e-4, symmetries=[0, 1, 0, 0, 1, 0])),
+    ("dna16_freqs_alpha_lbfgsb", dict(tips=16, sites=1000), dict(which=8 | 2, factr=1e7, pgtol=1e-4)),
+    ("dna16_freerates_weights_lbfgsb", dict(tips=16, sites=1000), dict(which=256 | 512, factr=1e7, pgtol=1e-4)),
+    ("dna16_pinv_alpha_lbfgsb", dict(tips=16, sites=1000, pinv=0.2), dict(which=4 | 2, factr=1e7, pgtol=1e-4)),
+    ("aa12_alpha_brent", dict(tips=12, sites=200, states=20), dict(which=2, onedim=True, pgtol=1e-3, alpha_guess=0.7)),
+]
+
+
+def dump_opt():
+    import pllharness as PH
+    out = {"brent": [], "lbfgsb": [], "model": {}}
+    for fn, lo, g, hi, tol in BRENT_CASES:
+        r = PH.test_brent("ref", fn, lo, g, hi, tol)
+        out["brent"].append(dict(args=[fn, lo, g, hi, tol], x=float(r["x"]), fx=float(r["fx"]), evals=r["evals"]))
+    for c in LBFGSB_CASES:
+        r = PH.test_lbfgsb("ref", c["fn"], c["x0"], c["lo"], c["hi"], c["bound"])
+        out["lbfgsb"].append(dict(args=c, score=r["score"], x=r["x"].tolist(), evals=r["evals"]))
+    rng = np.random.RandomState(3)
+    base = rng.rand(200, 4) * np.array([1, 2, 0.5, 3.0])
+    sw = rng.randint(1, 4, 200)
+    out["em"] = dict(seed=3, w=PH.test_em("ref", base, sw, [0.25] * 4).tolist())
+    for name, kw, okw in MODEL_OPT_CASES:
+        with PH.Harness("ref", **kw) as h:
+            start = h.loglh()
+            score = h.optimize_params(**okw)
+            m = h.model()
+            after = h.loglh()
+        out["model"][name] = dict(args=kw, opt=okw, start_loglh=start, score=score, loglh_after=after,
+                                  model={k: (v.tolist() if hasattr(v, "tolist") else float(v)) for k, v in m.items()})
+        print(name, start, score)
+    with open(os.path.join(GOLD, "ref_opt.json"), "w") as f:
+        json.dump(out, f, indent=1)
+
+
 def main():
+    if "--opt-only" in sys.argv:
+        return dump_opt()
     os.makedirs(GOLD, exist_ok=True)
     dump_lg()
     from pllharness import Harness
@@ -75,6 +130,7 @@ def main():
         print(name, res[name]["ref"]["loglh"])
     with open(os.path.join(GOLD, "ref_cases.json"), "w") as f:
         json.dump(res, f, indent=1)
+    dump_opt()
 
 
 if __name__ == "__main__":

@@ -599,3 +599,268 @@ void h_op_type_counts(void * hv, unsigned int p, unsigned int nops, unsigned int
     out[t1 && t2 ? 0 : ((t1 || t2) ? 1 : 2)]++;
   }
 }
+
+/* ---- scalar optimisers --------------------------------------------------- */
+
+/* analytic objectives so that Brent / L-BFGS-B / EM can be compared between the two libraries
+ * without a device: the algorithms are pure host code */
+typedef struct
+{
+  int kind;
+  int n;
+  int evals;
+} analytic_t;
+
+static double analytic_value(const analytic_t * a, const double * x)
+{
+  double f = 0.0;
+  switch (a->kind)
+  {
+    case 0: /* extended Rosenbrock */
+      for (int i = 0; i + 1 < a->n; ++i)
+        f += 100.0 * (x[i + 1] - x[i] * x[i]) * (x[i + 1] - x[i] * x[i]) + (1.0 - x[i]) * (1.0 - x[i]);
+      return f + 3.0;
+    case 1: /* ill-conditioned quadratic with minimum outside typical boxes */
+      for (int i = 0; i < a->n; ++i) f += (double)(i + 1) * (i + 1) * (x[i] - 3.0 + i) * (x[i] - 3.0 + i);
+      return f + 10.0;
+    case 2: /* smooth non-quadratic: sum of cosh + coupling */
+      for (int i = 0; i < a->n; ++i) f += cosh(0.5 * (x[i] - 1.5)) + 0.1 * x[i] * x[(i + 1) % a->n];
+      return f + 100.0;
+    default: /* -log of a Gamma-like density in every coordinate (likelihood-shaped) */
+      for (int i = 0; i < a->n; ++i) f += -((2.0 + i) * log(x[i]) - 1.7 * x[i]);
+      return f + 50.0;
+  }
+}
+static double analytic_cb(void * p, double * x)
+{
+  analytic_t * a = (analytic_t *)p;
+  a->evals++;
+  const double v = analytic_value(a, x);
+  if (getenv("H_TRACE"))
+  {
+    fprintf(stderr, "eval %d f=%.17g x=", a->evals, v);
+    for (int i = 0; i < a->n; ++i) fprintf(stderr, " %.17g", x[i]);
+    fprintf(stderr, "\n");
+  }
+  return v;
+}
+static double analytic_cb1(void * p, double x)
+{
+  analytic_t * a = (analytic_t *)p;
+  a->evals++;
+  switch (a->kind)
+  {
+    case 0: return (x - 2.0) * (x - 2.0) + 1.0;
+    case 1: return cosh(x - 0.3) + 0.01 * x;
+    case 2: return -(3.0 * log(x) - 4.0 * x) + 20.0;
+    default: return fabs(x - 0.7) + 0.5 * x * x; /* kink */
+  }
+}
+
+/* out = {xopt, fx, f2x, evals} */
+void h_test_brent(int kind, double xmin, double xguess, double xmax, double xtol, double * out)
+{
+  analytic_t a = {kind, 1, 0};
+  double fx = 0, f2x = 0;
+  out[0] = pllmod_opt_minimize_brent(xmin, xguess, xmax, xtol, &fx, &f2x, &a, analytic_cb1);
+  out[1] = fx;
+  out[2] = f2x;
+  out[3] = a.evals;
+}
+
+typedef struct
+{
+  int n;
+  int kinds[8];
+  int evals;
+} analytic_multi_t;
+static double analytic_multi_cb(void * p, double * x, double * fx, int * converged)
+{
+  analytic_multi_t * a = (analytic_multi_t *)p;
+  a->evals++;
+  double tot = 0;
+  for (int i = 0; i < a->n; ++i)
+  {
+    analytic_t one = {a->kinds[i], 1, 0};
+    const double v = analytic_cb1(&one, x[i]);
+    if (fx) fx[i] = v;
+    tot += v;
+  }
+  if (converged)
+  {
+    int all = 1;
+    for (int i = 0; i < a->n; ++i) all &= converged[i];
+    converged[a->n] = all;
+  }
+  return tot;
+}
+/* xguess[n] in; out = xopt[n] then fx[n] then {evals} */
+int h_test_brent_multi(int n, const int * kinds, const int * mask, const double * xmin,
+                       double * xguess, const double * xmax, double xtol, int global_range, double * out)
+{
+  analytic_multi_t a;
+  a.n = n;
+  a.evals = 0;
+  for (int i = 0; i < n; ++i) a.kinds[i] = kinds[i];
+  double f2x[8] = {0};
+  const int rc = pllmod_opt_minimize_brent_multi((unsigned)n, (int *)mask, (double *)xmin, xguess,
+                                                 (double *)xmax, xtol, out, out + n, f2x, &a,
+                                                 analytic_multi_cb, global_range);
+  out[2 * n] = a.evals;
+  return rc;
+}
+
+/* x[n] in/out; returns score; evals[0] = number of objective calls */
+double h_test_lbfgsb(int kind, int n, double * x, double * xmin, double * xmax, int * bound,
+                     double factr, double pgtol, int * evals)
+{
+  analytic_t a = {kind, n, 0};
+  const double score = pllmod_opt_minimize_lbfgsb(x, xmin, xmax, bound, (unsigned)n, factr, pgtol, &a,
+                                                  analytic_cb);
+  *evals = a.evals;
+  return score;
+}
+
+typedef struct
+{
+  int parts;
+  int kinds[8];
+  int n[8];
+  int evals;
+} lbfgsb_multi_t;
+static double lbfgsb_multi_cb(void * p, double ** x, double * fx, int * flags)
+{
+  lbfgsb_multi_t * a = (lbfgsb_multi_t *)p;
+  if (!x)
+  {
+    /* flag reduction (what the parallel callback does across ranks) */
+    int all = 1;
+    for (int i = 0; i < a->parts; ++i) all &= flags[i];
+    flags[a->parts] = all;
+    return 0.0;
+  }
+  a->evals++;
+  double tot = 0;
+  for (int i = 0; i < a->parts; ++i)
+  {
+    if (flags && flags[i]) continue;
+    analytic_t one = {a->kinds[i], a->n[i], 0};
+    const double v = analytic_value(&one, x[i]);
+    if (fx) fx[i] = v;
+    tot += v;
+  }
+  return tot;
+}
+/* xflat: concatenated x per partition (in/out), bounds likewise */
+double h_test_lbfgsb_multi(int parts, const int * kinds, const int * n, double * xflat, double * lo,
+                           double * hi, int * bound, double factr, double pgtol, int * evals)
+{
+  lbfgsb_multi_t a;
+  a.parts = parts;
+  a.evals = 0;
+  double * xs[8], *los[8], *his[8];
+  int * bs[8];
+  unsigned int ns[8], nmax = 0;
+  int off = 0;
+  for (int i = 0; i < parts; ++i)
+  {
+    a.kinds[i] = kinds[i];
+    a.n[i] = n[i];
+    xs[i] = xflat + off, los[i] = lo + off, his[i] = hi + off, bs[i] = bound + off;
+    ns[i] = (unsigned)n[i];
+    if (ns[i] > nmax) nmax = ns[i];
+    off += n[i];
+  }
+  const double s = pllmod_opt_minimize_lbfgsb_multi((unsigned)parts, xs, los, his, bs, ns, nmax, factr,
+                                                    pgtol, &a, lbfgsb_multi_cb);
+  *evals = a.evals;
+  return s;
+}
+
+typedef struct
+{
+  unsigned int l, c;
+  const double * base; /* l*c per-site, per-category conditional likelihoods */
+  double * w;
+} em_t;
+static double em_cb(void * p, double * sitecat)
+{
+  em_t * e = (em_t *)p;
+  for (unsigned int i = 0; i < e->l; ++i)
+    for (unsigned int k = 0; k < e->c; ++k) sitecat[i * e->c + k] = e->base[i * e->c + k] * e->w[k];
+  return 0.0;
+}
+void h_test_em(unsigned int l, unsigned int c, const double * base, unsigned int * site_w, double * w)
+{
+  em_t e = {l, c, base, w};
+  double * buf = (double *)calloc((size_t)l * c, sizeof(double));
+  pllmod_opt_minimize_em(w, c, buf, site_w, l, &e, em_cb);
+  free(buf);
+}
+
+/* model-parameter optimisation of partition p at the current root edge through
+ * pllmod_opt_optimize_onedim (Brent) or _multidim (L-BFGS-B); `which` = PLLMOD_OPT_PARAM_* mask.
+ * out = {score, alpha, pinv, rates[6 or n], freqs[states], ...} filled by h_get_model */
+static int cb_trav_all(pll_unode_t * n)
+{
+  (void)n;
+  return 1;
+}
+double h_optimize_params(void * hv, unsigned int p, unsigned int which, double factr, double pgtol,
+                         double alpha_guess, const int * symmetries, int use_onedim)
+{
+  harness_t * h = (harness_t *)hv;
+  pllmod_treeinfo_t * ti = h->ti;
+  pll_partition_t * part = h->parts[p];
+  const unsigned int tips = h->tips, nodes = 2 * tips - 2;
+  pll_unode_t ** trav = (pll_unode_t **)malloc(sizeof(pll_unode_t *) * nodes);
+  unsigned int trav_size = 0, mcount = 0, ocount = 0;
+  pll_unode_t * root = ti->root;
+  if (!pll_utree_traverse(root, PLL_TREE_TRAVERSE_POSTORDER, cb_trav_all, trav, &trav_size)) return NAN;
+  double * brlens = (double *)malloc(sizeof(double) * (2 * tips - 3));
+  unsigned int * midx = (unsigned int *)malloc(sizeof(unsigned int) * (2 * tips - 3));
+  pll_operation_t * ops = (pll_operation_t *)malloc(sizeof(pll_operation_t) * (tips - 2));
+  pll_utree_create_operations(trav, trav_size, brlens, midx, ops, &mcount, &ocount);
+
+  pll_optimize_options_t o;
+  memset(&o, 0, sizeof(o));
+  o.lk_params.partition = part;
+  o.lk_params.operations = ops;
+  o.lk_params.branch_lengths = brlens;
+  o.lk_params.matrix_indices = midx;
+  o.lk_params.rooted = 0;
+  o.lk_params.params_indices = h->param_idx[p];
+  o.lk_params.alpha_value = alpha_guess;
+  o.lk_params.where.unrooted_t.parent_clv_index = root->clv_index;
+  o.lk_params.where.unrooted_t.parent_scaler_index = root->scaler_index;
+  o.lk_params.where.unrooted_t.child_clv_index = root->back->clv_index;
+  o.lk_params.where.unrooted_t.child_scaler_index = root->back->scaler_index;
+  o.lk_params.where.unrooted_t.edge_pmatrix_index = root->pmatrix_index;
+  o.params_index = 0;
+  o.which_parameters = which;
+  o.subst_params_symmetries = (int *)symmetries;
+  o.factr = factr;
+  o.pgtol = pgtol;
+  /* bring P-matrices and CLVs up to date first (the reference callers do the same) */
+  pll_update_prob_matrices(part, h->param_idx[p], midx, brlens, mcount);
+  pll_update_partials(part, ops, ocount);
+  const double score = use_onedim ? pllmod_opt_optimize_onedim(&o, 0, 0) : pllmod_opt_optimize_multidim(&o, NULL, NULL);
+  free(trav);
+  free(brlens);
+  free(midx);
+  free(ops);
+  pllmod_treeinfo_invalidate_all(ti);
+  return score;
+}
+
+/* out: alpha-independent model read-back = rates[K], rate_weights[K], pinv, subst[s(s-1)/2], freqs[s] */
+void h_get_model(void * hv, unsigned int p, double * out)
+{
+  pll_partition_t * part = ((harness_t *)hv)->parts[p];
+  const unsigned int K = part->rate_cats, s = part->states, nr = s * (s - 1) / 2;
+  memcpy(out, part->rates, sizeof(double) * K);
+  memcpy(out + K, part->rate_weights, sizeof(double) * K);
+  out[2 * K] = part->prop_invar[0];
+  memcpy(out + 2 * K + 1, part->subst_params[0], sizeof(double) * nr);
+  memcpy(out + 2 * K + 1 + nr, part->frequencies[0], sizeof(double) * s);
+}

@@ -111,8 +111,75 @@ def _lib(kind):
         lib.h_op_type_counts.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p]
         lib.h_ops_counter.restype = C.c_uint
         lib.h_ops_counter.argtypes = [C.c_void_p]
+        lib.h_test_brent.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_void_p]
+        lib.h_test_brent_multi.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_double, C.c_int, C.c_void_p]
+        lib.h_test_lbfgsb.restype = C.c_double
+        lib.h_test_lbfgsb.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                      C.c_double, C.c_double, C.c_void_p]
+        lib.h_test_lbfgsb_multi.restype = C.c_double
+        lib.h_test_lbfgsb_multi.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_void_p, C.c_void_p, C.c_double, C.c_double, C.c_void_p]
+        lib.h_test_em.argtypes = [C.c_uint, C.c_uint, C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.h_optimize_params.restype = C.c_double
+        lib.h_optimize_params.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_double, C.c_double,
+                                          C.c_double, C.c_void_p, C.c_int]
+        lib.h_get_model.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
         _libs[kind] = lib
     return _libs[kind]
+
+
+# ---- scalar optimisers on analytic objectives (pure host code: no device involved) ----
+def test_brent(kind, fn, xmin, xguess, xmax, xtol):
+    out = np.zeros(4)
+    _lib(kind).h_test_brent(fn, xmin, xguess, xmax, xtol, out.ctypes.data)
+    return dict(x=out[0], fx=out[1], f2x=out[2], evals=int(out[3]))
+
+
+def test_brent_multi(kind, fns, mask, xmin, xguess, xmax, xtol, global_range):
+    n = len(fns)
+    i32 = lambda v: np.ascontiguousarray(v, dtype=np.int32)
+    f64 = lambda v: np.ascontiguousarray(v, dtype=np.float64)
+    fns, lo, g, hi = i32(fns), f64(xmin), f64(xguess).copy(), f64(xmax)
+    m = i32(mask) if mask is not None else None
+    out = np.zeros(2 * n + 1)
+    rc = _lib(kind).h_test_brent_multi(n, fns.ctypes.data, m.ctypes.data if m is not None else None,
+                                       lo.ctypes.data, g.ctypes.data, hi.ctypes.data, xtol, global_range,
+                                       out.ctypes.data)
+    return dict(rc=rc, x=out[:n].copy(), fx=out[n:2 * n].copy(), evals=int(out[2 * n]))
+
+
+def test_lbfgsb(kind, fn, x0, lo, hi, bound, factr=1e7, pgtol=1e-5):
+    x = np.ascontiguousarray(x0, dtype=np.float64).copy()
+    lo = np.ascontiguousarray(lo, dtype=np.float64)
+    hi = np.ascontiguousarray(hi, dtype=np.float64)
+    b = np.ascontiguousarray(bound, dtype=np.int32)
+    ev = C.c_int(0)
+    score = _lib(kind).h_test_lbfgsb(fn, len(x), x.ctypes.data, lo.ctypes.data, hi.ctypes.data,
+                                     b.ctypes.data, factr, pgtol, C.byref(ev))
+    return dict(score=score, x=x, evals=ev.value)
+
+
+def test_lbfgsb_multi(kind, fns, ns, x0, lo, hi, bound, factr=1e7, pgtol=1e-5):
+    x = np.ascontiguousarray(x0, dtype=np.float64).copy()
+    lo = np.ascontiguousarray(lo, dtype=np.float64)
+    hi = np.ascontiguousarray(hi, dtype=np.float64)
+    b = np.ascontiguousarray(bound, dtype=np.int32)
+    fns = np.ascontiguousarray(fns, dtype=np.int32)
+    ns = np.ascontiguousarray(ns, dtype=np.int32)
+    ev = C.c_int(0)
+    score = _lib(kind).h_test_lbfgsb_multi(len(fns), fns.ctypes.data, ns.ctypes.data, x.ctypes.data,
+                                           lo.ctypes.data, hi.ctypes.data, b.ctypes.data, factr, pgtol,
+                                           C.byref(ev))
+    return dict(score=score, x=x, evals=ev.value)
+
+
+def test_em(kind, base, site_w, w0):
+    base = np.ascontiguousarray(base, dtype=np.float64)
+    sw = np.ascontiguousarray(site_w, dtype=np.uint32)
+    w = np.ascontiguousarray(w0, dtype=np.float64).copy()
+    _lib(kind).h_test_em(base.shape[0], base.shape[1], base.ctypes.data, sw.ctypes.data, w.ctypes.data)
+    return w
 
 
 class Harness:
@@ -239,6 +306,20 @@ class Harness:
 
     def optimize_branch_lengths_single(self, radius=-1, smoothings=2, tolerance=0.1):
         return self.lib.h_optimize_branch_lengths_single(self.h, radius, smoothings, tolerance)
+
+    def optimize_params(self, which, p=0, factr=1e7, pgtol=1e-4, alpha_guess=0.7, symmetries=None,
+                        onedim=False):
+        sym = np.ascontiguousarray(symmetries, dtype=np.int32) if symmetries is not None else None
+        return self.lib.h_optimize_params(self.h, p, which, factr, pgtol, alpha_guess,
+                                          sym.ctypes.data if sym is not None else None, int(onedim))
+
+    def model(self, p=0):
+        K, s = self.rate_cats, self.states[p]
+        nr = s * (s - 1) // 2
+        out = np.zeros(2 * K + 1 + nr + s)
+        self.lib.h_get_model(self.h, p, out.ctypes.data)
+        return dict(rates=out[:K].copy(), weights=out[K:2 * K].copy(), pinv=out[2 * K],
+                    subst=out[2 * K + 1:2 * K + 1 + nr].copy(), freqs=out[2 * K + 1 + nr:].copy())
 
     def set_alpha(self, alpha, p=0):
         assert self.lib.h_set_alpha(self.h, p, alpha)

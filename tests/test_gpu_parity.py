@@ -247,3 +247,29 @@ def test_large_full_size_properties():
         for node in (kw["tips"], kw["tips"] + 17, nsub - 1):
             h.set_root(node)
             assert rel(h.loglh(), full) < 1e-9
+
+
+# ---- model-parameter optimisers over device-resident state ----
+OPT_GOLD = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_opt.json")))
+
+
+@pytest.mark.parametrize("name", sorted(OPT_GOLD["model"].keys()))
+def test_model_parameter_optimisation_matches_reference(name):
+    """pllmod_opt_optimize_onedim (Brent) / _multidim (L-BFGS-B): every objective call is a device
+    traversal + logL.  Tolerances: final -logL 1e-7 relative (the optimisers stop at factr=1e7*eps ~ 2e-9
+    relative improvements / xtol 1e-3), parameters 2e-3 relative."""
+    case = OPT_GOLD["model"][name]
+    with Harness("b200", **case["args"]) as h:
+        start = h.loglh()
+        assert rel(start, case["start_loglh"]) < 1e-8
+        score = h.optimize_params(**case["opt"])
+        m = h.model()
+        after = h.loglh()
+    assert rel(score, case["score"]) < 1e-7, (score, case["score"])
+    assert rel(-after, score) < 1e-9  # the partition is left at the optimum
+    for k, v in case["model"].items():
+        np.testing.assert_allclose(m[k], v, rtol=2e-3, atol=1e-5, err_msg=k)
+    if have_reference():
+        with Harness("ref", **case["args"]) as r:
+            rscore = r.optimize_params(**case["opt"])
+        assert rel(score, rscore) < 1e-7

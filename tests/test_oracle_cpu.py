@@ -190,3 +190,71 @@ def test_multi_rank_site_sharding_with_gloo():
     line = [l for l in out.splitlines() if l.startswith("RESULT")][0]
     sharded, single = [float(x) for x in line.split()[1:3]]
     assert abs(sharded - single) <= 1e-10 * abs(single)
+
+
+# ---- scalar optimisers: pure host code, so parity is checked on the CPU box ----
+OPT_GOLD = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_opt.json")))
+
+
+def test_brent_is_bit_identical_to_reference_golden():
+    """pllmod_opt_minimize_brent (opt_algorithms.c:1404): same abscissae, same number of objective calls."""
+    import pllharness as PH
+    for case in OPT_GOLD["brent"]:
+        r = PH.test_brent("b200", *case["args"])
+        assert r["x"] == case["x"] and r["fx"] == case["fx"] and r["evals"] == case["evals"], (case, r)
+        if have_reference():
+            q = PH.test_brent("ref", *case["args"])
+            assert q["x"] == r["x"] and q["f2x"] == r["f2x"]
+
+
+def test_brent_multi_lockstep_mask_and_ranges():
+    """pllmod_opt_minimize_brent_multi (opt_algorithms.c:1448): masks, per-variable ranges, global range."""
+    import pllharness as PH
+    a = PH.test_brent_multi("b200", [0, 1, 2, 3], [1, 1, 0, 1], [0.02], [0.5, 1.0, 2.0, 0.1], [100.0], 1e-3, 1)
+    assert abs(a["x"][0] - 2.0) < 1e-3 and abs(a["x"][1] - 0.29) < 1e-3 and abs(a["x"][3] - 0.7) < 1e-3
+    assert a["x"][2] == 0.0  # masked out: untouched slot, as in the reference
+    b = PH.test_brent_multi("b200", [0, 2], None, [0.02, 0.1], [0.5, 1.0], [1.5, 0.6], 1e-3, 0)
+    assert abs(b["x"][0] - 1.5) < 2e-3 and abs(b["x"][1] - 0.6) < 2e-3  # minima outside -> upper bounds
+    if have_reference():
+        ra = PH.test_brent_multi("ref", [0, 1, 2, 3], [1, 1, 0, 1], [0.02], [0.5, 1.0, 2.0, 0.1], [100.0], 1e-3, 1)
+        rb = PH.test_brent_multi("ref", [0, 2], None, [0.02, 0.1], [0.5, 1.0], [1.5, 0.6], 1e-3, 0)
+        assert np.array_equal(ra["x"], a["x"]) and ra["evals"] == a["evals"]
+        assert np.array_equal(rb["x"], b["x"]) and rb["evals"] == b["evals"]
+
+
+def test_lbfgsb_matches_reference_golden():
+    """pllmod_opt_minimize_lbfgsb (opt_algorithms.c:418): our from-the-paper L-BFGS-B reproduces the
+    reference's iterates on box-constrained problems (same number of objective calls; x to 1e-8), and its
+    optimum within the solver's own stopping tolerance on the unconstrained one."""
+    import pllharness as PH
+    for case in OPT_GOLD["lbfgsb"]:
+        c = case["args"]
+        r = PH.test_lbfgsb("b200", c["fn"], c["x0"], c["lo"], c["hi"], c["bound"])
+        assert abs(r["score"] - case["score"]) <= 1e-7 * abs(case["score"]), (case, r)
+        if all(b == 2 for b in c["bound"]):
+            assert r["evals"] == case["evals"], (case["evals"], r["evals"])
+            np.testing.assert_allclose(r["x"], case["x"], rtol=1e-8, atol=1e-10)
+        else:
+            np.testing.assert_allclose(r["x"], case["x"], rtol=1e-4, atol=1e-5)
+
+
+def test_lbfgsb_multi_and_em():
+    import pllharness as PH
+    fns, ns = [0, 3, 1], [4, 6, 3]
+    x0 = [1.2, 1, 1.2, 1] + [1] * 6 + [1] * 3
+    lo, hi, bd = [0.001] * 13, [5] * 4 + [1000] * 6 + [2.5] * 3, [2] * 13
+    m = PH.test_lbfgsb_multi("b200", fns, ns, x0, lo, hi, bd)
+    off = 0
+    for fn, n in zip(fns, ns):
+        s = PH.test_lbfgsb("b200", fn, x0[off:off + n], lo[off:off + n], hi[off:off + n], bd[off:off + n])
+        np.testing.assert_allclose(m["x"][off:off + n], s["x"], rtol=1e-12)  # lock-step == one by one
+        off += n
+    if have_reference():
+        r = PH.test_lbfgsb_multi("ref", fns, ns, x0, lo, hi, bd)
+        np.testing.assert_allclose(m["x"], r["x"], rtol=1e-8)
+        assert abs(m["score"] - r["score"]) < 1e-9 * abs(r["score"])
+    rng = np.random.RandomState(OPT_GOLD["em"]["seed"])
+    base = rng.rand(200, 4) * np.array([1, 2, 0.5, 3.0])
+    sw = rng.randint(1, 4, 200)
+    w = PH.test_em("b200", base, sw, [0.25] * 4)
+    np.testing.assert_allclose(w, OPT_GOLD["em"]["w"], rtol=1e-12)
