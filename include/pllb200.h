@@ -222,6 +222,11 @@ void pll_set_pattern_weights(pll_partition_t * partition, const unsigned int * p
 /* L:674-675 (pll.c:133,148) */
 void * pll_aligned_alloc(size_t size, size_t alignment);
 void pll_aligned_free(void * ptr);
+/* L:655-659 (pll.c:1145,1193): ascertainment-bias correction type (PLL_ATTRIB_AB_LEWIS /
+ * _FELSENSTEIN / _STAMATAKIS; the partition must have been created with an AB attribute) and the
+ * weights of the `states` invariant dummy sites */
+int pll_set_asc_bias_type(pll_partition_t * partition, int asc_bias_type);
+void pll_set_asc_state_weights(pll_partition_t * partition, const unsigned int * state_weights);
 /* pll.c:1202 */
 void pll_fill_parent_scaler(unsigned int scaler_size, unsigned int * parent_scaler,
                             const unsigned int * left_scaler, const unsigned int * right_scaler);

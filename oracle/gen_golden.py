@@ -41,6 +41,13 @@ CASES = [
                                      attributes=(1 << 4) | (1 << 9))),
     ("aa12", dict(tips=12, sites=200, states=20, rate_cats=4)),
     ("odd5", dict(tips=10, sites=300, states=5, rate_cats=3)),
+    # ascertainment bias (attributes: PATTERN_TIP 1<<4, AB_FLAG 1<<8, type 1..3 << 5)
+    ("dna12_asc_lewis", dict(tips=12, sites=300, states=4, rate_cats=4, attributes=(1 << 4) | (1 << 8) | (1 << 5))),
+    ("dna12_asc_felsenstein_notip", dict(tips=12, sites=300, states=4, rate_cats=4, attributes=(1 << 8) | (2 << 5))),
+    ("aa12_asc_stamatakis", dict(tips=12, sites=150, states=20, rate_cats=4, attributes=(1 << 4) | (1 << 8) | (3 << 5))),
+    ("aa12_asc_lewis", dict(tips=12, sites=150, states=20, rate_cats=4, attributes=(1 << 4) | (1 << 8) | (1 << 5))),
+    ("dna150_deep_asc_felsenstein", dict(tips=150, sites=200, states=4, rate_cats=4, brlen_scale=8.0,
+                                         attributes=(1 << 4) | (1 << 8) | (2 << 5))),
     ("multi", dict(tips=20, sites=[300, 150, 200], states=[4, 20, 4], rate_cats=4, alpha=[0.3, 0.5, 1.1])),
 ]
 

@@ -185,6 +185,13 @@ static pll_partition_t * make_partition(unsigned int part, unsigned int tips, un
     }
   }
   free(seq);
+  if (attributes & PLL_ATTRIB_AB_MASK)
+  {
+    /* ascertainment bias: weights of the per-state dummy sites (used by Felsenstein / Stamatakis) */
+    unsigned int aw[64];
+    for (unsigned int i = 0; i < states; ++i) aw[i] = 1 + (i % 3);
+    pll_set_asc_state_weights(p, aw);
+  }
   if (pinv > 0.0)
     if (!pll_update_invariant_sites_proportion(p, 0, pinv)) return NULL;
   return p;

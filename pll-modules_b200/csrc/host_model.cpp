@@ -450,6 +450,42 @@ extern "C" void pll_set_pattern_weights(pll_partition_t * partition,
   ctx_of(p)->weights_dirty = true;
 }
 
+extern "C" int pll_set_asc_bias_type(pll_partition_t * p, int asc_bias_type)
+{
+  /* pll.c:1145-1191 */
+  const int attr = asc_bias_type & PLL_ATTRIB_AB_MASK;
+  if (!p->asc_bias_alloc)
+  {
+    pllb200_set_error(PLL_ERROR_AB_NOSUPPORT,
+                      "Partition was not created with ascertainment bias support");
+    return PLL_FAILURE;
+  }
+  double pinv = 0.0;
+  for (unsigned int i = 0; i < p->rate_matrices; ++i) pinv += p->prop_invar[i];
+  if (asc_bias_type != 0 && pinv != 0.0)
+  {
+    pllb200_set_error(PLL_ERROR_INVAR_INCOMPAT,
+                      "Invariant sites are not compatible with asc bias correction");
+    return PLL_FAILURE;
+  }
+  if (attr != asc_bias_type || attr > PLL_ATTRIB_AB_STAMATAKIS)
+  {
+    pllb200_set_error(PLL_ERROR_AB_INVALIDMETHOD, "Illegal ascertainment bias algorithm \"%d\"",
+                      asc_bias_type);
+    return PLL_FAILURE;
+  }
+  p->attributes &= ~(unsigned int)PLL_ATTRIB_AB_MASK;
+  p->attributes |= (unsigned int)attr;
+  return PLL_SUCCESS;
+}
+
+extern "C" void pll_set_asc_state_weights(pll_partition_t * p, const unsigned int * state_weights)
+{
+  /* pll.c:1193-1200: weights of the `states` dummy sites that follow the real ones */
+  memcpy(p->pattern_weights + p->sites, state_weights, sizeof(unsigned int) * p->states);
+  ctx_of(p)->weights_dirty = true;
+}
+
 extern "C" void pll_fill_parent_scaler(unsigned int scaler_size, unsigned int * parent_scaler,
                                        const unsigned int * left_scaler,
                                        const unsigned int * right_scaler)

@@ -340,6 +340,77 @@ __global__ void __launch_bounds__(DVG_THREADS) deriv_generic_kernel(DerivArgs a)
   grid_reduce_finish<2>(v, a.red);
 }
 
+/* ---- ascertainment-bias terms of the derivatives (core_derivatives.c:852-924) ------------------
+ * Lewis / Felsenstein: (A0,A1,A2) = sum over the `states` extra sites of (L,L',L'') * 2^(-256 c_n);
+ *   Lewis        d_f  += W A1/(A0-1),            dd_f += W ((A0-1) A2 - A1^2)/(A0-1)^2
+ *   Felsenstein  d_f  -= Winv A1/A0,             dd_f -= Winv (A2 A0 - A1^2)/A0^2
+ * Stamatakis needs nothing here: the main kernel simply runs over sites + states.
+ * One CTA, thread n = state n, same stream as the reducing kernel whose result slot it rewrites. */
+#define ASC_THREADS 64
+
+__global__ void __launch_bounds__(ASC_THREADS) asc_deriv_kernel(DerivArgs a, unsigned int real_sites,
+                                                               const unsigned int * pscaler,
+                                                               const unsigned int * cscaler,
+                                                               int asc_type, unsigned int weight_sum)
+{
+  __shared__ double s_l[3][ASC_THREADS];
+  const unsigned int K = a.K, s = a.states, sp = a.sp, n = threadIdx.x;
+  if (n < s)
+  {
+    const unsigned long long site = (unsigned long long)real_sites + n;
+    double t0 = 0.0, t1 = 0.0, t2 = 0.0;
+    for (unsigned int k = 0; k < K; ++k)
+    {
+      const double * sm = a.sum + (site * K + k) * sp;
+      const double * dg = a.diag + (size_t)k * s * 3;
+      double L0 = 0.0, L1 = 0.0, L2 = 0.0;
+      for (unsigned int j = 0; j < s; ++j)
+      {
+        const double v = sm[j];
+        L0 += v * dg[j * 3 + 0];
+        L1 += v * dg[j * 3 + 1];
+        L2 += v * dg[j * 3 + 2];
+      }
+      t0 += L0 * a.w[k];
+      t1 += L1 * a.w[k];
+      t2 += L2 * a.w[k];
+    }
+    int sc = 0;
+    if (pscaler) sc += (int)pscaler[site];
+    if (cscaler) sc += (int)cscaler[site];
+    s_l[0][n] = scalbn(t0, -256 * sc);
+    s_l[1][n] = scalbn(t1, -256 * sc);
+    s_l[2][n] = scalbn(t2, -256 * sc);
+  }
+  __syncthreads();
+  if (n != 0) return;
+  double A0 = 0.0, A1 = 0.0, A2 = 0.0;
+  unsigned int sum_w_inv = 0;
+  for (unsigned int q = 0; q < s; ++q)
+  {
+    A0 += s_l[0][q];
+    A1 += s_l[1][q];
+    A2 += s_l[2][q];
+    sum_w_inv += a.weights[real_sites + q];
+  }
+  double df = a.red.result_dev[0], ddf = a.red.result_dev[1];
+  if (asc_type == PLL_ATTRIB_AB_LEWIS)
+  {
+    df += (double)weight_sum * (A1 / (A0 - 1.0));
+    ddf += (double)weight_sum * (((A0 - 1.0) * A2 - A1 * A1) / ((A0 - 1.0) * (A0 - 1.0)));
+  }
+  else
+  {
+    df -= (double)sum_w_inv * (A1 / A0);
+    ddf -= (double)sum_w_inv * (((A2 * A0) - A1 * A1) / (A0 * A0));
+  }
+  a.red.result_dev[0] = df;
+  a.red.result_dev[1] = ddf;
+  a.red.result_host[0] = df;
+  a.red.result_host[1] = ddf;
+  __threadfence_system();
+}
+
 /* ---- host ------------------------------------------------------------------------------------ */
 
 bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_clv,
@@ -423,8 +494,7 @@ bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_cl
 bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double branch_length,
                         const unsigned int * params_indices, const double * d_sumtable, int slot)
 {
-  (void)parent_scaler;
-  (void)child_scaler; /* ratios L'/L cancel the scaling; only asc-bias would need them */
+  /* ratios L'/L cancel the scaling; only the asc-bias terms need the scalers */
   pll_partition_t * p = &c->pub;
   const unsigned int K = p->rate_cats, s = p->states, sp = p->states_padded;
   if (K > DV_MAXK)
@@ -432,10 +502,16 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats > %d is not supported.", DV_MAXK);
     return false;
   }
-  if (p->attributes & PLL_ATTRIB_AB_MASK)
+  const int asc_type = (int)(p->attributes & PLL_ATTRIB_AB_MASK);
+  if (asc_type && (s > ASC_THREADS || (p->attributes & PLL_ATTRIB_RATE_SCALERS)))
   {
     pllb200_set_error(PLL_ERROR_AB_NOSUPPORT,
-                      "Ascertainment bias correction is not implemented on the device path yet.");
+                      "Ascertainment bias correction needs states <= %d and per-site scalers.", ASC_THREADS);
+    return false;
+  }
+  if (parent_scaler >= (int)p->scale_buffers || child_scaler >= (int)p->scale_buffers)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid scaler index in derivative call.");
     return false;
   }
   if (!dev_sync_inputs(c) || !dev_sync_eigen(c, params_indices)) return false;
@@ -445,7 +521,8 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
   a.weights = c->d_weights;
   a.eigen = c->d_eigen;
   a.eigen_stride = c->eigen_stride;
-  a.sites = p->sites;
+  /* Stamatakis: the extra per-state sites are ordinary weighted sites (core_derivatives.c:733-741) */
+  a.sites = asc_type == PLL_ATTRIB_AB_STAMATAKIS ? c->sites_alloc : p->sites;
   a.states = s;
   a.sp = sp;
   a.K = K;
@@ -478,9 +555,10 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
 
   /* diagonal table on the host: K*s exponentials (core_derivatives.c:757-772) */
   const bool dna = s == 4 && (K == 1 || K == 2 || K == 4 || K == 8);
+  const bool asc_terms = asc_type == PLL_ATTRIB_AB_LEWIS || asc_type == PLL_ATTRIB_AB_FELSENSTEIN;
   DiagDna dg;
   std::vector<double> diag;
-  if (!dna) diag.resize((size_t)K * s * 3);
+  if (!dna || asc_terms) diag.resize((size_t)K * s * 3);
   for (unsigned int k = 0; k < K; ++k)
   {
     const double * evals = p->eigenvals[params_indices[k]];
@@ -496,7 +574,7 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
         dg.d[k][j][1] = e1;
         dg.d[k][j][2] = e2;
       }
-      else
+      if (!dna || asc_terms)
       {
         diag[((size_t)k * s + j) * 3 + 0] = e0;
         diag[((size_t)k * s + j) * 3 + 1] = e1;
@@ -531,5 +609,19 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     deriv_generic_kernel<<<(unsigned)blocks, DVG_THREADS, 0, c->stream>>>(a);
   }
   ++g_kernel_launches;
-  return pllb200_cuda_ok(cudaGetLastError(), "derivative kernel launch");
+  if (!pllb200_cuda_ok(cudaGetLastError(), "derivative kernel launch")) return false;
+  if (asc_terms)
+  {
+    if (dna)
+    {
+      a.diag = (const double *)dev_stage(c, diag.data(), sizeof(double) * diag.size());
+      if (!a.diag) return false;
+    }
+    asc_deriv_kernel<<<1, ASC_THREADS, 0, c->stream>>>(a, p->sites, scaler_dev(c, parent_scaler),
+                                                       scaler_dev(c, child_scaler), asc_type,
+                                                       p->pattern_weight_sum);
+    ++g_kernel_launches;
+    return pllb200_cuda_ok(cudaGetLastError(), "asc derivative kernel launch");
+  }
+  return true;
 }

@@ -274,6 +274,110 @@ __global__ void __launch_bounds__(LKG_THREADS) logl_generic_kernel(LoglArgs a, i
   grid_reduce_finish<1>(v, a.red);
 }
 
+/* ---- ascertainment-bias correction ------------------------------------------------------------
+ * likelihood.c:24-120 (root), :191-268 (tip-inner), :342-440 (inner-inner): the partition carries
+ * `states` extra "sites" after the real ones (site sites+n = every tip in state n).  Their
+ * likelihoods l_n (unscaled: times 2^(-256 c_n)) correct the sum of the main kernel:
+ *   Lewis        logL -= W ln(1 - sum_n l_n)           W = pattern_weight_sum
+ *   Felsenstein  logL += (sum_n w_n) ln(sum_n l_n)     w_n = pattern_weights[sites+n]
+ *   Stamatakis   logL += sum_n [ w_n ln l'_n + c_n ln 2^-256 ]   (l'_n still scaled; the reference
+ *                does not weight the scaling term)
+ * One CTA, thread n = state n; runs on the same stream right after the reducing kernel and rewrites
+ * its result slot (device copy and mapped host copy). */
+#define ASC_THREADS 64
+
+__global__ void __launch_bounds__(ASC_THREADS) asc_logl_kernel(LoglArgs a, int root, int asc_type,
+                                                              unsigned int weight_sum)
+{
+  __shared__ double s_term[ASC_THREADS];
+  __shared__ unsigned int s_sc[ASC_THREADS];
+  const unsigned int K = a.K, s = a.states, sp = a.sp, n = threadIdx.x;
+  if (n < s)
+  {
+    const unsigned long long site = (unsigned long long)a.sites + n;
+    double term = 0.0;
+    unsigned long long cmask = 0;
+    if (a.ctip)
+    {
+      const unsigned int code = a.ctip[site];
+      cmask = a.is4 ? (unsigned long long)code : a.tipmap[code];
+    }
+    for (unsigned int k = 0; k < K; ++k)
+    {
+      const unsigned long long e = site * K + k;
+      const double * freqs = a.eigen + (unsigned long long)a.freq_idx[k] * a.eigen_stride + 2 * s * sp + sp;
+      const double * pv = a.pclv + e * sp;
+      const double * mat = root ? nullptr : a.pmat + (size_t)k * s * sp;
+      const double * cv = a.cclv ? a.cclv + e * sp : nullptr;
+      double term_r = 0.0;
+      for (unsigned int i = 0; i < s; ++i)
+      {
+        double tb = 1.0;
+        if (!root)
+        {
+          tb = 0.0;
+          if (cv)
+            for (unsigned int j = 0; j < s; ++j) tb += mat[i * sp + j] * cv[j];
+          else
+            for (unsigned int j = 0; j < s; ++j)
+              if ((cmask >> j) & 1ull) tb += mat[i * sp + j];
+        }
+        term_r += pv[i] * freqs[i] * tb;
+      }
+      term += term_r * a.w[k];
+    }
+    unsigned int sc = 0;
+    if (a.pscaler) sc += a.pscaler[site];
+    if (a.cscaler) sc += a.cscaler[site];
+    s_term[n] = term;
+    s_sc[n] = sc;
+  }
+  __syncthreads();
+  if (n != 0) return;
+  double base = 0.0;
+  unsigned int sum_w_inv = 0;
+  for (unsigned int q = 0; q < s; ++q)
+  {
+    const unsigned int w = a.weights[a.sites + q];
+    sum_w_inv += w;
+    if (asc_type == PLL_ATTRIB_AB_STAMATAKIS)
+    {
+      double lk = log(s_term[q]) * (double)w;
+      if (s_sc[q]) lk += (double)s_sc[q] * LN_SCALE_THRESHOLD;
+      base += lk;
+    }
+    else
+      base += scalbn(s_term[q], -256 * (int)s_sc[q]);
+  }
+  double corr;
+  if (asc_type == PLL_ATTRIB_AB_LEWIS)
+    corr = -((double)weight_sum * log(1.0 - base));
+  else if (asc_type == PLL_ATTRIB_AB_FELSENSTEIN)
+    corr = (double)sum_w_inv * log(base);
+  else
+    corr = base;
+  const double v = a.red.result_dev[0] + corr;
+  a.red.result_dev[0] = v;
+  a.red.result_host[0] = v;
+  __threadfence_system();
+}
+
+static bool launch_asc_logl(PartCtx * c, const LoglArgs & a, int root)
+{
+  const pll_partition_t * p = &c->pub;
+  const int asc_type = (int)(p->attributes & PLL_ATTRIB_AB_MASK);
+  if (!asc_type) return true;
+  if (p->states > ASC_THREADS || (p->attributes & PLL_ATTRIB_RATE_SCALERS))
+  {
+    pllb200_set_error(PLL_ERROR_AB_NOSUPPORT,
+                      "Ascertainment bias correction needs states <= %d and per-site scalers.", ASC_THREADS);
+    return false;
+  }
+  asc_logl_kernel<<<1, ASC_THREADS, 0, c->stream>>>(a, root, asc_type, p->pattern_weight_sum);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "asc logl kernel launch");
+}
+
 /* ---- host ------------------------------------------------------------------------------------ */
 
 static bool fill_common(PartCtx * c, LoglArgs & a, const unsigned int * freqs_indices,
@@ -283,12 +387,6 @@ static bool fill_common(PartCtx * c, LoglArgs & a, const unsigned int * freqs_in
   if (p->rate_cats > LK_MAXK)
   {
     pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats > %d is not supported.", LK_MAXK);
-    return false;
-  }
-  if (p->attributes & PLL_ATTRIB_AB_MASK)
-  {
-    pllb200_set_error(PLL_ERROR_AB_NOSUPPORT,
-                      "Ascertainment bias correction is not implemented on the device path yet.");
     return false;
   }
   if (!dev_sync_inputs(c) || !dev_sync_eigen(c, freqs_indices)) return false;
@@ -406,7 +504,7 @@ bool launch_edge_logl(PartCtx * c, unsigned int parent_clv, int parent_scaler,
     a.cscaler = scaler_dev(c, child_scaler);
   }
   a.pmat = c->d_pmat + (size_t)matrix_index * c->pmat_elems;
-  return dispatch_logl<false>(c, a);
+  return dispatch_logl<false>(c, a) && launch_asc_logl(c, a, 0);
 }
 
 bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
@@ -422,5 +520,5 @@ bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
   if (!fill_common(c, a, freqs_indices, d_persite, slot)) return false;
   a.pclv = clv_dev(c, clv_index);
   a.pscaler = scaler_dev(c, scaler_index);
-  return dispatch_logl<true>(c, a);
+  return dispatch_logl<true>(c, a) && launch_asc_logl(c, a, 1);
 }

@@ -48,7 +48,9 @@ def run_oracle(tips, sites, states=4, rate_cats=4, attributes=1 << 4, seed=42, b
     return out[0], df, ddf, sc
 
 
-SINGLE = [n for n in sorted(GOLD) if not isinstance(GOLD[n]["args"]["sites"], list)]
+# the C restatement covers the core recurrences; ascertainment-bias cases are pinned by the reference's
+# goldens and the live reference only (tests/test_gpu_parity.py)
+SINGLE = [n for n in sorted(GOLD) if not isinstance(GOLD[n]["args"]["sites"], list) and "asc" not in n]
 
 
 @pytest.mark.parametrize("name", SINGLE)
