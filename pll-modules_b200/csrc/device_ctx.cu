@@ -67,6 +67,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_reorder")) slot = &g_opt_trav_reorder;
   else if (!strcmp(name, "fuse_root")) slot = &g_opt_fuse_root;
   else if (!strcmp(name, "trav_variant")) slot = &g_opt_trav_variant;
+  else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
   if (!slot) return -1;
   int old = *slot;
   *slot = value;

@@ -117,6 +117,7 @@ extern int g_opt_trav_ctas_per_sm;
 extern int g_opt_trav_reorder;
 extern int g_opt_fuse_root;
 extern int g_opt_trav_variant;
+extern int g_opt_trav_forward;
 
 /* device context (device_ctx.cu) */
 bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */

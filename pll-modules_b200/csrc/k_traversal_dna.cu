@@ -43,6 +43,10 @@ struct __align__(16) DevOp
 #define OPF_PS 4u
 #define OPF_S1 8u
 #define OPF_S2 16u
+#define OPF_FWD1 32u  /* child 1 is the parent of the previous op: take it from registers */
+#define OPF_FWD2 64u
+#define OPF_FS1 128u  /* child-1 scaler is the previous op's parent scaler */
+#define OPF_FS2 256u
 
 struct TravArgs
 {
@@ -122,17 +126,32 @@ __device__ __forceinline__ void op_body(const double * __restrict__ p1, const do
                                         unsigned int t1, unsigned int t2, const double * sL,
                                         const double * sR, int k, unsigned int actmask,
                                         unsigned long long * bar, unsigned int parity,
-                                        double (&out)[R][4])
+                                        const d4 (&fw)[R], unsigned int flags, double (&out)[R][4])
 {
   constexpr int ESTEP = K * 4;
   d4 v1[R], v2[R];
+  /* register forwarding: with the depth-first schedule the op right before a parent is (almost
+   * always) one of its inner children, so that operand never makes the round trip through L1/L2 */
+  const bool f1 = !T1 && (flags & OPF_FWD1), f2 = !T2 && (flags & OPF_FWD2);
 #pragma unroll
   for (int r = 0; r < R; ++r)
   {
     if (FULL || ((actmask >> r) & 1u))
     {
-      if (!T1) v1[r] = ldg256(p1 + ESTEP * r);
-      if (!T2) v2[r] = ldg256(p2 + ESTEP * r);
+      if (!T1)
+      {
+        if (f1)
+          v1[r] = fw[r];
+        else
+          v1[r] = ldg256(p1 + ESTEP * r);
+      }
+      if (!T2)
+      {
+        if (f2)
+          v2[r] = fw[r];
+        else
+          v2[r] = ldg256(p2 + ESTEP * r);
+      }
     }
     else
       v1[r] = v2[r] = d4{0.0, 0.0, 0.0, 0.0};
@@ -219,6 +238,14 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     tma_load_1d(sm.mat[warp][0][0], a.pmat_il + sm.ops[0].m1_off, MAT_BYTES, &sm.bar[warp][0]);
     tma_load_1d(sm.mat[warp][0][1], a.pmat_il + sm.ops[0].m2_off, MAT_BYTES, &sm.bar[warp][0]);
   }
+  d4 fw[R];                /* parent CLV elements of the previous op (register forwarding) */
+  unsigned int fsc[R];     /* ... and its scaler counts */
+#pragma unroll
+  for (int r = 0; r < R; ++r)
+  {
+    fw[r] = d4{0.0, 0.0, 0.0, 0.0};
+    fsc[r] = 0;
+  }
   unsigned int t1 = 0, t2 = 0; /* packed tip codes of the CURRENT op */
   {
     const unsigned int f0 = sm.ops[0].flags;
@@ -254,8 +281,20 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     for (int r = 0; r < R; ++r) sc[r] = 0;
     if ((flags & OPF_PS) && sc_lane)
     {
-      if (flags & OPF_S1) add_scalers(a.scaler + d.s1_off + sidx0, sc);
-      if (flags & OPF_S2) add_scalers(a.scaler + d.s2_off + sidx0, sc);
+      if (flags & OPF_FS1)
+      {
+#pragma unroll
+        for (int r = 0; r < R; ++r) sc[r] += fsc[r];
+      }
+      else if (flags & OPF_S1)
+        add_scalers(a.scaler + d.s1_off + sidx0, sc);
+      if (flags & OPF_FS2)
+      {
+#pragma unroll
+        for (int r = 0; r < R; ++r) sc[r] += fsc[r];
+      }
+      else if (flags & OPF_S2)
+        add_scalers(a.scaler + d.s2_off + sidx0, sc);
     }
 
     /* ---- parent[i] = (L_k[i,:] . v1) * (R_k[i,:] . v2), one specialised body per tip pattern ---- */
@@ -269,10 +308,10 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     double out[R][4];
     switch (flags & (OPF_TIP1 | OPF_TIP2))
     {
-      case 0: op_body<K, R, false, false, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
-      case OPF_TIP1: op_body<K, R, true, false, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
-      case OPF_TIP2: op_body<K, R, false, true, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
-      default: op_body<K, R, true, true, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, out); break;
+      case 0: op_body<K, R, false, false, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, fw, flags, out); break;
+      case OPF_TIP1: op_body<K, R, true, false, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, fw, flags, out); break;
+      case OPF_TIP2: op_body<K, R, false, true, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, fw, flags, out); break;
+      default: op_body<K, R, true, true, FULL>(p1, p2, t1, t2, sL, sR, k, actmask, bar, parity, fw, flags, out); break;
     }
 
     /* ---- underflow scaling vote + scaler update ---- */
@@ -325,7 +364,12 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     double * pdst = a.clv + d.p_off + eoff;
 #pragma unroll
     for (int r = 0; r < R; ++r)
-      if (FULL || ((actmask >> r) & 1u)) stg256(pdst + ESTEP * r, d4{out[r][0], out[r][1], out[r][2], out[r][3]});
+    {
+      fw[r] = d4{out[r][0], out[r][1], out[r][2], out[r][3]};
+      if (FULL || ((actmask >> r) & 1u)) stg256(pdst + ESTEP * r, fw[r]);
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) fsc[r] = (flags & OPF_PS) ? sc[r] + ((scalemask >> r) & 1u) : 0u;
     t1 = n1;
     t2 = n2;
   }
@@ -386,6 +430,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArg
 /* ---- host ------------------------------------------------------------------------------------ */
 
 int g_opt_trav_variant = 0;
+int g_opt_trav_forward = 1;
 
 template <int K, int R, bool RS, int MINB>
 static bool launch_variant(PartCtx * c, const TravArgs & a)
@@ -478,6 +523,21 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
     }
     d.m1_off = o.child1_matrix_index * 16 * K;
     d.m2_off = o.child2_matrix_index * 16 * K;
+    /* forwarding from the previous op of the same staged segment (segments restart per chunk) */
+    const unsigned int seg_len = K == 8 ? 128 : 256;
+    if (g_opt_trav_forward && i % seg_len != 0)
+    {
+      const pll_operation_t & q = ops[i - 1];
+      if (!(d.flags & OPF_TIP1) && o.child1_clv_index == q.parent_clv_index) d.flags |= OPF_FWD1;
+      if (!(d.flags & OPF_TIP2) && o.child2_clv_index == q.parent_clv_index &&
+          !(d.flags & OPF_FWD1))
+        d.flags |= OPF_FWD2;
+      if (q.parent_scaler_index >= 0 && (d.flags & OPF_PS))
+      {
+        if (o.child1_scaler_index == q.parent_scaler_index) d.flags |= OPF_FS1;
+        if (o.child2_scaler_index == q.parent_scaler_index) d.flags |= OPF_FS2;
+      }
+    }
   }
   const DevOp * d_ops = (const DevOp *)dev_stage(c, dops, sizeof(DevOp) * count);
   if (!d_ops) return false;
