@@ -187,14 +187,14 @@ __device__ __forceinline__ void op_body(const double * __restrict__ p1, const do
  * FULL: every site of the chunk exists (no guards).  ph: mbarrier phase bits of the two stages. */
 template <int K, int R, bool RATE_SCALERS, bool FULL>
 __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm, unsigned int nseg,
-                                            unsigned long long s0, int lane, int warp,
+                                            unsigned int s0, int lane, int warp,
                                             unsigned int & ph)
 {
   const int k = lane % K;
   constexpr unsigned int MAT_BYTES = 16 * K * sizeof(double);
   constexpr int ESTEP = K * 4;                               /* doubles between consecutive sites */
-  const unsigned long long eoff = (s0 * K + k) * 4;          /* doubles */
-  const unsigned long long sidx0 = RATE_SCALERS ? s0 * K + k : s0; /* scaler element of r = 0 */
+  const unsigned long long eoff = ((unsigned long long)s0 * K + k) * 4; /* doubles */
+  const unsigned long long sidx0 = RATE_SCALERS ? (unsigned long long)s0 * K + k : s0; /* scaler element of r = 0 */
   constexpr int SC_STEP = RATE_SCALERS ? K : 1;
   const bool sc_lane = RATE_SCALERS || k == 0;
   unsigned int actmask = 0;
@@ -275,26 +275,28 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
       if (fn & OPF_TIP1) n1 = load_tips(a.tipchars + sm.ops[o + 1].c1_off + s0);
       if (fn & OPF_TIP2) n2 = load_tips(a.tipchars + sm.ops[o + 1].c2_off + s0);
     }
-    /* child scaler counts (the lanes that own a scaler entry only) */
-    unsigned int sc[R];
+    /* child scaler counts (the lanes that own a scaler entry only): the loads are issued here, the
+     * counts are only combined when the parent scaler is written, after the arithmetic (ncu: adding
+     * them right away exposed the full L2 latency, 22 % of all stall samples) */
+    unsigned int q1[R], q2[R];
 #pragma unroll
-    for (int r = 0; r < R; ++r) sc[r] = 0;
+    for (int r = 0; r < R; ++r) q1[r] = q2[r] = 0;
     if ((flags & OPF_PS) && sc_lane)
     {
       if (flags & OPF_FS1)
       {
 #pragma unroll
-        for (int r = 0; r < R; ++r) sc[r] += fsc[r];
+        for (int r = 0; r < R; ++r) q1[r] = fsc[r];
       }
       else if (flags & OPF_S1)
-        add_scalers(a.scaler + d.s1_off + sidx0, sc);
+        add_scalers(a.scaler + d.s1_off + sidx0, q1);
       if (flags & OPF_FS2)
       {
 #pragma unroll
-        for (int r = 0; r < R; ++r) sc[r] += fsc[r];
+        for (int r = 0; r < R; ++r) q2[r] = fsc[r];
       }
       else if (flags & OPF_S2)
-        add_scalers(a.scaler + d.s2_off + sidx0, sc);
+        add_scalers(a.scaler + d.s2_off + sidx0, q2);
     }
 
     /* ---- parent[i] = (L_k[i,:] . v1) * (R_k[i,:] . v2), one specialised body per tip pattern ---- */
@@ -316,6 +318,9 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
 
     /* ---- underflow scaling vote + scaler update ---- */
     unsigned int scalemask = 0;
+    unsigned int sc[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) sc[r] = q1[r] + q2[r];
     if (flags & OPF_PS)
     {
       if ((flags & (OPF_TIP1 | OPF_TIP2)) != (OPF_TIP1 | OPF_TIP2))
@@ -380,7 +385,7 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
  * so that ptxas sizes it under that kernel's register cap. */
 template <int K, int R, bool RATE_SCALERS, int MINB>
 __device__ __noinline__ void run_segment_tail(const TravArgs & a, TravSmem<K> & sm, unsigned int nseg,
-                                              unsigned long long s0, int lane, int warp,
+                                              unsigned int s0, int lane, int warp,
                                               unsigned int & ph)
 {
   run_segment<K, R, RATE_SCALERS, false>(a, sm, nseg, s0, lane, warp, ph);
@@ -418,7 +423,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArg
     __syncthreads();
     for (unsigned long long chunk = gwarp; chunk < nchunks; chunk += nwarps)
     {
-      const unsigned long long s0 = chunk * SPC + (unsigned long long)(lane / K) * R;
+      const unsigned int s0 = (unsigned int)(chunk * SPC) + (unsigned int)(lane / K) * R;
       if ((chunk + 1) * SPC <= a.sites)
         run_segment<K, R, RATE_SCALERS, true>(a, sm, nseg, s0, lane, warp, ph);
       else
