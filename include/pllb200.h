@@ -678,6 +678,13 @@ int pllb200_edge_loglikelihood_async(pll_partition_t * partition,
                                      unsigned int child_clv_index, int child_scaler_index,
                                      unsigned int matrix_index,
                                      const unsigned int * freqs_indices, double * result);
+/* Asynchronous twin of pll_compute_likelihood_derivatives: queues the derivative pass; *d_f / *dd_f
+ * (caller-owned host memory) are filled by pllb200_partition_synchronize or any later blocking call
+ * on the partition.  Lets a multi-partition Newton step queue every partition before waiting once. */
+int pllb200_likelihood_derivatives_async(pll_partition_t * partition, int parent_scaler_index,
+                                         int child_scaler_index, double branch_length,
+                                         const unsigned int * params_indices,
+                                         const double * sumtable, double * d_f, double * dd_f);
 /* Device address (as integer) of the partition's most recent reduction results
  * {logL, d_f, dd_f}: lets a caller run an NCCL all-reduce on them without a host round trip. */
 uint64_t pllb200_result_device_ptr(pll_partition_t * partition);

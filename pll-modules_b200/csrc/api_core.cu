@@ -200,6 +200,26 @@ extern "C" int pll_update_sumtable(pll_partition_t * partition, unsigned int par
                          child_scaler_index, params_indices, d) ? PLL_SUCCESS : PLL_FAILURE;
 }
 
+extern "C" int pllb200_likelihood_derivatives_async(pll_partition_t * partition,
+                                                    int parent_scaler_index, int child_scaler_index,
+                                                    double branch_length,
+                                                    const unsigned int * params_indices,
+                                                    const double * sumtable, double * d_f,
+                                                    double * dd_f)
+{
+  if (!enter(partition)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(partition);
+  double * d = sumtable_shadow(c, sumtable, false);
+  if (!d) return PLL_FAILURE;
+  const int slot = dev_alloc_slot(c);
+  if (!launch_derivatives(c, parent_scaler_index, child_scaler_index, branch_length,
+                          params_indices, d, slot))
+    return PLL_FAILURE;
+  c->pending.push_back(PendingResult{d_f, slot, 0});
+  c->pending.push_back(PendingResult{dd_f, slot, 1});
+  return PLL_SUCCESS;
+}
+
 extern "C" int pll_compute_likelihood_derivatives(pll_partition_t * partition,
                                                   int parent_scaler_index, int child_scaler_index,
                                                   double branch_length,

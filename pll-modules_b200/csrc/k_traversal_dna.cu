@@ -91,7 +91,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long * bar, unsigned int
 __device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gmem, unsigned int bytes,
                                             unsigned long long * bar)
 {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                    smem_u32(dst_smem)),
                "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
                : "memory");

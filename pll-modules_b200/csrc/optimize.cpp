@@ -393,15 +393,25 @@ static void multi_deriv_cb(void * parameters, double * proposal, double * df, do
     for (unsigned int p = 0; p < P; ++p) df[p] = ddf[p] = 0;
   else
     *df = *ddf = 0;
+  /* queue the derivative pass of every local partition (one stream each), then wait once per stream */
+  std::vector<double> pd(2 * (size_t)P, NAN);
+  bool ok = true;
   for (unsigned int p = 0; p < P; ++p)
   {
     if (!prm->partitions[p]) continue;
     const double s = prm->brlen_scalers ? prm->brlen_scalers[p] : 1.;
     const double brlen = s * (unlinked ? proposal[p] : proposal[0]);
-    double p_df = NAN, p_ddf = NAN;
-    pll_compute_likelihood_derivatives(prm->partitions[p], prm->tree->scaler_index,
-                                       prm->tree->back->scaler_index, brlen,
-                                       prm->params_indices[p], prm->precomp_buffers[p], &p_df, &p_ddf);
+    ok = pllb200_likelihood_derivatives_async(prm->partitions[p], prm->tree->scaler_index,
+                                              prm->tree->back->scaler_index, brlen,
+                                              prm->params_indices[p], prm->precomp_buffers[p],
+                                              &pd[2 * p], &pd[2 * p + 1]) && ok;
+  }
+  for (unsigned int p = 0; p < P; ++p)
+  {
+    if (!prm->partitions[p]) continue;
+    ok = pllb200_partition_synchronize(prm->partitions[p]) && ok;
+    const double s = prm->brlen_scalers ? prm->brlen_scalers[p] : 1.;
+    const double p_df = ok ? pd[2 * p] : NAN, p_ddf = ok ? pd[2 * p + 1] : NAN;
     if (unlinked)
     {
       df[p] = s * p_df;
