@@ -434,6 +434,104 @@ int pllmod_treeinfo_set_tree(pllmod_treeinfo_t * treeinfo, pll_utree_t * tree);
  * evaluation and no host synchronisation; the work that treeinfo.c:973-1041 does inline. */
 int pllmod_treeinfo_update_partials(pllmod_treeinfo_t * treeinfo, int incremental);
 
+/* ---- tree rearrangement subset (T:42-64,139-189,293-330; libpll utree_moves.c:119-260) ------- */
+#define PLLMOD_TREE_ERROR_SPR_INVALID_NODE 3104
+#define PLLMOD_TREE_ERROR_SPR_MASK 3168
+#define PLLMOD_TREE_REARRANGE_SPR 0
+#define PLLMOD_TREE_REARRANGE_NNI 1
+#define PLLMOD_TREE_REARRANGE_TBR 2
+#define PLL_ERROR_SPR_TERMINALBRANCH 123
+#define PLL_ERROR_SPR_NOCHANGE 124
+
+/* T:139-154 */
+typedef struct pll_tree_edge
+{
+  union
+  {
+    struct
+    {
+      pll_unode_t * parent;
+      pll_unode_t * child;
+    } utree;
+    struct
+    {
+      void * parent;
+      void * child;
+    } rtree;
+  } edge;
+  double length;
+} pll_tree_edge_t;
+
+/* T:156-189 */
+typedef struct
+{
+  int rearrange_type;
+  int rooted;
+  double likelihood;
+  union
+  {
+    struct
+    {
+      void * prune_edge;
+      void * regraft_edge;
+      double prune_bl;
+      double prune_left_bl;
+      double prune_right_bl;
+      double regraft_bl;
+    } SPR;
+    struct
+    {
+      void * edge;
+      double left_left_bl;
+      double left_right_bl;
+      double right_left_bl;
+      double right_right_bl;
+      double edge_bl;
+      int type;
+    } NNI;
+    struct
+    {
+      void * bisect_edge;
+      pll_tree_edge_t reconn_edge;
+      double bisect_left_bl;
+      double bisect_right_bl;
+      double reconn_parent_left_bl;
+      double reconn_parent_right_bl;
+      double reconn_child_left_bl;
+      double reconn_child_right_bl;
+    } TBR;
+  };
+} pll_tree_rollback_t;
+
+/* utree_operations.c:184,229,389; pll_tree.c:159,253 (SPR rollback only) */
+pll_unode_t * pllmod_utree_prune(pll_unode_t * edge);
+int pllmod_utree_regraft(pll_unode_t * edge, pll_unode_t * tree);
+int pllmod_utree_spr(pll_unode_t * p_edge, pll_unode_t * r_edge, pll_tree_rollback_t * rollback_info);
+int pllmod_tree_rollback(pll_tree_rollback_t * rollback_info);
+int pllmod_utree_nodes_at_node_dist(pll_unode_t * node, pll_unode_t ** outbuffer,
+                                    unsigned int * node_count, unsigned int min_distance,
+                                    unsigned int max_distance);
+
+/* ---- SPR search round (src/algorithm/pllmod_algorithm.h:41-47,205-219; algo_search.c:1039) ---- */
+typedef struct cutoff_info
+{
+  double lh_start;
+  double lh_cutoff;
+  double lh_dec_sum;
+  int lh_dec_count;
+} cutoff_info_t;
+
+/* One round of subtree pruning and regrafting over every inner subnode: candidate regraft edges in
+ * [radius_min, radius_max] of the pruning point are scored by partial traversals (fast) or after a
+ * 3-branch Newton-Raphson optimisation (thorough); improving moves are applied, the best `ntopol_keep`
+ * others are re-evaluated after full branch-length optimisation.  Returns the final logL (0 on error).
+ * Topological constraints are not supported (the treeinfo must not carry a constraint tree). */
+double pllmod_algo_spr_round(pllmod_treeinfo_t * treeinfo, unsigned int radius_min,
+                             unsigned int radius_max, unsigned int ntopol_keep, pll_bool_t thorough,
+                             int brlen_opt_method, double bl_min, double bl_max, int smoothings,
+                             double epsilon, cutoff_info_t * cutoff_info, double subtree_cutoff,
+                             double lh_epsilon_brlen_triplet, pll_bool_t fast_clv_updates);
+
 /* ---- pll-modules optimize subset (O:60-62,71-76,88-102,158-187,194-354) --------------------- */
 #define PLLMOD_OPT_DEFAULT_BRANCH_LEN 0.1
 #define PLLMOD_OPT_MIN_BRANCH_LEN 1.0e-4

@@ -99,9 +99,28 @@ MODEL_OPT_CASES = [
 ]
 
 
+SPR_CASES = [
+    ("dna24_fast", dict(tips=24, sites=400, seed=11), dict(thorough=False, radius_max=5)),
+    ("dna24_thorough", dict(tips=24, sites=400, seed=11), dict(thorough=True, radius_max=5)),
+    ("dna40_fast_r10_nocutoff", dict(tips=40, sites=300, seed=5), dict(thorough=False, radius_max=10, cutoff=False,
+                                                                     fast_clv_updates=False)),
+    ("aa16_fast", dict(tips=16, sites=150, states=20, seed=3), dict(thorough=False, radius_max=4)),
+    ("multi_unlinked_thorough", dict(tips=14, sites=[200, 150], states=[4, 4], alpha=[0.5, 1.0], linkage=2, seed=9),
+     dict(thorough=True, radius_max=3, ntopol_keep=3)),
+]
+
+
 def dump_opt():
     import pllharness as PH
-    out = {"brent": [], "lbfgsb": [], "model": {}}
+    out = {"brent": [], "lbfgsb": [], "model": {}, "spr": {}}
+    for name, kw, skw in SPR_CASES:
+        with PH.Harness("ref", **kw) as h:
+            start = h.loglh()
+            lh, co = h.spr_round(**skw)
+            hs, ln = h.topology_signature()
+            out["spr"][name] = dict(args=kw, spr=skw, start_loglh=start, loglh=lh, cutoff=co.tolist(),
+                                    splits=[str(int(x)) for x in hs], brlens=ln.tolist(), ops=h.ops_counter())
+            print(name, start, lh, h.ops_counter())
     for fn, lo, g, hi, tol in BRENT_CASES:
         r = PH.test_brent("ref", fn, lo, g, hi, tol)
         out["brent"].append(dict(args=[fn, lo, g, hi, tol], x=float(r["x"]), fx=float(r["fx"]), evals=r["evals"]))

@@ -871,3 +871,80 @@ void h_get_model(void * hv, unsigned int p, double * out)
   memcpy(out + 2 * K + 1, part->subst_params[0], sizeof(double) * nr);
   memcpy(out + 2 * K + 1 + nr, part->frequencies[0], sizeof(double) * s);
 }
+
+/* ---- SPR round (BASELINE configs[4]) -------------------------------------- */
+#ifdef HARNESS_REFERENCE
+#include "pllmod_algorithm.h"
+#endif
+
+double h_spr_round(void * hv, unsigned int radius_min, unsigned int radius_max, unsigned int ntopol_keep,
+                   int thorough, int blo_method, double bl_min, double bl_max, int smoothings,
+                   double epsilon, int use_cutoff, double subtree_cutoff, double lh_eps_triplet,
+                   int fast_clv_updates, double * cutoff_out)
+{
+  harness_t * h = (harness_t *)hv;
+  cutoff_info_t ci;
+  memset(&ci, 0, sizeof(ci));
+  ci.lh_cutoff = 1e30; /* first round: no cutoff yet (what raxml-ng passes) */
+  const double lh = pllmod_algo_spr_round(h->ti, radius_min, radius_max, ntopol_keep, thorough, blo_method,
+                                          bl_min, bl_max, smoothings, epsilon, use_cutoff ? &ci : NULL,
+                                          subtree_cutoff, lh_eps_triplet, fast_clv_updates);
+  if (cutoff_out)
+  {
+    cutoff_out[0] = ci.lh_cutoff;
+    cutoff_out[1] = ci.lh_dec_sum;
+    cutoff_out[2] = ci.lh_dec_count;
+  }
+  return lh;
+}
+
+/* order-independent description of the current topology: for every branch the hash of the tip set on
+ * the side that does not contain tip 0, with the branch length; sorted by hash.
+ * out_hash / out_len: 2*tips-3 entries */
+static unsigned long long split_hash(pll_unode_t * n, int * has0)
+{
+  if (!n->next)
+  {
+    if (n->clv_index == 0) *has0 = 1;
+    return mix64(0xABCDEFull + n->clv_index);
+  }
+  return split_hash(n->next->back, has0) + split_hash(n->next->next->back, has0);
+}
+void h_topology_signature(void * hv, unsigned long long * out_hash, double * out_len)
+{
+  harness_t * h = (harness_t *)hv;
+  pllmod_treeinfo_t * ti = h->ti;
+  const unsigned int nb = 2 * h->tips - 3;
+  unsigned long long total = 0;
+  for (unsigned int t = 0; t < h->tips; ++t) total += mix64(0xABCDEFull + t);
+  unsigned int k = 0;
+  char * seen = (char *)calloc(ti->subnode_count, 1);
+  for (unsigned int i = 0; i < ti->subnode_count && k < nb; ++i)
+  {
+    pll_unode_t * n = ti->subnodes[i];
+    if (seen[n->node_index] || seen[n->back->node_index]) continue;
+    seen[n->node_index] = seen[n->back->node_index] = 1;
+    int has0 = 0;
+    unsigned long long hsh = split_hash(n->back, &has0); /* subtree behind n->back's far side */
+    if (has0) hsh = total - hsh;
+    out_hash[k] = hsh;
+    out_len[k] = n->length;
+    ++k;
+  }
+  free(seen);
+  /* insertion sort by hash */
+  for (unsigned int i = 1; i < k; ++i)
+  {
+    unsigned long long hh = out_hash[i];
+    double ll = out_len[i];
+    unsigned int j = i;
+    while (j > 0 && out_hash[j - 1] > hh)
+    {
+      out_hash[j] = out_hash[j - 1];
+      out_len[j] = out_len[j - 1];
+      --j;
+    }
+    out_hash[j] = hh;
+    out_len[j] = ll;
+  }
+}

@@ -125,6 +125,11 @@ def _lib(kind):
         lib.h_optimize_params.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_double, C.c_double,
                                           C.c_double, C.c_void_p, C.c_int]
         lib.h_get_model.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
+        lib.h_spr_round.restype = C.c_double
+        lib.h_spr_round.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_double,
+                                    C.c_double, C.c_int, C.c_double, C.c_int, C.c_double, C.c_double, C.c_int,
+                                    C.c_void_p]
+        lib.h_topology_signature.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         _libs[kind] = lib
     return _libs[kind]
 
@@ -320,6 +325,22 @@ class Harness:
         self.lib.h_get_model(self.h, p, out.ctypes.data)
         return dict(rates=out[:K].copy(), weights=out[K:2 * K].copy(), pinv=out[2 * K],
                     subst=out[2 * K + 1:2 * K + 1 + nr].copy(), freqs=out[2 * K + 1 + nr:].copy())
+
+    def spr_round(self, radius_min=1, radius_max=5, ntopol_keep=5, thorough=False, blo_method=BLO_NEWTON_FAST,
+                  bl_min=1e-6, bl_max=100.0, smoothings=32, epsilon=0.1, cutoff=True, subtree_cutoff=1.0,
+                  lh_eps_triplet=1000.0, fast_clv_updates=True):
+        """pllmod_algo_spr_round; returns (logL, cutoff stats)."""
+        co = np.zeros(3)
+        lh = self.lib.h_spr_round(self.h, radius_min, radius_max, ntopol_keep, int(thorough), blo_method, bl_min,
+                                  bl_max, smoothings, epsilon, int(cutoff), subtree_cutoff, lh_eps_triplet,
+                                  int(fast_clv_updates), co.ctypes.data)
+        return lh, co
+
+    def topology_signature(self):
+        n = 2 * self.tips - 3
+        hs, ln = np.zeros(n, dtype=np.uint64), np.zeros(n)
+        self.lib.h_topology_signature(self.h, hs.ctypes.data, ln.ctypes.data)
+        return hs, ln
 
     def set_alpha(self, alpha, p=0):
         assert self.lib.h_set_alpha(self.h, p, alpha)

@@ -276,3 +276,24 @@ def test_model_parameter_optimisation_matches_reference(name):
         with Harness("ref", **case["args"]) as r:
             rscore = r.optimize_params(**case["opt"])
         assert rel(score, rscore) < 1e-7
+
+
+# ---- SPR round over device-resident CLVs (BASELINE configs[4]) ----
+@pytest.mark.parametrize("name", sorted(OPT_GOLD["spr"].keys()))
+def test_spr_round_ends_on_the_reference_topology(name):
+    """pllmod_algo_spr_round: identical final topology (every bipartition; RF distance 0), logL within the
+    reference's own 1e-6 absolute assert (algo_search.c:1453), branch lengths within the NR tolerance, and
+    the same number of CLV operations (= the same candidate moves were evaluated in the same order)."""
+    case = OPT_GOLD["spr"][name]
+    with Harness("b200", **case["args"]) as h:
+        start = h.loglh()
+        assert rel(start, case["start_loglh"]) < 1e-8
+        lh, co = h.spr_round(**case["spr"])
+        hs, ln = h.topology_signature()
+        ops = h.ops_counter()
+    assert lh != 0.0
+    assert [str(int(x)) for x in hs] == case["splits"], "topology differs from the reference"
+    assert abs(lh - case["loglh"]) <= 1e-6 * max(1.0, abs(case["loglh"]) * 1e-3), (lh, case["loglh"])
+    np.testing.assert_allclose(ln, case["brlens"], rtol=1e-4, atol=1e-6)
+    assert ops == case["ops"]
+    np.testing.assert_allclose(co, case["cutoff"], rtol=1e-6)
