@@ -532,6 +532,38 @@ double pllmod_algo_spr_round(pllmod_treeinfo_t * treeinfo, unsigned int radius_m
                              double epsilon, cutoff_info_t * cutoff_info, double subtree_cutoff,
                              double lh_epsilon_brlen_triplet, pll_bool_t fast_clv_updates);
 
+/* ---- model-parameter optimisation over a treeinfo (src/algorithm/pllmod_algorithm.h:49-58,123-203;
+ *      pllmod_algorithm.c:729-1870): all partitions advance in lock step, every objective evaluation is
+ *      one pllmod_treeinfo_compute_loglh(treeinfo, 0) on the device.  All return -logL. ---- */
+typedef int (*treeinfo_param_set_cb)(pllmod_treeinfo_t * treeinfo, unsigned int part_num,
+                                     const double * param_vals, unsigned int param_count);
+typedef int (*treeinfo_param_get_cb)(const pllmod_treeinfo_t * treeinfo, unsigned int part_num,
+                                     double * param_vals, unsigned int param_count);
+double pllmod_algo_opt_onedim_treeinfo(pllmod_treeinfo_t * treeinfo, int param_to_optimize,
+                                       double min_value, double max_value, double tolerance);
+double pllmod_algo_opt_onedim_treeinfo_custom(pllmod_treeinfo_t * treeinfo, int param_to_optimize,
+                                              treeinfo_param_get_cb params_getter,
+                                              treeinfo_param_set_cb params_setter, double min_value,
+                                              double max_value, double tolerance);
+double pllmod_algo_opt_subst_rates_treeinfo(pllmod_treeinfo_t * treeinfo, unsigned int params_index,
+                                            double min_rate, double max_rate, double bfgs_factor,
+                                            double tolerance);
+double pllmod_algo_opt_frequencies_treeinfo(pllmod_treeinfo_t * treeinfo, unsigned int params_index,
+                                            double min_freq, double max_freq, double bfgs_factor,
+                                            double tolerance);
+double pllmod_algo_opt_rates_weights_treeinfo(pllmod_treeinfo_t * treeinfo, double min_rate,
+                                              double max_rate, double min_brlen, double max_brlen,
+                                              double bfgs_factor, double tolerance);
+double pllmod_algo_opt_alpha_pinv_treeinfo(pllmod_treeinfo_t * treeinfo, unsigned int params_index,
+                                           double min_alpha, double max_alpha, double min_pinv,
+                                           double max_pinv, double bfgs_factor, double tolerance);
+double pllmod_algo_opt_brlen_scalers_treeinfo(pllmod_treeinfo_t * treeinfo, double min_scaler,
+                                              double max_scaler, double min_brlen, double max_brlen,
+                                              double lh_epsilon);
+double pllmod_algo_opt_brlen_treeinfo(pllmod_treeinfo_t * treeinfo, double min_brlen,
+                                      double max_brlen, double lh_epsilon, int max_iters,
+                                      int opt_method, int radius);
+
 /* ---- pll-modules optimize subset (O:60-62,71-76,88-102,158-187,194-354) --------------------- */
 #define PLLMOD_OPT_DEFAULT_BRANCH_LEN 0.1
 #define PLLMOD_OPT_MIN_BRANCH_LEN 1.0e-4

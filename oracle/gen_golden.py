@@ -110,9 +110,35 @@ SPR_CASES = [
 ]
 
 
+TWO_PART = dict(tips=14, sites=[300, 200], states=[4, 4], alpha=[0.5, 1.0], seed=21)
+ALGO_OPT_CASES = [
+    ("alpha_2parts", TWO_PART, "alpha"),
+    ("pinv_2parts", dict(TWO_PART, pinv=[0.1, 0.2]), "pinv"),
+    ("subst_rates_2parts", TWO_PART, "subst_rates"),
+    ("frequencies_2parts", TWO_PART, "frequencies"),
+    ("alpha_pinv_2parts", dict(TWO_PART, pinv=[0.1, 0.2]), "alpha_pinv"),
+    ("rates_weights_2parts_unlinked", dict(TWO_PART, linkage=2), "rates_weights"),
+    ("rates_weights_1part", dict(tips=14, sites=400, seed=21), "rates_weights"),
+    ("brlen_scalers_scaled", dict(TWO_PART, linkage=1), "brlen_scalers"),
+    ("brlen_2parts", TWO_PART, "brlen"),
+    ("subst_rates_dna_aa", dict(tips=10, sites=[200, 80], states=[4, 20], alpha=[0.5, 1.0], seed=4), "alpha"),
+]
+
+
 def dump_opt():
     import pllharness as PH
-    out = {"brent": [], "lbfgsb": [], "model": {}, "spr": {}}
+    out = {"brent": [], "lbfgsb": [], "model": {}, "spr": {}, "algo_opt": {}}
+    for name, kw, what in ALGO_OPT_CASES:
+        with PH.Harness("ref", **kw) as h:
+            start = h.loglh()
+            score = h.algo_opt_treeinfo(what)
+            after = h.loglh()
+            models = [{k: (v.tolist() if hasattr(v, "tolist") else float(v)) for k, v in h.model(p).items()}
+                      for p in range(h.nparts)]
+            tp = {k: v.tolist() for k, v in h.treeinfo_params().items()}
+            out["algo_opt"][name] = dict(args=kw, what=what, start_loglh=start, score=score, loglh_after=after,
+                                         models=models, treeinfo=tp, brlens=h.branch_lengths().tolist())
+            print(name, start, score, after)
     for name, kw, skw in SPR_CASES:
         with PH.Harness("ref", **kw) as h:
             start = h.loglh()

@@ -948,3 +948,41 @@ void h_topology_signature(void * hv, unsigned long long * out_hash, double * out
     out_len[j] = ll;
   }
 }
+
+/* ---- treeinfo-level model optimisers ---------------------------------------- */
+/* which: 0 alpha (Brent)  1 pinv (Brent)  2 subst rates  3 frequencies  4 alpha+pinv  5 free rates+weights
+ *        6 branch-length scalers (SCALED linkage)  7 branch lengths (NR, all branches)
+ * params_to_optimize of every partition is set to the family under test first. Returns -logL. */
+double h_algo_opt_treeinfo(void * hv, int which, double tolerance)
+{
+  harness_t * h = (harness_t *)hv;
+  pllmod_treeinfo_t * ti = h->ti;
+  static const int masks[8] = {PLLMOD_OPT_PARAM_ALPHA, PLLMOD_OPT_PARAM_PINV, PLLMOD_OPT_PARAM_SUBST_RATES,
+                               PLLMOD_OPT_PARAM_FREQUENCIES, PLLMOD_OPT_PARAM_ALPHA | PLLMOD_OPT_PARAM_PINV,
+                               PLLMOD_OPT_PARAM_FREE_RATES | PLLMOD_OPT_PARAM_RATE_WEIGHTS,
+                               PLLMOD_OPT_PARAM_BRANCH_LEN_SCALER, 0};
+  for (unsigned int p = 0; p < ti->partition_count; ++p) ti->params_to_optimize[p] = masks[which];
+  pllmod_treeinfo_compute_loglh(ti, 0);
+  switch (which)
+  {
+    case 0: return pllmod_algo_opt_onedim_treeinfo(ti, PLLMOD_OPT_PARAM_ALPHA, 0.02, 100.0, tolerance);
+    case 1: return pllmod_algo_opt_onedim_treeinfo(ti, PLLMOD_OPT_PARAM_PINV, 1e-4, 0.99, tolerance);
+    case 2: return pllmod_algo_opt_subst_rates_treeinfo(ti, 0, 1e-3, 1000.0, 1e7, tolerance);
+    case 3: return pllmod_algo_opt_frequencies_treeinfo(ti, 0, 1e-3, 100.0, 1e7, tolerance);
+    case 4: return pllmod_algo_opt_alpha_pinv_treeinfo(ti, 0, 0.02, 100.0, 1e-4, 0.99, 1e7, tolerance);
+    case 5: return pllmod_algo_opt_rates_weights_treeinfo(ti, 0.02, 100.0, 1e-6, 100.0, 1e7, tolerance);
+    case 6: return pllmod_algo_opt_brlen_scalers_treeinfo(ti, 0.01, 100.0, 1e-6, 100.0, tolerance);
+    default: return pllmod_algo_opt_brlen_treeinfo(ti, 1e-6, 100.0, tolerance, 4, PLLMOD_OPT_BLO_NEWTON_FAST, -1);
+  }
+}
+
+/* out: alphas[nparts] then brlen_scalers[nparts] (1.0 when the treeinfo has none) */
+void h_get_treeinfo_params(void * hv, double * out)
+{
+  harness_t * h = (harness_t *)hv;
+  for (unsigned int p = 0; p < h->nparts; ++p)
+  {
+    out[p] = h->ti->alphas[p];
+    out[h->nparts + p] = h->ti->brlen_scalers ? h->ti->brlen_scalers[p] : 1.0;
+  }
+}

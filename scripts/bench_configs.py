@@ -104,3 +104,33 @@ if "c5" in which:
                           "partial_traversal_evals_per_s": 1.0 / tpart, "partial_eval_ms": tpart * 1e3,
                           "incremental_equals_full": abs(ll_inc - ll_full) <= 1e-9 * abs(ll_full),
                           "blo_one_smoothing_s": tb, "blo_branches": 2 * tips - 3, "blo_neg_loglh": nll}), flush=True)
+
+if "c5spr" in which:
+    # one full pllmod_algo_spr_round (fast mode, cutoff on) -- BASELINE configs[4]
+    tips, sites, rmax = opt("--c5-tips", 2000), opt("--c5-sites", 500000), opt("--c5-radius", 5)
+    with Harness("b200", tips=tips, sites=sites) as h:
+        ll = h.loglh(0)
+        pkg.reset_stats()
+        c0 = h.ops_counter()
+        t0 = time.perf_counter()
+        lh, co = h.spr_round(thorough=False, radius_min=1, radius_max=rmax, ntopol_keep=20, smoothings=32,
+                             epsilon=1.0, bl_min=1e-6)
+        dt = time.perf_counter() - t0
+        st = pkg.stats()
+        print(json.dumps({"config": "C5 pllmod_algo_spr_round fast, radius 1..%d, DNA GTR+G4 %d taxa x %d sites" % (rmax, tips, sites),
+                          "start_loglh": ll, "loglh": lh, "seconds": dt, "clv_ops": h.ops_counter() - c0,
+                          "clv_site_updates_per_s": (h.ops_counter() - c0) * sites / dt,
+                          "kernel_launches": st["kernel_launches"], "launches_per_s": st["kernel_launches"] / dt,
+                          "cutoff": co.tolist()}), flush=True)
+    if have_reference() and "--no-ref" not in args:
+        rs = opt("--c5-ref-sites", 2000)
+        with Harness("ref", tips=tips, sites=rs) as r:
+            r.loglh(0)
+            c0 = r.ops_counter()
+            t0 = time.perf_counter()
+            lh, co = r.spr_round(thorough=False, radius_min=1, radius_max=rmax, ntopol_keep=20, smoothings=32,
+                                 epsilon=1.0, bl_min=1e-6)
+            dt = time.perf_counter() - t0
+            print(json.dumps({"config": "C5 reference CPU (1 core, AVX2) same round at %d sites" % rs, "loglh": lh,
+                              "seconds": dt, "clv_ops": r.ops_counter() - c0,
+                              "clv_site_updates_per_s": (r.ops_counter() - c0) * rs / dt}), flush=True)

@@ -125,6 +125,9 @@ def _lib(kind):
         lib.h_optimize_params.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_double, C.c_double,
                                           C.c_double, C.c_void_p, C.c_int]
         lib.h_get_model.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
+        lib.h_algo_opt_treeinfo.restype = C.c_double
+        lib.h_algo_opt_treeinfo.argtypes = [C.c_void_p, C.c_int, C.c_double]
+        lib.h_get_treeinfo_params.argtypes = [C.c_void_p, C.c_void_p]
         lib.h_spr_round.restype = C.c_double
         lib.h_spr_round.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_int, C.c_int, C.c_double,
                                     C.c_double, C.c_int, C.c_double, C.c_int, C.c_double, C.c_double, C.c_int,
@@ -341,6 +344,18 @@ class Harness:
         hs, ln = np.zeros(n, dtype=np.uint64), np.zeros(n)
         self.lib.h_topology_signature(self.h, hs.ctypes.data, ln.ctypes.data)
         return hs, ln
+
+    ALGO_OPT = dict(alpha=0, pinv=1, subst_rates=2, frequencies=3, alpha_pinv=4, rates_weights=5,
+                    brlen_scalers=6, brlen=7)
+
+    def algo_opt_treeinfo(self, what, tolerance=1e-3):
+        """pllmod_algo_opt_*_treeinfo over all partitions; returns -logL."""
+        return self.lib.h_algo_opt_treeinfo(self.h, self.ALGO_OPT[what], tolerance)
+
+    def treeinfo_params(self):
+        out = np.zeros(2 * self.nparts)
+        self.lib.h_get_treeinfo_params(self.h, out.ctypes.data)
+        return dict(alphas=out[:self.nparts].copy(), brlen_scalers=out[self.nparts:].copy())
 
     def set_alpha(self, alpha, p=0):
         assert self.lib.h_set_alpha(self.h, p, alpha)

@@ -297,3 +297,30 @@ def test_spr_round_ends_on_the_reference_topology(name):
     np.testing.assert_allclose(ln, case["brlens"], rtol=1e-4, atol=1e-6)
     assert ops == case["ops"]
     np.testing.assert_allclose(co, case["cutoff"], rtol=1e-6)
+
+
+# ---- treeinfo-level model optimisers, all partitions in lock step ----
+@pytest.mark.parametrize("name", sorted(OPT_GOLD["algo_opt"].keys()))
+def test_algo_opt_treeinfo_matches_reference(name):
+    """pllmod_algo_opt_{onedim,subst_rates,frequencies,alpha_pinv,rates_weights,brlen_scalers,brlen}_treeinfo.
+    Tolerances: -logL 1e-6 relative (Brent xtol 1e-3 / L-BFGS-B factr 1e7 stop well before that),
+    parameters 1 % (5 % for the weakly identified free-rate mixtures)."""
+    case = OPT_GOLD["algo_opt"][name]
+    with Harness("b200", **case["args"]) as h:
+        start = h.loglh()
+        assert rel(start, case["start_loglh"]) < 1e-8
+        score = h.algo_opt_treeinfo(case["what"])
+        after = h.loglh()
+        models = [h.model(p) for p in range(h.nparts)]
+        tp = h.treeinfo_params()
+        brl = h.branch_lengths()
+    assert rel(score, case["score"]) < 1e-6, (score, case["score"])
+    assert rel(-after, score) < 1e-9
+    ptol = 5e-2 if "rates_weights" in name else 1e-2
+    for m, gm in zip(models, case["models"]):
+        for k, v in gm.items():
+            np.testing.assert_allclose(m[k], v, rtol=ptol, atol=1e-4, err_msg=k)
+    for k, v in case["treeinfo"].items():
+        np.testing.assert_allclose(tp[k], v, rtol=ptol, atol=1e-4, err_msg=k)
+    if not case["args"].get("linkage"):
+        np.testing.assert_allclose(brl, case["brlens"], rtol=ptol, atol=1e-5)
