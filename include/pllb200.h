@@ -815,6 +815,14 @@ int pllb200_likelihood_derivatives_async(pll_partition_t * partition, int parent
                                          int child_scaler_index, double branch_length,
                                          const unsigned int * params_indices,
                                          const double * sumtable, double * d_f, double * dd_f);
+/* The whole damped Newton-Raphson iteration of pllmod_opt_minimize_newton_multi (one variable) on the
+ * device: one cooperative launch and one host wait per branch instead of one per iteration.
+ * Returns 1 converged, 0 iteration limit reached (pll_errno = PLLMOD_OPT_ERROR_NEWTON_LIMIT, *x_out =
+ * last iterate), -1 error, -2 unsupported for this partition (asc-bias, K not a power of two, ...). */
+int pllb200_newton_branch(pll_partition_t * partition, const unsigned int * params_indices,
+                          const double * sumtable, double xmin, double xguess, double xmax,
+                          double tolerance, unsigned int max_iters, double brlen_scaler,
+                          double * x_out, int * iterations);
 /* Device address (as integer) of the partition's most recent reduction results
  * {logL, d_f, dd_f}: lets a caller run an NCCL all-reduce on them without a host round trip. */
 uint64_t pllb200_result_device_ptr(pll_partition_t * partition);
@@ -825,10 +833,11 @@ typedef struct
   unsigned long long kernel_launches;   /* kernels launched by this library so far */
   unsigned long long h2d_bytes;         /* bytes staged host->device */
   unsigned long long d2h_bytes;         /* bytes copied device->host */
+  unsigned long long newton_iterations; /* derivative passes run inside the fused Newton kernel */
 } pllb200_stats_t;
 void pllb200_get_stats(pllb200_stats_t * out);
 void pllb200_reset_stats(void);
-/* name in {"trav_ctas_per_sm","trav_reorder","fuse_root"}; returns previous value, -1 if unknown */
+/* name in {"trav_ctas_per_sm","trav_reorder","fuse_root","trav_variant","trav_forward","fused_newton"}; returns previous value, -1 if unknown */
 int pllb200_set_option(const char * name, int value);
 
 #ifdef __cplusplus

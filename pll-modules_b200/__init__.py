@@ -18,7 +18,7 @@ _lib = None
 
 class Stats(ctypes.Structure):
     _fields_ = [("kernel_launches", ctypes.c_ulonglong), ("h2d_bytes", ctypes.c_ulonglong),
-                ("d2h_bytes", ctypes.c_ulonglong)]
+                ("d2h_bytes", ctypes.c_ulonglong), ("newton_iterations", ctypes.c_ulonglong)]
 
 
 def load():
@@ -52,7 +52,8 @@ def device_count():
 def stats():
     s = Stats()
     load().pllb200_get_stats(ctypes.byref(s))
-    return {"kernel_launches": s.kernel_launches, "h2d_bytes": s.h2d_bytes, "d2h_bytes": s.d2h_bytes}
+    return {"kernel_launches": s.kernel_launches, "h2d_bytes": s.h2d_bytes, "d2h_bytes": s.d2h_bytes,
+            "newton_iterations": s.newton_iterations}
 
 
 def reset_stats():

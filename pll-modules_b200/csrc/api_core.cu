@@ -200,6 +200,37 @@ extern "C" int pll_update_sumtable(pll_partition_t * partition, unsigned int par
                          child_scaler_index, params_indices, d) ? PLL_SUCCESS : PLL_FAILURE;
 }
 
+extern "C" int pllb200_newton_branch(pll_partition_t * partition, const unsigned int * params_indices,
+                                     const double * sumtable, double xmin, double xguess, double xmax,
+                                     double tolerance, unsigned int max_iters, double brlen_scaler,
+                                     double * x_out, int * iterations)
+{
+  /* returns 1 converged, 0 iteration limit (pll_errno = NEWTON_LIMIT), -1 error, -2 not supported for
+   * this partition (caller falls back to one derivative call per iteration) */
+  if (!enter(partition)) return -1;
+  PartCtx * c = ctx_of(partition);
+  if (!newton_fused_supported(c)) return -2;
+  double * d = sumtable_shadow(c, sumtable, false);
+  if (!d) return -1;
+  const int slot = dev_alloc_slot(c);
+  if (!launch_newton(c, params_indices, d, xmin, xguess, xmax, tolerance, max_iters, brlen_scaler, slot))
+    return -1;
+  if (!dev_flush(c)) return -1;
+  g_d2h_bytes += 4 * sizeof(double);
+  const double * r = c->h_result + slot * 4;
+  *x_out = r[0];
+  if (iterations) *iterations = (int)r[2];
+  g_newton_iterations += (unsigned long long)r[2];
+  if (r[1] == 0.0) return 1;
+  if (r[1] == 1.0)
+  {
+    pllmod_set_error(PLLMOD_OPT_ERROR_NEWTON_LIMIT, "Exceeded maximum number of iterations");
+    return 0;
+  }
+  pllmod_set_error(PLLMOD_OPT_ERROR_NEWTON_DERIV, "Wrong likelihood derivatives");
+  return -1;
+}
+
 extern "C" int pllb200_likelihood_derivatives_async(pll_partition_t * partition,
                                                     int parent_scaler_index, int child_scaler_index,
                                                     double branch_length,

@@ -18,6 +18,7 @@
 #include <algorithm>
 
 unsigned long long g_kernel_launches = 0;
+unsigned long long g_newton_iterations = 0;
 unsigned long long g_h2d_bytes = 0;
 unsigned long long g_d2h_bytes = 0;
 int g_opt_trav_ctas_per_sm = 0; /* 0 = occupancy query */
@@ -56,9 +57,10 @@ extern "C" void pllb200_get_stats(pllb200_stats_t * out)
   out->kernel_launches = g_kernel_launches;
   out->h2d_bytes = g_h2d_bytes;
   out->d2h_bytes = g_d2h_bytes;
+  out->newton_iterations = g_newton_iterations;
 }
 
-extern "C" void pllb200_reset_stats(void) { g_kernel_launches = g_h2d_bytes = g_d2h_bytes = 0; }
+extern "C" void pllb200_reset_stats(void) { g_kernel_launches = g_h2d_bytes = g_d2h_bytes = g_newton_iterations = 0; }
 
 extern "C" int pllb200_set_option(const char * name, int value)
 {
@@ -68,6 +70,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "fuse_root")) slot = &g_opt_fuse_root;
   else if (!strcmp(name, "trav_variant")) slot = &g_opt_trav_variant;
   else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
+  else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;
   if (!slot) return -1;
   int old = *slot;
   *slot = value;

@@ -111,6 +111,7 @@ bool pllb200_cuda_ok(cudaError_t e, const char * what);
 
 /* global counters (device_ctx.cu) */
 extern unsigned long long g_kernel_launches;
+extern unsigned long long g_newton_iterations;
 extern unsigned long long g_h2d_bytes;
 extern unsigned long long g_d2h_bytes;
 extern int g_opt_trav_ctas_per_sm;
@@ -118,6 +119,7 @@ extern int g_opt_trav_reorder;
 extern int g_opt_fuse_root;
 extern int g_opt_trav_variant;
 extern int g_opt_trav_forward;
+extern int g_opt_fused_newton;
 
 /* device context (device_ctx.cu) */
 bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */
@@ -159,6 +161,12 @@ bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
 bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_clv,
                      int parent_scaler, int child_scaler, const unsigned int * params_indices,
                      double * d_sumtable);
+/* k_newton.cu: whole Newton-Raphson loop on one branch in one cooperative launch; result slot =
+ * {x, status (0 ok / 1 iteration limit / 2 non-finite derivative), iterations, last f} */
+bool newton_fused_supported(const PartCtx * c);
+bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
+                   double xmin, double x0, double xmax, double tol, unsigned int max_iters,
+                   double scale, int slot);
 bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double branch_length,
                         const unsigned int * params_indices, const double * d_sumtable, int slot);
 

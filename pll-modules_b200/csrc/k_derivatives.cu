@@ -45,11 +45,15 @@ struct SumArgs
   unsigned int model_idx[DV_MAXK];
 };
 
+#define SUM_U 2    /* elements per thread per trip: 2 x (2 x 32 B) loads in flight */
+#define SUM_LD 18  /* row stride of the staged eigen tables in doubles: rows of different rates sit in
+                      different banks (16 would put all K rows on the same bank) */
+
 template <int K>
-__global__ void __launch_bounds__(DV_THREADS) sumtable_dna_kernel(SumArgs a)
+__global__ void __launch_bounds__(DV_THREADS, 4) sumtable_dna_kernel(SumArgs a)
 {
-  __shared__ double s_w[K][16];  /* pi_i * Vinv[i][j] */
-  __shared__ double s_v[K][16];  /* V[j][i] */
+  __shared__ __align__(16) double s_w[K][SUM_LD];  /* pi_i * Vinv[i][j] */
+  __shared__ __align__(16) double s_v[K][SUM_LD];  /* V[j][i] */
   for (int t = threadIdx.x; t < 16 * K; t += blockDim.x)
   {
     const int k = t / 16, q = t % 16;
@@ -60,72 +64,88 @@ __global__ void __launch_bounds__(DV_THREADS) sumtable_dna_kernel(SumArgs a)
   __syncthreads();
   const int lane = threadIdx.x & 31;
   const int k = lane % K;
+  const double * w = s_w[k];
+  const double * v = s_v[k];
   const unsigned long long E = (unsigned long long)a.sites * K;
   const unsigned long long Eround = (E + 31) / 32 * 32;
   const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-  for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < Eround;
-       e += stride)
+  for (unsigned long long e0 = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e0 < Eround;
+       e0 += SUM_U * stride)
   {
-    const bool act = e < E;
-    d4 out = {0, 0, 0, 0};
-    unsigned int sc = 0;
-    if (act)
+    d4 p[SUM_U], c[SUM_U];
+    unsigned int sc[SUM_U];
+    bool act[SUM_U];
+#pragma unroll
+    for (int u = 0; u < SUM_U; ++u)
     {
-      const unsigned long long site = e / K;
-      d4 p;
-      if (a.ptip)
+      const unsigned long long e = e0 + u * stride;
+      act[u] = e < E;
+      sc[u] = 0;
+      if (act[u])
       {
-        const unsigned int code = a.ptip[site];
-        p.x = (code & 1) ? 1.0 : 0.0;
-        p.y = (code & 2) ? 1.0 : 0.0;
-        p.z = (code & 4) ? 1.0 : 0.0;
-        p.w = (code & 8) ? 1.0 : 0.0;
+        if (a.ptip)
+        {
+          const unsigned int code = a.ptip[e / K];
+          p[u].x = (code & 1) ? 1.0 : 0.0;
+          p[u].y = (code & 2) ? 1.0 : 0.0;
+          p[u].z = (code & 4) ? 1.0 : 0.0;
+          p[u].w = (code & 8) ? 1.0 : 0.0;
+        }
+        else
+          p[u] = ldg256(a.pclv + e * 4);
+        c[u] = ldg256(a.cclv + e * 4);
+        if (a.rate_scalers)
+        {
+          if (a.pscaler) sc[u] += a.pscaler[e];
+          if (a.cscaler) sc[u] += a.cscaler[e];
+        }
       }
-      else
-        p = ldg256(a.pclv + e * 4);
-      const d4 c = ldg256(a.cclv + e * 4);
-      const double * w = s_w[k];
-      const double * v = s_v[k];
-      const double l0 = p.x * w[0] + p.y * w[4] + p.z * w[8] + p.w * w[12];
-      const double l1 = p.x * w[1] + p.y * w[5] + p.z * w[9] + p.w * w[13];
-      const double l2 = p.x * w[2] + p.y * w[6] + p.z * w[10] + p.w * w[14];
-      const double l3 = p.x * w[3] + p.y * w[7] + p.z * w[11] + p.w * w[15];
-      const double r0 = v[0] * c.x + v[1] * c.y + v[2] * c.z + v[3] * c.w;
-      const double r1 = v[4] * c.x + v[5] * c.y + v[6] * c.z + v[7] * c.w;
-      const double r2 = v[8] * c.x + v[9] * c.y + v[10] * c.z + v[11] * c.w;
-      const double r3 = v[12] * c.x + v[13] * c.y + v[14] * c.z + v[15] * c.w;
-      out.x = l0 * r0;
-      out.y = l1 * r1;
-      out.z = l2 * r2;
-      out.w = l3 * r3;
+    }
+#pragma unroll
+    for (int u = 0; u < SUM_U; ++u)
+    {
+      const unsigned long long e = e0 + u * stride;
+      if (e >= Eround) break; /* warp-uniform */
+      d4 out = {0, 0, 0, 0};
+      if (act[u])
+      {
+        const d4 pp = p[u], cc = c[u];
+        const double l0 = pp.x * w[0] + pp.y * w[4] + pp.z * w[8] + pp.w * w[12];
+        const double l1 = pp.x * w[1] + pp.y * w[5] + pp.z * w[9] + pp.w * w[13];
+        const double l2 = pp.x * w[2] + pp.y * w[6] + pp.z * w[10] + pp.w * w[14];
+        const double l3 = pp.x * w[3] + pp.y * w[7] + pp.z * w[11] + pp.w * w[15];
+        const double r0 = v[0] * cc.x + v[1] * cc.y + v[2] * cc.z + v[3] * cc.w;
+        const double r1 = v[4] * cc.x + v[5] * cc.y + v[6] * cc.z + v[7] * cc.w;
+        const double r2 = v[8] * cc.x + v[9] * cc.y + v[10] * cc.z + v[11] * cc.w;
+        const double r3 = v[12] * cc.x + v[13] * cc.y + v[14] * cc.z + v[15] * cc.w;
+        out.x = l0 * r0;
+        out.y = l1 * r1;
+        out.z = l2 * r2;
+        out.w = l3 * r3;
+      }
       if (a.rate_scalers)
       {
-        if (a.pscaler) sc += a.pscaler[e];
-        if (a.cscaler) sc += a.cscaler[e];
-      }
-    }
-    if (a.rate_scalers)
-    {
-      unsigned int mn = sc;
+        unsigned int mn = sc[u];
 #pragma unroll
-      for (int off = 1; off < K; off <<= 1)
-      {
-        const unsigned int o = __shfl_xor_sync(0xffffffffu, mn, off);
-        mn = o < mn ? o : mn;
+        for (int off = 1; off < K; off <<= 1)
+        {
+          const unsigned int o = __shfl_xor_sync(0xffffffffu, mn, off);
+          mn = o < mn ? o : mn;
+        }
+        unsigned int diff = sc[u] - mn;
+        if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
+        double f = 1.0;
+        for (unsigned int q = 0; q < diff; ++q) f *= SCALE_THRESHOLD_D;
+        if (diff)
+        {
+          out.x *= f;
+          out.y *= f;
+          out.z *= f;
+          out.w *= f;
+        }
       }
-      unsigned int diff = sc - mn;
-      if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
-      double f = 1.0;
-      for (unsigned int q = 0; q < diff; ++q) f *= SCALE_THRESHOLD_D;
-      if (diff)
-      {
-        out.x *= f;
-        out.y *= f;
-        out.z *= f;
-        out.w *= f;
-      }
+      if (act[u]) stg256(a.sum + e * 4, out);
     }
-    if (act) stg256(a.sum + e * 4, out);
   }
 }
 
@@ -471,7 +491,7 @@ bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_cl
   {
     const unsigned long long E = (unsigned long long)a.sites * K;
     unsigned long long blocks = (E + DV_THREADS - 1) / DV_THREADS;
-    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 4; /* one resident wave (launch bounds) */
     if (blocks > cap) blocks = cap;
     switch (K)
     {

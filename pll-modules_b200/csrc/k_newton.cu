@@ -1,0 +1,445 @@
+/*
+ * k_newton.cu — the whole Newton-Raphson iteration on ONE branch length in ONE persistent kernel.
+ *
+ * The reference's inner loop (pllmod_opt_minimize_newton_multi, src/optimize/opt_algorithms.c:133-262,
+ * driven from pll_optimize.c:1395-1560) calls pll_compute_likelihood_derivatives once per iteration:
+ * on a GPU that is one launch + one host wait per iteration (3-30 per branch), and branch-length
+ * optimisation is what an SPR round spends 85 % of its time in (profiles/README.md).  Here a
+ * cooperative grid keeps the bracket [xl, xh], the iterate and the convergence tests on the device:
+ *
+ *   repeat:  every CTA rebuilds the diagonal table diag[k][j] = (e, l e, l^2 e), e = exp(l t),
+ *            l = eigenvalue_j * rate_k / (1 - pinv_k)               (core_derivatives.c:757-772)
+ *            grid-stride pass over the sumtable -> per-CTA partial (d_f, dd_f)     (A.7)
+ *            grid barrier; every CTA sums the partials in index order (deterministic, identical
+ *            in all CTAs) and applies the SAME damped Newton update to its private copy of the state
+ *   until converged / iteration limit / non-finite derivative.
+ *
+ * One launch and one host wait per branch; the sumtable (one CLV-sized buffer) is re-read from L2
+ * when it fits.  Conditions for this path (checked by the host, otherwise the per-iteration path
+ * runs): one local partition, no cross-rank reduction callback, no ascertainment bias, rate
+ * categories a power of two <= 32, K * states <= 512.
+ */
+#include "internal.h"
+#include "devutil.cuh"
+
+#include <algorithm>
+#include <cooperative_groups.h>
+
+namespace cg = cooperative_groups;
+
+#define NW_THREADS 256
+#define NW_MAXK 32
+#define NW_MAX_DIAG 512 /* K * states */
+
+struct NewtonArgs
+{
+  const double * sum;
+  const unsigned int * weights;
+  const int * invariant; /* may be null */
+  const double * eigen;
+  unsigned long long eigen_stride;
+  unsigned int sites, states, sp, K, kshift, any_pinv;
+  unsigned int model_idx[NW_MAXK];
+  double w[NW_MAXK], pinv[NW_MAXK], rate[NW_MAXK];
+  double xmin, xmax, x0, tol, scale; /* scale: brlen scaler s (df *= s, ddf *= s^2, t = s x) */
+  unsigned int max_iters;
+  double * partials; /* [2 buffers][2][gridDim.x] */
+  double * result_dev;
+  double * result_host;
+};
+
+/* status codes returned in result[1] */
+#define NW_OK 0.0
+#define NW_LIMIT 1.0
+#define NW_BAD_DERIV 2.0
+
+/* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates) */
+template <int MODE>
+__global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(NewtonArgs a)
+{
+  constexpr bool DNA = MODE != 0;
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double s_diag[NW_MAX_DIAG * 3];
+  __shared__ double s_red[2][NW_THREADS / 32];
+  __shared__ double s_tot[2];
+
+  const unsigned int K = a.K, s = a.states, sp = a.sp;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned int k = (unsigned int)lane & (K - 1); /* K is a power of two <= 32 */
+  const unsigned int kshift = a.kshift;
+  const double wk = a.w[k], pinv = a.pinv[k];
+  const bool any_pinv = a.any_pinv != 0;
+  const double * fr = a.eigen + (unsigned long long)a.model_idx[k] * a.eigen_stride + 2 * s * sp + sp;
+  const unsigned long long E = (unsigned long long)a.sites * K;
+  const unsigned long long Eround = (E + 31) / 32 * 32;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  const unsigned long long base = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  /* same for all lanes of a warp: Eround and the warp's first index are multiples of 32 */
+  const unsigned int n_it = base < Eround ? (unsigned int)((Eround - base + stride - 1) / stride) : 0u;
+  constexpr int U = DNA ? 4 : 1; /* independent 32-byte loads in flight per thread */
+
+  /* optimiser state, replicated in every thread (all threads see the same f, df) */
+  double xl = a.xmin, xh = a.xmax;
+  double x = fmax(fmin(a.x0, a.xmax), a.xmin);
+  const double dxmax = a.xmax / a.max_iters;
+  unsigned int iter = 0;
+  double status = NW_OK;
+  double f = 0.0, df = 0.0;
+
+  for (;;)
+  {
+    if (iter++ > a.max_iters)
+    {
+      status = NW_LIMIT;
+      break;
+    }
+    /* diagonal table for the current branch length */
+    const double t = a.scale * x;
+    __syncthreads();
+    for (unsigned int i = threadIdx.x; i < K * s; i += blockDim.x)
+    {
+      const unsigned int kk = i / s, j = i % s;
+      const double ev = a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * s * sp + j];
+      const double ki = a.rate[kk] / (1.0 - a.pinv[kk]);
+      const double e0 = exp(ev * ki * t);
+      s_diag[i * 3 + 0] = e0;
+      s_diag[i * 3 + 1] = ev * ki * e0;
+      s_diag[i * 3 + 2] = ev * ki * ev * ki * e0;
+      if (MODE == 2)
+      {
+        /* the K = 4 pass reads a second copy with w_k (1 - pinv_k) folded in (last 48 entries) */
+        const double wf = a.w[kk] * (1.0 - a.pinv[kk]);
+        double * d = s_diag + NW_MAX_DIAG * 3 - 48;
+        d[i * 3 + 0] = wf * e0;
+        d[i * 3 + 1] = wf * ev * ki * e0;
+        d[i * 3 + 2] = wf * ev * ki * ev * ki * e0;
+      }
+    }
+    __syncthreads();
+
+    double acc1 = 0.0, acc2 = 0.0;
+    const double * dg = s_diag + (size_t)k * s * 3;
+    /* odd passes walk the table backwards: what the previous pass (or the sumtable kernel, which
+     * writes ascending) touched last is still in the 126 MB L2 */
+    const bool fwd = (iter & 1u) == 0;
+    if (MODE == 2)
+    {
+      /* K = 4: a thread's 4 elements belong to 4 different sites and one rate.  Register slot j holds
+       * trip it0 + (j ^ perm), perm = bit-reversed rate index, so that two exchange rounds with FIXED
+       * send/keep slots (2,3 -> 0,1 then 1 -> 0) leave in slot 0 the sum over the 4 rates of a
+       * different site in each lane: 9 shuffles per 4 elements, and the division runs on all lanes. */
+      const unsigned int perm = ((k & 1u) << 1) | ((k >> 1) & 1u);
+      const double * dgw = s_diag + NW_MAX_DIAG * 3 - 48 + (size_t)k * 12; /* diag * w_k (1 - pinv_k) */
+      for (unsigned int it0 = 0; it0 < n_it; it0 += 4)
+      {
+        d4 v[4];
+        double L0[4], L1[4], L2[4];
+        const unsigned int itf = it0 + perm; /* slot 0's trip: the site this lane finishes */
+        const unsigned int idxf = fwd ? itf : n_it - 1 - itf;
+        const unsigned long long sitef = (base + (unsigned long long)idxf * stride) >> 2;
+        const bool actf = itf < n_it && sitef < a.sites;
+        unsigned int wgt = 0;
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+          const unsigned int it = it0 + ((unsigned int)j ^ perm);
+          const unsigned int idx = fwd ? it : n_it - 1 - it;
+          const unsigned long long e = base + (unsigned long long)idx * stride;
+          v[j].x = v[j].y = v[j].z = v[j].w = 0.0;
+          if (it < n_it && e < E) v[j] = ldg256(a.sum + e * 4);
+        }
+        if (actf) wgt = __ldg(a.weights + sitef);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+          L0[j] = v[j].x * dgw[0] + v[j].y * dgw[3] + v[j].z * dgw[6] + v[j].w * dgw[9];
+          L1[j] = v[j].x * dgw[1] + v[j].y * dgw[4] + v[j].z * dgw[7] + v[j].w * dgw[10];
+          L2[j] = v[j].x * dgw[2] + v[j].y * dgw[5] + v[j].z * dgw[8] + v[j].w * dgw[11];
+        }
+        if (any_pinv && a.invariant)
+        {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+          {
+            const unsigned int it = it0 + ((unsigned int)j ^ perm);
+            const unsigned int idx = fwd ? it : n_it - 1 - it;
+            const unsigned long long e = base + (unsigned long long)idx * stride;
+            if (it < n_it && e < E)
+            {
+              const int inv = a.invariant[e >> 2];
+              if (inv >= 0) L0[j] += fr[inv] * pinv * wk;
+            }
+          }
+        }
+        L0[0] += __shfl_xor_sync(0xffffffffu, L0[2], 1);
+        L0[1] += __shfl_xor_sync(0xffffffffu, L0[3], 1);
+        L1[0] += __shfl_xor_sync(0xffffffffu, L1[2], 1);
+        L1[1] += __shfl_xor_sync(0xffffffffu, L1[3], 1);
+        L2[0] += __shfl_xor_sync(0xffffffffu, L2[2], 1);
+        L2[1] += __shfl_xor_sync(0xffffffffu, L2[3], 1);
+        L0[0] += __shfl_xor_sync(0xffffffffu, L0[1], 2);
+        L1[0] += __shfl_xor_sync(0xffffffffu, L1[1], 2);
+        L2[0] += __shfl_xor_sync(0xffffffffu, L2[1], 2);
+        if (actf)
+        {
+          const double r1 = -L1[0] / L0[0];
+          acc1 += (double)wgt * r1;
+          acc2 += (double)wgt * (r1 * r1 - L2[0] / L0[0]);
+        }
+      }
+    }
+    else
+    for (unsigned int it0 = 0; it0 < n_it; it0 += U)
+    {
+      bool act[U];
+      d4 v[U];
+      unsigned int wgt[U];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+      {
+        const unsigned int it = it0 + u;
+        const unsigned int idx = fwd ? it : n_it - 1 - it;
+        const unsigned long long e = base + (unsigned long long)idx * stride;
+        act[u] = it < n_it && e < E;
+        wgt[u] = 0;
+        if (act[u])
+        {
+          if (DNA) v[u] = ldg256(a.sum + e * 4);
+          wgt[u] = __ldg(a.weights + (e >> kshift));
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+      {
+        if (it0 + u >= n_it) break; /* warp-uniform */
+        const unsigned int idx = fwd ? it0 + u : n_it - 1 - (it0 + u);
+        const unsigned long long e = base + (unsigned long long)idx * stride;
+        const unsigned long long site = e >> kshift;
+        double L0 = 0.0, L1 = 0.0, L2 = 0.0;
+        if (act[u])
+        {
+          if (DNA)
+          {
+            L0 = v[u].x * dg[0] + v[u].y * dg[3] + v[u].z * dg[6] + v[u].w * dg[9];
+            L1 = v[u].x * dg[1] + v[u].y * dg[4] + v[u].z * dg[7] + v[u].w * dg[10];
+            L2 = v[u].x * dg[2] + v[u].y * dg[5] + v[u].z * dg[8] + v[u].w * dg[11];
+          }
+          else
+          {
+            const double * sm = a.sum + e * sp;
+            for (unsigned int j = 0; j < s; ++j)
+            {
+              const double sv = sm[j];
+              L0 += sv * dg[j * 3 + 0];
+              L1 += sv * dg[j * 3 + 1];
+              L2 += sv * dg[j * 3 + 2];
+            }
+          }
+          if (pinv > 0.0)
+          {
+            double inv_lk = 0.0;
+            if (a.invariant)
+            {
+              const int inv = a.invariant[site];
+              if (inv >= 0) inv_lk = fr[inv] * pinv;
+            }
+            L0 = L0 * (1.0 - pinv) + inv_lk;
+            L1 = L1 * (1.0 - pinv);
+            L2 = L2 * (1.0 - pinv);
+          }
+          L0 *= wk;
+          L1 *= wk;
+          L2 *= wk;
+        }
+        for (unsigned int off = 1; off < K; off <<= 1)
+        {
+          L0 += __shfl_xor_sync(0xffffffffu, L0, off);
+          L1 += __shfl_xor_sync(0xffffffffu, L1, off);
+          L2 += __shfl_xor_sync(0xffffffffu, L2, off);
+        }
+        if (act[u] && k == 0)
+        {
+          const double r1 = -L1 / L0;
+          acc1 += (double)wgt[u] * r1;
+          acc2 += (double)wgt[u] * (r1 * r1 - L2 / L0);
+        }
+      }
+    }
+    /* CTA partial */
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+    {
+      acc1 += __shfl_down_sync(0xffffffffu, acc1, off);
+      acc2 += __shfl_down_sync(0xffffffffu, acc2, off);
+    }
+    if (lane == 0)
+    {
+      s_red[0][warp] = acc1;
+      s_red[1][warp] = acc2;
+    }
+    __syncthreads();
+    double * buf = a.partials + (size_t)(iter & 1u) * 2 * gridDim.x;
+    if (threadIdx.x == 0)
+    {
+      double p1 = 0.0, p2 = 0.0;
+      for (int wi = 0; wi < NW_THREADS / 32; ++wi)
+      {
+        p1 += s_red[0][wi];
+        p2 += s_red[1][wi];
+      }
+      buf[blockIdx.x] = p1;
+      buf[gridDim.x + blockIdx.x] = p2;
+    }
+    grid.sync();
+    /* every CTA: the same ordered sum of all partials */
+    if (warp == 0)
+    {
+      double t1 = 0.0, t2 = 0.0;
+      for (unsigned int b = lane; b < gridDim.x; b += 32)
+      {
+        t1 += __ldcg(buf + b);
+        t2 += __ldcg(buf + gridDim.x + b);
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1)
+      {
+        t1 += __shfl_down_sync(0xffffffffu, t1, off);
+        t2 += __shfl_down_sync(0xffffffffu, t2, off);
+      }
+      if (lane == 0)
+      {
+        s_tot[0] = t1;
+        s_tot[1] = t2;
+      }
+    }
+    __syncthreads();
+    f = a.scale * s_tot[0];
+    df = a.scale * a.scale * s_tot[1];
+
+    /* damped Newton step inside the shrinking bracket (opt_algorithms.c:187-252) */
+    if (!isfinite(f) || !isfinite(df))
+    {
+      status = NW_BAD_DERIV;
+      break;
+    }
+    double dx;
+    if (df > 0.0)
+    {
+      if (fabs(f) < a.tol) break;
+      if (f < 0.0)
+        xl = x;
+      else
+        xh = x;
+      dx = -f / df;
+    }
+    else
+      dx = -f / fabs(df);
+    dx = fmax(fmin(dx, dxmax), -dxmax);
+    if (x + dx < xl) dx = xl - x;
+    if (x + dx > xh) dx = xh - x;
+    if (fabs(dx) < a.tol) break;
+    x += dx;
+    x = fmax(fmin(x, a.xmax), a.xmin);
+  }
+
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+  {
+    a.result_dev[0] = x;
+    a.result_dev[1] = status;
+    a.result_dev[2] = (double)iter;
+    a.result_dev[3] = f;
+    a.result_host[0] = x;
+    a.result_host[1] = status;
+    a.result_host[2] = (double)iter;
+    a.result_host[3] = f;
+    __threadfence_system();
+  }
+}
+
+/* can the fused path serve this partition? */
+int g_opt_fused_newton = 1;
+
+bool newton_fused_supported(const PartCtx * c)
+{
+  const pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats;
+  if (p->attributes & PLL_ATTRIB_AB_MASK) return false;
+  if (K == 0 || K > NW_MAXK || (K & (K - 1)) != 0) return false;
+  if ((size_t)K * p->states > NW_MAX_DIAG) return false;
+  return g_opt_fused_newton != 0;
+}
+
+bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
+                   double xmin, double x0, double xmax, double tol, unsigned int max_iters,
+                   double scale, int slot)
+{
+  pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats, s = p->states;
+  if (!dev_sync_inputs(c) || !dev_sync_eigen(c, params_indices)) return false;
+  NewtonArgs a;
+  memset(&a, 0, sizeof(a));
+  a.sum = d_sumtable;
+  a.weights = c->d_weights;
+  a.eigen = c->d_eigen;
+  a.eigen_stride = c->eigen_stride;
+  a.sites = p->sites;
+  a.states = s;
+  a.sp = p->states_padded;
+  a.K = K;
+  for (a.kshift = 0; (1u << a.kshift) < K; ++a.kshift) {}
+  bool any_pinv = false;
+  for (unsigned int k = 0; k < K; ++k)
+  {
+    a.model_idx[k] = params_indices[k];
+    a.w[k] = p->rate_weights[k];
+    a.pinv[k] = p->prop_invar[params_indices[k]];
+    a.rate[k] = p->rates[k];
+    any_pinv |= a.pinv[k] > 0.0;
+  }
+  if (any_pinv)
+  {
+    if (!p->invariant)
+    {
+      pllb200_set_error(PLL_ERROR_INVAR_NONEFOUND, "prop_invar > 0 but no invariant site array.");
+      return false;
+    }
+    if (!c->d_invariant)
+    {
+      c->invariant_dirty = true;
+      if (!dev_sync_inputs(c)) return false;
+    }
+    a.invariant = c->d_invariant;
+  }
+  a.any_pinv = any_pinv;
+  a.xmin = xmin;
+  a.xmax = xmax;
+  a.x0 = x0;
+  a.tol = tol;
+  a.scale = scale;
+  a.max_iters = max_iters;
+  a.partials = c->d_partials;
+  a.result_dev = c->d_result + slot * 4;
+  a.result_host = c->h_result_dev + slot * 4;
+
+  /* cooperative grid: never more CTAs than can be co-resident, never more than there is work */
+  static int per_sm[3] = {0, 0, 0};
+  const int dna = s == 4 ? (K == 4 ? 2 : 1) : 0;
+  const void * fn = dna == 2 ? (const void *)newton_kernel<2>
+                             : dna == 1 ? (const void *)newton_kernel<1> : (const void *)newton_kernel<0>;
+  if (!per_sm[dna])
+  {
+    int nb = 0;
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, NW_THREADS, 0);
+    per_sm[dna] = (e == cudaSuccess && nb > 0) ? nb : 1;
+  }
+  const unsigned long long E = (unsigned long long)a.sites * K;
+  unsigned long long blocks = (E + NW_THREADS - 1) / NW_THREADS;
+  unsigned long long cap = (unsigned long long)c->sm_count * std::min(per_sm[dna], 4);
+  if (cap > PLLB200_MAX_RED_BLOCKS * 3 / 4) cap = PLLB200_MAX_RED_BLOCKS * 3 / 4; /* partials: 2 buffers x 2 values */
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  void * kargs[] = {&a};
+  const cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3((unsigned)blocks), dim3(NW_THREADS), kargs, 0, c->stream);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(e, "newton kernel launch");
+}

@@ -504,10 +504,27 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
   {
     case PLLMOD_OPT_BLO_NEWTON_FAST:
     case PLLMOD_OPT_BLO_NEWTON_SAFE:
-      retval = pllmod_opt_minimize_newton_multi(xnum, xmin, xguess, xmax, xtol,
-                                                prm->max_newton_iters, prm->converged, prm,
-                                                multi_deriv_cb);
+    {
+      /* one local partition and nothing to reduce across ranks: the whole iteration runs on the
+       * device (k_newton.cu); otherwise one derivative pass per iteration and partition */
+      int fused = -2;
+      if (xnum == 1 && prm->partition_count == 1 && prm->partitions[0] && !prm->parallel_reduce_cb)
+      {
+        pll_errno = 0;
+        const double s = prm->brlen_scalers ? prm->brlen_scalers[0] : 1.;
+        fused = pllb200_newton_branch(prm->partitions[0], prm->params_indices[0],
+                                      prm->precomp_buffers[0], xmin, xguess[0], xmax, xtol,
+                                      (unsigned int)prm->max_newton_iters, s, &xguess[0], nullptr);
+        if (fused >= 0 && prm->converged) prm->converged[0] = fused == 1;
+      }
+      if (fused == -2)
+        retval = pllmod_opt_minimize_newton_multi(xnum, xmin, xguess, xmax, xtol,
+                                                  prm->max_newton_iters, prm->converged, prm,
+                                                  multi_deriv_cb);
+      else
+        retval = fused == 1 ? PLL_SUCCESS : PLL_FAILURE;
       break;
+    }
     case PLLMOD_OPT_BLO_NEWTON_OLDFAST:
     case PLLMOD_OPT_BLO_NEWTON_OLDSAFE:
       assert(!unlinked);
