@@ -21,6 +21,8 @@
 #include "internal.h"
 
 #include <cassert>
+#include <chrono>
+#include <cstdio>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -252,11 +254,28 @@ double optimize_bl(pll_unode_t * node, pllmod_treeinfo_t * ti, const SearchParam
   return nll ? -nll : 0.0;
 }
 
+/* PLLB200_TRACE_SPR=1: phase times of one round on stderr */
+struct PhaseClock
+{
+  double search_s = 0, blo_s = 0;
+  unsigned long long search_launches = 0, blo_launches = 0, blo_calls = 0;
+  static double now()
+  {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+  }
+} g_phase;
+
 double optimize_bl_all(pllmod_treeinfo_t * ti, const SearchParams & prm, double lh_epsilon,
                        double smooth_factor)
 {
+  const double t0 = PhaseClock::now();
+  const unsigned long long l0 = g_kernel_launches;
   pllmod_treeinfo_compute_loglh(ti, 0);
-  return optimize_bl(ti->root, ti, prm, PLLMOD_OPT_BRLEN_OPTIMIZE_ALL, lh_epsilon, smooth_factor);
+  const double r = optimize_bl(ti->root, ti, prm, PLLMOD_OPT_BRLEN_OPTIMIZE_ALL, lh_epsilon, smooth_factor);
+  g_phase.blo_s += PhaseClock::now() - t0;
+  g_phase.blo_launches += g_kernel_launches - l0;
+  ++g_phase.blo_calls;
+  return r;
 }
 
 /* clamp the length(s) of one branch into [bl_min, bl_max] (algo_search.c:382-424) */
@@ -619,7 +638,14 @@ extern "C" double pllmod_algo_spr_round(pllmod_treeinfo_t * ti, unsigned int rad
   collect_inner_subnodes(ti->root->back, allnodes);
   collect_inner_subnodes(ti->root, allnodes);
 
-  loglh = reinsert_nodes(ti, allnodes.data(), (int)allnodes.size(), ring, top, cutoff, prm);
+  g_phase = PhaseClock();
+  {
+    const double t0 = PhaseClock::now();
+    const unsigned long long l0 = g_kernel_launches;
+    loglh = reinsert_nodes(ti, allnodes.data(), (int)allnodes.size(), ring, top, cutoff, prm);
+    g_phase.search_s = PhaseClock::now() - t0;
+    g_phase.search_launches = g_kernel_launches - l0;
+  }
   if (!loglh) return 0;
 
   /* NOTE: the reference has a second, thorough pass over the best rejected subtrees in fast mode, but
@@ -688,6 +714,9 @@ extern "C" double pllmod_algo_spr_round(pllmod_treeinfo_t * ti, unsigned int rad
     if (!rc) return 0;
   }
   loglh = pllmod_treeinfo_compute_loglh(ti, 0);
+  if (getenv("PLLB200_TRACE_SPR"))
+    fprintf(stderr, "[spr_round] search %.3f s (%llu launches), all-branch optimisation %.3f s in %llu calls (%llu launches)\n",
+            g_phase.search_s, g_phase.search_launches, g_phase.blo_s, g_phase.blo_calls, g_phase.blo_launches);
   if (fabs(loglh - best_lh) > 1e-6)
   {
     pllmod_set_error(PLLMOD_TREE_ERROR_INVALID_TREE, "LH mismatch after SPR round: %.12f != %.12f",
