@@ -171,7 +171,10 @@ bool dev_ctx_init(PartCtx * c)
     CUDA_TRY(cudaMalloc(&c->d_tipmap, 256 * sizeof(unsigned long long)), false);
     CUDA_TRY(cudaMemsetAsync(c->d_tipmap, 0, 256 * sizeof(unsigned long long), c->stream), false);
   }
-  CUDA_TRY(cudaMalloc(&c->d_weights, sizeof(unsigned int) * c->sites_alloc), false);
+  /* padded to whole 256-site tiles: the Newton kernel fetches weights by 16-byte-granular bulk copies */
+  CUDA_TRY(cudaMalloc(&c->d_weights, sizeof(unsigned int) * round_up(c->sites_alloc + 4, 256)), false);
+  CUDA_TRY(cudaMemsetAsync(c->d_weights, 0, sizeof(unsigned int) * round_up(c->sites_alloc + 4, 256),
+                           c->stream), false);
   CUDA_TRY(cudaMalloc(&c->d_eigen, sizeof(double) * c->eigen_stride * p->rate_matrices), false);
   CUDA_TRY(cudaMemsetAsync(c->d_eigen, 0, sizeof(double) * c->eigen_stride * p->rate_matrices,
                            c->stream), false);

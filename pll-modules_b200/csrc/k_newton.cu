@@ -182,9 +182,10 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
         L2[0] += __shfl_xor_sync(0xffffffffu, L2[1], 2);
         if (actf)
         {
-          const double r1 = -L1[0] / L0[0];
+          const double inv = 1.0 / L0[0]; /* one reciprocal for both ratios */
+          const double r1 = -L1[0] * inv;
           acc1 += (double)wgt * r1;
-          acc2 += (double)wgt * (r1 * r1 - L2[0] / L0[0]);
+          acc2 += (double)wgt * (r1 * r1 - L2[0] * inv);
         }
       }
     }
@@ -356,6 +357,289 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
   }
 }
 
+/* ---- 4 states, 4 rates: the same iteration with the sumtable streamed through a TMA ring ----------
+ *
+ * The register version above is latency-bound: a warp issues its four 32-byte loads, waits ~2 us under
+ * load, computes, and only then asks for more (13 trips per warp and pass at 1 M sites; ncu: 25 % of
+ * the warps resident, issue slots 29 % busy, DRAM 20-33 %).  Here the table arrives in 32 KB tiles
+ * (1024 elements = 256 sites, plus their 256 pattern weights) by cp.async.bulk into a 3-stage shared
+ * memory ring, completion on one mbarrier per stage: two stages (66 KB) per CTA are always in flight
+ * without holding a register, one elected thread refills a stage as soon as the CTA has lifted it into
+ * registers.  Thread t owns elements {j*256 + t} of a tile: one rate (t & 3) of four different sites,
+ * reduced over the rates with the fixed-slot exchange described above.
+ */
+#define NT_TILE 1024 /* elements per tile */
+#define NT_STAGES 3
+#define NT_THREADS (NW_THREADS + 32) /* 8 consumer warps + 1 producer warp */
+
+struct NewtonTmaSmem
+{
+  double tile[NT_STAGES][NT_TILE * 4];
+  unsigned int wts[NT_STAGES][NT_TILE / 4];
+  unsigned long long full[NT_STAGES];  /* TMA -> consumers: bytes have landed */
+  unsigned long long empty[NT_STAGES]; /* consumers -> producer: stage is in registers (8 arrivals) */
+  double diag[48]; /* [k][j][3], w_k (1 - pinv_k) folded in */
+  double red[2][NW_THREADS / 32];
+  double tot[2];
+};
+
+__device__ __forceinline__ void mbar_arrive(unsigned long long * bar)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+__global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonArgs a)
+{
+  cg::grid_group grid = cg::this_grid();
+  extern __shared__ __align__(128) unsigned char nt_smem_raw[];
+  NewtonTmaSmem & sm = *reinterpret_cast<NewtonTmaSmem *>(nt_smem_raw);
+
+  const unsigned int tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5;
+  const bool producer = warp == NW_THREADS / 32;
+  const unsigned int k = tid & 3u;
+  const unsigned int perm = ((k & 1u) << 1) | ((k >> 1) & 1u);
+  const double wk = a.w[k], pinv = a.pinv[k];
+  const bool any_pinv = a.any_pinv != 0;
+  const double * fr = a.eigen + (unsigned long long)a.model_idx[k] * a.eigen_stride + 36;
+  const unsigned long long E = (unsigned long long)a.sites * 4;
+  const unsigned int ntiles = (unsigned int)((E + NT_TILE - 1) / NT_TILE);
+  const unsigned int G = gridDim.x, b = blockIdx.x;
+  const unsigned int nt = b < ntiles ? (ntiles - b + G - 1) / G : 0u; /* tiles of this CTA per pass */
+  /* conflict-free 16-byte halves: lanes 4-7 of every 8 read the upper half first */
+  const unsigned int swz = (tid >> 2) & 1u;
+
+  if (tid == 0)
+  {
+    for (int st = 0; st < NT_STAGES; ++st)
+    {
+      mbar_init(&sm.full[st], 1);
+      mbar_init(&sm.empty[st], NW_THREADS / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+
+  double xl = a.xmin, xh = a.xmax;
+  double x = fmax(fmin(a.x0, a.xmax), a.xmin);
+  const double dxmax = a.xmax / a.max_iters;
+  unsigned int iter = 0;
+  unsigned int used = 0; /* tiles through the ring so far (all passes): stage = n % 3, fill number n / 3 */
+  double status = NW_OK;
+  double f = 0.0, df = 0.0;
+
+  for (;;)
+  {
+    if (iter++ > a.max_iters)
+    {
+      status = NW_LIMIT;
+      break;
+    }
+    const bool fwd = (iter & 1u) == 0;
+    double acc1 = 0.0, acc2 = 0.0;
+
+    if (producer)
+    {
+      if (lane == 0)
+        for (unsigned int i = 0; i < nt; ++i)
+        {
+          const unsigned int n = used + i, slot = n % NT_STAGES, fill = n / NT_STAGES;
+          if (fill) mbar_wait(&sm.empty[slot], (fill - 1u) & 1u); /* previous contents consumed */
+          const unsigned int mine = fwd ? i : nt - 1 - i;
+          const unsigned long long e0 = ((unsigned long long)b + (unsigned long long)mine * G) * NT_TILE;
+          const unsigned int elems = (unsigned int)((E - e0) < NT_TILE ? (E - e0) : NT_TILE);
+          const unsigned int wbytes = ((elems / 4 + 3u) & ~3u) * 4u; /* weights are padded to whole tiles */
+          mbar_expect_tx(&sm.full[slot], elems * 32u + wbytes);
+          tma_load_1d(sm.tile[slot], a.sum + e0 * 4, elems * 32u, &sm.full[slot]);
+          tma_load_1d(sm.wts[slot], a.weights + e0 / 4, wbytes, &sm.full[slot]);
+        }
+    }
+    else if (tid < 16)
+    {
+      /* diagonal table for the current branch length, while the first tiles are on their way */
+      const double t = a.scale * x;
+      const unsigned int kk = tid >> 2, j = tid & 3u;
+      const double ev = a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 32 + j];
+      const double ki = a.rate[kk] / (1.0 - a.pinv[kk]);
+      const double e0 = exp(ev * ki * t);
+      const double wf = a.w[kk] * (1.0 - a.pinv[kk]);
+      sm.diag[tid * 3 + 0] = wf * e0;
+      sm.diag[tid * 3 + 1] = wf * ev * ki * e0;
+      sm.diag[tid * 3 + 2] = wf * ev * ki * ev * ki * e0;
+    }
+    /* consumers only (named barrier 1): the table is ready */
+    if (!producer)
+    {
+      asm volatile("bar.sync 1, %0;" ::"n"(NW_THREADS) : "memory");
+      const double * dgw = sm.diag + k * 12;
+      for (unsigned int i = 0; i < nt; ++i)
+      {
+        const unsigned int n = used + i, slot = n % NT_STAGES;
+        const unsigned int mine = fwd ? i : nt - 1 - i;
+        const unsigned long long e0 = ((unsigned long long)b + (unsigned long long)mine * G) * NT_TILE;
+        const unsigned int elems = (unsigned int)((E - e0) < NT_TILE ? (E - e0) : NT_TILE);
+        mbar_wait(&sm.full[slot], (n / NT_STAGES) & 1u);
+
+        /* lift this thread's four elements and its site's weight out of the stage */
+        d4 v[4];
+        const unsigned int sitef = perm * 64u + (tid >> 2); /* tile-local site this lane finishes */
+        const bool actf = sitef * 4u < elems;
+        const unsigned int wgt = sm.wts[slot][sitef];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+          const unsigned int el = (((unsigned int)j ^ perm) << 8) + tid;
+          const double * src = sm.tile[slot] + (size_t)el * 4;
+          const d2 h0 = *reinterpret_cast<const d2 *>(src + 2 * swz);
+          const d2 h1 = *reinterpret_cast<const d2 *>(src + 2 * (swz ^ 1u));
+          const d2 lo = swz ? h1 : h0, hi = swz ? h0 : h1;
+          v[j].x = lo.x;
+          v[j].y = lo.y;
+          v[j].z = hi.x;
+          v[j].w = hi.y;
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&sm.empty[slot]); /* this warp no longer needs the stage */
+        if (elems != NT_TILE)
+        {
+          /* last, partial tile of the table: whatever lies behind it in the stage counts as zero */
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if ((((unsigned int)j ^ perm) << 8) + tid >= elems) v[j].x = v[j].y = v[j].z = v[j].w = 0.0;
+        }
+
+        double L0[4], L1[4], L2[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+          L0[j] = v[j].x * dgw[0] + v[j].y * dgw[3] + v[j].z * dgw[6] + v[j].w * dgw[9];
+          L1[j] = v[j].x * dgw[1] + v[j].y * dgw[4] + v[j].z * dgw[7] + v[j].w * dgw[10];
+          L2[j] = v[j].x * dgw[2] + v[j].y * dgw[5] + v[j].z * dgw[8] + v[j].w * dgw[11];
+        }
+        if (any_pinv && a.invariant)
+        {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+          {
+            const unsigned int el = (((unsigned int)j ^ perm) << 8) + tid;
+            if (el < elems)
+            {
+              const int inv = a.invariant[(e0 + el) >> 2];
+              if (inv >= 0) L0[j] += fr[inv] * pinv * wk;
+            }
+          }
+        }
+        L0[0] += __shfl_xor_sync(0xffffffffu, L0[2], 1);
+        L0[1] += __shfl_xor_sync(0xffffffffu, L0[3], 1);
+        L1[0] += __shfl_xor_sync(0xffffffffu, L1[2], 1);
+        L1[1] += __shfl_xor_sync(0xffffffffu, L1[3], 1);
+        L2[0] += __shfl_xor_sync(0xffffffffu, L2[2], 1);
+        L2[1] += __shfl_xor_sync(0xffffffffu, L2[3], 1);
+        L0[0] += __shfl_xor_sync(0xffffffffu, L0[1], 2);
+        L1[0] += __shfl_xor_sync(0xffffffffu, L1[1], 2);
+        L2[0] += __shfl_xor_sync(0xffffffffu, L2[1], 2);
+        if (actf)
+        {
+          const double inv = 1.0 / L0[0];
+          const double r1 = -L1[0] * inv;
+          acc1 += (double)wgt * r1;
+          acc2 += (double)wgt * (r1 * r1 - L2[0] * inv);
+        }
+      }
+      /* warp partial */
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1)
+      {
+        acc1 += __shfl_down_sync(0xffffffffu, acc1, off);
+        acc2 += __shfl_down_sync(0xffffffffu, acc2, off);
+      }
+      if (lane == 0)
+      {
+        sm.red[0][warp] = acc1;
+        sm.red[1][warp] = acc2;
+      }
+    }
+    used += nt;
+    __syncthreads();
+
+    /* CTA partial -> grid total (deterministic: fixed order in every CTA) */
+    double * buf = a.partials + (size_t)(iter & 1u) * 2 * G;
+    if (tid == 0)
+    {
+      double p1 = 0.0, p2 = 0.0;
+      for (int wi = 0; wi < NW_THREADS / 32; ++wi)
+      {
+        p1 += sm.red[0][wi];
+        p2 += sm.red[1][wi];
+      }
+      buf[b] = p1;
+      buf[G + b] = p2;
+    }
+    grid.sync();
+    if (warp == 0)
+    {
+      double t1 = 0.0, t2 = 0.0;
+      for (unsigned int q = lane; q < G; q += 32)
+      {
+        t1 += __ldcg(buf + q);
+        t2 += __ldcg(buf + G + q);
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1)
+      {
+        t1 += __shfl_down_sync(0xffffffffu, t1, off);
+        t2 += __shfl_down_sync(0xffffffffu, t2, off);
+      }
+      if (lane == 0)
+      {
+        sm.tot[0] = t1;
+        sm.tot[1] = t2;
+      }
+    }
+    __syncthreads();
+    f = a.scale * sm.tot[0];
+    df = a.scale * a.scale * sm.tot[1];
+
+    /* damped Newton step inside the shrinking bracket (opt_algorithms.c:187-252) */
+    if (!isfinite(f) || !isfinite(df))
+    {
+      status = NW_BAD_DERIV;
+      break;
+    }
+    double dx;
+    if (df > 0.0)
+    {
+      if (fabs(f) < a.tol) break;
+      if (f < 0.0)
+        xl = x;
+      else
+        xh = x;
+      dx = -f / df;
+    }
+    else
+      dx = -f / fabs(df);
+    dx = fmax(fmin(dx, dxmax), -dxmax);
+    if (x + dx < xl) dx = xl - x;
+    if (x + dx > xh) dx = xh - x;
+    if (fabs(dx) < a.tol) break;
+    x += dx;
+    x = fmax(fmin(x, a.xmax), a.xmin);
+  }
+
+  if (b == 0 && tid == 0)
+  {
+    a.result_dev[0] = x;
+    a.result_dev[1] = status;
+    a.result_dev[2] = (double)iter;
+    a.result_dev[3] = f;
+    a.result_host[0] = x;
+    a.result_host[1] = status;
+    a.result_host[2] = (double)iter;
+    a.result_host[3] = f;
+    __threadfence_system();
+  }
+}
+
 /* can the fused path serve this partition? */
 int g_opt_fused_newton = 1;
 
@@ -422,24 +706,31 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   a.result_host = c->h_result_dev + slot * 4;
 
   /* cooperative grid: never more CTAs than can be co-resident, never more than there is work */
-  static int per_sm[3] = {0, 0, 0};
-  const int dna = s == 4 ? (K == 4 ? 2 : 1) : 0;
-  const void * fn = dna == 2 ? (const void *)newton_kernel<2>
-                             : dna == 1 ? (const void *)newton_kernel<1> : (const void *)newton_kernel<0>;
-  if (!per_sm[dna])
+  static int per_sm[4] = {0, 0, 0, 0};
+  int mode = s == 4 ? (K == 4 ? 2 : 1) : 0;
+  if (mode == 2 && g_opt_fused_newton == 1) mode = 3; /* fused_newton=2 keeps the register version */
+  const void * fn = mode == 3   ? (const void *)newton_dna4_tma_kernel
+                    : mode == 2 ? (const void *)newton_kernel<2>
+                    : mode == 1 ? (const void *)newton_kernel<1>
+                                : (const void *)newton_kernel<0>;
+  const size_t dyn = mode == 3 ? sizeof(NewtonTmaSmem) + 128 : 0;
+  if (!per_sm[mode])
   {
+    if (dyn && cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn) != cudaSuccess)
+      return pllb200_cuda_ok(cudaGetLastError(), "newton kernel shared memory");
     int nb = 0;
-    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, NW_THREADS, 0);
-    per_sm[dna] = (e == cudaSuccess && nb > 0) ? nb : 1;
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, mode == 3 ? NT_THREADS : NW_THREADS, dyn);
+    per_sm[mode] = (e == cudaSuccess && nb > 0) ? nb : 1;
   }
   const unsigned long long E = (unsigned long long)a.sites * K;
-  unsigned long long blocks = (E + NW_THREADS - 1) / NW_THREADS;
-  unsigned long long cap = (unsigned long long)c->sm_count * std::min(per_sm[dna], 4);
+  unsigned long long blocks = mode == 3 ? (E + NT_TILE - 1) / NT_TILE : (E + NW_THREADS - 1) / NW_THREADS;
+  unsigned long long cap = (unsigned long long)c->sm_count * std::min(per_sm[mode], 4);
   if (cap > PLLB200_MAX_RED_BLOCKS * 3 / 4) cap = PLLB200_MAX_RED_BLOCKS * 3 / 4; /* partials: 2 buffers x 2 values */
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   void * kargs[] = {&a};
-  const cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3((unsigned)blocks), dim3(NW_THREADS), kargs, 0, c->stream);
+  const cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3((unsigned)blocks), dim3(mode == 3 ? NT_THREADS : NW_THREADS), kargs, dyn,
+                                                      c->stream);
   ++g_kernel_launches;
   return pllb200_cuda_ok(e, "newton kernel launch");
 }

@@ -62,41 +62,6 @@ struct TravArgs
 #define TRAV_WARPS 8
 #define TRAV_SEG(K) ((K) == 8 ? 128 : 256) /* DevOps staged per CTA at a time (<= 16 KB) */
 
-/* ---- mbarrier / TMA bulk copy (PTX ISA: cp.async.bulk, mbarrier) ------------------------------ */
-__device__ __forceinline__ unsigned int smem_u32(const void * p)
-{
-  return (unsigned int)__cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(unsigned long long * bar, unsigned int count)
-{
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long * bar, unsigned int bytes)
-{
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
-               : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long * bar, unsigned int parity)
-{
-  asm volatile(
-      "{\n\t.reg .pred p;\n\t"
-      "WAIT_%=:\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-      "@p bra DONE_%=;\n\t"
-      "bra WAIT_%=;\n\t"
-      "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gmem, unsigned int bytes,
-                                            unsigned long long * bar)
-{
-  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
-                   smem_u32(dst_smem)),
-               "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
-               : "memory");
-}
-
 /* 4-bit tip code -> 0.0/1.0 vector (hi word of 1.0 is 0x3FF00000) */
 __device__ __forceinline__ d4 tip_vector(unsigned int code)
 {
