@@ -29,6 +29,7 @@
 #define PLLB200_H_
 
 #include <stddef.h>
+#include <stdio.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -83,6 +84,9 @@ extern "C" {
 #define PLL_GAMMA_RATES_MEDIAN 1
 
 /* ---- error codes (L:162-196) -------------------------------------------------------------- */
+#define PLL_ERROR_FILE_OPEN 100
+#define PLL_ERROR_FILE_SEEK 101
+#define PLL_ERROR_FILE_EOF 102
 #define PLL_ERROR_MEM_ALLOC 112
 #define PLL_ERROR_PARAM_INVALID 113
 #define PLL_ERROR_TIPDATA_ILLEGALSTATE 114
@@ -290,6 +294,8 @@ int pll_compute_gamma_cats(double alpha, unsigned int categories, double * outpu
 /* ---- libpll utree subset the treeinfo/optimize drivers need -------------------------------- */
 /* L:1010-1011 (parse_utree.y:99-145) */
 void pll_utree_destroy(pll_utree_t * tree, void (*cb_destroy)(void *));
+/* L:927 (parse_utree.y:99) */
+void pll_utree_graph_destroy(pll_unode_t * root, void (*cb_destroy)(void *));
 /* L:1020-1021 (parse_utree.y:522) */
 pll_utree_t * pll_utree_wraptree(pll_unode_t * root, unsigned int tip_count);
 /* L:929-933 (utree.c:427) */
@@ -774,6 +780,91 @@ double pllmod_opt_compute_edge_loglikelihood_multi(
     unsigned int matrix_index, unsigned int ** const params_indices, double * persite_lnl,
     void * parallel_context, void (*parallel_reduce_cb)(void *, double *, size_t, int));
 
+/* ---- pll-modules binary checkpoint I/O (src/binary/pll_binary.h:29-181) ----------------------
+ * Same on-disk format as the reference (headers, block map, partition / CLV / tree / custom blocks), so
+ * checkpoints written by either library load in the other.  CLVs, scalers and P-matrices are streamed
+ * between the file and HBM; there is no host copy to keep in sync.  Site-repeat blocks are accepted
+ * as no-ops exactly like the reference does for partitions without PLL_ATTRIB_SITE_REPEATS. */
+#define PLLMOD_BIN_BLOCK_PARTITION 0
+#define PLLMOD_BIN_BLOCK_CLV 1
+#define PLLMOD_BIN_BLOCK_TREE 2
+#define PLLMOD_BIN_BLOCK_CUSTOM 3
+#define PLLMOD_BIN_BLOCK_REPEATS 4
+#define PLLMOD_BIN_ACCESS_SEQUENTIAL 0
+#define PLLMOD_BIN_ACCESS_RANDOM 1
+#define PLLMOD_BIN_ACCESS_SEEK -1
+#define PLLMOD_BIN_INVALID_OFFSET -1
+#define PLLMOD_BIN_ATTRIB_UPDATE_MAP (1 << 0)
+#define PLLMOD_BIN_ATTRIB_PARTITION_DUMP_CLV (1 << 1)
+#define PLLMOD_BIN_ATTRIB_PARTITION_DUMP_WGT (1 << 2)
+#define PLLMOD_BIN_ATTRIB_ALIGNED (1 << 3)
+#define PLLMOD_BIN_ATTRIB_PARTITION_LOAD_SKELETON (1 << 4)
+#define PLLMOD_BIN_ERROR_BLOCK_MISMATCH 4001
+#define PLLMOD_BIN_ERROR_BLOCK_LENGTH 4002
+#define PLLMOD_BIN_ERROR_BINARY_IO 4003
+#define PLLMOD_BIN_ERROR_INVALID_INDEX 4010
+#define PLLMOD_BIN_ERROR_INVALID_SIZE 4011
+#define PLLMOD_BIN_ERROR_LOADSTORE 4012
+#define PLLMOD_BIN_ERROR_MISSING_BLOCK 4020
+
+/* pll_binary.h:63-71 */
+typedef struct
+{
+  unsigned int n_blocks;
+  unsigned int max_blocks;
+  unsigned int access_type;
+  char pad[4];
+  long map_offset;
+} pll_binary_header_t;
+/* pll_binary.h:74-78 */
+typedef struct
+{
+  long block_id;
+  long block_offset;
+} pll_block_map_t;
+/* pll_binary.h:87-95 */
+typedef struct
+{
+  long block_id;
+  unsigned int type;
+  unsigned int attributes;
+  unsigned int alignment;
+  char pad[4];
+  size_t block_len;
+} pll_block_header_t;
+
+/* pll_binary.h:97-181 */
+FILE * pllmod_binary_create(const char * filename, pll_binary_header_t * header, unsigned int access_type,
+                            unsigned int n_blocks);
+FILE * pllmod_binary_open(const char * filename, pll_binary_header_t * header);
+FILE * pllmod_binary_append_open(const char * filename, pll_binary_header_t * header);
+int pllmod_binary_close(FILE * bin_file);
+pll_block_map_t * pllmod_binary_get_map(FILE * bin_file, unsigned int * n_blocks);
+int pllmod_binary_partition_dump(FILE * bin_file, int block_id, pll_partition_t * partition,
+                                 unsigned int attributes);
+pll_partition_t * pllmod_binary_partition_load(FILE * bin_file, int block_id, pll_partition_t * partition,
+                                               unsigned int * attributes, long int offset);
+int pllmod_binary_repeats_dump(FILE * bin_file, int block_id, pll_partition_t * partition,
+                               unsigned int attributes);
+int pllmod_binary_repeats_load(FILE * bin_file, int block_id, pll_partition_t * partition,
+                               unsigned int * attributes, long int offset);
+int pllmod_binary_pernoderepeats_dump(FILE * bin_file, int block_id, pll_partition_t * partition,
+                                      unsigned int clv_index, unsigned int attributes);
+int pllmod_binary_pernoderepeats_load(FILE * bin_file, int block_id, pll_partition_t * partition,
+                                      unsigned int clv_index, unsigned int * attributes, long int offset);
+int pllmod_binary_clv_dump(FILE * bin_file, int block_id, pll_partition_t * partition,
+                           unsigned int clv_index, unsigned int attributes);
+int pllmod_binary_clv_load(FILE * bin_file, int block_id, pll_partition_t * partition,
+                           unsigned int clv_index, unsigned int * attributes, long int offset);
+int pllmod_binary_utree_dump(FILE * bin_file, int block_id, pll_unode_t * tree, unsigned int tip_count,
+                             unsigned int attributes);
+pll_unode_t * pllmod_binary_utree_load(FILE * bin_file, int block_id, unsigned int * attributes,
+                                       long int offset);
+int pllmod_binary_custom_dump(FILE * bin_file, int block_id, void * data, size_t size,
+                              unsigned int attributes);
+void * pllmod_binary_custom_load(FILE * bin_file, int block_id, size_t * size, unsigned int * type,
+                                 unsigned int * attributes, long int offset);
+
 /* ---- additive device-side API (pllb200_*) ------------------------------------------------- */
 
 /* Number of usable CUDA devices (0 when the driver/GPU is absent). Never fails. */
@@ -791,6 +882,11 @@ int pllb200_download_clv(pll_partition_t * partition, unsigned int clv_index, do
 int pllb200_upload_clv(pll_partition_t * partition, unsigned int clv_index, const double * src);
 int pllb200_download_scaler(pll_partition_t * partition, unsigned int scaler_index, unsigned int * dst);
 int pllb200_download_pmatrix(pll_partition_t * partition, unsigned int matrix_index, double * dst);
+/* All P-matrices at once, reference layout [prob_matrices][rate_cats][states][states_padded]; the upload
+ * also rebuilds the kernels' interleaved copies. */
+int pllb200_download_pmatrices(pll_partition_t * partition, double * dst);
+int pllb200_upload_pmatrices(pll_partition_t * partition, const double * src);
+int pllb200_upload_scaler(pll_partition_t * partition, unsigned int scaler_index, const unsigned int * src);
 int pllb200_download_sumtable(pll_partition_t * partition, const double * sumtable_key, double * dst);
 /* Re-mirror host arrays a caller modified in place (pattern_weights / invariant / tipchars). */
 int pllb200_sync_host_arrays(pll_partition_t * partition);

@@ -13,7 +13,7 @@ if [ ! -d "$REF/libs/libpll/src" ]; then
 fi
 mkdir -p "$O/obj"
 S=$REF/libs/libpll/src ; M=$REF/src
-BASE="-O3 -fPIC -D_GNU_SOURCE -DHAVE_SSE3 -DHAVE_AVX -DHAVE_AVX2 -DHAVE_X86INTRIN_H -I$S -I$M -I$M/tree -I$M/optimize -I$M/algorithm -I$M/util -I$M/msa -w"
+BASE="-O3 -fPIC -D_GNU_SOURCE -DHAVE_SSE3 -DHAVE_AVX -DHAVE_AVX2 -DHAVE_X86INTRIN_H -I$S -I$M -I$M/tree -I$M/optimize -I$M/algorithm -I$M/util -I$M/msa -I$M/binary -w"
 cd "$O/obj"
 pids=()
 cc() { gcc $BASE "$@" & pids+=($!); if [ ${#pids[@]} -ge 8 ]; then wait ${pids[0]}; pids=("${pids[@]:1}"); fi; }
@@ -32,7 +32,7 @@ for f in tree/treeinfo tree/pll_tree tree/utree_operations tree/utree_distances 
          optimize/opt_algorithms optimize/lbfgsb/lbfgsb optimize/lbfgsb/linesearch optimize/lbfgsb/linpack \
          optimize/lbfgsb/miniCBLAS optimize/lbfgsb/subalgorithms pllmod_common algorithm/pllmod_algorithm \
          algorithm/algo_search algorithm/algo_callback util/models util/models_dna util/models_aa \
-         util/models_gt util/models_mult msa/pll_msa; do cc -c $M/$f.c -o m_$(echo $f | tr / _).o; done
+         util/models_gt util/models_mult msa/pll_msa binary/pll_binary binary/binary_io_operations; do cc -c $M/$f.c -o m_$(echo $f | tr / _).o; done
 printf 'void*pll_utree_parse_newick_string(const char*s){return 0;}\nvoid*pll_utree_split_newick_string(char*s,unsigned t,void*h){return 0;}\n' > stubs.c
 cc -c stubs.c -o l_stubs.o
 wait
@@ -40,7 +40,7 @@ wait
 gcc -shared -Wl,-Bsymbolic -o "$O/libpll_ref.so" l_*.o m_*.o -lm
 # the same-source harness (oracle/harness.c) compiled against the reference headers + library
 if [ -f "$HERE/harness.c" ]; then
-  gcc -O2 -fPIC -shared -Wl,-Bsymbolic -DHARNESS_REFERENCE -I$S -I$M -I$M/tree -I$M/optimize -I$M/algorithm -I$M/util -I$M/msa -w \
+  gcc -O2 -fPIC -shared -Wl,-Bsymbolic -DHARNESS_REFERENCE -I$S -I$M -I$M/tree -I$M/optimize -I$M/algorithm -I$M/util -I$M/msa -I$M/binary -w \
       "$HERE/harness.c" -o "$O/libharness_ref.so" -L"$O" -l:libpll_ref.so -Wl,-rpath,'$ORIGIN' -lm
 fi
 echo "build_ref: ok -> $O/libpll_ref.so"

@@ -873,9 +873,7 @@ void h_get_model(void * hv, unsigned int p, double * out)
 }
 
 /* ---- SPR round (BASELINE configs[4]) -------------------------------------- */
-#ifdef HARNESS_REFERENCE
 #include "pllmod_algorithm.h"
-#endif
 
 double h_spr_round(void * hv, unsigned int radius_min, unsigned int radius_max, unsigned int ntopol_keep,
                    int thorough, int blo_method, double bl_min, double bl_max, int smoothings,
@@ -985,4 +983,161 @@ void h_get_treeinfo_params(void * hv, double * out)
     out[p] = h->ti->alphas[p];
     out[h->nparts + p] = h->ti->brlen_scalers ? h->ti->brlen_scalers[p] : 1.0;
   }
+}
+
+/* ---- binary checkpoint I/O (src/binary/pll_binary.h) ----------------------- */
+#include "pll_binary.h"
+
+#define H_BIN_PARTITION 10
+#define H_BIN_TREE 11
+#define H_BIN_CUSTOM 12
+#define H_BIN_CLV 13
+
+/* partition 0 (with CLVs, scalers, P-matrices, weights), the tree, the branch lengths as a custom
+ * block and the root CLV as a block of its own, in a random-access file */
+int h_binary_dump(void * hv, const char * path)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_binary_header_t hd;
+  FILE * f = pllmod_binary_create(path, &hd, PLLMOD_BIN_ACCESS_RANDOM, 8);
+  if (!f) return 0;
+  pll_unode_t * root = h->ti->root;
+  const unsigned int nbr = 2 * h->tips - 3;
+  int ok = pllmod_binary_partition_dump(f, H_BIN_PARTITION, h->parts[0],
+                                        PLLMOD_BIN_ATTRIB_UPDATE_MAP | PLLMOD_BIN_ATTRIB_PARTITION_DUMP_CLV |
+                                            PLLMOD_BIN_ATTRIB_PARTITION_DUMP_WGT);
+  ok = ok && pllmod_binary_utree_dump(f, H_BIN_TREE, root, h->tips, PLLMOD_BIN_ATTRIB_UPDATE_MAP);
+  ok = ok && pllmod_binary_custom_dump(f, H_BIN_CUSTOM, h->ti->branch_lengths[0], sizeof(double) * nbr,
+                                       PLLMOD_BIN_ATTRIB_UPDATE_MAP);
+  ok = ok && pllmod_binary_clv_dump(f, H_BIN_CLV, h->parts[0], root->clv_index, PLLMOD_BIN_ATTRIB_UPDATE_MAP);
+  pllmod_binary_close(f);
+  return ok;
+}
+
+static double tree_length_rec(const pll_unode_t * n, unsigned int * tips)
+{
+  if (!n->next)
+  {
+    ++*tips;
+    return 0.0;
+  }
+  return n->next->length + tree_length_rec(n->next->back, tips) + n->next->next->length +
+         tree_length_rec(n->next->next->back, tips);
+}
+
+/* Open a file written by h_binary_dump (of either library) and use what is in it WITHOUT recomputing
+ * anything: out[0] = edge logL at the stored root from the loaded CLVs / scalers / P-matrices / weights,
+ * out[1] = the same after the root CLV was loaded again from its own block, out[2] = tips of the loaded
+ * tree, out[3] = its total branch length, out[4] = sum of the custom block's doubles, out[5] = blocks in
+ * the map, out[6] = attributes stored with the partition block.  Returns 1 on success. */
+int h_binary_load(const char * path, double * out)
+{
+  pll_binary_header_t hd;
+  FILE * f = pllmod_binary_open(path, &hd);
+  if (!f) return 0;
+  int ok = 0;
+  unsigned int attr = 0, tattr = 0, cattr = 0, ctype = 0, vattr = 0, nblocks = 0;
+  size_t csize = 0;
+  pll_partition_t * part = NULL;
+  pll_unode_t * root = NULL;
+  double * custom = NULL;
+  pll_block_map_t * map = pllmod_binary_get_map(f, &nblocks);
+  part = pllmod_binary_partition_load(f, H_BIN_PARTITION, NULL, &attr, PLLMOD_BIN_ACCESS_SEEK);
+  if (part) root = pllmod_binary_utree_load(f, H_BIN_TREE, &tattr, PLLMOD_BIN_ACCESS_SEEK);
+  if (root) custom = (double *)pllmod_binary_custom_load(f, H_BIN_CUSTOM, &csize, &ctype, &cattr, PLLMOD_BIN_ACCESS_SEEK);
+  if (custom && ctype == PLLMOD_BIN_BLOCK_CUSTOM)
+  {
+    unsigned int * pidx = (unsigned int *)calloc(part->rate_cats, sizeof(unsigned int));
+    out[0] = pll_compute_edge_loglikelihood(part, root->clv_index, root->scaler_index, root->back->clv_index,
+                                            root->back->scaler_index, root->pmatrix_index, pidx, NULL);
+    ok = pllmod_binary_clv_load(f, H_BIN_CLV, part, root->clv_index, &vattr, PLLMOD_BIN_ACCESS_SEEK);
+    out[1] = pll_compute_edge_loglikelihood(part, root->clv_index, root->scaler_index, root->back->clv_index,
+                                            root->back->scaler_index, root->pmatrix_index, pidx, NULL);
+    unsigned int tips = 0;
+    out[3] = root->length + tree_length_rec(root, &tips) + tree_length_rec(root->back, &tips);
+    out[2] = tips;
+    out[4] = 0.0;
+    for (size_t i = 0; i < csize / sizeof(double); ++i) out[4] += custom[i];
+    out[5] = nblocks;
+    out[6] = attr;
+    free(pidx);
+  }
+  free(custom);
+  free(map);
+  if (root) pll_utree_graph_destroy(root, NULL);
+  if (part) pll_partition_destroy(part);
+  pllmod_binary_close(f);
+  return ok;
+}
+
+/* tree + custom blocks only (no partition, so no device): sequential file.  h_binary_tree_load returns
+ * tips, total length, label checksum and the custom payload sum in out[0..3]. */
+int h_binary_tree_dump(const char * path, unsigned int tips, unsigned int seed)
+{
+  char ** names = (char **)malloc(sizeof(char *) * tips);
+  for (unsigned int i = 0; i < tips; ++i)
+  {
+    names[i] = (char *)malloc(24);
+    snprintf(names[i], 24, "taxon_%u_%u", i, (i * 2654435761u) % 97u);
+  }
+  pll_utree_t * t = pllmod_utree_create_random(tips, (const char * const *)names, seed);
+  for (unsigned int i = 0; i < tips; ++i) free(names[i]);
+  free(names);
+  if (!t) return 0;
+  unsigned long long s = 88172645463325252ull + seed;
+  for (unsigned int i = 0; i < t->tip_count + 3 * t->inner_count; ++i)
+  {
+    pll_unode_t * n = t->nodes[i < t->tip_count ? i : t->tip_count + (i - t->tip_count) / 3];
+    if (i >= t->tip_count)
+      for (unsigned int r = 0; r < (i - t->tip_count) % 3; ++r) n = n->next;
+    if (n->node_index < n->back->node_index) n->length = n->back->length = 0.001 + u01(&s);
+  }
+  pll_binary_header_t hd;
+  FILE * f = pllmod_binary_create(path, &hd, PLLMOD_BIN_ACCESS_SEQUENTIAL, 0);
+  if (!f) return 0;
+  double payload[5] = {1.5, -2.25, 3.0, (double)tips, (double)seed};
+  int ok = pllmod_binary_custom_dump(f, 1, payload, sizeof(payload), 0);
+  ok = ok && pllmod_binary_utree_dump(f, 2, t->vroot, tips, 0);
+  pllmod_binary_close(f);
+  pll_utree_destroy(t, NULL);
+  return ok;
+}
+
+static void label_sum_rec(const pll_unode_t * n, double * acc)
+{
+  if (!n->next)
+  {
+    if (n->label)
+      for (const char * c = n->label; *c; ++c) *acc += (double)(unsigned char)*c * (1 + n->node_index % 7);
+    return;
+  }
+  label_sum_rec(n->next->back, acc);
+  label_sum_rec(n->next->next->back, acc);
+}
+
+int h_binary_tree_load(const char * path, double * out)
+{
+  pll_binary_header_t hd;
+  FILE * f = pllmod_binary_open(path, &hd);
+  if (!f) return 0;
+  size_t csize = 0;
+  unsigned int ctype = 0, cattr = 0, tattr = 0, tips = 0;
+  double * custom = (double *)pllmod_binary_custom_load(f, 1, &csize, &ctype, &cattr, 0);
+  pll_unode_t * root = custom ? pllmod_binary_utree_load(f, 2, &tattr, 0) : NULL;
+  int ok = root != NULL;
+  if (ok)
+  {
+    out[1] = root->length + tree_length_rec(root, &tips) + tree_length_rec(root->back, &tips);
+    out[0] = tips;
+    out[2] = 0.0;
+    label_sum_rec(root, &out[2]);
+    label_sum_rec(root->back, &out[2]);
+    out[3] = 0.0;
+    for (size_t i = 0; i < csize / sizeof(double); ++i) out[3] += custom[i];
+    out[4] = hd.n_blocks;
+    pll_utree_graph_destroy(root, NULL);
+  }
+  free(custom);
+  pllmod_binary_close(f);
+  return ok;
 }

@@ -427,6 +427,38 @@ extern "C" int pllb200_download_pmatrix(pll_partition_t * p, unsigned int matrix
   return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
 }
 
+extern "C" int pllb200_download_pmatrices(pll_partition_t * p, double * dst)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  const size_t bytes = sizeof(double) * c->pmat_elems * p->prob_matrices;
+  CUDA_TRY(cudaMemcpyAsync(dst, c->d_pmat, bytes, cudaMemcpyDeviceToHost, c->stream), PLL_FAILURE);
+  g_d2h_bytes += bytes;
+  return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_upload_pmatrices(pll_partition_t * p, const double * src)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (!upload_big(c, c->d_pmat, src, sizeof(double) * c->pmat_elems * p->prob_matrices)) return PLL_FAILURE;
+  return launch_pmatrix_reinterleave(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_upload_scaler(pll_partition_t * p, unsigned int scaler_index, const unsigned int * src)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (scaler_index >= p->scale_buffers)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid scaler index %u.", scaler_index);
+    return PLL_FAILURE;
+  }
+  return upload_big(c, scaler_dev(c, (int)scaler_index), src, sizeof(unsigned int) * c->scaler_elems)
+             ? PLL_SUCCESS
+             : PLL_FAILURE;
+}
+
 extern "C" int pllb200_download_sumtable(pll_partition_t * p, const double * key, double * dst)
 {
   if (!check_ctx(p)) return PLL_FAILURE;

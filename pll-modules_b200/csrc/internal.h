@@ -150,6 +150,7 @@ static inline bool is_tip_pattern(const PartCtx * c, unsigned int clv_index)
 bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
                     const unsigned int * matrix_indices, const double * branch_lengths,
                     unsigned int count);
+bool launch_pmatrix_reinterleave(PartCtx * c);
 bool launch_partials(PartCtx * c, const pll_operation_t * ops, unsigned int count);
 bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int count); /* k_traversal_dna.cu */
 bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count);  /* k_traversal_aa.cu */

@@ -80,6 +80,37 @@ __global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__
   }
 }
 
+/* rebuild the interleaved copies from the plain array (after P-matrices were uploaded from a
+ * checkpoint, binary_io.cpp): same index maps as pmatrix_kernel */
+__global__ void pmatrix_reinterleave_kernel(const double * __restrict__ pmat, double * __restrict__ pmat_il,
+                                            unsigned int states, unsigned int sp, unsigned int K)
+{
+  const unsigned int m = blockIdx.x / K, k = blockIdx.x % K;
+  const double * in = pmat + ((size_t)m * K + k) * states * sp;
+  for (unsigned int idx = threadIdx.x; idx < states * sp; idx += blockDim.x)
+  {
+    const unsigned int i = idx / sp, j = idx % sp;
+    const double v = in[idx];
+    if (states == 4)
+      pmat_il[(size_t)m * K * 16 + (i * K + k) * 4 + j] = v;
+    else if (states == 20)
+    {
+      const unsigned int nt = i >> 3, ks = j >> 2, lane = ((i & 7u) << 2) | (j & 3u);
+      pmat_il[(((size_t)m * K + k) * 3 + nt) * 160 + ks * 32 + lane] = v;
+    }
+  }
+}
+
+bool launch_pmatrix_reinterleave(PartCtx * c)
+{
+  pll_partition_t * p = &c->pub;
+  if (!c->d_pmat_il || !p->prob_matrices || (p->states != 4 && p->states != 20)) return true;
+  pmatrix_reinterleave_kernel<<<p->prob_matrices * p->rate_cats, 128, 0, c->stream>>>(
+      c->d_pmat, c->d_pmat_il, p->states, p->states_padded, p->rate_cats);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "pmatrix_reinterleave_kernel launch");
+}
+
 bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
                     const unsigned int * matrix_indices, const double * branch_lengths,
                     unsigned int count)

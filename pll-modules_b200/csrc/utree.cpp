@@ -3,7 +3,8 @@
  * Host pointer surgery only (no likelihood arithmetic).  Reference behaviour:
  *   pll_utree_wraptree          libs/libpll/src/parse_utree.y:436-535 (node order: tips first, then
  *                               inner nodes, both in a depth-first walk from the root)
- *   pll_utree_destroy           parse_utree.y:99-145
+ *   pll_utree_destroy           parse_utree.y:107-145
+ *   pll_utree_graph_destroy     parse_utree.y:68-105
  *   pll_utree_traverse          libs/libpll/src/utree.c:394-459 (root->back subtree first, then root)
  *   pll_utree_create_operations utree.c:317-366
  *   pllmod_utree_create_random  src/tree/pll_tree.c:903-980 (random branch insertion)
@@ -114,6 +115,34 @@ extern "C" void pll_utree_destroy(pll_utree_t * tree, void (*cb_destroy)(void *)
   }
   free(tree->nodes);
   free(tree);
+}
+
+/* Free a node graph that has no pll_utree_t wrapper (parse_utree.y:68-105): everything reachable
+ * from `root`, both sides of its edge.  The records of an inner node share one label. */
+static void free_subtree(pll_unode_t * entry, bool also_behind_entry, void (*cb_destroy)(void *))
+{
+  if (!entry->next)
+  {
+    if (cb_destroy && entry->data) cb_destroy(entry->data);
+    free(entry->label);
+    free(entry);
+    return;
+  }
+  free(entry->label);
+  pll_unode_t * n = entry;
+  do
+  {
+    pll_unode_t * nx = n->next;
+    if ((n != entry || also_behind_entry) && n->back) free_subtree(n->back, false, cb_destroy);
+    if (cb_destroy && n->data) cb_destroy(n->data);
+    free(n);
+    n = nx;
+  } while (n && n != entry);
+}
+
+extern "C" void pll_utree_graph_destroy(pll_unode_t * root, void (*cb_destroy)(void *))
+{
+  if (root) free_subtree(root, true, cb_destroy);
 }
 
 static void traverse_rec(pll_unode_t * node, int traversal, int (*cb)(pll_unode_t *),

@@ -133,6 +133,10 @@ def _lib(kind):
                                     C.c_double, C.c_int, C.c_double, C.c_int, C.c_double, C.c_double, C.c_int,
                                     C.c_void_p]
         lib.h_topology_signature.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.h_binary_dump.argtypes = [C.c_void_p, C.c_char_p]
+        lib.h_binary_load.argtypes = [C.c_char_p, C.c_void_p]
+        lib.h_binary_tree_dump.argtypes = [C.c_char_p, C.c_uint, C.c_uint]
+        lib.h_binary_tree_load.argtypes = [C.c_char_p, C.c_void_p]
         _libs[kind] = lib
     return _libs[kind]
 
@@ -188,6 +192,25 @@ def test_em(kind, base, site_w, w0):
     w = np.ascontiguousarray(w0, dtype=np.float64).copy()
     _lib(kind).h_test_em(base.shape[0], base.shape[1], base.ctypes.data, sw.ctypes.data, w.ctypes.data)
     return w
+
+
+def binary_tree_dump(kind, path, tips, seed):
+    """tree + custom block into a sequential pll-modules binary file (no partition, no device)."""
+    assert _lib(kind).h_binary_tree_dump(str(path).encode(), tips, seed)
+
+
+def binary_tree_load(kind, path):
+    out = np.zeros(5)
+    assert _lib(kind).h_binary_tree_load(str(path).encode(), out.ctypes.data)
+    return dict(tips=int(out[0]), length=out[1], label_sum=out[2], custom_sum=out[3], blocks=int(out[4]))
+
+
+def binary_load(kind, path):
+    """Load a checkpoint written by Harness.binary_dump (either library) and evaluate it as stored."""
+    out = np.zeros(7)
+    assert _lib(kind).h_binary_load(str(path).encode(), out.ctypes.data)
+    return dict(loglh=out[0], loglh_after_clv_block=out[1], tips=int(out[2]), length=out[3],
+                custom_sum=out[4], blocks=int(out[5]), attributes=int(out[6]))
 
 
 class Harness:
@@ -351,6 +374,10 @@ class Harness:
     def algo_opt_treeinfo(self, what, tolerance=1e-3):
         """pllmod_algo_opt_*_treeinfo over all partitions; returns -logL."""
         return self.lib.h_algo_opt_treeinfo(self.h, self.ALGO_OPT[what], tolerance)
+
+    def binary_dump(self, path):
+        """partition 0 + tree + branch lengths + root CLV as blocks 10..13 of a random-access file"""
+        assert self.lib.h_binary_dump(self.h, str(path).encode())
 
     def treeinfo_params(self):
         out = np.zeros(2 * self.nparts)

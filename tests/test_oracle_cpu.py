@@ -260,3 +260,27 @@ def test_lbfgsb_multi_and_em():
     sw = rng.randint(1, 4, 200)
     w = PH.test_em("b200", base, sw, [0.25] * 4)
     np.testing.assert_allclose(w, OPT_GOLD["em"]["w"], rtol=1e-12)
+
+
+@pytest.mark.skipif(not have_reference(), reason="oracle/_ref not built")
+def test_binary_tree_and_custom_blocks_cross_load(tmp_path):
+    """pll-modules binary format (src/binary/pll_binary.c): a tree + custom block written by either library
+    loads in the other with the same topology size, branch lengths, labels and payload."""
+    import os
+    from pllharness import binary_tree_dump, binary_tree_load
+    for tips, seed in ((5, 1), (40, 7), (333, 3)):
+        got = {}
+        for writer in ("ref", "b200"):
+            path = tmp_path / ("tree_%s_%d.bin" % (writer, tips))
+            binary_tree_dump(writer, path, tips, seed)
+            for reader in ("ref", "b200"):
+                got[writer, reader] = binary_tree_load(reader, path)
+        sizes = {w: os.path.getsize(tmp_path / ("tree_%s_%d.bin" % (w, tips))) for w in ("ref", "b200")}
+        assert sizes["ref"] == sizes["b200"]
+        base = got["ref", "ref"]
+        assert base["tips"] == tips and base["blocks"] == 2 and base["label_sum"] > 0
+        for k, v in got.items():
+            assert v["tips"] == tips and v["blocks"] == 2, k
+            assert abs(v["length"] - base["length"]) < 1e-12, k
+            assert v["label_sum"] == base["label_sum"], k
+            assert v["custom_sum"] == base["custom_sum"], k
