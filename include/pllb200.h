@@ -272,6 +272,17 @@ double pll_compute_edge_loglikelihood(pll_partition_t * partition,
                                       unsigned int matrix_index,
                                       const unsigned int * freqs_indices,
                                       double * persite_lnl);
+/* L:799-818 (likelihood.c:639-823): marginal ancestral state probabilities of an inner node,
+ * ancestral[site][state], normalised per site; the _extbuf scratch arguments are ignored */
+int pll_compute_node_ancestral(pll_partition_t * partition, unsigned int node_clv_index,
+                               int node_scaler_index, unsigned int other_clv_index, int other_scaler_index,
+                               unsigned int matrix_index, const unsigned int * freqs_indices,
+                               double * ancestral);
+int pll_compute_node_ancestral_extbuf(pll_partition_t * partition, unsigned int node_clv_index,
+                                      int node_scaler_index, unsigned int other_clv_index,
+                                      int other_scaler_index, unsigned int pmatrix_index,
+                                      const unsigned int * freqs_indices, double * ancestral,
+                                      double * temp_clv, unsigned int * temp_scaler, double * ident_pmat);
 /* L:823-825 (partials.c:237) — asynchronous on the partition's stream */
 void pll_update_partials(pll_partition_t * partition, const pll_operation_t * operations,
                          unsigned int count);
@@ -296,6 +307,9 @@ int pll_compute_gamma_cats(double alpha, unsigned int categories, double * outpu
 void pll_utree_destroy(pll_utree_t * tree, void (*cb_destroy)(void *));
 /* L:927 (parse_utree.y:99) */
 void pll_utree_graph_destroy(pll_unode_t * root, void (*cb_destroy)(void *));
+/* L:943-945 (utree.c:605-633) */
+pll_unode_t * pll_utree_graph_clone(const pll_unode_t * root);
+pll_utree_t * pll_utree_clone(const pll_utree_t * tree);
 /* L:1020-1021 (parse_utree.y:522) */
 pll_utree_t * pll_utree_wraptree(pll_unode_t * root, unsigned int tip_count);
 /* L:929-933 (utree.c:427) */
@@ -431,6 +445,18 @@ double pllmod_treeinfo_compute_loglh_flex(pllmod_treeinfo_t * treeinfo, int incr
                                           int update_pmatrices);
 double pllmod_treeinfo_compute_loglh_persite(pllmod_treeinfo_t * treeinfo, int incremental,
                                              double ** persite_lnl);
+/* T:279-289, 788-790 (treeinfo.c:1558-1712) */
+typedef struct
+{
+  unsigned int node_count;
+  pll_unode_t ** nodes;
+  unsigned int partition_count;
+  unsigned int * partition_indices;
+  pll_utree_t * tree;
+  double ** probs;
+} pllmod_ancestral_t;
+pllmod_ancestral_t * pllmod_treeinfo_compute_ancestral(pllmod_treeinfo_t * treeinfo);
+void pllmod_treeinfo_destroy_ancestral(pllmod_ancestral_t * ancestral);
 int pllmod_treeinfo_scale_branches_all(pllmod_treeinfo_t * treeinfo, double scaler);
 int pllmod_treeinfo_scale_branches_partition(pllmod_treeinfo_t * treeinfo,
                                              unsigned int partition_idx, double scaler);

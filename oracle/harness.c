@@ -1141,3 +1141,27 @@ int h_binary_tree_load(const char * path, double * out)
   pllmod_binary_close(f);
   return ok;
 }
+
+/* ---- marginal ancestral states (treeinfo.c:1611-1712) ----------------------- */
+
+/* out: node_count * sum_p(sites_p * states_p) doubles, nodes in the order of the result; labels_sum gets a
+ * checksum of the generated node labels.  Returns the node count (0 on failure). */
+unsigned int h_ancestral(void * hv, double * out, double * labels_sum)
+{
+  harness_t * h = (harness_t *)hv;
+  pllmod_ancestral_t * a = pllmod_treeinfo_compute_ancestral(h->ti);
+  if (!a) return 0;
+  size_t span = 0;
+  for (unsigned int p = 0; p < h->nparts; ++p) span += (size_t)h->parts[p]->sites * h->parts[p]->states;
+  *labels_sum = 0.0;
+  /* results are keyed by clv_index so that both libraries report the nodes in one order */
+  for (unsigned int i = 0; i < a->node_count; ++i)
+  {
+    const unsigned int slot = a->nodes[i]->clv_index - h->tips;
+    memcpy(out + (size_t)slot * span, a->probs[i], sizeof(double) * span);
+    for (const char * c = a->nodes[i]->label; c && *c; ++c) *labels_sum += (double)(unsigned char)*c * (1 + slot % 5);
+  }
+  const unsigned int n = a->node_count;
+  pllmod_treeinfo_destroy_ancestral(a);
+  return n;
+}

@@ -89,6 +89,47 @@ extern "C" double pll_compute_edge_loglikelihood(pll_partition_t * partition,
   return finish_scalar(c, slot, persite_lnl, d_ps);
 }
 
+/* likelihood.c:639-823: marginal ancestral state probabilities of an inner node, [site][state] */
+extern "C" int pll_compute_node_ancestral(pll_partition_t * partition, unsigned int node_clv_index,
+                                          int node_scaler_index, unsigned int other_clv_index,
+                                          int other_scaler_index, unsigned int matrix_index,
+                                          const unsigned int * freqs_indices, double * ancestral)
+{
+  if (!enter(partition)) return PLL_FAILURE;
+  if (!ancestral)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Parameter value is NULL!");
+    return PLL_FAILURE;
+  }
+  PartCtx * c = ctx_of(partition);
+  const size_t bytes = sizeof(double) * partition->sites * partition->states;
+  if (!c->d_ancestral && !pllb200_cuda_ok(cudaMalloc(&c->d_ancestral, bytes), "ancestral buffer"))
+    return PLL_FAILURE;
+  if (!launch_ancestral(c, node_clv_index, node_scaler_index, other_clv_index, other_scaler_index,
+                        matrix_index, freqs_indices, c->d_ancestral))
+    return PLL_FAILURE;
+  if (!pllb200_cuda_ok(cudaMemcpyAsync(ancestral, c->d_ancestral, bytes, cudaMemcpyDeviceToHost, c->stream),
+                       "ancestral D2H"))
+    return PLL_FAILURE;
+  g_d2h_bytes += bytes;
+  return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+/* the caller's scratch buffers (temporary CLV, scaler, identity matrix) are not needed on the device */
+extern "C" int pll_compute_node_ancestral_extbuf(pll_partition_t * partition, unsigned int node_clv_index,
+                                                 int node_scaler_index, unsigned int other_clv_index,
+                                                 int other_scaler_index, unsigned int pmatrix_index,
+                                                 const unsigned int * freqs_indices, double * ancestral,
+                                                 double * temp_clv, unsigned int * temp_scaler,
+                                                 double * ident_pmat)
+{
+  (void)temp_clv;
+  (void)temp_scaler;
+  (void)ident_pmat;
+  return pll_compute_node_ancestral(partition, node_clv_index, node_scaler_index, other_clv_index,
+                                    other_scaler_index, pmatrix_index, freqs_indices, ancestral);
+}
+
 extern "C" int pllb200_edge_loglikelihood_async(pll_partition_t * partition,
                                                 unsigned int parent_clv_index,
                                                 int parent_scaler_index,

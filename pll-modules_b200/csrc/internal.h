@@ -60,6 +60,7 @@ struct PartCtx
   double * d_eigen;           /* [rate_matrix][ evecs s*sp | inv_evecs s*sp | evals sp | freqs sp ] */
   unsigned long long * d_tipmap;
   double * d_persite;         /* lazily allocated, sites doubles */
+  double * d_ancestral;       /* lazily allocated, sites*states doubles (pll_compute_node_ancestral) */
 
   /* staging ring: pinned host + device mirror, stream-ordered */
   char * h_stage;
@@ -154,6 +155,9 @@ bool launch_pmatrix_reinterleave(PartCtx * c);
 bool launch_partials(PartCtx * c, const pll_operation_t * ops, unsigned int count);
 bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int count); /* k_traversal_dna.cu */
 bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count);  /* k_traversal_aa.cu */
+bool launch_ancestral(PartCtx * c, unsigned int node_clv, int node_scaler, unsigned int other_clv,
+                      int other_scaler, unsigned int matrix_index, const unsigned int * freqs_indices,
+                      double * d_out);
 bool launch_edge_logl(PartCtx * c, unsigned int parent_clv, int parent_scaler,
                       unsigned int child_clv, int child_scaler, unsigned int matrix_index,
                       const unsigned int * freqs_indices, double * d_persite, int slot);

@@ -15,7 +15,9 @@
 
 #include <cassert>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 static int cb_full_traversal(pll_unode_t *) { return PLL_SUCCESS; }
@@ -751,4 +753,92 @@ extern "C" int pllmod_treeinfo_set_tree(pllmod_treeinfo_t * ti, pll_utree_t * tr
   ti->tree->nodes = nodes;
   memcpy(ti->tree->nodes, tree->nodes, sizeof(pll_unode_t *) * node_count);
   return init_tree(ti);
+}
+
+
+/* ---- marginal ancestral states at every inner node (treeinfo.c:1558-1712) ------------------------ */
+
+static int anc_visit_all(pll_unode_t *) { return 1; }
+
+extern "C" void pllmod_treeinfo_destroy_ancestral(pllmod_ancestral_t * ancestral)
+{
+  if (!ancestral) return;
+  free(ancestral->nodes);
+  free(ancestral->partition_indices);
+  if (ancestral->probs)
+    for (unsigned int i = 0; i < ancestral->node_count; ++i) free(ancestral->probs[i]);
+  free(ancestral->probs);
+  if (ancestral->tree) pll_utree_destroy(ancestral->tree, nullptr);
+  free(ancestral);
+}
+
+extern "C" pllmod_ancestral_t * pllmod_treeinfo_compute_ancestral(pllmod_treeinfo_t * ti)
+{
+  const unsigned int inner = ti->tree->inner_count, total = ti->tree->tip_count + inner;
+  pllmod_ancestral_t * anc = (pllmod_ancestral_t *)calloc(1, sizeof(pllmod_ancestral_t));
+  if (!anc)
+  {
+    pllmod_set_error(PLL_ERROR_MEM_ALLOC, "Can't allocate memory for ancestral probabilities\n");
+    return nullptr;
+  }
+  size_t span = 0; /* doubles per node: all (local) partitions back to back, [site][state] each */
+  for (unsigned int p = 0; p < ti->init_partition_count; ++p)
+    span += (size_t)ti->init_partitions[p]->sites * ti->init_partitions[p]->states;
+  anc->node_count = inner;
+  anc->partition_count = ti->init_partition_count;
+  anc->nodes = (pll_unode_t **)calloc(inner, sizeof(pll_unode_t *));
+  anc->partition_indices = (unsigned int *)calloc(anc->partition_count ? anc->partition_count : 1, sizeof(unsigned int));
+  anc->probs = (double **)calloc(inner, sizeof(double *));
+  anc->tree = pll_utree_clone(ti->tree);
+  bool ok = anc->nodes && anc->partition_indices && anc->probs && anc->tree;
+  for (unsigned int i = 0; ok && i < inner; ++i) ok = (anc->probs[i] = (double *)calloc(span ? span : 1, sizeof(double))) != nullptr;
+  std::vector<pll_unode_t *> order(total);
+  unsigned int visited = 0;
+  ok = ok && pll_utree_traverse(anc->tree->vroot, PLL_TREE_TRAVERSE_POSTORDER, anc_visit_all, order.data(), &visited) &&
+       visited == total;
+  if (!ok)
+  {
+    pllmod_treeinfo_destroy_ancestral(anc);
+    if (!pll_errno) pllmod_set_error(PLL_ERROR_MEM_ALLOC, "Can't allocate memory for ancestral probabilities\n");
+    return nullptr;
+  }
+  /* inner nodes of the cloned tree in post-order; unnamed ones are called Node1, Node2, ... */
+  unsigned int n = 0;
+  for (pll_unode_t * node : order)
+  {
+    if (!node->next) continue;
+    if (!node->label)
+    {
+      char name[100];
+      snprintf(name, sizeof(name), "Node%u", n + 1);
+      node->label = node->next->label = node->next->next->label = strdup(name);
+    }
+    anc->nodes[n++] = node;
+  }
+
+  pll_unode_t * old_root = ti->root;
+  for (unsigned int i = 0; i < inner; ++i)
+  {
+    const pll_unode_t * node = anc->nodes[i];
+    /* orient all CLVs towards this node (partial traversal), then combine the two ends of its edge */
+    ti->root = ti->subnodes[node->node_index];
+    pllmod_treeinfo_compute_loglh(ti, 1);
+    double * out = anc->probs[i];
+    for (unsigned int p = 0; p < ti->init_partition_count; ++p)
+    {
+      pll_partition_t * part = ti->init_partitions[p];
+      const unsigned int pidx = ti->init_partition_idx[p];
+      anc->partition_indices[p] = pidx;
+      if (!pll_compute_node_ancestral(part, node->clv_index, node->scaler_index, node->back->clv_index,
+                                      node->back->scaler_index, node->pmatrix_index, ti->param_indices[pidx], out))
+      {
+        ti->root = old_root;
+        pllmod_treeinfo_destroy_ancestral(anc);
+        return nullptr;
+      }
+      out += (size_t)part->sites * part->states;
+    }
+  }
+  ti->root = old_root;
+  return anc;
 }

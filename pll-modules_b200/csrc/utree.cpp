@@ -5,6 +5,7 @@
  *                               inner nodes, both in a depth-first walk from the root)
  *   pll_utree_destroy           parse_utree.y:107-145
  *   pll_utree_graph_destroy     parse_utree.y:68-105
+ *   pll_utree_graph_clone/clone utree.c:549-633
  *   pll_utree_traverse          libs/libpll/src/utree.c:394-459 (root->back subtree first, then root)
  *   pll_utree_create_operations utree.c:317-366
  *   pllmod_utree_create_random  src/tree/pll_tree.c:903-980 (random branch insertion)
@@ -13,6 +14,7 @@
 #include "internal.h"
 
 #include <cstdlib>
+#include <cstring>
 #include <vector>
 
 extern "C" int pllmod_utree_is_tip(const pll_unode_t * node) { return node->next == nullptr; }
@@ -143,6 +145,67 @@ static void free_subtree(pll_unode_t * entry, bool also_behind_entry, void (*cb_
 extern "C" void pll_utree_graph_destroy(pll_unode_t * root, void (*cb_destroy)(void *))
 {
   if (root) free_subtree(root, true, cb_destroy);
+}
+
+/* Deep copy of a node graph (utree.c:549-633): every ring is duplicated with ONE copy of its label,
+ * `data` pointers are carried over as they are. */
+static pll_unode_t * clone_ring(const pll_unode_t * node)
+{
+  pll_unode_t * first = nullptr;
+  pll_unode_t * prev = nullptr;
+  char * label = node->label ? strdup(node->label) : nullptr;
+  const pll_unode_t * n = node;
+  do
+  {
+    pll_unode_t * copy = (pll_unode_t *)malloc(sizeof(pll_unode_t));
+    *copy = *n;
+    copy->label = label;
+    copy->back = nullptr;
+    copy->next = nullptr;
+    if (prev)
+      prev->next = copy;
+    else
+      first = copy;
+    prev = copy;
+    n = n->next;
+  } while (n && n != node);
+  if (node->next) prev->next = first;
+  return first;
+}
+
+static void clone_behind(pll_unode_t * copy, const pll_unode_t * orig)
+{
+  if (!orig->back) return;
+  pll_unode_t * far = clone_ring(orig->back);
+  copy->back = far;
+  far->back = copy;
+  const pll_unode_t * o = orig->back->next;
+  pll_unode_t * c = far->next;
+  while (o && o != orig->back)
+  {
+    clone_behind(c, o);
+    o = o->next;
+    c = c->next;
+  }
+}
+
+extern "C" pll_unode_t * pll_utree_graph_clone(const pll_unode_t * root)
+{
+  pll_unode_t * copy = clone_ring(root);
+  const pll_unode_t * o = root;
+  pll_unode_t * c = copy;
+  do
+  {
+    clone_behind(c, o);
+    o = o->next;
+    c = c->next;
+  } while (o && o != root);
+  return copy;
+}
+
+extern "C" pll_utree_t * pll_utree_clone(const pll_utree_t * tree)
+{
+  return pll_utree_wraptree(pll_utree_graph_clone(tree->vroot), tree->tip_count);
 }
 
 static void traverse_rec(pll_unode_t * node, int traversal, int (*cb)(pll_unode_t *),

@@ -133,6 +133,8 @@ def _lib(kind):
                                     C.c_double, C.c_int, C.c_double, C.c_int, C.c_double, C.c_double, C.c_int,
                                     C.c_void_p]
         lib.h_topology_signature.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
+        lib.h_ancestral.restype = C.c_uint
+        lib.h_ancestral.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
         lib.h_binary_dump.argtypes = [C.c_void_p, C.c_char_p]
         lib.h_binary_load.argtypes = [C.c_char_p, C.c_void_p]
         lib.h_binary_tree_dump.argtypes = [C.c_char_p, C.c_uint, C.c_uint]
@@ -374,6 +376,15 @@ class Harness:
     def algo_opt_treeinfo(self, what, tolerance=1e-3):
         """pllmod_algo_opt_*_treeinfo over all partitions; returns -logL."""
         return self.lib.h_algo_opt_treeinfo(self.h, self.ALGO_OPT[what], tolerance)
+
+    def ancestral(self):
+        """pllmod_treeinfo_compute_ancestral: (inner nodes by clv_index, concatenated [site][state] per partition)"""
+        span = sum(self.sites[p] * self.states[p] for p in range(self.nparts))
+        out = np.zeros((self.tips - 2, span))
+        lab = C.c_double(0.0)
+        n = self.lib.h_ancestral(self.h, out.ctypes.data, C.byref(lab))
+        assert n == self.tips - 2, self.lib.h_errmsg().decode()
+        return out, lab.value
 
     def binary_dump(self, path):
         """partition 0 + tree + branch lengths + root CLV as blocks 10..13 of a random-access file"""

@@ -359,3 +359,26 @@ def test_binary_checkpoints_cross_load(tmp_path, kw):
             assert rel(got["loglh"], want[writer]) < 1e-11, (writer, reader, got, want)
             assert rel(got["loglh_after_clv_block"], want[writer]) < 1e-11, (writer, reader, got)
             assert abs(got["length"] - length) < 1e-9 and abs(got["custom_sum"] - length) < 1e-9, (writer, reader)
+
+
+@needs_ref
+@pytest.mark.parametrize("kw", [
+    dict(tips=12, sites=300),
+    dict(tips=8, sites=77, states=20),
+    dict(tips=9, sites=100, attributes=0),
+    dict(tips=120, sites=50, brlen_scale=0.01),                     # per-site scalers cancel
+    dict(tips=10, sites=[120, 40], states=[4, 20], alpha=[0.5, 1.5]),
+], ids=["dna", "protein", "no_pattern_tip", "scalers", "two_partitions"])
+def test_ancestral_states_match_reference(kw):
+    """pllmod_treeinfo_compute_ancestral / pll_compute_node_ancestral (treeinfo.c:1611, likelihood.c:639)."""
+    ref, dev = pair(**kw)
+    with ref, dev:
+        ref.loglh(), dev.loglh()
+        want, wl = ref.ancestral()
+        got, gl = dev.ancestral()
+        assert wl == gl and wl > 0                                   # Node1.. labels in the same places
+        np.testing.assert_allclose(got, want, rtol=1e-9, atol=1e-12)
+        s = kw["states"][0] if isinstance(kw.get("states", 4), list) else kw.get("states", 4)
+        n0 = (kw["sites"][0] if isinstance(kw["sites"], list) else kw["sites"]) * s
+        np.testing.assert_allclose(got[:, :n0].reshape(got.shape[0], -1, s).sum(axis=2), 1.0, rtol=1e-12)
+        assert rel(dev.loglh(), ref.loglh()) < 1e-8                   # the root is back where it was
