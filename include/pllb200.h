@@ -945,6 +945,17 @@ int pllb200_newton_branch(pll_partition_t * partition, const unsigned int * para
                           const double * sumtable, double xmin, double xguess, double xmax,
                           double tolerance, unsigned int max_iters, double brlen_scaler,
                           double * x_out, int * iterations);
+/* The same without a host wait, for a whole smoothing pass: queues Newton on the branch and the update of
+ * its P-matrix from the length left on the device; pllb200_newton_collect waits once and returns lengths
+ * and statuses (0 converged, 1 iteration limit, 2 non-finite derivative).  An unconverged branch keeps
+ * its old length when `revert_on_limit` (the reference's rule for the methods without a likelihood check,
+ * pll_optimize.c:1524-1549); changes below 1e-10 are dropped (:1551-1560). */
+int pllb200_newton_branch_queued(pll_partition_t * partition, const unsigned int * params_indices,
+                                 const double * sumtable, double xmin, double host_x0, double xmax,
+                                 double tolerance, unsigned int max_iters, double brlen_scaler,
+                                 unsigned int matrix_index, int use_device_x0, int revert_on_limit);
+int pllb200_newton_collect(pll_partition_t * partition, const unsigned int * matrix_indices,
+                           unsigned int count, double * lengths, int * status);
 /* Device address (as integer) of the partition's most recent reduction results
  * {logL, d_f, dd_f}: lets a caller run an NCCL all-reduce on them without a host round trip. */
 uint64_t pllb200_result_device_ptr(pll_partition_t * partition);
@@ -959,7 +970,7 @@ typedef struct
 } pllb200_stats_t;
 void pllb200_get_stats(pllb200_stats_t * out);
 void pllb200_reset_stats(void);
-/* name in {"trav_ctas_per_sm","trav_reorder","fuse_root","trav_variant","trav_forward","fused_newton"}; returns previous value, -1 if unknown */
+/* name in {"trav_ctas_per_sm","trav_reorder","fuse_root","trav_variant","trav_forward","fused_newton","queued_newton"}; returns previous value, -1 if unknown */
 int pllb200_set_option(const char * name, int value);
 
 #ifdef __cplusplus

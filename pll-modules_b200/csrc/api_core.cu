@@ -14,6 +14,8 @@
  */
 #include "internal.h"
 
+#include <vector>
+
 #include <cmath>
 #include <mutex>
 
@@ -270,6 +272,75 @@ extern "C" int pllb200_newton_branch(pll_partition_t * partition, const unsigned
   }
   pllmod_set_error(PLLMOD_OPT_ERROR_NEWTON_DERIV, "Wrong likelihood derivatives");
   return -1;
+}
+
+/* Queued variant for a whole smoothing pass: Newton on one branch, then the P-matrix of that branch from
+ * the length the kernel left on the device — no host wait.  The start value is `host_x0` on the first
+ * visit of a branch and the device value afterwards (`use_device_x0`).  Results are fetched with
+ * pllb200_newton_collect.  Returns 1 queued, -1 error, -2 not supported for this partition. */
+extern "C" int pllb200_newton_branch_queued(pll_partition_t * partition, const unsigned int * params_indices,
+                                            const double * sumtable, double xmin, double host_x0, double xmax,
+                                            double tolerance, unsigned int max_iters, double brlen_scaler,
+                                            unsigned int matrix_index, int use_device_x0, int revert_on_limit)
+{
+  if (!enter(partition)) return -1;
+  PartCtx * c = ctx_of(partition);
+  if (!newton_fused_supported(c)) return -2;
+  if (matrix_index >= partition->prob_matrices)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid matrix index %u.", matrix_index);
+    return -1;
+  }
+  if (!c->d_brlen)
+  {
+    const size_t bytes = sizeof(double) * 4 * partition->prob_matrices;
+    if (!pllb200_cuda_ok(cudaMalloc(&c->d_brlen, bytes), "branch length buffer")) return -1;
+    if (!pllb200_cuda_ok(cudaMemsetAsync(c->d_brlen, 0, bytes, c->stream), "branch length buffer")) return -1;
+  }
+  double * d = sumtable_shadow(c, sumtable, false);
+  if (!d) return -1;
+  double * io = c->d_brlen + (size_t)matrix_index * 4;
+  const int slot = dev_alloc_slot(c);
+  if (!launch_newton(c, params_indices, d, xmin, host_x0, xmax, tolerance, max_iters, brlen_scaler, slot, io,
+                     use_device_x0, revert_on_limit))
+    return -1;
+  return launch_pmatrix_devlen(c, params_indices, matrix_index, io + 1) ? 1 : -1;
+}
+
+/* Wait for the queued work and return, per requested matrix index, the final branch length and the
+ * Newton status (0 converged, 1 iteration limit, 2 non-finite derivative). */
+extern "C" int pllb200_newton_collect(pll_partition_t * partition, const unsigned int * matrix_indices,
+                                      unsigned int count, double * lengths, int * status)
+{
+  if (!enter(partition)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(partition);
+  if (!c->d_brlen || !count) return dev_flush(c) ? PLL_SUCCESS : PLL_FAILURE;
+  std::vector<double> host((size_t)4 * partition->prob_matrices);
+  if (count <= 8)
+  {
+    for (unsigned int i = 0; i < count; ++i)
+      if (!pllb200_cuda_ok(cudaMemcpyAsync(host.data() + (size_t)matrix_indices[i] * 4,
+                                           c->d_brlen + (size_t)matrix_indices[i] * 4, 4 * sizeof(double),
+                                           cudaMemcpyDeviceToHost, c->stream), "branch lengths D2H"))
+        return PLL_FAILURE;
+    g_d2h_bytes += (size_t)count * 4 * sizeof(double);
+  }
+  else
+  {
+    if (!pllb200_cuda_ok(cudaMemcpyAsync(host.data(), c->d_brlen, host.size() * sizeof(double),
+                                         cudaMemcpyDeviceToHost, c->stream), "branch lengths D2H"))
+      return PLL_FAILURE;
+    g_d2h_bytes += host.size() * sizeof(double);
+  }
+  if (!dev_flush(c)) return PLL_FAILURE;
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    const double * r = host.data() + (size_t)matrix_indices[i] * 4;
+    lengths[i] = r[0];
+    status[i] = (int)r[2];
+    g_newton_iterations += (unsigned long long)r[3];
+  }
+  return PLL_SUCCESS;
 }
 
 extern "C" int pllb200_likelihood_derivatives_async(pll_partition_t * partition,

@@ -71,6 +71,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_variant")) slot = &g_opt_trav_variant;
   else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
   else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;
+  else if (!strcmp(name, "queued_newton")) slot = &g_opt_queued_newton;
   if (!slot) return -1;
   int old = *slot;
   *slot = value;
@@ -113,7 +114,7 @@ bool dev_ctx_init(PartCtx * c)
 
   c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr;
   c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
-  c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->h_stage = nullptr; c->d_stage = nullptr;
+  c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->h_stage = nullptr; c->d_stage = nullptr;
   c->d_partials = nullptr; c->d_ticket = nullptr; c->d_result = nullptr; c->h_result = nullptr;
   c->own_stream = nullptr;
 
@@ -206,7 +207,7 @@ void dev_ctx_destroy(PartCtx * c)
   c->sumtables.clear();
   cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
-  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_stage); cudaFree(c->d_partials);
+  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_stage); cudaFree(c->d_partials);
   cudaFree(c->d_ticket); cudaFree(c->d_result);
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->h_result) cudaFreeHost(c->h_result);

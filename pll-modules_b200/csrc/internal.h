@@ -61,6 +61,7 @@ struct PartCtx
   unsigned long long * d_tipmap;
   double * d_persite;         /* lazily allocated, sites doubles */
   double * d_ancestral;       /* lazily allocated, sites*states doubles (pll_compute_node_ancestral) */
+  double * d_brlen;           /* lazily allocated, [prob_matrices][4]: queued Newton results (k_newton.cu) */
 
   /* staging ring: pinned host + device mirror, stream-ordered */
   char * h_stage;
@@ -121,6 +122,7 @@ extern int g_opt_fuse_root;
 extern int g_opt_trav_variant;
 extern int g_opt_trav_forward;
 extern int g_opt_fused_newton;
+extern int g_opt_queued_newton;
 
 /* device context (device_ctx.cu) */
 bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */
@@ -171,7 +173,10 @@ bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_cl
 bool newton_fused_supported(const PartCtx * c);
 bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
                    double xmin, double x0, double xmax, double tol, unsigned int max_iters,
-                   double scale, int slot);
+                   double scale, int slot, double * brlen_io = nullptr, int x0_from_device = 0,
+                   int revert_on_limit = 0);
+bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,
+                           const double * d_length);
 bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double branch_length,
                         const unsigned int * params_indices, const double * d_sumtable, int slot);
 

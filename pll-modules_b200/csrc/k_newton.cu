@@ -31,6 +31,11 @@ namespace cg = cooperative_groups;
 #define NW_MAXK 32
 #define NW_MAX_DIAG 512 /* K * states */
 
+/* status codes returned in result[1] */
+#define NW_OK 0.0
+#define NW_LIMIT 1.0
+#define NW_BAD_DERIV 2.0
+
 struct NewtonArgs
 {
   const double * sum;
@@ -46,12 +51,26 @@ struct NewtonArgs
   double * partials; /* [2 buffers][2][gridDim.x] */
   double * result_dev;
   double * result_host;
+  /* queued mode (a whole smoothing pass without a host wait): {x, x * scale, status, iterations} of this
+   * branch in device memory; the start value comes from there when the branch was already visited */
+  double * brlen_io;
+  int x0_from_device, revert_on_limit;
 };
 
-/* status codes returned in result[1] */
-#define NW_OK 0.0
-#define NW_LIMIT 1.0
-#define NW_BAD_DERIV 2.0
+/* what the host does with a result (pll_optimize.c:1524-1560), for the queued mode: an unconverged or
+ * failed branch keeps its old length, and so does a change below 1e-10 */
+__device__ __forceinline__ void newton_publish(const NewtonArgs & a, double x, double xorig, double status,
+                                               unsigned int iter)
+{
+  if (!a.brlen_io) return;
+  if ((status == NW_LIMIT && a.revert_on_limit) || status == NW_BAD_DERIV) x = xorig;
+  if (fabs(x - xorig) < 1e-10) x = xorig;
+  a.brlen_io[0] = x;
+  a.brlen_io[1] = x * a.scale;
+  a.brlen_io[2] = status;
+  a.brlen_io[3] = (double)iter;
+}
+
 
 /* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates) */
 template <int MODE>
@@ -80,7 +99,8 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
 
   /* optimiser state, replicated in every thread (all threads see the same f, df) */
   double xl = a.xmin, xh = a.xmax;
-  double x = fmax(fmin(a.x0, a.xmax), a.xmin);
+  const double xorig = (a.brlen_io && a.x0_from_device) ? __ldcg(a.brlen_io) : a.x0;
+  double x = fmax(fmin(xorig, a.xmax), a.xmin);
   const double dxmax = a.xmax / a.max_iters;
   unsigned int iter = 0;
   double status = NW_OK;
@@ -345,6 +365,7 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
 
   if (blockIdx.x == 0 && threadIdx.x == 0)
   {
+    newton_publish(a, x, xorig, status, iter);
     a.result_dev[0] = x;
     a.result_dev[1] = status;
     a.result_dev[2] = (double)iter;
@@ -421,10 +442,12 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
   __syncthreads();
 
   double xl = a.xmin, xh = a.xmax;
-  double x = fmax(fmin(a.x0, a.xmax), a.xmin);
+  const double xorig = (a.brlen_io && a.x0_from_device) ? __ldcg(a.brlen_io) : a.x0;
+  double x = fmax(fmin(xorig, a.xmax), a.xmin);
   const double dxmax = a.xmax / a.max_iters;
   unsigned int iter = 0;
   unsigned int used = 0; /* tiles through the ring so far (all passes): stage = n % 3, fill number n / 3 */
+  unsigned int prefetched = 0; /* tiles of the coming pass the producer has already asked for */
   double status = NW_OK;
   double f = 0.0, df = 0.0;
 
@@ -441,18 +464,25 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
     if (producer)
     {
       if (lane == 0)
-        for (unsigned int i = 0; i < nt; ++i)
-        {
-          const unsigned int n = used + i, slot = n % NT_STAGES, fill = n / NT_STAGES;
+      {
+        /* ring position n (all passes), pass-local tile i in direction dir */
+        auto issue = [&](unsigned int n, unsigned int i, bool dir) {
+          const unsigned int slot = n % NT_STAGES, fill = n / NT_STAGES;
           if (fill) mbar_wait(&sm.empty[slot], (fill - 1u) & 1u); /* previous contents consumed */
-          const unsigned int mine = fwd ? i : nt - 1 - i;
+          const unsigned int mine = dir ? i : nt - 1 - i;
           const unsigned long long e0 = ((unsigned long long)b + (unsigned long long)mine * G) * NT_TILE;
           const unsigned int elems = (unsigned int)((E - e0) < NT_TILE ? (E - e0) : NT_TILE);
           const unsigned int wbytes = ((elems / 4 + 3u) & ~3u) * 4u; /* weights are padded to whole tiles */
           mbar_expect_tx(&sm.full[slot], elems * 32u + wbytes);
           tma_load_1d(sm.tile[slot], a.sum + e0 * 4, elems * 32u, &sm.full[slot]);
           tma_load_1d(sm.wts[slot], a.weights + e0 / 4, wbytes, &sm.full[slot]);
-        }
+        };
+        for (unsigned int i = prefetched; i < nt; ++i) issue(used + i, i, fwd);
+        /* the table does not change between passes: start the next pass (opposite direction) now, so
+         * that its first tiles land while the grid reduces; if there is no next pass they are drained
+         * before the kernel ends */
+        for (unsigned int i = 0; i < NT_STAGES && i < nt; ++i) issue(used + nt + i, i, !fwd);
+      }
     }
     else if (tid < 16)
     {
@@ -560,6 +590,7 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
       }
     }
     used += nt;
+    prefetched = nt < NT_STAGES ? nt : NT_STAGES;
     __syncthreads();
 
     /* CTA partial -> grid total (deterministic: fixed order in every CTA) */
@@ -626,8 +657,13 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
     x = fmax(fmin(x, a.xmax), a.xmin);
   }
 
+  /* tiles requested for a pass that will not happen must land before the CTA gives up its shared memory */
+  for (unsigned int i = 0; i < prefetched; ++i)
+    mbar_wait(&sm.full[(used + i) % NT_STAGES], ((used + i) / NT_STAGES) & 1u);
+
   if (b == 0 && tid == 0)
   {
+    newton_publish(a, x, xorig, status, iter);
     a.result_dev[0] = x;
     a.result_dev[1] = status;
     a.result_dev[2] = (double)iter;
@@ -642,6 +678,7 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
 
 /* can the fused path serve this partition? */
 int g_opt_fused_newton = 1;
+int g_opt_queued_newton = 1;
 
 bool newton_fused_supported(const PartCtx * c)
 {
@@ -655,7 +692,7 @@ bool newton_fused_supported(const PartCtx * c)
 
 bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
                    double xmin, double x0, double xmax, double tol, unsigned int max_iters,
-                   double scale, int slot)
+                   double scale, int slot, double * brlen_io, int x0_from_device, int revert_on_limit)
 {
   pll_partition_t * p = &c->pub;
   const unsigned int K = p->rate_cats, s = p->states;
@@ -704,6 +741,9 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   a.partials = c->d_partials;
   a.result_dev = c->d_result + slot * 4;
   a.result_host = c->h_result_dev + slot * 4;
+  a.brlen_io = brlen_io;
+  a.x0_from_device = x0_from_device;
+  a.revert_on_limit = revert_on_limit;
 
   /* cooperative grid: never more CTAs than can be co-resident, never more than there is work */
   static int per_sm[4] = {0, 0, 0, 0};

@@ -80,6 +80,36 @@ __global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__
   }
 }
 
+/* one matrix whose branch length is already on the device (written by the queued Newton kernel) */
+bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,
+                           const double * d_length)
+{
+  pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats, s = p->states, sp = p->states_padded;
+  if (K > PM_MAXK || matrix_index >= p->prob_matrices)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid matrix index %u or rate_cats > %d.", matrix_index, PM_MAXK);
+    return false;
+  }
+  if (!dev_sync_eigen(c, params_indices)) return false;
+  PmatArgs a;
+  for (unsigned int k = 0; k < K; ++k)
+  {
+    a.params_idx[k] = params_indices[k];
+    a.rates[k] = p->rates[k];
+    a.pinv[k] = p->prop_invar[params_indices[k]];
+  }
+  const unsigned int * d_idx = (const unsigned int *)dev_stage(c, &matrix_index, sizeof(unsigned int));
+  if (!d_idx) return false;
+  unsigned int threads = ((s * sp + 31) / 32) * 32;
+  if (threads > 512) threads = 512;
+  const size_t smem = sizeof(double) * (sp + 2 * s * sp);
+  pmatrix_kernel<<<K, threads, smem, c->stream>>>(c->d_pmat, c->d_pmat_il, c->d_eigen, c->eigen_stride, d_idx,
+                                                  d_length, s, sp, K, a);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "pmatrix_kernel launch");
+}
+
 /* rebuild the interleaved copies from the plain array (after P-matrices were uploaded from a
  * checkpoint, binary_io.cpp): same index maps as pmatrix_kernel */
 __global__ void pmatrix_reinterleave_kernel(const double * __restrict__ pmat, double * __restrict__ pmat_il,

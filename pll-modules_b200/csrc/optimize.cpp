@@ -445,6 +445,15 @@ static void multi_deriv_cb_old(void * parameters, double proposal, double * df, 
   multi_deriv_cb(parameters, &proposal, df, ddf);
 }
 
+/* A smoothing pass without host waits (single local partition, Newton without likelihood check, fused
+ * Newton kernel available): branches are only queued; lengths come back once per pass. */
+struct QueuedPass
+{
+  std::vector<pll_unode_t *> nodes;       /* visited branches in order (the root edge appears twice) */
+  std::vector<unsigned char> on_device;   /* by pmatrix index: length already left on the device */
+};
+static thread_local QueuedPass * t_queued = nullptr;
+
 static void refresh_pmatrix_multi(pll_partition_t ** partitions, size_t partition_count,
                                   unsigned int ** params_indices, double ** brlen_buffers,
                                   double * brlen_scalers, pll_unode_t * node)
@@ -500,6 +509,27 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
 
   const double xmin = prm->branch_length_min, xmax = prm->branch_length_max, xtol = prm->tolerance;
   int retval;
+  bool queued = false;
+  if (t_queued)
+  {
+    if (t_queued->on_device.size() <= m) t_queued->on_device.resize(m + 1, 0);
+    const double s = prm->brlen_scalers ? prm->brlen_scalers[0] : 1.;
+    const int rc = pllb200_newton_branch_queued(prm->partitions[0], prm->params_indices[0],
+                                                prm->precomp_buffers[0], xmin, xguess[0], xmax, xtol,
+                                                (unsigned int)prm->max_newton_iters, s, m,
+                                                t_queued->on_device[m], 1);
+    if (rc == -1) return PLL_FAILURE;
+    if (rc == 1)
+    {
+      t_queued->on_device[m] = 1;
+      t_queued->nodes.push_back(tr_p);
+      queued = true;
+    }
+    else
+      t_queued = nullptr; /* not supported after all: finish the pass the ordinary way */
+  }
+  if (!queued)
+  {
   switch (prm->opt_method)
   {
     case PLLMOD_OPT_BLO_NEWTON_FAST:
@@ -583,6 +613,8 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
     }
   }
 
+  } /* !queued */
+
   if (radius && tr_q && tr_z)
   {
     pll_newton_tree_params_multi_t sub = *prm;
@@ -595,6 +627,30 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
     reorient_clv(prm->partitions, prm->partition_count, tr_p, tr_z, tr_q);
   }
   return PLL_SUCCESS;
+}
+
+static bool collect_queued(QueuedPass & q, pll_partition_t * partition, double ** brlen_buffers)
+{
+  if (q.nodes.empty()) return true;
+  std::vector<unsigned int> idx(q.nodes.size());
+  for (size_t i = 0; i < q.nodes.size(); ++i) idx[i] = q.nodes[i]->pmatrix_index;
+  std::vector<double> len(idx.size());
+  std::vector<int> st(idx.size());
+  const int rc = pllb200_newton_collect(partition, idx.data(), (unsigned int)idx.size(), len.data(), st.data());
+  bool ok = rc == PLL_SUCCESS;
+  for (size_t i = 0; rc == PLL_SUCCESS && i < q.nodes.size(); ++i)
+  {
+    pll_unode_t * n = q.nodes[i];
+    n->length = n->back->length = len[i];
+    if (brlen_buffers && brlen_buffers[0]) brlen_buffers[0][idx[i]] = len[i];
+    if (st[i] == 2)
+    {
+      pllmod_set_error(PLLMOD_OPT_ERROR_NEWTON_DERIV, "Wrong likelihood derivatives");
+      ok = false;
+    }
+  }
+  q.nodes.clear();
+  return ok;
 }
 
 extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
@@ -644,6 +700,7 @@ extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
 
   /* buffers the caller did not provide (pll_optimize.c:1324-1393); sumtables are device-side, the
    * host allocation is only the 64-byte key */
+  QueuedPass queue;
   std::vector<double *> own_precomp;
   std::vector<int> conv;
   std::vector<double> orig, guess;
@@ -670,17 +727,28 @@ extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
   }
 
   {
+    /* queue whole passes when nothing between two branches needs a number on the host */
+    const bool can_queue = keep_update && opt_method == PLLMOD_OPT_BLO_NEWTON_FAST && partition_count == 1 &&
+                           partitions[0] && !parallel_reduce_cb && g_opt_fused_newton != 0 &&
+                           g_opt_queued_newton != 0;
     unsigned int iters = (unsigned int)max_iters;
     while (iters)
     {
       double new_loglh = loglh;
       prm.tree = tree;
-      if (!optimise_branch_rec_multi(&prm, radius, &new_loglh, keep_update)) goto cleanup;
-      if (radius)
+      queue.nodes.clear();
+      queue.on_device.assign(queue.on_device.size(), 0);
+      t_queued = can_queue ? &queue : nullptr;
+      int ok = optimise_branch_rec_multi(&prm, radius, &new_loglh, keep_update);
+      if (ok && radius)
       {
         prm.tree = tree->back;
-        if (!optimise_branch_rec_multi(&prm, radius - 1, &new_loglh, keep_update)) goto cleanup;
+        ok = optimise_branch_rec_multi(&prm, radius - 1, &new_loglh, keep_update);
       }
+      t_queued = nullptr;
+      /* lengths the device decided on -> tree and caller's buffers (also after a failure: the P-matrices
+       * on the device already use them) */
+      if (!collect_queued(queue, partitions[0], brlen_buffers) || !ok) goto cleanup;
       new_loglh = pllmod_opt_compute_edge_loglikelihood_multi(
           partitions, partition_count, tree->back->clv_index, tree->back->scaler_index,
           tree->clv_index, tree->scaler_index, tree->pmatrix_index, params_indices, nullptr,
