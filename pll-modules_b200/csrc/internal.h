@@ -123,6 +123,7 @@ extern int g_opt_trav_variant;
 extern int g_opt_trav_forward;
 extern int g_opt_fused_newton;
 extern int g_opt_queued_newton;
+extern int g_opt_aa_variant;
 
 /* device context (device_ctx.cu) */
 bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */

@@ -50,8 +50,7 @@ struct AaArgs
   const unsigned long long * tipmap;
 };
 
-#define AA_WARPS 4
-#define AA_T 4     /* 8-site tiles per warp and chunk */
+/* defaults: 4 warps per CTA, 4 tiles of 8 sites per warp and chunk (template parameters below) */
 #define AA_SEG 128 /* ops staged per CTA */
 #define AA_FRAG 480 /* doubles per (matrix, category): 3 ntiles x 5 ksteps x 32 lanes */
 #define AA_THR_HI 0x2FF00000u
@@ -82,19 +81,21 @@ __device__ __forceinline__ void aa_tma(void * dst, const void * src, unsigned in
 }
 __device__ __forceinline__ void dmma(double & c0, double & c1, double a, double b)
 {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1)
                : "d"(a), "d"(b));
 }
 
-/* dynamic shared memory: AaOp ops[AA_SEG] | u64 tipmap[256] | u64 bar[2] | double mat[2 stages][2][K*480] */
-__global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
+/* dynamic shared memory: AaOp ops[AA_SEG] | u64 tipmap[256] | u64 bar[2] | u32 cnt[2] | double mat[2 stages][2][K*480] */
+template <int AA_T, int AA_WARPS, int MINB>
+__global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_kernel(AaArgs a)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   AaOp * s_ops = reinterpret_cast<AaOp *>(smem_raw);
   unsigned long long * s_tipmap = reinterpret_cast<unsigned long long *>(smem_raw + sizeof(AaOp) * AA_SEG);
   unsigned long long * s_bar = s_tipmap + 256;
-  double * s_mat = reinterpret_cast<double *>(s_bar + 2);
+  unsigned int * s_cnt = reinterpret_cast<unsigned int *>(s_bar + 2); /* warps done with stage 0 / 1 */
+  double * s_mat = reinterpret_cast<double *>(s_bar + 4); /* keeps the TMA destination 16-byte aligned */
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int row = lane >> 2, col = lane & 3; /* fragment coordinates */
@@ -110,6 +111,7 @@ __global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
   {
     aa_mbar_init(&s_bar[0], 1);
     aa_mbar_init(&s_bar[1], 1);
+    s_cnt[0] = s_cnt[1] = 0;
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   unsigned int ph = 0;
@@ -128,27 +130,24 @@ __global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
     for (unsigned long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x)
     {
       const unsigned long long wsite0 = chunk * sites_per_cta + (unsigned long long)warp * 8 * AA_T;
-      __syncthreads(); /* both stages free */
+      __syncthreads(); /* both stages free, counters zero */
       if (threadIdx.x == 0)
-      {
-        aa_mbar_expect(&s_bar[0], 2 * mat_bytes);
-        aa_tma(s_mat, a.frag + s_ops[0].m1_off, mat_bytes, &s_bar[0]);
-        aa_tma(s_mat + mat_doubles, a.frag + s_ops[0].m2_off, mat_bytes, &s_bar[0]);
-      }
+        for (unsigned int o = 0; o < 2 && o < nseg; ++o)
+        {
+          double * dstm = s_mat + (size_t)o * 2 * mat_doubles;
+          aa_mbar_expect(&s_bar[o], 2 * mat_bytes);
+          aa_tma(dstm, a.frag + s_ops[o].m1_off, mat_bytes, &s_bar[o]);
+          aa_tma(dstm + mat_doubles, a.frag + s_ops[o].m2_off, mat_bytes, &s_bar[o]);
+        }
       for (unsigned int o = 0; o < nseg; ++o)
       {
         const AaOp & d = s_ops[o];
         const unsigned int flags = d.flags;
         const bool tip1 = flags & AOPF_TIP1, tip2 = flags & AOPF_TIP2;
         const unsigned int st = o & 1u;
-        __syncthreads(); /* op o-1 complete everywhere: its CLV is visible, stage st^1 is free */
-        if (threadIdx.x == 0 && o + 1 < nseg)
-        {
-          double * dstm = s_mat + (size_t)(st ^ 1u) * 2 * mat_doubles;
-          aa_mbar_expect(&s_bar[st ^ 1u], 2 * mat_bytes);
-          aa_tma(dstm, a.frag + s_ops[o + 1].m1_off, mat_bytes, &s_bar[st ^ 1u]);
-          aa_tma(dstm + mat_doubles, a.frag + s_ops[o + 1].m2_off, mat_bytes, &s_bar[st ^ 1u]);
-        }
+        /* A warp only ever touches its own sites, so the warps of a CTA are not kept in step: the CLV this
+         * warp wrote in op o-1 only has to be visible to its own lanes */
+        __syncwarp();
         aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
         ph ^= 1u << st;
         const double * sL = s_mat + (size_t)st * 2 * mat_doubles;
@@ -158,6 +157,39 @@ __global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
 #pragma unroll
         for (int t = 0; t < AA_T; ++t) smax[t] = 0;
 
+        /* A fragments (child values of 8 sites x 4 child states per k-step) are the only operands that
+         * come from global memory; the ones of step (k, t) + 1 are requested before the 30 DMMAs of step
+         * (k, t) run (ncu: the first DMMA of every tile was waiting on them, 34 % of all stall samples) */
+        auto load_a = [&](unsigned int k, int t, double (&aL)[5], double (&aR)[5]) {
+          const unsigned long long site = wsite0 + 8 * t + row;
+          const bool act = site < a.sites;
+          if (tip1)
+          {
+            const unsigned long long m = act ? s_tipmap[a.tipchars[d.c1_off + site]] : 0ull;
+#pragma unroll
+            for (int ks = 0; ks < 5; ++ks) aL[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+          }
+          else
+          {
+            const double * p = a.clv + d.c1_off + site * span + k * 20 + col;
+#pragma unroll
+            for (int ks = 0; ks < 5; ++ks) aL[ks] = act ? p[ks * 4] : 0.0;
+          }
+          if (tip2)
+          {
+            const unsigned long long m = act ? s_tipmap[a.tipchars[d.c2_off + site]] : 0ull;
+#pragma unroll
+            for (int ks = 0; ks < 5; ++ks) aR[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+          }
+          else
+          {
+            const double * p = a.clv + d.c2_off + site * span + k * 20 + col;
+#pragma unroll
+            for (int ks = 0; ks < 5; ++ks) aR[ks] = act ? p[ks * 4] : 0.0;
+          }
+        };
+        double aL[5], aR[5];
+        load_a(0, 0, aL, aR);
         for (unsigned int k = 0; k < K; ++k)
         {
           double bL[15], bR[15];
@@ -172,43 +204,24 @@ __global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
           {
             const unsigned long long site = wsite0 + 8 * t + row;
             const bool act = site < a.sites;
-            double aL[5], aR[5];
-            if (tip1)
-            {
-              const unsigned long long m = act ? s_tipmap[a.tipchars[d.c1_off + site]] : 0ull;
-#pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aL[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
-            }
-            else
-            {
-              const double * p = a.clv + d.c1_off + site * span + k * 20 + col;
-#pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aL[ks] = act ? p[ks * 4] : 0.0;
-            }
-            if (tip2)
-            {
-              const unsigned long long m = act ? s_tipmap[a.tipchars[d.c2_off + site]] : 0ull;
-#pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aR[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
-            }
-            else
-            {
-              const double * p = a.clv + d.c2_off + site * span + k * 20 + col;
-#pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aR[ks] = act ? p[ks * 4] : 0.0;
-            }
+            double nL[5], nR[5];
+            if (t + 1 < AA_T)
+              load_a(k, t + 1, nL, nR);
+            else if (k + 1 < K)
+              load_a(k + 1, 0, nL, nR);
+            /* k-step outermost: six independent accumulator chains are interleaved, so a DMMA never waits
+             * on the one issued just before it */
             double xl[3][2], xr[3][2];
 #pragma unroll
-            for (int nt = 0; nt < 3; ++nt)
-            {
-              xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
+            for (int nt = 0; nt < 3; ++nt) xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
 #pragma unroll
-              for (int ks = 0; ks < 5; ++ks)
+            for (int ks = 0; ks < 5; ++ks)
+#pragma unroll
+              for (int nt = 0; nt < 3; ++nt)
               {
                 dmma(xl[nt][0], xl[nt][1], aL[ks], bL[nt * 5 + ks]);
                 dmma(xr[nt][0], xr[nt][1], aR[ks], bR[nt * 5 + ks]);
               }
-            }
             /* D fragment: this lane holds parent[site][k][nt*8 + 2*col, +1] */
             double * pd = a.clv + d.p_off + site * span + k * 20 + 2 * col;
 #pragma unroll
@@ -220,6 +233,12 @@ __global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
                 if (check) smax[t] = max(smax[t], max((unsigned int)__double2hiint(o0), (unsigned int)__double2hiint(o1)));
                 if (act) *reinterpret_cast<double2 *>(pd + nt * 8) = make_double2(o0, o1);
               }
+            }
+#pragma unroll
+            for (int ks = 0; ks < 5; ++ks)
+            {
+              aL[ks] = nL[ks];
+              aR[ks] = nR[ks];
             }
           }
         }
@@ -261,12 +280,58 @@ __global__ void __launch_bounds__(AA_WARPS * 32, 3) trav_aa_kernel(AaArgs a)
             }
           }
         }
+        /* the last warp to leave op o refills its stage with the matrices of op o+2 */
+        __syncwarp();
+        if (lane == 0)
+        {
+          const unsigned int done = atomicAdd(&s_cnt[st], 1u);
+          if (done == AA_WARPS - 1)
+          {
+            s_cnt[st] = 0;
+            if (o + 2 < nseg)
+            {
+              double * dstm = s_mat + (size_t)st * 2 * mat_doubles;
+              aa_mbar_expect(&s_bar[st], 2 * mat_bytes);
+              aa_tma(dstm, a.frag + s_ops[o + 2].m1_off, mat_bytes, &s_bar[st]);
+              aa_tma(dstm + mat_doubles, a.frag + s_ops[o + 2].m2_off, mat_bytes, &s_bar[st]);
+            }
+          }
+        }
       }
     }
   }
 }
 
 /* ---- host ------------------------------------------------------------------------------------ */
+
+int g_opt_aa_variant = 0;
+
+template <int T, int W, int MINB>
+static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
+{
+  const unsigned int K = a.K;
+  const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * K * AA_FRAG * sizeof(double);
+  static size_t smem_set = 0;
+  static int per_sm = 0;
+  if (smem > smem_set)
+  {
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa_kernel<T, W, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem),
+                         "trav_aa smem attribute"))
+      return false;
+    smem_set = smem;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa_kernel<T, W, MINB>, W * 32, smem) != cudaSuccess ||
+        per_sm < 1)
+      per_sm = 1;
+  }
+  const unsigned long long spc = (unsigned long long)W * 8 * T;
+  unsigned long long blocks = (a.sites + spc - 1) / spc;
+  blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
+  if (blocks < 1) blocks = 1;
+  trav_aa_kernel<T, W, MINB><<<(unsigned int)blocks, W * 32, smem, c->stream>>>(a);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "trav_aa_kernel launch");
+}
 
 bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count)
 {
@@ -326,23 +391,21 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
   a.frag = c->d_pmat_il;
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
-  const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 2 * 8 + (size_t)2 * 2 * K * AA_FRAG * sizeof(double);
-  static size_t smem_set = 0;
-  if (smem > smem_set)
+  switch (g_opt_aa_variant)
   {
-    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
-                         "trav_aa smem attribute"))
-      return false;
-    smem_set = smem;
+    case 1: return launch_aa_variant<8, 4, 3>(c, a);
+    case 2: return launch_aa_variant<4, 8, 2>(c, a);
+    case 3: return launch_aa_variant<2, 4, 3>(c, a);
+    case 4: return launch_aa_variant<4, 6, 2>(c, a);
+    case 5: return launch_aa_variant<3, 4, 3>(c, a);
+    case 6: return launch_aa_variant<2, 8, 2>(c, a);
+    case 7: return launch_aa_variant<2, 6, 3>(c, a);
+    case 8: return launch_aa_variant<1, 4, 3>(c, a);
+    case 9: return launch_aa_variant<2, 6, 2>(c, a);
+    case 10: return launch_aa_variant<1, 8, 2>(c, a);
+    case 11: return launch_aa_variant<1, 8, 3>(c, a);
+    case 12: return launch_aa_variant<4, 4, 3>(c, a);
+    default: return launch_aa_variant<2, 4, 3>(c, a);
   }
-  int per_sm = 0;
-  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa_kernel, AA_WARPS * 32, smem) != cudaSuccess || per_sm < 1)
-    per_sm = 1;
-  const unsigned long long spc = (unsigned long long)AA_WARPS * 8 * AA_T;
-  unsigned long long blocks = (c->sites_alloc + spc - 1) / spc;
-  blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
-  if (blocks < 1) blocks = 1;
-  trav_aa_kernel<<<(unsigned int)blocks, AA_WARPS * 32, smem, c->stream>>>(a);
-  ++g_kernel_launches;
-  return pllb200_cuda_ok(cudaGetLastError(), "trav_aa_kernel launch");
 }
+
