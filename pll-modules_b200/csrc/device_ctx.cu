@@ -115,7 +115,7 @@ bool dev_ctx_init(PartCtx * c)
 
   c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr;
   c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
-  c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->h_stage = nullptr; c->d_stage = nullptr;
+  c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->d_sumfrag = nullptr; c->h_stage = nullptr; c->d_stage = nullptr;
   c->d_partials = nullptr; c->d_ticket = nullptr; c->d_result = nullptr; c->h_result = nullptr;
   c->own_stream = nullptr;
 
@@ -208,7 +208,7 @@ void dev_ctx_destroy(PartCtx * c)
   c->sumtables.clear();
   cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
-  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_stage); cudaFree(c->d_partials);
+  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag); cudaFree(c->d_stage); cudaFree(c->d_partials);
   cudaFree(c->d_ticket); cudaFree(c->d_result);
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->h_result) cudaFreeHost(c->h_result);

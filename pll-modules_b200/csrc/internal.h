@@ -61,6 +61,8 @@ struct PartCtx
   unsigned long long * d_tipmap;
   double * d_persite;         /* lazily allocated, sites doubles */
   double * d_ancestral;       /* lazily allocated, sites*states doubles (pll_compute_node_ancestral) */
+  double * d_sumfrag;         /* lazily allocated: 20-state sumtable matrices as DMMA fragment images */
+  std::vector<unsigned long long> sumfrag_key;
   double * d_brlen;           /* lazily allocated, [prob_matrices][4]: queued Newton results (k_newton.cu) */
 
   /* staging ring: pinned host + device mirror, stream-ordered */
@@ -176,6 +178,8 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
                    double xmin, double x0, double xmax, double tol, unsigned int max_iters,
                    double scale, int slot, double * brlen_io = nullptr, int x0_from_device = 0,
                    int revert_on_limit = 0);
+bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsigned int second,
+                        const unsigned int * params_indices, double * d_sumtable);
 bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,
                            const double * d_length);
 bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double branch_length,

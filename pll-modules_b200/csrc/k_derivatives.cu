@@ -457,6 +457,12 @@ bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_cl
     return false;
   }
   if (!dev_sync_inputs(c) || !dev_sync_eigen(c, params_indices)) return false;
+  if (p->states == 20 && p->states_padded == 20 && !(p->attributes & PLL_ATTRIB_RATE_SCALERS) && K <= 8)
+  {
+    /* the tip (if any) takes the "parent" role (derivatives.c:66-78) */
+    const unsigned int first = ctip ? child_clv : parent_clv, second = ctip ? parent_clv : child_clv;
+    return launch_sumtable_aa(c, ptip || ctip, first, second, params_indices, d_sumtable);
+  }
   SumArgs a;
   memset(&a, 0, sizeof(a));
   if (ptip || ctip)

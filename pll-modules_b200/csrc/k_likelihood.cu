@@ -179,6 +179,123 @@ __global__ void __launch_bounds__(LK_THREADS) logl_dna_kernel(LoglArgs a)
   grid_reduce_finish<1>(v, a.red);
 }
 
+/* ---- 20-state path (protein) ------------------------------------------------------------------
+ * thread = (site, category) like the 4-state kernel; the child's 20 values (or the tip mask as 0/1) and
+ * the parent's sit in registers (5 + 5 256-bit loads), the K P-matrices in shared memory with a row
+ * pitch that puts the K categories on different banks, so that the 10 LDS.128 of a matrix row are
+ * conflict-free broadcasts.  400 FMA + 200 LDS.128 per (site, category): 1292 B/site (ii) stay the
+ * bound at ~6 TB/s (the generic kernel re-read matrix and child from L1 400 times: 0.3 TB/s). */
+#define LKA_THREADS 128
+#define LKA_KPITCH 404 /* doubles between the matrices of two categories: 808 words = 8 banks apart */
+
+template <int K, bool ROOT>
+__global__ void __launch_bounds__(LKA_THREADS) logl_aa_kernel(LoglArgs a)
+{
+  __shared__ __align__(16) double s_mat[K * LKA_KPITCH];
+  __shared__ double s_freq[K * 20];
+  if (!ROOT)
+    for (int i = threadIdx.x; i < 400 * K; i += blockDim.x) s_mat[(i / 400) * LKA_KPITCH + i % 400] = a.pmat[i];
+  for (int i = threadIdx.x; i < 20 * K; i += blockDim.x)
+    s_freq[i] = a.eigen[(unsigned long long)a.freq_idx[i / 20] * a.eigen_stride + 2 * 20 * 20 + 20 + i % 20];
+  __syncthreads();
+
+  const int lane = threadIdx.x & 31;
+  const int k = lane % K;
+  const double wk = a.w[k], pinv = a.pinv[k];
+  const double * fk = s_freq + k * 20;
+  const double * mk = s_mat + k * LKA_KPITCH;
+  const unsigned long long E = (unsigned long long)a.sites * K;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  const unsigned long long Eround = (E + 31) / 32 * 32;
+  double acc = 0.0;
+
+  for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < Eround;
+       e += stride)
+  {
+    const bool act = e < E;
+    const unsigned long long site = e / K;
+    double term = 0.0, tinv = 0.0;
+    unsigned int sc = 0;
+    if (act)
+    {
+      d4 p[5], c[5];
+#pragma unroll
+      for (int q = 0; q < 5; ++q) p[q] = ldg256(a.pclv + e * 20 + q * 4);
+      if (!ROOT)
+      {
+        if (a.ctip)
+        {
+          const unsigned long long m = a.tipmap[a.ctip[site]];
+#pragma unroll
+          for (int q = 0; q < 5; ++q)
+          {
+            c[q].x = (double)((m >> (4 * q)) & 1ull);
+            c[q].y = (double)((m >> (4 * q + 1)) & 1ull);
+            c[q].z = (double)((m >> (4 * q + 2)) & 1ull);
+            c[q].w = (double)((m >> (4 * q + 3)) & 1ull);
+          }
+        }
+        else
+        {
+#pragma unroll
+          for (int q = 0; q < 5; ++q) c[q] = ldg256(a.cclv + e * 20 + q * 4);
+        }
+      }
+      const double * pp = reinterpret_cast<const double *>(p);
+#pragma unroll
+      for (int i = 0; i < 20; ++i)
+      {
+        double tb = 1.0;
+        if (!ROOT)
+        {
+          const d2 * row = reinterpret_cast<const d2 *>(mk + i * 20);
+          double t0 = 0.0, t1 = 0.0;
+#pragma unroll
+          for (int q = 0; q < 5; ++q)
+          {
+            const d2 r0 = row[2 * q], r1 = row[2 * q + 1];
+            t0 += r0.x * c[q].x + r0.y * c[q].y;
+            t1 += r1.x * c[q].z + r1.y * c[q].w;
+          }
+          tb = t0 + t1;
+        }
+        term += pp[i] * fk[i] * tb;
+      }
+      if (k == 0)
+      {
+        if (a.pscaler) sc += a.pscaler[site];
+        if (a.cscaler) sc += a.cscaler[site];
+      }
+    }
+    if (pinv > 0.0)
+    {
+      term = wk * term * (1.0 - pinv);
+      if (act && a.invariant)
+      {
+        const int inv = a.invariant[site];
+        if (inv >= 0) tinv = wk * fk[inv] * pinv;
+      }
+    }
+    else
+      term = term * wk;
+#pragma unroll
+    for (int off = 1; off < K; off <<= 1)
+    {
+      term += __shfl_xor_sync(0xffffffffu, term, off);
+      tinv += __shfl_xor_sync(0xffffffffu, tinv, off);
+    }
+    if (act && k == 0)
+    {
+      double lk = site_finish(term, tinv, sc, ROOT);
+      lk *= (double)a.weights[site];
+      if (a.persite) a.persite[site] = lk;
+      acc += lk;
+    }
+  }
+  double v[1] = {acc};
+  grid_reduce_finish<1>(v, a.red);
+}
+
 /* ---- generic path --------------------------------------------------------------------------- */
 #define LKG_THREADS 128
 
@@ -449,6 +566,22 @@ static bool dispatch_logl(PartCtx * c, const LoglArgs & a)
       case 2: logl_dna_kernel<2, ROOT><<<(unsigned)blocks, LK_THREADS, 0, c->stream>>>(a); break;
       case 4: logl_dna_kernel<4, ROOT><<<(unsigned)blocks, LK_THREADS, 0, c->stream>>>(a); break;
       default: logl_dna_kernel<8, ROOT><<<(unsigned)blocks, LK_THREADS, 0, c->stream>>>(a); break;
+    }
+  }
+  else if (a.states == 20 && a.sp == 20 && !a.rate_scalers && (K == 1 || K == 2 || K == 4 || K == 8))
+  {
+    const unsigned long long E = (unsigned long long)a.sites * K;
+    unsigned long long blocks = (E + LKA_THREADS - 1) / LKA_THREADS;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 4;
+    if (blocks > cap) blocks = cap;
+    if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+    if (blocks < 1) blocks = 1;
+    switch (K)
+    {
+      case 1: logl_aa_kernel<1, ROOT><<<(unsigned)blocks, LKA_THREADS, 0, c->stream>>>(a); break;
+      case 2: logl_aa_kernel<2, ROOT><<<(unsigned)blocks, LKA_THREADS, 0, c->stream>>>(a); break;
+      case 4: logl_aa_kernel<4, ROOT><<<(unsigned)blocks, LKA_THREADS, 0, c->stream>>>(a); break;
+      default: logl_aa_kernel<8, ROOT><<<(unsigned)blocks, LKA_THREADS, 0, c->stream>>>(a); break;
     }
   }
   else
