@@ -163,6 +163,7 @@ def main():
         print(json.dumps(line))
         return 0
 
+    os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries exactly one JSON line
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -196,6 +197,12 @@ def main():
 
     if world > 1:
         h.set_reduce_cb(reduce_cb)
+        if os.environ.get("PLLB200_EXCHANGE", "1") != "0":
+            # device-side exchange for the fused Newton kernel: all-gather the CUDA IPC handles once
+            mine = torch.frombuffer(bytearray(pkg.exchange_create(h.partition_ptr(0))), dtype=torch.uint8).cuda()
+            every = [torch.empty_like(mine) for _ in range(world)]
+            dist.all_gather(every, mine)
+            pkg.exchange_connect(h.partition_ptr(0), rank, world, b"".join(bytes(t.cpu().numpy()) for t in every))
 
     ll0 = h.loglh(0)            # first full evaluation: uploads tips, builds everything
     setup_s = time.perf_counter() - t_setup

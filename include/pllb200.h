@@ -956,6 +956,15 @@ int pllb200_newton_branch_queued(pll_partition_t * partition, const unsigned int
                                  unsigned int matrix_index, int use_device_x0, int revert_on_limit);
 int pllb200_newton_collect(pll_partition_t * partition, const unsigned int * matrix_indices,
                            unsigned int count, double * lengths, int * status);
+/* Multi-GPU (one process per GPU, sites sharded): let the fused Newton kernel sum (d_f, dd_f) over the
+ * ranks itself through NVLink peer memory instead of one host callback per iteration.  Every rank calls
+ * exchange_create (64-byte CUDA IPC handle out), the handles are all-gathered by the caller (MPI,
+ * torch.distributed, ...) and passed to exchange_connect in rank order (<= 8 ranks of one node).  With an
+ * exchange in place pllmod_opt_optimize_branch_lengths_local_multi uses the fused kernel even though a
+ * parallel_reduce_cb is set (the callback still serves the log-likelihood sums). */
+int pllb200_exchange_create(pll_partition_t * partition, void * ipc_handle_out);
+int pllb200_exchange_connect(pll_partition_t * partition, int rank, int nranks, const void * all_handles);
+int pllb200_exchange_ranks(pll_partition_t * partition);
 /* Device address (as integer) of the partition's most recent reduction results
  * {logL, d_f, dd_f}: lets a caller run an NCCL all-reduce on them without a host round trip. */
 uint64_t pllb200_result_device_ptr(pll_partition_t * partition);

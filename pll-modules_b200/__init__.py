@@ -37,6 +37,9 @@ def load():
         lib.pllb200_partition_set_stream.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
         lib.pllb200_partition_synchronize.argtypes = [ctypes.c_void_p]
         lib.pllb200_set_device.argtypes = [ctypes.c_int]
+        lib.pllb200_exchange_create.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+        lib.pllb200_exchange_connect.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p]
+        lib.pllb200_exchange_ranks.argtypes = [ctypes.c_void_p]
         _lib = lib
     return _lib
 
@@ -62,6 +65,21 @@ def reset_stats():
 
 def set_option(name, value):
     return load().pllb200_set_option(name.encode(), int(value))
+
+
+def exchange_create(partition_ptr):
+    """CUDA IPC handle (64 bytes) of this rank's exchange buffer for the multi-GPU Newton kernel."""
+    buf = ctypes.create_string_buffer(64)
+    if not load().pllb200_exchange_create(partition_ptr, buf):
+        raise RuntimeError("pllb200_exchange_create failed")
+    return buf.raw
+
+
+def exchange_connect(partition_ptr, rank, nranks, handles):
+    """handles: the ranks' 64-byte handles concatenated in rank order."""
+    assert len(handles) == 64 * nranks
+    if not load().pllb200_exchange_connect(partition_ptr, rank, nranks, ctypes.c_char_p(handles)):
+        raise RuntimeError("pllb200_exchange_connect failed")
 
 
 def declared_symbols():

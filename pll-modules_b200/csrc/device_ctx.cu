@@ -115,7 +115,9 @@ bool dev_ctx_init(PartCtx * c)
 
   c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr;
   c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
-  c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->d_sumfrag = nullptr; c->h_stage = nullptr; c->d_stage = nullptr;
+  c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->d_sumfrag = nullptr;
+  for (int r = 0; r < 8; ++r) c->xchg_peer[r] = nullptr;
+  c->xchg_rank = 0; c->xchg_nranks = 0; c->h_stage = nullptr; c->d_stage = nullptr;
   c->d_partials = nullptr; c->d_ticket = nullptr; c->d_result = nullptr; c->h_result = nullptr;
   c->own_stream = nullptr;
 
@@ -208,7 +210,12 @@ void dev_ctx_destroy(PartCtx * c)
   c->sumtables.clear();
   cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
-  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag); cudaFree(c->d_stage); cudaFree(c->d_partials);
+  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag);
+  for (int r = 0; r < 8; ++r)
+    if (c->xchg_peer[r])
+    {
+      if (c->xchg_nranks > 0 && r != c->xchg_rank) cudaIpcCloseMemHandle(c->xchg_peer[r]); else cudaFree(c->xchg_peer[r]);
+    } cudaFree(c->d_stage); cudaFree(c->d_partials);
   cudaFree(c->d_ticket); cudaFree(c->d_result);
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->h_result) cudaFreeHost(c->h_result);
@@ -459,6 +466,70 @@ extern "C" int pllb200_upload_scaler(pll_partition_t * p, unsigned int scaler_in
   return upload_big(c, scaler_dev(c, (int)scaler_index), src, sizeof(unsigned int) * c->scaler_elems)
              ? PLL_SUCCESS
              : PLL_FAILURE;
+}
+
+/* ---- multi-GPU exchange buffers (one process per GPU, CUDA IPC over NVLink/NVSwitch) ---------- */
+
+#define XCHG_BYTES 1024 /* NW_XCHG_DOUBLES * 8, rounded up */
+
+extern "C" int pllb200_exchange_create(pll_partition_t * p, void * ipc_handle_out)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (c->xchg_nranks != 0)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "exchange_create: the partition is already connected.");
+    return PLL_FAILURE;
+  }
+  if (!c->xchg_peer[0])
+  {
+    double * buf = nullptr;
+    CUDA_TRY(cudaMalloc(&buf, XCHG_BYTES), PLL_FAILURE);
+    CUDA_TRY(cudaMemset(buf, 0, XCHG_BYTES), PLL_FAILURE);
+    c->xchg_peer[0] = buf; /* parked in slot 0 until the rank is known */
+    c->xchg_rank = 0;
+    c->xchg_nranks = 0;
+  }
+  cudaIpcMemHandle_t h;
+  CUDA_TRY(cudaIpcGetMemHandle(&h, c->xchg_peer[0]), PLL_FAILURE);
+  static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+  memcpy(ipc_handle_out, &h, sizeof(h));
+  return PLL_SUCCESS;
+}
+
+extern "C" int pllb200_exchange_connect(pll_partition_t * p, int rank, int nranks, const void * all_handles)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  PartCtx * c = ctx_of(p);
+  if (nranks < 1 || nranks > 8 || rank < 0 || rank >= nranks || !c->xchg_peer[0] || c->xchg_nranks != 0)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "exchange_connect: need 1..8 ranks and a buffer from exchange_create.");
+    return PLL_FAILURE;
+  }
+  double * own = c->xchg_peer[0];
+  c->xchg_peer[0] = nullptr;
+  for (int r = 0; r < nranks; ++r)
+  {
+    if (r == rank)
+    {
+      c->xchg_peer[r] = own;
+      continue;
+    }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char *)all_handles + (size_t)r * sizeof(h), sizeof(h));
+    void * ptr = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess), PLL_FAILURE);
+    c->xchg_peer[r] = (double *)ptr;
+  }
+  c->xchg_rank = rank;
+  c->xchg_nranks = nranks;
+  return PLL_SUCCESS;
+}
+
+extern "C" int pllb200_exchange_ranks(pll_partition_t * p)
+{
+  if (!p || ctx_of(p)->magic != PLLB200_MAGIC) return 0;
+  return ctx_of(p)->xchg_nranks;
 }
 
 extern "C" int pllb200_download_sumtable(pll_partition_t * p, const double * key, double * dst)

@@ -61,6 +61,9 @@ struct PartCtx
   unsigned long long * d_tipmap;
   double * d_persite;         /* lazily allocated, sites doubles */
   double * d_ancestral;       /* lazily allocated, sites*states doubles (pll_compute_node_ancestral) */
+  /* multi-GPU exchange for the fused Newton kernel (k_newton.cu): own buffer + peers' IPC mappings */
+  double * xchg_peer[8];
+  int xchg_rank, xchg_nranks;
   double * d_sumfrag;         /* lazily allocated: 20-state sumtable matrices as DMMA fragment images */
   std::vector<unsigned long long> sumfrag_key;
   double * d_brlen;           /* lazily allocated, [prob_matrices][4]: queued Newton results (k_newton.cu) */

@@ -29,6 +29,7 @@ namespace cg = cooperative_groups;
 
 #define NW_THREADS 256
 #define NW_MAXK 32
+#define NW_MAXRANKS 8
 #define NW_MAX_DIAG 512 /* K * states */
 
 /* status codes returned in result[1] */
@@ -55,7 +56,86 @@ struct NewtonArgs
    * branch in device memory; the start value comes from there when the branch was already visited */
   double * brlen_io;
   int x0_from_device, revert_on_limit;
+  /* multi-GPU (site-sharded ranks, one process per GPU): every pass ends with an all-gather of the local
+   * (d_f, dd_f) over NVLink peer memory instead of a host callback.  inbox[r] is rank r's exchange
+   * buffer (own: local pointer, others: CUDA IPC mappings): [2 parities][8 ranks]{f, df, seq, -} then the
+   * local mailbox [2]{f, df, seq, -} and the running pass counter. */
+  int rank, nranks;
+  double * inbox[NW_MAXRANKS];
 };
+
+#define NW_XCHG_MAIL 64  /* doubles: offset of the local mailbox inside an exchange buffer */
+#define NW_XCHG_COUNTER 72
+#define NW_XCHG_DOUBLES 80
+#define NW_SPIN_LIMIT 40000000ull /* tens of seconds: a rank that never shows up must not hang the GPU */
+
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long * p)
+{
+  unsigned long long v;
+  asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long * p, unsigned long long v)
+{
+  asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_gpu(const unsigned long long * p)
+{
+  unsigned long long v;
+  asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(unsigned long long * p, unsigned long long v)
+{
+  asm volatile("st.release.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+/* Called by ONE thread per CTA with this rank's totals: CTA 0 pushes them into every rank's inbox, waits
+ * for all ranks' values in its own inbox, adds them in rank order (identical on every GPU) and leaves the
+ * result in the local mailbox, where the other CTAs pick it up.  `pass` is the running pass number (same
+ * on all ranks, alternating parity => a slot is rewritten only after everybody has read it).  Returns
+ * false if a peer did not answer. */
+__device__ __forceinline__ bool newton_allgather(const NewtonArgs & a, unsigned long long pass, double & t1,
+                                                 double & t2)
+{
+  const unsigned int par = (unsigned int)(pass & 1ull);
+  double * own = a.inbox[a.rank];
+  double * mail = own + NW_XCHG_MAIL + par * 4;
+  unsigned long long spins = 0;
+  if (blockIdx.x == 0)
+  {
+    for (int r = 0; r < a.nranks; ++r)
+    {
+      double * slot = a.inbox[r] + (par * NW_MAXRANKS + a.rank) * 4;
+      slot[0] = t1;
+      slot[1] = t2;
+    }
+    __threadfence_system();
+    for (int r = 0; r < a.nranks; ++r)
+      st_release_sys(reinterpret_cast<unsigned long long *>(a.inbox[r] + (par * NW_MAXRANKS + a.rank) * 4 + 2), pass);
+    double g1 = 0.0, g2 = 0.0;
+    for (int r = 0; r < a.nranks; ++r)
+    {
+      const double * slot = own + (par * NW_MAXRANKS + r) * 4;
+      while (ld_acquire_sys(reinterpret_cast<const unsigned long long *>(slot + 2)) != pass)
+        if (++spins > NW_SPIN_LIMIT) return false;
+      g1 += slot[0];
+      g2 += slot[1];
+    }
+    mail[0] = g1;
+    mail[1] = g2;
+    __threadfence();
+    st_release_gpu(reinterpret_cast<unsigned long long *>(mail + 2), pass);
+    t1 = g1;
+    t2 = g2;
+    return true;
+  }
+  while (ld_acquire_gpu(reinterpret_cast<const unsigned long long *>(mail + 2)) != pass)
+    if (++spins > NW_SPIN_LIMIT) return false;
+  t1 = mail[0];
+  t2 = mail[1];
+  return true;
+}
 
 /* what the host does with a result (pll_optimize.c:1524-1560), for the queued mode: an unconverged or
  * failed branch keeps its old length, and so does a change below 1e-10 */
@@ -100,6 +180,9 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
   /* optimiser state, replicated in every thread (all threads see the same f, df) */
   double xl = a.xmin, xh = a.xmax;
   const double xorig = (a.brlen_io && a.x0_from_device) ? __ldcg(a.brlen_io) : a.x0;
+  /* passes done by earlier launches (device-resident: the host does not know how many a launch needs) */
+  const unsigned long long pass0 =
+      a.nranks > 1 ? __ldcg(reinterpret_cast<const unsigned long long *>(a.inbox[a.rank] + NW_XCHG_COUNTER)) : 0ull;
   double x = fmax(fmin(xorig, a.xmax), a.xmin);
   const double dxmax = a.xmax / a.max_iters;
   unsigned int iter = 0;
@@ -329,6 +412,7 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
       }
       if (lane == 0)
       {
+        if (a.nranks > 1 && !newton_allgather(a, pass0 + iter, t1, t2)) t1 = t2 = nan("");
         s_tot[0] = t1;
         s_tot[1] = t2;
       }
@@ -366,6 +450,9 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
   if (blockIdx.x == 0 && threadIdx.x == 0)
   {
     newton_publish(a, x, xorig, status, iter);
+    if (a.nranks > 1) /* passes really made: the iteration-limit exit counted one it did not run */
+      *reinterpret_cast<unsigned long long *>(a.inbox[a.rank] + NW_XCHG_COUNTER) =
+          pass0 + iter - (status == NW_LIMIT ? 1u : 0u);
     a.result_dev[0] = x;
     a.result_dev[1] = status;
     a.result_dev[2] = (double)iter;
@@ -443,6 +530,9 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
 
   double xl = a.xmin, xh = a.xmax;
   const double xorig = (a.brlen_io && a.x0_from_device) ? __ldcg(a.brlen_io) : a.x0;
+  /* passes done by earlier launches (device-resident: the host does not know how many a launch needs) */
+  const unsigned long long pass0 =
+      a.nranks > 1 ? __ldcg(reinterpret_cast<const unsigned long long *>(a.inbox[a.rank] + NW_XCHG_COUNTER)) : 0ull;
   double x = fmax(fmin(xorig, a.xmax), a.xmin);
   const double dxmax = a.xmax / a.max_iters;
   unsigned int iter = 0;
@@ -623,6 +713,7 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
       }
       if (lane == 0)
       {
+        if (a.nranks > 1 && !newton_allgather(a, pass0 + iter, t1, t2)) t1 = t2 = nan("");
         sm.tot[0] = t1;
         sm.tot[1] = t2;
       }
@@ -664,6 +755,9 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
   if (b == 0 && tid == 0)
   {
     newton_publish(a, x, xorig, status, iter);
+    if (a.nranks > 1) /* passes really made: the iteration-limit exit counted one it did not run */
+      *reinterpret_cast<unsigned long long *>(a.inbox[a.rank] + NW_XCHG_COUNTER) =
+          pass0 + iter - (status == NW_LIMIT ? 1u : 0u);
     a.result_dev[0] = x;
     a.result_dev[1] = status;
     a.result_dev[2] = (double)iter;
@@ -741,6 +835,9 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   a.partials = c->d_partials;
   a.result_dev = c->d_result + slot * 4;
   a.result_host = c->h_result_dev + slot * 4;
+  a.rank = c->xchg_rank;
+  a.nranks = c->xchg_nranks > 1 ? c->xchg_nranks : 1;
+  for (int r = 0; r < a.nranks && r < NW_MAXRANKS; ++r) a.inbox[r] = c->xchg_peer[r];
   a.brlen_io = brlen_io;
   a.x0_from_device = x0_from_device;
   a.revert_on_limit = revert_on_limit;

@@ -538,7 +538,8 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
       /* one local partition and nothing to reduce across ranks: the whole iteration runs on the
        * device (k_newton.cu); otherwise one derivative pass per iteration and partition */
       int fused = -2;
-      if (xnum == 1 && prm->partition_count == 1 && prm->partitions[0] && !prm->parallel_reduce_cb)
+      if (xnum == 1 && prm->partition_count == 1 && prm->partitions[0] &&
+          (!prm->parallel_reduce_cb || pllb200_exchange_ranks(prm->partitions[0]) > 1))
       {
         pll_errno = 0;
         const double s = prm->brlen_scalers ? prm->brlen_scalers[0] : 1.;
@@ -729,7 +730,8 @@ extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
   {
     /* queue whole passes when nothing between two branches needs a number on the host */
     const bool can_queue = keep_update && opt_method == PLLMOD_OPT_BLO_NEWTON_FAST && partition_count == 1 &&
-                           partitions[0] && !parallel_reduce_cb && g_opt_fused_newton != 0 &&
+                           partitions[0] && (!parallel_reduce_cb || pllb200_exchange_ranks(partitions[0]) > 1) &&
+                           g_opt_fused_newton != 0 &&
                            g_opt_queued_newton != 0;
     unsigned int iters = (unsigned int)max_iters;
     while (iters)
