@@ -331,13 +331,29 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
           else
           {
             const double * sm = a.sum + e * sp;
-            for (unsigned int j = 0; j < s; ++j)
+            if (s == 20)
             {
-              const double sv = sm[j];
-              L0 += sv * dg[j * 3 + 0];
-              L1 += sv * dg[j * 3 + 1];
-              L2 += sv * dg[j * 3 + 2];
+              /* protein: the element's 160 bytes as five 256-bit loads, all in flight before the first FMA */
+              d4 q[5];
+#pragma unroll
+              for (int c = 0; c < 5; ++c) q[c] = ldg256(sm + 4 * c);
+#pragma unroll
+              for (int c = 0; c < 5; ++c)
+              {
+                const double * g = dg + 12 * c;
+                L0 += q[c].x * g[0] + q[c].y * g[3] + q[c].z * g[6] + q[c].w * g[9];
+                L1 += q[c].x * g[1] + q[c].y * g[4] + q[c].z * g[7] + q[c].w * g[10];
+                L2 += q[c].x * g[2] + q[c].y * g[5] + q[c].z * g[8] + q[c].w * g[11];
+              }
             }
+            else
+              for (unsigned int j = 0; j < s; ++j)
+              {
+                const double sv = sm[j];
+                L0 += sv * dg[j * 3 + 0];
+                L1 += sv * dg[j * 3 + 1];
+                L2 += sv * dg[j * 3 + 2];
+              }
           }
           if (pinv > 0.0)
           {
