@@ -249,6 +249,56 @@ def test_large_full_size_properties():
             assert rel(h.loglh(), full) < 1e-9
 
 
+def test_baseline_c2_full_size_properties():
+    """BASELINE.json configs[1] at its real size (1000 taxa x 1 M sites, 128 GB of CLVs): the CPU oracle cannot
+    hold it, so parity goes through size-independent properties — logL is additive over site slices, one
+    slice is checked against the reference itself, logL does not depend on the root, and a Newton-Raphson
+    smoothing pass over all 1997 branches does not lose likelihood."""
+    import torch
+    if torch.cuda.get_device_properties(0).total_memory < 150e9:
+        pytest.skip("needs the 180 GB of a B200")
+    kw = dict(tips=1000, sites=1000000)
+    with Harness("b200", **kw) as h:
+        full = h.loglh()
+        for node in (kw["tips"] + 5, kw["tips"] + 1501):
+            h.set_root(node)
+            assert rel(h.loglh(), full) < 1e-9
+        nll = h.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=1, lh_epsilon=1.0)
+        assert -nll > full
+        assert rel(h.loglh(), -nll) < 1e-9
+    parts = []
+    for r in range(4):
+        with Harness("b200", rank=r, nranks=4, **kw) as s:
+            parts.append(s.loglh())
+    assert rel(sum(parts), full) < 1e-10
+    if have_reference():
+        with Harness("ref", rank=7, nranks=40, **kw) as r, Harness("b200", rank=7, nranks=40, **kw) as d:
+            assert r.sites == d.sites == [25000]
+            assert rel(d.loglh(), r.loglh()) < 1e-8
+
+
+def test_baseline_c3_full_size_properties():
+    """BASELINE.json configs[2] at its real size (protein LG+G4, 500 taxa x 200 k sites, 64 GB of CLVs):
+    additive over site slices, independent of the root, one slice against the reference."""
+    import torch
+    if torch.cuda.get_device_properties(0).total_memory < 100e9:
+        pytest.skip("needs a B200-sized memory")
+    kw = dict(tips=500, sites=200000, states=20)
+    with Harness("b200", **kw) as h:
+        full = h.loglh()
+        h.set_root(kw["tips"] + 701)
+        assert rel(h.loglh(), full) < 1e-9
+    parts = []
+    for r in range(2):
+        with Harness("b200", rank=r, nranks=2, **kw) as s:
+            parts.append(s.loglh())
+    assert rel(sum(parts), full) < 1e-10
+    if have_reference():
+        with Harness("ref", rank=3, nranks=50, **kw) as r, Harness("b200", rank=3, nranks=50, **kw) as d:
+            assert r.sites == d.sites == [4000]
+            assert rel(d.loglh(), r.loglh()) < 1e-8
+
+
 # ---- model-parameter optimisers over device-resident state (SURVEY.md §8a rows a13/a14) ----
 OPT_GOLD = json.load(open(os.path.join(ROOT, "tests", "golden", "ref_opt.json")))
 
