@@ -72,6 +72,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
   else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;
   else if (!strcmp(name, "queued_newton")) slot = &g_opt_queued_newton;
+  else if (!strcmp(name, "trav_prefetch")) slot = &g_opt_trav_prefetch;
   else if (!strcmp(name, "aa_variant")) slot = &g_opt_aa_variant;
   if (!slot) return -1;
   int old = *slot;

@@ -126,6 +126,7 @@ extern int g_opt_trav_reorder;
 extern int g_opt_fuse_root;
 extern int g_opt_trav_variant;
 extern int g_opt_trav_forward;
+extern int g_opt_trav_prefetch;
 extern int g_opt_fused_newton;
 extern int g_opt_queued_newton;
 extern int g_opt_aa_variant;

@@ -57,6 +57,7 @@ struct TravArgs
   unsigned int * scaler;
   const double * pmat_il;
   const unsigned char * tipchars;
+  int l2_prefetch; /* ask L2 for the next op's children that are neither tips nor forwarded in registers */
 };
 
 #define TRAV_WARPS 8
@@ -240,6 +241,18 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
       if (fn & OPF_TIP1) n1 = load_tips(a.tipchars + sm.ops[o + 1].c1_off + s0);
       if (fn & OPF_TIP2) n2 = load_tips(a.tipchars + sm.ops[o + 1].c2_off + s0);
     }
+    /* inner children of the NEXT op that will not come out of registers: one 128-byte line per lane
+     * covers the warp's 4 KB of each child.  Costs no register; turns the DRAM miss that op o+1 would
+     * wait for (ncu: 15 % of the stall samples sit on the first use of those loads) into an L2 hit. */
+    if (FULL && R == 4 && K == 4 && a.l2_prefetch && o + 1 < nseg)
+    {
+      const DevOp & nx = sm.ops[o + 1];
+      const unsigned long long woff = (unsigned long long)(s0 - (unsigned int)(lane / K) * R) * ESTEP + lane * 16;
+      if (!(nx.flags & (OPF_TIP1 | OPF_FWD1)))
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.clv + nx.c1_off + woff));
+      if (!(nx.flags & (OPF_TIP2 | OPF_FWD2)))
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.clv + nx.c2_off + woff));
+    }
     /* child scaler counts (the lanes that own a scaler entry only): the loads are issued here, the
      * counts are only combined when the parent scaler is written, after the arithmetic (ncu: adding
      * them right away exposed the full L2 latency, 22 % of all stall samples) */
@@ -401,6 +414,7 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArg
 
 int g_opt_trav_variant = 0;
 int g_opt_trav_forward = 1;
+int g_opt_trav_prefetch = 0; /* measured: 28.3 ms with, 27.9 ms without at C2 — the kernel is not waiting on DRAM latency */
 
 template <int K, int R, bool RS, int MINB>
 static bool launch_variant(PartCtx * c, const TravArgs & a)
@@ -519,6 +533,7 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
   a.scaler = c->d_scaler;
   a.pmat_il = c->d_pmat_il;
   a.tipchars = c->d_tipchars;
+  a.l2_prefetch = g_opt_trav_prefetch;
   switch (K)
   {
     case 1: return launch_k<1>(c, a, rate_scalers);
