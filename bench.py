@@ -321,10 +321,14 @@ def main():
                     "what": "host tree with new branch lengths -> pllmod_treeinfo_compute_loglh -> logL on host"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": 27.816e9 * S / 200000.0,
+                         "traffic": 27.766e9 * S / 200000.0,
                          "traffic_note": "dram__bytes_read+write of one ncu --set full capture at 200k sites "
                                          "(profiles/r01_trav_dna_ncu_full_summary.csv), scaled linearly in sites "
                                          "(a 400k-site capture agrees); a 1M-site launch cannot be replayed by ncu",
+                         # frac > 1 is possible: children written a few ops earlier are re-read from registers /
+                         # L1 / L2, so the kernel moves about half of the algorithmic bytes through DRAM
+                         "dram_GBps": 27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9,
+                         "frac_dram": 27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9 / peak,
                          "peak_kind": peak_kind, "kernel": "trav_dna_kernel<4,false>",
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kern_avg,
                          "kernel_share_of_step": kern_avg / dev_ms},
