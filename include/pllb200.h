@@ -918,6 +918,9 @@ int pllb200_download_sumtable(pll_partition_t * partition, const double * sumtab
 int pllb200_sync_host_arrays(pll_partition_t * partition);
 /* Wait for all queued device work of the partition. */
 int pllb200_partition_synchronize(pll_partition_t * partition);
+/* Wait only for the results queued by the *_async calls (polls their completion tags in mapped host
+ * memory: no stream synchronisation) and deliver them to the addresses given at queue time. */
+int pllb200_partition_wait_results(pll_partition_t * partition);
 /* Run the partition's kernels on a caller-provided CUDA stream (cudaStream_t passed as void*),
  * e.g. torch.cuda.current_stream().cuda_stream.  NULL restores the partition's own stream. */
 int pllb200_partition_set_stream(pll_partition_t * partition, void * cuda_stream);

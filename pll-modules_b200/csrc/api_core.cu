@@ -66,7 +66,8 @@ static double finish_scalar(PartCtx * c, int slot, double * persite_lnl, double 
       return -INFINITY;
     g_d2h_bytes += sizeof(double) * c->pub.sites;
   }
-  if (!dev_flush(c)) return -INFINITY;
+  /* with a per-site copy queued behind the kernel the stream has to drain; otherwise poll the tag */
+  if (persite_lnl ? !dev_flush(c) : !(dev_wait_results(c) && dev_wait_slot(c, slot))) return -INFINITY;
   g_d2h_bytes += sizeof(double);
   return c->h_result[slot * 4];
 }
@@ -258,7 +259,7 @@ extern "C" int pllb200_newton_branch(pll_partition_t * partition, const unsigned
   const int slot = dev_alloc_slot(c);
   if (!launch_newton(c, params_indices, d, xmin, xguess, xmax, tolerance, max_iters, brlen_scaler, slot))
     return -1;
-  if (!dev_flush(c)) return -1;
+  if (!dev_wait_results(c) || !dev_wait_slot(c, slot)) return -1;
   g_d2h_bytes += 4 * sizeof(double);
   const double * r = c->h_result + slot * 4;
   *x_out = r[0];
@@ -378,7 +379,7 @@ extern "C" int pll_compute_likelihood_derivatives(pll_partition_t * partition,
   if (!launch_derivatives(c, parent_scaler_index, child_scaler_index, branch_length,
                           params_indices, d, slot))
     return PLL_FAILURE;
-  if (!dev_flush(c)) return PLL_FAILURE;
+  if (!dev_wait_results(c) || !dev_wait_slot(c, slot)) return PLL_FAILURE;
   g_d2h_bytes += 2 * sizeof(double);
   *d_f = c->h_result[slot * 4 + 0];
   *dd_f = c->h_result[slot * 4 + 1];

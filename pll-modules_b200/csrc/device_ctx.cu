@@ -194,9 +194,15 @@ bool dev_ctx_init(PartCtx * c)
   CUDA_TRY(cudaMemsetAsync(c->d_ticket, 0, sizeof(unsigned int) * 4, c->stream), false);
   CUDA_TRY(cudaMalloc(&c->d_result, sizeof(double) * 4 * PLLB200_RESULT_SLOTS), false);
   CUDA_TRY(cudaMemsetAsync(c->d_result, 0, sizeof(double) * 4 * PLLB200_RESULT_SLOTS, c->stream), false);
-  CUDA_TRY(cudaHostAlloc(&c->h_result, sizeof(double) * 4 * PLLB200_RESULT_SLOTS,
+  /* results and, behind them, one completion tag per slot */
+  CUDA_TRY(cudaHostAlloc(&c->h_result, (sizeof(double) * 4 + sizeof(unsigned long long)) * PLLB200_RESULT_SLOTS,
                          cudaHostAllocMapped), false);
+  memset(c->h_result, 0, (sizeof(double) * 4 + sizeof(unsigned long long)) * PLLB200_RESULT_SLOTS);
   CUDA_TRY(cudaHostGetDevicePointer(&c->h_result_dev, c->h_result, 0), false);
+  c->h_tag = reinterpret_cast<volatile unsigned long long *>(c->h_result + 4 * PLLB200_RESULT_SLOTS);
+  c->h_tag_dev = reinterpret_cast<unsigned long long *>(c->h_result_dev + 4 * PLLB200_RESULT_SLOTS);
+  memset(c->slot_tag, 0, sizeof(c->slot_tag));
+  c->tag_counter = 0;
   c->next_slot = 0;
   CUDA_TRY(cudaStreamSynchronize(c->stream), false);
   return true;
@@ -351,7 +357,50 @@ int dev_alloc_slot(PartCtx * c)
   if (c->pending.size() >= PLLB200_RESULT_SLOTS - 2) dev_flush(c);
   int s = c->next_slot;
   c->next_slot = (c->next_slot + 1) % PLLB200_RESULT_SLOTS;
+  c->slot_tag[s] = ++c->tag_counter;
   return s;
+}
+
+void dev_slot_tag(PartCtx * c, int slot, unsigned long long ** tag_host, unsigned long long * tag)
+{
+  *tag_host = c->h_tag_dev + slot;
+  *tag = c->slot_tag[slot];
+}
+
+/* Poll the slot's completion tag in mapped host memory.  Every so often the stream is queried: a failed
+ * launch or a kernel fault would otherwise never show up, and an idle stream without the tag means the
+ * slot was never written. */
+bool dev_wait_slot(PartCtx * c, int slot)
+{
+  const unsigned long long want = c->slot_tag[slot];
+  for (unsigned long long spins = 0;; ++spins)
+  {
+    if (c->h_tag[slot] == want) return true;
+    if ((spins & 0x3fffull) == 0x3fffull)
+    {
+      const cudaError_t e = cudaStreamQuery(c->stream);
+      if (e == cudaErrorNotReady) continue;
+      if (e != cudaSuccess) return pllb200_cuda_ok(e, "waiting for a device result");
+      /* stream idle: the tag is there now, or nobody is going to write it */
+      if (c->h_tag[slot] == want) return true;
+      CUDA_TRY(cudaStreamSynchronize(c->stream), false);
+      return true;
+    }
+#if defined(__x86_64__)
+    __builtin_ia32_pause();
+#endif
+  }
+}
+
+bool dev_wait_results(PartCtx * c)
+{
+  if (c->pending.empty()) return true;
+  /* one stream, in-order: the last queued result is the last to arrive */
+  if (!dev_wait_slot(c, c->pending.back().slot)) return false;
+  for (const PendingResult & r : c->pending) *r.host_dst = c->h_result[r.slot * 4 + r.comp];
+  g_d2h_bytes += sizeof(double) * c->pending.size();
+  c->pending.clear();
+  return true;
 }
 
 bool dev_flush(PartCtx * c)
@@ -566,6 +615,12 @@ extern "C" int pllb200_partition_synchronize(pll_partition_t * p)
 {
   if (!check_ctx(p)) return PLL_FAILURE;
   return dev_flush(ctx_of(p)) ? PLL_SUCCESS : PLL_FAILURE;
+}
+
+extern "C" int pllb200_partition_wait_results(pll_partition_t * p)
+{
+  if (!check_ctx(p)) return PLL_FAILURE;
+  return dev_wait_results(ctx_of(p)) ? PLL_SUCCESS : PLL_FAILURE;
 }
 
 extern "C" int pllb200_partition_set_stream(pll_partition_t * p, void * cuda_stream)

@@ -80,6 +80,12 @@ struct PartCtx
   double * d_result;          /* PLLB200_RESULT_SLOTS*4 doubles on device */
   double * h_result;          /* same, pinned + mapped: kernels write results straight to the host */
   double * h_result_dev;      /* device alias of h_result */
+  /* completion tags, one per slot, behind the results in the same mapped allocation: a kernel writes
+   * slot_tag[slot] there after its result, the host polls (dev_wait_slot) instead of synchronising */
+  volatile unsigned long long * h_tag;
+  unsigned long long * h_tag_dev;
+  unsigned long long slot_tag[PLLB200_RESULT_SLOTS];
+  unsigned long long tag_counter;
   int next_slot;
   std::vector<PendingResult> pending;
 
@@ -137,7 +143,10 @@ void dev_ctx_destroy(PartCtx * c);
 void * dev_stage(PartCtx * c, const void * src, size_t bytes); /* returns device ptr, stream ordered */
 bool dev_sync_inputs(PartCtx * c);   /* push dirty tipchars / weights / invariant / tipmap */
 bool dev_sync_eigen(PartCtx * c, const unsigned int * params_indices); /* ensure eigen block current */
-bool dev_flush(PartCtx * c);         /* stream sync + deliver pending async results */
+bool dev_flush(PartCtx * c);            /* stream sync + deliver pending async results */
+void dev_slot_tag(PartCtx * c, int slot, unsigned long long ** tag_host, unsigned long long * tag);
+bool dev_wait_slot(PartCtx * c, int slot);
+bool dev_wait_results(PartCtx * c);  /* wait (by tag) for the last queued result, deliver all pending ones */
 int dev_alloc_slot(PartCtx * c);
 /* sumtable shadows: global key registry so pll_aligned_free(key) releases the device buffer */
 void sumtable_forget_key(const void * key);

@@ -428,7 +428,7 @@ __global__ void __launch_bounds__(ASC_THREADS) asc_deriv_kernel(DerivArgs a, uns
   a.red.result_dev[1] = ddf;
   a.red.result_host[0] = df;
   a.red.result_host[1] = ddf;
-  __threadfence_system();
+  publish_tag(a.red);
 }
 
 /* ---- host ------------------------------------------------------------------------------------ */
@@ -582,6 +582,12 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
   /* diagonal table on the host: K*s exponentials (core_derivatives.c:757-772) */
   const bool dna = s == 4 && (K == 1 || K == 2 || K == 4 || K == 8);
   const bool asc_terms = asc_type == PLL_ATTRIB_AB_LEWIS || asc_type == PLL_ATTRIB_AB_FELSENSTEIN;
+  /* completion tag: published by the kernel that touches the slot last */
+  unsigned long long * tag_host = nullptr;
+  unsigned long long tag = 0;
+  dev_slot_tag(c, slot, &tag_host, &tag);
+  a.red.tag = tag;
+  a.red.tag_host = asc_terms ? nullptr : tag_host;
   DiagDna dg;
   std::vector<double> diag;
   if (!dna || asc_terms) diag.resize((size_t)K * s * 3);
@@ -638,6 +644,7 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
   if (!pllb200_cuda_ok(cudaGetLastError(), "derivative kernel launch")) return false;
   if (asc_terms)
   {
+    a.red.tag_host = tag_host;
     if (dna)
     {
       a.diag = (const double *)dev_stage(c, diag.data(), sizeof(double) * diag.size());

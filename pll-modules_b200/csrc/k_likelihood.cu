@@ -476,7 +476,14 @@ __global__ void __launch_bounds__(ASC_THREADS) asc_logl_kernel(LoglArgs a, int r
   const double v = a.red.result_dev[0] + corr;
   a.red.result_dev[0] = v;
   a.red.result_host[0] = v;
-  __threadfence_system();
+  publish_tag(a.red);
+}
+
+/* with an ascertainment-bias correction the correction kernel is the one that completes the slot */
+static LoglArgs without_tag_if_asc(const PartCtx * c, LoglArgs a)
+{
+  if (c->pub.attributes & PLL_ATTRIB_AB_MASK) a.red.tag_host = nullptr;
+  return a;
 }
 
 static bool launch_asc_logl(PartCtx * c, const LoglArgs & a, int root)
@@ -545,6 +552,7 @@ static bool fill_common(PartCtx * c, LoglArgs & a, const unsigned int * freqs_in
   a.red.ticket = c->d_ticket;
   a.red.result_dev = c->d_result + slot * 4;
   a.red.result_host = c->h_result_dev + slot * 4;
+  dev_slot_tag(c, slot, &a.red.tag_host, &a.red.tag);
   return true;
 }
 
@@ -637,7 +645,7 @@ bool launch_edge_logl(PartCtx * c, unsigned int parent_clv, int parent_scaler,
     a.cscaler = scaler_dev(c, child_scaler);
   }
   a.pmat = c->d_pmat + (size_t)matrix_index * c->pmat_elems;
-  return dispatch_logl<false>(c, a) && launch_asc_logl(c, a, 0);
+  return dispatch_logl<false>(c, without_tag_if_asc(c, a)) && launch_asc_logl(c, a, 0);
 }
 
 bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
@@ -653,5 +661,5 @@ bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
   if (!fill_common(c, a, freqs_indices, d_persite, slot)) return false;
   a.pclv = clv_dev(c, clv_index);
   a.pscaler = scaler_dev(c, scaler_index);
-  return dispatch_logl<true>(c, a) && launch_asc_logl(c, a, 1);
+  return dispatch_logl<true>(c, without_tag_if_asc(c, a)) && launch_asc_logl(c, a, 1);
 }

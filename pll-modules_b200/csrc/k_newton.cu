@@ -52,6 +52,8 @@ struct NewtonArgs
   double * partials; /* [2 buffers][2][gridDim.x] */
   double * result_dev;
   double * result_host;
+  unsigned long long * tag_host; /* completion tag in mapped host memory, written after the result */
+  unsigned long long tag;
   /* queued mode (a whole smoothing pass without a host wait): {x, x * scale, status, iterations} of this
    * branch in device memory; the start value comes from there when the branch was already visited */
   double * brlen_io;
@@ -478,6 +480,7 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
     a.result_host[2] = (double)iter;
     a.result_host[3] = f;
     __threadfence_system();
+    *reinterpret_cast<volatile unsigned long long *>(a.tag_host) = a.tag;
   }
 }
 
@@ -783,6 +786,7 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
     a.result_host[2] = (double)iter;
     a.result_host[3] = f;
     __threadfence_system();
+    *reinterpret_cast<volatile unsigned long long *>(a.tag_host) = a.tag;
   }
 }
 
@@ -851,6 +855,7 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   a.partials = c->d_partials;
   a.result_dev = c->d_result + slot * 4;
   a.result_host = c->h_result_dev + slot * 4;
+  dev_slot_tag(c, slot, &a.tag_host, &a.tag);
   a.rank = c->xchg_rank;
   a.nranks = c->xchg_nranks > 1 ? c->xchg_nranks : 1;
   for (int r = 0; r < a.nranks && r < NW_MAXRANKS; ++r) a.inbox[r] = c->xchg_peer[r];

@@ -207,7 +207,7 @@ extern "C" double pllmod_opt_compute_edge_loglikelihood_multi(
                                              child_clv_index, child_scaler_index, matrix_index,
                                              params_indices[p], &part[p]) == PLL_SUCCESS;
   for (size_t p = 0; p < partition_count; ++p)
-    if (partitions[p]) ok &= pllb200_partition_synchronize(partitions[p]) == PLL_SUCCESS;
+    if (partitions[p]) ok &= pllb200_partition_wait_results(partitions[p]) == PLL_SUCCESS;
   if (!ok) return -INFINITY;
   double total = 0.0;
   for (size_t p = 0; p < partition_count; ++p) total += part[p];
@@ -409,7 +409,7 @@ static void multi_deriv_cb(void * parameters, double * proposal, double * df, do
   for (unsigned int p = 0; p < P; ++p)
   {
     if (!prm->partitions[p]) continue;
-    ok = pllb200_partition_synchronize(prm->partitions[p]) && ok;
+    ok = pllb200_partition_wait_results(prm->partitions[p]) && ok;
     const double s = prm->brlen_scalers ? prm->brlen_scalers[p] : 1.;
     const double p_df = ok ? pd[2 * p] : NAN, p_ddf = ok ? pd[2 * p + 1] : NAN;
     if (unlinked)

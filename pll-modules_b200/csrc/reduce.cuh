@@ -19,7 +19,18 @@ struct ReduceOut
   unsigned int * ticket;
   double * result_dev;     /* slot base: N doubles */
   double * result_host;    /* mapped host alias of the same slot */
+  /* completion tag: written to mapped host memory after the result (system-scope fence in between), so
+   * the host can poll for a result instead of paying a stream synchronisation; null = a later kernel on
+   * the stream finishes this slot (ascertainment-bias correction) */
+  unsigned long long * tag_host;
+  unsigned long long tag;
 };
+
+__device__ __forceinline__ void publish_tag(const ReduceOut & r)
+{
+  __threadfence_system();
+  if (r.tag_host) *reinterpret_cast<volatile unsigned long long *>(r.tag_host) = r.tag;
+}
 
 template <int N>
 __device__ __forceinline__ void grid_reduce_finish(double (&v)[N], const ReduceOut & r)
@@ -76,7 +87,7 @@ __device__ __forceinline__ void grid_reduce_finish(double (&v)[N], const ReduceO
     if (lane == 0)
     {
       *r.ticket = 0;
-      __threadfence_system();
+      publish_tag(r);
     }
   }
 }

@@ -655,7 +655,7 @@ static double compute_loglh(pllmod_treeinfo_t * ti, int incremental, int update_
   }
   /* one wait per partition stream, after everything has been queued */
   for (unsigned int p = 0; p < ti->partition_count; ++p)
-    if (ti->partitions[p] && !pllb200_partition_synchronize(ti->partitions[p])) failed = true;
+    if (ti->partitions[p] && !pllb200_partition_wait_results(ti->partitions[p])) failed = true;
   pllmod_treeinfo_set_active_partition(ti, old_active);
   if (failed) return LOGLH_NONE;
 
