@@ -20,6 +20,10 @@ ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/la
 # full captures of the dominant kernels
 ncu --set full --clock-control none --import-source on -k regex:trav_dna -s 1 -c 1 -o $O/trav_dna_full \
     python bench.py --sites 200000 --steps 2 --warmup 1 --no-cpu-baseline > $O/ncu_trav.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:"newton_kernel|sumtable_dna" -s 40 -c 4 -o $O/blo_full \
+ncu --set full --clock-control none --import-source on -k regex:"newton|sumtable_dna" -s 40 -c 4 -o $O/blo_full \
     python scripts/bench_blo.py 50 1000000 > $O/ncu_blo_full.log 2>&1
+
+ncu --set full --clock-control none --import-source on -k regex:trav_aa -s 1 -c 1 -o $O/trav_aa_full \
+    python scripts/bench_aa.py 500 50000 > $O/ncu_trav_aa.log 2>&1
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > $O/smoke.log 2>&1; tail -1 $O/smoke.log
 ls -la $O
