@@ -948,6 +948,13 @@ int pllb200_newton_branch(pll_partition_t * partition, const unsigned int * para
                           const double * sumtable, double xmin, double xguess, double xmax,
                           double tolerance, unsigned int max_iters, double brlen_scaler,
                           double * x_out, int * iterations);
+/* The same for ONE branch length shared by several partitions (linked or scaled branch lengths,
+ * pll_optimize.c:1223-1287): one launch sums s_p * d_f and s_p^2 * dd_f over all partitions in every
+ * iteration.  Null entries of `partitions` are skipped; -2 if any partition is not eligible. */
+int pllb200_newton_branch_multi(pll_partition_t ** partitions, unsigned int partition_count,
+                                unsigned int ** params_indices, double ** sumtables,
+                                const double * brlen_scalers, double xmin, double xguess, double xmax,
+                                double tolerance, unsigned int max_iters, double * x_out, int * iterations);
 /* The same without a host wait, for a whole smoothing pass: queues Newton on the branch and the update of
  * its P-matrix from the length left on the device; pllb200_newton_collect waits once and returns lengths
  * and statuses (0 converged, 1 iteration limit, 2 non-finite derivative).  An unconverged branch keeps

@@ -275,6 +275,55 @@ extern "C" int pllb200_newton_branch(pll_partition_t * partition, const unsigned
   return -1;
 }
 
+/* One Newton iteration loop on a branch length shared by several partitions (linked or scaled branch
+ * lengths; replaces the per-iteration derivative callback of pll_optimize.c:1223-1287 + 1395-1560 for that
+ * case).  Null partitions are skipped.  Returns like pllb200_newton_branch; -2 if any partition is not
+ * eligible for the fused path. */
+extern "C" int pllb200_newton_branch_multi(pll_partition_t ** partitions, unsigned int partition_count,
+                                           unsigned int ** params_indices, double ** sumtables,
+                                           const double * brlen_scalers, double xmin, double xguess,
+                                           double xmax, double tolerance, unsigned int max_iters,
+                                           double * x_out, int * iterations)
+{
+  std::vector<PartCtx *> cs;
+  std::vector<unsigned int *> pi;
+  std::vector<double *> st;
+  std::vector<double> sc;
+  for (unsigned int p = 0; p < partition_count; ++p)
+  {
+    if (!partitions[p]) continue;
+    if (!enter(partitions[p])) return -1;
+    PartCtx * c = ctx_of(partitions[p]);
+    if (!newton_fused_supported(c) || c->xchg_nranks > 1) return -2;
+    double * d = sumtable_shadow(c, sumtables[p], false);
+    if (!d) return -1;
+    cs.push_back(c);
+    pi.push_back(params_indices[p]);
+    st.push_back(d);
+    sc.push_back(brlen_scalers ? brlen_scalers[p] : 1.0);
+  }
+  if (cs.empty()) return -2;
+  PartCtx * c0 = cs[0];
+  const int slot = dev_alloc_slot(c0);
+  if (!launch_newton_multi(cs.data(), (unsigned int)cs.size(), pi.data(), st.data(), sc.data(), xmin, xguess,
+                           xmax, tolerance, max_iters, slot))
+    return -1;
+  if (!dev_wait_results(c0) || !dev_wait_slot(c0, slot)) return -1;
+  g_d2h_bytes += 4 * sizeof(double);
+  const double * r = c0->h_result + slot * 4;
+  *x_out = r[0];
+  if (iterations) *iterations = (int)r[2];
+  g_newton_iterations += (unsigned long long)r[2];
+  if (r[1] == 0.0) return 1;
+  if (r[1] == 1.0)
+  {
+    pllmod_set_error(PLLMOD_OPT_ERROR_NEWTON_LIMIT, "Exceeded maximum number of iterations");
+    return 0;
+  }
+  pllmod_set_error(PLLMOD_OPT_ERROR_NEWTON_DERIV, "Wrong likelihood derivatives");
+  return -1;
+}
+
 /* Queued variant for a whole smoothing pass: Newton on one branch, then the P-matrix of that branch from
  * the length the kernel left on the device — no host wait.  The start value is `host_x0` on the first
  * visit of a branch and the device value afterwards (`use_device_x0`).  Results are fetched with

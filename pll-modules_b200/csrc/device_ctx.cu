@@ -117,6 +117,7 @@ bool dev_ctx_init(PartCtx * c)
   c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr;
   c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
   c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->d_sumfrag = nullptr;
+  c->d_multi = nullptr; c->multi_cap = 0; c->ev_batch = nullptr;
   for (int r = 0; r < 8; ++r) c->xchg_peer[r] = nullptr;
   c->xchg_rank = 0; c->xchg_nranks = 0; c->h_stage = nullptr; c->d_stage = nullptr;
   c->d_partials = nullptr; c->d_ticket = nullptr; c->d_result = nullptr; c->h_result = nullptr;
@@ -218,6 +219,8 @@ void dev_ctx_destroy(PartCtx * c)
   cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
   cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag);
+  cudaFree(c->d_multi);
+  if (c->ev_batch) cudaEventDestroy(c->ev_batch);
   for (int r = 0; r < 8; ++r)
     if (c->xchg_peer[r])
     {

@@ -67,6 +67,12 @@ struct PartCtx
   double * d_sumfrag;         /* lazily allocated: 20-state sumtable matrices as DMMA fragment images */
   std::vector<unsigned long long> sumfrag_key;
   double * d_brlen;           /* lazily allocated, [prob_matrices][4]: queued Newton results (k_newton.cu) */
+  /* multi-partition Newton (k_newton.cu): descriptor array on the device + the host image it mirrors;
+   * used on the first partition of a set; ev_batch orders this partition's stream before a batched launch */
+  void * d_multi;
+  size_t multi_cap;
+  std::vector<unsigned char> multi_shadow, multi_shadow_next;
+  cudaEvent_t ev_batch;
 
   /* staging ring: pinned host + device mirror, stream-ordered */
   char * h_stage;
@@ -191,6 +197,9 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
                    double xmin, double x0, double xmax, double tol, unsigned int max_iters,
                    double scale, int slot, double * brlen_io = nullptr, int x0_from_device = 0,
                    int revert_on_limit = 0);
+bool launch_newton_multi(PartCtx ** cs, unsigned int count, unsigned int * const * params_indices,
+                         double * const * d_sumtables, const double * scales, double xmin, double x0,
+                         double xmax, double tol, unsigned int max_iters, int slot);
 bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsigned int second,
                         const unsigned int * params_indices, double * d_sumtable);
 bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,

@@ -790,6 +790,293 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
   }
 }
 
+/* ---- many partitions, one shared branch length ------------------------------------------------------
+ *
+ * With linked (or proportionally scaled) branch lengths the Newton iteration needs, per pass, the sum of
+ * the derivatives of ALL partitions (pll_optimize.c:1223-1287): per partition and pass one launch and one
+ * host wait — 580 of the 930 launches per branch of a 100-partition analysis.  Here one cooperative grid
+ * walks every partition's sumtable: the work is cut into items of 256 threads x U elements (U = 4 for 4
+ * states, 1 otherwise), each CTA owns a contiguous run of items (so it switches partition — rebuilds the
+ * diagonal table — once or twice per pass), per-thread sums carry the chain-rule factors s_p and s_p^2,
+ * and the grid barrier / ordered sum / damped update are those of newton_kernel.  Partition descriptors
+ * (NewtonArgs, model part only) live in a device array that the host re-uploads only when they change.
+ */
+struct NewtonMultiArgs
+{
+  const NewtonArgs * parts;
+  const unsigned int * item_first; /* [nparts + 1] prefix sums of the items per partition */
+  unsigned int nparts, total_items;
+  double xmin, xmax, x0, tol;
+  unsigned int max_iters;
+  double * partials;
+  double * result_dev;
+  double * result_host;
+  unsigned long long * tag_host;
+  unsigned long long tag;
+};
+
+template <bool DNA>
+__device__ __forceinline__ void newton_multi_item(const NewtonArgs & a, const double * s_diag, unsigned int tile,
+                                                  int lane, double wk, double pinv, const double * fr,
+                                                  double & acc1, double & acc2)
+{
+  constexpr int U = DNA ? 4 : 1;
+  const unsigned int K = a.K, s = a.states, sp = a.sp;
+  const unsigned int k = (unsigned int)lane & (K - 1);
+  const unsigned long long E = (unsigned long long)a.sites * K;
+  const unsigned long long base = (unsigned long long)tile * (NW_THREADS * U) + threadIdx.x;
+  const double * dg = s_diag + (size_t)k * s * 3;
+  bool act[U];
+  d4 v[U];
+  unsigned int wgt[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+  {
+    const unsigned long long e = base + (unsigned long long)u * NW_THREADS;
+    act[u] = e < E;
+    wgt[u] = 0;
+    if (act[u])
+    {
+      if (DNA) v[u] = ldg256(a.sum + e * 4);
+      wgt[u] = __ldg(a.weights + (e >> a.kshift));
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u)
+  {
+    const unsigned long long e = base + (unsigned long long)u * NW_THREADS;
+    double L0 = 0.0, L1 = 0.0, L2 = 0.0;
+    if (act[u])
+    {
+      if (DNA)
+      {
+        L0 = v[u].x * dg[0] + v[u].y * dg[3] + v[u].z * dg[6] + v[u].w * dg[9];
+        L1 = v[u].x * dg[1] + v[u].y * dg[4] + v[u].z * dg[7] + v[u].w * dg[10];
+        L2 = v[u].x * dg[2] + v[u].y * dg[5] + v[u].z * dg[8] + v[u].w * dg[11];
+      }
+      else
+      {
+        const double * sm = a.sum + e * sp;
+        if (s == 20)
+        {
+          d4 q[5];
+#pragma unroll
+          for (int c = 0; c < 5; ++c) q[c] = ldg256(sm + 4 * c);
+#pragma unroll
+          for (int c = 0; c < 5; ++c)
+          {
+            const double * g = dg + 12 * c;
+            L0 += q[c].x * g[0] + q[c].y * g[3] + q[c].z * g[6] + q[c].w * g[9];
+            L1 += q[c].x * g[1] + q[c].y * g[4] + q[c].z * g[7] + q[c].w * g[10];
+            L2 += q[c].x * g[2] + q[c].y * g[5] + q[c].z * g[8] + q[c].w * g[11];
+          }
+        }
+        else
+          for (unsigned int j = 0; j < s; ++j)
+          {
+            const double sv = sm[j];
+            L0 += sv * dg[j * 3 + 0];
+            L1 += sv * dg[j * 3 + 1];
+            L2 += sv * dg[j * 3 + 2];
+          }
+      }
+      if (pinv > 0.0)
+      {
+        double inv_lk = 0.0;
+        if (a.invariant)
+        {
+          const int inv = a.invariant[e >> a.kshift];
+          if (inv >= 0) inv_lk = fr[inv] * pinv;
+        }
+        L0 = L0 * (1.0 - pinv) + inv_lk;
+        L1 = L1 * (1.0 - pinv);
+        L2 = L2 * (1.0 - pinv);
+      }
+      L0 *= wk;
+      L1 *= wk;
+      L2 *= wk;
+    }
+    for (unsigned int off = 1; off < K; off <<= 1)
+    {
+      L0 += __shfl_xor_sync(0xffffffffu, L0, off);
+      L1 += __shfl_xor_sync(0xffffffffu, L1, off);
+      L2 += __shfl_xor_sync(0xffffffffu, L2, off);
+    }
+    if (act[u] && k == 0)
+    {
+      const double r1 = -L1 / L0;
+      acc1 += a.scale * (double)wgt[u] * r1;
+      acc2 += a.scale * a.scale * (double)wgt[u] * (r1 * r1 - L2 / L0);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(NW_THREADS, 3) newton_multi_kernel(NewtonMultiArgs m)
+{
+  cg::grid_group grid = cg::this_grid();
+  __shared__ double s_diag[NW_MAX_DIAG * 3];
+  __shared__ double s_red[2][NW_THREADS / 32];
+  __shared__ double s_tot[2];
+
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  /* this CTA's run of items and the partition its first item belongs to */
+  const unsigned int lo = (unsigned int)((unsigned long long)m.total_items * blockIdx.x / gridDim.x);
+  const unsigned int hi = (unsigned int)((unsigned long long)m.total_items * (blockIdx.x + 1) / gridDim.x);
+  unsigned int p_lo = 0;
+  {
+    unsigned int l = 0, h = m.nparts; /* last p with item_first[p] <= lo */
+    while (l + 1 < h)
+    {
+      const unsigned int mid = (l + h) >> 1;
+      if (__ldg(m.item_first + mid) <= lo)
+        l = mid;
+      else
+        h = mid;
+    }
+    p_lo = l;
+  }
+
+  double xl = m.xmin, xh = m.xmax;
+  const double xorig = m.x0;
+  double x = fmax(fmin(xorig, m.xmax), m.xmin);
+  const double dxmax = m.xmax / m.max_iters;
+  unsigned int iter = 0;
+  double status = NW_OK;
+  double f = 0.0, df = 0.0;
+
+  for (;;)
+  {
+    if (iter++ > m.max_iters)
+    {
+      status = NW_LIMIT;
+      break;
+    }
+    double acc1 = 0.0, acc2 = 0.0;
+    unsigned int p = p_lo, cur = 0xffffffffu;
+    double wk = 0.0, pinv = 0.0;
+    const double * fr = nullptr;
+    for (unsigned int item = lo; item < hi; ++item)
+    {
+      while (item >= __ldg(m.item_first + p + 1)) ++p;
+      const NewtonArgs & a = m.parts[p];
+      if (p != cur)
+      {
+        cur = p;
+        const unsigned int K = a.K, s = a.states, sp = a.sp;
+        const double t = a.scale * x;
+        __syncthreads();
+        for (unsigned int i = threadIdx.x; i < K * s; i += blockDim.x)
+        {
+          const unsigned int kk = i / s, j = i % s;
+          const double ev = a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * s * sp + j];
+          const double ki = a.rate[kk] / (1.0 - a.pinv[kk]);
+          const double e0 = exp(ev * ki * t);
+          s_diag[i * 3 + 0] = e0;
+          s_diag[i * 3 + 1] = ev * ki * e0;
+          s_diag[i * 3 + 2] = ev * ki * ev * ki * e0;
+        }
+        __syncthreads();
+        const unsigned int k = (unsigned int)lane & (K - 1);
+        wk = a.w[k];
+        pinv = a.pinv[k];
+        fr = a.eigen + (unsigned long long)a.model_idx[k] * a.eigen_stride + 2 * s * sp + sp;
+      }
+      const unsigned int tile = item - __ldg(m.item_first + p);
+      if (a.states == 4)
+        newton_multi_item<true>(a, s_diag, tile, lane, wk, pinv, fr, acc1, acc2);
+      else
+        newton_multi_item<false>(a, s_diag, tile, lane, wk, pinv, fr, acc1, acc2);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1)
+    {
+      acc1 += __shfl_down_sync(0xffffffffu, acc1, off);
+      acc2 += __shfl_down_sync(0xffffffffu, acc2, off);
+    }
+    if (lane == 0)
+    {
+      s_red[0][warp] = acc1;
+      s_red[1][warp] = acc2;
+    }
+    __syncthreads();
+    double * buf = m.partials + (size_t)(iter & 1u) * 2 * gridDim.x;
+    if (threadIdx.x == 0)
+    {
+      double p1 = 0.0, p2 = 0.0;
+      for (int wi = 0; wi < NW_THREADS / 32; ++wi)
+      {
+        p1 += s_red[0][wi];
+        p2 += s_red[1][wi];
+      }
+      buf[blockIdx.x] = p1;
+      buf[gridDim.x + blockIdx.x] = p2;
+    }
+    grid.sync();
+    if (warp == 0)
+    {
+      double t1 = 0.0, t2 = 0.0;
+      for (unsigned int b = lane; b < gridDim.x; b += 32)
+      {
+        t1 += __ldcg(buf + b);
+        t2 += __ldcg(buf + gridDim.x + b);
+      }
+#pragma unroll
+      for (int off = 16; off > 0; off >>= 1)
+      {
+        t1 += __shfl_down_sync(0xffffffffu, t1, off);
+        t2 += __shfl_down_sync(0xffffffffu, t2, off);
+      }
+      if (lane == 0)
+      {
+        s_tot[0] = t1;
+        s_tot[1] = t2;
+      }
+    }
+    __syncthreads();
+    f = s_tot[0];
+    df = s_tot[1];
+
+    /* damped Newton step inside the shrinking bracket (opt_algorithms.c:187-252) */
+    if (!isfinite(f) || !isfinite(df))
+    {
+      status = NW_BAD_DERIV;
+      break;
+    }
+    double dx;
+    if (df > 0.0)
+    {
+      if (fabs(f) < m.tol) break;
+      if (f < 0.0)
+        xl = x;
+      else
+        xh = x;
+      dx = -f / df;
+    }
+    else
+      dx = -f / fabs(df);
+    dx = fmax(fmin(dx, dxmax), -dxmax);
+    if (x + dx < xl) dx = xl - x;
+    if (x + dx > xh) dx = xh - x;
+    if (fabs(dx) < m.tol) break;
+    x += dx;
+    x = fmax(fmin(x, m.xmax), m.xmin);
+  }
+
+  if (blockIdx.x == 0 && threadIdx.x == 0)
+  {
+    m.result_dev[0] = x;
+    m.result_dev[1] = status;
+    m.result_dev[2] = (double)iter;
+    m.result_dev[3] = f;
+    m.result_host[0] = x;
+    m.result_host[1] = status;
+    m.result_host[2] = (double)iter;
+    m.result_host[3] = f;
+    __threadfence_system();
+    *reinterpret_cast<volatile unsigned long long *>(m.tag_host) = m.tag;
+  }
+}
+
 /* can the fused path serve this partition? */
 int g_opt_fused_newton = 1;
 int g_opt_queued_newton = 1;
@@ -804,14 +1091,13 @@ bool newton_fused_supported(const PartCtx * c)
   return g_opt_fused_newton != 0;
 }
 
-bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
-                   double xmin, double x0, double xmax, double tol, unsigned int max_iters,
-                   double scale, int slot, double * brlen_io, int x0_from_device, int revert_on_limit)
+/* the model part of a partition's descriptor: sumtable, weights, eigen system, rates */
+static bool fill_newton_model(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
+                              double scale, NewtonArgs & a)
 {
   pll_partition_t * p = &c->pub;
   const unsigned int K = p->rate_cats, s = p->states;
   if (!dev_sync_inputs(c) || !dev_sync_eigen(c, params_indices)) return false;
-  NewtonArgs a;
   memset(&a, 0, sizeof(a));
   a.sum = d_sumtable;
   a.weights = c->d_weights;
@@ -846,11 +1132,23 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
     a.invariant = c->d_invariant;
   }
   a.any_pinv = any_pinv;
+  a.scale = scale;
+  a.nranks = 1;
+  return true;
+}
+
+bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
+                   double xmin, double x0, double xmax, double tol, unsigned int max_iters,
+                   double scale, int slot, double * brlen_io, int x0_from_device, int revert_on_limit)
+{
+  pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats, s = p->states;
+  NewtonArgs a;
+  if (!fill_newton_model(c, params_indices, d_sumtable, scale, a)) return false;
   a.xmin = xmin;
   a.xmax = xmax;
   a.x0 = x0;
   a.tol = tol;
-  a.scale = scale;
   a.max_iters = max_iters;
   a.partials = c->d_partials;
   a.result_dev = c->d_result + slot * 4;
@@ -891,4 +1189,99 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
                                                       c->stream);
   ++g_kernel_launches;
   return pllb200_cuda_ok(e, "newton kernel launch");
+}
+
+/* One shared branch length over `count` partitions (linked / scaled branch lengths): descriptors in a
+ * device array owned by the first partition's context, launch on its stream after the other partitions'
+ * streams (their sumtables) by event, result in one of its slots. */
+bool launch_newton_multi(PartCtx ** cs, unsigned int count, unsigned int * const * params_indices,
+                         double * const * d_sumtables, const double * scales, double xmin, double x0,
+                         double xmax, double tol, unsigned int max_iters, int slot)
+{
+  PartCtx * c0 = cs[0];
+  const size_t desc_bytes = sizeof(NewtonArgs) * count;
+  const size_t first_bytes = sizeof(unsigned int) * (count + 1);
+  const size_t total = desc_bytes + ((first_bytes + 15) & ~(size_t)15);
+  std::vector<unsigned char> & img = c0->multi_shadow_next;
+  img.assign(total, 0);
+  NewtonArgs * parts = reinterpret_cast<NewtonArgs *>(img.data());
+  unsigned int * first = reinterpret_cast<unsigned int *>(img.data() + desc_bytes);
+  unsigned long long items = 0;
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    if (!fill_newton_model(cs[i], params_indices[i], d_sumtables[i], scales ? scales[i] : 1.0, parts[i]))
+      return false;
+    first[i] = (unsigned int)items;
+    const unsigned long long E = (unsigned long long)parts[i].sites * parts[i].K;
+    const unsigned long long per = (unsigned long long)NW_THREADS * (parts[i].states == 4 ? 4 : 1);
+    items += (E + per - 1) / per;
+    if (items > 0x7fffffffull)
+    {
+      pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Too many sites for the multi-partition Newton kernel.");
+      return false;
+    }
+  }
+  first[count] = (unsigned int)items;
+  if (c0->multi_cap < total)
+  {
+    if (c0->d_multi) cudaFree(c0->d_multi);
+    c0->d_multi = nullptr;
+    c0->multi_cap = 0;
+    c0->multi_shadow.clear();
+    if (!pllb200_cuda_ok(cudaMalloc(&c0->d_multi, total), "multi-partition Newton descriptors")) return false;
+    c0->multi_cap = total;
+  }
+  if (c0->multi_shadow.size() != total || memcmp(c0->multi_shadow.data(), img.data(), total) != 0)
+  {
+    /* pageable source: the runtime stages it before returning, the copy itself is ordered on the stream */
+    if (!pllb200_cuda_ok(cudaMemcpyAsync(c0->d_multi, img.data(), total, cudaMemcpyHostToDevice, c0->stream),
+                         "multi-partition Newton descriptors H2D"))
+      return false;
+    g_h2d_bytes += total;
+    c0->multi_shadow = img;
+  }
+  /* the other partitions' sumtables (and input uploads) were queued on their own streams */
+  for (unsigned int i = 1; i < count; ++i)
+  {
+    PartCtx * c = cs[i];
+    if (c->stream == c0->stream) continue;
+    if (!c->ev_batch &&
+        !pllb200_cuda_ok(cudaEventCreateWithFlags(&c->ev_batch, cudaEventDisableTiming), "batch event"))
+      return false;
+    if (!pllb200_cuda_ok(cudaEventRecord(c->ev_batch, c->stream), "batch event record")) return false;
+    if (!pllb200_cuda_ok(cudaStreamWaitEvent(c0->stream, c->ev_batch, 0), "batch event wait")) return false;
+  }
+  NewtonMultiArgs m;
+  memset(&m, 0, sizeof(m));
+  m.parts = reinterpret_cast<const NewtonArgs *>(c0->d_multi);
+  m.item_first = reinterpret_cast<const unsigned int *>(reinterpret_cast<const unsigned char *>(c0->d_multi) + desc_bytes);
+  m.nparts = count;
+  m.total_items = (unsigned int)items;
+  m.xmin = xmin;
+  m.xmax = xmax;
+  m.x0 = x0;
+  m.tol = tol;
+  m.max_iters = max_iters;
+  m.partials = c0->d_partials;
+  m.result_dev = c0->d_result + slot * 4;
+  m.result_host = c0->h_result_dev + slot * 4;
+  dev_slot_tag(c0, slot, &m.tag_host, &m.tag);
+
+  static int per_sm = 0;
+  if (!per_sm)
+  {
+    int nb = 0;
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, newton_multi_kernel, NW_THREADS, 0);
+    per_sm = (e == cudaSuccess && nb > 0) ? nb : 1;
+  }
+  unsigned long long blocks = items;
+  unsigned long long cap = (unsigned long long)c0->sm_count * std::min(per_sm, 3);
+  if (cap > PLLB200_MAX_RED_BLOCKS * 3 / 4) cap = PLLB200_MAX_RED_BLOCKS * 3 / 4;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  void * kargs[] = {&m};
+  const cudaError_t e = cudaLaunchCooperativeKernel((const void *)newton_multi_kernel, dim3((unsigned)blocks),
+                                                      dim3(NW_THREADS), kargs, 0, c0->stream);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(e, "multi-partition newton kernel launch");
 }

@@ -548,6 +548,16 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
                                       (unsigned int)prm->max_newton_iters, s, &xguess[0], nullptr);
         if (fused >= 0 && prm->converged) prm->converged[0] = fused == 1;
       }
+      else if (xnum == 1 && !unlinked && prm->partition_count > 1 && !prm->parallel_reduce_cb)
+      {
+        /* one shared length over several local partitions: all partitions' derivatives per iteration in
+         * one cooperative launch (k_newton.cu, newton_multi_kernel) */
+        pll_errno = 0;
+        fused = pllb200_newton_branch_multi(prm->partitions, prm->partition_count, prm->params_indices,
+                                            prm->precomp_buffers, prm->brlen_scalers, xmin, xguess[0], xmax,
+                                            xtol, (unsigned int)prm->max_newton_iters, &xguess[0], nullptr);
+        if (fused >= 0 && prm->converged) prm->converged[0] = fused == 1;
+      }
       if (fused == -2)
         retval = pllmod_opt_minimize_newton_multi(xnum, xmin, xguess, xmax, xtol,
                                                   prm->max_newton_iters, prm->converged, prm,

@@ -70,14 +70,17 @@ if "c4" in which:
         pkg.reset_stats()
         t = timed(lambda: h.loglh(0), 5)
         launches = pkg.stats()["kernel_launches"] / 6
+        pkg.reset_stats()
         tb0 = time.perf_counter()
         nll = h.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)
         tb = time.perf_counter() - tb0
+        blo_launches = pkg.stats()["kernel_launches"] / (2 * tips - 3)
         upd = (tips - 2) * sites * nparts
         print(json.dumps({"config": "C4 %d partitions (DNA/protein alternating, per-partition alpha) x %d sites, %d taxa"
                                     % (nparts, sites, tips), "loglh": ll, "full_loglh_ms": t * 1e3,
                           "site_updates_per_s": upd / t, "kernel_launches_per_eval": launches,
-                          "blo_one_smoothing_s": tb, "blo_neg_loglh": nll}), flush=True)
+                          "blo_one_smoothing_s": tb, "blo_launches_per_branch": blo_launches,
+                          "blo_neg_loglh": nll}), flush=True)
 
 if "c5" in which:
     tips, sites = 2000, opt("--c5-sites", 500000)

@@ -204,6 +204,45 @@ def test_multi_partition_mixed_models_linked_and_unlinked():
 
 
 @needs_ref
+@pytest.mark.parametrize("linkage", [0, 1])
+def test_shared_branch_length_newton_over_many_partitions(linkage):
+    """Linked / scaled branch lengths: one cooperative launch sums all partitions' derivatives per
+    iteration (newton_multi_kernel); same lengths as the reference and as the per-iteration path."""
+    pkg = load_product_package()
+    kw = dict(tips=18, sites=[900, 300, 1300, 77, 520, 33], states=[4, 20, 4, 20, 4, 4],
+              alpha=[0.3, 0.6, 1.0, 2.0, 0.5, 0.8], pinv=0.15, linkage=linkage)
+    ref, dev = pair(**kw)
+    with ref, dev:
+        assert rel(dev.loglh(), ref.loglh()) < 1e-8
+        if linkage == 1:   # give the partitions different scalers first
+            a = ref.algo_opt_treeinfo("brlen_scalers", 1e-2)
+            b = dev.algo_opt_treeinfo("brlen_scalers", 1e-2)
+            assert rel(b, a) < 1e-6
+            np.testing.assert_allclose(dev.treeinfo_params()["brlen_scalers"],
+                                       ref.treeinfo_params()["brlen_scalers"], rtol=1e-3)
+        pkg.reset_stats()
+        a = ref.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=3, lh_epsilon=0.01)
+        b = dev.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=3, lh_epsilon=0.01)
+        fused_launches = pkg.stats()["kernel_launches"]
+        assert rel(b, a) < 1e-8, (linkage, b, a)
+        np.testing.assert_allclose(dev.branch_lengths(), ref.branch_lengths(), atol=1e-5, rtol=1e-5)
+    # the per-iteration path (one derivative launch per partition and iteration) gives the same answer
+    _, dev2 = pair(**kw)
+    pkg.set_option("fused_newton", 0)
+    try:
+        with dev2:
+            dev2.loglh()
+            if linkage == 1:
+                dev2.algo_opt_treeinfo("brlen_scalers", 1e-2)
+            pkg.reset_stats()
+            c = dev2.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=3, lh_epsilon=0.01)
+            assert rel(c, b) < 1e-9, (c, b)
+            assert pkg.stats()["kernel_launches"] > 1.5 * fused_launches
+    finally:
+        pkg.set_option("fused_newton", 1)
+
+
+@needs_ref
 def test_persite_root_and_alpha_change():
     kw = dict(tips=16, sites=900)
     ref, dev = pair(**kw)
