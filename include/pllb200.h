@@ -955,6 +955,15 @@ int pllb200_newton_branch_multi(pll_partition_t ** partitions, unsigned int part
                                 unsigned int ** params_indices, double ** sumtables,
                                 const double * brlen_scalers, double xmin, double xguess, double xmax,
                                 double tolerance, unsigned int max_iters, double * x_out, int * iterations);
+/* Batch mode for many small partitions on one tree: between begin and end, pll_update_partials,
+ * pll_update_sumtable and pll_update_prob_matrices (one matrix) on the member partitions only collect
+ * their work; pllb200_batch_flush issues one launch per kernel kind (blockIdx.y = partition).  Only these
+ * calls, pllb200_newton_branch_multi and flush may be used on the members in between.  begin returns 1
+ * when batch mode is on, 0 when these partitions cannot be batched (nothing changes), -1 on error. */
+int pllb200_batch_begin(pll_partition_t ** partitions, unsigned int count);
+int pllb200_batch_flush(void);
+int pllb200_batch_active(void);
+int pllb200_batch_end(void);
 /* The same without a host wait, for a whole smoothing pass: queues Newton on the branch and the update of
  * its P-matrix from the length left on the device; pllb200_newton_collect waits once and returns lengths
  * and statuses (0 converged, 1 iteration limit, 2 non-finite derivative).  An unconverged branch keeps

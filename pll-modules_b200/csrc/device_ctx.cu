@@ -74,6 +74,8 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "queued_newton")) slot = &g_opt_queued_newton;
   else if (!strcmp(name, "trav_prefetch")) slot = &g_opt_trav_prefetch;
   else if (!strcmp(name, "aa_variant")) slot = &g_opt_aa_variant;
+  else if (!strcmp(name, "small_stage")) slot = &g_opt_small_stage;
+  else if (!strcmp(name, "batch")) slot = &g_opt_batch;
   if (!slot) return -1;
   int old = *slot;
   *slot = value;
@@ -120,6 +122,7 @@ bool dev_ctx_init(PartCtx * c)
   c->d_multi = nullptr; c->multi_cap = 0; c->ev_batch = nullptr;
   for (int r = 0; r < 8; ++r) c->xchg_peer[r] = nullptr;
   c->xchg_rank = 0; c->xchg_nranks = 0; c->h_stage = nullptr; c->d_stage = nullptr;
+  c->h_small = nullptr; c->h_small_dev = nullptr; c->small_head = 0;
   c->d_partials = nullptr; c->d_ticket = nullptr; c->d_result = nullptr; c->h_result = nullptr;
   c->own_stream = nullptr;
 
@@ -188,6 +191,8 @@ bool dev_ctx_init(PartCtx * c)
   c->stage_size = 4u << 20;
   c->stage_head = 0;
   CUDA_TRY(cudaHostAlloc(&c->h_stage, c->stage_size, cudaHostAllocDefault), false);
+  CUDA_TRY(cudaHostAlloc(&c->h_small, PLLB200_SMALL_RING, cudaHostAllocMapped), false);
+  CUDA_TRY(cudaHostGetDevicePointer((void **)&c->h_small_dev, c->h_small, 0), false);
   CUDA_TRY(cudaMalloc(&c->d_stage, c->stage_size), false);
 
   CUDA_TRY(cudaMalloc(&c->d_partials, sizeof(double) * 4 * PLLB200_MAX_RED_BLOCKS), false);
@@ -228,6 +233,7 @@ void dev_ctx_destroy(PartCtx * c)
     } cudaFree(c->d_stage); cudaFree(c->d_partials);
   cudaFree(c->d_ticket); cudaFree(c->d_result);
   if (c->h_stage) cudaFreeHost(c->h_stage);
+  if (c->h_small) cudaFreeHost(c->h_small);
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   cudaGetLastError();
@@ -240,6 +246,7 @@ void dev_ctx_destroy(PartCtx * c)
  * waits for the stream so earlier async copies have consumed their source. */
 void * dev_stage(PartCtx * c, const void * src, size_t bytes)
 {
+  if (g_batch && g_batch->lead != c) return dev_stage(g_batch->lead, src, bytes);
   const size_t need = round_up(bytes, 256);
   if (need > c->stage_size)
   {
@@ -268,6 +275,31 @@ void * dev_stage(PartCtx * c, const void * src, size_t bytes)
   return d;
 }
 
+/* Few bytes (one or two resolved ops, a matrix index and its length): written into a ring of MAPPED
+ * pinned memory that the kernel reads directly — no copy call.  A branch of a 100-partition analysis
+ * queued 250 such copies (profiles/README.md); the read costs the kernel one PCIe round trip. */
+int g_opt_small_stage = 1; /* 0 never, 1 for partitions whose kernels are shorter than the round trip saved, 2 always */
+void * dev_stage_small(PartCtx * c, const void * src, size_t bytes)
+{
+  if (g_batch) return dev_stage(g_batch->lead, src, bytes); /* batched kernels read argument arrays from HBM */
+  /* measured (BLO pass, 200 taxa): 1 k sites 45.3 -> 40.5 us per branch, 1 M sites 259.7 -> 269.2 us — a
+   * long kernel would rather have the copy overlap its predecessor than wait ~2.7 us at its start */
+  if (bytes > PLLB200_SMALL_MAX || !g_opt_small_stage || (g_opt_small_stage == 1 && c->clv_elems > (1u << 20)))
+    return dev_stage(c, src, bytes);
+  const size_t need = round_up(bytes, 64);
+  if (c->small_head + need > PLLB200_SMALL_RING)
+  {
+    /* one lap = thousands of launches; everything that read the old entries must be done */
+    if (!pllb200_cuda_ok(cudaStreamSynchronize(c->stream), "small stage lap sync")) return nullptr;
+    c->small_head = 0;
+  }
+  memcpy(c->h_small + c->small_head, src, bytes);
+  void * d = c->h_small_dev + c->small_head;
+  c->small_head += need;
+  g_h2d_bytes += bytes;
+  return d;
+}
+
 /* big host arrays: chunk through the staging ring (pageable sources, async-safe) */
 static bool upload_big(PartCtx * c, void * dst, const void * src, size_t bytes)
 {
@@ -279,7 +311,7 @@ static bool upload_big(PartCtx * c, void * dst, const void * src, size_t bytes)
     const size_t n = std::min(bytes, chunk);
     void * st = dev_stage(c, s, n);
     if (!st) return false;
-    if (!pllb200_cuda_ok(cudaMemcpyAsync(d, st, n, cudaMemcpyDeviceToDevice, c->stream), "upload_big"))
+    if (!pllb200_cuda_ok(cudaMemcpyAsync(d, st, n, cudaMemcpyDeviceToDevice, xstream(c)), "upload_big"))
       return false;
     s += n; d += n; bytes -= n;
   }
@@ -305,7 +337,7 @@ bool dev_sync_inputs(PartCtx * c)
     void * st = dev_stage(c, p->tipmap, 256 * sizeof(unsigned long long));
     if (!st) return false;
     CUDA_TRY(cudaMemcpyAsync(c->d_tipmap, st, 256 * sizeof(unsigned long long),
-                             cudaMemcpyDeviceToDevice, c->stream), false);
+                             cudaMemcpyDeviceToDevice, xstream(c)), false);
     c->tipmap_dirty = false;
   }
   if (c->weights_dirty)
@@ -347,7 +379,7 @@ bool dev_sync_eigen(PartCtx * c, const unsigned int * params_indices)
     void * st = dev_stage(c, blk.data(), sizeof(double) * c->eigen_stride);
     if (!st) return false;
     CUDA_TRY(cudaMemcpyAsync(c->d_eigen + (size_t)m * c->eigen_stride, st,
-                             sizeof(double) * c->eigen_stride, cudaMemcpyDeviceToDevice, c->stream),
+                             sizeof(double) * c->eigen_stride, cudaMemcpyDeviceToDevice, xstream(c)),
              false);
     c->eigen_version_dev[m] = c->eigen_version[m];
   }
@@ -639,4 +671,121 @@ extern "C" uint64_t pllb200_result_device_ptr(pll_partition_t * p)
 {
   if (!check_ctx(p)) return 0;
   return (uint64_t)(uintptr_t)ctx_of(p)->d_result;
+}
+
+
+/* ---- batch mode --------------------------------------------------------------------------------- */
+thread_local BatchCtx * g_batch = nullptr;
+int g_opt_batch = 1; /* bit 0: on; bits 1.. : keep kind (bit - 1) out of the collector (debugging) */
+
+bool batch_eligible(const PartCtx * c)
+{
+  const pll_partition_t * p = &c->pub;
+  if (p->attributes & (PLL_ATTRIB_RATE_SCALERS | PLL_ATTRIB_AB_MASK)) return false;
+  if (p->states == 4) return p->rate_cats == 4;
+  if (p->states == 20)
+    return p->states_padded == 20 && (p->rate_cats == 1 || p->rate_cats == 2 || p->rate_cats == 4 || p->rate_cats == 8) &&
+           c->d_pmat_il != nullptr;
+  return false;
+}
+
+void batch_collect(int kind, const void * args, size_t bytes, unsigned int blocks, size_t smem)
+{
+  BatchKind & k = g_batch->kind[kind];
+  const unsigned char * b = static_cast<const unsigned char *>(args);
+  k.bytes.insert(k.bytes.end(), b, b + bytes);
+  ++k.count;
+  if (blocks > k.max_blocks) k.max_blocks = blocks;
+  if (smem > k.smem) k.smem = smem;
+}
+
+bool batch_flush()
+{
+  BatchCtx * b = g_batch;
+  if (!b) return true;
+  bool ok = true;
+  for (int kind = 0; kind < BK_COUNT && ok; ++kind)
+  {
+    BatchKind & k = b->kind[kind];
+    if (!k.count) continue;
+    const void * d_args = dev_stage(b->lead, k.bytes.data(), k.bytes.size());
+    if (!d_args)
+      ok = false;
+    else
+      switch (kind)
+      {
+        case BK_SUM_DNA4: ok = flush_sum_dna4(b->lead, d_args, k); break;
+        case BK_TRAV_DNA4: ok = flush_trav_dna4(b->lead, d_args, k); break;
+        case BK_TRAV_AA: ok = flush_trav_aa(b->lead, d_args, k); break;
+        default: ok = flush_pmat(b->lead, d_args, k); break;
+      }
+    k.bytes.clear();
+    k.count = k.max_blocks = 0;
+    k.smem = 0;
+  }
+  return ok;
+}
+
+/* Returns 1 when batch mode is on, 0 when these partitions cannot be batched (callers carry on with the
+ * per-partition path), -1 on error. */
+extern "C" int pllb200_batch_begin(pll_partition_t ** partitions, unsigned int count)
+{
+  if (g_batch || !(g_opt_batch & 1)) return 0;
+  std::vector<PartCtx *> m;
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    if (!partitions[i]) continue;
+    PartCtx * c = ctx_of(partitions[i]);
+    if (c->magic != PLLB200_MAGIC || !batch_eligible(c) || c->xchg_nranks > 1) return 0;
+    if (!m.empty() && c->device != m[0]->device) return 0;
+    m.push_back(c);
+  }
+  if (m.size() < 2) return 0;
+  PartCtx * lead = m[0];
+  if (!pllb200_cuda_ok(cudaSetDevice(lead->device), "cudaSetDevice")) return -1;
+  for (size_t i = 1; i < m.size(); ++i)
+  {
+    PartCtx * c = m[i];
+    if (c->stream == lead->stream) continue;
+    if (!c->ev_batch &&
+        !pllb200_cuda_ok(cudaEventCreateWithFlags(&c->ev_batch, cudaEventDisableTiming), "batch event"))
+      return -1;
+    if (!pllb200_cuda_ok(cudaEventRecord(c->ev_batch, c->stream), "batch event record") ||
+        !pllb200_cuda_ok(cudaStreamWaitEvent(lead->stream, c->ev_batch, 0), "batch event wait"))
+      return -1;
+  }
+  BatchCtx * b = new BatchCtx();
+  b->lead = lead;
+  b->members = m;
+  for (int k = 0; k < BK_COUNT; ++k)
+  {
+    b->kind[k].count = b->kind[k].max_blocks = 0;
+    b->kind[k].smem = 0;
+  }
+  g_batch = b;
+  return 1;
+}
+
+extern "C" int pllb200_batch_flush(void) { return batch_flush() ? PLL_SUCCESS : PLL_FAILURE; }
+
+extern "C" int pllb200_batch_active(void) { return g_batch != nullptr; }
+
+extern "C" int pllb200_batch_end(void)
+{
+  BatchCtx * b = g_batch;
+  if (!b) return PLL_SUCCESS;
+  bool ok = batch_flush();
+  g_batch = nullptr;
+  PartCtx * lead = b->lead;
+  if (!lead->ev_batch)
+    ok = pllb200_cuda_ok(cudaEventCreateWithFlags(&lead->ev_batch, cudaEventDisableTiming), "batch event") && ok;
+  if (lead->ev_batch)
+  {
+    ok = pllb200_cuda_ok(cudaEventRecord(lead->ev_batch, lead->stream), "batch event record") && ok;
+    for (size_t i = 1; i < b->members.size(); ++i)
+      if (b->members[i]->stream != lead->stream)
+        ok = pllb200_cuda_ok(cudaStreamWaitEvent(b->members[i]->stream, lead->ev_batch, 0), "batch event wait") && ok;
+  }
+  delete b;
+  return ok ? PLL_SUCCESS : PLL_FAILURE;
 }

@@ -79,6 +79,9 @@ struct PartCtx
   char * d_stage;
   size_t stage_size;
   size_t stage_head;
+  char * h_small;            /* mapped pinned ring for payloads of a few bytes (dev_stage_small) */
+  char * h_small_dev;
+  size_t small_head;
 
   /* reductions */
   double * d_partials;        /* PLLB200_MAX_RED_BLOCKS*3 doubles */
@@ -143,10 +146,46 @@ extern int g_opt_fused_newton;
 extern int g_opt_queued_newton;
 extern int g_opt_aa_variant;
 
+/* ---- batch mode (device_ctx.cu) ------------------------------------------------------------------
+ * Many small partitions sharing one tree: between batch_begin and batch_end the per-partition launchers
+ * of the kinds below do not launch; they append their argument struct to the collector, and batch_flush
+ * issues ONE launch per kind with blockIdx.y = partition, on the lead partition's stream (staging goes
+ * through the lead's ring too).  begin makes the lead stream wait for every member stream, end makes the
+ * member streams wait for the lead.  Launchers that are not batch-aware must not run in between. */
+enum { BK_SUM_DNA4 = 0, BK_TRAV_DNA4, BK_TRAV_AA, BK_PMAT, BK_COUNT };
+struct BatchKind
+{
+  std::vector<unsigned char> bytes; /* argument structs back to back */
+  unsigned int count, max_blocks;
+  size_t smem;
+};
+struct BatchCtx
+{
+  PartCtx * lead;
+  std::vector<PartCtx *> members;
+  BatchKind kind[BK_COUNT];
+};
+extern thread_local BatchCtx * g_batch;
+void batch_collect(int kind, const void * args, size_t bytes, unsigned int blocks, size_t smem);
+bool batch_flush();
+/* per kind, in the kernel's own file: launch `k.count` argument structs staged at `d_args` */
+bool flush_sum_dna4(PartCtx * lead, const void * d_args, const BatchKind & k);
+bool flush_trav_dna4(PartCtx * lead, const void * d_args, const BatchKind & k);
+bool flush_trav_aa(PartCtx * lead, const void * d_args, const BatchKind & k);
+bool flush_pmat(PartCtx * lead, const void * d_args, const BatchKind & k);
+bool batch_eligible(const PartCtx * c);
+/* the stream a launcher uses: the lead's in batch mode */
+static inline cudaStream_t xstream(const PartCtx * c) { return g_batch ? g_batch->lead->stream : c->stream; }
+
 /* device context (device_ctx.cu) */
 bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */
 void dev_ctx_destroy(PartCtx * c);
 void * dev_stage(PartCtx * c, const void * src, size_t bytes); /* returns device ptr, stream ordered */
+#define PLLB200_SMALL_RING (256u << 10)
+#define PLLB200_SMALL_MAX 256u
+void * dev_stage_small(PartCtx * c, const void * src, size_t bytes); /* <= 256 B: mapped host memory, no copy call */
+extern int g_opt_small_stage;
+extern int g_opt_batch;
 bool dev_sync_inputs(PartCtx * c);   /* push dirty tipchars / weights / invariant / tipmap */
 bool dev_sync_eigen(PartCtx * c, const unsigned int * params_indices); /* ensure eigen block current */
 bool dev_flush(PartCtx * c);            /* stream sync + deliver pending async results */

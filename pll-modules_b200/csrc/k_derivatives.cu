@@ -49,8 +49,8 @@ struct SumArgs
 #define SUM_LD 18  /* row stride of the staged eigen tables in doubles: rows of different rates sit in
                       different banks (16 would put all K rows on the same bank) */
 
-template <int K>
-__global__ void __launch_bounds__(DV_THREADS, 4) sumtable_dna_kernel(SumArgs a)
+template <int K, int TAG> /* TAG: the static shared tables are one symbol per kernel */
+__device__ __forceinline__ void sumtable_dna_body(const SumArgs & a)
 {
   __shared__ __align__(16) double s_w[K][SUM_LD];  /* pi_i * Vinv[i][j] */
   __shared__ __align__(16) double s_v[K][SUM_LD];  /* V[j][i] */
@@ -147,6 +147,24 @@ __global__ void __launch_bounds__(DV_THREADS, 4) sumtable_dna_kernel(SumArgs a)
       if (act[u]) stg256(a.sum + e * 4, out);
     }
   }
+}
+
+template <int K>
+__global__ void __launch_bounds__(DV_THREADS, 4) sumtable_dna_kernel(SumArgs a)
+{
+  sumtable_dna_body<K, 0>(a);
+}
+
+/* the same for many partitions in one launch (blockIdx.y = partition): a branch of a 100-partition
+ * analysis otherwise costs 100 launches here (optimize.cpp, batch mode) */
+template <int K>
+__global__ void __launch_bounds__(DV_THREADS, 4) sumtable_dna_batch_kernel(const SumArgs * __restrict__ arr)
+{
+  __shared__ SumArgs sa;
+  for (unsigned int i = threadIdx.x; i < sizeof(SumArgs) / 4; i += blockDim.x)
+    reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
+  __syncthreads();
+  sumtable_dna_body<K, 1>(sa);
 }
 
 __global__ void __launch_bounds__(DVG_THREADS) sumtable_generic_kernel(SumArgs a)
@@ -499,19 +517,24 @@ bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_cl
     unsigned long long blocks = (E + DV_THREADS - 1) / DV_THREADS;
     const unsigned long long cap = (unsigned long long)c->sm_count * 4; /* one resident wave (launch bounds) */
     if (blocks > cap) blocks = cap;
+    if (g_batch && !(g_opt_batch & (2 << BK_SUM_DNA4)) && K == 4)
+    {
+      batch_collect(BK_SUM_DNA4, &a, sizeof(a), (unsigned)blocks, 0);
+      return true;
+    }
     switch (K)
     {
-      case 1: sumtable_dna_kernel<1><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
-      case 2: sumtable_dna_kernel<2><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
-      case 4: sumtable_dna_kernel<4><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
-      default: sumtable_dna_kernel<8><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a); break;
+      case 1: sumtable_dna_kernel<1><<<(unsigned)blocks, DV_THREADS, 0, xstream(c)>>>(a); break;
+      case 2: sumtable_dna_kernel<2><<<(unsigned)blocks, DV_THREADS, 0, xstream(c)>>>(a); break;
+      case 4: sumtable_dna_kernel<4><<<(unsigned)blocks, DV_THREADS, 0, xstream(c)>>>(a); break;
+      default: sumtable_dna_kernel<8><<<(unsigned)blocks, DV_THREADS, 0, xstream(c)>>>(a); break;
     }
   }
   else
   {
     const unsigned int spb = DVG_THREADS / K;
     const unsigned int blocks = (a.sites + spb - 1) / spb;
-    sumtable_generic_kernel<<<blocks, DVG_THREADS, 0, c->stream>>>(a);
+    sumtable_generic_kernel<<<blocks, DVG_THREADS, 0, xstream(c)>>>(a);
   }
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "sumtable kernel launch");
@@ -657,4 +680,12 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     return pllb200_cuda_ok(cudaGetLastError(), "asc derivative kernel launch");
   }
   return true;
+}
+
+bool flush_sum_dna4(PartCtx * lead, const void * d_args, const BatchKind & k)
+{
+  sumtable_dna_batch_kernel<4><<<dim3(k.max_blocks, k.count), DV_THREADS, 0, lead->stream>>>(
+      static_cast<const SumArgs *>(d_args));
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "batched sumtable kernel launch");
 }

@@ -1241,7 +1241,7 @@ bool launch_newton_multi(PartCtx ** cs, unsigned int count, unsigned int * const
     c0->multi_shadow = img;
   }
   /* the other partitions' sumtables (and input uploads) were queued on their own streams */
-  for (unsigned int i = 1; i < count; ++i)
+  for (unsigned int i = 1; i < count && !g_batch; ++i) /* in batch mode everything already runs on one stream */
   {
     PartCtx * c = cs[i];
     if (c->stream == c0->stream) continue;

@@ -20,23 +20,21 @@ struct PmatArgs
   unsigned int params_idx[PM_MAXK];
   double rates[PM_MAXK];
   double pinv[PM_MAXK];
+  /* a single matrix travels in the kernel parameters: index when `matrix_indices` is null, length when
+   * `branch_lengths` is null */
+  unsigned int one_index;
+  double one_length;
 };
 
-__global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__ pmat_il,
-                               const double * __restrict__ eigen, size_t eigen_stride,
-                               const unsigned int * __restrict__ matrix_indices,
-                               const double * __restrict__ branch_lengths, unsigned int states,
-                               unsigned int sp, unsigned int K, PmatArgs a)
+__device__ __forceinline__ void pmatrix_body(double * __restrict__ pmat, double * __restrict__ pmat_il,
+                                             const double * __restrict__ eigen, size_t eigen_stride,
+                                             unsigned int m, double t, unsigned int k, unsigned int states,
+                                             unsigned int sp, unsigned int K, const PmatArgs & a)
 {
   extern __shared__ double sm[]; /* expd[sp] | inv[s*sp] | ev[s*sp] */
   double * expd = sm;
   double * s_inv = sm + sp;
   double * s_ev = s_inv + states * sp;
-
-  const unsigned int e = blockIdx.x / K;
-  const unsigned int k = blockIdx.x % K;
-  const unsigned int m = matrix_indices[e];
-  const double t = branch_lengths[e];
   const double * blk = eigen + (size_t)a.params_idx[k] * eigen_stride;
   const double * g_ev = blk;
   const double * g_inv = blk + states * sp;
@@ -80,6 +78,42 @@ __global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__
   }
 }
 
+__global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__ pmat_il,
+                               const double * __restrict__ eigen, size_t eigen_stride,
+                               const unsigned int * __restrict__ matrix_indices,
+                               const double * __restrict__ branch_lengths, unsigned int states,
+                               unsigned int sp, unsigned int K, PmatArgs a)
+{
+  const unsigned int e = blockIdx.x / K;
+  const unsigned int k = blockIdx.x % K;
+  const unsigned int m = matrix_indices ? matrix_indices[e] : a.one_index;
+  const double t = branch_lengths ? branch_lengths[e] : a.one_length;
+  pmatrix_body(pmat, pmat_il, eigen, eigen_stride, m, t, k, states, sp, K, a);
+}
+
+/* one matrix of each of many partitions in one launch (blockIdx.y = partition, blockIdx.x = category;
+ * batch mode, internal.h) */
+struct PmatBatchPart
+{
+  double * pmat;
+  double * pmat_il;
+  const double * eigen;
+  unsigned long long eigen_stride;
+  unsigned int states, sp, K, pad;
+  PmatArgs a;
+};
+
+__global__ void pmatrix_batch_kernel(const PmatBatchPart * __restrict__ parts)
+{
+  __shared__ PmatBatchPart sp_;
+  for (unsigned int i = threadIdx.x; i < sizeof(PmatBatchPart) / 4; i += blockDim.x)
+    reinterpret_cast<unsigned int *>(&sp_)[i] = reinterpret_cast<const unsigned int *>(parts + blockIdx.y)[i];
+  __syncthreads();
+  if (blockIdx.x >= sp_.K) return;
+  pmatrix_body(sp_.pmat, sp_.pmat_il, sp_.eigen, sp_.eigen_stride, sp_.a.one_index, sp_.a.one_length, blockIdx.x,
+               sp_.states, sp_.sp, sp_.K, sp_.a);
+}
+
 /* one matrix whose branch length is already on the device (written by the queued Newton kernel) */
 bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,
                            const double * d_length)
@@ -99,8 +133,9 @@ bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, uns
     a.rates[k] = p->rates[k];
     a.pinv[k] = p->prop_invar[params_indices[k]];
   }
-  const unsigned int * d_idx = (const unsigned int *)dev_stage(c, &matrix_index, sizeof(unsigned int));
-  if (!d_idx) return false;
+  a.one_index = matrix_index;
+  a.one_length = 0.0;
+  const unsigned int * d_idx = nullptr;
   unsigned int threads = ((s * sp + 31) / 32) * 32;
   if (threads > 512) threads = 512;
   const size_t smem = sizeof(double) * (sp + 2 * s * sp);
@@ -168,14 +203,55 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
       return false;
     }
   }
-  const unsigned int * d_idx = (const unsigned int *)dev_stage(c, matrix_indices, sizeof(unsigned int) * count);
-  const double * d_len = (const double *)dev_stage(c, branch_lengths, sizeof(double) * count);
-  if (!d_idx || !d_len) return false;
+  const unsigned int * d_idx = nullptr;
+  const double * d_len = nullptr;
+  a.one_index = count ? matrix_indices[0] : 0;
+  a.one_length = count ? branch_lengths[0] : 0.0;
   unsigned int threads = ((s * sp + 31) / 32) * 32;
   if (threads > 512) threads = 512;
   const size_t smem = sizeof(double) * (sp + 2 * s * sp);
-  pmatrix_kernel<<<count * K, threads, smem, c->stream>>>(c->d_pmat, c->d_pmat_il, c->d_eigen,
-                                                          c->eigen_stride, d_idx, d_len, s, sp, K, a);
+  if (g_batch && !(g_opt_batch & (2 << BK_PMAT)) && count == 1)
+  {
+    PmatBatchPart b;
+    memset(&b, 0, sizeof(b));
+    b.pmat = c->d_pmat;
+    b.pmat_il = c->d_pmat_il;
+    b.eigen = c->d_eigen;
+    b.eigen_stride = c->eigen_stride;
+    b.states = s;
+    b.sp = sp;
+    b.K = K;
+    b.a = a;
+    batch_collect(BK_PMAT, &b, sizeof(b), (K << 16) | threads, smem);
+    return true;
+  }
+  if (count != 1)
+  {
+    d_idx = (const unsigned int *)dev_stage_small(c, matrix_indices, sizeof(unsigned int) * count);
+    d_len = (const double *)dev_stage_small(c, branch_lengths, sizeof(double) * count);
+    if (!d_idx || !d_len) return false;
+  }
+  pmatrix_kernel<<<count * K, threads, smem, xstream(c)>>>(c->d_pmat, c->d_pmat_il, c->d_eigen,
+                                                           c->eigen_stride, d_idx, d_len, s, sp, K, a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "pmatrix_kernel launch");
+}
+
+bool flush_pmat(PartCtx * lead, const void * d_args, const BatchKind & k)
+{
+  /* max_blocks carries (largest K << 16) | largest thread count: both maxima of the packed word's halves
+   * only if taken separately, so recompute them from the collected structs */
+  unsigned int maxK = 1, threads = 32;
+  const PmatBatchPart * h = reinterpret_cast<const PmatBatchPart *>(k.bytes.data());
+  for (unsigned int i = 0; i < k.count; ++i)
+  {
+    maxK = h[i].K > maxK ? h[i].K : maxK;
+    unsigned int t = ((h[i].states * h[i].sp + 31) / 32) * 32;
+    if (t > 512) t = 512;
+    threads = t > threads ? t : threads;
+  }
+  pmatrix_batch_kernel<<<dim3(maxK, k.count), threads, k.smem, lead->stream>>>(
+      static_cast<const PmatBatchPart *>(d_args));
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "batched pmatrix kernel launch");
 }

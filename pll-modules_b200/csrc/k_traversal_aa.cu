@@ -94,7 +94,7 @@ __device__ __forceinline__ void dmma(double & c0, double & c1, double a, double 
 
 /* dynamic shared memory: AaOp ops[AA_SEG] | u64 tipmap[256] | u64 bar[2] | u32 cnt[2] | double mat[2 stages][2][K*480] */
 template <int AA_T, int AA_WARPS, int MINB>
-__global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_kernel(AaArgs a)
+__device__ __forceinline__ void trav_aa_body(const AaArgs & a)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   AaOp * s_ops = reinterpret_cast<AaOp *>(smem_raw);
@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_kernel(AaArgs a)
   const unsigned long long span = (unsigned long long)K * 20; /* doubles per site */
   const unsigned long long sites_per_cta = (unsigned long long)AA_WARPS * 8 * AA_T;
   const unsigned long long nchunks = (a.sites + sites_per_cta - 1) / sites_per_cta;
+  if (blockIdx.x >= nchunks) return; /* batched launch: the grid is sized for the largest partition */
 
   for (int i = threadIdx.x; i < 256; i += blockDim.x) s_tipmap[i] = a.tipmap ? a.tipmap[i] : 0ull;
   if (threadIdx.x == 0)
@@ -308,6 +309,23 @@ __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_kernel(AaArgs a)
   }
 }
 
+template <int AA_T, int AA_WARPS, int MINB>
+__global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_kernel(AaArgs a)
+{
+  trav_aa_body<AA_T, AA_WARPS, MINB>(a);
+}
+
+/* many partitions in one launch (blockIdx.y = partition; batch mode, internal.h) */
+template <int AA_T, int AA_WARPS, int MINB>
+__global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_batch_kernel(const AaArgs * __restrict__ arr)
+{
+  __shared__ AaArgs sa;
+  for (unsigned int i = threadIdx.x; i < sizeof(AaArgs) / 4; i += blockDim.x)
+    reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
+  __syncthreads();
+  trav_aa_body<AA_T, AA_WARPS, MINB>(sa);
+}
+
 /* ---- host ------------------------------------------------------------------------------------ */
 
 int g_opt_aa_variant = 0;
@@ -334,7 +352,12 @@ static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
   unsigned long long blocks = (a.sites + spc - 1) / spc;
   blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
   if (blocks < 1) blocks = 1;
-  trav_aa_kernel<T, W, MINB><<<(unsigned int)blocks, W * 32, smem, c->stream>>>(a);
+  if (g_batch && !(g_opt_batch & (2 << BK_TRAV_AA)) && T == 2 && W == 4 && MINB == 3)
+  {
+    batch_collect(BK_TRAV_AA, &a, sizeof(a), (unsigned int)blocks, smem);
+    return true;
+  }
+  trav_aa_kernel<T, W, MINB><<<(unsigned int)blocks, W * 32, smem, xstream(c)>>>(a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_aa_kernel launch");
 }
@@ -385,7 +408,7 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
     d.m1_off = o.child1_matrix_index * K * AA_FRAG;
     d.m2_off = o.child2_matrix_index * K * AA_FRAG;
   }
-  const AaOp * d_ops = (const AaOp *)dev_stage(c, dops, sizeof(AaOp) * count);
+  const AaOp * d_ops = (const AaOp *)dev_stage_small(c, dops, sizeof(AaOp) * count);
   if (!d_ops) return false;
   AaArgs a;
   a.ops = d_ops;
@@ -414,6 +437,23 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
     case 12: return launch_aa_variant<4, 4, 3>(c, a);
     default: return launch_aa_variant<2, 4, 3>(c, a);
   }
+}
+
+bool flush_trav_aa(PartCtx * lead, const void * d_args, const BatchKind & k)
+{
+  static size_t smem_set = 0;
+  if (k.smem > smem_set)
+  {
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa_batch_kernel<2, 4, 3>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k.smem),
+                         "trav_aa batch smem attribute"))
+      return false;
+    smem_set = k.smem;
+  }
+  trav_aa_batch_kernel<2, 4, 3><<<dim3(k.max_blocks, k.count), 4 * 32, k.smem, lead->stream>>>(
+      static_cast<const AaArgs *>(d_args));
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "batched trav_aa kernel launch");
 }
 
 
@@ -448,7 +488,7 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
   if (!c->d_sumfrag)
   {
     if (!pllb200_cuda_ok(cudaMalloc(&c->d_sumfrag, frag_doubles * sizeof(double)), "sumtable fragments")) return false;
-    if (!pllb200_cuda_ok(cudaMemsetAsync(c->d_sumfrag, 0, frag_doubles * sizeof(double), c->stream), "sumtable fragments"))
+    if (!pllb200_cuda_ok(cudaMemsetAsync(c->d_sumfrag, 0, frag_doubles * sizeof(double), xstream(c)), "sumtable fragments"))
       return false;
     c->sumfrag_key.clear();
   }
@@ -459,7 +499,7 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
   {
     PmatIdx idx;
     for (unsigned int k = 0; k < K; ++k) idx.v[k] = params_indices[k];
-    sumfrag_kernel<<<K, 128, 0, c->stream>>>(c->d_sumfrag, c->d_eigen, c->eigen_stride, K, idx);
+    sumfrag_kernel<<<K, 128, 0, xstream(c)>>>(c->d_sumfrag, c->d_eigen, c->eigen_stride, K, idx);
     ++g_kernel_launches;
     if (!pllb200_cuda_ok(cudaGetLastError(), "sumfrag_kernel launch")) return false;
     c->sumfrag_key = key;
@@ -476,7 +516,7 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
   op.c2_off = (unsigned long long)(second - c->clv_first) * c->clv_stride;
   op.m1_off = 0;
   op.m2_off = K * AA_FRAG;
-  const AaOp * d_ops = (const AaOp *)dev_stage(c, &op, sizeof(op));
+  const AaOp * d_ops = (const AaOp *)dev_stage_small(c, &op, sizeof(op));
   if (!d_ops) return false;
   AaArgs a;
   a.ops = d_ops;

@@ -361,7 +361,7 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
 /* the last, partial chunk: same code with guards, kept out of line so that it does not inflate the
  * register allocation of the hot path.  MINB is a template parameter on purpose: one callee per kernel,
  * so that ptxas sizes it under that kernel's register cap. */
-template <int K, int R, bool RATE_SCALERS, int MINB>
+template <int K, int R, bool RATE_SCALERS, int MINB, int TAG>
 __device__ __noinline__ void run_segment_tail(const TravArgs & a, TravSmem<K> & sm, unsigned int nseg,
                                               unsigned int s0, int lane, int warp,
                                               unsigned int & ph)
@@ -369,8 +369,8 @@ __device__ __noinline__ void run_segment_tail(const TravArgs & a, TravSmem<K> & 
   run_segment<K, R, RATE_SCALERS, false>(a, sm, nseg, s0, lane, warp, ph);
 }
 
-template <int K, int R, bool RATE_SCALERS, int MINB>
-__global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArgs a)
+template <int K, int R, bool RATE_SCALERS, int MINB, int TAG> /* TAG: one out-of-line tail per kernel */
+__device__ __forceinline__ void trav_dna_body(const TravArgs & a)
 {
   __shared__ __align__(128) TravSmem<K> sm;
 
@@ -405,9 +405,27 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArg
       if ((chunk + 1) * SPC <= a.sites)
         run_segment<K, R, RATE_SCALERS, true>(a, sm, nseg, s0, lane, warp, ph);
       else
-        run_segment_tail<K, R, RATE_SCALERS, MINB>(a, sm, nseg, s0, lane, warp, ph);
+        run_segment_tail<K, R, RATE_SCALERS, MINB, TAG>(a, sm, nseg, s0, lane, warp, ph);
     }
   }
+}
+
+template <int K, int R, bool RATE_SCALERS, int MINB>
+__global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArgs a)
+{
+  trav_dna_body<K, R, RATE_SCALERS, MINB, 0>(a);
+}
+
+/* many partitions in one launch (blockIdx.y = partition; batch mode, internal.h) */
+template <int K, int R, bool RATE_SCALERS, int MINB>
+__global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_batch_kernel(const TravArgs * __restrict__ arr)
+{
+  __shared__ TravArgs sa;
+  for (unsigned int i = threadIdx.x; i < sizeof(TravArgs) / 4; i += blockDim.x)
+    reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
+  __syncthreads();
+  const TravArgs a = sa; /* by value like the plain kernel (the out-of-line tail takes its address) */
+  trav_dna_body<K, R, RATE_SCALERS, MINB, 1>(a);
 }
 
 /* ---- host ------------------------------------------------------------------------------------ */
@@ -436,7 +454,12 @@ static bool launch_variant(PartCtx * c, const TravArgs & a)
   const unsigned long long cap = (unsigned long long)c->sm_count * per_sm;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  trav_dna_kernel<K, R, RS, MINB><<<(unsigned int)blocks, TRAV_WARPS * 32, 0, c->stream>>>(a);
+  if (g_batch && !(g_opt_batch & (2 << BK_TRAV_DNA4)) && K == 4 && R == 4 && !RS && MINB == 2)
+  {
+    batch_collect(BK_TRAV_DNA4, &a, sizeof(a), (unsigned int)blocks, 0);
+    return true;
+  }
+  trav_dna_kernel<K, R, RS, MINB><<<(unsigned int)blocks, TRAV_WARPS * 32, 0, xstream(c)>>>(a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_dna_kernel launch");
 }
@@ -523,7 +546,7 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
       }
     }
   }
-  const DevOp * d_ops = (const DevOp *)dev_stage(c, dops, sizeof(DevOp) * count);
+  const DevOp * d_ops = (const DevOp *)dev_stage_small(c, dops, sizeof(DevOp) * count);
   if (!d_ops) return false;
   TravArgs a;
   a.ops = d_ops;
@@ -541,4 +564,12 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
     case 4: return launch_k<4>(c, a, rate_scalers);
     default: return launch_k<8>(c, a, rate_scalers);
   }
+}
+
+bool flush_trav_dna4(PartCtx * lead, const void * d_args, const BatchKind & k)
+{
+  trav_dna_batch_kernel<4, 4, false, 2><<<dim3(k.max_blocks, k.count), TRAV_WARPS * 32, 0, lead->stream>>>(
+      static_cast<const TravArgs *>(d_args));
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "batched trav_dna kernel launch");
 }

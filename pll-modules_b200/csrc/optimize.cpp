@@ -230,6 +230,7 @@ static void reorient_clv(pll_partition_t ** partitions, size_t partition_count, 
   op.child2_scaler_index = left_child->back->scaler_index;
   for (size_t p = 0; p < partition_count; ++p)
     if (partitions[p]) pll_update_partials(partitions[p], &op, 1);
+  pllb200_batch_flush(); /* batch mode: the loop only collected; one launch per kernel kind */
 }
 
 /* ---- single partition (legacy NR) ------------------------------------------------------------- */
@@ -466,6 +467,7 @@ static void refresh_pmatrix_multi(pll_partition_t ** partitions, size_t partitio
     if (brlen_scalers) l *= brlen_scalers[p];
     pll_update_prob_matrices(partitions[p], params_indices[p], &m, &l, 1);
   }
+  pllb200_batch_flush();
 }
 
 static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int radius,
@@ -506,6 +508,7 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
                                tr_p->scaler_index, tr_p->back->scaler_index,
                                prm->params_indices[p], prm->precomp_buffers[p]))
         return PLL_FAILURE;
+  if (!pllb200_batch_flush()) return PLL_FAILURE;
 
   const double xmin = prm->branch_length_min, xmax = prm->branch_length_max, xtol = prm->tolerance;
   int retval;
@@ -558,6 +561,8 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
                                             xtol, (unsigned int)prm->max_newton_iters, &xguess[0], nullptr);
         if (fused >= 0 && prm->converged) prm->converged[0] = fused == 1;
       }
+      if (fused == -2 && pllb200_batch_active())
+        pllb200_batch_end(); /* the derivative kernels of the fallback are launched per partition */
       if (fused == -2)
         retval = pllmod_opt_minimize_newton_multi(xnum, xmin, xguess, xmax, xtol,
                                                   prm->max_newton_iters, prm->converged, prm,
@@ -751,6 +756,12 @@ extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
       queue.nodes.clear();
       queue.on_device.assign(queue.on_device.size(), 0);
       t_queued = can_queue ? &queue : nullptr;
+      /* many small partitions with one shared length per branch: one launch per kernel kind and branch
+       * instead of one per partition (device_ctx.cu, batch mode) */
+      if (keep_update && opt_method == PLLMOD_OPT_BLO_NEWTON_FAST && partition_count > 1 && !parallel_reduce_cb &&
+          prm.brlen_linkage != PLLMOD_COMMON_BRLEN_UNLINKED && g_opt_fused_newton != 0 &&
+          pllb200_batch_begin(partitions, (unsigned int)partition_count) < 0)
+        goto cleanup;
       int ok = optimise_branch_rec_multi(&prm, radius, &new_loglh, keep_update);
       if (ok && radius)
       {
@@ -758,6 +769,7 @@ extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
         ok = optimise_branch_rec_multi(&prm, radius - 1, &new_loglh, keep_update);
       }
       t_queued = nullptr;
+      if (!pllb200_batch_end()) ok = 0;
       /* lengths the device decided on -> tree and caller's buffers (also after a failure: the P-matrices
        * on the device already use them) */
       if (!collect_queued(queue, partitions[0], brlen_buffers) || !ok) goto cleanup;
