@@ -699,11 +699,39 @@ void batch_collect(int kind, const void * args, size_t bytes, unsigned int block
   if (smem > k.smem) k.smem = smem;
 }
 
+const void * batch_pool_add(const void * src, size_t bytes)
+{
+  std::vector<unsigned char> & pool = g_batch->pool;
+  const size_t off = round_up(pool.size(), 64);
+  pool.resize(off + bytes);
+  memcpy(pool.data() + off, src, bytes);
+  g_h2d_bytes += bytes;
+  return reinterpret_cast<const void *>(BATCH_POOL_TAG + off);
+}
+
 bool batch_flush()
 {
   BatchCtx * b = g_batch;
   if (!b) return true;
   bool ok = true;
+  if (!b->pool.empty())
+  {
+    const unsigned long long d_pool = (unsigned long long)dev_stage(b->lead, b->pool.data(), b->pool.size());
+    if (!d_pool) ok = false;
+    g_h2d_bytes -= b->pool.size(); /* counted when added */
+    for (int kind : {(int)BK_TRAV_DNA4, (int)BK_TRAV_AA})
+    {
+      BatchKind & k = b->kind[kind];
+      if (!k.count) continue;
+      const size_t stride = k.bytes.size() / k.count;
+      for (unsigned int i = 0; i < k.count; ++i)
+      {
+        unsigned long long * ops = reinterpret_cast<unsigned long long *>(k.bytes.data() + i * stride);
+        if ((*ops >> 60) == 7ull) *ops = d_pool + (*ops - BATCH_POOL_TAG);
+      }
+    }
+    b->pool.clear();
+  }
   for (int kind = 0; kind < BK_COUNT && ok; ++kind)
   {
     BatchKind & k = b->kind[kind];

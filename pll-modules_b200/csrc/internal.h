@@ -164,8 +164,15 @@ struct BatchCtx
   PartCtx * lead;
   std::vector<PartCtx *> members;
   BatchKind kind[BK_COUNT];
+  std::vector<unsigned char> pool; /* resolved ops of the collected launches: staged once per flush */
 };
+/* ops of a launch that WILL be collected: returns a token that batch_flush turns into a device pointer
+ * (the `ops` pointer is the first member of TravArgs and AaArgs) */
+#define BATCH_POOL_TAG 0x7000000000000000ull
+const void * batch_pool_add(const void * src, size_t bytes);
+static inline bool batch_collects(int kind);
 extern thread_local BatchCtx * g_batch;
+extern int g_opt_batch;
 void batch_collect(int kind, const void * args, size_t bytes, unsigned int blocks, size_t smem);
 bool batch_flush();
 /* per kind, in the kernel's own file: launch `k.count` argument structs staged at `d_args` */
@@ -176,6 +183,7 @@ bool flush_pmat(PartCtx * lead, const void * d_args, const BatchKind & k);
 bool batch_eligible(const PartCtx * c);
 /* the stream a launcher uses: the lead's in batch mode */
 static inline cudaStream_t xstream(const PartCtx * c) { return g_batch ? g_batch->lead->stream : c->stream; }
+static inline bool batch_collects(int kind) { return g_batch && !(g_opt_batch & (2 << kind)); }
 
 /* device context (device_ctx.cu) */
 bool dev_ctx_init(PartCtx * c);      /* allocates arenas for c->pub geometry */
@@ -185,7 +193,6 @@ void * dev_stage(PartCtx * c, const void * src, size_t bytes); /* returns device
 #define PLLB200_SMALL_MAX 256u
 void * dev_stage_small(PartCtx * c, const void * src, size_t bytes); /* <= 256 B: mapped host memory, no copy call */
 extern int g_opt_small_stage;
-extern int g_opt_batch;
 bool dev_sync_inputs(PartCtx * c);   /* push dirty tipchars / weights / invariant / tipmap */
 bool dev_sync_eigen(PartCtx * c, const unsigned int * params_indices); /* ensure eigen block current */
 bool dev_flush(PartCtx * c);            /* stream sync + deliver pending async results */

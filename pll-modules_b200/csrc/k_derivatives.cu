@@ -517,7 +517,7 @@ bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_cl
     unsigned long long blocks = (E + DV_THREADS - 1) / DV_THREADS;
     const unsigned long long cap = (unsigned long long)c->sm_count * 4; /* one resident wave (launch bounds) */
     if (blocks > cap) blocks = cap;
-    if (g_batch && !(g_opt_batch & (2 << BK_SUM_DNA4)) && K == 4)
+    if (batch_collects(BK_SUM_DNA4) && K == 4)
     {
       batch_collect(BK_SUM_DNA4, &a, sizeof(a), (unsigned)blocks, 0);
       return true;

@@ -210,7 +210,7 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
   unsigned int threads = ((s * sp + 31) / 32) * 32;
   if (threads > 512) threads = 512;
   const size_t smem = sizeof(double) * (sp + 2 * s * sp);
-  if (g_batch && !(g_opt_batch & (2 << BK_PMAT)) && count == 1)
+  if (batch_collects(BK_PMAT) && count == 1)
   {
     PmatBatchPart b;
     memset(&b, 0, sizeof(b));

@@ -352,7 +352,7 @@ static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
   unsigned long long blocks = (a.sites + spc - 1) / spc;
   blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
   if (blocks < 1) blocks = 1;
-  if (g_batch && !(g_opt_batch & (2 << BK_TRAV_AA)) && T == 2 && W == 4 && MINB == 3)
+  if (batch_collects(BK_TRAV_AA) && T == 2 && W == 4 && MINB == 3)
   {
     batch_collect(BK_TRAV_AA, &a, sizeof(a), (unsigned int)blocks, smem);
     return true;
@@ -408,7 +408,9 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
     d.m1_off = o.child1_matrix_index * K * AA_FRAG;
     d.m2_off = o.child2_matrix_index * K * AA_FRAG;
   }
-  const AaOp * d_ops = (const AaOp *)dev_stage_small(c, dops, sizeof(AaOp) * count);
+  const bool collect = batch_collects(BK_TRAV_AA) && g_opt_aa_variant == 0; /* as in launch_aa_variant */
+  const AaOp * d_ops = collect ? (const AaOp *)batch_pool_add(dops, sizeof(AaOp) * count)
+                               : (const AaOp *)dev_stage_small(c, dops, sizeof(AaOp) * count);
   if (!d_ops) return false;
   AaArgs a;
   a.ops = d_ops;
@@ -516,7 +518,8 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
   op.c2_off = (unsigned long long)(second - c->clv_first) * c->clv_stride;
   op.m1_off = 0;
   op.m2_off = K * AA_FRAG;
-  const AaOp * d_ops = (const AaOp *)dev_stage_small(c, &op, sizeof(op));
+  const AaOp * d_ops = batch_collects(BK_TRAV_AA) ? (const AaOp *)batch_pool_add(&op, sizeof(op))
+                                                   : (const AaOp *)dev_stage_small(c, &op, sizeof(op));
   if (!d_ops) return false;
   AaArgs a;
   a.ops = d_ops;

@@ -454,7 +454,7 @@ static bool launch_variant(PartCtx * c, const TravArgs & a)
   const unsigned long long cap = (unsigned long long)c->sm_count * per_sm;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  if (g_batch && !(g_opt_batch & (2 << BK_TRAV_DNA4)) && K == 4 && R == 4 && !RS && MINB == 2)
+  if (batch_collects(BK_TRAV_DNA4) && g_opt_trav_variant == 0 && K == 4 && R == 4 && !RS && MINB == 2)
   {
     batch_collect(BK_TRAV_DNA4, &a, sizeof(a), (unsigned int)blocks, 0);
     return true;
@@ -546,7 +546,10 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
       }
     }
   }
-  const DevOp * d_ops = (const DevOp *)dev_stage_small(c, dops, sizeof(DevOp) * count);
+  /* same condition as the collect branch of launch_variant (default variant of K = 4) */
+  const bool collect = batch_collects(BK_TRAV_DNA4) && K == 4 && !rate_scalers && g_opt_trav_variant == 0;
+  const DevOp * d_ops = collect ? (const DevOp *)batch_pool_add(dops, sizeof(DevOp) * count)
+                                : (const DevOp *)dev_stage_small(c, dops, sizeof(DevOp) * count);
   if (!d_ops) return false;
   TravArgs a;
   a.ops = d_ops;

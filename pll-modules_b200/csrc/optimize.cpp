@@ -16,6 +16,7 @@
 #include <cassert>
 #include <cmath>
 #include <cstdlib>
+#include <chrono>
 #include <vector>
 
 #define BETTER_LL_THRESHOLD 1e-13 /* pll_optimize.c:40 */
@@ -215,6 +216,19 @@ extern "C" double pllmod_opt_compute_edge_loglikelihood_multi(
   return total;
 }
 
+/* PLLB200_TRACE_BLO=1: host wall time per phase of the smoothing passes on stderr */
+struct BloTrace
+{
+  double sum_s = 0, newton_s = 0, pmat_s = 0, reorient_s = 0;
+  unsigned long long branches = 0;
+  bool on = getenv("PLLB200_TRACE_BLO") != nullptr;
+  static double now()
+  {
+    return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+  }
+};
+static BloTrace g_blo_trace;
+
 /* re-orient one inner CLV: parent <- (right_child->back, left_child->back)  (pll_optimize.c:748-775) */
 static void reorient_clv(pll_partition_t ** partitions, size_t partition_count, pll_unode_t * parent,
                          pll_unode_t * right_child, pll_unode_t * left_child)
@@ -228,9 +242,11 @@ static void reorient_clv(pll_partition_t ** partitions, size_t partition_count, 
   op.child2_clv_index = left_child->back->clv_index;
   op.child2_matrix_index = left_child->back->pmatrix_index;
   op.child2_scaler_index = left_child->back->scaler_index;
+  const double t0 = g_blo_trace.on ? BloTrace::now() : 0.0;
   for (size_t p = 0; p < partition_count; ++p)
     if (partitions[p]) pll_update_partials(partitions[p], &op, 1);
   pllb200_batch_flush(); /* batch mode: the loop only collected; one launch per kernel kind */
+  if (g_blo_trace.on) g_blo_trace.reorient_s += BloTrace::now() - t0;
 }
 
 /* ---- single partition (legacy NR) ------------------------------------------------------------- */
@@ -383,6 +399,7 @@ extern "C" double pllmod_opt_optimize_branch_lengths_iterative(
 
 /* ---- multi partition -------------------------------------------------------------------------- */
 
+
 static void multi_deriv_cb(void * parameters, double * proposal, double * df, double * ddf)
 {
   /* pll_optimize.c:1223-1287.  Derivative kernels of all local partitions are queued first and
@@ -502,6 +519,7 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
   }
   if (prm->converged) memset(prm->converged, 0, sizeof(int) * xnum);
 
+  const double tr0 = g_blo_trace.on ? BloTrace::now() : 0.0;
   for (unsigned int p = 0; p < prm->partition_count; ++p)
     if (prm->partitions[p])
       if (!pll_update_sumtable(prm->partitions[p], tr_p->clv_index, tr_p->back->clv_index,
@@ -509,6 +527,7 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
                                prm->params_indices[p], prm->precomp_buffers[p]))
         return PLL_FAILURE;
   if (!pllb200_batch_flush()) return PLL_FAILURE;
+  const double tr1 = g_blo_trace.on ? BloTrace::now() : 0.0;
 
   const double xmin = prm->branch_length_min, xmax = prm->branch_length_max, xtol = prm->tolerance;
   int retval;
@@ -595,6 +614,7 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
     pllmod_reset_error();
   }
 
+  const double tr2 = g_blo_trace.on ? BloTrace::now() : 0.0;
   bool apply_change = false;
   for (unsigned int p = 0; p < xnum; ++p)
   {
@@ -629,6 +649,13 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
     }
   }
 
+  if (g_blo_trace.on)
+  {
+    g_blo_trace.sum_s += tr1 - tr0;
+    g_blo_trace.newton_s += tr2 - tr1;
+    g_blo_trace.pmat_s += BloTrace::now() - tr2;
+    ++g_blo_trace.branches;
+  }
   } /* !queued */
 
   if (radius && tr_q && tr_z)
@@ -796,6 +823,14 @@ extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
     result = -1 * loglh;
   }
 cleanup:
+  if (g_blo_trace.on && g_blo_trace.branches)
+  {
+    fprintf(stderr, "[pllb200 blo] %llu branches: sumtable %.1f us, newton %.1f us, pmatrix %.1f us, reorient %.1f us per branch\n",
+            g_blo_trace.branches, 1e6 * g_blo_trace.sum_s / g_blo_trace.branches,
+            1e6 * g_blo_trace.newton_s / g_blo_trace.branches, 1e6 * g_blo_trace.pmat_s / g_blo_trace.branches,
+            1e6 * g_blo_trace.reorient_s / g_blo_trace.branches);
+    g_blo_trace = BloTrace();
+  }
   for (double * b : own_precomp) pll_aligned_free(b);
   return result;
 }
