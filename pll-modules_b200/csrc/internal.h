@@ -183,6 +183,15 @@ bool flush_pmat(PartCtx * lead, const void * d_args, const BatchKind & k);
 bool batch_eligible(const PartCtx * c);
 /* the stream a launcher uses: the lead's in batch mode */
 static inline cudaStream_t xstream(const PartCtx * c) { return g_batch ? g_batch->lead->stream : c->stream; }
+/* grid.x of a batched launch: enough CTAs per partition for the largest one, but not more than one
+ * resident wave over all partitions (every CTA then pays its start-up — matrices by TMA, tables — once) */
+static inline unsigned int batch_grid_x(const PartCtx * lead, const BatchKind & k, unsigned int ctas_per_sm)
+{
+  const unsigned int wave = (unsigned int)lead->sm_count * ctas_per_sm;
+  unsigned int gx = (wave + k.count - 1) / k.count;
+  if (gx > k.max_blocks) gx = k.max_blocks;
+  return gx < 1 ? 1 : gx;
+}
 static inline bool batch_collects(int kind) { return g_batch && !(g_opt_batch & (2 << kind)); }
 
 /* device context (device_ctx.cu) */

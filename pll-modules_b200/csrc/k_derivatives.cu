@@ -684,7 +684,7 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
 
 bool flush_sum_dna4(PartCtx * lead, const void * d_args, const BatchKind & k)
 {
-  sumtable_dna_batch_kernel<4><<<dim3(k.max_blocks, k.count), DV_THREADS, 0, lead->stream>>>(
+  sumtable_dna_batch_kernel<4><<<dim3(batch_grid_x(lead, k, 4), k.count), DV_THREADS, 0, lead->stream>>>(
       static_cast<const SumArgs *>(d_args));
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "batched sumtable kernel launch");

@@ -452,6 +452,7 @@ bool flush_trav_aa(PartCtx * lead, const void * d_args, const BatchKind & k)
       return false;
     smem_set = k.smem;
   }
+  /* measured at 50 x 2500 sites: one CTA per 64-site chunk 80 us, one resident wave of CTAs looping over chunks 98 us */
   trav_aa_batch_kernel<2, 4, 3><<<dim3(k.max_blocks, k.count), 4 * 32, k.smem, lead->stream>>>(
       static_cast<const AaArgs *>(d_args));
   ++g_kernel_launches;

@@ -571,7 +571,7 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
 
 bool flush_trav_dna4(PartCtx * lead, const void * d_args, const BatchKind & k)
 {
-  trav_dna_batch_kernel<4, 4, false, 2><<<dim3(k.max_blocks, k.count), TRAV_WARPS * 32, 0, lead->stream>>>(
+  trav_dna_batch_kernel<4, 4, false, 2><<<dim3(batch_grid_x(lead, k, 2), k.count), TRAV_WARPS * 32, 0, lead->stream>>>(
       static_cast<const TravArgs *>(d_args));
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "batched trav_dna kernel launch");

@@ -73,6 +73,7 @@ if "c4" in which:
         pkg.reset_stats()
         t = timed(lambda: h.loglh(0), 5)
         launches = pkg.stats()["kernel_launches"] / 6
+        h.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)   # first pass: allocates the sumtables
         pkg.reset_stats()
         tb0 = time.perf_counter()
         nll = h.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)

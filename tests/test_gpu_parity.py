@@ -240,6 +240,20 @@ def test_shared_branch_length_newton_over_many_partitions(linkage):
             assert pkg.stats()["kernel_launches"] > 1.5 * fused_launches
     finally:
         pkg.set_option("fused_newton", 1)
+    # batch mode off (one launch per partition and kernel): bit-identical lengths, several times the launches
+    _, dev3 = pair(**kw)
+    pkg.set_option("batch", 0)
+    try:
+        with dev3:
+            dev3.loglh()
+            if linkage == 1:
+                dev3.algo_opt_treeinfo("brlen_scalers", 1e-2)
+            pkg.reset_stats()
+            d = dev3.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=3, lh_epsilon=0.01)
+            assert d == b, (d, b)
+            assert pkg.stats()["kernel_launches"] > 2 * fused_launches
+    finally:
+        pkg.set_option("batch", 1)
 
 
 @needs_ref
