@@ -719,16 +719,21 @@ bool batch_flush()
     const unsigned long long d_pool = (unsigned long long)dev_stage(b->lead, b->pool.data(), b->pool.size());
     if (!d_pool) ok = false;
     g_h2d_bytes -= b->pool.size(); /* counted when added */
-    for (int kind : {(int)BK_TRAV_DNA4, (int)BK_TRAV_AA})
+    /* pointer members that may hold pool tokens: the first one of TravArgs / AaArgs (ops), the first two
+     * of PmatBatchPart (indices, lengths) */
+    static const int kinds[3] = {BK_TRAV_DNA4, BK_TRAV_AA, BK_PMAT};
+    static const int nptr[3] = {1, 1, 2};
+    for (int q = 0; q < 3; ++q)
     {
-      BatchKind & k = b->kind[kind];
+      BatchKind & k = b->kind[kinds[q]];
       if (!k.count) continue;
       const size_t stride = k.bytes.size() / k.count;
       for (unsigned int i = 0; i < k.count; ++i)
-      {
-        unsigned long long * ops = reinterpret_cast<unsigned long long *>(k.bytes.data() + i * stride);
-        if ((*ops >> 60) == 7ull) *ops = d_pool + (*ops - BATCH_POOL_TAG);
-      }
+        for (int f = 0; f < nptr[q]; ++f)
+        {
+          unsigned long long * ptr = reinterpret_cast<unsigned long long *>(k.bytes.data() + i * stride) + f;
+          if ((*ptr >> 60) == 7ull) *ptr = d_pool + (*ptr - BATCH_POOL_TAG);
+        }
     }
     b->pool.clear();
   }
@@ -742,10 +747,10 @@ bool batch_flush()
     else
       switch (kind)
       {
-        case BK_SUM_DNA4: ok = flush_sum_dna4(b->lead, d_args, k); break;
+        case BK_PMAT: ok = flush_pmat(b->lead, d_args, k); break;
         case BK_TRAV_DNA4: ok = flush_trav_dna4(b->lead, d_args, k); break;
         case BK_TRAV_AA: ok = flush_trav_aa(b->lead, d_args, k); break;
-        default: ok = flush_pmat(b->lead, d_args, k); break;
+        default: ok = flush_sum_dna4(b->lead, d_args, k); break;
       }
     k.bytes.clear();
     k.count = k.max_blocks = 0;

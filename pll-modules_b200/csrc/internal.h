@@ -152,7 +152,9 @@ extern int g_opt_aa_variant;
  * issues ONE launch per kind with blockIdx.y = partition, on the lead partition's stream (staging goes
  * through the lead's ring too).  begin makes the lead stream wait for every member stream, end makes the
  * member streams wait for the lead.  Launchers that are not batch-aware must not run in between. */
-enum { BK_SUM_DNA4 = 0, BK_TRAV_DNA4, BK_TRAV_AA, BK_PMAT, BK_COUNT };
+/* flush order: P-matrices, CLV updates, sumtables.  Calls collected between two flushes must otherwise be
+ * independent of each other (a flush is one phase of the caller's loop over partitions). */
+enum { BK_PMAT = 0, BK_TRAV_DNA4, BK_TRAV_AA, BK_SUM_DNA4, BK_COUNT };
 struct BatchKind
 {
   std::vector<unsigned char> bytes; /* argument structs back to back */

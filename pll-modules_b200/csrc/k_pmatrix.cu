@@ -95,11 +95,13 @@ __global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__
  * batch mode, internal.h) */
 struct PmatBatchPart
 {
+  const unsigned int * idx; /* pool tokens -> device pointers at flush (first two members, device_ctx.cu); */
+  const double * len;       /* null: one matrix, index and length in `a` */
   double * pmat;
   double * pmat_il;
   const double * eigen;
   unsigned long long eigen_stride;
-  unsigned int states, sp, K, pad;
+  unsigned int states, sp, K, count;
   PmatArgs a;
 };
 
@@ -109,9 +111,11 @@ __global__ void pmatrix_batch_kernel(const PmatBatchPart * __restrict__ parts)
   for (unsigned int i = threadIdx.x; i < sizeof(PmatBatchPart) / 4; i += blockDim.x)
     reinterpret_cast<unsigned int *>(&sp_)[i] = reinterpret_cast<const unsigned int *>(parts + blockIdx.y)[i];
   __syncthreads();
-  if (blockIdx.x >= sp_.K) return;
-  pmatrix_body(sp_.pmat, sp_.pmat_il, sp_.eigen, sp_.eigen_stride, sp_.a.one_index, sp_.a.one_length, blockIdx.x,
-               sp_.states, sp_.sp, sp_.K, sp_.a);
+  const unsigned int e = blockIdx.x / sp_.K, k = blockIdx.x % sp_.K;
+  if (e >= sp_.count) return;
+  const unsigned int m = sp_.idx ? sp_.idx[e] : sp_.a.one_index;
+  const double t = sp_.len ? sp_.len[e] : sp_.a.one_length;
+  pmatrix_body(sp_.pmat, sp_.pmat_il, sp_.eigen, sp_.eigen_stride, m, t, k, sp_.states, sp_.sp, sp_.K, sp_.a);
 }
 
 /* one matrix whose branch length is already on the device (written by the queued Newton kernel) */
@@ -210,10 +214,16 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
   unsigned int threads = ((s * sp + 31) / 32) * 32;
   if (threads > 512) threads = 512;
   const size_t smem = sizeof(double) * (sp + 2 * s * sp);
-  if (batch_collects(BK_PMAT) && count == 1)
+  if (batch_collects(BK_PMAT))
   {
     PmatBatchPart b;
     memset(&b, 0, sizeof(b));
+    b.count = count;
+    if (count != 1)
+    {
+      b.idx = (const unsigned int *)batch_pool_add(matrix_indices, sizeof(unsigned int) * count);
+      b.len = (const double *)batch_pool_add(branch_lengths, sizeof(double) * count);
+    }
     b.pmat = c->d_pmat;
     b.pmat_il = c->d_pmat_il;
     b.eigen = c->d_eigen;
@@ -222,7 +232,7 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
     b.sp = sp;
     b.K = K;
     b.a = a;
-    batch_collect(BK_PMAT, &b, sizeof(b), (K << 16) | threads, smem);
+    batch_collect(BK_PMAT, &b, sizeof(b), count * K, smem);
     return true;
   }
   if (count != 1)
@@ -239,18 +249,16 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
 
 bool flush_pmat(PartCtx * lead, const void * d_args, const BatchKind & k)
 {
-  /* max_blocks carries (largest K << 16) | largest thread count: both maxima of the packed word's halves
-   * only if taken separately, so recompute them from the collected structs */
-  unsigned int maxK = 1, threads = 32;
+  /* max_blocks = largest count * K; the thread count is the largest any member needs */
+  unsigned int threads = 32;
   const PmatBatchPart * h = reinterpret_cast<const PmatBatchPart *>(k.bytes.data());
   for (unsigned int i = 0; i < k.count; ++i)
   {
-    maxK = h[i].K > maxK ? h[i].K : maxK;
     unsigned int t = ((h[i].states * h[i].sp + 31) / 32) * 32;
     if (t > 512) t = 512;
     threads = t > threads ? t : threads;
   }
-  pmatrix_batch_kernel<<<dim3(maxK, k.count), threads, k.smem, lead->stream>>>(
+  pmatrix_batch_kernel<<<dim3(k.max_blocks, k.count), threads, k.smem, lead->stream>>>(
       static_cast<const PmatBatchPart *>(d_args));
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "batched pmatrix kernel launch");

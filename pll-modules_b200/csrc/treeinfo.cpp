@@ -599,12 +599,26 @@ static int queue_traversal(pllmod_treeinfo_t * ti, int incremental, int update_p
     if (!pll_utree_traverse(ti->root, PLL_TREE_TRAVERSE_POSTORDER, cb_full_traversal,
                             ti->travbuffer, &traversal_size))
       return PLL_FAILURE;
+  /* many partitions: P-matrices and CLV updates of all of them in one launch per kernel kind
+   * (device_ctx.cu, batch mode; 0 = these partitions cannot be batched, nothing changes) */
+  struct BatchScope
+  {
+    bool on;
+    ~BatchScope() { if (on) pllb200_batch_end(); }
+  } scope{false};
+  if (ti->partition_count > 1)
+  {
+    const int b = pllb200_batch_begin(ti->partitions, ti->partition_count);
+    if (b < 0) return PLL_FAILURE;
+    scope.on = b == 1;
+  }
   if (update_pmatrices)
   {
     if (collect_brlen)
       for (unsigned int i = 0; i < traversal_size; ++i)
         ti->branch_lengths[0][ti->travbuffer[i]->pmatrix_index] = ti->travbuffer[i]->length;
     if (!pllmod_treeinfo_update_prob_matrices(ti, !incremental)) return PLL_FAILURE;
+    if (scope.on && !pllb200_batch_flush()) return PLL_FAILURE;
   }
   if (incremental)
     if (!pll_utree_traverse(ti->root, PLL_TREE_TRAVERSE_POSTORDER, cb_partial_traversal,
@@ -622,6 +636,11 @@ static int queue_traversal(pllmod_treeinfo_t * ti, int incremental, int update_p
     pll_update_partials(ti->partitions[p], ti->operations, ops_count);
     if (pll_errno) return PLL_FAILURE;
     pllmod_treeinfo_validate_clvs(ti, ti->travbuffer, traversal_size);
+  }
+  if (scope.on)
+  {
+    scope.on = false;
+    if (!pllb200_batch_end()) return PLL_FAILURE;
   }
   return PLL_SUCCESS;
 }

@@ -1,5 +1,5 @@
 """Debug aid for batch mode (device_ctx.cu): the same smoothing pass with the collector off (0), on (1), and
-with single kernel kinds kept out of it (bit k+1 set = kind k launches per partition on the lead stream)."""
+with single kernel kinds kept out of it (bit k+1 set = kind k (internal.h: 0 P-matrix, 1 DNA CLV update, 2 protein CLV update, 3 DNA sumtable) launches per partition on the lead stream)."""
 import sys, os
 sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "..", "tests"))
 from pllharness import Harness, load_product_package
@@ -9,7 +9,7 @@ cases = [("mixed", dict(tips=18, sites=[900, 300, 1300, 77, 520, 33], states=[4,
          ("dna-ragged", dict(tips=18, sites=[900, 1300, 520], states=[4, 4, 4], alpha=[0.3, 1.0, 0.5], linkage=0)),
          ("aa", dict(tips=18, sites=[300, 77], states=[20, 20], alpha=[0.6, 2.0], linkage=0))]
 for name, kw in cases:
-    for mask in (0, 1, 29, 27, 23, 15):
+    for mask in (0, 1, 31 - 2, 31 - 4, 31 - 8, 31 - 16):
         pkg.set_option("batch", mask)
         with Harness("b200", **kw) as h:
             h.loglh()
