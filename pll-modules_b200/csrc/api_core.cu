@@ -294,7 +294,7 @@ extern "C" int pllb200_newton_branch_multi(pll_partition_t ** partitions, unsign
     if (!partitions[p]) continue;
     if (!enter(partitions[p])) return -1;
     PartCtx * c = ctx_of(partitions[p]);
-    if (!newton_fused_supported(c) || c->xchg_nranks > 1) return -2;
+    if (!newton_fused_supported(c)) return -2; /* an exchange, if any, is the FIRST partition's (site-sharded ranks) */
     double * d = sumtable_shadow(c, sumtables[p], false);
     if (!d) return -1;
     cs.push_back(c);

@@ -769,7 +769,7 @@ extern "C" int pllb200_batch_begin(pll_partition_t ** partitions, unsigned int c
   {
     if (!partitions[i]) continue;
     PartCtx * c = ctx_of(partitions[i]);
-    if (c->magic != PLLB200_MAGIC || !batch_eligible(c) || c->xchg_nranks > 1) return 0;
+    if (c->magic != PLLB200_MAGIC || !batch_eligible(c)) return 0;
     if (!m.empty() && c->device != m[0]->device) return 0;
     m.push_back(c);
   }

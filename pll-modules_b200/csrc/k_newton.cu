@@ -97,7 +97,8 @@ __device__ __forceinline__ void st_release_gpu(unsigned long long * p, unsigned 
  * result in the local mailbox, where the other CTAs pick it up.  `pass` is the running pass number (same
  * on all ranks, alternating parity => a slot is rewritten only after everybody has read it).  Returns
  * false if a peer did not answer. */
-__device__ __forceinline__ bool newton_allgather(const NewtonArgs & a, unsigned long long pass, double & t1,
+template <class Args> /* NewtonArgs or NewtonMultiArgs: needs rank, nranks, inbox[] */
+__device__ __forceinline__ bool newton_allgather(const Args & a, unsigned long long pass, double & t1,
                                                  double & t2)
 {
   const unsigned int par = (unsigned int)(pass & 1ull);
@@ -813,6 +814,9 @@ struct NewtonMultiArgs
   double * result_host;
   unsigned long long * tag_host;
   unsigned long long tag;
+  /* site-sharded ranks: the lead partition's exchange buffers (see NewtonArgs) */
+  int rank, nranks;
+  double * inbox[NW_MAXRANKS];
 };
 
 template <bool DNA>
@@ -938,6 +942,8 @@ __global__ void __launch_bounds__(NW_THREADS, 3) newton_multi_kernel(NewtonMulti
 
   double xl = m.xmin, xh = m.xmax;
   const double xorig = m.x0;
+  const unsigned long long pass0 =
+      m.nranks > 1 ? __ldcg(reinterpret_cast<const unsigned long long *>(m.inbox[m.rank] + NW_XCHG_COUNTER)) : 0ull;
   double x = fmax(fmin(xorig, m.xmax), m.xmin);
   const double dxmax = m.xmax / m.max_iters;
   unsigned int iter = 0;
@@ -1028,6 +1034,7 @@ __global__ void __launch_bounds__(NW_THREADS, 3) newton_multi_kernel(NewtonMulti
       }
       if (lane == 0)
       {
+        if (m.nranks > 1 && !newton_allgather(m, pass0 + iter, t1, t2)) t1 = t2 = nan("");
         s_tot[0] = t1;
         s_tot[1] = t2;
       }
@@ -1064,6 +1071,9 @@ __global__ void __launch_bounds__(NW_THREADS, 3) newton_multi_kernel(NewtonMulti
 
   if (blockIdx.x == 0 && threadIdx.x == 0)
   {
+    if (m.nranks > 1)
+      *reinterpret_cast<unsigned long long *>(m.inbox[m.rank] + NW_XCHG_COUNTER) =
+          pass0 + iter - (status == NW_LIMIT ? 1u : 0u);
     m.result_dev[0] = x;
     m.result_dev[1] = status;
     m.result_dev[2] = (double)iter;
@@ -1266,6 +1276,9 @@ bool launch_newton_multi(PartCtx ** cs, unsigned int count, unsigned int * const
   m.result_dev = c0->d_result + slot * 4;
   m.result_host = c0->h_result_dev + slot * 4;
   dev_slot_tag(c0, slot, &m.tag_host, &m.tag);
+  m.rank = c0->xchg_rank;
+  m.nranks = c0->xchg_nranks > 1 ? c0->xchg_nranks : 1;
+  for (int r = 0; r < m.nranks && r < NW_MAXRANKS; ++r) m.inbox[r] = c0->xchg_peer[r];
 
   static int per_sm = 0;
   if (!per_sm)

@@ -570,7 +570,8 @@ static int optimise_branch_rec_multi(pll_newton_tree_params_multi_t * prm, int r
                                       (unsigned int)prm->max_newton_iters, s, &xguess[0], nullptr);
         if (fused >= 0 && prm->converged) prm->converged[0] = fused == 1;
       }
-      else if (xnum == 1 && !unlinked && prm->partition_count > 1 && !prm->parallel_reduce_cb)
+      else if (xnum == 1 && !unlinked && prm->partition_count > 1 &&
+               (!prm->parallel_reduce_cb || (prm->partitions[0] && pllb200_exchange_ranks(prm->partitions[0]) > 1)))
       {
         /* one shared length over several local partitions: all partitions' derivatives per iteration in
          * one cooperative launch (k_newton.cu, newton_multi_kernel) */
@@ -785,7 +786,8 @@ extern "C" double pllmod_opt_optimize_branch_lengths_local_multi(
       t_queued = can_queue ? &queue : nullptr;
       /* many small partitions with one shared length per branch: one launch per kernel kind and branch
        * instead of one per partition (device_ctx.cu, batch mode) */
-      if (keep_update && opt_method == PLLMOD_OPT_BLO_NEWTON_FAST && partition_count > 1 && !parallel_reduce_cb &&
+      if (keep_update && opt_method == PLLMOD_OPT_BLO_NEWTON_FAST && partition_count > 1 &&
+          (!parallel_reduce_cb || (partitions[0] && pllb200_exchange_ranks(partitions[0]) > 1)) &&
           prm.brlen_linkage != PLLMOD_COMMON_BRLEN_UNLINKED && g_opt_fused_newton != 0 &&
           pllb200_batch_begin(partitions, (unsigned int)partition_count) < 0)
         goto cleanup;
