@@ -75,6 +75,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_prefetch")) slot = &g_opt_trav_prefetch;
   else if (!strcmp(name, "aa_variant")) slot = &g_opt_aa_variant;
   else if (!strcmp(name, "small_stage")) slot = &g_opt_small_stage;
+  else if (!strcmp(name, "aa_tiptab")) slot = &g_opt_aa_tiptab;
   else if (!strcmp(name, "batch")) slot = &g_opt_batch;
   if (!slot) return -1;
   int old = *slot;
@@ -116,7 +117,7 @@ bool dev_ctx_init(PartCtx * c)
   c->tip_stride = round_up(c->sites_alloc, 256);
   c->eigen_stride = (size_t)2 * s * sp + 2 * sp;
 
-  c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr;
+  c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr; c->d_tiptab = nullptr; c->tiptab_stale = false;
   c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
   c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->d_sumfrag = nullptr;
   c->d_multi = nullptr; c->multi_cap = 0; c->ev_batch = nullptr;
@@ -170,6 +171,11 @@ bool dev_ctx_init(PartCtx * c)
       const size_t fbytes = (size_t)p->prob_matrices * K * 480 * sizeof(double);
       CUDA_TRY(cudaMalloc(&c->d_pmat_il, fbytes), false);
       CUDA_TRY(cudaMemsetAsync(c->d_pmat_il, 0, fbytes, c->stream), false);
+      if (pattern_tip && sp == 20 && !rate_scalers)
+      {
+        CUDA_TRY(cudaMalloc(&c->d_tiptab, fbytes), false);
+        CUDA_TRY(cudaMemsetAsync(c->d_tiptab, 0, fbytes, c->stream), false);
+      }
     }
   }
   if (pattern_tip && p->tips)
@@ -221,7 +227,7 @@ void dev_ctx_destroy(PartCtx * c)
   if (c->stream && c->stream != c->own_stream) cudaStreamSynchronize(c->stream);
   for (auto & kv : c->sumtables) cudaFree(kv.second);
   c->sumtables.clear();
-  cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il);
+  cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il); cudaFree(c->d_tiptab);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
   cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag);
   cudaFree(c->d_multi);
@@ -339,6 +345,7 @@ bool dev_sync_inputs(PartCtx * c)
     CUDA_TRY(cudaMemcpyAsync(c->d_tipmap, st, 256 * sizeof(unsigned long long),
                              cudaMemcpyDeviceToDevice, xstream(c)), false);
     c->tipmap_dirty = false;
+    if (c->d_tiptab) c->tiptab_stale = true; /* tables of already computed matrices lack the new codes */
   }
   if (c->weights_dirty)
   {

@@ -54,6 +54,11 @@ struct PartCtx
   unsigned int * d_scaler;
   double * d_pmat;
   double * d_pmat_il;         /* 4-state interleaved copy [i][k][j] for the DNA traversal kernel */
+  /* 20 states + tip patterns: per matrix the products P x (tip state vector) of every tip code,
+   * [prob_matrices][code 24][k][20] — the same K*480 doubles per matrix as the fragment image, so a tip
+   * child's slot in the traversal kernel's shared memory holds this table instead (k_traversal_aa.cu) */
+  double * d_tiptab;
+  bool tiptab_stale;          /* tip map changed after tables were built: rebuild before the next use */
   unsigned char * d_tipchars;
   unsigned int * d_weights;
   int * d_invariant;
@@ -145,6 +150,7 @@ extern int g_opt_trav_prefetch;
 extern int g_opt_fused_newton;
 extern int g_opt_queued_newton;
 extern int g_opt_aa_variant;
+extern int g_opt_aa_tiptab;
 
 /* ---- batch mode (device_ctx.cu) ------------------------------------------------------------------
  * Many small partitions sharing one tree: between batch_begin and batch_end the per-partition launchers

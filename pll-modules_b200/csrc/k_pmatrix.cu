@@ -24,7 +24,28 @@ struct PmatArgs
    * `branch_lengths` is null */
   unsigned int one_index;
   double one_length;
+  /* 20 states with tip patterns: also emit, per tip code c < 24, sum_{j in mask(c)} P[i][j] (internal.h) */
+  double * tiptab;
+  const unsigned long long * tipmap;
 };
+
+#define PM_TIP_CODES 24
+
+/* rows of the tip table of matrix (m, k) from the finished matrix `out` (written by this CTA) */
+__device__ __forceinline__ void pmatrix_tip_rows(const double * out, double * tiptab, const unsigned long long * tipmap,
+                                                 unsigned int m, unsigned int k, unsigned int K, unsigned int sp)
+{
+  double * tab = tiptab + (size_t)m * K * (PM_TIP_CODES * 20);
+  for (unsigned int idx = threadIdx.x; idx < PM_TIP_CODES * 20; idx += blockDim.x)
+  {
+    const unsigned int code = idx / 20, i = idx % 20;
+    const unsigned long long mask = tipmap[code];
+    double v = 0.0;
+    for (unsigned int j = 0; j < 20; ++j)
+      if ((mask >> j) & 1ull) v += out[i * sp + j];
+    tab[(code * K + k) * 20 + i] = v;
+  }
+}
 
 __device__ __forceinline__ void pmatrix_body(double * __restrict__ pmat, double * __restrict__ pmat_il,
                                              const double * __restrict__ eigen, size_t eigen_stride,
@@ -76,6 +97,11 @@ __device__ __forceinline__ void pmatrix_body(double * __restrict__ pmat, double 
       pmat_il[(((size_t)m * K + k) * 3 + nt) * 160 + ks * 32 + lane] = v;
     }
   }
+  if (a.tiptab && states == 20)
+  {
+    __syncthreads(); /* `out` complete and visible to the whole CTA */
+    pmatrix_tip_rows(out, a.tiptab, a.tipmap, m, k, K, sp);
+  }
 }
 
 __global__ void pmatrix_kernel(double * __restrict__ pmat, double * __restrict__ pmat_il,
@@ -118,6 +144,9 @@ __global__ void pmatrix_batch_kernel(const PmatBatchPart * __restrict__ parts)
   pmatrix_body(sp_.pmat, sp_.pmat_il, sp_.eigen, sp_.eigen_stride, m, t, k, sp_.states, sp_.sp, sp_.K, sp_.a);
 }
 
+/* tip tables are used when the partition has them and every tip code fits */
+static bool tiptab_usable(const PartCtx * c) { return c->d_tiptab && c->d_tipmap && c->pub.maxstates <= PM_TIP_CODES; }
+
 /* one matrix whose branch length is already on the device (written by the queued Newton kernel) */
 bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,
                            const double * d_length)
@@ -137,6 +166,14 @@ bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, uns
     a.rates[k] = p->rates[k];
     a.pinv[k] = p->prop_invar[params_indices[k]];
   }
+  a.tiptab = nullptr;
+  a.tipmap = nullptr;
+  if (tiptab_usable(c))
+  {
+    if (!dev_sync_inputs(c)) return false;
+    a.tiptab = c->d_tiptab;
+    a.tipmap = c->d_tipmap;
+  }
   a.one_index = matrix_index;
   a.one_length = 0.0;
   const unsigned int * d_idx = nullptr;
@@ -152,7 +189,8 @@ bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, uns
 /* rebuild the interleaved copies from the plain array (after P-matrices were uploaded from a
  * checkpoint, binary_io.cpp): same index maps as pmatrix_kernel */
 __global__ void pmatrix_reinterleave_kernel(const double * __restrict__ pmat, double * __restrict__ pmat_il,
-                                            unsigned int states, unsigned int sp, unsigned int K)
+                                            unsigned int states, unsigned int sp, unsigned int K,
+                                            double * tiptab, const unsigned long long * tipmap)
 {
   const unsigned int m = blockIdx.x / K, k = blockIdx.x % K;
   const double * in = pmat + ((size_t)m * K + k) * states * sp;
@@ -168,14 +206,18 @@ __global__ void pmatrix_reinterleave_kernel(const double * __restrict__ pmat, do
       pmat_il[(((size_t)m * K + k) * 3 + nt) * 160 + ks * 32 + lane] = v;
     }
   }
+  if (tiptab && states == 20) pmatrix_tip_rows(in, tiptab, tipmap, m, k, K, sp);
 }
 
 bool launch_pmatrix_reinterleave(PartCtx * c)
 {
   pll_partition_t * p = &c->pub;
   if (!c->d_pmat_il || !p->prob_matrices || (p->states != 4 && p->states != 20)) return true;
-  pmatrix_reinterleave_kernel<<<p->prob_matrices * p->rate_cats, 128, 0, c->stream>>>(
-      c->d_pmat, c->d_pmat_il, p->states, p->states_padded, p->rate_cats);
+  if (tiptab_usable(c) && !dev_sync_inputs(c)) return false; /* the tip map must be on the device */
+  c->tiptab_stale = false;
+  pmatrix_reinterleave_kernel<<<p->prob_matrices * p->rate_cats, 128, 0, xstream(c)>>>(
+      c->d_pmat, c->d_pmat_il, p->states, p->states_padded, p->rate_cats, tiptab_usable(c) ? c->d_tiptab : nullptr,
+      c->d_tipmap);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "pmatrix_reinterleave_kernel launch");
 }
@@ -197,6 +239,14 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
     a.params_idx[k] = params_indices[k];
     a.rates[k] = p->rates[k];
     a.pinv[k] = p->prop_invar[params_indices[k]];
+  }
+  a.tiptab = nullptr;
+  a.tipmap = nullptr;
+  if (tiptab_usable(c))
+  {
+    if (!dev_sync_inputs(c)) return false;
+    a.tiptab = c->d_tiptab;
+    a.tipmap = c->d_tipmap;
   }
   for (unsigned int i = 0; i < count; ++i)
   {

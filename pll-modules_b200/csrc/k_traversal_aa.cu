@@ -25,6 +25,7 @@
 #include "devutil.cuh"
 
 #include <algorithm>
+#include <type_traits>
 #include <vector>
 
 struct __align__(16) AaOp
@@ -48,6 +49,7 @@ struct AaArgs
   double * pbase; /* where parents are written: the CLV arena, or a sumtable buffer (launch_sumtable_aa) */
   unsigned int * scaler;
   const double * frag;
+  const double * tiptab; /* per matrix [code 24][k][20] = P x tip vector (k_pmatrix.cu), or null */
   const unsigned char * tipchars;
   const unsigned long long * tipmap;
 };
@@ -143,14 +145,18 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
         {
           double * dstm = s_mat + (size_t)o * 2 * mat_doubles;
           aa_mbar_expect(&s_bar[o], 2 * mat_bytes);
-          aa_tma(dstm, a.frag + s_ops[o].m1_off, mat_bytes, &s_bar[o]);
-          aa_tma(dstm + mat_doubles, a.frag + s_ops[o].m2_off, mat_bytes, &s_bar[o]);
+          aa_tma(dstm, ((s_ops[o].flags & AOPF_TIP1) && a.tiptab ? a.tiptab : a.frag) + s_ops[o].m1_off, mat_bytes, &s_bar[o]);
+          aa_tma(dstm + mat_doubles, ((s_ops[o].flags & AOPF_TIP2) && a.tiptab ? a.tiptab : a.frag) + s_ops[o].m2_off,
+                 mat_bytes, &s_bar[o]);
         }
       for (unsigned int o = 0; o < nseg; ++o)
       {
         const AaOp & d = s_ops[o];
         const unsigned int flags = d.flags;
         const bool tip1 = flags & AOPF_TIP1, tip2 = flags & AOPF_TIP2;
+        /* a tip child with a table: its slot holds T[code][k][20] = P x (tip vector of the code); the D
+         * fragment of that child is two table entries per n-tile instead of 5 k-steps of DMMA */
+        const bool look1 = tip1 && a.tiptab, look2 = tip2 && a.tiptab;
         const unsigned int st = o & 1u;
         /* A warp only ever touches its own sites, so the warps of a CTA are not kept in step: the CLV this
          * warp wrote in op o-1 only has to be visible to its own lanes */
@@ -166,89 +172,129 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
 
         /* A fragments (child values of 8 sites x 4 child states per k-step) are the only operands that
          * come from global memory; the ones of step (k, t) + 1 are requested before the 30 DMMAs of step
-         * (k, t) run (ncu: the first DMMA of every tile was waiting on them, 34 % of all stall samples) */
-        auto load_a = [&](unsigned int k, int t, double (&aL)[5], double (&aR)[5]) {
-          const unsigned long long site = wsite0 + 8 * t + row;
-          const bool act = site < a.sites;
-          if (tip1)
-          {
-            const unsigned long long m = act ? s_tipmap[a.tipchars[d.c1_off + site]] : 0ull;
-#pragma unroll
-            for (int ks = 0; ks < 5; ++ks) aL[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
-          }
-          else
-          {
-            const double * p = a.clv + d.c1_off + site * span + k * 20 + col;
-#pragma unroll
-            for (int ks = 0; ks < 5; ++ks) aL[ks] = act ? p[ks * 4] : 0.0;
-          }
-          if (tip2)
-          {
-            const unsigned long long m = act ? s_tipmap[a.tipchars[d.c2_off + site]] : 0ull;
-#pragma unroll
-            for (int ks = 0; ks < 5; ++ks) aR[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
-          }
-          else
-          {
-            const double * p = a.clv + d.c2_off + site * span + k * 20 + col;
-#pragma unroll
-            for (int ks = 0; ks < 5; ++ks) aR[ks] = act ? p[ks * 4] : 0.0;
-          }
-        };
-        double aL[5], aR[5];
-        load_a(0, 0, aL, aR);
-        for (unsigned int k = 0; k < K; ++k)
-        {
-          double bL[15], bR[15];
-#pragma unroll
-          for (int f = 0; f < 15; ++f)
-          {
-            bL[f] = sL[(k * 15 + f) * 32 + lane];
-            bR[f] = sR[(k * 15 + f) * 32 + lane];
-          }
-#pragma unroll
-          for (int t = 0; t < AA_T; ++t)
-          {
+         * (k, t) run (ncu: the first DMMA of every tile was waiting on them, 34 % of all stall samples).
+         * The op body is instantiated per (LOOK1, LOOK2): a tip-tip op has no DMMA at all, a tip-inner op
+         * one accumulator family, and neither pays registers for the other's operands. */
+        auto run = [&](auto look1_tag, auto look2_tag) {
+          constexpr bool LOOK1 = decltype(look1_tag)::value, LOOK2 = decltype(look2_tag)::value;
+          auto load_a = [&](unsigned int k, int t, double (&aL)[5], double (&aR)[5]) {
             const unsigned long long site = wsite0 + 8 * t + row;
             const bool act = site < a.sites;
-            double nL[5], nR[5];
-            if (t + 1 < AA_T)
-              load_a(k, t + 1, nL, nR);
-            else if (k + 1 < K)
-              load_a(k + 1, 0, nL, nR);
-            /* k-step outermost: six independent accumulator chains are interleaved, so a DMMA never waits
-             * on the one issued just before it */
-            double xl[3][2], xr[3][2];
+            if (LOOK1)
+              aL[0] = __hiloint2double(0, act ? (int)a.tipchars[d.c1_off + site] : 0); /* the code rides in the fragment */
+            else if (tip1)
+            {
+              const unsigned long long m = act ? s_tipmap[a.tipchars[d.c1_off + site]] : 0ull;
 #pragma unroll
-            for (int nt = 0; nt < 3; ++nt) xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
+              for (int ks = 0; ks < 5; ++ks) aL[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+            }
+            else
+            {
+              const double * p = a.clv + d.c1_off + site * span + k * 20 + col;
 #pragma unroll
-            for (int ks = 0; ks < 5; ++ks)
+              for (int ks = 0; ks < 5; ++ks) aL[ks] = act ? p[ks * 4] : 0.0;
+            }
+            if (LOOK2)
+              aR[0] = __hiloint2double(0, act ? (int)a.tipchars[d.c2_off + site] : 0);
+            else if (tip2)
+            {
+              const unsigned long long m = act ? s_tipmap[a.tipchars[d.c2_off + site]] : 0ull;
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks) aR[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+            }
+            else
+            {
+              const double * p = a.clv + d.c2_off + site * span + k * 20 + col;
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks) aR[ks] = act ? p[ks * 4] : 0.0;
+            }
+          };
+          constexpr int NA1 = LOOK1 ? 1 : 5, NA2 = LOOK2 ? 1 : 5; /* live operand registers per child */
+          double aL[5], aR[5];
+          load_a(0, 0, aL, aR);
+          for (unsigned int k = 0; k < K; ++k)
+          {
+            double bL[LOOK1 ? 1 : 15], bR[LOOK2 ? 1 : 15];
+            if (!LOOK1)
+#pragma unroll
+              for (int f = 0; f < 15; ++f) bL[LOOK1 ? 0 : f] = sL[(k * 15 + f) * 32 + lane];
+            if (!LOOK2)
+#pragma unroll
+              for (int f = 0; f < 15; ++f) bR[LOOK2 ? 0 : f] = sR[(k * 15 + f) * 32 + lane];
+#pragma unroll
+            for (int t = 0; t < AA_T; ++t)
+            {
+              const unsigned long long site = wsite0 + 8 * t + row;
+              const bool act = site < a.sites;
+              double nL[5], nR[5];
+              if (t + 1 < AA_T)
+                load_a(k, t + 1, nL, nR);
+              else if (k + 1 < K)
+                load_a(k + 1, 0, nL, nR);
+              double xl[3][2], xr[3][2];
+#pragma unroll
+              for (int nt = 0; nt < 3; ++nt) xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
+              if (LOOK1)
+              {
+                const double * row_l = sL + ((unsigned int)__double2loint(aL[0]) * K + k) * 20 + 2 * col;
+#pragma unroll
+                for (int nt = 0; nt < 3; ++nt)
+                  if (nt < 2 || col < 2)
+                  {
+                    const double2 v = *reinterpret_cast<const double2 *>(row_l + nt * 8);
+                    xl[nt][0] = v.x;
+                    xl[nt][1] = v.y;
+                  }
+              }
+              if (LOOK2)
+              {
+                const double * row_r = sR + ((unsigned int)__double2loint(aR[0]) * K + k) * 20 + 2 * col;
+#pragma unroll
+                for (int nt = 0; nt < 3; ++nt)
+                  if (nt < 2 || col < 2)
+                  {
+                    const double2 v = *reinterpret_cast<const double2 *>(row_r + nt * 8);
+                    xr[nt][0] = v.x;
+                    xr[nt][1] = v.y;
+                  }
+              }
+              /* k-step outermost: the independent accumulator chains are interleaved, so a DMMA never
+               * waits on the one issued just before it */
+#pragma unroll
+              for (int ks = 0; ks < 5; ++ks)
+#pragma unroll
+                for (int nt = 0; nt < 3; ++nt)
+                {
+                  if (!LOOK1) dmma(xl[nt][0], xl[nt][1], aL[ks], bL[LOOK1 ? 0 : nt * 5 + ks]);
+                  if (!LOOK2) dmma(xr[nt][0], xr[nt][1], aR[ks], bR[LOOK2 ? 0 : nt * 5 + ks]);
+                }
+              /* D fragment: this lane holds parent[site][k][nt*8 + 2*col, +1] */
+              double * pd = a.pbase + d.p_off + site * span + k * 20 + 2 * col;
 #pragma unroll
               for (int nt = 0; nt < 3; ++nt)
               {
-                dmma(xl[nt][0], xl[nt][1], aL[ks], bL[nt * 5 + ks]);
-                dmma(xr[nt][0], xr[nt][1], aR[ks], bR[nt * 5 + ks]);
+                const double o0 = xl[nt][0] * xr[nt][0], o1 = xl[nt][1] * xr[nt][1];
+                if (nt < 2 || col < 2)
+                {
+                  if (check) smax[t] = max(smax[t], max((unsigned int)__double2hiint(o0), (unsigned int)__double2hiint(o1)));
+                  if (act) *reinterpret_cast<double2 *>(pd + nt * 8) = make_double2(o0, o1);
+                }
               }
-            /* D fragment: this lane holds parent[site][k][nt*8 + 2*col, +1] */
-            double * pd = a.pbase + d.p_off + site * span + k * 20 + 2 * col;
 #pragma unroll
-            for (int nt = 0; nt < 3; ++nt)
-            {
-              const double o0 = xl[nt][0] * xr[nt][0], o1 = xl[nt][1] * xr[nt][1];
-              if (nt < 2 || col < 2)
-              {
-                if (check) smax[t] = max(smax[t], max((unsigned int)__double2hiint(o0), (unsigned int)__double2hiint(o1)));
-                if (act) *reinterpret_cast<double2 *>(pd + nt * 8) = make_double2(o0, o1);
-              }
-            }
+              for (int ks = 0; ks < NA1; ++ks) aL[ks] = nL[ks];
 #pragma unroll
-            for (int ks = 0; ks < 5; ++ks)
-            {
-              aL[ks] = nL[ks];
-              aR[ks] = nR[ks];
+              for (int ks = 0; ks < NA2; ++ks) aR[ks] = nR[ks];
             }
           }
-        }
+        };
+        if (look1 && look2)
+          run(std::true_type{}, std::true_type{});
+        else if (look1)
+          run(std::true_type{}, std::false_type{});
+        else if (look2)
+          run(std::false_type{}, std::true_type{});
+        else
+          run(std::false_type{}, std::false_type{});
 
         /* ---- scalers + (rare) rescale pass ---- */
         if (flags & AOPF_PS)
@@ -299,8 +345,11 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
             {
               double * dstm = s_mat + (size_t)st * 2 * mat_doubles;
               aa_mbar_expect(&s_bar[st], 2 * mat_bytes);
-              aa_tma(dstm, a.frag + s_ops[o + 2].m1_off, mat_bytes, &s_bar[st]);
-              aa_tma(dstm + mat_doubles, a.frag + s_ops[o + 2].m2_off, mat_bytes, &s_bar[st]);
+              aa_tma(dstm, ((s_ops[o + 2].flags & AOPF_TIP1) && a.tiptab ? a.tiptab : a.frag) + s_ops[o + 2].m1_off,
+                     mat_bytes, &s_bar[st]);
+              aa_tma(dstm + mat_doubles,
+                     ((s_ops[o + 2].flags & AOPF_TIP2) && a.tiptab ? a.tiptab : a.frag) + s_ops[o + 2].m2_off, mat_bytes,
+                     &s_bar[st]);
             }
           }
         }
@@ -329,6 +378,7 @@ __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_batch_kernel(cons
 /* ---- host ------------------------------------------------------------------------------------ */
 
 int g_opt_aa_variant = 0;
+int g_opt_aa_tiptab = 1; /* tip children by table lookup instead of DMMA */
 
 template <int T, int W, int MINB>
 static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
@@ -421,6 +471,12 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
   a.pbase = c->d_clv;
   a.scaler = c->d_scaler;
   a.frag = c->d_pmat_il;
+  a.tiptab = nullptr;
+  if (g_opt_aa_tiptab && c->d_tiptab && c->d_tipmap && p->maxstates <= 24)
+  {
+    if (c->tiptab_stale && !launch_pmatrix_reinterleave(c)) return false; /* tip map changed since the tables were built */
+    a.tiptab = c->d_tiptab;
+  }
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
   switch (g_opt_aa_variant)
@@ -531,6 +587,7 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
   a.pbase = d_sumtable;
   a.scaler = c->d_scaler;
   a.frag = c->d_sumfrag;
+  a.tiptab = nullptr; /* the "matrices" here are eigenvector images, not P-matrices */
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
   return launch_aa_variant<2, 4, 3>(c, a);

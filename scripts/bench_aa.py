@@ -6,6 +6,8 @@ from pllharness import Harness, load_product_package
 tips = int(sys.argv[1]) if len(sys.argv) > 1 else 500
 sites = int(sys.argv[2]) if len(sys.argv) > 2 else 200000
 pkg = load_product_package()
+if os.environ.get("PLLB200_AA_TIPTAB"):
+    pkg.set_option("aa_tiptab", int(os.environ["PLLB200_AA_TIPTAB"]))
 if os.environ.get("PLLB200_AA_VARIANT"):
     pkg.set_option("aa_variant", int(os.environ["PLLB200_AA_VARIANT"]))
 h = Harness("b200", tips=tips, sites=sites, states=20)

@@ -21,7 +21,7 @@ which = [a for a in args if not a.startswith("--")] or ["c1", "c3", "c4", "c5"]
 def opt(name, default):
     return int(args[args.index(name) + 1]) if name in args else default
 pkg = load_product_package()
-for _o in ("fused_newton", "queued_newton", "small_stage", "batch", "aa_variant"):
+for _o in ("fused_newton", "queued_newton", "small_stage", "batch", "aa_variant", "aa_tiptab"):
     if os.environ.get("PLLB200_" + _o.upper()):
         pkg.set_option(_o, int(os.environ["PLLB200_" + _o.upper()]))
 
