@@ -256,6 +256,29 @@ def test_shared_branch_length_newton_over_many_partitions(linkage):
         pkg.set_option("batch", 1)
 
 
+def test_protein_tip_tables_equal_the_dmma_path():
+    """20 states: tip children by table lookup (default) and through the tensor pipe give the same CLVs, on a
+    shallow and on a deep tree (scaling), after a branch-length change (tables rebuilt with the P-matrices)."""
+    pkg = load_product_package()
+    for kw in (dict(tips=30, sites=777, states=20), dict(tips=60, sites=250, states=20, brlen_scale=14.0)):
+        vals = {}
+        for mode in (1, 0):
+            pkg.set_option("aa_tiptab", mode)
+            try:
+                with Harness("b200", **kw) as h:
+                    a = h.loglh(0)
+                    brl = h.branch_lengths()
+                    h.set_branch_lengths(brl * 1.3)
+                    b = h.loglh(0)
+                    vals[mode] = (a, b, h.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=1,
+                                                                  lh_epsilon=0.1))
+            finally:
+                pkg.set_option("aa_tiptab", 1)
+        for x, y in zip(vals[0], vals[1]):
+            assert rel(x, y) < 1e-12, (kw, vals)
+        assert vals[1][0] != vals[1][1]
+
+
 @needs_ref
 def test_persite_root_and_alpha_change():
     kw = dict(tips=16, sites=900)
