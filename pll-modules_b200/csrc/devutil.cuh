@@ -67,6 +67,28 @@ __device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gm
                : "memory");
 }
 
+/* ---- 20-state DMMA operand order (k_traversal_aa.cu, k_pmatrix.cu) -------------------------------
+ * The contraction index j of X[site][i] = sum_j C[site][j] P[i][j] may be fed to the five m8n8k4
+ * k-steps in any order as long as the A fragment (child CLV) and the B fragment (P^T image) agree.
+ * The order is chosen so that lane column c of k-step ks holds the state the SAME lane holds in the
+ * D fragment of the previous update: D of n-tile nt = states nt*8 + 2c, 2c+1, hence
+ *   (ks, c) <-> state (ks>>1)*8 + 2c + (ks&1)   for ks < 4,      (4, c) <-> state 16 + c.
+ * A parent written by one operation is then the A operand of the next one without leaving the
+ * registers (one shuffle for k-step 4), and a CLV read from memory is two 16-byte loads and one
+ * 8-byte load per category instead of five 8-byte loads. */
+__host__ __device__ __forceinline__ unsigned int aa_state_of_slot(unsigned int ks, unsigned int c)
+{
+  return ks < 4 ? (ks >> 1) * 8 + 2 * c + (ks & 1u) : 16 + c;
+}
+__host__ __device__ __forceinline__ unsigned int aa_kstep_of_state(unsigned int j)
+{
+  return j < 16 ? (j >> 3) * 2 + (j & 1u) : 4;
+}
+__host__ __device__ __forceinline__ unsigned int aa_col_of_state(unsigned int j)
+{
+  return j < 16 ? (j & 7u) >> 1 : j - 16;
+}
+
 #define SCALE_FACTOR_D 115792089237316195423570985008687907853269984665640564039457584007913129639936.0
 #define SCALE_THRESHOLD_D (1.0 / SCALE_FACTOR_D)
 #define LN_SCALE_THRESHOLD (-177.445678223345993274) /* ln(2^-256) */

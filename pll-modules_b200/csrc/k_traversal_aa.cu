@@ -25,6 +25,7 @@
 #include "devutil.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <type_traits>
 #include <vector>
 
@@ -92,6 +93,24 @@ __device__ __forceinline__ void dmma(double & c0, double & c1, double a, double 
   asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
                : "+d"(c0), "+d"(c1)
                : "d"(a), "d"(b));
+}
+
+/* A fragment of one (site, category) from memory in the slot order of devutil.cuh: states 2c, 2c+1 (k-steps 0, 1),
+ * 8+2c, 8+2c+1 (k-steps 2, 3) and 16+c (k-step 4) */
+__device__ __forceinline__ void aa_load_slots(const double * p, int col, bool act, double (&A)[5])
+{
+  if (act)
+  {
+    const double2 v0 = *reinterpret_cast<const double2 *>(p + 2 * col);
+    const double2 v1 = *reinterpret_cast<const double2 *>(p + 8 + 2 * col);
+    A[0] = v0.x;
+    A[1] = v0.y;
+    A[2] = v1.x;
+    A[3] = v1.y;
+    A[4] = p[16 + col];
+  }
+  else
+    A[0] = A[1] = A[2] = A[3] = A[4] = 0.0;
 }
 
 /* dynamic shared memory: AaOp ops[AA_SEG] | u64 tipmap[256] | u64 bar[2] | u32 cnt[2] | double mat[2 stages][2][K*480] */
@@ -186,13 +205,11 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
             {
               const unsigned long long m = act ? s_tipmap[a.tipchars[d.c1_off + site]] : 0ull;
 #pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aL[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+              for (int ks = 0; ks < 5; ++ks) aL[ks] = (double)((m >> aa_state_of_slot(ks, col)) & 1ull);
             }
             else
             {
-              const double * p = a.clv + d.c1_off + site * span + k * 20 + col;
-#pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aL[ks] = act ? p[ks * 4] : 0.0;
+              aa_load_slots(a.clv + d.c1_off + site * span + k * 20, col, act, aL);
             }
             if (LOOK2)
               aR[0] = __hiloint2double(0, act ? (int)a.tipchars[d.c2_off + site] : 0);
@@ -200,13 +217,11 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
             {
               const unsigned long long m = act ? s_tipmap[a.tipchars[d.c2_off + site]] : 0ull;
 #pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aR[ks] = (double)((m >> (ks * 4 + col)) & 1ull);
+              for (int ks = 0; ks < 5; ++ks) aR[ks] = (double)((m >> aa_state_of_slot(ks, col)) & 1ull);
             }
             else
             {
-              const double * p = a.clv + d.c2_off + site * span + k * 20 + col;
-#pragma unroll
-              for (int ks = 0; ks < 5; ++ks) aR[ks] = act ? p[ks * 4] : 0.0;
+              aa_load_slots(a.clv + d.c2_off + site * span + k * 20, col, act, aR);
             }
           };
           constexpr int NA1 = LOOK1 ? 1 : 5, NA2 = LOOK2 ? 1 : 5; /* live operand registers per child */
@@ -375,9 +390,309 @@ __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_batch_kernel(cons
   trav_aa_body<AA_T, AA_WARPS, MINB>(sa);
 }
 
+/* ---- Gamma4 kernel with register forwarding ------------------------------------------------------
+ * In a post-order operation list the parent written by operation o-1 is a child of operation o whenever
+ * o has an inner child at all that was not finished earlier: always for a tip-inner operation, and for
+ * one of the two children of an inner-inner operation.  With the slot order of devutil.cuh the D
+ * fragments a lane holds after o-1 ARE its A fragments for o (k-steps 0-3; one shuffle for k-step 4), so
+ * that child is never read back: of 2 x 129 + 238 child CLVs of the C3 tree only 129 come from memory.
+ * The host puts the children of every operation in the order (lookup | load, lookup | load | forward)
+ * — the product of the two child terms commutes bit for bit — so five op bodies cover all cases.
+ * Rate categories are a template constant (4): the forwarded fragments live in registers
+ * fw[k][tile][slot], which needs every index to be known at compile time. */
+#define AOPF_FWD2 32u
+enum { AK_LOOK = 0, AK_LOAD = 2, AK_FWD = 3 };
+
+template <int C1, int C2, int AA_T>
+__device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const double * __restrict__ sL,
+                                       const double * __restrict__ sR, unsigned long long wsite0, int lane, bool check,
+                                       double (&fw)[4][AA_T][5], unsigned int (&smax)[AA_T])
+{
+  constexpr int K = 4;
+  constexpr unsigned long long span = K * 20;
+  const int row = lane >> 2, col = lane & 3;
+  const int src4 = (lane & ~3) | (col >> 1); /* lane that holds state 16 + col of this row in its D fragment */
+  bool act[AA_T];
+  unsigned int code1[AA_T], code2[AA_T];
+  const double * c1p[AA_T];
+  const double * c2p[AA_T];
+  double * pp[AA_T];
+#pragma unroll
+  for (int t = 0; t < AA_T; ++t)
+  {
+    const unsigned long long site = wsite0 + 8 * t + row;
+    act[t] = site < a.sites;
+    if (C1 == AK_LOOK) code1[t] = act[t] ? a.tipchars[d.c1_off + site] : 0u;
+    if (C2 == AK_LOOK) code2[t] = act[t] ? a.tipchars[d.c2_off + site] : 0u;
+    if (C1 == AK_LOAD) c1p[t] = a.clv + d.c1_off + site * span;
+    if (C2 == AK_LOAD) c2p[t] = a.clv + d.c2_off + site * span;
+    pp[t] = a.pbase + d.p_off + site * span + 2 * col;
+  }
+  double aL[5], aR[5];
+  if (C1 == AK_LOAD) aa_load_slots(c1p[0], col, act[0], aL);
+  if (C2 == AK_LOAD) aa_load_slots(c2p[0], col, act[0], aR);
+#pragma unroll
+  for (int k = 0; k < K; ++k)
+  {
+    double bL[C1 == AK_LOOK ? 1 : 15], bR[C2 == AK_LOOK ? 1 : 15];
+    if (C1 != AK_LOOK)
+#pragma unroll
+      for (int f = 0; f < 15; ++f) bL[C1 == AK_LOOK ? 0 : f] = sL[(k * 15 + f) * 32 + lane];
+    if (C2 != AK_LOOK)
+#pragma unroll
+      for (int f = 0; f < 15; ++f) bR[C2 == AK_LOOK ? 0 : f] = sR[(k * 15 + f) * 32 + lane];
+#pragma unroll
+    for (int t = 0; t < AA_T; ++t)
+    {
+      /* operands of the next (k, tile) step are requested before the DMMAs of this one run */
+      double nL[5], nR[5];
+      const int nk = (t + 1 < AA_T) ? k : k + 1, ntile = (t + 1 < AA_T) ? t + 1 : 0;
+      if (nk < K)
+      {
+        if (C1 == AK_LOAD) aa_load_slots(c1p[ntile] + nk * 20, col, act[ntile], nL);
+        if (C2 == AK_LOAD) aa_load_slots(c2p[ntile] + nk * 20, col, act[ntile], nR);
+      }
+      if (C2 == AK_FWD)
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks) aR[ks] = fw[k][t][ks];
+      double xl[3][2], xr[3][2];
+#pragma unroll
+      for (int nt = 0; nt < 3; ++nt) xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
+      if (C1 == AK_LOOK)
+      {
+        const double * row_l = sL + (code1[t] * K + k) * 20 + 2 * col;
+#pragma unroll
+        for (int nt = 0; nt < 3; ++nt)
+          if (nt < 2 || col < 2)
+          {
+            const double2 v = *reinterpret_cast<const double2 *>(row_l + nt * 8);
+            xl[nt][0] = v.x;
+            xl[nt][1] = v.y;
+          }
+      }
+      if (C2 == AK_LOOK)
+      {
+        const double * row_r = sR + (code2[t] * K + k) * 20 + 2 * col;
+#pragma unroll
+        for (int nt = 0; nt < 3; ++nt)
+          if (nt < 2 || col < 2)
+          {
+            const double2 v = *reinterpret_cast<const double2 *>(row_r + nt * 8);
+            xr[nt][0] = v.x;
+            xr[nt][1] = v.y;
+          }
+      }
+#pragma unroll
+      for (int ks = 0; ks < 5; ++ks)
+#pragma unroll
+        for (int nt = 0; nt < 3; ++nt)
+        {
+          if (C1 != AK_LOOK) dmma(xl[nt][0], xl[nt][1], aL[ks], bL[C1 == AK_LOOK ? 0 : nt * 5 + ks]);
+          if (C2 != AK_LOOK) dmma(xr[nt][0], xr[nt][1], aR[ks], bR[C2 == AK_LOOK ? 0 : nt * 5 + ks]);
+        }
+      /* D fragment: this lane holds parent[site][k][nt*8 + 2*col, +1] */
+      double o[3][2];
+#pragma unroll
+      for (int nt = 0; nt < 3; ++nt)
+      {
+        o[nt][0] = xl[nt][0] * xr[nt][0];
+        o[nt][1] = xl[nt][1] * xr[nt][1];
+        if (nt < 2 || col < 2)
+        {
+          if (check)
+            smax[t] = max(smax[t], max((unsigned int)__double2hiint(o[nt][0]), (unsigned int)__double2hiint(o[nt][1])));
+          if (act[t]) *reinterpret_cast<double2 *>(pp[t] + k * 20 + nt * 8) = make_double2(o[nt][0], o[nt][1]);
+        }
+      }
+      /* ... and, re-read as an A fragment, the operand of the next operation */
+      fw[k][t][0] = o[0][0];
+      fw[k][t][1] = o[0][1];
+      fw[k][t][2] = o[1][0];
+      fw[k][t][3] = o[1][1];
+      {
+        const double v0 = __shfl_sync(0xffffffffu, o[2][0], src4), v1 = __shfl_sync(0xffffffffu, o[2][1], src4);
+        fw[k][t][4] = (col & 1) ? v1 : v0;
+      }
+      if (nk < K)
+      {
+        if (C1 == AK_LOAD)
+#pragma unroll
+          for (int ks = 0; ks < 5; ++ks) aL[ks] = nL[ks];
+        if (C2 == AK_LOAD)
+#pragma unroll
+          for (int ks = 0; ks < 5; ++ks) aR[ks] = nR[ks];
+      }
+    }
+  }
+}
+
+/* dynamic shared memory as in trav_aa_body with K = 4 */
+template <int AA_T, int AA_WARPS, int MINB>
+__device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
+{
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  AaOp * s_ops = reinterpret_cast<AaOp *>(smem_raw);
+  unsigned long long * s_bar = reinterpret_cast<unsigned long long *>(smem_raw + sizeof(AaOp) * AA_SEG) + 256;
+  unsigned int * s_cnt = reinterpret_cast<unsigned int *>(s_bar + 2);
+  double * s_mat = reinterpret_cast<double *>(s_bar + 4);
+
+  constexpr unsigned int K = 4;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = lane >> 2, col = lane & 3;
+  constexpr unsigned int mat_doubles = K * AA_FRAG;
+  constexpr unsigned int mat_bytes = mat_doubles * sizeof(double);
+  constexpr unsigned long long span = K * 20;
+  const unsigned long long sites_per_cta = (unsigned long long)AA_WARPS * 8 * AA_T;
+  const unsigned long long nchunks = (a.sites + sites_per_cta - 1) / sites_per_cta;
+  if (blockIdx.x >= nchunks) return;
+
+  if (threadIdx.x == 0)
+  {
+    aa_mbar_init(&s_bar[0], 1);
+    aa_mbar_init(&s_bar[1], 1);
+    s_cnt[0] = s_cnt[1] = 0;
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  unsigned int ph = 0;
+  double fw[4][AA_T][5];
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+#pragma unroll
+    for (int t = 0; t < AA_T; ++t)
+#pragma unroll
+      for (int ks = 0; ks < 5; ++ks) fw[k][t][ks] = 0.0;
+
+  for (unsigned int seg = 0; seg < a.nops; seg += AA_SEG)
+  {
+    const unsigned int nseg = min(a.nops - seg, (unsigned int)AA_SEG);
+    __syncthreads();
+    {
+      const uint4 * src = reinterpret_cast<const uint4 *>(a.ops + seg);
+      uint4 * dst = reinterpret_cast<uint4 *>(s_ops);
+      for (unsigned int i = threadIdx.x; i < nseg * 4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+
+    for (unsigned long long chunk = blockIdx.x; chunk < nchunks; chunk += gridDim.x)
+    {
+      const unsigned long long wsite0 = chunk * sites_per_cta + (unsigned long long)warp * 8 * AA_T;
+      __syncthreads(); /* both stages free, counters zero */
+      if (threadIdx.x == 0)
+        for (unsigned int o = 0; o < 2 && o < nseg; ++o)
+        {
+          double * dstm = s_mat + (size_t)o * 2 * mat_doubles;
+          aa_mbar_expect(&s_bar[o], 2 * mat_bytes);
+          aa_tma(dstm, ((s_ops[o].flags & AOPF_TIP1) ? a.tiptab : a.frag) + s_ops[o].m1_off, mat_bytes, &s_bar[o]);
+          aa_tma(dstm + mat_doubles, ((s_ops[o].flags & AOPF_TIP2) ? a.tiptab : a.frag) + s_ops[o].m2_off, mat_bytes,
+                 &s_bar[o]);
+        }
+      for (unsigned int o = 0; o < nseg; ++o)
+      {
+        const AaOp & d = s_ops[o];
+        const unsigned int flags = d.flags;
+        const bool look1 = flags & AOPF_TIP1, look2 = flags & AOPF_TIP2;
+        const bool fwd2 = (flags & AOPF_FWD2) && o > 0; /* the first operation of a chunk has no predecessor */
+        const unsigned int st = o & 1u;
+        __syncwarp(); /* children written by earlier operations of this warp are visible to all its lanes */
+        aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
+        ph ^= 1u << st;
+        const double * sL = s_mat + (size_t)st * 2 * mat_doubles;
+        const double * sR = sL + mat_doubles;
+        const bool check = (flags & AOPF_PS) && !(look1 && look2);
+        unsigned int smax[AA_T];
+#pragma unroll
+        for (int t = 0; t < AA_T; ++t) smax[t] = 0;
+
+        if (look1 && look2)
+          aa4_op<AK_LOOK, AK_LOOK, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+        else if (look1 && fwd2)
+          aa4_op<AK_LOOK, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+        else if (look1)
+          aa4_op<AK_LOOK, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+        else if (fwd2)
+          aa4_op<AK_LOAD, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+        else
+          aa4_op<AK_LOAD, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+
+        /* ---- scalers + (rare) rescale pass ---- */
+        if (flags & AOPF_PS)
+        {
+#pragma unroll
+          for (int t = 0; t < AA_T; ++t)
+          {
+            unsigned int m = smax[t];
+            m = max(m, __shfl_xor_sync(0xffffffffu, m, 1));
+            m = max(m, __shfl_xor_sync(0xffffffffu, m, 2));
+            const bool scale = check && m < AA_THR_HI;
+            const unsigned long long site = wsite0 + 8 * t + row;
+            if (site < a.sites)
+            {
+              if (col == 0)
+              {
+                unsigned int v = scale ? 1u : 0u;
+                if (flags & AOPF_S1) v += a.scaler[d.s1_off + site];
+                if (flags & AOPF_S2) v += a.scaler[d.s2_off + site];
+                a.scaler[d.ps_off + site] = v;
+              }
+              if (scale)
+              {
+                /* each lane rescales exactly the entries it wrote, in memory and in the forwarded copy */
+                for (unsigned int k = 0; k < K; ++k)
+                {
+                  double * pd = a.pbase + d.p_off + site * span + k * 20 + 2 * col;
+                  for (int nt = 0; nt < 3; ++nt)
+                    if (nt < 2 || col < 2)
+                    {
+                      pd[nt * 8] *= SCALE_FACTOR_D;
+                      pd[nt * 8 + 1] *= SCALE_FACTOR_D;
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+#pragma unroll
+                  for (int ks = 0; ks < 5; ++ks) fw[k][t][ks] *= SCALE_FACTOR_D;
+              }
+            }
+          }
+        }
+        /* the last warp to leave op o refills its stage with the matrices of op o+2 */
+        __syncwarp();
+        if (lane == 0)
+        {
+          const unsigned int done = atomicAdd(&s_cnt[st], 1u);
+          if (done == AA_WARPS - 1)
+          {
+            s_cnt[st] = 0;
+            if (o + 2 < nseg)
+            {
+              double * dstm = s_mat + (size_t)st * 2 * mat_doubles;
+              aa_mbar_expect(&s_bar[st], 2 * mat_bytes);
+              aa_tma(dstm, ((s_ops[o + 2].flags & AOPF_TIP1) ? a.tiptab : a.frag) + s_ops[o + 2].m1_off, mat_bytes,
+                     &s_bar[st]);
+              aa_tma(dstm + mat_doubles, ((s_ops[o + 2].flags & AOPF_TIP2) ? a.tiptab : a.frag) + s_ops[o + 2].m2_off,
+                     mat_bytes, &s_bar[st]);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int AA_T, int AA_WARPS, int MINB>
+__global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa4_kernel(AaArgs a)
+{
+  trav_aa4_body<AA_T, AA_WARPS, MINB>(a);
+}
+
 /* ---- host ------------------------------------------------------------------------------------ */
 
-int g_opt_aa_variant = 0;
+static int aa_env_int(const char * name, int dflt)
+{
+  const char * v = getenv(name);
+  return v && *v ? atoi(v) : dflt;
+}
+int g_opt_aa_variant = aa_env_int("PLLB200_AA_VARIANT", 0); /* tuning knob: tile / warp / occupancy variants below */
 int g_opt_aa_tiptab = 1; /* tip children by table lookup instead of DMMA */
 
 template <int T, int W, int MINB>
@@ -410,6 +725,55 @@ static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
   trav_aa_kernel<T, W, MINB><<<(unsigned int)blocks, W * 32, smem, xstream(c)>>>(a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_aa_kernel launch");
+}
+
+template <int T, int W, int MINB>
+static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
+{
+  const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double);
+  static bool attr_set = false;
+  static int per_sm = 0;
+  if (!attr_set)
+  {
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_kernel<T, W, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)smem),
+                         "trav_aa4 smem attribute"))
+      return false;
+    attr_set = true;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa4_kernel<T, W, MINB>, W * 32, smem) != cudaSuccess ||
+        per_sm < 1)
+      per_sm = 1;
+  }
+  const unsigned long long spc = (unsigned long long)W * 8 * T;
+  unsigned long long blocks = (a.sites + spc - 1) / spc;
+  blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
+  if (blocks < 1) blocks = 1;
+  trav_aa4_kernel<T, W, MINB><<<(unsigned int)blocks, W * 32, smem, xstream(c)>>>(a);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "trav_aa4_kernel launch");
+}
+
+/* children in the order the Gamma4 kernel expects (lookup | load, lookup | load | forward) */
+static void aa4_canonical_children(AaOp * dops, unsigned int count)
+{
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    AaOp & d = dops[i];
+    const bool t1 = d.flags & AOPF_TIP1, t2 = d.flags & AOPF_TIP2;
+    const bool f1 = i > 0 && !t1 && d.c1_off == dops[i - 1].p_off;
+    const bool f2 = i > 0 && !t2 && d.c2_off == dops[i - 1].p_off;
+    const bool swap = f1 ? !f2 : (!f2 && !t1 && t2);
+    if (swap)
+    {
+      std::swap(d.c1_off, d.c2_off);
+      std::swap(d.s1_off, d.s2_off);
+      std::swap(d.m1_off, d.m2_off);
+      const unsigned int f = d.flags;
+      d.flags = (f & ~(AOPF_TIP1 | AOPF_TIP2 | AOPF_S1 | AOPF_S2)) | ((f & AOPF_TIP1) ? AOPF_TIP2 : 0u) |
+                ((f & AOPF_TIP2) ? AOPF_TIP1 : 0u) | ((f & AOPF_S1) ? AOPF_S2 : 0u) | ((f & AOPF_S2) ? AOPF_S1 : 0u);
+    }
+    if (f1 || f2) d.flags |= AOPF_FWD2;
+  }
 }
 
 bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count)
@@ -459,6 +823,10 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
     d.m2_off = o.child2_matrix_index * K * AA_FRAG;
   }
   const bool collect = batch_collects(BK_TRAV_AA) && g_opt_aa_variant == 0; /* as in launch_aa_variant */
+  const bool tiptab_ok = g_opt_aa_tiptab && c->d_tiptab && c->d_tipmap && p->maxstates <= 24;
+  /* Gamma4 kernel with register forwarding: every tip child must be a table lookup */
+  const bool fwd_kernel = K == 4 && !collect && g_opt_aa_variant >= 20 && (tiptab_ok || !pattern_tip);
+  if (fwd_kernel) aa4_canonical_children(dops, count);
   const AaOp * d_ops = collect ? (const AaOp *)batch_pool_add(dops, sizeof(AaOp) * count)
                                : (const AaOp *)dev_stage_small(c, dops, sizeof(AaOp) * count);
   if (!d_ops) return false;
@@ -479,6 +847,18 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
   }
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
+  if (fwd_kernel)
+    switch (g_opt_aa_variant)
+    {
+      case 21: return launch_aa4_variant<1, 4, 3>(c, a);
+      case 22: return launch_aa4_variant<2, 4, 2>(c, a);
+      case 23: return launch_aa4_variant<1, 8, 1>(c, a);
+      case 24: return launch_aa4_variant<2, 4, 3>(c, a);
+      case 25: return launch_aa4_variant<1, 6, 2>(c, a);
+      case 26: return launch_aa4_variant<1, 5, 3>(c, a);
+      case 27: return launch_aa4_variant<1, 8, 2>(c, a);
+      default: return launch_aa4_variant<1, 4, 3>(c, a);
+    }
   switch (g_opt_aa_variant)
   {
     case 1: return launch_aa_variant<8, 4, 3>(c, a);
@@ -531,7 +911,7 @@ __global__ void sumfrag_kernel(double * __restrict__ frag, const double * __rest
   for (unsigned int t = threadIdx.x; t < 400; t += blockDim.x)
   {
     const unsigned int o = t / 20, n = t % 20; /* output state j, summed state i */
-    const unsigned int nt = o >> 3, ks = n >> 2, lane = ((o & 7u) << 2) | (n & 3u);
+    const unsigned int nt = o >> 3, ks = aa_kstep_of_state(n), lane = ((o & 7u) << 2) | aa_col_of_state(n);
     const size_t at = (size_t)nt * 160 + ks * 32 + lane;
     frag[(size_t)k * AA_FRAG + at] = fr[n] * iev[n * 20 + o];
     frag[((size_t)K + k) * AA_FRAG + at] = ev[o * 20 + n];
