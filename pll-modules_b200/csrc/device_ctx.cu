@@ -728,9 +728,9 @@ bool batch_flush()
     g_h2d_bytes -= b->pool.size(); /* counted when added */
     /* pointer members that may hold pool tokens: the first one of TravArgs / AaArgs (ops), the first two
      * of PmatBatchPart (indices, lengths) */
-    static const int kinds[3] = {BK_TRAV_DNA4, BK_TRAV_AA, BK_PMAT};
-    static const int nptr[3] = {1, 1, 2};
-    for (int q = 0; q < 3; ++q)
+    static const int kinds[4] = {BK_TRAV_DNA4, BK_TRAV_AA, BK_TRAV_AA4, BK_PMAT};
+    static const int nptr[4] = {1, 1, 1, 2};
+    for (int q = 0; q < 4; ++q)
     {
       BatchKind & k = b->kind[kinds[q]];
       if (!k.count) continue;
@@ -744,8 +744,10 @@ bool batch_flush()
     }
     b->pool.clear();
   }
-  for (int kind = 0; kind < BK_COUNT && ok; ++kind)
+  static const int order[BK_COUNT] = {BK_PMAT, BK_TRAV_DNA4, BK_TRAV_AA4, BK_TRAV_AA, BK_SUM_DNA4};
+  for (int q = 0; q < BK_COUNT && ok; ++q)
   {
+    const int kind = order[q];
     BatchKind & k = b->kind[kind];
     if (!k.count) continue;
     const void * d_args = dev_stage(b->lead, k.bytes.data(), k.bytes.size());
@@ -757,6 +759,7 @@ bool batch_flush()
         case BK_PMAT: ok = flush_pmat(b->lead, d_args, k); break;
         case BK_TRAV_DNA4: ok = flush_trav_dna4(b->lead, d_args, k); break;
         case BK_TRAV_AA: ok = flush_trav_aa(b->lead, d_args, k); break;
+        case BK_TRAV_AA4: ok = flush_trav_aa4(b->lead, d_args, k); break;
         default: ok = flush_sum_dna4(b->lead, d_args, k); break;
       }
     k.bytes.clear();

@@ -68,25 +68,32 @@ __device__ __forceinline__ void tma_load_1d(void * dst_smem, const void * src_gm
 }
 
 /* ---- 20-state DMMA operand order (k_traversal_aa.cu, k_pmatrix.cu) -------------------------------
- * The contraction index j of X[site][i] = sum_j C[site][j] P[i][j] may be fed to the five m8n8k4
- * k-steps in any order as long as the A fragment (child CLV) and the B fragment (P^T image) agree.
- * The order is chosen so that lane column c of k-step ks holds the state the SAME lane holds in the
- * D fragment of the previous update: D of n-tile nt = states nt*8 + 2c, 2c+1, hence
- *   (ks, c) <-> state (ks>>1)*8 + 2c + (ks&1)   for ks < 4,      (4, c) <-> state 16 + c.
- * A parent written by one operation is then the A operand of the next one without leaving the
- * registers (one shuffle for k-step 4), and a CLV read from memory is two 16-byte loads and one
- * 8-byte load per category instead of five 8-byte loads. */
+ * X[site][i] = sum_j C[site][j] P[i][j] runs as m8n8k4 tiles: M = 8 sites, N = 8 parent states i
+ * (3 n-tiles), K = 4 child states j (5 k-steps).  Which state sits in which k-slot and which n-column
+ * is free as long as the A fragment (child CLV), the B fragment (P^T image) and the reader of the D
+ * fragment agree.  The order is chosen so that fragment lane column c (= lane & 3) owns the SAME states
+ * on both sides, and owns them contiguously in memory:
+ *   k-slot  (ks, c):  state 4c + ks for ks < 4,           state 16 + c for ks = 4;
+ *   D pair  (nt, c):  states 4c + 2nt, 4c + 2nt + 1 for nt < 2,   16 + 2c, 16 + 2c + 1 for nt = 2 (c < 2).
+ * A parent written by one operation is then the A operand of the next one without leaving the registers
+ * (one shuffle for k-slot 4), a CLV row is read with one 32-byte and one 8-byte load per lane and category,
+ * and written with one 32-byte store (+ one 16-byte store from half the lanes). */
 __host__ __device__ __forceinline__ unsigned int aa_state_of_slot(unsigned int ks, unsigned int c)
 {
-  return ks < 4 ? (ks >> 1) * 8 + 2 * c + (ks & 1u) : 16 + c;
+  return ks < 4 ? 4 * c + ks : 16 + c;
 }
-__host__ __device__ __forceinline__ unsigned int aa_kstep_of_state(unsigned int j)
+__host__ __device__ __forceinline__ unsigned int aa_kstep_of_state(unsigned int j) { return j < 16 ? (j & 3u) : 4; }
+__host__ __device__ __forceinline__ unsigned int aa_col_of_state(unsigned int j) { return j < 16 ? j >> 2 : j - 16; }
+/* first state of the D pair (nt, c) */
+__host__ __device__ __forceinline__ unsigned int aa_dstate(unsigned int nt, unsigned int c)
 {
-  return j < 16 ? (j >> 3) * 2 + (j & 1u) : 4;
+  return nt < 2 ? 4 * c + 2 * nt : 16 + 2 * c;
 }
-__host__ __device__ __forceinline__ unsigned int aa_col_of_state(unsigned int j)
+/* n-tile and column inside the tile (0..7) of parent state i */
+__host__ __device__ __forceinline__ unsigned int aa_ntile_of_state(unsigned int i) { return i < 16 ? (i & 3u) >> 1 : 2; }
+__host__ __device__ __forceinline__ unsigned int aa_ncol_of_state(unsigned int i)
 {
-  return j < 16 ? (j & 7u) >> 1 : j - 16;
+  return i < 16 ? 2 * (i >> 2) + (i & 1u) : i - 16;
 }
 
 #define SCALE_FACTOR_D 115792089237316195423570985008687907853269984665640564039457584007913129639936.0

@@ -160,7 +160,8 @@ extern int g_opt_aa_tiptab;
  * member streams wait for the lead.  Launchers that are not batch-aware must not run in between. */
 /* flush order: P-matrices, CLV updates, sumtables.  Calls collected between two flushes must otherwise be
  * independent of each other (a flush is one phase of the caller's loop over partitions). */
-enum { BK_PMAT = 0, BK_TRAV_DNA4, BK_TRAV_AA, BK_SUM_DNA4, BK_COUNT };
+/* BK_TRAV_AA4: Gamma4 20-state CLV updates on the register-forwarding kernel; flushed before BK_TRAV_AA */
+enum { BK_PMAT = 0, BK_TRAV_DNA4, BK_TRAV_AA, BK_SUM_DNA4, BK_TRAV_AA4, BK_COUNT };
 struct BatchKind
 {
   std::vector<unsigned char> bytes; /* argument structs back to back */
@@ -187,6 +188,7 @@ bool batch_flush();
 bool flush_sum_dna4(PartCtx * lead, const void * d_args, const BatchKind & k);
 bool flush_trav_dna4(PartCtx * lead, const void * d_args, const BatchKind & k);
 bool flush_trav_aa(PartCtx * lead, const void * d_args, const BatchKind & k);
+bool flush_trav_aa4(PartCtx * lead, const void * d_args, const BatchKind & k);
 bool flush_pmat(PartCtx * lead, const void * d_args, const BatchKind & k);
 bool batch_eligible(const PartCtx * c);
 /* the stream a launcher uses: the lead's in batch mode */

@@ -92,9 +92,9 @@ __device__ __forceinline__ void pmatrix_body(double * __restrict__ pmat, double 
       pmat_il[(size_t)m * K * 16 + (i * K + k) * 4 + j] = v;
     if (pmat_il && states == 20)
     {
-      /* m8n8k4 B fragment (col-major 4x8): lane l holds B[row l%4][col l/4] = P[i = nt*8 + l/4][j = state of
-       * slot (ks, l%4), devutil.cuh]; rows i >= 20 of the third n-tile stay zero from the allocation-time memset */
-      const unsigned int nt = i >> 3, ks = aa_kstep_of_state(j), lane = ((i & 7u) << 2) | aa_col_of_state(j);
+      /* m8n8k4 B fragment (col-major 4x8): lane l holds B[row l%4][col l/4] = P[i][j] with i the state of
+       * column l/4 of n-tile nt and j the state of k-slot (ks, l%4) (devutil.cuh); columns 4..7 of the third n-tile stay zero from the allocation-time memset */
+      const unsigned int nt = aa_ntile_of_state(i), ks = aa_kstep_of_state(j), lane = (aa_ncol_of_state(i) << 2) | aa_col_of_state(j);
       pmat_il[(((size_t)m * K + k) * 3 + nt) * 160 + ks * 32 + lane] = v;
     }
   }
@@ -203,7 +203,7 @@ __global__ void pmatrix_reinterleave_kernel(const double * __restrict__ pmat, do
       pmat_il[(size_t)m * K * 16 + (i * K + k) * 4 + j] = v;
     else if (states == 20)
     {
-      const unsigned int nt = i >> 3, ks = aa_kstep_of_state(j), lane = ((i & 7u) << 2) | aa_col_of_state(j);
+      const unsigned int nt = aa_ntile_of_state(i), ks = aa_kstep_of_state(j), lane = (aa_ncol_of_state(i) << 2) | aa_col_of_state(j);
       pmat_il[(((size_t)m * K + k) * 3 + nt) * 160 + ks * 32 + lane] = v;
     }
   }

@@ -95,18 +95,17 @@ __device__ __forceinline__ void dmma(double & c0, double & c1, double a, double 
                : "d"(a), "d"(b));
 }
 
-/* A fragment of one (site, category) from memory in the slot order of devutil.cuh: states 2c, 2c+1 (k-steps 0, 1),
- * 8+2c, 8+2c+1 (k-steps 2, 3) and 16+c (k-step 4) */
+/* A fragment of one (site, category) from memory in the slot order of devutil.cuh: states 4c .. 4c+3 (k-slots
+ * 0-3, one 32-byte load) and 16+c (k-slot 4) */
 __device__ __forceinline__ void aa_load_slots(const double * p, int col, bool act, double (&A)[5])
 {
   if (act)
   {
-    const double2 v0 = *reinterpret_cast<const double2 *>(p + 2 * col);
-    const double2 v1 = *reinterpret_cast<const double2 *>(p + 8 + 2 * col);
-    A[0] = v0.x;
-    A[1] = v0.y;
-    A[2] = v1.x;
-    A[3] = v1.y;
+    const d4 v = ldg256(p + 4 * col);
+    A[0] = v.x;
+    A[1] = v.y;
+    A[2] = v.z;
+    A[3] = v.w;
     A[4] = p[16 + col];
   }
   else
@@ -251,24 +250,24 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
               for (int nt = 0; nt < 3; ++nt) xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
               if (LOOK1)
               {
-                const double * row_l = sL + ((unsigned int)__double2loint(aL[0]) * K + k) * 20 + 2 * col;
+                const double * row_l = sL + ((unsigned int)__double2loint(aL[0]) * K + k) * 20;
 #pragma unroll
                 for (int nt = 0; nt < 3; ++nt)
                   if (nt < 2 || col < 2)
                   {
-                    const double2 v = *reinterpret_cast<const double2 *>(row_l + nt * 8);
+                    const double2 v = *reinterpret_cast<const double2 *>(row_l + aa_dstate(nt, col));
                     xl[nt][0] = v.x;
                     xl[nt][1] = v.y;
                   }
               }
               if (LOOK2)
               {
-                const double * row_r = sR + ((unsigned int)__double2loint(aR[0]) * K + k) * 20 + 2 * col;
+                const double * row_r = sR + ((unsigned int)__double2loint(aR[0]) * K + k) * 20;
 #pragma unroll
                 for (int nt = 0; nt < 3; ++nt)
                   if (nt < 2 || col < 2)
                   {
-                    const double2 v = *reinterpret_cast<const double2 *>(row_r + nt * 8);
+                    const double2 v = *reinterpret_cast<const double2 *>(row_r + aa_dstate(nt, col));
                     xr[nt][0] = v.x;
                     xr[nt][1] = v.y;
                   }
@@ -283,8 +282,8 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
                   if (!LOOK1) dmma(xl[nt][0], xl[nt][1], aL[ks], bL[LOOK1 ? 0 : nt * 5 + ks]);
                   if (!LOOK2) dmma(xr[nt][0], xr[nt][1], aR[ks], bR[LOOK2 ? 0 : nt * 5 + ks]);
                 }
-              /* D fragment: this lane holds parent[site][k][nt*8 + 2*col, +1] */
-              double * pd = a.pbase + d.p_off + site * span + k * 20 + 2 * col;
+              /* D fragment: this lane holds parent[site][k][aa_dstate(nt, col), +1] */
+              double * pd = a.pbase + d.p_off + site * span + k * 20;
 #pragma unroll
               for (int nt = 0; nt < 3; ++nt)
               {
@@ -292,7 +291,7 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
                 if (nt < 2 || col < 2)
                 {
                   if (check) smax[t] = max(smax[t], max((unsigned int)__double2hiint(o0), (unsigned int)__double2hiint(o1)));
-                  if (act) *reinterpret_cast<double2 *>(pd + nt * 8) = make_double2(o0, o1);
+                  if (act) *reinterpret_cast<double2 *>(pd + aa_dstate(nt, col)) = make_double2(o0, o1);
                 }
               }
 #pragma unroll
@@ -336,12 +335,12 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
                 /* each lane rescales exactly the entries it wrote: all k, cols 2*col(+1) of the n-tiles */
                 for (unsigned int k = 0; k < K; ++k)
                 {
-                  double * pd = a.pbase + d.p_off + site * span + k * 20 + 2 * col;
+                  double * pd = a.pbase + d.p_off + site * span + k * 20;
                   for (int nt = 0; nt < 3; ++nt)
                     if (nt < 2 || col < 2)
                     {
-                      pd[nt * 8] *= SCALE_FACTOR_D;
-                      pd[nt * 8 + 1] *= SCALE_FACTOR_D;
+                      pd[aa_dstate(nt, col)] *= SCALE_FACTOR_D;
+                      pd[aa_dstate(nt, col) + 1] *= SCALE_FACTOR_D;
                     }
                 }
               }
@@ -406,6 +405,7 @@ enum { AK_LOOK = 0, AK_LOAD = 2, AK_FWD = 3 };
 template <int C1, int C2, int AA_T>
 __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const double * __restrict__ sL,
                                        const double * __restrict__ sR, unsigned long long wsite0, int lane, bool check,
+                                       const unsigned int (&code1)[AA_T], const unsigned int (&code2)[AA_T],
                                        double (&fw)[4][AA_T][5], unsigned int (&smax)[AA_T])
 {
   constexpr int K = 4;
@@ -413,7 +413,6 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
   const int row = lane >> 2, col = lane & 3;
   const int src4 = (lane & ~3) | (col >> 1); /* lane that holds state 16 + col of this row in its D fragment */
   bool act[AA_T];
-  unsigned int code1[AA_T], code2[AA_T];
   const double * c1p[AA_T];
   const double * c2p[AA_T];
   double * pp[AA_T];
@@ -422,107 +421,112 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
   {
     const unsigned long long site = wsite0 + 8 * t + row;
     act[t] = site < a.sites;
-    if (C1 == AK_LOOK) code1[t] = act[t] ? a.tipchars[d.c1_off + site] : 0u;
-    if (C2 == AK_LOOK) code2[t] = act[t] ? a.tipchars[d.c2_off + site] : 0u;
     if (C1 == AK_LOAD) c1p[t] = a.clv + d.c1_off + site * span;
     if (C2 == AK_LOAD) c2p[t] = a.clv + d.c2_off + site * span;
-    pp[t] = a.pbase + d.p_off + site * span + 2 * col;
+    pp[t] = a.pbase + d.p_off + site * span;
   }
-  double aL[5], aR[5];
-  if (C1 == AK_LOAD) aa_load_slots(c1p[0], col, act[0], aL);
-  if (C2 == AK_LOAD) aa_load_slots(c2p[0], col, act[0], aR);
+  /* children that come from memory: the fragments of category k+1 are requested before the DMMAs of k run */
+  double aL[AA_T][5], aR[AA_T][5], nL[AA_T][5], nR[AA_T][5];
+#pragma unroll
+  for (int t = 0; t < AA_T; ++t)
+  {
+    if (C1 == AK_LOAD) aa_load_slots(c1p[t], col, act[t], aL[t]);
+    if (C2 == AK_LOAD) aa_load_slots(c2p[t], col, act[t], aR[t]);
+  }
 #pragma unroll
   for (int k = 0; k < K; ++k)
   {
-    double bL[C1 == AK_LOOK ? 1 : 15], bR[C2 == AK_LOOK ? 1 : 15];
-    if (C1 != AK_LOOK)
+    if (k + 1 < K)
 #pragma unroll
-      for (int f = 0; f < 15; ++f) bL[C1 == AK_LOOK ? 0 : f] = sL[(k * 15 + f) * 32 + lane];
-    if (C2 != AK_LOOK)
+      for (int t = 0; t < AA_T; ++t)
+      {
+        if (C1 == AK_LOAD) aa_load_slots(c1p[t] + (k + 1) * 20, col, act[t], nL[t]);
+        if (C2 == AK_LOAD) aa_load_slots(c2p[t] + (k + 1) * 20, col, act[t], nR[t]);
+      }
+    if (C2 == AK_FWD)
 #pragma unroll
-      for (int f = 0; f < 15; ++f) bR[C2 == AK_LOOK ? 0 : f] = sR[(k * 15 + f) * 32 + lane];
+      for (int t = 0; t < AA_T; ++t)
 #pragma unroll
-    for (int t = 0; t < AA_T; ++t)
+        for (int ks = 0; ks < 5; ++ks) aR[t][ks] = fw[k][t][ks];
+    double o[AA_T][3][2];
+    /* n-tile outermost: only the five B fragments of one n-tile (per child) are live, and they serve all tiles */
+#pragma unroll
+    for (int nt = 0; nt < 3; ++nt)
     {
-      /* operands of the next (k, tile) step are requested before the DMMAs of this one run */
-      double nL[5], nR[5];
-      const int nk = (t + 1 < AA_T) ? k : k + 1, ntile = (t + 1 < AA_T) ? t + 1 : 0;
-      if (nk < K)
+      double bL[5], bR[5];
+      if (C1 != AK_LOOK)
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks) bL[ks] = sL[(k * 15 + nt * 5 + ks) * 32 + lane];
+      if (C2 != AK_LOOK)
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks) bR[ks] = sR[(k * 15 + nt * 5 + ks) * 32 + lane];
+      double xl[AA_T][2], xr[AA_T][2];
+#pragma unroll
+      for (int t = 0; t < AA_T; ++t)
       {
-        if (C1 == AK_LOAD) aa_load_slots(c1p[ntile] + nk * 20, col, act[ntile], nL);
-        if (C2 == AK_LOAD) aa_load_slots(c2p[ntile] + nk * 20, col, act[ntile], nR);
+        xl[t][0] = xl[t][1] = xr[t][0] = xr[t][1] = 0.0;
+        if (C1 == AK_LOOK && (nt < 2 || col < 2))
+        {
+          const double2 v = *reinterpret_cast<const double2 *>(sL + (code1[t] * K + k) * 20 + aa_dstate(nt, col));
+          xl[t][0] = v.x;
+          xl[t][1] = v.y;
+        }
+        if (C2 == AK_LOOK && (nt < 2 || col < 2))
+        {
+          const double2 v = *reinterpret_cast<const double2 *>(sR + (code2[t] * K + k) * 20 + aa_dstate(nt, col));
+          xr[t][0] = v.x;
+          xr[t][1] = v.y;
+        }
       }
-      if (C2 == AK_FWD)
-#pragma unroll
-        for (int ks = 0; ks < 5; ++ks) aR[ks] = fw[k][t][ks];
-      double xl[3][2], xr[3][2];
-#pragma unroll
-      for (int nt = 0; nt < 3; ++nt) xl[nt][0] = xl[nt][1] = xr[nt][0] = xr[nt][1] = 0.0;
-      if (C1 == AK_LOOK)
-      {
-        const double * row_l = sL + (code1[t] * K + k) * 20 + 2 * col;
-#pragma unroll
-        for (int nt = 0; nt < 3; ++nt)
-          if (nt < 2 || col < 2)
-          {
-            const double2 v = *reinterpret_cast<const double2 *>(row_l + nt * 8);
-            xl[nt][0] = v.x;
-            xl[nt][1] = v.y;
-          }
-      }
-      if (C2 == AK_LOOK)
-      {
-        const double * row_r = sR + (code2[t] * K + k) * 20 + 2 * col;
-#pragma unroll
-        for (int nt = 0; nt < 3; ++nt)
-          if (nt < 2 || col < 2)
-          {
-            const double2 v = *reinterpret_cast<const double2 *>(row_r + nt * 8);
-            xr[nt][0] = v.x;
-            xr[nt][1] = v.y;
-          }
-      }
+      /* k-step outermost: the 2 x AA_T accumulator chains are interleaved */
 #pragma unroll
       for (int ks = 0; ks < 5; ++ks)
 #pragma unroll
-        for (int nt = 0; nt < 3; ++nt)
+        for (int t = 0; t < AA_T; ++t)
         {
-          if (C1 != AK_LOOK) dmma(xl[nt][0], xl[nt][1], aL[ks], bL[C1 == AK_LOOK ? 0 : nt * 5 + ks]);
-          if (C2 != AK_LOOK) dmma(xr[nt][0], xr[nt][1], aR[ks], bR[C2 == AK_LOOK ? 0 : nt * 5 + ks]);
+          if (C1 != AK_LOOK) dmma(xl[t][0], xl[t][1], aL[t][ks], bL[ks]);
+          if (C2 != AK_LOOK) dmma(xr[t][0], xr[t][1], aR[t][ks], bR[ks]);
         }
-      /* D fragment: this lane holds parent[site][k][nt*8 + 2*col, +1] */
-      double o[3][2];
 #pragma unroll
-      for (int nt = 0; nt < 3; ++nt)
+      for (int t = 0; t < AA_T; ++t)
       {
-        o[nt][0] = xl[nt][0] * xr[nt][0];
-        o[nt][1] = xl[nt][1] * xr[nt][1];
-        if (nt < 2 || col < 2)
-        {
-          if (check)
-            smax[t] = max(smax[t], max((unsigned int)__double2hiint(o[nt][0]), (unsigned int)__double2hiint(o[nt][1])));
-          if (act[t]) *reinterpret_cast<double2 *>(pp[t] + k * 20 + nt * 8) = make_double2(o[nt][0], o[nt][1]);
-        }
-      }
-      /* ... and, re-read as an A fragment, the operand of the next operation */
-      fw[k][t][0] = o[0][0];
-      fw[k][t][1] = o[0][1];
-      fw[k][t][2] = o[1][0];
-      fw[k][t][3] = o[1][1];
-      {
-        const double v0 = __shfl_sync(0xffffffffu, o[2][0], src4), v1 = __shfl_sync(0xffffffffu, o[2][1], src4);
-        fw[k][t][4] = (col & 1) ? v1 : v0;
-      }
-      if (nk < K)
-      {
-        if (C1 == AK_LOAD)
-#pragma unroll
-          for (int ks = 0; ks < 5; ++ks) aL[ks] = nL[ks];
-        if (C2 == AK_LOAD)
-#pragma unroll
-          for (int ks = 0; ks < 5; ++ks) aR[ks] = nR[ks];
+        o[t][nt][0] = xl[t][0] * xr[t][0];
+        o[t][nt][1] = xl[t][1] * xr[t][1];
+        if (check && (nt < 2 || col < 2))
+          smax[t] = max(smax[t], max((unsigned int)__double2hiint(o[t][nt][0]), (unsigned int)__double2hiint(o[t][nt][1])));
       }
     }
+    /* D fragments of this lane: parent[site][k][4 col .. 4 col + 3] and, for col < 2, [16 + 2 col, + 1] */
+#pragma unroll
+    for (int t = 0; t < AA_T; ++t)
+    {
+      if (act[t])
+      {
+        d4 v;
+        v.x = o[t][0][0];
+        v.y = o[t][0][1];
+        v.z = o[t][1][0];
+        v.w = o[t][1][1];
+        stg256(pp[t] + k * 20 + 4 * col, v);
+        if (col < 2) *reinterpret_cast<double2 *>(pp[t] + k * 20 + 16 + 2 * col) = make_double2(o[t][2][0], o[t][2][1]);
+      }
+      /* ... and, re-read as an A fragment, the operand of the next operation */
+      fw[k][t][0] = o[t][0][0];
+      fw[k][t][1] = o[t][0][1];
+      fw[k][t][2] = o[t][1][0];
+      fw[k][t][3] = o[t][1][1];
+      const double v0 = __shfl_sync(0xffffffffu, o[t][2][0], src4), v1 = __shfl_sync(0xffffffffu, o[t][2][1], src4);
+      fw[k][t][4] = (col & 1) ? v1 : v0;
+    }
+    if (k + 1 < K)
+#pragma unroll
+      for (int t = 0; t < AA_T; ++t)
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks)
+        {
+          if (C1 == AK_LOAD) aL[t][ks] = nL[t][ks];
+          if (C2 == AK_LOAD) aR[t][ks] = nR[t][ks];
+        }
   }
 }
 
@@ -586,12 +590,38 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           aa_tma(dstm + mat_doubles, ((s_ops[o].flags & AOPF_TIP2) ? a.tiptab : a.frag) + s_ops[o].m2_off, mat_bytes,
                  &s_bar[o]);
         }
+      /* tip codes of the sites of this warp: the ones of op o+1 are requested while op o computes */
+      unsigned int code1[AA_T], code2[AA_T], ncode1[AA_T], ncode2[AA_T];
+      auto load_codes = [&](const AaOp & q, unsigned int (&q1)[AA_T], unsigned int (&q2)[AA_T]) {
+#pragma unroll
+        for (int t = 0; t < AA_T; ++t)
+        {
+          const unsigned long long site = wsite0 + 8 * t + row;
+          q1[t] = ((q.flags & AOPF_TIP1) && site < a.sites) ? a.tipchars[q.c1_off + site] : 0u;
+          q2[t] = ((q.flags & AOPF_TIP2) && site < a.sites) ? a.tipchars[q.c2_off + site] : 0u;
+        }
+      };
+      load_codes(s_ops[0], code1, code2);
       for (unsigned int o = 0; o < nseg; ++o)
       {
         const AaOp & d = s_ops[o];
         const unsigned int flags = d.flags;
         const bool look1 = flags & AOPF_TIP1, look2 = flags & AOPF_TIP2;
         const bool fwd2 = (flags & AOPF_FWD2) && o > 0; /* the first operation of a chunk has no predecessor */
+        if (o + 1 < nseg) load_codes(s_ops[o + 1], ncode1, ncode2);
+        /* child scaler counts: requested now, added after the operation */
+        unsigned int sv[AA_T];
+#pragma unroll
+        for (int t = 0; t < AA_T; ++t)
+        {
+          const unsigned long long site = wsite0 + 8 * t + row;
+          sv[t] = 0;
+          if (col == 0 && site < a.sites)
+          {
+            if (flags & AOPF_S1) sv[t] = a.scaler[d.s1_off + site];
+            if (flags & AOPF_S2) sv[t] += a.scaler[d.s2_off + site];
+          }
+        }
         const unsigned int st = o & 1u;
         __syncwarp(); /* children written by earlier operations of this warp are visible to all its lanes */
         aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
@@ -604,15 +634,15 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
         for (int t = 0; t < AA_T; ++t) smax[t] = 0;
 
         if (look1 && look2)
-          aa4_op<AK_LOOK, AK_LOOK, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+          aa4_op<AK_LOOK, AK_LOOK, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
         else if (look1 && fwd2)
-          aa4_op<AK_LOOK, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+          aa4_op<AK_LOOK, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
         else if (look1)
-          aa4_op<AK_LOOK, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+          aa4_op<AK_LOOK, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
         else if (fwd2)
-          aa4_op<AK_LOAD, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+          aa4_op<AK_LOAD, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
         else
-          aa4_op<AK_LOAD, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, fw, smax);
+          aa4_op<AK_LOAD, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
 
         /* ---- scalers + (rare) rescale pass ---- */
         if (flags & AOPF_PS)
@@ -627,24 +657,18 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
             const unsigned long long site = wsite0 + 8 * t + row;
             if (site < a.sites)
             {
-              if (col == 0)
-              {
-                unsigned int v = scale ? 1u : 0u;
-                if (flags & AOPF_S1) v += a.scaler[d.s1_off + site];
-                if (flags & AOPF_S2) v += a.scaler[d.s2_off + site];
-                a.scaler[d.ps_off + site] = v;
-              }
+              if (col == 0) a.scaler[d.ps_off + site] = sv[t] + (scale ? 1u : 0u);
               if (scale)
               {
                 /* each lane rescales exactly the entries it wrote, in memory and in the forwarded copy */
                 for (unsigned int k = 0; k < K; ++k)
                 {
-                  double * pd = a.pbase + d.p_off + site * span + k * 20 + 2 * col;
+                  double * pd = a.pbase + d.p_off + site * span + k * 20;
                   for (int nt = 0; nt < 3; ++nt)
                     if (nt < 2 || col < 2)
                     {
-                      pd[nt * 8] *= SCALE_FACTOR_D;
-                      pd[nt * 8 + 1] *= SCALE_FACTOR_D;
+                      pd[aa_dstate(nt, col)] *= SCALE_FACTOR_D;
+                      pd[aa_dstate(nt, col) + 1] *= SCALE_FACTOR_D;
                     }
                 }
 #pragma unroll
@@ -654,6 +678,12 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
               }
             }
           }
+        }
+#pragma unroll
+        for (int t = 0; t < AA_T; ++t)
+        {
+          code1[t] = ncode1[t];
+          code2[t] = ncode2[t];
         }
         /* the last warp to leave op o refills its stage with the matrices of op o+2 */
         __syncwarp();
@@ -683,6 +713,16 @@ template <int AA_T, int AA_WARPS, int MINB>
 __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa4_kernel(AaArgs a)
 {
   trav_aa4_body<AA_T, AA_WARPS, MINB>(a);
+}
+
+template <int AA_T, int AA_WARPS, int MINB>
+__global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa4_batch_kernel(const AaArgs * __restrict__ arr)
+{
+  __shared__ AaArgs sa;
+  for (unsigned int i = threadIdx.x; i < sizeof(AaArgs) / 4; i += blockDim.x)
+    reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
+  __syncthreads();
+  trav_aa4_body<AA_T, AA_WARPS, MINB>(sa);
 }
 
 /* ---- host ------------------------------------------------------------------------------------ */
@@ -752,6 +792,12 @@ static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_aa4_kernel launch");
 }
+
+/* tile / warp / occupancy of the default Gamma4 kernel (measured best of the variants below at C3) */
+#define AA4_T 1
+#define AA4_W 8
+#define AA4_MINB 2
+static const size_t AA4_SMEM = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double);
 
 /* children in the order the Gamma4 kernel expects (lookup | load, lookup | load | forward) */
 static void aa4_canonical_children(AaOp * dops, unsigned int count)
@@ -825,7 +871,7 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
   const bool collect = batch_collects(BK_TRAV_AA) && g_opt_aa_variant == 0; /* as in launch_aa_variant */
   const bool tiptab_ok = g_opt_aa_tiptab && c->d_tiptab && c->d_tipmap && p->maxstates <= 24;
   /* Gamma4 kernel with register forwarding: every tip child must be a table lookup */
-  const bool fwd_kernel = K == 4 && !collect && g_opt_aa_variant >= 20 && (tiptab_ok || !pattern_tip);
+  const bool fwd_kernel = K == 4 && (g_opt_aa_variant == 0 || g_opt_aa_variant >= 20) && (tiptab_ok || !pattern_tip);
   if (fwd_kernel) aa4_canonical_children(dops, count);
   const AaOp * d_ops = collect ? (const AaOp *)batch_pool_add(dops, sizeof(AaOp) * count)
                                : (const AaOp *)dev_stage_small(c, dops, sizeof(AaOp) * count);
@@ -847,6 +893,12 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
   }
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
+  if (fwd_kernel && collect)
+  {
+    const unsigned long long spc = (unsigned long long)AA4_W * 8 * AA4_T;
+    batch_collect(BK_TRAV_AA4, &a, sizeof(a), (unsigned int)((a.sites + spc - 1) / spc), AA4_SMEM);
+    return true;
+  }
   if (fwd_kernel)
     switch (g_opt_aa_variant)
     {
@@ -857,7 +909,9 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
       case 25: return launch_aa4_variant<1, 6, 2>(c, a);
       case 26: return launch_aa4_variant<1, 5, 3>(c, a);
       case 27: return launch_aa4_variant<1, 8, 2>(c, a);
-      default: return launch_aa4_variant<1, 4, 3>(c, a);
+      case 28: return launch_aa4_variant<2, 5, 2>(c, a);
+      case 29: return launch_aa4_variant<2, 6, 2>(c, a);
+      default: return launch_aa4_variant<AA4_T, AA4_W, AA4_MINB>(c, a);
     }
   switch (g_opt_aa_variant)
   {
@@ -895,6 +949,22 @@ bool flush_trav_aa(PartCtx * lead, const void * d_args, const BatchKind & k)
   return pllb200_cuda_ok(cudaGetLastError(), "batched trav_aa kernel launch");
 }
 
+bool flush_trav_aa4(PartCtx * lead, const void * d_args, const BatchKind & k)
+{
+  static bool attr_set = false;
+  if (!attr_set)
+  {
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_batch_kernel<AA4_T, AA4_W, AA4_MINB>,
+                                              cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AA4_SMEM),
+                         "trav_aa4 batch smem attribute"))
+      return false;
+    attr_set = true;
+  }
+  trav_aa4_batch_kernel<AA4_T, AA4_W, AA4_MINB><<<dim3(k.max_blocks, k.count), AA4_W * 32, AA4_SMEM, lead->stream>>>(
+      static_cast<const AaArgs *>(d_args));
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "batched trav_aa4 kernel launch");
+}
 
 /* ---- 20-state sumtable on the same kernel ------------------------------------------------------
  * sum[n,k,j] = (sum_i P[n,k,i] pi_i Vinv[i][j]) * (sum_i V[j][i] C[n,k,i])   (core_derivatives.c:116-640)
@@ -911,7 +981,7 @@ __global__ void sumfrag_kernel(double * __restrict__ frag, const double * __rest
   for (unsigned int t = threadIdx.x; t < 400; t += blockDim.x)
   {
     const unsigned int o = t / 20, n = t % 20; /* output state j, summed state i */
-    const unsigned int nt = o >> 3, ks = aa_kstep_of_state(n), lane = ((o & 7u) << 2) | aa_col_of_state(n);
+    const unsigned int nt = aa_ntile_of_state(o), ks = aa_kstep_of_state(n), lane = (aa_ncol_of_state(o) << 2) | aa_col_of_state(n);
     const size_t at = (size_t)nt * 160 + ks * 32 + lane;
     frag[(size_t)k * AA_FRAG + at] = fr[n] * iev[n * 20 + o];
     frag[((size_t)K + k) * AA_FRAG + at] = ev[o * 20 + n];
