@@ -334,6 +334,23 @@ def main():
         dev_ms, e2e_s, kern_avg = [float(x) for x in t.cpu()]
     peak, peak_kind = measured_peak()
     achieved = alg_bytes / (kern_avg * 1e-3) / 1e9
+    # 95 % of the kernel's DRAM traffic is the parent CLVs going out (children come from registers / L2), and a
+    # write-only stream does not reach the copy figure of MEASURED_PEAKS.json: time one here (4 GiB fill, best of 5)
+    write_peak = None
+    try:
+        wbuf = torch.empty(1 << 30, dtype=torch.float32, device="cuda")
+        wts = []
+        for _ in range(6):
+            w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            w0.record()
+            wbuf.fill_(1.0)
+            w1.record()
+            torch.cuda.synchronize()
+            wts.append(w0.elapsed_time(w1))
+        write_peak = wbuf.numel() * 4 / (min(wts[1:]) * 1e-3) / 1e9
+        del wbuf
+    except Exception:
+        pass
 
     if rank == 0:
         line = {
@@ -360,6 +377,9 @@ def main():
                          # L1 / L2, so the kernel moves about half of the algorithmic bytes through DRAM
                          "dram_GBps": 27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9,
                          "frac_dram": 27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9 / peak,
+                         "write_stream_GBps": write_peak,
+                         "frac_dram_of_write_stream": (27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9 / write_peak
+                                                       if write_peak else None),
                          "peak_kind": peak_kind, "kernel": "trav_dna_kernel<4,false>",
                          "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kern_avg,
                          "kernel_share_of_step": kern_avg / dev_ms},

@@ -449,6 +449,50 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
 #pragma unroll
         for (int ks = 0; ks < 5; ++ks) aR[t][ks] = fw[k][t][ks];
     double o[AA_T][3][2];
+    /* tip children: x = T[code][k][.] from the table in this child's matrix slot.  A 16-byte shared-memory load is
+     * served a quarter warp (two site rows) at a time and every table row starts at the same bank, so two rows with
+     * different codes would collide on every access: even rows therefore fetch their n-tile 0 pair while odd rows
+     * fetch their n-tile 1 pair (the other 16 bytes of the same 32), and the second load does the opposite */
+    double lk1[AA_T][3][2], lk2[AA_T][3][2];
+    const int odd = row & 1;
+#pragma unroll
+    for (int t = 0; t < AA_T; ++t)
+    {
+      if (C1 == AK_LOOK)
+      {
+        const double * rp = sL + (code1[t] * K + k) * 20;
+        const double2 x = *reinterpret_cast<const double2 *>(rp + 4 * col + 2 * odd);
+        const double2 y = *reinterpret_cast<const double2 *>(rp + 4 * col + 2 * (1 - odd));
+        lk1[t][0][0] = odd ? y.x : x.x;
+        lk1[t][0][1] = odd ? y.y : x.y;
+        lk1[t][1][0] = odd ? x.x : y.x;
+        lk1[t][1][1] = odd ? x.y : y.y;
+        lk1[t][2][0] = lk1[t][2][1] = 0.0;
+        if (col < 2)
+        {
+          const double2 z = *reinterpret_cast<const double2 *>(rp + 16 + 2 * col);
+          lk1[t][2][0] = z.x;
+          lk1[t][2][1] = z.y;
+        }
+      }
+      if (C2 == AK_LOOK)
+      {
+        const double * rp = sR + (code2[t] * K + k) * 20;
+        const double2 x = *reinterpret_cast<const double2 *>(rp + 4 * col + 2 * odd);
+        const double2 y = *reinterpret_cast<const double2 *>(rp + 4 * col + 2 * (1 - odd));
+        lk2[t][0][0] = odd ? y.x : x.x;
+        lk2[t][0][1] = odd ? y.y : x.y;
+        lk2[t][1][0] = odd ? x.x : y.x;
+        lk2[t][1][1] = odd ? x.y : y.y;
+        lk2[t][2][0] = lk2[t][2][1] = 0.0;
+        if (col < 2)
+        {
+          const double2 z = *reinterpret_cast<const double2 *>(rp + 16 + 2 * col);
+          lk2[t][2][0] = z.x;
+          lk2[t][2][1] = z.y;
+        }
+      }
+    }
     /* n-tile outermost: only the five B fragments of one n-tile (per child) are live, and they serve all tiles */
 #pragma unroll
     for (int nt = 0; nt < 3; ++nt)
@@ -465,17 +509,15 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
       for (int t = 0; t < AA_T; ++t)
       {
         xl[t][0] = xl[t][1] = xr[t][0] = xr[t][1] = 0.0;
-        if (C1 == AK_LOOK && (nt < 2 || col < 2))
+        if (C1 == AK_LOOK)
         {
-          const double2 v = *reinterpret_cast<const double2 *>(sL + (code1[t] * K + k) * 20 + aa_dstate(nt, col));
-          xl[t][0] = v.x;
-          xl[t][1] = v.y;
+          xl[t][0] = lk1[t][nt][0];
+          xl[t][1] = lk1[t][nt][1];
         }
-        if (C2 == AK_LOOK && (nt < 2 || col < 2))
+        if (C2 == AK_LOOK)
         {
-          const double2 v = *reinterpret_cast<const double2 *>(sR + (code2[t] * K + k) * 20 + aa_dstate(nt, col));
-          xr[t][0] = v.x;
-          xr[t][1] = v.y;
+          xr[t][0] = lk2[t][nt][0];
+          xr[t][1] = lk2[t][nt][1];
         }
       }
       /* k-step outermost: the 2 x AA_T accumulator chains are interleaved */
