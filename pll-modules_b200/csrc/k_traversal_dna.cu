@@ -248,10 +248,22 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     {
       const DevOp & nx = sm.ops[o + 1];
       const unsigned long long woff = (unsigned long long)(s0 - (unsigned int)(lane / K) * R) * ESTEP + lane * 16;
-      if (!(nx.flags & (OPF_TIP1 | OPF_FWD1)))
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.clv + nx.c1_off + woff));
-      if (!(nx.flags & (OPF_TIP2 | OPF_FWD2)))
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(a.clv + nx.c2_off + woff));
+      /* mode 2: into L1 — the child was written by this warp (L2 holds it), and a CLV is written once per launch,
+       * so the line cannot go stale before its single reader uses it */
+      if (a.l2_prefetch == 2)
+      {
+        if (!(nx.flags & (OPF_TIP1 | OPF_FWD1)))
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(a.clv + nx.c1_off + woff));
+        if (!(nx.flags & (OPF_TIP2 | OPF_FWD2)))
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(a.clv + nx.c2_off + woff));
+      }
+      else
+      {
+        if (!(nx.flags & (OPF_TIP1 | OPF_FWD1)))
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(a.clv + nx.c1_off + woff));
+        if (!(nx.flags & (OPF_TIP2 | OPF_FWD2)))
+          asm volatile("prefetch.global.L2 [%0];" ::"l"(a.clv + nx.c2_off + woff));
+      }
     }
     /* child scaler counts (the lanes that own a scaler entry only): the loads are issued here, the
      * counts are only combined when the parent scaler is written, after the arithmetic (ncu: adding

@@ -25,4 +25,8 @@ for _ in range(4):
 ms = sorted(ts)[1]
 print(json.dumps({"workload": "protein LG+G4 %d taxa x %d sites" % (tips, sites), "loglh": ll, "ops": c, "kernel_ms": ms,
                   "site_updates_per_s": (tips - 2) * sites / ms * 1e3, "algorithmic_GBps": alg / ms / 1e6,
-                  "TFLOPs_fp64": flops / ms / 1e9}))
+                  "TFLOPs_fp64": flops / ms / 1e9,
+                  # what the tensor pipe executes: 15 m8n8k4 DMMAs (512 flop) per 8 sites, category and inner
+                  # child (n padded 20 -> 24); tip children are table lookups.  Peak: scripts/probes/dmma_peak.cu
+                  "dmma_TFLOPs_issued": (c["ii"] * 2 + c["ti"]) * sites * 4 * 15 * 512 / 8 / ms / 1e9,
+                  "dmma_frac_of_37.15_peak": (c["ii"] * 2 + c["ti"]) * sites * 4 * 15 * 512 / 8 / ms / 1e9 / 37.15}))

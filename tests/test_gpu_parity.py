@@ -108,6 +108,35 @@ def test_clvs_scalers_logl_match_reference(kw):
             np.testing.assert_allclose(dev.pmatrix(m), ref.pmatrix(m), rtol=1e-9, atol=1e-15)
 
 
+@pytest.mark.parametrize("kw", [
+    dict(tips=150, sites=203, states=20, brlen_scale=6.0),   # > 128 operations: two staged segments, scaling active
+    dict(tips=40, sites=1000, states=20),
+    dict(tips=33, sites=130, states=20, attributes=0),       # tip CLVs: every child is loaded or forwarded
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_protein_forwarding_kernel_equals_the_per_operation_kernel(kw):
+    """20 states, Gamma4: the kernel that hands a parent's D fragments to the next operation as A fragments
+    (default; tile / warp variants 22 and 26) writes the same CLVs and scaler counts as the kernel that reads
+    every inner child from memory (variant 3) — the two run their DMMA k-steps in the same order."""
+    pkg = load_product_package()
+    tips = kw["tips"]
+    out = {}
+    for variant in (3, 0, 22, 26):
+        pkg.set_option("aa_variant", variant)
+        try:
+            with Harness("b200", **kw) as h:
+                ll = h.loglh(0)
+                out[variant] = (ll, [h.clv(tips + i).copy() for i in range(tips - 2)],
+                                [h.scaler(i).copy() for i in range(tips - 2)])
+        finally:
+            pkg.set_option("aa_variant", 0)
+    for variant in (0, 22, 26):
+        assert rel(out[variant][0], out[3][0]) < 1e-13, (variant, out[variant][0], out[3][0])
+        for i in range(tips - 2):
+            assert np.array_equal(out[variant][2][i], out[3][2][i]), (variant, i)
+            np.testing.assert_allclose(out[variant][1][i], out[3][1][i], rtol=1e-13, atol=0)
+    assert any(int(s.sum()) > 0 for s in out[0][2]) or kw.get("brlen_scale", 1.0) == 1.0
+
+
 @needs_ref
 @pytest.mark.parametrize("kw", [
     dict(tips=16, sites=5000),
