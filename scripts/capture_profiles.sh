@@ -10,6 +10,9 @@ python bench.py --steps 5 --warmup 3 --blo > $O/bench_n1.json 2> $O/bench_n1.err
 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_reference_arm.json 2>> $O/bench_n1.err
 python scripts/bench_configs.py c1 c3 c4 c5 > $O/bench_configs.jsonl 2> $O/bench_configs.err
 python scripts/bench_blo.py 200 1000000 > $O/bench_blo.jsonl 2>&1
+python scripts/bench_aa.py 500 200000 > $O/bench_aa_c3.json 2>&1
+# FP64 tensor-pipe peak (the 20-state kernel's second roofline)
+nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o /tmp/dmma_peak scripts/probes/dmma_peak.cu && /tmp/dmma_peak > $O/dmma_peak.jsonl 2>&1
 # launch lists (share of the step per kernel)
 python bench.py --sites 200000 --steps 2 --warmup 1 --no-cpu-baseline > /dev/null 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches_bench_sites200k.csv \
