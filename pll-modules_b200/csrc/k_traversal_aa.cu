@@ -400,13 +400,33 @@ __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_batch_kernel(cons
  * Rate categories are a template constant (4): the forwarded fragments live in registers
  * fw[k][tile][slot], which needs every index to be known at compile time. */
 #define AOPF_FWD2 32u
+#define AOPF_SYNC0 64u /* a child read from memory is the previous operation's parent (both children are that node) */
 enum { AK_LOOK = 0, AK_LOAD = 2, AK_FWD = 3 };
 
-template <int C1, int C2, int AA_T>
+/* TS: the parent tile (8 sites x 640 B, contiguous in the CLV arena) is assembled in a per-warp shared-memory
+ * buffer `stg` and leaves with one TMA bulk store per operation instead of 16-/32-byte global stores from the
+ * fragment layout (which cost twice the L1TEX wavefronts of the bytes they carry) */
+__device__ __forceinline__ void aa_bulk_wait_read()
+{
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+template <int N>
+__device__ __forceinline__ void aa_bulk_wait()
+{
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+__device__ __forceinline__ void aa_bulk_store(double * gdst, const double * ssrc, unsigned int bytes)
+{
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(aa_smem_u32(ssrc)), "r"(bytes)
+               : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+
+template <int C1, int C2, int AA_T, bool TS>
 __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const double * __restrict__ sL,
                                        const double * __restrict__ sR, unsigned long long wsite0, int lane, bool check,
                                        const unsigned int (&code1)[AA_T], const unsigned int (&code2)[AA_T],
-                                       double (&fw)[4][AA_T][5], unsigned int (&smax)[AA_T])
+                                       double (&fw)[4][AA_T][5], unsigned int (&smax)[AA_T], double * stg)
 {
   constexpr int K = 4;
   constexpr unsigned long long span = K * 20;
@@ -426,22 +446,31 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
     pp[t] = a.pbase + d.p_off + site * span;
   }
   /* children that come from memory: the fragments of category k+1 are requested before the DMMAs of k run */
+  constexpr bool PF = AA_T == 1; /* two tiles per warp: no registers left for the look-ahead copy */
   double aL[AA_T][5], aR[AA_T][5], nL[AA_T][5], nR[AA_T][5];
+  if (PF)
 #pragma unroll
-  for (int t = 0; t < AA_T; ++t)
-  {
-    if (C1 == AK_LOAD) aa_load_slots(c1p[t], col, act[t], aL[t]);
-    if (C2 == AK_LOAD) aa_load_slots(c2p[t], col, act[t], aR[t]);
-  }
+    for (int t = 0; t < AA_T; ++t)
+    {
+      if (C1 == AK_LOAD) aa_load_slots(c1p[t], col, act[t], aL[t]);
+      if (C2 == AK_LOAD) aa_load_slots(c2p[t], col, act[t], aR[t]);
+    }
 #pragma unroll
   for (int k = 0; k < K; ++k)
   {
-    if (k + 1 < K)
+    if (PF && k + 1 < K)
 #pragma unroll
       for (int t = 0; t < AA_T; ++t)
       {
         if (C1 == AK_LOAD) aa_load_slots(c1p[t] + (k + 1) * 20, col, act[t], nL[t]);
         if (C2 == AK_LOAD) aa_load_slots(c2p[t] + (k + 1) * 20, col, act[t], nR[t]);
+      }
+    if (!PF)
+#pragma unroll
+      for (int t = 0; t < AA_T; ++t)
+      {
+        if (C1 == AK_LOAD) aa_load_slots(c1p[t] + k * 20, col, act[t], aL[t]);
+        if (C2 == AK_LOAD) aa_load_slots(c2p[t] + k * 20, col, act[t], aR[t]);
       }
     if (C2 == AK_FWD)
 #pragma unroll
@@ -542,7 +571,23 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
 #pragma unroll
     for (int t = 0; t < AA_T; ++t)
     {
-      if (act[t])
+      if (TS)
+      {
+        if (k == 0 && t == 0)
+        {
+          /* the bulk store of the previous operation has finished reading the buffer */
+          if (lane == 0) aa_bulk_wait_read();
+          __syncwarp();
+        }
+        /* every row of the buffer starts at the same bank: odd rows write the two halves of their 32 bytes in the
+         * opposite order (as for the table lookups) */
+        double * sp = stg + (8 * t + row) * 80 + k * 20;
+        const int odd = row & 1;
+        *reinterpret_cast<double2 *>(sp + 4 * col + 2 * odd) = odd ? make_double2(o[t][1][0], o[t][1][1]) : make_double2(o[t][0][0], o[t][0][1]);
+        *reinterpret_cast<double2 *>(sp + 4 * col + 2 * (1 - odd)) = odd ? make_double2(o[t][0][0], o[t][0][1]) : make_double2(o[t][1][0], o[t][1][1]);
+        if (col < 2) *reinterpret_cast<double2 *>(sp + 16 + 2 * col) = make_double2(o[t][2][0], o[t][2][1]);
+      }
+      else if (act[t])
       {
         d4 v;
         v.x = o[t][0][0];
@@ -560,7 +605,7 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
       const double v0 = __shfl_sync(0xffffffffu, o[t][2][0], src4), v1 = __shfl_sync(0xffffffffu, o[t][2][1], src4);
       fw[k][t][4] = (col & 1) ? v1 : v0;
     }
-    if (k + 1 < K)
+    if (PF && k + 1 < K)
 #pragma unroll
       for (int t = 0; t < AA_T; ++t)
 #pragma unroll
@@ -573,7 +618,7 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
 }
 
 /* dynamic shared memory as in trav_aa_body with K = 4 */
-template <int AA_T, int AA_WARPS, int MINB>
+template <int AA_T, int AA_WARPS, int MINB, bool TS>
 __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -586,6 +631,8 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int row = lane >> 2, col = lane & 3;
   constexpr unsigned int mat_doubles = K * AA_FRAG;
+  /* TS: per-warp parent tile buffers behind the matrix stages, [AA_T x 8 sites][K][20] */
+  double * const stg = TS ? s_mat + (size_t)4 * mat_doubles + (size_t)warp * AA_T * 8 * 80 : nullptr;
   constexpr unsigned int mat_bytes = mat_doubles * sizeof(double);
   constexpr unsigned long long span = K * 20;
   const unsigned long long sites_per_cta = (unsigned long long)AA_WARPS * 8 * AA_T;
@@ -674,17 +721,30 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
         unsigned int smax[AA_T];
 #pragma unroll
         for (int t = 0; t < AA_T; ++t) smax[t] = 0;
+        if (TS && !(look1 && (look2 || fwd2)))
+        {
+          /* a child read from memory was written at least two operations ago: all bulk stores but the newest are
+           * complete (and their data visible to this thread, then to the warp) */
+          if (lane == 0)
+          {
+            if (flags & AOPF_SYNC0)
+              aa_bulk_wait<0>();
+            else
+              aa_bulk_wait<1>();
+          }
+          __syncwarp();
+        }
 
         if (look1 && look2)
-          aa4_op<AK_LOOK, AK_LOOK, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
+          aa4_op<AK_LOOK, AK_LOOK, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
         else if (look1 && fwd2)
-          aa4_op<AK_LOOK, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
+          aa4_op<AK_LOOK, AK_FWD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
         else if (look1)
-          aa4_op<AK_LOOK, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
+          aa4_op<AK_LOOK, AK_LOAD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
         else if (fwd2)
-          aa4_op<AK_LOAD, AK_FWD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
+          aa4_op<AK_LOAD, AK_FWD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
         else
-          aa4_op<AK_LOAD, AK_LOAD, AA_T>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax);
+          aa4_op<AK_LOAD, AK_LOAD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
 
         /* ---- scalers + (rare) rescale pass ---- */
         if (flags & AOPF_PS)
@@ -705,7 +765,7 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
                 /* each lane rescales exactly the entries it wrote, in memory and in the forwarded copy */
                 for (unsigned int k = 0; k < K; ++k)
                 {
-                  double * pd = a.pbase + d.p_off + site * span + k * 20;
+                  double * pd = TS ? stg + (8 * t + row) * 80 + k * 20 : a.pbase + d.p_off + site * span + k * 20;
                   for (int nt = 0; nt < 3; ++nt)
                     if (nt < 2 || col < 2)
                     {
@@ -727,6 +787,16 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           code1[t] = ncode1[t];
           code2[t] = ncode2[t];
         }
+        if (TS)
+        {
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); /* this lane's buffer writes -> async proxy */
+          __syncwarp();
+          if (lane == 0 && wsite0 < a.sites)
+          {
+            const unsigned long long n = min((unsigned long long)(8 * AA_T), (unsigned long long)a.sites - wsite0);
+            aa_bulk_store(a.pbase + d.p_off + wsite0 * span, stg, (unsigned int)(n * span * sizeof(double)));
+          }
+        }
         /* the last warp to leave op o refills its stage with the matrices of op o+2 */
         __syncwarp();
         if (lane == 0)
@@ -747,24 +817,30 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           }
         }
       }
+      if (TS)
+      {
+        /* segment / chunk boundary: every store of this warp is complete before its sites are revisited */
+        if (lane == 0) aa_bulk_wait<0>();
+        __syncwarp();
+      }
     }
   }
 }
 
-template <int AA_T, int AA_WARPS, int MINB>
+template <int AA_T, int AA_WARPS, int MINB, bool TS>
 __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa4_kernel(AaArgs a)
 {
-  trav_aa4_body<AA_T, AA_WARPS, MINB>(a);
+  trav_aa4_body<AA_T, AA_WARPS, MINB, TS>(a);
 }
 
-template <int AA_T, int AA_WARPS, int MINB>
+template <int AA_T, int AA_WARPS, int MINB, bool TS>
 __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa4_batch_kernel(const AaArgs * __restrict__ arr)
 {
   __shared__ AaArgs sa;
   for (unsigned int i = threadIdx.x; i < sizeof(AaArgs) / 4; i += blockDim.x)
     reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
   __syncthreads();
-  trav_aa4_body<AA_T, AA_WARPS, MINB>(sa);
+  trav_aa4_body<AA_T, AA_WARPS, MINB, TS>(sa);
 }
 
 /* ---- host ------------------------------------------------------------------------------------ */
@@ -809,20 +885,21 @@ static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
   return pllb200_cuda_ok(cudaGetLastError(), "trav_aa_kernel launch");
 }
 
-template <int T, int W, int MINB>
+template <int T, int W, int MINB, bool TS = false>
 static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
 {
-  const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double);
+  const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double) +
+                      (TS ? (size_t)W * T * 8 * 80 * sizeof(double) : 0);
   static bool attr_set = false;
   static int per_sm = 0;
   if (!attr_set)
   {
-    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_kernel<T, W, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_kernel<T, W, MINB, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem),
                          "trav_aa4 smem attribute"))
       return false;
     attr_set = true;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa4_kernel<T, W, MINB>, W * 32, smem) != cudaSuccess ||
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa4_kernel<T, W, MINB, TS>, W * 32, smem) != cudaSuccess ||
         per_sm < 1)
       per_sm = 1;
   }
@@ -830,7 +907,7 @@ static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
   unsigned long long blocks = (a.sites + spc - 1) / spc;
   blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
   if (blocks < 1) blocks = 1;
-  trav_aa4_kernel<T, W, MINB><<<(unsigned int)blocks, W * 32, smem, xstream(c)>>>(a);
+  trav_aa4_kernel<T, W, MINB, TS><<<(unsigned int)blocks, W * 32, smem, xstream(c)>>>(a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_aa4_kernel launch");
 }
@@ -839,6 +916,7 @@ static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
 #define AA4_T 1
 #define AA4_W 8
 #define AA4_MINB 2
+#define AA4_TS false
 static const size_t AA4_SMEM = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double);
 
 /* children in the order the Gamma4 kernel expects (lookup | load, lookup | load | forward) */
@@ -861,6 +939,7 @@ static void aa4_canonical_children(AaOp * dops, unsigned int count)
                 ((f & AOPF_TIP2) ? AOPF_TIP1 : 0u) | ((f & AOPF_S1) ? AOPF_S2 : 0u) | ((f & AOPF_S2) ? AOPF_S1 : 0u);
     }
     if (f1 || f2) d.flags |= AOPF_FWD2;
+    if (f1 && f2) d.flags |= AOPF_SYNC0;
   }
 }
 
@@ -953,7 +1032,14 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
       case 27: return launch_aa4_variant<1, 8, 2>(c, a);
       case 28: return launch_aa4_variant<2, 5, 2>(c, a);
       case 29: return launch_aa4_variant<2, 6, 2>(c, a);
-      default: return launch_aa4_variant<AA4_T, AA4_W, AA4_MINB>(c, a);
+      case 30: return launch_aa4_variant<1, 6, 3>(c, a);
+      case 31: return launch_aa4_variant<1, 9, 2>(c, a);
+      case 32: return launch_aa4_variant<1, 10, 2>(c, a);
+      case 33: return launch_aa4_variant<1, 7, 3>(c, a);
+      case 40: return launch_aa4_variant<1, 8, 2, true>(c, a);
+      case 41: return launch_aa4_variant<1, 6, 3, true>(c, a);
+      case 42: return launch_aa4_variant<1, 9, 2, true>(c, a);
+      default: return launch_aa4_variant<AA4_T, AA4_W, AA4_MINB, AA4_TS>(c, a);
     }
   switch (g_opt_aa_variant)
   {
@@ -996,13 +1082,13 @@ bool flush_trav_aa4(PartCtx * lead, const void * d_args, const BatchKind & k)
   static bool attr_set = false;
   if (!attr_set)
   {
-    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_batch_kernel<AA4_T, AA4_W, AA4_MINB>,
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_batch_kernel<AA4_T, AA4_W, AA4_MINB, AA4_TS>,
                                               cudaFuncAttributeMaxDynamicSharedMemorySize, (int)AA4_SMEM),
                          "trav_aa4 batch smem attribute"))
       return false;
     attr_set = true;
   }
-  trav_aa4_batch_kernel<AA4_T, AA4_W, AA4_MINB><<<dim3(k.max_blocks, k.count), AA4_W * 32, AA4_SMEM, lead->stream>>>(
+  trav_aa4_batch_kernel<AA4_T, AA4_W, AA4_MINB, AA4_TS><<<dim3(k.max_blocks, k.count), AA4_W * 32, AA4_SMEM, lead->stream>>>(
       static_cast<const AaArgs *>(d_args));
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "batched trav_aa4 kernel launch");

@@ -115,12 +115,12 @@ def test_clvs_scalers_logl_match_reference(kw):
 ], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
 def test_protein_forwarding_kernel_equals_the_per_operation_kernel(kw):
     """20 states, Gamma4: the kernel that hands a parent's D fragments to the next operation as A fragments
-    (default; tile / warp variants 22 and 26) writes the same CLVs and scaler counts as the kernel that reads
+    (default; tile / warp variants 22 and 26; 40 = parent tiles leave through a TMA bulk store) writes the same CLVs and scaler counts as the kernel that reads
     every inner child from memory (variant 3) — the two run their DMMA k-steps in the same order."""
     pkg = load_product_package()
     tips = kw["tips"]
     out = {}
-    for variant in (3, 0, 22, 26):
+    for variant in (3, 0, 22, 26, 40):
         pkg.set_option("aa_variant", variant)
         try:
             with Harness("b200", **kw) as h:
@@ -129,7 +129,7 @@ def test_protein_forwarding_kernel_equals_the_per_operation_kernel(kw):
                                 [h.scaler(i).copy() for i in range(tips - 2)])
         finally:
             pkg.set_option("aa_variant", 0)
-    for variant in (0, 22, 26):
+    for variant in (0, 22, 26, 40):
         assert rel(out[variant][0], out[3][0]) < 1e-13, (variant, out[variant][0], out[3][0])
         for i in range(tips - 2):
             assert np.array_equal(out[variant][2][i], out[3][2][i]), (variant, i)
