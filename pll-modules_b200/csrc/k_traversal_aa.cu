@@ -426,7 +426,8 @@ template <int C1, int C2, int AA_T, bool TS>
 __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const double * __restrict__ sL,
                                        const double * __restrict__ sR, unsigned long long wsite0, int lane, bool check,
                                        const unsigned int (&code1)[AA_T], const unsigned int (&code2)[AA_T],
-                                       double (&fw)[4][AA_T][5], unsigned int (&smax)[AA_T], double * stg)
+                                       double (&fw)[4][AA_T][5], unsigned int (&smax)[AA_T], double * stg,
+                                       const double (&cur)[AA_T][5])
 {
   constexpr int K = 4;
   constexpr unsigned long long span = K * 20;
@@ -448,12 +449,18 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
   /* children that come from memory: the fragments of category k+1 are requested before the DMMAs of k run */
   constexpr bool PF = AA_T == 1; /* two tiles per warp: no registers left for the look-ahead copy */
   double aL[AA_T][5], aR[AA_T][5], nL[AA_T][5], nR[AA_T][5];
+  /* category 0 of the first child that comes from memory was requested during the previous operation (`cur`) */
   if (PF)
 #pragma unroll
     for (int t = 0; t < AA_T; ++t)
     {
-      if (C1 == AK_LOAD) aa_load_slots(c1p[t], col, act[t], aL[t]);
-      if (C2 == AK_LOAD) aa_load_slots(c2p[t], col, act[t], aR[t]);
+      if (C1 == AK_LOAD)
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks) aL[t][ks] = cur[t][ks];
+      if (C2 == AK_LOAD && C1 != AK_LOAD)
+#pragma unroll
+        for (int ks = 0; ks < 5; ++ks) aR[t][ks] = cur[t][ks];
+      if (C2 == AK_LOAD && C1 == AK_LOAD) aa_load_slots(c2p[t], col, act[t], aR[t]);
     }
 #pragma unroll
   for (int k = 0; k < K; ++k)
@@ -691,13 +698,38 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
         }
       };
       load_codes(s_ops[0], code1, code2);
+      /* category 0 of the first child of an operation that is read from memory (not a tip, not forwarded): requested
+       * one operation ahead, like the tip codes.  That child was written at least two operations earlier. */
+      double cur[AA_T][5], nxt[AA_T][5];
+      auto load_first = [&](const AaOp & q, bool fwd_ok, double (&dst)[AA_T][5]) {
+        const bool l1 = !(q.flags & AOPF_TIP1);
+        const bool l2 = !(q.flags & AOPF_TIP2) && !((q.flags & AOPF_FWD2) && fwd_ok);
+        if (AA_T == 1 && (l1 || l2))
+        {
+          const unsigned long long off = l1 ? q.c1_off : q.c2_off;
+#pragma unroll
+          for (int t = 0; t < AA_T; ++t)
+          {
+            const unsigned long long site = wsite0 + 8 * t + row;
+            aa_load_slots(a.clv + off + site * span, col, site < a.sites, dst[t]);
+          }
+        }
+      };
+      load_first(s_ops[0], false, nxt);
       for (unsigned int o = 0; o < nseg; ++o)
       {
+        const bool prefetched = o == 0 || (!TS && !(s_ops[o].flags & AOPF_SYNC0));
+        if (prefetched)
+#pragma unroll
+          for (int t = 0; t < AA_T; ++t)
+#pragma unroll
+            for (int ks = 0; ks < 5; ++ks) cur[t][ks] = nxt[t][ks];
         const AaOp & d = s_ops[o];
         const unsigned int flags = d.flags;
         const bool look1 = flags & AOPF_TIP1, look2 = flags & AOPF_TIP2;
         const bool fwd2 = (flags & AOPF_FWD2) && o > 0; /* the first operation of a chunk has no predecessor */
         if (o + 1 < nseg) load_codes(s_ops[o + 1], ncode1, ncode2);
+        if (!TS && o + 1 < nseg && !(s_ops[o + 1].flags & AOPF_SYNC0)) load_first(s_ops[o + 1], true, nxt);
         /* child scaler counts: requested now, added after the operation */
         unsigned int sv[AA_T];
 #pragma unroll
@@ -734,17 +766,18 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           }
           __syncwarp();
         }
+        if (!prefetched) load_first(d, true, cur);
 
         if (look1 && look2)
-          aa4_op<AK_LOOK, AK_LOOK, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
+          aa4_op<AK_LOOK, AK_LOOK, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg, cur);
         else if (look1 && fwd2)
-          aa4_op<AK_LOOK, AK_FWD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
+          aa4_op<AK_LOOK, AK_FWD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg, cur);
         else if (look1)
-          aa4_op<AK_LOOK, AK_LOAD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
+          aa4_op<AK_LOOK, AK_LOAD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg, cur);
         else if (fwd2)
-          aa4_op<AK_LOAD, AK_FWD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
+          aa4_op<AK_LOAD, AK_FWD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg, cur);
         else
-          aa4_op<AK_LOAD, AK_LOAD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg);
+          aa4_op<AK_LOAD, AK_LOAD, AA_T, TS>(a, d, sL, sR, wsite0, lane, check, code1, code2, fw, smax, stg, cur);
 
         /* ---- scalers + (rare) rescale pass ---- */
         if (flags & AOPF_PS)
