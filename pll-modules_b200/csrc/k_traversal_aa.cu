@@ -53,6 +53,7 @@ struct AaArgs
   const double * tiptab; /* per matrix [code 24][k][20] = P x tip vector (k_pmatrix.cu), or null */
   const unsigned char * tipchars;
   const unsigned long long * tipmap;
+  int l1_prefetch; /* Gamma4 kernel: pull the next operation's memory children into L1 while this one computes */
 };
 
 /* defaults: 4 warps per CTA, 4 tiles of 8 sites per warp and chunk (template parameters below) */
@@ -730,6 +731,22 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
         const bool fwd2 = (flags & AOPF_FWD2) && o > 0; /* the first operation of a chunk has no predecessor */
         if (o + 1 < nseg) load_codes(s_ops[o + 1], ncode1, ncode2);
         if (!TS && o + 1 < nseg && !(s_ops[o + 1].flags & AOPF_SYNC0)) load_first(s_ops[o + 1], true, nxt);
+        if (!TS && a.l1_prefetch && o + 1 < nseg && wsite0 + 8 * AA_T <= a.sites)
+        {
+          /* the warp's tile of a child is AA_T x 5 KB of consecutive memory: 40 lines per 8 sites */
+          const AaOp & q = s_ops[o + 1];
+          const bool l1 = !(q.flags & AOPF_TIP1), l2 = !(q.flags & (AOPF_TIP2 | AOPF_FWD2));
+#pragma unroll
+          for (int i = 0; i < (40 * AA_T + 31) / 32; ++i)
+          {
+            const int line = i * 32 + lane;
+            if (line < 40 * AA_T)
+            {
+              if (l1) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.clv + q.c1_off + wsite0 * span + line * 16));
+              if (l2) asm volatile("prefetch.global.L1 [%0];" ::"l"(a.clv + q.c2_off + wsite0 * span + line * 16));
+            }
+          }
+        }
         /* child scaler counts: requested now, added after the operation */
         unsigned int sv[AA_T];
 #pragma unroll
@@ -1047,6 +1064,7 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
   }
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
+  a.l1_prefetch = g_opt_trav_prefetch;
   if (fwd_kernel && collect)
   {
     const unsigned long long spc = (unsigned long long)AA4_W * 8 * AA4_T;
@@ -1201,5 +1219,6 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
   a.tiptab = nullptr; /* the "matrices" here are eigenvector images, not P-matrices */
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
+  a.l1_prefetch = 0;
   return launch_aa_variant<2, 4, 3>(c, a);
 }

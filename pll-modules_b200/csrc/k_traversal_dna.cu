@@ -24,6 +24,7 @@
 #include "devutil.cuh"
 
 #include <algorithm>
+#include <type_traits>
 
 struct __align__(16) DevOp
 {
@@ -89,7 +90,7 @@ __device__ __forceinline__ unsigned int hi_word(double x) { return (unsigned int
 /* arithmetic of one op for the R elements of a lane; T1/T2: child is a pattern tip */
 template <int K, int R, bool T1, bool T2, bool FULL>
 __device__ __forceinline__ void op_body(const double * __restrict__ p1, const double * __restrict__ p2,
-                                        unsigned int t1, unsigned int t2, const double * sL,
+                                        unsigned long long t1, unsigned long long t2, const double * sL,
                                         const double * sR, int k, unsigned int actmask,
                                         unsigned long long * bar, unsigned int parity,
                                         const d4 (&fw)[R], unsigned int flags, double (&out)[R][4])
@@ -125,8 +126,8 @@ __device__ __forceinline__ void op_body(const double * __restrict__ p1, const do
 #pragma unroll
   for (int r = 0; r < R; ++r)
   {
-    if (T1) v1[r] = tip_vector(t1 >> (8 * r));
-    if (T2) v2[r] = tip_vector(t2 >> (8 * r));
+    if (T1) v1[r] = tip_vector((unsigned int)(t1 >> (8 * r)));
+    if (T2) v2[r] = tip_vector((unsigned int)(t2 >> (8 * r)));
   }
   mbar_wait(bar, parity); /* matrices of this op have landed */
 #pragma unroll
@@ -168,25 +169,31 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
   for (int r = 0; r < R; ++r)
     if (FULL || s0 + r < a.sites) actmask |= 1u << r;
 
-  /* R tip codes packed little-endian into one word (R = 4: one aligned 32-bit load) */
-  auto load_tips = [&](const unsigned char * base) -> unsigned int {
+  /* R tip codes packed little-endian into one word (R = 4: one aligned 32-bit load, R = 8: one 64-bit load) */
+  using tip_t = typename std::conditional<(R > 4), unsigned long long, unsigned int>::type;
+  auto load_tips = [&](const unsigned char * base) -> tip_t {
+    if (FULL && R == 8) return (tip_t)__ldg(reinterpret_cast<const unsigned long long *>(base));
     if (FULL && R == 4) return __ldg(reinterpret_cast<const unsigned int *>(base));
     if (FULL && R == 2) return __ldg(reinterpret_cast<const unsigned short *>(base));
-    unsigned int t = 0;
+    tip_t t = 0;
 #pragma unroll
     for (int r = 0; r < R; ++r)
-      if ((actmask >> r) & 1u) t |= (unsigned int)__ldg(base + r) << (8 * r);
+      if ((actmask >> r) & 1u) t |= (tip_t)__ldg(base + r) << (8 * r);
     return t;
   };
   /* R scaler counts of one child (per-site mode with R = 4: one 128-bit load) */
   auto add_scalers = [&](const unsigned int * base, unsigned int (&sc)[R]) {
-    if (FULL && R == 4 && !RATE_SCALERS)
+    if (FULL && (R == 4 || R == 8) && !RATE_SCALERS)
     {
-      const uint4 q = *reinterpret_cast<const uint4 *>(base);
-      sc[0] += q.x;
-      sc[1] += q.y;
-      sc[2] += q.z;
-      sc[3] += q.w;
+#pragma unroll
+      for (int h = 0; h < R / 4; ++h)
+      {
+        const uint4 q = *reinterpret_cast<const uint4 *>(base + 4 * h);
+        sc[4 * h + 0] += q.x;
+        sc[4 * h + 1] += q.y;
+        sc[4 * h + 2] += q.z;
+        sc[4 * h + 3] += q.w;
+      }
     }
     else
     {
@@ -212,7 +219,7 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     fw[r] = d4{0.0, 0.0, 0.0, 0.0};
     fsc[r] = 0;
   }
-  unsigned int t1 = 0, t2 = 0; /* packed tip codes of the CURRENT op */
+  tip_t t1 = 0, t2 = 0; /* packed tip codes of the CURRENT op */
   {
     const unsigned int f0 = sm.ops[0].flags;
     if (f0 & OPF_TIP1) t1 = load_tips(a.tipchars + sm.ops[0].c1_off + s0);
@@ -234,7 +241,7 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
       tma_load_1d(sm.mat[warp][st ^ 1u][1], a.pmat_il + sm.ops[o + 1].m2_off, MAT_BYTES, &sm.bar[warp][st ^ 1u]);
     }
     /* tip codes of the NEXT op (always a DRAM access: issued a whole op early) */
-    unsigned int n1 = 0, n2 = 0;
+    tip_t n1 = 0, n2 = 0;
     if (o + 1 < nseg)
     {
       const unsigned int fn = sm.ops[o + 1].flags;
@@ -331,9 +338,14 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
       if (sc_lane)
       {
         unsigned int * ps = a.scaler + d.ps_off + sidx0;
-        if (FULL && R == 4 && !RATE_SCALERS)
-          *reinterpret_cast<uint4 *>(ps) = make_uint4(sc[0] + (scalemask & 1u), sc[1] + ((scalemask >> 1) & 1u),
-                                                      sc[2] + ((scalemask >> 2) & 1u), sc[3] + ((scalemask >> 3) & 1u));
+        if (FULL && (R == 4 || R == 8) && !RATE_SCALERS)
+        {
+#pragma unroll
+          for (int h = 0; h < R / 4; ++h)
+            *reinterpret_cast<uint4 *>(ps + 4 * h) =
+                make_uint4(sc[4 * h] + ((scalemask >> (4 * h)) & 1u), sc[4 * h + 1] + ((scalemask >> (4 * h + 1)) & 1u),
+                           sc[4 * h + 2] + ((scalemask >> (4 * h + 2)) & 1u), sc[4 * h + 3] + ((scalemask >> (4 * h + 3)) & 1u));
+        }
         else
         {
 #pragma unroll
@@ -488,6 +500,7 @@ static bool launch_k(PartCtx * c, const TravArgs & a, bool rate_scalers)
       case 2: return launch_variant<K, 2, false, 3>(c, a);
       case 3: return launch_variant<K, 4, false, 2>(c, a);
       case 4: return launch_variant<K, 2, false, 2>(c, a);
+      case 5: return launch_variant<K, 8, false, 1>(c, a);
       default: break;
     }
     return launch_variant<K, 4, false, 2>(c, a);

@@ -8,6 +8,8 @@ sites = int(sys.argv[2]) if len(sys.argv) > 2 else 200000
 pkg = load_product_package()
 if os.environ.get("PLLB200_AA_TIPTAB"):
     pkg.set_option("aa_tiptab", int(os.environ["PLLB200_AA_TIPTAB"]))
+if os.environ.get("PLLB200_TRAV_PREFETCH"):
+    pkg.set_option("trav_prefetch", int(os.environ["PLLB200_TRAV_PREFETCH"]))
 if os.environ.get("PLLB200_AA_VARIANT"):
     pkg.set_option("aa_variant", int(os.environ["PLLB200_AA_VARIANT"]))
 h = Harness("b200", tips=tips, sites=sites, states=20)
