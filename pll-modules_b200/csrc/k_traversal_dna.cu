@@ -248,16 +248,29 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
       if (fn & OPF_TIP1) n1 = load_tips(a.tipchars + sm.ops[o + 1].c1_off + s0);
       if (fn & OPF_TIP2) n2 = load_tips(a.tipchars + sm.ops[o + 1].c2_off + s0);
     }
+    /* tip codes are the one operand that always comes from DRAM, and under the kernel's write load a DRAM read
+     * takes about as long as a whole operation: ask L2 for the codes of op o + (l2_prefetch >> 4) now, so that the
+     * register load one op ahead (above) finds them there.  32*R/K sites = one 32-byte sector (R = 4) per child. */
+    {
+      const unsigned int tipd = (unsigned int)a.l2_prefetch >> 4;
+      if (tipd && o + tipd < nseg && lane < 2)
+      {
+        const DevOp & q = sm.ops[o + tipd];
+        const unsigned int cs0 = s0 - (unsigned int)(lane / K) * R;
+        if (lane == 0 && (q.flags & OPF_TIP1)) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.tipchars + q.c1_off + cs0));
+        if (lane == 1 && (q.flags & OPF_TIP2)) asm volatile("prefetch.global.L2 [%0];" ::"l"(a.tipchars + q.c2_off + cs0));
+      }
+    }
     /* inner children of the NEXT op that will not come out of registers: one 128-byte line per lane
      * covers the warp's 4 KB of each child.  Costs no register; turns the DRAM miss that op o+1 would
      * wait for (ncu: 15 % of the stall samples sit on the first use of those loads) into an L2 hit. */
-    if (FULL && R == 4 && K == 4 && a.l2_prefetch && o + 1 < nseg)
+    if (FULL && R == 4 && K == 4 && (a.l2_prefetch & 3) && o + 1 < nseg)
     {
       const DevOp & nx = sm.ops[o + 1];
       const unsigned long long woff = (unsigned long long)(s0 - (unsigned int)(lane / K) * R) * ESTEP + lane * 16;
       /* mode 2: into L1 — the child was written by this warp (L2 holds it), and a CLV is written once per launch,
        * so the line cannot go stale before its single reader uses it */
-      if (a.l2_prefetch == 2)
+      if ((a.l2_prefetch & 3) == 2)
       {
         if (!(nx.flags & (OPF_TIP1 | OPF_FWD1)))
           asm volatile("prefetch.global.L1 [%0];" ::"l"(a.clv + nx.c1_off + woff));
