@@ -748,16 +748,16 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           }
         }
         /* child scaler counts: requested now, added after the operation */
-        unsigned int sv[AA_T];
+        unsigned int sv1[AA_T], sv2[AA_T]; /* two registers: an add here would wait for both loads right away */
 #pragma unroll
         for (int t = 0; t < AA_T; ++t)
         {
           const unsigned long long site = wsite0 + 8 * t + row;
-          sv[t] = 0;
+          sv1[t] = sv2[t] = 0;
           if (col == 0 && site < a.sites)
           {
-            if (flags & AOPF_S1) sv[t] = a.scaler[d.s1_off + site];
-            if (flags & AOPF_S2) sv[t] += a.scaler[d.s2_off + site];
+            if (flags & AOPF_S1) sv1[t] = a.scaler[d.s1_off + site];
+            if (flags & AOPF_S2) sv2[t] = a.scaler[d.s2_off + site];
           }
         }
         const unsigned int st = o & 1u;
@@ -809,7 +809,7 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
             const unsigned long long site = wsite0 + 8 * t + row;
             if (site < a.sites)
             {
-              if (col == 0) a.scaler[d.ps_off + site] = sv[t] + (scale ? 1u : 0u);
+              if (col == 0) a.scaler[d.ps_off + site] = sv1[t] + sv2[t] + (scale ? 1u : 0u);
               if (scale)
               {
                 /* each lane rescales exactly the entries it wrote, in memory and in the forwarded copy */
