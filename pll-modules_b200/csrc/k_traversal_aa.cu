@@ -401,6 +401,9 @@ __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa_batch_kernel(cons
  * Rate categories are a template constant (4): the forwarded fragments live in registers
  * fw[k][tile][slot], which needs every index to be known at compile time. */
 #define AOPF_FWD2 32u
+/* ops staged per CTA.  64 x 64 B + 32 B + 2 stages x 30 KB = 65,568 B: two CTAs fit the 132 KB shared-memory
+ * carve-out and leave 124 KB of L1 (with 128 ops and the unused tip map the next step, 164 KB, was taken) */
+#define AA4_SEG 64
 #define AOPF_SYNC0 64u /* a child read from memory is the previous operation's parent (both children are that node) */
 enum { AK_LOOK = 0, AK_LOAD = 2, AK_FWD = 3 };
 
@@ -625,22 +628,22 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
   }
 }
 
-/* dynamic shared memory as in trav_aa_body with K = 4 */
-template <int AA_T, int AA_WARPS, int MINB, bool TS>
+/* dynamic shared memory: AaOp ops[AA4_SEG] | u64 bar[NS] | u32 cnt[NS] (+ pad) | double mat[NS stages][2][4*480] | staging */
+template <int AA_T, int AA_WARPS, int MINB, bool TS, int NS = 2> /* NS: matrix stages (operations in flight) */
 __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
 {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   AaOp * s_ops = reinterpret_cast<AaOp *>(smem_raw);
-  unsigned long long * s_bar = reinterpret_cast<unsigned long long *>(smem_raw + sizeof(AaOp) * AA_SEG) + 256;
-  unsigned int * s_cnt = reinterpret_cast<unsigned int *>(s_bar + 2);
-  double * s_mat = reinterpret_cast<double *>(s_bar + 4);
+  unsigned long long * s_bar = reinterpret_cast<unsigned long long *>(smem_raw + sizeof(AaOp) * AA4_SEG);
+  unsigned int * s_cnt = reinterpret_cast<unsigned int *>(s_bar + NS);
+  double * s_mat = reinterpret_cast<double *>(s_bar + 2 * NS); /* NS = 2: 32 bytes as in trav_aa_body, NS = 3: 48 */
 
   constexpr unsigned int K = 4;
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int row = lane >> 2, col = lane & 3;
   constexpr unsigned int mat_doubles = K * AA_FRAG;
   /* TS: per-warp parent tile buffers behind the matrix stages, [AA_T x 8 sites][K][20] */
-  double * const stg = TS ? s_mat + (size_t)4 * mat_doubles + (size_t)warp * AA_T * 8 * 80 : nullptr;
+  double * const stg = TS ? s_mat + (size_t)2 * NS * mat_doubles + (size_t)warp * AA_T * 8 * 80 : nullptr;
   constexpr unsigned int mat_bytes = mat_doubles * sizeof(double);
   constexpr unsigned long long span = K * 20;
   const unsigned long long sites_per_cta = (unsigned long long)AA_WARPS * 8 * AA_T;
@@ -649,9 +652,11 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
 
   if (threadIdx.x == 0)
   {
-    aa_mbar_init(&s_bar[0], 1);
-    aa_mbar_init(&s_bar[1], 1);
-    s_cnt[0] = s_cnt[1] = 0;
+    for (int i = 0; i < NS; ++i)
+    {
+      aa_mbar_init(&s_bar[i], 1);
+      s_cnt[i] = 0;
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   unsigned int ph = 0;
@@ -663,9 +668,9 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
 #pragma unroll
       for (int ks = 0; ks < 5; ++ks) fw[k][t][ks] = 0.0;
 
-  for (unsigned int seg = 0; seg < a.nops; seg += AA_SEG)
+  for (unsigned int seg = 0; seg < a.nops; seg += AA4_SEG)
   {
-    const unsigned int nseg = min(a.nops - seg, (unsigned int)AA_SEG);
+    const unsigned int nseg = min(a.nops - seg, (unsigned int)AA4_SEG);
     __syncthreads();
     {
       const uint4 * src = reinterpret_cast<const uint4 *>(a.ops + seg);
@@ -679,7 +684,7 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
       const unsigned long long wsite0 = chunk * sites_per_cta + (unsigned long long)warp * 8 * AA_T;
       __syncthreads(); /* both stages free, counters zero */
       if (threadIdx.x == 0)
-        for (unsigned int o = 0; o < 2 && o < nseg; ++o)
+        for (unsigned int o = 0; o < NS && o < nseg; ++o)
         {
           double * dstm = s_mat + (size_t)o * 2 * mat_doubles;
           aa_mbar_expect(&s_bar[o], 2 * mat_bytes);
@@ -687,6 +692,7 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           aa_tma(dstm + mat_doubles, ((s_ops[o].flags & AOPF_TIP2) ? a.tiptab : a.frag) + s_ops[o].m2_off, mat_bytes,
                  &s_bar[o]);
         }
+      unsigned int st = 0; /* stage of operation o: o mod NS */
       /* tip codes of the sites of this warp: the ones of op o+1 are requested while op o computes */
       unsigned int code1[AA_T], code2[AA_T], ncode1[AA_T], ncode2[AA_T];
       auto load_codes = [&](const AaOp & q, unsigned int (&q1)[AA_T], unsigned int (&q2)[AA_T]) {
@@ -760,7 +766,6 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
             if (flags & AOPF_S2) sv2[t] = a.scaler[d.s2_off + site];
           }
         }
-        const unsigned int st = o & 1u;
         __syncwarp(); /* children written by earlier operations of this warp are visible to all its lanes */
         aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
         ph ^= 1u << st;
@@ -855,17 +860,18 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           if (done == AA_WARPS - 1)
           {
             s_cnt[st] = 0;
-            if (o + 2 < nseg)
+            if (o + NS < nseg)
             {
               double * dstm = s_mat + (size_t)st * 2 * mat_doubles;
               aa_mbar_expect(&s_bar[st], 2 * mat_bytes);
-              aa_tma(dstm, ((s_ops[o + 2].flags & AOPF_TIP1) ? a.tiptab : a.frag) + s_ops[o + 2].m1_off, mat_bytes,
+              aa_tma(dstm, ((s_ops[o + NS].flags & AOPF_TIP1) ? a.tiptab : a.frag) + s_ops[o + NS].m1_off, mat_bytes,
                      &s_bar[st]);
-              aa_tma(dstm + mat_doubles, ((s_ops[o + 2].flags & AOPF_TIP2) ? a.tiptab : a.frag) + s_ops[o + 2].m2_off,
+              aa_tma(dstm + mat_doubles, ((s_ops[o + NS].flags & AOPF_TIP2) ? a.tiptab : a.frag) + s_ops[o + NS].m2_off,
                      mat_bytes, &s_bar[st]);
             }
           }
         }
+        st = st + 1 == NS ? 0 : st + 1;
       }
       if (TS)
       {
@@ -877,10 +883,10 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
   }
 }
 
-template <int AA_T, int AA_WARPS, int MINB, bool TS>
+template <int AA_T, int AA_WARPS, int MINB, bool TS, int NS>
 __global__ void __launch_bounds__(AA_WARPS * 32, MINB) trav_aa4_kernel(AaArgs a)
 {
-  trav_aa4_body<AA_T, AA_WARPS, MINB, TS>(a);
+  trav_aa4_body<AA_T, AA_WARPS, MINB, TS, NS>(a);
 }
 
 template <int AA_T, int AA_WARPS, int MINB, bool TS>
@@ -908,8 +914,11 @@ static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
 {
   const unsigned int K = a.K;
   const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * K * AA_FRAG * sizeof(double);
-  static size_t smem_set = 0;
-  static int per_sm = 0;
+  /* function attributes belong to a device: one slot per device (a process may drive several) */
+  static size_t smem_set_dev[64] = {0};
+  static int per_sm_dev[64] = {0};
+  size_t & smem_set = smem_set_dev[c->device & 63];
+  int & per_sm = per_sm_dev[c->device & 63];
   if (smem > smem_set)
   {
     if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa_kernel<T, W, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -935,21 +944,23 @@ static bool launch_aa_variant(PartCtx * c, const AaArgs & a)
   return pllb200_cuda_ok(cudaGetLastError(), "trav_aa_kernel launch");
 }
 
-template <int T, int W, int MINB, bool TS = false>
+template <int T, int W, int MINB, bool TS = false, int NS = 2>
 static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
 {
-  const size_t smem = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double) +
+  const size_t smem = sizeof(AaOp) * AA4_SEG + 2 * NS * 8 + (size_t)NS * 2 * 4 * AA_FRAG * sizeof(double) +
                       (TS ? (size_t)W * T * 8 * 80 * sizeof(double) : 0);
-  static bool attr_set = false;
-  static int per_sm = 0;
+  static bool attr_set_dev[64] = {false};
+  static int per_sm_dev[64] = {0};
+  bool & attr_set = attr_set_dev[c->device & 63];
+  int & per_sm = per_sm_dev[c->device & 63];
   if (!attr_set)
   {
-    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_kernel<T, W, MINB, TS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_kernel<T, W, MINB, TS, NS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                               (int)smem),
                          "trav_aa4 smem attribute"))
       return false;
     attr_set = true;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa4_kernel<T, W, MINB, TS>, W * 32, smem) != cudaSuccess ||
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trav_aa4_kernel<T, W, MINB, TS, NS>, W * 32, smem) != cudaSuccess ||
         per_sm < 1)
       per_sm = 1;
   }
@@ -957,7 +968,7 @@ static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
   unsigned long long blocks = (a.sites + spc - 1) / spc;
   blocks = std::min<unsigned long long>(blocks, (unsigned long long)c->sm_count * per_sm);
   if (blocks < 1) blocks = 1;
-  trav_aa4_kernel<T, W, MINB, TS><<<(unsigned int)blocks, W * 32, smem, xstream(c)>>>(a);
+  trav_aa4_kernel<T, W, MINB, TS, NS><<<(unsigned int)blocks, W * 32, smem, xstream(c)>>>(a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_aa4_kernel launch");
 }
@@ -967,7 +978,7 @@ static bool launch_aa4_variant(PartCtx * c, const AaArgs & a)
 #define AA4_W 8
 #define AA4_MINB 2
 #define AA4_TS false
-static const size_t AA4_SMEM = sizeof(AaOp) * AA_SEG + 256 * 8 + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double);
+static const size_t AA4_SMEM = sizeof(AaOp) * AA4_SEG + 4 * 8 + (size_t)2 * 2 * 4 * AA_FRAG * sizeof(double);
 
 /* children in the order the Gamma4 kernel expects (lookup | load, lookup | load | forward) */
 static void aa4_canonical_children(AaOp * dops, unsigned int count)
@@ -1088,6 +1099,8 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
       case 32: return launch_aa4_variant<1, 10, 2>(c, a);
       case 33: return launch_aa4_variant<1, 7, 3>(c, a);
       case 40: return launch_aa4_variant<1, 8, 2, true>(c, a);
+      case 50: return launch_aa4_variant<1, 8, 2, false, 3>(c, a);
+      case 51: return launch_aa4_variant<1, 6, 2, false, 3>(c, a);
       case 41: return launch_aa4_variant<1, 6, 3, true>(c, a);
       case 42: return launch_aa4_variant<1, 9, 2, true>(c, a);
       default: return launch_aa4_variant<AA4_T, AA4_W, AA4_MINB, AA4_TS>(c, a);
@@ -1112,7 +1125,8 @@ bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count
 
 bool flush_trav_aa(PartCtx * lead, const void * d_args, const BatchKind & k)
 {
-  static size_t smem_set = 0;
+  static size_t smem_set_dev[64] = {0};
+  size_t & smem_set = smem_set_dev[lead->device & 63];
   if (k.smem > smem_set)
   {
     if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa_batch_kernel<2, 4, 3>,
@@ -1130,7 +1144,8 @@ bool flush_trav_aa(PartCtx * lead, const void * d_args, const BatchKind & k)
 
 bool flush_trav_aa4(PartCtx * lead, const void * d_args, const BatchKind & k)
 {
-  static bool attr_set = false;
+  static bool attr_set_dev[64] = {false};
+  bool & attr_set = attr_set_dev[lead->device & 63];
   if (!attr_set)
   {
     if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_aa4_batch_kernel<AA4_T, AA4_W, AA4_MINB, AA4_TS>,

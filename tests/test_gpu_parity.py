@@ -120,7 +120,7 @@ def test_protein_forwarding_kernel_equals_the_per_operation_kernel(kw):
     pkg = load_product_package()
     tips = kw["tips"]
     out = {}
-    for variant in (3, 0, 22, 26, 40):
+    for variant in (3, 0, 22, 26, 40, 50):
         pkg.set_option("aa_variant", variant)
         try:
             with Harness("b200", **kw) as h:
@@ -129,7 +129,7 @@ def test_protein_forwarding_kernel_equals_the_per_operation_kernel(kw):
                                 [h.scaler(i).copy() for i in range(tips - 2)])
         finally:
             pkg.set_option("aa_variant", 0)
-    for variant in (0, 22, 26, 40):
+    for variant in (0, 22, 26, 40, 50):
         assert rel(out[variant][0], out[3][0]) < 1e-13, (variant, out[variant][0], out[3][0])
         for i in range(tips - 2):
             assert np.array_equal(out[variant][2][i], out[3][2][i]), (variant, i)
