@@ -159,7 +159,10 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
     {
       const unsigned long long wsite0 = chunk * sites_per_cta + (unsigned long long)warp * 8 * AA_T;
       __syncthreads(); /* both stages free, counters zero */
-      if (threadIdx.x == 0)
+      /* a launch of at most two operations (the single CLV updates and the sumtable of branch-length
+       * optimisation) keeps its matrices in the stages: loaded for the CTA's first chunk only */
+      const bool fresh = a.nops > 2 || chunk == blockIdx.x;
+      if (threadIdx.x == 0 && fresh)
         for (unsigned int o = 0; o < 2 && o < nseg; ++o)
         {
           double * dstm = s_mat + (size_t)o * 2 * mat_doubles;
@@ -180,8 +183,11 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
         /* A warp only ever touches its own sites, so the warps of a CTA are not kept in step: the CLV this
          * warp wrote in op o-1 only has to be visible to its own lanes */
         __syncwarp();
-        aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
-        ph ^= 1u << st;
+        if (fresh)
+        {
+          aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
+          ph ^= 1u << st;
+        }
         const double * sL = s_mat + (size_t)st * 2 * mat_doubles;
         const double * sR = sL + mat_doubles;
         const bool check = (flags & AOPF_PS) && !(tip1 && tip2);
@@ -683,7 +689,10 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
     {
       const unsigned long long wsite0 = chunk * sites_per_cta + (unsigned long long)warp * 8 * AA_T;
       __syncthreads(); /* both stages free, counters zero */
-      if (threadIdx.x == 0)
+      /* a launch of at most NS operations (the single CLV updates of branch-length optimisation) keeps its
+       * matrices in the stages: loaded for the CTA's first chunk only */
+      const bool fresh = a.nops > NS || chunk == blockIdx.x;
+      if (threadIdx.x == 0 && fresh)
         for (unsigned int o = 0; o < NS && o < nseg; ++o)
         {
           double * dstm = s_mat + (size_t)o * 2 * mat_doubles;
@@ -767,8 +776,11 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
           }
         }
         __syncwarp(); /* children written by earlier operations of this warp are visible to all its lanes */
-        aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
-        ph ^= 1u << st;
+        if (fresh)
+        {
+          aa_mbar_wait(&s_bar[st], (ph >> st) & 1u);
+          ph ^= 1u << st;
+        }
         const double * sL = s_mat + (size_t)st * 2 * mat_doubles;
         const double * sR = sL + mat_doubles;
         const bool check = (flags & AOPF_PS) && !(look1 && look2);
