@@ -77,6 +77,8 @@ def pair(**kw):
     dict(tips=24, sites=400, states=20),                         # protein LG+G4, generic kernels
     dict(tips=70, sites=301, states=20, brlen_scale=14.0),       # protein, deep: DMMA kernel rescale pass
     dict(tips=9, sites=77, states=20, rate_cats=1),              # protein, single category, ragged tiles
+    dict(tips=6, sites=5, states=20),                            # protein Gamma4, less than one 8-site tile
+    dict(tips=11, sites=9, states=20, brlen_scale=14.0),         # one full tile + one site, rescaling
     dict(tips=20, sites=130, states=20, attributes=0),           # protein with tip CLVs (all inner-inner)
     dict(tips=40, sites=200, states=20, brlen_scale=14.0, attributes=ATTR_PATTERN_TIP | ATTR_RATE_SCALERS),
     dict(tips=12, sites=300, states=7, rate_cats=3),             # odd state count (padding)
