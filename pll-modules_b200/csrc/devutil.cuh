@@ -32,6 +32,15 @@ __device__ __forceinline__ void stg256(double * p, const d4 & r)
                : "memory");
 }
 
+/* same store with the streaming hint: the line is not expected to be read again (a parent CLV whose only reader takes
+ * it from registers), so L2 may write it back first */
+__device__ __forceinline__ void stg256_cs(double * p, const d4 & r)
+{
+  asm volatile("st.global.cs.v4.f64 [%0], {%1,%2,%3,%4};" ::"l"(p), "d"(r.x), "d"(r.y), "d"(r.z),
+               "d"(r.w)
+               : "memory");
+}
+
 /* ---- mbarrier / TMA bulk copy (PTX ISA: cp.async.bulk, mbarrier) ------------------------------ */
 __device__ __forceinline__ unsigned int smem_u32(const void * p)
 {

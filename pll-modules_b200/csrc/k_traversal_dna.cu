@@ -48,6 +48,7 @@ struct __align__(16) DevOp
 #define OPF_FWD2 64u
 #define OPF_FS1 128u  /* child-1 scaler is the previous op's parent scaler */
 #define OPF_FS2 256u
+#define OPF_STREAM 512u /* the parent is read by the next op only, out of registers: store it with the streaming hint */
 
 struct TravArgs
 {
@@ -386,7 +387,13 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
     for (int r = 0; r < R; ++r)
     {
       fw[r] = d4{out[r][0], out[r][1], out[r][2], out[r][3]};
-      if (FULL || ((actmask >> r) & 1u)) stg256(pdst + ESTEP * r, fw[r]);
+      if (FULL || ((actmask >> r) & 1u))
+      {
+        if (flags & OPF_STREAM)
+          stg256_cs(pdst + ESTEP * r, fw[r]);
+        else
+          stg256(pdst + ESTEP * r, fw[r]);
+      }
     }
 #pragma unroll
     for (int r = 0; r < R; ++r) fsc[r] = (flags & OPF_PS) ? sc[r] + ((scalemask >> r) & 1u) : 0u;
@@ -582,6 +589,7 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
         if (o.child1_scaler_index == q.parent_scaler_index) d.flags |= OPF_FS1;
         if (o.child2_scaler_index == q.parent_scaler_index) d.flags |= OPF_FS2;
       }
+      if ((d.flags & (OPF_FWD1 | OPF_FWD2)) && (g_opt_trav_prefetch & 4)) dops[i - 1].flags |= OPF_STREAM;
     }
   }
   /* same condition as the collect branch of launch_variant (default variant of K = 4) */
