@@ -48,7 +48,8 @@ struct __align__(16) DevOp
 #define OPF_FWD2 64u
 #define OPF_FS1 128u  /* child-1 scaler is the previous op's parent scaler */
 #define OPF_FS2 256u
-#define OPF_STREAM 512u /* the parent is read by the next op only, out of registers: store it with the streaming hint */
+#define OPF_STREAM 512u /* the parent is read by the next op only, out of registers: store it with the streaming hint
+                           (trav_prefetch bit 2; measured: no change, 29.2-29.3 ms either way) */
 
 struct TravArgs
 {
