@@ -68,6 +68,8 @@ static char cell_char(unsigned long long seed, unsigned int part, unsigned int t
       mix64(seed ^ mix64(((unsigned long long)part << 48) ^ ((unsigned long long)tip << 32) ^ site));
   const unsigned int r = (unsigned int)(h % 10000u);
   if (r < 500u) return '-';
+  /* seeds with bit 40 set: 3 % IUPAC ambiguity codes in DNA (multi-bit tip masks other than the gap) */
+  if (states == 4 && ((seed >> 40) & 1ull) && r < 800u) return "RYMKSWBDHV"[(h >> 24) % 10u];
   const unsigned int st = (unsigned int)((h >> 20) % states);
   if (states == 4) return ALPHABET_NT[st];
   if (states == 20) return ALPHABET_AA[st];

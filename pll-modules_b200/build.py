@@ -22,7 +22,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC,-Wall,-Wno-unused-function", "-Xptxas", "-v",
 ]
 
-CU_SOURCES = ["device_ctx.cu", "api_core.cu", "k_pmatrix.cu", "k_partials.cu", "k_traversal_dna.cu", "k_traversal_aa.cu","k_likelihood.cu",
+CU_SOURCES = ["device_ctx.cu", "api_core.cu", "k_pmatrix.cu", "k_partials.cu", "k_traversal_dna.cu", "k_traversal_dna4.cu", "trav_schedule.cpp", "k_traversal_aa.cu","k_likelihood.cu",
               "k_derivatives.cu", "k_newton.cu", "k_ancestral.cu", "binary_io.cpp", "host_model.cpp", "utree.cpp", "treeinfo.cpp", "optimize.cpp", "opt_algorithms.cpp", "opt_params.cpp", "algo_search.cpp", "algo_opt.cpp"]
 C_SOURCES = ["state_maps.c"]
 

@@ -70,6 +70,8 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "fuse_root")) slot = &g_opt_fuse_root;
   else if (!strcmp(name, "trav_variant")) slot = &g_opt_trav_variant;
   else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
+  else if (!strcmp(name, "trav_stash")) slot = &g_opt_trav_stash;
+  else if (!strcmp(name, "trav_debug")) slot = &g_opt_trav_debug;
   else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;
   else if (!strcmp(name, "queued_newton")) slot = &g_opt_queued_newton;
   else if (!strcmp(name, "trav_prefetch")) slot = &g_opt_trav_prefetch;
@@ -118,6 +120,7 @@ bool dev_ctx_init(PartCtx * c)
   c->eigen_stride = (size_t)2 * s * sp + 2 * sp;
 
   c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr; c->d_tiptab = nullptr; c->tiptab_stale = false;
+  c->d_pmat_cols = nullptr; c->d_tipcols = nullptr;
   c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
   c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->d_sumfrag = nullptr;
   c->d_multi = nullptr; c->multi_cap = 0; c->ev_batch = nullptr;
@@ -164,6 +167,9 @@ bool dev_ctx_init(PartCtx * c)
     {
       CUDA_TRY(cudaMalloc(&c->d_pmat_il, bytes), false);
       CUDA_TRY(cudaMemsetAsync(c->d_pmat_il, 0, bytes, c->stream), false);
+      const size_t cbytes = (size_t)p->prob_matrices * 5 * K * 4 * sizeof(double);
+      CUDA_TRY(cudaMalloc(&c->d_pmat_cols, cbytes), false);
+      CUDA_TRY(cudaMemsetAsync(c->d_pmat_cols, 0, cbytes, c->stream), false);
     }
     else if (s == 20)
     {
@@ -183,6 +189,11 @@ bool dev_ctx_init(PartCtx * c)
     CUDA_TRY(cudaMalloc(&c->d_tipchars, (size_t)p->tips * c->tip_stride), false);
     CUDA_TRY(cudaMemsetAsync(c->d_tipchars, s == 4 ? 15 : 0, (size_t)p->tips * c->tip_stride,
                              c->stream), false);
+    if (s == 4)
+    {
+      CUDA_TRY(cudaMalloc(&c->d_tipcols, (size_t)p->tips * c->tip_stride), false);
+      CUDA_TRY(cudaMemsetAsync(c->d_tipcols, 4, (size_t)p->tips * c->tip_stride, c->stream), false); /* code 15 = N */
+    }
     CUDA_TRY(cudaMalloc(&c->d_tipmap, 256 * sizeof(unsigned long long)), false);
     CUDA_TRY(cudaMemsetAsync(c->d_tipmap, 0, 256 * sizeof(unsigned long long), c->stream), false);
   }
@@ -228,6 +239,7 @@ void dev_ctx_destroy(PartCtx * c)
   for (auto & kv : c->sumtables) cudaFree(kv.second);
   c->sumtables.clear();
   cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il); cudaFree(c->d_tiptab);
+  cudaFree(c->d_pmat_cols); cudaFree(c->d_tipcols);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
   cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag);
   cudaFree(c->d_multi);
@@ -334,6 +346,7 @@ bool dev_sync_inputs(PartCtx * c)
       {
         if (!upload_big(c, c->d_tipchars + (size_t)t * c->tip_stride, p->tipchars[t], c->sites_alloc))
           return false;
+        if (!launch_tipcols_encode(c, t)) return false;
         c->tip_dirty[t] = 0;
       }
     c->any_tip_dirty = false;

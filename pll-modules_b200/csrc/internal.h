@@ -54,6 +54,10 @@ struct PartCtx
   unsigned int * d_scaler;
   double * d_pmat;
   double * d_pmat_il;         /* 4-state interleaved copy [i][k][j] for the DNA traversal kernel */
+  /* 4 states: per matrix the five column sums a DNA tip code selects, [m][A C G T N][cat k][row i] — what a tip
+   * child contributes to a parent, read by table lookup in k_traversal_dna4.cu */
+  double * d_pmat_cols;
+  unsigned char * d_tipcols;  /* twin of d_tipchars (4 states + tip patterns): column number of every code */
   /* 20 states + tip patterns: per matrix the products P x (tip state vector) of every tip code,
    * [prob_matrices][code 24][k][20] — the same K*480 doubles per matrix as the fragment image, so a tip
    * child's slot in the traversal kernel's shared memory holds this table instead (k_traversal_aa.cu) */
@@ -243,6 +247,13 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
 bool launch_pmatrix_reinterleave(PartCtx * c);
 bool launch_partials(PartCtx * c, const pll_operation_t * ops, unsigned int count);
 bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int count); /* k_traversal_dna.cu */
+/* k_traversal_dna4.cu: Gamma-4, per-site scalers — forwarding + shared-memory stash + tip column tables */
+bool lean_supported(const PartCtx * c);
+bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int count);
+bool flush_trav_dna4_lean(PartCtx * lead, const void * d_args, const BatchKind & k);
+bool launch_tipcols_encode(PartCtx * c, unsigned int tip);
+extern int g_opt_trav_stash;
+extern int g_opt_trav_debug;
 bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count);  /* k_traversal_aa.cu */
 bool launch_ancestral(PartCtx * c, unsigned int node_clv, int node_scaler, unsigned int other_clv,
                       int other_scaler, unsigned int matrix_index, const unsigned int * freqs_indices,

@@ -30,6 +30,7 @@
  */
 #include "internal.h"
 #include "devutil.cuh"
+#include "trav_schedule.h"
 
 #include <algorithm>
 
@@ -228,7 +229,10 @@ bool launch_partials(PartCtx * c, const pll_operation_t * ops_in, unsigned int c
   const unsigned int K = p->rate_cats;
   if (p->states == 4 && (K == 1 || K == 2 || K == 4 || K == 8))
   {
-    const pll_operation_t * ops = schedule_ops(c, ops_in, count);
+    /* Sethi-Ullman order (trav_schedule.cpp): what the forwarding + stash kernel wants; the other 4-state
+     * variants take the same order (it is depth-first too) */
+    const pll_operation_t * ops = ops_in;
+    if (g_opt_trav_reorder && trav_order_ops(ops_in, count, p->nodes, true, c->op_scratch)) ops = c->op_scratch.data();
     return launch_trav_dna(c, ops, count);
   }
 

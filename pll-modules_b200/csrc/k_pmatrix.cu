@@ -28,6 +28,8 @@ struct PmatArgs
   /* 20 states with tip patterns: also emit, per tip code c < 24, sum_{j in mask(c)} P[i][j] (internal.h) */
   double * tiptab;
   const unsigned long long * tipmap;
+  /* 4 states: also emit the column table of k_traversal_dna4.cu, [m][A C G T N][k][row i] */
+  double * cols;
 };
 
 #define PM_TIP_CODES 24
@@ -45,6 +47,23 @@ __device__ __forceinline__ void pmatrix_tip_rows(const double * out, double * ti
     for (unsigned int j = 0; j < 20; ++j)
       if ((mask >> j) & 1ull) v += out[i * sp + j];
     tab[(code * K + k) * 20 + i] = v;
+  }
+}
+
+/* column table of matrix (m, k): what a DNA tip code contributes to parent row i — the column of a
+ * single base, or for N the row sum added in state order like the masked sums of core_partials.c:290-351 */
+__device__ __forceinline__ void pmatrix_dna_cols(const double * out, double * cols, unsigned int m, unsigned int k,
+                                                 unsigned int K, unsigned int sp)
+{
+  if (threadIdx.x < 20)
+  {
+    const unsigned int c = threadIdx.x >> 2, i = threadIdx.x & 3u;
+    double v;
+    if (c < 4)
+      v = out[i * sp + c];
+    else
+      v = ((out[i * sp] + out[i * sp + 1]) + out[i * sp + 2]) + out[i * sp + 3];
+    cols[(((size_t)m * 5 + c) * K + k) * 4 + i] = v;
   }
 }
 
@@ -102,6 +121,11 @@ __device__ __forceinline__ void pmatrix_body(double * __restrict__ pmat, double 
   {
     __syncthreads(); /* `out` complete and visible to the whole CTA */
     pmatrix_tip_rows(out, a.tiptab, a.tipmap, m, k, K, sp);
+  }
+  if (a.cols && states == 4)
+  {
+    __syncthreads();
+    pmatrix_dna_cols(out, a.cols, m, k, K, sp);
   }
 }
 
@@ -169,6 +193,7 @@ bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, uns
   }
   a.tiptab = nullptr;
   a.tipmap = nullptr;
+  a.cols = c->d_pmat_cols;
   if (tiptab_usable(c))
   {
     if (!dev_sync_inputs(c)) return false;
@@ -191,7 +216,7 @@ bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, uns
  * checkpoint, binary_io.cpp): same index maps as pmatrix_kernel */
 __global__ void pmatrix_reinterleave_kernel(const double * __restrict__ pmat, double * __restrict__ pmat_il,
                                             unsigned int states, unsigned int sp, unsigned int K,
-                                            double * tiptab, const unsigned long long * tipmap)
+                                            double * tiptab, const unsigned long long * tipmap, double * cols)
 {
   const unsigned int m = blockIdx.x / K, k = blockIdx.x % K;
   const double * in = pmat + ((size_t)m * K + k) * states * sp;
@@ -208,6 +233,7 @@ __global__ void pmatrix_reinterleave_kernel(const double * __restrict__ pmat, do
     }
   }
   if (tiptab && states == 20) pmatrix_tip_rows(in, tiptab, tipmap, m, k, K, sp);
+  if (cols && states == 4) pmatrix_dna_cols(in, cols, m, k, K, sp);
 }
 
 bool launch_pmatrix_reinterleave(PartCtx * c)
@@ -218,7 +244,7 @@ bool launch_pmatrix_reinterleave(PartCtx * c)
   c->tiptab_stale = false;
   pmatrix_reinterleave_kernel<<<p->prob_matrices * p->rate_cats, 128, 0, xstream(c)>>>(
       c->d_pmat, c->d_pmat_il, p->states, p->states_padded, p->rate_cats, tiptab_usable(c) ? c->d_tiptab : nullptr,
-      c->d_tipmap);
+      c->d_tipmap, c->d_pmat_cols);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "pmatrix_reinterleave_kernel launch");
 }
@@ -243,6 +269,7 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
   }
   a.tiptab = nullptr;
   a.tipmap = nullptr;
+  a.cols = c->d_pmat_cols;
   if (tiptab_usable(c))
   {
     if (!dev_sync_inputs(c)) return false;

@@ -461,18 +461,6 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArg
   trav_dna_body<K, R, RATE_SCALERS, MINB, 0>(a);
 }
 
-/* many partitions in one launch (blockIdx.y = partition; batch mode, internal.h) */
-template <int K, int R, bool RATE_SCALERS, int MINB>
-__global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_batch_kernel(const TravArgs * __restrict__ arr)
-{
-  __shared__ TravArgs sa;
-  for (unsigned int i = threadIdx.x; i < sizeof(TravArgs) / 4; i += blockDim.x)
-    reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
-  __syncthreads();
-  const TravArgs a = sa; /* by value like the plain kernel (the out-of-line tail takes its address) */
-  trav_dna_body<K, R, RATE_SCALERS, MINB, 1>(a);
-}
-
 /* ---- host ------------------------------------------------------------------------------------ */
 
 int g_opt_trav_variant = 0;
@@ -499,11 +487,6 @@ static bool launch_variant(PartCtx * c, const TravArgs & a)
   const unsigned long long cap = (unsigned long long)c->sm_count * per_sm;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  if (batch_collects(BK_TRAV_DNA4) && g_opt_trav_variant == 0 && K == 4 && R == 4 && !RS && MINB == 2)
-  {
-    batch_collect(BK_TRAV_DNA4, &a, sizeof(a), (unsigned int)blocks, 0);
-    return true;
-  }
   trav_dna_kernel<K, R, RS, MINB><<<(unsigned int)blocks, TRAV_WARPS * 32, 0, xstream(c)>>>(a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_dna_kernel launch");
@@ -535,6 +518,10 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
   const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
   const bool rate_scalers = (p->attributes & PLL_ATTRIB_RATE_SCALERS) != 0;
   const unsigned int K = p->rate_cats;
+
+  /* Gamma-4 with per-site scalers: the forwarding + stash kernel (variant 0, the default); the kernel
+   * below stays for other category counts, per-rate scalers and as the bit-for-bit cross-check */
+  if (g_opt_trav_variant == 0 && lean_supported(c)) return launch_trav_dna4(c, ops, count);
 
   static_assert(sizeof(DevOp) == 64, "DevOp is 8 x u64");
   c->devop_scratch.resize((size_t)count * 8);
@@ -593,10 +580,7 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
       if ((d.flags & (OPF_FWD1 | OPF_FWD2)) && (g_opt_trav_prefetch & 4)) dops[i - 1].flags |= OPF_STREAM;
     }
   }
-  /* same condition as the collect branch of launch_variant (default variant of K = 4) */
-  const bool collect = batch_collects(BK_TRAV_DNA4) && K == 4 && !rate_scalers && g_opt_trav_variant == 0;
-  const DevOp * d_ops = collect ? (const DevOp *)batch_pool_add(dops, sizeof(DevOp) * count)
-                                : (const DevOp *)dev_stage_small(c, dops, sizeof(DevOp) * count);
+  const DevOp * d_ops = (const DevOp *)dev_stage_small(c, dops, sizeof(DevOp) * count);
   if (!d_ops) return false;
   TravArgs a;
   a.ops = d_ops;
@@ -616,10 +600,8 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
   }
 }
 
+/* batch mode collects Gamma-4 partitions on the lean kernel only (k_traversal_dna4.cu) */
 bool flush_trav_dna4(PartCtx * lead, const void * d_args, const BatchKind & k)
 {
-  trav_dna_batch_kernel<4, 4, false, 2><<<dim3(batch_grid_x(lead, k, 2), k.count), TRAV_WARPS * 32, 0, lead->stream>>>(
-      static_cast<const TravArgs *>(d_args));
-  ++g_kernel_launches;
-  return pllb200_cuda_ok(cudaGetLastError(), "batched trav_dna kernel launch");
+  return flush_trav_dna4_lean(lead, d_args, k);
 }

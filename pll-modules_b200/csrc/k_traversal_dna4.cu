@@ -1,0 +1,773 @@
+/*
+ * k_traversal_dna4.cu — the 4-state, Gamma-4, per-site-scaler traversal kernel ("lean" site-column kernel).
+ *
+ * Same contract as k_traversal_dna.cu (pll_update_partials, partials.c:237-291; core kernels
+ * core_partials.c:48-200,202-351,612-764,1013-1210): one launch evaluates a whole operation list, a warp
+ * owns 32 consecutive sites (lane = (group of 4 consecutive sites, rate category)) and walks the list
+ * for them.  What differs is where operands come from — the round-1 kernel was bound by the latency
+ * chain of an operation (ncu: issue slots 50 % busy at 16 warps/SM, long_scoreboard 32 %), not by DRAM:
+ *
+ *   - NO inner child is read back from L1/L2 in the common case.  The host orders the list Sethi-Ullman
+ *     style (trav_schedule.cpp) and tells every operation where each child lives: in the registers that
+ *     still hold the previous operation's parent, or in one of two per-warp shared-memory stash slots
+ *     (4 KB each) that its producer filled next to the global store.  Subtrees of Strahler number <= 3
+ *     (all but a handful of operations of a 1000-taxon tree) never load a CLV; the rest, and children
+ *     computed by earlier launches, come from global memory as before.  Scaler counts travel the same way.
+ *   - tip children never touch the FP64 pipe: the P-matrix kernel also writes, per matrix, the five
+ *     column sums a DNA tip code can select ([A, C, G, T, N][cat][row], 640 B), the tip arena has a
+ *     twin that holds the column number of every code, and a tip term is two 128-bit shared-memory reads
+ *     (rare ambiguity codes add their columns in state order, which is what the masked row sum of
+ *     core_partials.c:290-351 does).  The table of a tip child takes the place of its matrix in the
+ *     TMA-staged ring.
+ *   - operations are 32-byte records of ROW indices; every address is one IMAD.WIDE from a per-lane base.
+ *   - the accumulator is updated in place: acc = R x child2 (child2 is loaded INTO acc, or is already there
+ *     when forwarded), then acc *= L x child1: no copy between operations, ~100 live registers.
+ *   - the scaling vote leaves early when no lane of the warp saw an element below 2^-256.
+ * Arithmetic per element is the same expression as the round-1 kernel (bit-identical results).
+ *
+ * HBM traffic per site and operation: 128 B CLV + 4 B scaler written, 0-1 B tip codes read; everything
+ * else is on chip.  Bound: DRAM writes.
+ */
+#include "internal.h"
+#include "devutil.cuh"
+#include "trav_schedule.h"
+
+#include <algorithm>
+
+struct LeanArgs
+{
+  const LeanOp * ops; /* MUST stay first (batch pool token, device_ctx.cu) */
+  unsigned int nops;
+  unsigned int sites; /* sites_alloc */
+  unsigned int seg;   /* operations per staged segment */
+  unsigned int tip_stride;
+  char * clv;
+  char * scaler;
+  const double * pmat_il;   /* [m][row i][cat k][col j] : 512 B per matrix */
+  const double * pmat_cols; /* [m][column c 0..4][cat k][row i] : 640 B per matrix */
+  const unsigned char * tipcols;
+  unsigned int clv_stride_b, scaler_stride_b; /* row strides in bytes (< 4 GB: lean_supported) */
+  unsigned int dbg; /* timing ablations only (option trav_debug): 1 no tip loads, 2 no CLV stores, 4 no scaler stores */
+};
+
+#define L4_WARPS 8
+#define L4_SEG_MAX 512
+#define L4_STASH_B 4096u
+#define L4_WARP_SM (2 * L4_STASH_B + 2 * 128 + 2 * 2 * 640 + 16 + 112) /* stash | scaler stash | matrices | barriers | pad -> 11136 */
+#define L4_OFF_SST (2 * L4_STASH_B)
+#define L4_OFF_MAT (L4_OFF_SST + 256)
+#define L4_OFF_BAR (L4_OFF_MAT + 2560)
+
+static_assert(L4_WARP_SM % 128 == 0, "per-warp shared memory block keeps 128-byte alignment");
+
+__device__ __forceinline__ double2 lds_d2(unsigned int addr)
+{
+  double2 v;
+  asm volatile("ld.shared.v2.f64 {%0,%1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_d2(unsigned int addr, double x, double y)
+{
+  asm volatile("st.shared.v2.f64 [%0], {%1,%2};" ::"r"(addr), "d"(x), "d"(y) : "memory");
+}
+__device__ __forceinline__ uint4 lds_u4(unsigned int addr)
+{
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ uint2 lds_u2(unsigned int addr)
+{
+  uint2 v;
+  asm volatile("ld.shared.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ unsigned int lds_u1(unsigned int addr)
+{
+  unsigned int v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts_u4(unsigned int addr, const uint4 & v)
+{
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void cp_async16(unsigned int dst, const void * src)
+{
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+__device__ __forceinline__ void mbar_wait_u32(unsigned int bar, unsigned int parity)
+{
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar),
+      "r"(parity)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_u32(unsigned int dst, const void * src, unsigned int bytes, unsigned int bar)
+{
+  asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_expect_u32(unsigned int bar, unsigned int bytes)
+{
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+
+/* signed compare on the high word: x < 2^-256 for every non-NaN x, negative values (round-off in a
+ * P-matrix) included, as the reference's `x < PLL_SCALE_THRESHOLD` (core_partials.c:729-763) */
+#define L4_THRESHOLD_HI 0x2FF00000
+__device__ __forceinline__ int hi_s(double x) { return __double2hiint(x); }
+
+/* term of a tip child for one element: column `b` of the staged table (b < 5), or — ambiguity codes other
+ * than N, flagged 0x80 — the sum of the columns of the code's bits in state order */
+template <bool SLOW>
+__device__ __forceinline__ void tip_term(unsigned int tab_k, unsigned int b, double (&t)[4])
+{
+  if (SLOW && (b & 0x80u))
+  {
+    t[0] = t[1] = t[2] = t[3] = 0.0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if ((b >> j) & 1u)
+      {
+        const double2 a = lds_d2(tab_k + j * 128), c = lds_d2(tab_k + j * 128 + 16);
+        t[0] += a.x;
+        t[1] += a.y;
+        t[2] += c.x;
+        t[3] += c.y;
+      }
+    return;
+  }
+  const double2 a = lds_d2(tab_k + b * 128), c = lds_d2(tab_k + b * 128 + 16);
+  t[0] = a.x;
+  t[1] = a.y;
+  t[2] = c.x;
+  t[3] = c.y;
+}
+
+/* acc[r] <- M_k x acc[r] for the 4 elements of the lane; M staged as [row i][cat k][col j] */
+__device__ __forceinline__ void transform_inplace(unsigned int mat_k, double (&acc)[4][4])
+{
+  double2 ma[4], mb[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+  {
+    ma[i] = lds_d2(mat_k + i * 128);
+    mb[i] = lds_d2(mat_k + i * 128 + 16);
+  }
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+  {
+    double t[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      t[i] = ma[i].x * acc[r][0] + ma[i].y * acc[r][1] + mb[i].x * acc[r][2] + mb[i].y * acc[r][3];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[r][i] = t[i];
+  }
+}
+
+/* acc[r][i] <- (M_k[i,:] . v[r]) * acc[r][i] */
+__device__ __forceinline__ void multiply_by_term(unsigned int mat_k, const double (&v)[4][4], double (&acc)[4][4])
+{
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+  {
+    const double2 la = lds_d2(mat_k + i * 128), lb = lds_d2(mat_k + i * 128 + 16);
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+    {
+      const double xl = la.x * v[r][0] + la.y * v[r][1] + lb.x * v[r][2] + lb.y * v[r][3];
+      acc[r][i] = xl * acc[r][i];
+    }
+  }
+}
+
+/* per-lane constants of one chunk: as few registers as possible, everything else is derived where it is used */
+struct LaneCtx
+{
+  unsigned int s0;      /* first of the lane's 4 consecutive sites */
+  unsigned int clv_off; /* byte offset of element (s0, k) inside a CLV: (s0 * 4 + k) * 32 (< 4 GB: lean_supported) */
+  unsigned int wsm;     /* this warp's shared-memory block (shared-window address) */
+  unsigned int lane, actmask;
+  __device__ __forceinline__ unsigned int k() const { return lane & 3u; }
+  __device__ __forceinline__ bool sc_lane() const { return (lane & 3u) == 0; }
+  __device__ __forceinline__ unsigned int stash_lane() const { return wsm + lane * 16; }
+  __device__ __forceinline__ unsigned int sst_lane() const { return wsm + L4_OFF_SST + (lane >> 2) * 16; }
+  __device__ __forceinline__ unsigned int mat_lane() const { return wsm + L4_OFF_MAT + lane * 16; }
+  __device__ __forceinline__ unsigned int mat_k(unsigned int st) const { return wsm + L4_OFF_MAT + st * 1280 + (lane & 3u) * 32; }
+};
+__device__ __forceinline__ char * lean_clv_ptr(const LeanArgs & a, const LaneCtx & L, unsigned int row)
+{
+  return a.clv + ((unsigned long long)row * a.clv_stride_b + L.clv_off);
+}
+__device__ __forceinline__ unsigned int * lean_scaler_ptr(const LeanArgs & a, const LaneCtx & L, unsigned int row)
+{
+  return reinterpret_cast<unsigned int *>(a.scaler + ((unsigned long long)row * a.scaler_stride_b + L.s0 * 4u));
+}
+
+template <bool FULL>
+__device__ __forceinline__ unsigned int lean_load_tips(const LeanArgs & a, const LaneCtx & L, unsigned int tip)
+{
+  const unsigned char * p = a.tipcols + ((unsigned long long)tip * a.tip_stride + L.s0);
+  if (a.dbg & 1u) return 0u;
+  if (FULL) return __ldg(reinterpret_cast<const unsigned int *>(p));
+  unsigned int t = 0;
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+    if ((L.actmask >> r) & 1u) t |= (unsigned int)__ldg(p + r) << (8 * r);
+  return t;
+}
+
+template <bool FULL>
+__device__ __forceinline__ uint4 lean_load_scalers(const LeanArgs & a, const LaneCtx & L, unsigned int row)
+{
+  const unsigned int * p = lean_scaler_ptr(a, L, row);
+  if (FULL) return *reinterpret_cast<const uint4 *>(p);
+  uint4 q = make_uint4(0, 0, 0, 0);
+  if (L.actmask & 1u) q.x = p[0];
+  if (L.actmask & 2u) q.y = p[1];
+  if (L.actmask & 4u) q.z = p[2];
+  if (L.actmask & 8u) q.w = p[3];
+  return q;
+}
+
+/* Matrices (or tip column tables) and tip codes of the operation whose record sits at `rec`, into stage `st`:
+ * 16-byte cp.async by all lanes (512 B = one per lane; the fifth column of a tip table is 128 B more from
+ * lanes 0-7), one commit group per call.  Straight-line (selects and predicated copies, no branch), so that
+ * it can be scheduled into the arithmetic of the current operation.  [A per-warp TMA bulk copy cost ~80 issue
+ * slots per operation: address set-up plus the elect / R2UR sequence around each UBLKCP.] */
+template <bool FULL>
+__device__ __forceinline__ void lean_prefetch(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
+                                              unsigned int & n1, unsigned int & n2)
+{
+  const uint4 x0 = lds_u4(rec), x1 = lds_u4(rec + 16);
+  const unsigned int fn = x1.z >> 24;
+  const bool t1 = LOPA_SRC1(fn) == SRC_TIP, t2 = LOPA_SRC2(fn) == SRC_TIP;
+  const char * cols = reinterpret_cast<const char *>(a.pmat_cols) + L.lane * 16;
+  const char * rows = reinterpret_cast<const char *>(a.pmat_il) + L.lane * 16;
+  const char * g1 = (t1 ? cols : rows) + (unsigned long long)(x1.z & LOP_MATRIX_MASK) * (t1 ? 640u : 512u);
+  const char * g2 = (t2 ? cols : rows) + (unsigned long long)(x1.w & LOP_MATRIX_MASK) * (t2 ? 640u : 512u);
+  const unsigned int dst = L.mat_lane() + st * 1280;
+  cp_async16(dst, g1);
+  cp_async16(dst + 640, g2);
+  if (t1 && L.lane < 8) cp_async16(dst + 512, g1 + 512);
+  if (t2 && L.lane < 8) cp_async16(dst + 640 + 512, g2 + 512);
+  cp_async_commit();
+  n1 = 0;
+  n2 = 0;
+  if (t1) n1 = lean_load_tips<FULL>(a, L, x0.y);
+  if (t2) n2 = lean_load_tips<FULL>(a, L, x0.z);
+}
+
+/* underflow scaling vote (core_partials.c:729-763; never for tip-tip: :185-186), scaler counts, global store,
+ * stash.  sc: sum of the children's counts (sc lanes).  w0 = {p, c1, c2, ps}. */
+template <bool FULL, bool TIPTIP>
+__device__ __forceinline__ void lean_finish(const LeanArgs & a, const LaneCtx & L, const uint4 & w0, unsigned int fa,
+                                            unsigned int fb, double (&acc)[4][4], uint4 sc, uint4 & fsc)
+{
+  if (fa & LOPA_PS)
+  {
+    if (!TIPTIP)
+    {
+      unsigned int scalemask = 0;
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+      {
+        const int m = max(max(hi_s(acc[r][0]), hi_s(acc[r][1])), max(hi_s(acc[r][2]), hi_s(acc[r][3])));
+        if (m < L4_THRESHOLD_HI) scalemask |= 1u << r;
+      }
+      if (__any_sync(0xffffffffu, scalemask != 0u))
+      {
+        scalemask &= __shfl_xor_sync(0xffffffffu, scalemask, 1);
+        scalemask &= __shfl_xor_sync(0xffffffffu, scalemask, 2);
+        if (scalemask)
+        {
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+            if ((scalemask >> r) & 1u)
+            {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) acc[r][i] *= SCALE_FACTOR_D;
+            }
+          sc.x += scalemask & 1u;
+          sc.y += (scalemask >> 1) & 1u;
+          sc.z += (scalemask >> 2) & 1u;
+          sc.w += (scalemask >> 3) & 1u;
+        }
+      }
+    }
+    if (L.sc_lane() && !(a.dbg & 4u))
+    {
+      unsigned int * ps = lean_scaler_ptr(a, L, w0.w);
+      if (FULL)
+        *reinterpret_cast<uint4 *>(ps) = sc;
+      else
+      {
+        if (L.actmask & 1u) ps[0] = sc.x;
+        if (L.actmask & 2u) ps[1] = sc.y;
+        if (L.actmask & 4u) ps[2] = sc.z;
+        if (L.actmask & 8u) ps[3] = sc.w;
+      }
+    }
+    fsc = sc;
+  }
+  else
+    fsc = make_uint4(0, 0, 0, 0);
+
+  double * pdst = reinterpret_cast<double *>(lean_clv_ptr(a, L, w0.x));
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+    if ((FULL || ((L.actmask >> r) & 1u)) && !(a.dbg & 2u)) stg256(pdst + 16 * r, d4{acc[r][0], acc[r][1], acc[r][2], acc[r][3]});
+  if (fa & LOPA_STASH_W)
+  {
+    const unsigned int ws = LOPB_WSLOT(fb);
+    const unsigned int sl = L.stash_lane() + ws * L4_STASH_B;
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+    {
+      sts_d2(sl + r * 1024, acc[r][0], acc[r][1]);
+      sts_d2(sl + r * 1024 + 512, acc[r][2], acc[r][3]);
+    }
+    if (L.sc_lane()) sts_u4(L.sst_lane() + ws * 128, fsc);
+  }
+}
+
+__device__ __forceinline__ void lean_stash_read(unsigned int sl, double (&v)[4][4])
+{
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+  {
+    const double2 x = lds_d2(sl + r * 1024), y = lds_d2(sl + r * 1024 + 512);
+    v[r][0] = x.x;
+    v[r][1] = x.y;
+    v[r][2] = y.x;
+    v[r][3] = y.y;
+  }
+}
+
+__device__ __forceinline__ void lean_tip_assign(unsigned int tab, unsigned int t, bool slow, double (&acc)[4][4])
+{
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+  {
+    if (slow)
+      tip_term<true>(tab, (t >> (8 * r)) & 0xffu, acc[r]);
+    else
+      tip_term<false>(tab, (t >> (8 * r)) & 0xffu, acc[r]);
+  }
+}
+__device__ __forceinline__ void lean_tip_multiply(unsigned int tab, unsigned int t, bool slow, double (&acc)[4][4])
+{
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+  {
+    double x[4];
+    if (slow)
+      tip_term<true>(tab, (t >> (8 * r)) & 0xffu, x);
+    else
+      tip_term<false>(tab, (t >> (8 * r)) & 0xffu, x);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) acc[r][i] = x[i] * acc[r][i];
+  }
+}
+
+/* One operation whose operand sources are compile-time constants: one basic block from the record read to the
+ * scaling vote, so that ptxas overlaps the next operation's prefetch, the scaler traffic and the shared-memory
+ * reads with the FP64 chains (the round-2 ncu capture of the all-runtime version: 49 branches per operation,
+ * issue slots 34 % busy, a ~2700-cycle dependent chain per operation).  Preconditions checked by the host
+ * (LOPB_TYPE != 0): the parent has a scaler row; scaler counts of a child come from where its CLV comes from;
+ * full chunk; no ambiguity code other than N in the tip codes (checked here: `slow` runs the generic body). */
+template <int SRC1, int SRC2>
+__device__ __forceinline__ void lean_op_hot(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
+                                            double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+{
+  const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
+  const unsigned int fa = w1.z >> 24, fb = w1.w >> 24;
+  unsigned int n1, n2;
+  lean_prefetch<true>(a, L, rec + 32, st ^ 1u, n1, n2);
+
+  uint4 q1 = make_uint4(0, 0, 0, 0), q2 = make_uint4(0, 0, 0, 0);
+  if (L.sc_lane())
+  {
+    if (SRC1 == SRC_STASH) q1 = lds_u4(L.sst_lane() + LOPA_SLOT1(fa) * 128);
+    if (SRC1 == SRC_GLOBAL) q1 = lean_load_scalers<true>(a, L, w1.x);
+    if (SRC2 == SRC_FWD) q2 = fsc;
+    if (SRC2 == SRC_STASH) q2 = lds_u4(L.sst_lane() + LOPA_SLOT2(fa) * 128);
+    if (SRC2 == SRC_GLOBAL) q2 = lean_load_scalers<true>(a, L, w1.y);
+  }
+  /* child 1 from global memory: ask L1 for its lines now (no register), read them after child 2's term */
+  if (SRC1 == SRC_GLOBAL)
+  {
+    const char * p1 = lean_clv_ptr(a, L, w0.y);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) asm volatile("prefetch.global.L1 [%0];" ::"l"(p1 + 128 * r));
+  }
+  if (SRC2 == SRC_GLOBAL)
+  {
+    const double * p2 = reinterpret_cast<const double *>(lean_clv_ptr(a, L, w0.z));
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+    {
+      const d4 v = ldg256(p2 + 16 * r);
+      acc[r][0] = v.x;
+      acc[r][1] = v.y;
+      acc[r][2] = v.z;
+      acc[r][3] = v.w;
+    }
+  }
+  if (SRC2 == SRC_STASH) lean_stash_read(L.stash_lane() + LOPA_SLOT2(fa) * L4_STASH_B, acc);
+
+  const unsigned int matL = L.mat_k(st), matR = matL + 640;
+  cp_async_wait1(); /* this operation's matrices have landed (the next one's may be in flight) ... */
+  __syncwarp();     /* ... for every lane's part of them */
+  if (SRC2 == SRC_TIP)
+    lean_tip_assign(matR, t2, false, acc);
+  else
+    transform_inplace(matR, acc);
+  if (SRC1 == SRC_TIP)
+    lean_tip_multiply(matL, t1, false, acc);
+  else
+  {
+    double v1[4][4];
+    if (SRC1 == SRC_STASH)
+      lean_stash_read(L.stash_lane() + LOPA_SLOT1(fa) * L4_STASH_B, v1);
+    else
+    {
+      const double * p1 = reinterpret_cast<const double *>(lean_clv_ptr(a, L, w0.y));
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+      {
+        const d4 v = ldg256(p1 + 16 * r);
+        v1[r][0] = v.x;
+        v1[r][1] = v.y;
+        v1[r][2] = v.z;
+        v1[r][3] = v.w;
+      }
+    }
+    multiply_by_term(matL, v1, acc);
+  }
+
+  const uint4 sc = make_uint4(q1.x + q2.x, q1.y + q2.y, q1.z + q2.z, q1.w + q2.w);
+  lean_finish<true, SRC1 == SRC_TIP && SRC2 == SRC_TIP>(a, L, w0, fa | LOPA_PS, fb, acc, sc, fsc);
+  t1 = n1;
+  t2 = n2;
+}
+
+/* any operation: sources, scaler sources and flags read at run time */
+template <bool FULL>
+__device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
+                                                double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+{
+  const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
+  const unsigned int fa = w1.z >> 24, fb = w1.w >> 24;
+  const unsigned int src1 = LOPA_SRC1(fa), src2 = LOPA_SRC2(fa);
+  unsigned int n1, n2;
+  lean_prefetch<FULL>(a, L, rec + 32, st ^ 1u, n1, n2);
+
+  uint4 q1 = make_uint4(0, 0, 0, 0), q2 = make_uint4(0, 0, 0, 0);
+  if ((fa & LOPA_PS) && L.sc_lane())
+  {
+    const unsigned int ss1 = LOPB_SS1(fb), ss2 = LOPB_SS2(fb);
+    if (ss1 == SSRC_GLOBAL)
+      q1 = lean_load_scalers<FULL>(a, L, w1.x);
+    else if (ss1 == SSRC_SAME)
+      q1 = lds_u4(L.sst_lane() + LOPA_SLOT1(fa) * 128); /* child 1 is never forwarded */
+    if (ss2 == SSRC_GLOBAL)
+      q2 = lean_load_scalers<FULL>(a, L, w1.y);
+    else if (ss2 == SSRC_SAME)
+      q2 = src2 == SRC_FWD ? fsc : lds_u4(L.sst_lane() + LOPA_SLOT2(fa) * 128);
+  }
+  const unsigned int matL = L.mat_k(st), matR = matL + 640;
+  const bool slow = __any_sync(0xffffffffu, ((t1 | t2) & 0x80808080u) != 0u);
+
+  /* ---- acc <- term of child 2 ---- */
+  if (src2 == SRC_GLOBAL)
+  {
+    const double * p2 = reinterpret_cast<const double *>(lean_clv_ptr(a, L, w0.z));
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+      if (FULL || ((L.actmask >> r) & 1u))
+      {
+        const d4 v = ldg256(p2 + 16 * r);
+        acc[r][0] = v.x;
+        acc[r][1] = v.y;
+        acc[r][2] = v.z;
+        acc[r][3] = v.w;
+      }
+  }
+  else if (src2 == SRC_STASH)
+    lean_stash_read(L.stash_lane() + LOPA_SLOT2(fa) * L4_STASH_B, acc);
+  cp_async_wait1();
+  __syncwarp();
+  if (src2 == SRC_TIP)
+    lean_tip_assign(matR, t2, slow, acc);
+  else
+    transform_inplace(matR, acc);
+
+  const uint4 sc = make_uint4(q1.x + q2.x, q1.y + q2.y, q1.z + q2.z, q1.w + q2.w);
+
+  /* ---- acc *= term of child 1 ---- */
+  if (src1 == SRC_TIP)
+    lean_tip_multiply(matL, t1, slow, acc);
+  else
+  {
+    double v1[4][4];
+    if (src1 == SRC_STASH)
+      lean_stash_read(L.stash_lane() + LOPA_SLOT1(fa) * L4_STASH_B, v1);
+    else
+    {
+      const double * p1 = reinterpret_cast<const double *>(lean_clv_ptr(a, L, w0.y));
+#pragma unroll
+      for (int r = 0; r < 4; ++r)
+      {
+        d4 v = d4{0.0, 0.0, 0.0, 0.0};
+        if (FULL || ((L.actmask >> r) & 1u)) v = ldg256(p1 + 16 * r);
+        v1[r][0] = v.x;
+        v1[r][1] = v.y;
+        v1[r][2] = v.z;
+        v1[r][3] = v.w;
+      }
+    }
+    multiply_by_term(matL, v1, acc);
+  }
+  if (src1 == SRC_TIP && src2 == SRC_TIP)
+    lean_finish<FULL, true>(a, L, w0, fa, fb, acc, sc, fsc);
+  else
+    lean_finish<FULL, false>(a, L, w0, fa, fb, acc, sc, fsc);
+  t1 = n1;
+  t2 = n2;
+}
+
+/* One chunk (32 consecutive sites) through the staged operations [0, nseg); the record after the last one is
+ * all zero (a harmless prefetch target).  wsm: this warp's shared-memory block (shared-window address), s0:
+ * first of the lane's 4 consecutive sites.  FULL: all 32 sites exist — only then the specialised bodies run. */
+template <bool FULL>
+__device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops, unsigned int nseg, unsigned int s0,
+                                           int lane, unsigned int wsm)
+{
+  LaneCtx L;
+  L.lane = (unsigned int)lane;
+  L.s0 = s0;
+  L.clv_off = (s0 * 4u + (lane & 3u)) * 32u;
+  L.wsm = wsm;
+  L.actmask = 0xfu;
+  if (!FULL)
+  {
+    L.actmask = 0;
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+      if (s0 + r < a.sites) L.actmask |= 1u << r;
+  }
+
+  double acc[4][4]; /* [element r][state i]: the parent of the previous operation when an operation starts */
+#pragma unroll
+  for (int r = 0; r < 4; ++r) acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.0;
+  uint4 fsc = make_uint4(0, 0, 0, 0); /* ... and its scaler counts (sc lanes) */
+  unsigned int t1, t2;                /* packed tip column codes of the CURRENT operation */
+
+  __syncwarp();
+  lean_prefetch<FULL>(a, L, sops, 0, t1, t2);
+
+  /* the loop variable is the record's shared-memory address (records are 32 bytes: bit 5 = stage) */
+  const unsigned int rec_end = sops + nseg * 32;
+  for (unsigned int rec = sops; rec != rec_end; rec += 32)
+  {
+    const unsigned int st = ((rec - sops) >> 5) & 1u;
+    __syncwarp(); /* every lane is done with stage st^1 (previous operation): the bodies refill it for the next one */
+    unsigned int type = 0;
+    if (FULL)
+    {
+      type = LOPB_TYPE(lds_u1(rec + 28) >> 24);
+      if (__any_sync(0xffffffffu, ((t1 | t2) & 0x80808080u) != 0u)) type = 0; /* ambiguity codes: generic body */
+    }
+    switch (type)
+    {
+      case LTYPE_TIP_TIP: lean_op_hot<SRC_TIP, SRC_TIP>(a, L, rec, st, acc, fsc, t1, t2); break;
+      case LTYPE_TIP_FWD: lean_op_hot<SRC_TIP, SRC_FWD>(a, L, rec, st, acc, fsc, t1, t2); break;
+      case LTYPE_STASH_FWD: lean_op_hot<SRC_STASH, SRC_FWD>(a, L, rec, st, acc, fsc, t1, t2); break;
+      case LTYPE_GLOBAL_FWD: lean_op_hot<SRC_GLOBAL, SRC_FWD>(a, L, rec, st, acc, fsc, t1, t2); break;
+      case LTYPE_TIP_GLOBAL: lean_op_hot<SRC_TIP, SRC_GLOBAL>(a, L, rec, st, acc, fsc, t1, t2); break;
+      case LTYPE_GLOBAL_GLOBAL: lean_op_hot<SRC_GLOBAL, SRC_GLOBAL>(a, L, rec, st, acc, fsc, t1, t2); break;
+      default: lean_op_generic<FULL>(a, L, rec, st, acc, fsc, t1, t2); break;
+    }
+  }
+}
+
+template <int TAG>
+__device__ __noinline__ void lean_chunk_tail(const LeanArgs & a, unsigned int sops, unsigned int nseg, unsigned int s0,
+                                             int lane, unsigned int wsm)
+{
+  lean_chunk<false>(a, sops, nseg, s0, lane, wsm);
+}
+
+template <int TAG>
+__device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
+{
+  extern __shared__ __align__(128) unsigned char l4_smem[];
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const unsigned int sm0 = smem_u32(l4_smem);
+  const unsigned int sops = sm0;
+  const unsigned int wsm = sm0 + (a.seg + 4) * 32 + warp * L4_WARP_SM; /* + the zero record, 128-byte aligned */
+  const unsigned long long nchunks = ((unsigned long long)a.sites + 31) / 32;
+  const unsigned long long gwarp = (unsigned long long)blockIdx.x * L4_WARPS + warp;
+  const unsigned long long nwarps = (unsigned long long)gridDim.x * L4_WARPS;
+
+
+  for (unsigned int seg = 0; seg < a.nops; seg += a.seg)
+  {
+    const unsigned int nseg = min(a.nops - seg, a.seg);
+    __syncthreads(); /* previous segment fully consumed by every warp of the CTA */
+    {
+      const uint4 * src = reinterpret_cast<const uint4 *>(a.ops + seg);
+      for (unsigned int i = threadIdx.x; i < nseg * 2; i += blockDim.x) sts_u4(sops + i * 16, __ldg(src + i));
+      if (threadIdx.x < 2) sts_u4(sops + (nseg * 2 + threadIdx.x) * 16, make_uint4(0, 0, 0, 0)); /* prefetch target of the last operation */
+    }
+    __syncthreads();
+    for (unsigned long long chunk = gwarp; chunk < nchunks; chunk += nwarps)
+    {
+      const unsigned int s0 = (unsigned int)(chunk * 32) + (unsigned int)(lane >> 2) * 4;
+      if ((chunk + 1) * 32 <= a.sites)
+        lean_chunk<true>(a, sops, nseg, s0, lane, wsm);
+      else
+        lean_chunk_tail<TAG>(a, sops, nseg, s0, lane, wsm);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_kernel(LeanArgs a) { trav_dna4_body<0>(a); }
+
+/* many partitions in one launch (blockIdx.y = partition; batch mode, internal.h) */
+__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_batch_kernel(const LeanArgs * __restrict__ arr)
+{
+  __shared__ LeanArgs sa;
+  for (unsigned int i = threadIdx.x; i < sizeof(LeanArgs) / 4; i += blockDim.x)
+    reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
+  __syncthreads();
+  const LeanArgs a = sa;
+  trav_dna4_body<1>(a);
+}
+
+/* ---- tip column codes ---------------------------------------------------------------------------- */
+
+/* 4-bit DNA code -> column of the table: A C G T -> 0..3, N (all four) -> 4, anything else -> 0x80 | code */
+__global__ void tipcols_encode_kernel(const unsigned char * __restrict__ src, unsigned char * __restrict__ dst, size_t n)
+{
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+  {
+    const unsigned int c = src[i] & 15u;
+    unsigned char v;
+    switch (c)
+    {
+      case 1: v = 0; break;
+      case 2: v = 1; break;
+      case 4: v = 2; break;
+      case 8: v = 3; break;
+      case 15: v = 4; break;
+      default: v = (unsigned char)(0x80u | c); break;
+    }
+    dst[i] = v;
+  }
+}
+
+bool launch_tipcols_encode(PartCtx * c, unsigned int tip)
+{
+  if (!c->d_tipcols) return true;
+  const size_t n = c->tip_stride;
+  const size_t off = (size_t)tip * c->tip_stride;
+  unsigned int blocks = (unsigned int)std::min<size_t>((n + 255) / 256, 1184);
+  tipcols_encode_kernel<<<blocks, 256, 0, xstream(c)>>>(c->d_tipchars + off, c->d_tipcols + off, n);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "tipcols_encode_kernel launch");
+}
+
+/* ---- host ------------------------------------------------------------------------------------ */
+
+int g_opt_trav_stash = 2; /* stash slots per warp: 0, 1 or 2 */
+int g_opt_trav_debug = 0; /* LeanArgs::dbg */
+
+static size_t lean_smem_bytes(unsigned int seg) { return (size_t)(seg + 4) * 32 + (size_t)L4_WARPS * L4_WARP_SM; }
+
+bool lean_supported(const PartCtx * c)
+{
+  const pll_partition_t * p = &c->pub;
+  return p->states == 4 && p->rate_cats == 4 && !(p->attributes & PLL_ATTRIB_RATE_SCALERS) && c->d_pmat_cols &&
+         (!(p->attributes & PLL_ATTRIB_PATTERN_TIP) || c->d_tipcols) &&
+         c->clv_stride * sizeof(double) < (1ull << 32) && c->scaler_stride * sizeof(unsigned int) < (1ull << 32);
+}
+
+bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int count)
+{
+  pll_partition_t * p = &c->pub;
+  const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
+  static thread_local std::vector<LeanOp> lean;
+  const unsigned int seg = std::min<unsigned int>(L4_SEG_MAX, count);
+  if (!trav_lean_resolve(ops, count, pattern_tip ? p->tips : 0, c->clv_first, seg, g_opt_trav_stash,
+                         g_opt_trav_forward != 0, lean, nullptr))
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Operation list cannot be packed (matrix index >= 2^24).");
+    return false;
+  }
+  static bool attr_set = false;
+  if (!attr_set)
+  {
+    const int maxb = (int)lean_smem_bytes(L4_SEG_MAX);
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
+                         "trav_dna4_kernel smem") ||
+        !pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
+                         "trav_dna4_batch_kernel smem"))
+      return false;
+    attr_set = true;
+  }
+  const bool collect = batch_collects(BK_TRAV_DNA4);
+  const LeanOp * d_ops = collect ? (const LeanOp *)batch_pool_add(lean.data(), sizeof(LeanOp) * count)
+                                 : (const LeanOp *)dev_stage_small(c, lean.data(), sizeof(LeanOp) * count);
+  if (!d_ops) return false;
+  LeanArgs a;
+  a.ops = d_ops;
+  a.nops = count;
+  a.sites = c->sites_alloc;
+  a.seg = seg;
+  a.tip_stride = (unsigned int)c->tip_stride;
+  a.clv = reinterpret_cast<char *>(c->d_clv);
+  a.scaler = reinterpret_cast<char *>(c->d_scaler);
+  a.pmat_il = c->d_pmat_il;
+  a.pmat_cols = c->d_pmat_cols;
+  a.tipcols = c->d_tipcols;
+  a.dbg = (unsigned int)g_opt_trav_debug;
+  a.clv_stride_b = (unsigned int)(c->clv_stride * sizeof(double));
+  a.scaler_stride_b = (unsigned int)(c->scaler_stride * sizeof(unsigned int));
+
+  const unsigned long long nchunks = ((unsigned long long)a.sites + 31) / 32;
+  unsigned long long blocks = (nchunks + L4_WARPS - 1) / L4_WARPS;
+  int per_sm = 2;
+  if (g_opt_trav_ctas_per_sm > 0) per_sm = std::min(per_sm, g_opt_trav_ctas_per_sm);
+  const unsigned long long cap = (unsigned long long)c->sm_count * per_sm;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  if (collect)
+  {
+    batch_collect(BK_TRAV_DNA4, &a, sizeof(a), (unsigned int)blocks, lean_smem_bytes(L4_SEG_MAX));
+    return true;
+  }
+  trav_dna4_kernel<<<(unsigned int)blocks, L4_WARPS * 32, lean_smem_bytes(seg), xstream(c)>>>(a);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_kernel launch");
+}
+
+bool flush_trav_dna4_lean(PartCtx * lead, const void * d_args, const BatchKind & k)
+{
+  trav_dna4_batch_kernel<<<dim3(batch_grid_x(lead, k, 2), k.count), L4_WARPS * 32, k.smem, lead->stream>>>(
+      static_cast<const LeanArgs *>(d_args));
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "batched trav_dna4 kernel launch");
+}

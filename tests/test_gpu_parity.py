@@ -110,6 +110,62 @@ def test_clvs_scalers_logl_match_reference(kw):
             np.testing.assert_allclose(dev.pmatrix(m), ref.pmatrix(m), rtol=1e-9, atol=1e-15)
 
 
+AMBIG = 1 << 40  # harness seed flag: 3 % IUPAC ambiguity codes in DNA alignments
+
+
+@pytest.mark.parametrize("kw", [
+    dict(tips=120, sites=1000),                               # forwarding + both stash slots + global children
+    dict(tips=700, sites=97),                                 # two staged segments (> 512 ops), ragged last chunk
+    dict(tips=60, sites=31),                                  # less than one 32-site chunk: guarded path only
+    dict(tips=100, sites=2000, brlen_scale=10.0),             # deep tree: scaling votes fire
+    dict(tips=80, sites=515, seed=AMBIG | 7),                 # ambiguity codes: slow tip path
+    dict(tips=40, sites=260, attributes=0),                   # tip CLVs: no tip tables, children from memory
+    dict(tips=50, sites=333, pinv=0.25),
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_dna_stash_kernel_equals_the_round1_kernel_bit_for_bit(kw):
+    """trav_dna4_kernel (children from registers / shared-memory stash / tip column tables; trav_variant 0) writes
+    exactly the CLVs and scaler counts of trav_dna_kernel (every inner child read back, tips as 0/1 vectors;
+    trav_variant 3), whatever the number of stash slots."""
+    pkg = load_product_package()
+    tips = kw["tips"]
+    out = {}
+    try:
+        for variant, stash in ((3, 2), (0, 2), (0, 1), (0, 0)):
+            pkg.set_option("trav_variant", variant)
+            pkg.set_option("trav_stash", stash)
+            with Harness("b200", **kw) as h:
+                ll = h.loglh()
+                out[(variant, stash)] = (ll, [h.clv(tips + i).copy() for i in range(tips - 2)],
+                                         [h.scaler(i).copy() for i in range(tips - 2)])
+    finally:
+        pkg.set_option("trav_variant", 0)
+        pkg.set_option("trav_stash", 2)
+    base = out[(3, 2)]
+    for key in ((0, 2), (0, 1), (0, 0)):
+        got = out[key]
+        assert got[0] == base[0] or rel(got[0], base[0]) < 1e-15, (key, got[0], base[0])
+        for i in range(tips - 2):
+            assert np.array_equal(got[2][i], base[2][i]), (key, "scaler", i)
+            assert np.array_equal(got[1][i], base[1][i]), (key, "clv", i)
+
+
+@needs_ref
+def test_dna_ambiguity_codes_match_reference():
+    kw = dict(tips=48, sites=700, seed=AMBIG | 3)
+    ref, dev = pair(**kw)
+    with ref, dev:
+        lr, ld = ref.loglh(), dev.loglh()
+        assert rel(ld, lr) < 1e-8, (ld, lr)
+        for i in range(kw["tips"] - 2):
+            np.testing.assert_allclose(dev.clv(kw["tips"] + i), ref.clv(kw["tips"] + i), rtol=1e-10, atol=0)
+            assert np.array_equal(dev.scaler(i), ref.scaler(i))
+        r = dev.root()
+        df, ddf = dev.derivatives(r, [0.01, 0.1, 1.0])
+        rf, rdf = ref.derivatives(ref.root(), [0.01, 0.1, 1.0])
+        assert_deriv_close(df, rf)
+        assert_deriv_close(ddf, rdf)
+
+
 @pytest.mark.parametrize("kw", [
     dict(tips=150, sites=203, states=20, brlen_scale=6.0),   # > 128 operations: two staged segments, scaling active
     dict(tips=40, sites=1000, states=20),
