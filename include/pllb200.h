@@ -462,6 +462,22 @@ int pllmod_treeinfo_scale_branches_partition(pllmod_treeinfo_t * treeinfo,
                                              unsigned int partition_idx, double scaler);
 int pllmod_treeinfo_normalize_brlen_scalers(pllmod_treeinfo_t * treeinfo);
 int pllmod_treeinfo_set_tree(pllmod_treeinfo_t * treeinfo, pll_utree_t * tree);
+/* src/tree/pll_tree.h:665, treeinfo.c:509: a clone of the tree carrying partition `partition_index`'s branch
+ * lengths (unlinked mode; otherwise the common lengths).  The caller destroys it with pll_utree_destroy. */
+pll_utree_t * pllmod_treeinfo_get_partition_tree(const pllmod_treeinfo_t * treeinfo, int partition_index);
+/* Topological constraints (src/tree/pll_tree.h:724-785, treeinfo.c:1298-1556).  The legacy per-node group
+ * vector (`set_constraint_clvmap`, and `constraint_check_spr` against it) is host logic and built; the
+ * split-based machinery (pllmod_utree_splitset_*, pllmod_utree_resolve_multi: src/tree/utree_constraint.c,
+ * outside the hot path) is not: `set_constraint_tree` fails with PLLMOD_ERROR_NOT_IMPLEMENTED, and the
+ * remaining three behave as the reference does for a treeinfo without constraint splits (PLL_SUCCESS). */
+int pllmod_treeinfo_set_constraint_clvmap(pllmod_treeinfo_t * treeinfo, const int * clv_index_map);
+int pllmod_treeinfo_set_constraint_tree(pllmod_treeinfo_t * treeinfo, const pll_utree_t * cons_tree,
+                                        int fast_and_dirty);
+int pllmod_treeinfo_constraint_check_spr(pllmod_treeinfo_t * treeinfo, pll_unode_t * subtree,
+                                         pll_unode_t * regraft_edge);
+int pllmod_treeinfo_constraint_subtree_affected(pllmod_treeinfo_t * treeinfo, pll_unode_t * subtree);
+int pllmod_treeinfo_constraint_update_splits(pllmod_treeinfo_t * treeinfo);
+int pllmod_treeinfo_constraint_check_current(pllmod_treeinfo_t * treeinfo);
 /* ADDITIVE (BASELINE.json north_star): traversal + P-matrix refresh + CLV update, no logL
  * evaluation and no host synchronisation; the work that treeinfo.c:973-1041 does inline. */
 int pllmod_treeinfo_update_partials(pllmod_treeinfo_t * treeinfo, int incremental);
@@ -557,7 +573,7 @@ typedef struct cutoff_info
  * [radius_min, radius_max] of the pruning point are scored by partial traversals (fast) or after a
  * 3-branch Newton-Raphson optimisation (thorough); improving moves are applied, the best `ntopol_keep`
  * others are re-evaluated after full branch-length optimisation.  Returns the final logL (0 on error).
- * Topological constraints are not supported (the treeinfo must not carry a constraint tree). */
+ * A constraint group vector (pllmod_treeinfo_set_constraint_clvmap) is honoured; constraint trees are not built. */
 double pllmod_algo_spr_round(pllmod_treeinfo_t * treeinfo, unsigned int radius_min,
                              unsigned int radius_max, unsigned int ntopol_keep, pll_bool_t thorough,
                              int brlen_opt_method, double bl_min, double bl_max, int smoothings,

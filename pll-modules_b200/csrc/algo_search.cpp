@@ -15,8 +15,8 @@
  *
  * The control flow (candidate order, acceptance thresholds 1e-6 / 0.01, cutoff statistics, rollback
  * bookkeeping) follows the reference step by step so that a round visits the same topologies and
- * ends on the same tree; topological constraints are out of scope (no constraint tree => every check
- * passes, exactly what the reference does when treeinfo->constraint is NULL).
+ * ends on the same tree; topological constraints are honoured through pllmod_treeinfo_constraint_check_spr
+ * (the legacy group vector; split-based constraint trees are not built, treeinfo.cpp).
  */
 #include "internal.h"
 
@@ -416,6 +416,10 @@ int best_reinsert_edge(pllmod_treeinfo_t * ti, Candidate & cand, cutoff_info_t *
   else
     loglh = pllmod_treeinfo_compute_loglh(ti, 0);
 
+  /* topological constraint (algo_search.c:661-662,736-742): candidates that contradict it are skipped */
+  pllmod_treeinfo_constraint_update_splits(ti);
+  const int check_cons = pllmod_treeinfo_constraint_subtree_affected(ti, p_edge);
+
   /* prune; the joined branch becomes the temporary root edge */
   pll_unode_t * orig_prune_edge = prune_with_lengths(ti, prm, p_edge);
   if (!orig_prune_edge) return PLL_FAILURE;
@@ -445,6 +449,7 @@ int best_reinsert_edge(pllmod_treeinfo_t * ti, Candidate & cand, cutoff_info_t *
   {
     pll_unode_t * r_edge = queue[j];
     if (r_edge == orig_prune_edge || r_edge == orig_prune_edge->back) continue;
+    if (check_cons && !pllmod_treeinfo_constraint_check_spr(ti, p_edge, r_edge)) continue;
     pllmod_treeinfo_get_branch_length_all(ti, r_edge, regraft_len.data());
     const unsigned int r_dist = dist[j];
 
@@ -615,9 +620,11 @@ extern "C" double pllmod_algo_spr_round(pllmod_treeinfo_t * ti, unsigned int rad
   const bool unlinked = ti->brlen_linkage == PLLMOD_COMMON_BRLEN_UNLINKED;
   prm.sets = unlinked ? ti->init_partition_count : 1;
   pll_errno = 0;
-  if (ti->constraint)
+  /* make sure the initial topology is compatible with the constraint (algo_search.c:1113-1119) */
+  if (!pllmod_treeinfo_constraint_check_current(ti))
   {
-    pllmod_set_error(PLLMOD_ERROR_NOT_IMPLEMENTED, "Topological constraints are not supported");
+    if (pll_errno != PLLMOD_ERROR_NOT_IMPLEMENTED)
+      pllmod_set_error(PLLMOD_TREE_ERROR_INVALID_TREE, "Constraint check failed before SPR round!");
     return 0;
   }
 
@@ -673,14 +680,21 @@ extern "C" double pllmod_algo_spr_round(pllmod_treeinfo_t * ti, unsigned int rad
     {
       pll_tree_rollback_t * rb = ring.prev();
       if (!rb || !rb->SPR.prune_edge) break;
+      /* algo_search.c:1297-1310: a stage whose move contradicts the constraint is undone but not scored */
+      pllmod_treeinfo_constraint_update_splits(ti);
+      const bool skip_topol = !pllmod_treeinfo_constraint_check_spr(ti, (pll_unode_t *)rb->SPR.prune_edge,
+                                                                     (pll_unode_t *)rb->SPR.regraft_edge);
       if (!pllmod_tree_rollback(rb)) goto fail;
       ++undone;
+      if (skip_topol) continue;
     }
     else
     {
       if ((unsigned int)top_index > prm.ntopol_keep) continue;
       Candidate & c = top.list[top_index];
       if (!c.p_node) break;
+      pllmod_treeinfo_constraint_update_splits(ti);
+      if (!pllmod_treeinfo_constraint_check_spr(ti, c.p_node, c.r_node)) continue; /* algo_search.c:1339-1344 */
       if (!pllmod_utree_spr(c.p_node, c.r_node, &undo_move)) goto fail;
       clamp_branch(ti, (pll_unode_t *)undo_move.SPR.regraft_edge, prm.bl_min, prm.bl_max);
       if (thorough)

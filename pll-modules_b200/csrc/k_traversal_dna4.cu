@@ -630,7 +630,7 @@ __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
     {
       const uint4 * src = reinterpret_cast<const uint4 *>(a.ops + seg);
       for (unsigned int i = threadIdx.x; i < nseg * 2; i += blockDim.x) sts_u4(sops + i * 16, __ldg(src + i));
-      if (threadIdx.x < 2) sts_u4(sops + (nseg * 2 + threadIdx.x) * 16, make_uint4(0, 0, 0, 0)); /* prefetch target of the last operation */
+      if (threadIdx.x < 8) sts_u4(sops + (nseg * 2 + threadIdx.x) * 16, make_uint4(0, 0, 0, 0)); /* prefetch targets behind the last operation */
     }
     __syncthreads();
     for (unsigned long long chunk = gwarp; chunk < nchunks; chunk += nwarps)

@@ -9,7 +9,8 @@
  *     log-likelihood of every partition go to that partition's stream, and the host waits once for
  *     all of them before the parallel_reduce_cb / sum (treeinfo.c:1061-1073);
  *   - deriv_precomp[p] is a 64-byte key for a device-resident sumtable, not a CLV-sized host buffer.
- * Topological-constraint support (treeinfo.c:1330-1718) is outside the hot path and not built.
+ * Topological constraints: the legacy group vector is built (set_constraint_clvmap, constraint_check_spr);
+ * the split-set machinery (utree_constraint.c) is outside the hot path and not built.
  */
 #include "internal.h"
 
@@ -778,6 +779,118 @@ extern "C" int pllmod_treeinfo_set_tree(pllmod_treeinfo_t * ti, pll_utree_t * tr
 /* ---- marginal ancestral states at every inner node (treeinfo.c:1558-1712) ------------------------ */
 
 static int anc_visit_all(pll_unode_t *) { return 1; }
+
+/* treeinfo.c:509-544 */
+extern "C" pll_utree_t * pllmod_treeinfo_get_partition_tree(const pllmod_treeinfo_t * ti, int partition_index)
+{
+  pll_utree_t * ptree = pll_utree_clone(ti->tree);
+  if (!ptree) return nullptr;
+  if (ti->brlen_linkage != PLLMOD_COMMON_BRLEN_UNLINKED) return ptree;
+  const double * lengths = ti->branch_lengths[partition_index];
+  const unsigned int node_count = ptree->tip_count + ptree->inner_count;
+  for (unsigned int i = 0; i < node_count; ++i)
+  {
+    pll_unode_t * first = ptree->nodes[i];
+    pll_unode_t * sub = first;
+    do
+    {
+      if (sub->pmatrix_index > ptree->edge_count)
+      {
+        pllmod_set_error(PLLMOD_TREE_ERROR_INVALID_TREE,
+                         "p-matrix index out of bounds (%u). treeinfo structure requires that each branch is "
+                         "assigned a unique p-matrix index between 0 and branch_count-1\n", sub->pmatrix_index);
+        pll_utree_destroy(ptree, nullptr);
+        return nullptr;
+      }
+      sub->length = lengths[sub->pmatrix_index];
+      sub = sub->next;
+    } while (sub && sub != first);
+  }
+  return ptree;
+}
+
+/* ---- topological constraints: the legacy group vector (treeinfo.c:1298-1326,1440-1520) -------------- */
+
+extern "C" int pllmod_treeinfo_set_constraint_clvmap(pllmod_treeinfo_t * ti, const int * clv_index_map)
+{
+  const unsigned int nodes = ti->tree->tip_count + ti->tree->inner_count;
+  if (!ti->constraint)
+  {
+    ti->constraint = (unsigned int *)malloc(nodes * sizeof(unsigned int));
+    if (!ti->constraint)
+    {
+      pllmod_set_error(PLL_ERROR_MEM_ALLOC, "Can't allocate memory for topological constraint\n");
+      return PLL_FAILURE;
+    }
+  }
+  /* group id 0 = freely movable (map value -1) */
+  for (unsigned int i = 0; i < nodes; ++i)
+  {
+    const unsigned int clv = ti->tree->nodes[i]->clv_index;
+    ti->constraint[clv] = (unsigned int)(clv_index_map[clv] + 1);
+  }
+  return PLL_SUCCESS;
+}
+
+extern "C" int pllmod_treeinfo_set_constraint_tree(pllmod_treeinfo_t *, const pll_utree_t *, int)
+{
+  pllmod_set_error(PLLMOD_ERROR_NOT_IMPLEMENTED,
+                   "Constraint trees need the split-set machinery (utree_constraint.c), which libpll_b200 does not "
+                   "build; use pllmod_treeinfo_set_constraint_clvmap");
+  return PLL_FAILURE;
+}
+
+/* group of the subtree behind `node`: its own id, else what its children agree on (s: the group being moved) */
+static unsigned int constraint_group(const pll_unode_t * node, const unsigned int * cons, unsigned int s)
+{
+  const unsigned int own = cons[node->clv_index];
+  if (!node->next || own > 0) return own;
+  const unsigned int l = constraint_group(node->next->back, cons, s);
+  const unsigned int r = constraint_group(node->next->next->back, cons, s);
+  if (l == r) return l;
+  if (!s) return l > r ? l : r;
+  return (l == 0 || l == s) ? r : l;
+}
+
+static bool constraint_free(const pll_unode_t * node, const unsigned int * cons)
+{
+  if (!node->next) return cons[node->clv_index] == 0;
+  return constraint_free(node->next->back, cons) && constraint_free(node->next->next->back, cons);
+}
+
+extern "C" int pllmod_treeinfo_constraint_check_spr(pllmod_treeinfo_t * ti, pll_unode_t * subtree,
+                                                    pll_unode_t * regraft_edge)
+{
+  if (ti->constraint)
+  {
+    unsigned int s = ti->constraint[subtree->clv_index];
+    if (!s) s = constraint_group(subtree->back, ti->constraint, 0);
+    if (constraint_free(subtree->back, ti->constraint) || !s) return PLL_SUCCESS;
+    const unsigned int r1 = constraint_group(regraft_edge, ti->constraint, s);
+    const unsigned int r2 = constraint_group(regraft_edge->back, ti->constraint, s);
+    return (s == r1 || s == r2) ? PLL_SUCCESS : PLL_FAILURE;
+  }
+  if (ti->cons_splits)
+  {
+    pllmod_set_error(PLLMOD_ERROR_NOT_IMPLEMENTED, "Split-based constraint checks are not built");
+    return PLL_FAILURE;
+  }
+  return PLL_SUCCESS;
+}
+
+/* without constraint splits the reference answers PLL_SUCCESS from all three (treeinfo.c:1522-1556) */
+static int no_splits_or_fail(const pllmod_treeinfo_t * ti)
+{
+  if (!ti->cons_splits) return PLL_SUCCESS;
+  pllmod_set_error(PLLMOD_ERROR_NOT_IMPLEMENTED, "Split-based constraint checks are not built");
+  return PLL_FAILURE;
+}
+extern "C" int pllmod_treeinfo_constraint_subtree_affected(pllmod_treeinfo_t * ti, pll_unode_t *)
+{
+  return no_splits_or_fail(ti);
+}
+extern "C" int pllmod_treeinfo_constraint_update_splits(pllmod_treeinfo_t * ti) { return no_splits_or_fail(ti); }
+extern "C" int pllmod_treeinfo_constraint_check_current(pllmod_treeinfo_t * ti) { return no_splits_or_fail(ti); }
 
 extern "C" void pllmod_treeinfo_destroy_ancestral(pllmod_ancestral_t * ancestral)
 {

@@ -1,5 +1,5 @@
 #!/bin/bash
-O=gpurun_out/r02e; mkdir -p $O
+O=gpurun_out/r02f; mkdir -p $O
 timeout 900 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "stash_kernel or ambiguity or clvs_scalers or golden" > $O/pytest_new.log 2>&1
 tail -3 $O/pytest_new.log
 run() { name=$1; shift
