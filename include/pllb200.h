@@ -929,6 +929,8 @@ int pllb200_download_pmatrix(pll_partition_t * partition, unsigned int matrix_in
 int pllb200_download_pmatrices(pll_partition_t * partition, double * dst);
 int pllb200_upload_pmatrices(pll_partition_t * partition, const double * src);
 int pllb200_upload_scaler(pll_partition_t * partition, unsigned int scaler_index, const unsigned int * src);
+/* release the device shadow of a caller-owned sumtable buffer (pll_aligned_free(key) does the same) */
+void pllb200_forget_sumtable(const void * sumtable_key);
 int pllb200_download_sumtable(pll_partition_t * partition, const double * sumtable_key, double * dst);
 /* Re-mirror host arrays a caller modified in place (pattern_weights / invariant / tipchars). */
 int pllb200_sync_host_arrays(pll_partition_t * partition);

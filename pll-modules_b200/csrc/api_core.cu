@@ -184,8 +184,12 @@ void sumtable_forget_key(const void * key)
     cudaStreamSynchronize(c->stream);
     cudaFree(sh->second);
     c->sumtables.erase(sh);
+    c->sumtable_stamp.erase(key);
   }
 }
+
+/* additive: release the device shadow of a sumtable buffer that is about to be freed with plain free() */
+extern "C" void pllb200_forget_sumtable(const void * sumtable_key) { sumtable_forget_key(sumtable_key); }
 
 void sumtable_forget_partition(PartCtx * c)
 {
@@ -196,12 +200,33 @@ void sumtable_forget_partition(PartCtx * c)
 static double * sumtable_shadow(PartCtx * c, const double * key, bool create)
 {
   auto it = c->sumtables.find(key);
-  if (it != c->sumtables.end()) return it->second;
+  if (it != c->sumtables.end())
+  {
+    c->sumtable_stamp[key] = ++c->sumtable_clock;
+    return it->second;
+  }
   if (!create)
   {
     pllb200_set_error(PLL_ERROR_PARAM_INVALID,
                       "pll_compute_likelihood_derivatives: sumtable was never built.");
     return nullptr;
+  }
+  /* a caller that frees its sumtable buffers with free() never tells us: cap the shadows, oldest use first */
+  while (c->sumtables.size() >= PLLB200_MAX_SUMTABLES)
+  {
+    const void * victim = nullptr;
+    unsigned long long oldest = ~0ull;
+    for (auto & kv : c->sumtables)
+    {
+      const unsigned long long st = c->sumtable_stamp[kv.first];
+      if (st < oldest)
+      {
+        oldest = st;
+        victim = kv.first;
+      }
+    }
+    sumtable_forget_key(victim);
+    if (c->sumtables.count(victim)) break; /* not ours to drop (cannot happen): do not spin */
   }
   double * d = nullptr;
   if (!pllb200_cuda_ok(cudaMalloc(&d, sizeof(double) * c->clv_stride), "sumtable alloc")) return nullptr;
@@ -215,14 +240,18 @@ static double * sumtable_shadow(PartCtx * c, const double * key, bool create)
       auto sh = o->sumtables.find(key);
       if (sh != o->sumtables.end())
       {
+        cudaSetDevice(o->device); /* the other partition may live on another GPU */
         cudaStreamSynchronize(o->stream);
         cudaFree(sh->second);
         o->sumtables.erase(sh);
+        o->sumtable_stamp.erase(key);
+        cudaSetDevice(c->device);
       }
     }
     g_key_owner[key] = c;
   }
   c->sumtables[key] = d;
+  c->sumtable_stamp[key] = ++c->sumtable_clock;
   return d;
 }
 

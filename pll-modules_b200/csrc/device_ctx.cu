@@ -266,13 +266,15 @@ void * dev_stage(PartCtx * c, const void * src, size_t bytes)
 {
   if (g_batch && g_batch->lead != c) return dev_stage(g_batch->lead, src, bytes);
   const size_t need = round_up(bytes, 256);
-  if (need > c->stage_size)
+  /* a launch stages a handful of arrays and holds their addresses until it is queued: keep one array below
+   * an eighth of the ring, so that a lap can never land on an address handed out for the same launch */
+  if (need * 8 > c->stage_size)
   {
-    /* grow: rare (op lists beyond 128k ops) */
-    if (!pllb200_cuda_ok(cudaStreamSynchronize(c->stream), "stage grow sync")) return nullptr;
-    cudaFreeHost(c->h_stage);
-    cudaFree(c->d_stage);
-    c->stage_size = round_up(need * 2, 1 << 20);
+    /* grow: rare (op lists beyond 16k ops).  Blocks handed out from the old ring stay valid until the next
+     * stream synchronisation of this partition (dev_flush). */
+    c->retired_host.push_back(c->h_stage);
+    c->retired_dev.push_back(c->d_stage);
+    c->stage_size = round_up(need * 16, 1 << 20);
     if (!pllb200_cuda_ok(cudaHostAlloc(&c->h_stage, c->stage_size, cudaHostAllocDefault), "stage grow") ||
         !pllb200_cuda_ok(cudaMalloc(&c->d_stage, c->stage_size), "stage grow"))
       return nullptr;
@@ -428,18 +430,22 @@ void dev_slot_tag(PartCtx * c, int slot, unsigned long long ** tag_host, unsigne
 bool dev_wait_slot(PartCtx * c, int slot)
 {
   const unsigned long long want = c->slot_tag[slot];
+  /* in batch mode the kernels of every member run on the lead partition's stream */
+  const cudaStream_t stream = xstream(c);
   for (unsigned long long spins = 0;; ++spins)
   {
     if (c->h_tag[slot] == want) return true;
     if ((spins & 0x3fffull) == 0x3fffull)
     {
-      const cudaError_t e = cudaStreamQuery(c->stream);
+      const cudaError_t e = cudaStreamQuery(stream);
       if (e == cudaErrorNotReady) continue;
       if (e != cudaSuccess) return pllb200_cuda_ok(e, "waiting for a device result");
       /* stream idle: the tag is there now, or nobody is going to write it */
       if (c->h_tag[slot] == want) return true;
-      CUDA_TRY(cudaStreamSynchronize(c->stream), false);
-      return true;
+      CUDA_TRY(cudaStreamSynchronize(stream), false);
+      if (c->h_tag[slot] == want) return true;
+      pllb200_set_error(PLLB200_ERROR_DEVICE, "A device result was awaited that no queued kernel writes (slot %d).", slot);
+      return false;
     }
 #if defined(__x86_64__)
     __builtin_ia32_pause();
@@ -461,6 +467,11 @@ bool dev_wait_results(PartCtx * c)
 bool dev_flush(PartCtx * c)
 {
   CUDA_TRY(cudaStreamSynchronize(c->stream), false);
+  if (g_batch && g_batch->lead != c) CUDA_TRY(cudaStreamSynchronize(g_batch->lead->stream), false);
+  for (void * p : c->retired_dev) cudaFree(p);
+  for (void * p : c->retired_host) cudaFreeHost(p);
+  c->retired_dev.clear();
+  c->retired_host.clear();
   for (const PendingResult & r : c->pending) *r.host_dst = c->h_result[r.slot * 4 + r.comp];
   g_d2h_bytes += sizeof(double) * c->pending.size(); /* written by the kernel into mapped host memory */
   c->pending.clear();

@@ -20,6 +20,7 @@
 #define PLLB200_MAGIC 0xB200C1F5u
 #define PLLB200_RESULT_SLOTS 64   /* async reduction results in flight per partition */
 #define PLLB200_MAX_RED_BLOCKS 2048 /* upper bound on reduction grid size */
+#define PLLB200_MAX_SUMTABLES 64   /* device shadows of caller-owned sumtable buffers per partition */
 
 struct PendingResult
 {
@@ -88,6 +89,7 @@ struct PartCtx
   char * d_stage;
   size_t stage_size;
   size_t stage_head;
+  std::vector<void *> retired_dev, retired_host; /* rings replaced by a bigger one: freed at the next dev_flush */
   char * h_small;            /* mapped pinned ring for payloads of a few bytes (dev_stage_small) */
   char * h_small_dev;
   size_t small_head;
@@ -109,6 +111,9 @@ struct PartCtx
 
   /* sumtable shadows keyed by the caller's host pointer */
   std::unordered_map<const void *, double *> sumtables;
+  /* last use of every shadow: at most PLLB200_MAX_SUMTABLES are kept, least recently used first out */
+  std::unordered_map<const void *, unsigned long long> sumtable_stamp;
+  unsigned long long sumtable_clock;
 
   /* host->device mirroring state */
   std::vector<unsigned char> tip_dirty;

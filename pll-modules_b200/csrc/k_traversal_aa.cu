@@ -59,7 +59,10 @@ struct AaArgs
 /* defaults: 4 warps per CTA, 4 tiles of 8 sites per warp and chunk (template parameters below) */
 #define AA_SEG 128 /* ops staged per CTA */
 #define AA_FRAG 480 /* doubles per (matrix, category): 3 ntiles x 5 ksteps x 32 lanes */
-#define AA_THR_HI 0x2FF00000u
+/* signed compare on the high word: x < 2^-256 for every non-NaN x, negative round-off values included,
+ * as the reference's `x < PLL_SCALE_THRESHOLD` (core_partials.c:729-763) */
+#define AA_THR_HI 0x2FF00000
+#define AA_HI_MIN (-2147483647 - 1)
 struct PmatIdx
 {
   unsigned int v[8];
@@ -191,9 +194,9 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
         const double * sL = s_mat + (size_t)st * 2 * mat_doubles;
         const double * sR = sL + mat_doubles;
         const bool check = (flags & AOPF_PS) && !(tip1 && tip2);
-        unsigned int smax[AA_T]; /* per tile: max hi word of this lane's site (row) over k, i */
+        int smax[AA_T]; /* per tile: max (signed) hi word of this lane's site (row) over k, i */
 #pragma unroll
-        for (int t = 0; t < AA_T; ++t) smax[t] = 0;
+        for (int t = 0; t < AA_T; ++t) smax[t] = AA_HI_MIN;
 
         /* A fragments (child values of 8 sites x 4 child states per k-step) are the only operands that
          * come from global memory; the ones of step (k, t) + 1 are requested before the 30 DMMAs of step
@@ -297,7 +300,7 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
                 const double o0 = xl[nt][0] * xr[nt][0], o1 = xl[nt][1] * xr[nt][1];
                 if (nt < 2 || col < 2)
                 {
-                  if (check) smax[t] = max(smax[t], max((unsigned int)__double2hiint(o0), (unsigned int)__double2hiint(o1)));
+                  if (check) smax[t] = max(smax[t], max(__double2hiint(o0), __double2hiint(o1)));
                   if (act) *reinterpret_cast<double2 *>(pd + aa_dstate(nt, col)) = make_double2(o0, o1);
                 }
               }
@@ -323,7 +326,7 @@ __device__ __forceinline__ void trav_aa_body(const AaArgs & a)
 #pragma unroll
           for (int t = 0; t < AA_T; ++t)
           {
-            unsigned int m = smax[t];
+            int m = smax[t];
             m = max(m, __shfl_xor_sync(0xffffffffu, m, 1));
             m = max(m, __shfl_xor_sync(0xffffffffu, m, 2));
             const bool scale = check && m < AA_THR_HI;
@@ -436,7 +439,7 @@ template <int C1, int C2, int AA_T, bool TS>
 __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const double * __restrict__ sL,
                                        const double * __restrict__ sR, unsigned long long wsite0, int lane, bool check,
                                        const unsigned int (&code1)[AA_T], const unsigned int (&code2)[AA_T],
-                                       double (&fw)[4][AA_T][5], unsigned int (&smax)[AA_T], double * stg,
+                                       double (&fw)[4][AA_T][5], int (&smax)[AA_T], double * stg,
                                        const double (&cur)[AA_T][5])
 {
   constexpr int K = 4;
@@ -581,7 +584,7 @@ __device__ __forceinline__ void aa4_op(const AaArgs & a, const AaOp & d, const d
         o[t][nt][0] = xl[t][0] * xr[t][0];
         o[t][nt][1] = xl[t][1] * xr[t][1];
         if (check && (nt < 2 || col < 2))
-          smax[t] = max(smax[t], max((unsigned int)__double2hiint(o[t][nt][0]), (unsigned int)__double2hiint(o[t][nt][1])));
+          smax[t] = max(smax[t], max(__double2hiint(o[t][nt][0]), __double2hiint(o[t][nt][1])));
       }
     }
     /* D fragments of this lane: parent[site][k][4 col .. 4 col + 3] and, for col < 2, [16 + 2 col, + 1] */
@@ -784,9 +787,9 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
         const double * sL = s_mat + (size_t)st * 2 * mat_doubles;
         const double * sR = sL + mat_doubles;
         const bool check = (flags & AOPF_PS) && !(look1 && look2);
-        unsigned int smax[AA_T];
+        int smax[AA_T];
 #pragma unroll
-        for (int t = 0; t < AA_T; ++t) smax[t] = 0;
+        for (int t = 0; t < AA_T; ++t) smax[t] = AA_HI_MIN;
         if (TS && !(look1 && (look2 || fwd2)))
         {
           /* a child read from memory was written at least two operations ago: all bulk stores but the newest are
@@ -819,7 +822,7 @@ __device__ __forceinline__ void trav_aa4_body(const AaArgs & a)
 #pragma unroll
           for (int t = 0; t < AA_T; ++t)
           {
-            unsigned int m = smax[t];
+            int m = smax[t];
             m = max(m, __shfl_xor_sync(0xffffffffu, m, 1));
             m = max(m, __shfl_xor_sync(0xffffffffu, m, 2));
             const bool scale = check && m < AA_THR_HI;

@@ -85,9 +85,10 @@ struct TravSmem
   unsigned long long bar[TRAV_WARPS][2];
 };
 
-/* hi word of a non-negative double: x < 2^-256  <=>  hi(x) < 0x2FF00000 (lo word of 2^-256 is 0) */
-__device__ __forceinline__ unsigned int hi_word(double x) { return (unsigned int)__double2hiint(x); }
-#define SCALE_THRESHOLD_HI 0x2FF00000u
+/* signed hi word: x < 2^-256  <=>  hi(x) < 0x2FF00000 (lo word of 2^-256 is 0) for every non-NaN x, negative
+ * round-off values included, as the reference's `x < PLL_SCALE_THRESHOLD` (core_partials.c:729-763) */
+__device__ __forceinline__ int hi_word(double x) { return __double2hiint(x); }
+#define SCALE_THRESHOLD_HI 0x2FF00000
 
 /* arithmetic of one op for the R elements of a lane; T1/T2: child is a pattern tip */
 template <int K, int R, bool T1, bool T2, bool FULL>
@@ -340,7 +341,7 @@ __device__ __forceinline__ void run_segment(const TravArgs & a, TravSmem<K> & sm
 #pragma unroll
         for (int r = 0; r < R; ++r)
         {
-          const unsigned int m = max(max(hi_word(out[r][0]), hi_word(out[r][1])),
+          const int m = max(max(hi_word(out[r][0]), hi_word(out[r][1])),
                                      max(hi_word(out[r][2]), hi_word(out[r][3])));
           if (m < SCALE_THRESHOLD_HI) scalemask |= 1u << r;
         }
