@@ -5,15 +5,21 @@ Workload (config.workload): BASELINE.json configs[1] — DNA GTR+G4, 1000 taxa x
 post-order traversal (998 CLV updates per site) + P-matrix rebuild + edge log-likelihood, i.e. one
 `pllmod_treeinfo_compute_loglh(treeinfo, 0)` per step; synthetic alignment/tree per SURVEY.md §8d.
 With --gpus N (torchrun) every rank owns its own contiguous 1 M-site slice of an N M-site alignment
-(weak scaling); the only cross-GPU traffic is the all-reduce of the per-partition logL scalar.
+(weak scaling, the line's `value`); the only cross-GPU traffic is the all-reduce of the per-partition logL
+scalar, done inside the library (pllb200_exchange_reduce_cb: one small kernel over NVLink peer memory).
+The same run also times STRONG scaling (BASELINE's "6.5x at 8 GPUs": the 1 M-site alignment split N ways,
+`strong_*` keys) and checks a sharded 64-taxon case against the same alignment on one GPU (`multi_gpu_check`).
+At N = 1 the line carries `secondary`: configs[2..4] measured in the same process (scripts/secondary.py).
 
   value   = CLV site-updates/s (whole job), device-timed with CUDA events on the library's stream,
             inputs resident in HBM (tip codes, P-matrix inputs staged before the events)
   e2e     = the same metric through the public C-ABI call from host data: new branch lengths are set
             on the host tree, pllmod_treeinfo_compute_loglh uploads op list + branch lengths and the
             logL comes back to the host; wall-clock, max over ranks
-  roofline= the traversal kernel alone: algorithmic bytes (396/265/134 B per site for ii/ti/tt ops)
-            / CUDA-event launch duration vs MEASURED_PEAKS.json hbm_gbs
+  roofline= the traversal kernel alone, DRAM reading: the bytes a fused traversal must move (every parent CLV
+            and scaler written once = 132 B per site and op, tip codes read once) / CUDA-event launch duration
+            vs MEASURED_PEAKS.json hbm_gbs.  SURVEY.md 8(d)'s per-op model (396/265/134 B per site for ii/ti/tt:
+            no reuse between ops) is kept as `algorithmic_equiv_GBps`; it is not a bound for a fused traversal
   cpu_baseline / --impl reference = the UNMODIFIED reference (oracle/_ref, AVX2, one site slice per
             host thread — the reference's own parallel_reduce_cb model) on a bounded site sample
 """
@@ -42,6 +48,10 @@ def parse():
     ap.add_argument("--cpu-sites-per-core", type=int, default=4000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--blo", action="store_true", help="also time one NR smoothing pass (extra keys)")
+    ap.add_argument("--no-secondary", action="store_true", help="skip configs[2..4] (N = 1 only)")
+    ap.add_argument("--no-strong", action="store_true", help="skip the strong-scaling arm and the sharding check (N > 1)")
+    ap.add_argument("--reduce", default="native", choices=["native", "nccl"],
+                    help="cross-rank reduction: the library's peer-memory kernel, or torch.distributed NCCL in a Python callback")
     return ap.parse_args()
 
 
@@ -168,6 +178,85 @@ def cpu_reference_run(tips, sites_per_core, reps, max_cores=None):
             "seconds_per_traversal": wall}
 
 
+def attach_reduce(h, pkg, a, rank, world):
+    """Cross-rank reduction of the logL / derivative sums for a site-sharded harness."""
+    if world == 1:
+        return
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    def allgather_bytes(b):
+        mine = torch.frombuffer(bytearray(b), dtype=torch.uint8).cuda()
+        every = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(every, mine)
+        return [bytes(t.cpu().numpy()) for t in every]
+
+    if a.reduce == "native":
+        # the library's own collective (CUDA-IPC inboxes over NVLink); also serves the fused Newton kernel
+        h.set_reduce_native(pkg, rank, world, allgather_bytes)
+        return
+
+    def reduce_cb(view, op):
+        n = len(view)
+        t = torch.from_numpy(np.array(view, copy=True)).to("cuda", non_blocking=False)
+        dist.all_reduce(t, op={0: dist.ReduceOp.SUM, 1: dist.ReduceOp.MAX, 2: dist.ReduceOp.MIN}[op])
+        view[:] = t.cpu().numpy()[:n]
+
+    h.set_reduce_cb(reduce_cb)
+    if os.environ.get("PLLB200_EXCHANGE", "1") != "0":
+        part = h.partition_ptr(0)
+        pkg.exchange_connect(part, rank, world, b"".join(allgather_bytes(pkg.exchange_create(part))))
+
+
+def multi_gpu_check(pkg, a, rank, world, barrier):
+    """A 64-taxon x (world * 40k)-site alignment sharded over the ranks against the same alignment on rank 0
+    alone: logL, and -logL after one Newton-Raphson smoothing pass (exercises the in-kernel exchange)."""
+    from pllharness import Harness
+    tips, S = 64, 40000 * world
+    with Harness("b200", tips=tips, sites=S, rank=rank, nranks=world) as hs:
+        attach_reduce(hs, pkg, a, rank, world)
+        ll_s = hs.loglh(0)
+        blo_s = hs.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)
+        barrier()
+    out = None
+    if rank == 0:
+        with Harness("b200", tips=tips, sites=S) as h1:
+            ll_1 = h1.loglh(0)
+            blo_1 = h1.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)
+        out = {"shape": "%d taxa x %d sites over %d ranks vs one GPU" % (tips, S, world),
+               "logl_sharded": ll_s, "logl_one_gpu": ll_1, "logl_rel_err": abs(ll_s - ll_1) / abs(ll_1),
+               "blo_sharded": blo_s, "blo_one_gpu": blo_1, "blo_rel_err": abs(blo_s - blo_1) / abs(blo_1),
+               "tolerance": 1e-10, "reduce": a.reduce}
+        out["ok"] = bool(out["logl_rel_err"] <= 1e-10 and out["blo_rel_err"] <= 1e-10)
+    barrier()
+    return out
+
+
+def strong_scaling_run(pkg, a, rank, world, barrier, torch, dist):
+    """BASELINE's strong-scaling target: the 1000 x 1 M alignment split `world` ways (S / world sites per GPU)."""
+    from pllharness import Harness
+    with Harness("b200", tips=a.tips, sites=a.sites, rank=rank, nranks=world) as h:
+        stream = torch.cuda.Stream()
+        pkg.load().pllb200_partition_set_stream(h.partition_ptr(0), stream.cuda_stream)
+        attach_reduce(h, pkg, a, rank, world)
+        ll = h.loglh(0)
+        for _ in range(a.warmup):
+            h.loglh(0)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(a.steps):
+            ll = h.loglh(0)
+        e1.record(stream)
+        barrier()
+        ms = e0.elapsed_time(e1) / a.steps
+        t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        pkg.load().pllb200_partition_set_stream(h.partition_ptr(0), None)
+    return float(t.cpu()[0]), ll
+
+
 def main():
     a = parse()
     rank = int(os.environ.get("RANK", "0"))
@@ -212,39 +301,29 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     tips, S = a.tips, a.sites
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    check = strong_ms = strong_ll = None
+    if world > 1 and not a.no_strong:
+        check = multi_gpu_check(pkg, a, rank, world, barrier)
+        strong_ms, strong_ll = strong_scaling_run(pkg, a, rank, world, barrier, torch, dist)
     t_setup = time.perf_counter()
     # weak scaling: a global alignment of world*S sites, this rank owns slice `rank`
     h = Harness("b200", tips=tips, sites=S * world, rank=rank, nranks=world)
     stream = torch.cuda.Stream()
     pkg.load().pllb200_partition_set_stream(h.partition_ptr(0), stream.cuda_stream)
 
-    red_buf = torch.zeros(8, dtype=torch.float64, device="cuda")
-
-    def reduce_cb(view, op):
-        n = len(view)
-        t = torch.from_numpy(np.array(view, copy=True)).to("cuda", non_blocking=False)
-        dist.all_reduce(t, op={0: dist.ReduceOp.SUM, 1: dist.ReduceOp.MAX, 2: dist.ReduceOp.MIN}[op])
-        view[:] = t.cpu().numpy()[:n]
-
-    if world > 1:
-        h.set_reduce_cb(reduce_cb)
-        if os.environ.get("PLLB200_EXCHANGE", "1") != "0":
-            # device-side exchange for the fused Newton kernel: all-gather the CUDA IPC handles once
-            mine = torch.frombuffer(bytearray(pkg.exchange_create(h.partition_ptr(0))), dtype=torch.uint8).cuda()
-            every = [torch.empty_like(mine) for _ in range(world)]
-            dist.all_gather(every, mine)
-            pkg.exchange_connect(h.partition_ptr(0), rank, world, b"".join(bytes(t.cpu().numpy()) for t in every))
+    attach_reduce(h, pkg, a, rank, world)
 
     ll0 = h.loglh(0)            # first full evaluation: uploads tips, builds everything
     setup_s = time.perf_counter() - t_setup
     counts = h.op_type_counts()
     alg_bytes = sum(BYTES[k] * counts[k] for k in counts) * S
     updates_per_step = (tips - 2) * S
-
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
 
     # ---- device-timed value: K steps of compute_loglh(0) --------------------------------------
     for _ in range(a.warmup):
@@ -333,9 +412,15 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dev_ms, e2e_s, kern_avg = [float(x) for x in t.cpu()]
     peak, peak_kind = measured_peak()
-    achieved = alg_bytes / (kern_avg * 1e-3) / 1e9
-    # 95 % of the kernel's DRAM traffic is the parent CLVs going out (children come from registers / L2), and a
-    # write-only stream does not reach the copy figure of MEASURED_PEAKS.json: time one here (4 GiB fill, best of 5)
+    # DRAM reading of the roofline: what a fused traversal has to move through HBM — every parent CLV (128 B)
+    # and scaler count (4 B) written once, every tip code read once; children come from registers / shared memory
+    fused_min_bytes = (tips - 2) * S * 132 + tips * S
+    achieved = fused_min_bytes / (kern_avg * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum of the kernel in one `ncu --set full` capture at 200k sites
+    # (profiles/r02_trav_dna4_ncu_full_summary.csv): 0.75 GB read + 26.46 GB written; linear in sites
+    traffic = 27.208e9 * S / 200000.0 * (tips - 2) / 998.0
+    # the kernel's DRAM traffic is writes, and a write-only stream does not reach the copy figure of
+    # MEASURED_PEAKS.json: time one here (4 GiB fill, best of 5)
     write_peak = None
     try:
         wbuf = torch.empty(1 << 30, dtype=torch.float32, device="cuda")
@@ -369,32 +454,66 @@ def main():
                     "what": "host tree with new branch lengths -> pllmod_treeinfo_compute_loglh -> logL on host"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": 27.766e9 * S / 200000.0,
-                         "traffic_note": "dram__bytes_read+write of one ncu --set full capture at 200k sites "
-                                         "(profiles/r01_trav_dna_ncu_full_summary.csv), scaled linearly in sites "
-                                         "(a 400k-site capture agrees); a 1M-site launch cannot be replayed by ncu",
-                         # frac > 1 is possible: children written a few ops earlier are re-read from registers /
-                         # L1 / L2, so the kernel moves about half of the algorithmic bytes through DRAM
-                         "dram_GBps": 27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9,
-                         "frac_dram": 27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9 / peak,
+                         "traffic": traffic,
+                         "traffic_note": "constant from one ncu --set full capture of this kernel at 200k sites "
+                                         "(profiles/r02_trav_dna4_ncu_full_summary.csv: dram read 0.75 GB + write 26.46 GB), "
+                                         "scaled linearly in sites and operations; not measured by this run "
+                                         "(a 1M-site launch cannot be replayed by ncu)",
+                         "achieved_is": "fused-minimum bytes / kernel time: (taxa-2) x sites x 132 B written + taxa x sites "
+                                        "tip codes read; children of an operation come from registers / shared memory",
+                         "fused_min_bytes_per_launch": fused_min_bytes,
                          "write_stream_GBps": write_peak,
-                         "frac_dram_of_write_stream": (27.766e9 * S / 200000.0 / (kern_avg * 1e-3) / 1e9 / write_peak
-                                                       if write_peak else None),
-                         "peak_kind": peak_kind, "kernel": "trav_dna_kernel<4,false>",
-                         "algorithmic_bytes_per_launch": alg_bytes, "kernel_ms": kern_avg,
-                         "kernel_share_of_step": kern_avg / dev_ms},
+                         "frac_of_write_stream": achieved / write_peak if write_peak else None,
+                         "algorithmic_equiv_GBps": alg_bytes / (kern_avg * 1e-3) / 1e9,
+                         "algorithmic_bytes_per_launch": alg_bytes,
+                         "peak_kind": peak_kind, "kernel": "trav_dna4_kernel(LeanArgs)",
+                         "kernel_ms": kern_avg, "kernel_share_of_step": kern_avg / dev_ms},
             "clocks": clocks, "loglh": ll, "loglh_first": ll0,
         }
         line.update(extra)
+        if world > 1:
+            line["reduce"] = ("library kernel over CUDA-IPC peer memory (pllb200_exchange_reduce_cb)" if a.reduce == "native"
+                              else "torch.distributed NCCL all-reduce in a Python parallel_reduce_cb")
+        if strong_ms is not None:
+            # N = 1 time of the same alignment = this run's per-GPU step (1 M sites per GPU) less nothing:
+            # the weak arm IS the one-GPU workload plus one 8-byte all-reduce
+            line["strong_scaling"] = {"workload": "the %d x %d alignment split over %d GPUs (%d sites per GPU)"
+                                                  % (tips, S, world, S // world),
+                                      "strong_ms_per_step": strong_ms, "n1_ms_per_step": dev_ms,
+                                      "n1_is": "this run's per-GPU step on %d sites (the weak arm)" % S,
+                                      "strong_speedup_vs_n1": dev_ms / strong_ms,
+                                      "value": updates_per_step / (strong_ms * 1e-3), "loglh": strong_ll}
+            line["strong_ms_per_step"] = strong_ms
+            line["strong_speedup_vs_n1"] = dev_ms / strong_ms
+        if check is not None:
+            line["multi_gpu_check"] = check
         if not a.no_cpu_baseline and world == 1:
             cb = cpu_reference_run(tips, a.cpu_sites_per_core, 2)
             if cb:
                 line["cpu_baseline"] = cb
-        print(json.dumps(line))
     h.close()
+    rc = 0
+    if rank == 0:
+        if world == 1 and not a.no_secondary:
+            # configs[2..4] under the same clock (each frees its HBM before the next starts)
+            sys.path.insert(0, os.path.join(ROOT, "scripts"))
+            import secondary
+            sec = {}
+            for name, fn in (("C3", secondary.c3), ("C4", secondary.c4), ("C5", secondary.c5)):
+                t0 = time.perf_counter()
+                try:
+                    sec[name] = fn()
+                except Exception as e:  # a secondary config must not cost the headline line
+                    sec[name] = {"error": repr(e)}
+                sec[name]["wall_s"] = round(time.perf_counter() - t0, 2)
+            line["secondary"] = sec
+        print(json.dumps(line))
+        if check is not None and not check["ok"]:
+            sys.stderr.write("multi_gpu_check failed: %r\n" % (check,))
+            rc = 1
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return rc
 
 
 if __name__ == "__main__":

@@ -1002,6 +1002,12 @@ int pllb200_newton_collect(pll_partition_t * partition, const unsigned int * mat
 int pllb200_exchange_create(pll_partition_t * partition, void * ipc_handle_out);
 int pllb200_exchange_connect(pll_partition_t * partition, int rank, int nranks, const void * all_handles);
 int pllb200_exchange_ranks(pll_partition_t * partition);
+/* The collective step of the path as a library call: a `parallel_reduce_cb` (pll_tree.h:271) whose context is a
+ * partition connected with pllb200_exchange_connect.  The doubles are all-reduced (op 0 sum / 1 max / 2 min)
+ * by one small kernel over NVLink peer memory, combined in rank order (bit-identical on every GPU), and come
+ * back through mapped host memory: no NCCL call, no copy call.  Replaces the caller-side callback of
+ * src/tree/treeinfo.c:1061-1067 and src/optimize/pll_optimize.c:1218,1270-1286. */
+void pllb200_exchange_reduce_cb(void * partition, double * data, size_t count, int op);
 /* Device address (as integer) of the partition's most recent reduction results
  * {logL, d_f, dd_f}: lets a caller run an NCCL all-reduce on them without a host round trip. */
 uint64_t pllb200_result_device_ptr(pll_partition_t * partition);

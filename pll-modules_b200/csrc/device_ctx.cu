@@ -71,6 +71,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_variant")) slot = &g_opt_trav_variant;
   else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
   else if (!strcmp(name, "trav_stash")) slot = &g_opt_trav_stash;
+  else if (!strcmp(name, "trav_short")) slot = &g_opt_trav_short;
   else if (!strcmp(name, "trav_debug")) slot = &g_opt_trav_debug;
   else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;
   else if (!strcmp(name, "queued_newton")) slot = &g_opt_queued_newton;
@@ -126,6 +127,7 @@ bool dev_ctx_init(PartCtx * c)
   c->d_multi = nullptr; c->multi_cap = 0; c->ev_batch = nullptr;
   for (int r = 0; r < 8; ++r) c->xchg_peer[r] = nullptr;
   c->xchg_rank = 0; c->xchg_nranks = 0; c->h_stage = nullptr; c->d_stage = nullptr;
+  c->h_xred = nullptr; c->h_xred_dev = nullptr; c->xred_seq = 0;
   c->h_small = nullptr; c->h_small_dev = nullptr; c->small_head = 0;
   c->d_partials = nullptr; c->d_ticket = nullptr; c->d_result = nullptr; c->h_result = nullptr;
   c->own_stream = nullptr;
@@ -252,6 +254,7 @@ void dev_ctx_destroy(PartCtx * c)
   cudaFree(c->d_ticket); cudaFree(c->d_result);
   if (c->h_stage) cudaFreeHost(c->h_stage);
   if (c->h_small) cudaFreeHost(c->h_small);
+  if (c->h_xred) cudaFreeHost(c->h_xred);
   if (c->h_result) cudaFreeHost(c->h_result);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   cudaGetLastError();
@@ -586,7 +589,75 @@ extern "C" int pllb200_upload_scaler(pll_partition_t * p, unsigned int scaler_in
 
 /* ---- multi-GPU exchange buffers (one process per GPU, CUDA IPC over NVLink/NVSwitch) ---------- */
 
-#define XCHG_BYTES 1024 /* NW_XCHG_DOUBLES * 8, rounded up */
+#define XCHG_BYTES 32768 /* Newton exchange (k_newton.cu: NW_XCHG_DOUBLES * 8 = 640 B) + the reduce inboxes below */
+/* all-reduce inboxes: [2 parities][8 ranks]{values[XRED_MAX], seq, -} from this double offset on */
+#define XRED_BASE 128
+#define XRED_MAX 128
+#define XRED_SLOT (XRED_MAX + 2)
+#define XRED_SPIN_LIMIT 40000000ull
+
+struct XredArgs
+{
+  double * inbox[8];
+  double * d_in;             /* this rank's values (staged) */
+  double * out;              /* mapped host result */
+  unsigned long long * tag_host;
+  unsigned long long tag, seq;
+  int rank, nranks, n, op;
+};
+
+/* All-reduce of n <= XRED_MAX doubles over NVLink peer memory (the collective step of
+ * pllmod_treeinfo_compute_loglh, treeinfo.c:1061-1067, and of the derivative callback, pll_optimize.c:1270-1286):
+ * every rank pushes its values into every rank's inbox (st.release.sys), waits for all ranks in its own inbox
+ * (ld.acquire.sys) and combines them in rank order — the result is bit-identical on all GPUs.  One CTA.
+ * `seq` comes from the host (same on all ranks: the call is collective), so a timed-out call cannot leave a
+ * stale counter behind; slots alternate with its parity. */
+__global__ void xchg_reduce_kernel(XredArgs a)
+{
+  const int i = threadIdx.x;
+  const unsigned int par = (unsigned int)(a.seq & 1ull);
+  __shared__ int s_fail;
+  if (i == 0) s_fail = 0;
+  if (i < a.n)
+  {
+    const double v = a.d_in[i];
+    for (int r = 0; r < a.nranks; ++r) a.inbox[r][XRED_BASE + (par * 8 + a.rank) * XRED_SLOT + i] = v;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (i == 0)
+  {
+    for (int r = 0; r < a.nranks; ++r)
+      asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(a.inbox[r] + XRED_BASE + (par * 8 + a.rank) * XRED_SLOT + XRED_MAX),
+                   "l"(a.seq)
+                   : "memory");
+    unsigned long long spins = 0;
+    for (int r = 0; r < a.nranks && !s_fail; ++r)
+    {
+      const double * flag = a.inbox[a.rank] + XRED_BASE + (par * 8 + r) * XRED_SLOT + XRED_MAX;
+      unsigned long long v;
+      do
+      {
+        asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(flag) : "memory");
+        if (v != a.seq && ++spins > XRED_SPIN_LIMIT) s_fail = 1;
+      } while (v != a.seq && !s_fail);
+    }
+  }
+  __syncthreads();
+  if (i < a.n)
+  {
+    double acc = 0.0;
+    for (int r = 0; r < a.nranks; ++r)
+    {
+      const double v = __ldcg(a.inbox[a.rank] + XRED_BASE + (par * 8 + r) * XRED_SLOT + i);
+      acc = r == 0 ? v : (a.op == 0 ? acc + v : (a.op == 1 ? fmax(acc, v) : fmin(acc, v)));
+    }
+    a.out[i] = s_fail ? __longlong_as_double(0x7ff8000000000000ll) : acc;
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (i == 0) *a.tag_host = a.tag;
+}
 
 extern "C" int pllb200_exchange_create(pll_partition_t * p, void * ipc_handle_out)
 {
@@ -634,12 +705,68 @@ extern "C" int pllb200_exchange_connect(pll_partition_t * p, int rank, int nrank
     cudaIpcMemHandle_t h;
     memcpy(&h, (const char *)all_handles + (size_t)r * sizeof(h), sizeof(h));
     void * ptr = nullptr;
-    CUDA_TRY(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess), PLL_FAILURE);
+    if (!pllb200_cuda_ok(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess), "cudaIpcOpenMemHandle"))
+    {
+      /* undo: close what was opened, park the own buffer in slot 0 again (destroy then frees it) */
+      for (int q = 0; q < r; ++q)
+        if (q != rank && c->xchg_peer[q]) cudaIpcCloseMemHandle(c->xchg_peer[q]);
+      for (int q = 0; q < 8; ++q) c->xchg_peer[q] = nullptr;
+      c->xchg_peer[0] = own;
+      return PLL_FAILURE;
+    }
     c->xchg_peer[r] = (double *)ptr;
   }
   c->xchg_rank = rank;
   c->xchg_nranks = nranks;
   return PLL_SUCCESS;
+}
+
+/* parallel_reduce_cb-compatible collective (pll_tree.h: void (*)(void *, double *, size_t, int)); context = a
+ * partition connected with pllb200_exchange_connect.  op: 0 sum, 1 max, 2 min (PLLMOD_COMMON_REDUCE_*). */
+extern "C" void pllb200_exchange_reduce_cb(void * context, double * data, size_t count, int op)
+{
+  pll_partition_t * p = static_cast<pll_partition_t *>(context);
+  if (!check_ctx(p)) return;
+  PartCtx * c = ctx_of(p);
+  if (c->xchg_nranks < 2) return;
+  if (!c->h_xred)
+  {
+    if (!pllb200_cuda_ok(cudaHostAlloc(&c->h_xred, (XRED_MAX + 1) * sizeof(double), cudaHostAllocMapped), "reduce buffer") ||
+        !pllb200_cuda_ok(cudaHostGetDevicePointer((void **)&c->h_xred_dev, c->h_xred, 0), "reduce buffer"))
+      return;
+    c->h_xred[XRED_MAX] = 0.0;
+  }
+  for (size_t off = 0; off < count; off += XRED_MAX)
+  {
+    const int n = (int)std::min<size_t>(XRED_MAX, count - off);
+    double * d_in = static_cast<double *>(dev_stage_small(c, data + off, sizeof(double) * n));
+    if (!d_in) return;
+    XredArgs a;
+    for (int r = 0; r < 8; ++r) a.inbox[r] = c->xchg_peer[r];
+    a.d_in = d_in;
+    a.out = c->h_xred_dev;
+    a.tag_host = reinterpret_cast<unsigned long long *>(c->h_xred_dev + XRED_MAX);
+    a.seq = ++c->xred_seq;
+    a.tag = a.seq;
+    a.rank = c->xchg_rank;
+    a.nranks = c->xchg_nranks;
+    a.n = n;
+    a.op = op;
+    xchg_reduce_kernel<<<1, XRED_MAX, 0, c->stream>>>(a);
+    ++g_kernel_launches;
+    if (!pllb200_cuda_ok(cudaGetLastError(), "xchg_reduce_kernel launch")) return;
+    volatile unsigned long long * tag = reinterpret_cast<volatile unsigned long long *>(c->h_xred + XRED_MAX);
+    for (unsigned long long spins = 0; *tag != a.tag; ++spins)
+      if ((spins & 0xfffffull) == 0xfffffull && cudaStreamQuery(c->stream) != cudaErrorNotReady)
+      {
+        if (*tag == a.tag) break;
+        if (!pllb200_cuda_ok(cudaStreamSynchronize(c->stream), "exchange reduce")) return;
+        break;
+      }
+    for (int i = 0; i < n; ++i) data[off + i] = c->h_xred[i];
+    g_d2h_bytes += sizeof(double) * n;
+    if (data[off] != data[off]) pllb200_set_error(PLLB200_ERROR_DEVICE, "exchange all-reduce: a peer did not answer");
+  }
 }
 
 extern "C" int pllb200_exchange_ranks(pll_partition_t * p)

@@ -74,6 +74,9 @@ struct PartCtx
   /* multi-GPU exchange for the fused Newton kernel (k_newton.cu): own buffer + peers' IPC mappings */
   double * xchg_peer[8];
   int xchg_rank, xchg_nranks;
+  double * h_xred;            /* mapped pinned result of pllb200_exchange_reduce_cb (+ completion tag) */
+  double * h_xred_dev;
+  unsigned long long xred_seq;
   double * d_sumfrag;         /* lazily allocated: 20-state sumtable matrices as DMMA fragment images */
   std::vector<unsigned long long> sumfrag_key;
   double * d_brlen;           /* lazily allocated, [prob_matrices][4]: queued Newton results (k_newton.cu) */
@@ -154,6 +157,7 @@ extern int g_opt_trav_ctas_per_sm;
 extern int g_opt_trav_reorder;
 extern int g_opt_fuse_root;
 extern int g_opt_trav_variant;
+extern int g_opt_trav_short;
 extern int g_opt_trav_forward;
 extern int g_opt_trav_prefetch;
 extern int g_opt_fused_newton;

@@ -465,6 +465,9 @@ __global__ void __launch_bounds__(TRAV_WARPS * 32, MINB) trav_dna_kernel(TravArg
 /* ---- host ------------------------------------------------------------------------------------ */
 
 int g_opt_trav_variant = 0;
+int g_opt_trav_short = 3; /* lists of at most this many operations run on the kernel below: they are pure streams of
+                             loads, and the stash kernel leaves only ~24 KB of L1 beside its shared memory — too little
+                             to keep a stream in flight (measured: 102 vs 60 us per single operation at 1 M sites) */
 int g_opt_trav_forward = 1;
 int g_opt_trav_prefetch = 0; /* measured: 28.3 ms with, 27.9 ms without at C2 — the kernel is not waiting on DRAM latency */
 
@@ -522,7 +525,8 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
 
   /* Gamma-4 with per-site scalers: the forwarding + stash kernel (variant 0, the default); the kernel
    * below stays for other category counts, per-rate scalers and as the bit-for-bit cross-check */
-  if (g_opt_trav_variant == 0 && lean_supported(c)) return launch_trav_dna4(c, ops, count);
+  if (g_opt_trav_variant == 0 && lean_supported(c) && (count > (unsigned int)g_opt_trav_short || g_batch))
+    return launch_trav_dna4(c, ops, count);
 
   static_assert(sizeof(DevOp) == 64, "DevOp is 8 x u64");
   c->devop_scratch.resize((size_t)count * 8);

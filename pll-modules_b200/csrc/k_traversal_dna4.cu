@@ -98,6 +98,7 @@ __device__ __forceinline__ void cp_async16(unsigned int dst, const void * src)
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void cp_async_wait1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait0() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void mbar_wait_u32(unsigned int bar, unsigned int parity)
 {
   asm volatile(
@@ -404,12 +405,21 @@ __device__ __forceinline__ void lean_op_hot(const LeanArgs & a, const LaneCtx & 
     if (SRC2 == SRC_STASH) q2 = lds_u4(L.sst_lane() + LOPA_SLOT2(fa) * 128);
     if (SRC2 == SRC_GLOBAL) q2 = lean_load_scalers<true>(a, L, w1.y);
   }
-  /* child 1 from global memory: ask L1 for its lines now (no register), read them after child 2's term */
+  /* child 1 from global memory: requested now, next to child 2, so that both are in flight together — a
+   * short list (branch-length optimisation, a regraft candidate) is a pure stream and needs the bytes in flight */
+  double v1[4][4];
   if (SRC1 == SRC_GLOBAL)
   {
-    const char * p1 = lean_clv_ptr(a, L, w0.y);
+    const double * p1 = reinterpret_cast<const double *>(lean_clv_ptr(a, L, w0.y));
 #pragma unroll
-    for (int r = 0; r < 4; ++r) asm volatile("prefetch.global.L1 [%0];" ::"l"(p1 + 128 * r));
+    for (int r = 0; r < 4; ++r)
+    {
+      const d4 v = ldg256(p1 + 16 * r);
+      v1[r][0] = v.x;
+      v1[r][1] = v.y;
+      v1[r][2] = v.z;
+      v1[r][3] = v.w;
+    }
   }
   if (SRC2 == SRC_GLOBAL)
   {
@@ -437,22 +447,7 @@ __device__ __forceinline__ void lean_op_hot(const LeanArgs & a, const LaneCtx & 
     lean_tip_multiply(matL, t1, false, acc);
   else
   {
-    double v1[4][4];
-    if (SRC1 == SRC_STASH)
-      lean_stash_read(L.stash_lane() + LOPA_SLOT1(fa) * L4_STASH_B, v1);
-    else
-    {
-      const double * p1 = reinterpret_cast<const double *>(lean_clv_ptr(a, L, w0.y));
-#pragma unroll
-      for (int r = 0; r < 4; ++r)
-      {
-        const d4 v = ldg256(p1 + 16 * r);
-        v1[r][0] = v.x;
-        v1[r][1] = v.y;
-        v1[r][2] = v.z;
-        v1[r][3] = v.w;
-      }
-    }
+    if (SRC1 == SRC_STASH) lean_stash_read(L.stash_lane() + LOPA_SLOT1(fa) * L4_STASH_B, v1);
     multiply_by_term(matL, v1, acc);
   }
 
@@ -600,6 +595,10 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
       default: lean_op_generic<FULL>(a, L, rec, st, acc, fsc, t1, t2); break;
     }
   }
+  /* the last operation prefetched the zero record behind the segment: that copy must have landed before the
+   * next chunk's first copies go into the same stage (copies of different groups may land in any order) */
+  cp_async_wait0();
+  __syncwarp();
 }
 
 template <int TAG>

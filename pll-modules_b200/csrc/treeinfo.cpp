@@ -684,6 +684,11 @@ static double compute_loglh(pllmod_treeinfo_t * ti, int incremental, int update_
                            PLLMOD_COMMON_REDUCE_SUM);
   for (unsigned int p = 0; p < ti->partition_count; ++p) total += ti->partition_loglh[p];
   assert(total < 0.);
+  {
+    /* debugging aid (PLLB200_TRACE_LOGLH=file): every evaluation's result, bit-exact, one per line */
+    static FILE * trace = getenv("PLLB200_TRACE_LOGLH") ? fopen(getenv("PLLB200_TRACE_LOGLH"), "w") : nullptr;
+    if (trace) fprintf(trace, "%a %d %u\n", total, incremental, r->node_index);
+  }
   return total;
 }
 

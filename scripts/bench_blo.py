@@ -7,7 +7,7 @@ tips = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 sites = int(sys.argv[2]) if len(sys.argv) > 2 else 1000000
 states = int(sys.argv[3]) if len(sys.argv) > 3 else 4
 pkg = load_product_package()
-for opt in ("fused_newton", "queued_newton", "small_stage"):
+for opt in ("fused_newton", "queued_newton", "small_stage", "trav_variant", "trav_stash", "trav_short"):
     if os.environ.get("PLLB200_" + opt.upper()):
         pkg.set_option(opt, int(os.environ["PLLB200_" + opt.upper()]))
 with Harness("b200", tips=tips, sites=sites, states=states) as h:

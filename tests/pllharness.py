@@ -421,6 +421,17 @@ class Harness:
         self._cb = REDUCE_CB(_cb)
         self.lib.h_set_reduce_cb(self.h, None, self._cb)
 
+    def set_reduce_native(self, pkg, rank, world, allgather_bytes):
+        """Connect partition 0's CUDA-IPC exchange over `world` ranks (allgather_bytes(bytes) -> list of every
+        rank's bytes) and make the library's own collective, pllb200_exchange_reduce_cb, the treeinfo's
+        parallel_reduce_cb: logL and derivative sums then cross NVLink inside the library."""
+        part = self.partition_ptr(0)
+        every = allgather_bytes(pkg.exchange_create(part))
+        pkg.exchange_connect(part, rank, world, b"".join(every))
+        fn = C.cast(pkg.load().pllb200_exchange_reduce_cb, C.c_void_p).value
+        self._cb = REDUCE_CB(fn)
+        self.lib.h_set_reduce_cb(self.h, C.c_void_p(part), self._cb)
+
     def op_type_counts(self, p=0):
         out = np.zeros(3, dtype=np.uint32)
         self.lib.h_op_type_counts(self.h, p, self.tips - 2, out.ctypes.data)

@@ -149,6 +149,40 @@ def test_dna_stash_kernel_equals_the_round1_kernel_bit_for_bit(kw):
             assert np.array_equal(got[1][i], base[1][i]), (key, "clv", i)
 
 
+def test_dna_partial_traversals_are_bit_stable_when_a_warp_takes_several_chunks():
+    """100 k sites = 3125 chunks for 2368 resident warps: warps of the persistent grid walk more than one chunk.
+    A sequence of re-rootings + incremental evaluations (what an SPR round does) must give bit-identical logL on
+    the stash kernel (all list lengths), on the default routing and on the round-1 kernel reading every child
+    back from memory — and again on a second pass (regression: a stale asynchronous matrix copy of the previous
+    chunk once raced with the first copies of the next one)."""
+    pkg = load_product_package()
+    tips, sites, n = 60, 100000, 120
+
+    def run(opts):
+        for k, v in (("trav_short", 3), ("trav_variant", 0), ("trav_stash", 2), ("trav_forward", 1)):
+            pkg.set_option(k, opts.get(k, v))
+        out = []
+        with Harness("b200", tips=tips, sites=sites) as h:
+            h.loglh(0)
+            rng = np.random.RandomState(5)
+            for nd in rng.randint(tips, 4 * tips - 6, size=n):
+                h.perturb_edge(int(nd), 0.05 + 0.1 * rng.rand())
+                h.set_root(int(nd))
+                out.append(h.loglh(1))
+            out.append(h.loglh(0))
+        return out
+
+    try:
+        ref = run({"trav_variant": 3, "trav_forward": 0})
+        for opts in ({"trav_short": 0}, {"trav_short": 0}, {}, {"trav_short": 0, "trav_stash": 0}, {"trav_variant": 3}):
+            got = run(opts)
+            bad = [i for i, (a, b) in enumerate(zip(ref, got)) if a != b]
+            assert not bad, (opts, bad[:5], [(ref[i], got[i]) for i in bad[:2]])
+    finally:
+        for k, v in (("trav_short", 3), ("trav_variant", 0), ("trav_stash", 2), ("trav_forward", 1)):
+            pkg.set_option(k, v)
+
+
 @needs_ref
 def test_dna_ambiguity_codes_match_reference():
     kw = dict(tips=48, sites=700, seed=AMBIG | 3)
