@@ -951,6 +951,21 @@ int pllb200_edge_loglikelihood_async(pll_partition_t * partition,
                                      unsigned int child_clv_index, int child_scaler_index,
                                      unsigned int matrix_index,
                                      const unsigned int * freqs_indices, double * result);
+/* No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it).  The same value as
+ * pll_compute_edge_loglikelihood (and, if persite_lnl is not NULL, the same `sites` per-site log-likelihoods),
+ * computed by the same kernels, but the scratch memory — per-CTA partial sums, the reduction ticket and the
+ * per-site values — lives in a static device array of the library (2.1 MB per GPU, held until exit) instead of
+ * buffers from cudaMalloc: the call allocates nothing on the device.  Limits: at most 262144 sites per partition
+ * (larger partitions are rejected with PLL_ERROR_PARAM_INVALID); every host-side input and the model must
+ * already be mirrored on the device by an earlier ordinary call (else PLL_ERROR_PARAM_INVALID); all calls on one
+ * GPU share the array, so calls whose kernels overlap on the GPU (other streams, other threads) race — serialise
+ * them.  Returns PLL_SUCCESS / PLL_FAILURE, the value in *loglh_out. */
+int pllb200_edge_loglikelihood_noalloc(pll_partition_t * partition, unsigned int parent_clv_index,
+                                       int parent_scaler_index, unsigned int child_clv_index,
+                                       int child_scaler_index, unsigned int matrix_index,
+                                       const unsigned int * freqs_indices, double * loglh_out,
+                                       double * persite_lnl);
 /* Asynchronous twin of pll_compute_likelihood_derivatives: queues the derivative pass; *d_f / *dd_f
  * (caller-owned host memory) are filled by pllb200_partition_synchronize or any later blocking call
  * on the partition.  Lets a multi-partition Newton step queue every partition before waiting once. */

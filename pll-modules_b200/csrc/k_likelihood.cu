@@ -663,3 +663,139 @@ bool launch_root_logl(PartCtx * c, unsigned int clv_index, int scaler_index,
   a.pscaler = scaler_dev(c, scaler_index);
   return dispatch_logl<true>(c, without_tag_if_asc(c, a)) && launch_asc_logl(c, a, 1);
 }
+
+/* ---- edge log-likelihood without any allocation ----------
+ * Callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it) get
+ * pllb200_edge_loglikelihood_noalloc: the edge logL kernels above with their scratch — one partial sum per CTA,
+ * the ticket of the last-CTA reduction, and the per-site log-likelihoods — in a file-scope device array instead
+ * of the partition's cudaMalloc'ed buffers (d_partials / d_ticket, and d_persite which pll_compute_edge_
+ * loglikelihood allocates on first use).  Every GPU that loads the library holds the array (2.1 MB) until exit.
+ * All calls on a device share it and it keeps the last call's contents: the ticket is cleared on the stream
+ * before every launch, partials and per-site values are fully overwritten before they are read.  Two calls
+ * whose kernels overlap on the GPU (different partitions on different streams, several host threads) RACE on
+ * it: serialise them. */
+#define NOALLOC_MAX_SITES 262144u /* stated maximum: partitions with more sites are rejected */
+#define NOALLOC_PERSITE_BYTES ((size_t)NOALLOC_MAX_SITES * sizeof(double))
+#define NOALLOC_PARTIALS_BYTES ((size_t)PLLB200_MAX_RED_BLOCKS * 4 * sizeof(double))
+#define NOALLOC_TICKET_BYTES 256
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_PERSITE_BYTES + NOALLOC_PARTIALS_BYTES + NOALLOC_TICKET_BYTES];
+
+/* In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address: the address is
+ * asked for once per device, with that device current, and kept here. */
+#define NOALLOC_MAX_DEVICES 64
+static unsigned char * g_noalloc_ptr[NOALLOC_MAX_DEVICES];
+
+static unsigned char * noalloc_scratch_on(int device)
+{
+  if (device < 0 || device >= NOALLOC_MAX_DEVICES)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "pllb200_edge_loglikelihood_noalloc: device %d out of range.", device);
+    return nullptr;
+  }
+  if (!g_noalloc_ptr[device])
+  {
+    void * ptr = nullptr;
+    if (!pllb200_cuda_ok(cudaSetDevice(device), "cudaSetDevice") ||
+        !pllb200_cuda_ok(cudaGetSymbolAddress(&ptr, g_noalloc_scratch), "cudaGetSymbolAddress(g_noalloc_scratch)"))
+      return nullptr;
+    g_noalloc_ptr[device] = static_cast<unsigned char *>(ptr);
+  }
+  return g_noalloc_ptr[device];
+}
+
+extern "C" int pllb200_edge_loglikelihood_noalloc(pll_partition_t * partition, unsigned int parent_clv_index,
+                                                  int parent_scaler_index, unsigned int child_clv_index,
+                                                  int child_scaler_index, unsigned int matrix_index,
+                                                  const unsigned int * freqs_indices, double * loglh_out,
+                                                  double * persite_lnl)
+{
+  if (!partition || ctx_of(partition)->magic != PLLB200_MAGIC || !freqs_indices || !loglh_out)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "pllb200_edge_loglikelihood_noalloc: not a libpll_b200 partition, or a null argument.");
+    return PLL_FAILURE;
+  }
+  PartCtx * c = ctx_of(partition);
+  pll_partition_t * p = &c->pub;
+  if (p->sites > NOALLOC_MAX_SITES)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID,
+                      "pllb200_edge_loglikelihood_noalloc: %u sites exceed the static scratch (maximum %u sites); "
+                      "use pll_compute_edge_loglikelihood.", p->sites, NOALLOC_MAX_SITES);
+    return PLL_FAILURE;
+  }
+  if (p->rate_cats > LK_MAXK)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "rate_cats > %d is not supported.", LK_MAXK);
+    return PLL_FAILURE;
+  }
+  /* everything the kernel reads must already be mirrored on the device: mirroring stages and may allocate */
+  bool current = !c->any_tip_dirty && !c->weights_dirty && !c->tipmap_dirty && !(c->invariant_dirty && p->invariant);
+  for (unsigned int k = 0; k < p->rate_cats && current; ++k)
+  {
+    const unsigned int m = freqs_indices[k];
+    if (m >= p->rate_matrices || !p->eigen_decomp_valid[m] || c->eigen_version_dev[m] != c->eigen_version[m]) current = false;
+    else if (p->prop_invar[m] > 0.0 && !c->d_invariant) current = false;
+  }
+  if (!current)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID,
+                      "pllb200_edge_loglikelihood_noalloc: host-side inputs or model are newer than their device copies; "
+                      "run an ordinary evaluation (pll_update_prob_matrices / pll_compute_edge_loglikelihood) once first.");
+    return PLL_FAILURE;
+  }
+  unsigned char * scratch = noalloc_scratch_on(c->device);
+  if (!scratch) return PLL_FAILURE;
+  if (!pllb200_cuda_ok(cudaSetDevice(c->device), "cudaSetDevice")) return PLL_FAILURE;
+  double * d_persite = reinterpret_cast<double *>(scratch);
+  double * d_partials = reinterpret_cast<double *>(scratch + NOALLOC_PERSITE_BYTES);
+  unsigned int * d_ticket = reinterpret_cast<unsigned int *>(scratch + NOALLOC_PERSITE_BYTES + NOALLOC_PARTIALS_BYTES);
+
+  if (parent_clv_index >= p->nodes || child_clv_index >= p->nodes || matrix_index >= p->prob_matrices ||
+      parent_scaler_index >= (int)p->scale_buffers || child_scaler_index >= (int)p->scale_buffers)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid index in edge log-likelihood call.");
+    return PLL_FAILURE;
+  }
+  const bool ptip = is_tip_pattern(c, parent_clv_index), ctip = is_tip_pattern(c, child_clv_index);
+  if (ptip && ctip)
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Edge log-likelihood between two pattern tips.");
+    return PLL_FAILURE;
+  }
+  if (ptip)
+  {
+    std::swap(parent_clv_index, child_clv_index);
+    std::swap(parent_scaler_index, child_scaler_index);
+  }
+  const int slot = dev_alloc_slot(c);
+  LoglArgs a;
+  if (!fill_common(c, a, freqs_indices, persite_lnl ? d_persite : nullptr, slot)) return PLL_FAILURE;
+  a.red.partials = d_partials; /* the static scratch instead of the partition's buffers */
+  a.red.ticket = d_ticket;
+  a.pclv = clv_dev(c, parent_clv_index);
+  a.pscaler = scaler_dev(c, parent_scaler_index);
+  if (ptip || ctip)
+    a.ctip = c->d_tipchars + (size_t)child_clv_index * c->tip_stride;
+  else
+  {
+    a.cclv = clv_dev(c, child_clv_index);
+    a.cscaler = scaler_dev(c, child_scaler_index);
+  }
+  a.pmat = c->d_pmat + (size_t)matrix_index * c->pmat_elems;
+  /* the ticket must start at zero whatever an earlier (possibly failed) call left behind */
+  if (!pllb200_cuda_ok(cudaMemsetAsync(d_ticket, 0, NOALLOC_TICKET_BYTES, c->stream), "scratch ticket clear")) return PLL_FAILURE;
+  if (!dispatch_logl<false>(c, without_tag_if_asc(c, a)) || !launch_asc_logl(c, a, 0)) return PLL_FAILURE;
+  if (persite_lnl)
+  {
+    if (!pllb200_cuda_ok(cudaMemcpyAsync(persite_lnl, d_persite, sizeof(double) * p->sites, cudaMemcpyDeviceToHost, c->stream),
+                         "persite copy"))
+      return PLL_FAILURE;
+    g_d2h_bytes += sizeof(double) * p->sites;
+    if (!dev_flush(c)) return PLL_FAILURE;
+  }
+  else if (!(dev_wait_results(c) && dev_wait_slot(c, slot)))
+    return PLL_FAILURE;
+  g_d2h_bytes += sizeof(double);
+  *loglh_out = c->h_result[slot * 4];
+  return PLL_SUCCESS;
+}
