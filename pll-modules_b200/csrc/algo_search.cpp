@@ -19,6 +19,7 @@
  * (the legacy group vector; split-based constraint trees are not built, treeinfo.cpp).
  */
 #include "internal.h"
+#include "trav_schedule.h"
 
 #include <cassert>
 #include <chrono>
@@ -393,6 +394,169 @@ void invalidate3(pllmod_treeinfo_t * ti, pll_unode_t * e)
   pllmod_treeinfo_invalidate_pmatrix(ti, e->next->next);
 }
 
+/* ---- batched regraft scoring (fast mode) ------------------------------------------------------------
+ * The reference scores the candidates of one pruned subtree one after the other: regraft, two P-matrices, a
+ * partial traversal that re-orients one to three CLVs, one edge logL, prune again (algo_search.c:727-860) —
+ * here ~5 launches and a host wait each.  But all candidates share everything except the branch they split:
+ * with the tree rooted at the pruning point every CLV already points TOWARDS it, and the CLV pointing AWAY from
+ * it at a branch of depth d follows from the one of its parent branch and one sibling CLV.  One depth-first walk
+ * to radius_max therefore emits, per branch, one ordinary operation (the away-CLV, into a scratch row per depth)
+ * and one SCORE operation (k_traversal_dna4.cu: new inner node between the two halves of the branch + edge logL
+ * against the pruned subtree, nothing stored), and the whole list is ONE launch of the site-column kernel plus
+ * one launch for all half-length P-matrices.  Scores are computed for every branch within radius_max; the
+ * reference's breadth-first loop with its cutoff rule is then replayed on the host over these numbers, so the
+ * same candidates are visited in the same order and the same statistics accumulate. */
+struct BatchScores
+{
+  std::vector<pll_unode_t *> edge; /* candidate branch (the subnode the reference's queue holds) */
+  std::vector<double> score;
+  double lookup(const pll_unode_t * e, bool & found) const
+  {
+    for (size_t i = 0; i < edge.size(); ++i)
+      if (edge[i] == e)
+      {
+        found = true;
+        return score[i];
+      }
+    found = false;
+    return 0.0;
+  }
+};
+
+struct BatchBuilder
+{
+  pllmod_treeinfo_t * ti;
+  const SearchParams * prm;
+  unsigned int nodes, scale_buffers, prob_matrices;
+  std::vector<pll_operation_t> ops;
+  std::vector<unsigned char> kind;
+  std::vector<unsigned int> cand;
+  std::vector<unsigned int> mat_idx;
+  std::vector<double> mat_len;
+  BatchScores * out;
+
+  struct Src
+  {
+    unsigned int clv;
+    int scaler;
+    unsigned int matrix;
+  };
+  static Src real(const pll_unode_t * n, unsigned int matrix) { return Src{n->clv_index, n->scaler_index, matrix}; }
+
+  double branch_length(const pll_unode_t * e) const
+  {
+    return ti->brlen_linkage == PLLMOD_COMMON_BRLEN_UNLINKED ? ti->branch_lengths[0][e->pmatrix_index] : e->length;
+  }
+
+  /* far: the subnode at the far end of a branch of depth `depth`; up: what enters its near node from the
+   * pruning point's side, sib: the near node's other subtree */
+  void walk(pll_unode_t * far, unsigned int depth, const Src & up, const Src & sib)
+  {
+    pll_operation_t o;
+    o.parent_clv_index = nodes + depth;
+    o.parent_scaler_index = (int)(scale_buffers + depth);
+    o.child1_clv_index = up.clv;
+    o.child1_scaler_index = up.scaler;
+    o.child1_matrix_index = up.matrix;
+    o.child2_clv_index = sib.clv;
+    o.child2_scaler_index = sib.scaler;
+    o.child2_matrix_index = sib.matrix;
+    ops.push_back(o);
+    kind.push_back(0);
+    cand.push_back(0);
+    if (depth >= prm->radius_min)
+    {
+      /* both halves get half the branch, clamped (regraft_with_lengths + clamp_branch) */
+      double half = branch_length(far) / 2.;
+      if (half < prm->bl_min) half = prm->bl_min;
+      if (half > prm->bl_max) half = prm->bl_max;
+      if (ti->brlen_linkage == PLLMOD_COMMON_BRLEN_SCALED) half *= ti->brlen_scalers[0];
+      const unsigned int m = prob_matrices + (unsigned int)mat_idx.size();
+      mat_idx.push_back(m);
+      mat_len.push_back(half);
+      pll_operation_t sop;
+      sop.parent_clv_index = nodes; /* scratch row 0: written by nobody, read by nobody */
+      sop.parent_scaler_index = -1;
+      sop.child1_clv_index = far->clv_index; /* points towards the pruning point: valid */
+      sop.child1_scaler_index = far->scaler_index;
+      sop.child1_matrix_index = m;
+      sop.child2_clv_index = nodes + depth; /* the away-CLV just computed: forwarded in registers */
+      sop.child2_scaler_index = (int)(scale_buffers + depth);
+      sop.child2_matrix_index = m;
+      ops.push_back(sop);
+      kind.push_back(LSPECIAL_SCORE);
+      cand.push_back((unsigned int)out->edge.size());
+      out->edge.push_back(far);
+    }
+    if (depth >= prm->radius_max || !far->next) return;
+    pll_unode_t * c1 = far->next;
+    pll_unode_t * c2 = far->next->next;
+    const Src here{nodes + depth, (int)(scale_buffers + depth), far->pmatrix_index};
+    walk(c1->back, depth + 1, here, real(c2->back, c2->pmatrix_index));
+    walk(c2->back, depth + 1, here, real(c1->back, c1->pmatrix_index));
+  }
+};
+
+/* true: `scores` holds the logL of every candidate within radius_max of the (already pruned) subtree behind
+ * p_edge; false: this case is not eligible (the caller scores sequentially) or an error occurred (pll_errno) */
+static bool score_candidates_batched(pllmod_treeinfo_t * ti, const SearchParams & prm, pll_unode_t * p_edge,
+                                     BatchScores & scores)
+{
+  if (!g_opt_spr_batch || prm.thorough || ti->partition_count != 1 || !ti->partitions[0]) return false;
+  pll_partition_t * part = ti->partitions[0];
+  PartCtx * c = ctx_of(part);
+  if (c->magic != PLLB200_MAGIC || !lean_supported(c) || (part->attributes & PLL_ATTRIB_AB_MASK)) return false;
+  if (c->scratch_rows < prm.radius_max + 2 || !part->scale_buffers || prm.radius_min < 1) return false;
+  for (unsigned int k = 0; k < part->rate_cats; ++k)
+    if (part->prop_invar[ti->param_indices[0][k]] > 0.0) return false;
+  pll_unode_t * R = ti->root; /* the joined branch left behind by the pruning */
+  /* every CLV must point towards the pruning point (the two at the joined branch were invalidated) */
+  if (!pllmod_treeinfo_update_partials(ti, 1)) return false;
+  BatchBuilder b;
+  b.ti = ti;
+  b.prm = &prm;
+  b.nodes = part->nodes;
+  b.scale_buffers = part->scale_buffers;
+  b.prob_matrices = part->prob_matrices;
+  b.out = &scores;
+  scores.edge.clear();
+  /* SETUP: the pruned subtree's CLV over the prune branch (p_edge keeps its length in every candidate) */
+  {
+    pll_operation_t o;
+    o.parent_clv_index = part->nodes;
+    o.parent_scaler_index = -1;
+    o.child1_clv_index = p_edge->back->clv_index; /* SETUP uses child 2 only: child 1 names no scaler, so that */
+    o.child1_scaler_index = -1;                   /* the subtree's counts are not taken twice */
+    o.child1_matrix_index = p_edge->pmatrix_index;
+    o.child2_clv_index = p_edge->back->clv_index;
+    o.child2_scaler_index = p_edge->back->scaler_index;
+    o.child2_matrix_index = p_edge->pmatrix_index;
+    b.ops.push_back(o);
+    b.kind.push_back(LSPECIAL_SETUP);
+    b.cand.push_back(0);
+  }
+  for (int side = 0; side < 2; ++side)
+  {
+    pll_unode_t * top = side ? R->back : R;
+    if (!top->next) continue;
+    pll_unode_t * n1 = top->next;
+    pll_unode_t * n2 = top->next->next;
+    const BatchBuilder::Src up = BatchBuilder::real(top->back, top->pmatrix_index);
+    b.walk(n1->back, 1, up, BatchBuilder::real(n2->back, n2->pmatrix_index));
+    b.walk(n2->back, 1, up, BatchBuilder::real(n1->back, n1->pmatrix_index));
+  }
+  const unsigned int ncand = (unsigned int)scores.edge.size();
+  if (!ncand || ncand > c->scratch_mats || ncand > PLLB200_SCORE_MAX || b.ops.size() > 512) return false;
+  if (!pll_update_prob_matrices(part, ti->param_indices[0], b.mat_idx.data(), b.mat_len.data(), ncand)) return false;
+  scores.score.assign(ncand, 0.0);
+  if (!launch_trav_dna4_score(c, b.ops.data(), b.kind.data(), b.cand.data(), (unsigned int)b.ops.size(), ncand,
+                              ti->param_indices[0], scores.score.data()))
+    return false;
+  if (ti->parallel_reduce_cb)
+    ti->parallel_reduce_cb(ti->parallel_context, scores.score.data(), ncand, PLLMOD_COMMON_REDUCE_SUM);
+  return true;
+}
+
 /* Try every regraft edge within the radius window for the subtree behind `cand.p_node`, remember the
  * best one, and put the subtree back where it was (algo_search.c:603-899). */
 int best_reinsert_edge(pllmod_treeinfo_t * ti, Candidate & cand, cutoff_info_t * cutoff,
@@ -430,6 +594,16 @@ int best_reinsert_edge(pllmod_treeinfo_t * ti, Candidate & cand, cutoff_info_t *
   pllmod_treeinfo_invalidate_pmatrix(ti, orig_prune_edge);
   if (!refresh_edge_pmatrix(ti, orig_prune_edge)) return PLL_FAILURE;
 
+  /* fast mode, one Gamma-4 DNA partition: every candidate within radius_max is scored by one launch */
+  BatchScores scores;
+  pll_errno = 0;
+  bool batched = score_candidates_batched(ti, prm, p_edge, scores);
+  if (!batched && pll_errno) return PLL_FAILURE;
+  /* debugging aid (PLLB200_SPR_VERIFY=1): score sequentially as well and report every disagreement */
+  static const bool verify = getenv("PLLB200_SPR_VERIFY") != nullptr;
+  const bool have_scores = batched;
+  if (verify) batched = false;
+
   /* breadth-first list of regraft candidates, seeded at distance radius_min on both sides */
   std::vector<pll_unode_t *> queue(total_edges + 2, nullptr);
   std::vector<unsigned int> dist(total_edges + 2, 0);
@@ -450,41 +624,67 @@ int best_reinsert_edge(pllmod_treeinfo_t * ti, Candidate & cand, cutoff_info_t *
     pll_unode_t * r_edge = queue[j];
     if (r_edge == orig_prune_edge || r_edge == orig_prune_edge->back) continue;
     if (check_cons && !pllmod_treeinfo_constraint_check_spr(ti, p_edge, r_edge)) continue;
-    pllmod_treeinfo_get_branch_length_all(ti, r_edge, regraft_len.data());
     const unsigned int r_dist = dist[j];
-
-    if (!regraft_with_lengths(ti, prm, p_edge, r_edge)) return PLL_FAILURE;
-    pllmod_treeinfo_set_root(ti, p_edge);
-    pllmod_treeinfo_invalidate_clv(ti, p_edge);
-    get3(ti, p_edge, b1, b2, b3);
-    clamp_branch(ti, p_edge->next, prm.bl_min, prm.bl_max);
-    clamp_branch(ti, p_edge->next->next, prm.bl_min, prm.bl_max);
-    pllmod_treeinfo_invalidate_pmatrix(ti, p_edge->next);
-    pllmod_treeinfo_invalidate_pmatrix(ti, p_edge->next->next);
-    if (!refresh_edge_pmatrix(ti, p_edge->next) || !refresh_edge_pmatrix(ti, p_edge->next->next))
-      return PLL_FAILURE;
-
-    /* score: partial traversal (+ triplet optimisation in thorough mode) */
-    loglh = pllmod_treeinfo_compute_loglh_flex(ti, 1, 0);
-    if (prm.thorough)
+    if (batched)
     {
-      loglh = optimize_bl(p_edge, ti, prm, 1, prm.lh_epsilon_triplet, 1.0);
-      if (!loglh) return PLL_FAILURE;
+      bool found = false;
+      loglh = scores.lookup(r_edge, found);
+      if (!found)
+      {
+        pllmod_set_error(PLLMOD_TREE_ERROR_INVALID_TREE, "Regraft candidate outside the scored neighbourhood");
+        return PLL_FAILURE;
+      }
+      if (loglh > cand.lh)
+      {
+        cand.lh = loglh;
+        cand.r_node = r_edge;
+      }
     }
-    if (loglh > cand.lh)
+    else
     {
-      cand.lh = loglh;
-      cand.r_node = r_edge;
-      get3(ti, p_edge, cand.b1, cand.b2, cand.b3);
-    }
+      pllmod_treeinfo_get_branch_length_all(ti, r_edge, regraft_len.data());
 
-    /* undo: original lengths, prune again, restore the split branch */
-    set3(ti, p_edge, b1, b2, b3);
-    invalidate3(ti, p_edge);
-    pll_unode_t * rejoined = pllmod_utree_prune(p_edge);
-    pllmod_treeinfo_set_branch_length_all(ti, rejoined, regraft_len.data());
-    pllmod_treeinfo_invalidate_pmatrix(ti, rejoined);
-    if (!refresh_edge_pmatrix(ti, p_edge) || !refresh_edge_pmatrix(ti, rejoined)) return PLL_FAILURE;
+      if (!regraft_with_lengths(ti, prm, p_edge, r_edge)) return PLL_FAILURE;
+      pllmod_treeinfo_set_root(ti, p_edge);
+      pllmod_treeinfo_invalidate_clv(ti, p_edge);
+      get3(ti, p_edge, b1, b2, b3);
+      clamp_branch(ti, p_edge->next, prm.bl_min, prm.bl_max);
+      clamp_branch(ti, p_edge->next->next, prm.bl_min, prm.bl_max);
+      pllmod_treeinfo_invalidate_pmatrix(ti, p_edge->next);
+      pllmod_treeinfo_invalidate_pmatrix(ti, p_edge->next->next);
+      if (!refresh_edge_pmatrix(ti, p_edge->next) || !refresh_edge_pmatrix(ti, p_edge->next->next))
+        return PLL_FAILURE;
+
+      /* score: partial traversal (+ triplet optimisation in thorough mode) */
+      loglh = pllmod_treeinfo_compute_loglh_flex(ti, 1, 0);
+      if (prm.thorough)
+      {
+        loglh = optimize_bl(p_edge, ti, prm, 1, prm.lh_epsilon_triplet, 1.0);
+        if (!loglh) return PLL_FAILURE;
+      }
+      if (verify && have_scores)
+      {
+        bool found = false;
+        const double bs = scores.lookup(r_edge, found);
+        if (!found || fabs(bs - loglh) > 1e-9 * fabs(loglh))
+          fprintf(stderr, "[spr verify] prune clv %u candidate clv %u (back %u) dist %u: sequential %.12g batched %.12g%s\n",
+                  p_edge->clv_index, r_edge->clv_index, r_edge->back->clv_index, r_dist, loglh, bs, found ? "" : " (not scored)");
+      }
+      if (loglh > cand.lh)
+      {
+        cand.lh = loglh;
+        cand.r_node = r_edge;
+        get3(ti, p_edge, cand.b1, cand.b2, cand.b3);
+      }
+
+      /* undo: original lengths, prune again, restore the split branch */
+      set3(ti, p_edge, b1, b2, b3);
+      invalidate3(ti, p_edge);
+      pll_unode_t * rejoined = pllmod_utree_prune(p_edge);
+      pllmod_treeinfo_set_branch_length_all(ti, rejoined, regraft_len.data());
+      pllmod_treeinfo_invalidate_pmatrix(ti, rejoined);
+      if (!refresh_edge_pmatrix(ti, p_edge) || !refresh_edge_pmatrix(ti, rejoined)) return PLL_FAILURE;
+    }
 
     bool descend = r_dist < prm.radius_max;
     if (cutoff && loglh < cutoff->lh_start)

@@ -24,6 +24,10 @@ unsigned long long g_d2h_bytes = 0;
 int g_opt_trav_ctas_per_sm = 0; /* 0 = occupancy query */
 int g_opt_trav_reorder = 1;
 int g_opt_fuse_root = 1;
+/* scratch CLV / scaler rows behind the arenas of Gamma-4 DNA partitions: the batched regraft scoring of
+ * pllmod_algo_spr_round keeps one outward-pointing CLV per search depth there (radius_max + 2 rows) */
+int g_opt_scratch_rows = 12;
+int g_opt_spr_batch = 1; /* pllmod_algo_spr_round, fast mode: score all candidates of a pruned subtree in one launch */
 
 static __thread int t_device = -1;
 
@@ -72,6 +76,8 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
   else if (!strcmp(name, "trav_stash")) slot = &g_opt_trav_stash;
   else if (!strcmp(name, "trav_short")) slot = &g_opt_trav_short;
+  else if (!strcmp(name, "scratch_rows")) slot = &g_opt_scratch_rows;
+  else if (!strcmp(name, "spr_batch")) slot = &g_opt_spr_batch;
   else if (!strcmp(name, "trav_debug")) slot = &g_opt_trav_debug;
   else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;
   else if (!strcmp(name, "queued_newton")) slot = &g_opt_queued_newton;
@@ -135,7 +141,11 @@ bool dev_ctx_init(PartCtx * c)
   CUDA_TRY(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking), false);
   c->stream = c->own_stream;
 
-  const unsigned int nclv = p->nodes - c->clv_first;
+  const bool lean_shape = s == 4 && K == 4 && !rate_scalers;
+  c->scratch_rows = lean_shape && g_opt_scratch_rows > 0 ? (unsigned int)g_opt_scratch_rows : 0;
+  c->scratch_mats = c->scratch_rows ? 512 : 0;
+  c->d_score = nullptr; c->score_cap = 0; c->h_score = nullptr;
+  const unsigned int nclv = p->nodes - c->clv_first + c->scratch_rows;
   if (nclv)
   {
     const size_t bytes = (size_t)nclv * c->clv_stride * sizeof(double);
@@ -154,14 +164,14 @@ bool dev_ctx_init(PartCtx * c)
   }
   if (p->scale_buffers)
   {
-    const size_t bytes = (size_t)p->scale_buffers * c->scaler_stride * sizeof(unsigned int);
+    const size_t bytes = (size_t)(p->scale_buffers + c->scratch_rows) * c->scaler_stride * sizeof(unsigned int);
     CUDA_TRY(cudaMalloc(&c->d_scaler, bytes), false);
     CUDA_TRY(cudaMemsetAsync(c->d_scaler, 0, bytes, c->stream), false);
     for (unsigned int i = 0; i < p->scale_buffers; ++i) p->scale_buffer[i] = scaler_dev(c, (int)i);
   }
   if (p->prob_matrices)
   {
-    const size_t bytes = (size_t)p->prob_matrices * c->pmat_elems * sizeof(double);
+    const size_t bytes = (size_t)(p->prob_matrices + c->scratch_mats) * c->pmat_elems * sizeof(double);
     CUDA_TRY(cudaMalloc(&c->d_pmat, bytes), false);
     CUDA_TRY(cudaMemsetAsync(c->d_pmat, 0, bytes, c->stream), false);
     for (unsigned int i = 0; i < p->prob_matrices; ++i) p->pmatrix[i] = c->d_pmat + i * c->pmat_elems;
@@ -169,7 +179,7 @@ bool dev_ctx_init(PartCtx * c)
     {
       CUDA_TRY(cudaMalloc(&c->d_pmat_il, bytes), false);
       CUDA_TRY(cudaMemsetAsync(c->d_pmat_il, 0, bytes, c->stream), false);
-      const size_t cbytes = (size_t)p->prob_matrices * 5 * K * 4 * sizeof(double);
+      const size_t cbytes = (size_t)(p->prob_matrices + c->scratch_mats) * 5 * K * 4 * sizeof(double);
       CUDA_TRY(cudaMalloc(&c->d_pmat_cols, cbytes), false);
       CUDA_TRY(cudaMemsetAsync(c->d_pmat_cols, 0, cbytes, c->stream), false);
     }
@@ -241,7 +251,8 @@ void dev_ctx_destroy(PartCtx * c)
   for (auto & kv : c->sumtables) cudaFree(kv.second);
   c->sumtables.clear();
   cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il); cudaFree(c->d_tiptab);
-  cudaFree(c->d_pmat_cols); cudaFree(c->d_tipcols);
+  cudaFree(c->d_pmat_cols); cudaFree(c->d_tipcols); cudaFree(c->d_score);
+  if (c->h_score) cudaFreeHost(c->h_score);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
   cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag);
   cudaFree(c->d_multi);

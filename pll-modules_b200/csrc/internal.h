@@ -20,6 +20,7 @@
 #define PLLB200_MAGIC 0xB200C1F5u
 #define PLLB200_RESULT_SLOTS 64   /* async reduction results in flight per partition */
 #define PLLB200_MAX_RED_BLOCKS 2048 /* upper bound on reduction grid size */
+#define PLLB200_SCORE_MAX 1024     /* regraft candidates per scoring launch */
 #define PLLB200_MAX_SUMTABLES 64   /* device shadows of caller-owned sumtable buffers per partition */
 
 struct PendingResult
@@ -79,6 +80,12 @@ struct PartCtx
   unsigned long long xred_seq;
   double * d_sumfrag;         /* lazily allocated: 20-state sumtable matrices as DMMA fragment images */
   std::vector<unsigned long long> sumfrag_key;
+  /* batched regraft scoring (k_traversal_dna4.cu): per-warp partial sums + results, pinned landing buffer */
+  double * d_score;
+  size_t score_cap;
+  double * h_score;
+  unsigned int scratch_rows;  /* extra CLV / scaler rows behind the arenas (clv index nodes + r, scaler index scale_buffers + r) */
+  unsigned int scratch_mats;  /* extra P-matrix slots (matrix index prob_matrices + j) */
   double * d_brlen;           /* lazily allocated, [prob_matrices][4]: queued Newton results (k_newton.cu) */
   /* multi-partition Newton (k_newton.cu): descriptor array on the device + the host image it mirrors;
    * used on the first partition of a set; ev_batch orders this partition's stream before a batched launch */
@@ -261,6 +268,10 @@ bool lean_supported(const PartCtx * c);
 bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int count);
 bool flush_trav_dna4_lean(PartCtx * lead, const void * d_args, const BatchKind & k);
 bool launch_tipcols_encode(PartCtx * c, unsigned int tip);
+bool launch_trav_dna4_score(PartCtx * c, const pll_operation_t * ops, const unsigned char * kind, const unsigned int * cand,
+                            unsigned int count, unsigned int ncand, const unsigned int * params_indices, double * host_scores);
+extern int g_opt_scratch_rows;
+extern int g_opt_spr_batch;
 extern int g_opt_trav_stash;
 extern int g_opt_trav_debug;
 bool launch_trav_aa(PartCtx * c, const pll_operation_t * ops, unsigned int count);  /* k_traversal_aa.cu */

@@ -278,7 +278,7 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
   }
   for (unsigned int i = 0; i < count; ++i)
   {
-    if (matrix_indices[i] >= p->prob_matrices || !(branch_lengths[i] >= 0.0))
+    if (matrix_indices[i] >= p->prob_matrices + c->scratch_mats || !(branch_lengths[i] >= 0.0))
     {
       pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid matrix index %u or branch length %g.",
                         matrix_indices[i], branch_lengths[i]);

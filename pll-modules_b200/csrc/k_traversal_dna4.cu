@@ -47,6 +47,11 @@ struct LeanArgs
   const double * pmat_cols; /* [m][column c 0..4][cat k][row i] : 640 B per matrix */
   const unsigned char * tipcols;
   unsigned int clv_stride_b, scaler_stride_b; /* row strides in bytes (< 4 GB: lean_supported) */
+  /* regraft scoring (lean_op_special) */
+  double * score_out;        /* [candidate][score_stride] per-warp partial sums */
+  const unsigned int * weights;
+  unsigned int score_stride;
+  double wpi[16];            /* [category][state]: rate weight x frequency */
   unsigned int dbg; /* timing ablations only (option trav_debug): 1 no tip loads, 2 no CLV stores, 4 no scaler stores */
 };
 
@@ -457,19 +462,18 @@ __device__ __forceinline__ void lean_op_hot(const LeanArgs & a, const LaneCtx & 
   t2 = n2;
 }
 
-/* any operation: sources, scaler sources and flags read at run time */
+/* both child terms of an operation whose sources are read at run time: acc <- (M2 x child2) * (M1 x child1),
+ * sc <- sum of the children's scaler counts (valid in the lanes with want_scalers).  one_child: child 2 only. */
 template <bool FULL>
-__device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
-                                                double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+__device__ __forceinline__ void lean_children_generic(const LeanArgs & a, const LaneCtx & L, const uint4 & w0,
+                                                      const uint4 & w1, unsigned int st, bool want_scalers, bool one_child,
+                                                      double (&acc)[4][4], const uint4 & fsc, unsigned int t1,
+                                                      unsigned int t2, uint4 & sc)
 {
-  const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
   const unsigned int fa = w1.z >> 24, fb = w1.w >> 24;
   const unsigned int src1 = LOPA_SRC1(fa), src2 = LOPA_SRC2(fa);
-  unsigned int n1, n2;
-  lean_prefetch<FULL>(a, L, rec + 32, st ^ 1u, n1, n2);
-
   uint4 q1 = make_uint4(0, 0, 0, 0), q2 = make_uint4(0, 0, 0, 0);
-  if ((fa & LOPA_PS) && L.sc_lane())
+  if (want_scalers)
   {
     const unsigned int ss1 = LOPB_SS1(fb), ss2 = LOPB_SS2(fb);
     if (ss1 == SSRC_GLOBAL)
@@ -508,7 +512,8 @@ __device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCt
   else
     transform_inplace(matR, acc);
 
-  const uint4 sc = make_uint4(q1.x + q2.x, q1.y + q2.y, q1.z + q2.z, q1.w + q2.w);
+  sc = make_uint4(q1.x + q2.x, q1.y + q2.y, q1.z + q2.z, q1.w + q2.w);
+  if (one_child) return;
 
   /* ---- acc *= term of child 1 ---- */
   if (src1 == SRC_TIP)
@@ -534,7 +539,20 @@ __device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCt
     }
     multiply_by_term(matL, v1, acc);
   }
-  if (src1 == SRC_TIP && src2 == SRC_TIP)
+}
+
+/* any operation: sources, scaler sources and flags read at run time */
+template <bool FULL>
+__device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
+                                                double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+{
+  const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
+  const unsigned int fa = w1.z >> 24, fb = w1.w >> 24;
+  unsigned int n1, n2;
+  lean_prefetch<FULL>(a, L, rec + 32, st ^ 1u, n1, n2);
+  uint4 sc;
+  lean_children_generic<FULL>(a, L, w0, w1, st, (fa & LOPA_PS) && L.sc_lane(), false, acc, fsc, t1, t2, sc);
+  if (LOPA_SRC1(fa) == SRC_TIP && LOPA_SRC2(fa) == SRC_TIP)
     lean_finish<FULL, true>(a, L, w0, fa, fb, acc, sc, fsc);
   else
     lean_finish<FULL, false>(a, L, w0, fa, fb, acc, sc, fsc);
@@ -542,10 +560,78 @@ __device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCt
   t2 = n2;
 }
 
+/* The two operations of a batched regraft scoring list (algo_search.cpp, pllmod_algo_spr_round: every candidate
+ * branch of one pruned subtree in ONE launch; reference loop: src/algorithm/algo_search.c:727-860).
+ *   SETUP (once, first): U[k][i] = w_k pi_i sum_j P_z[i][j] S[k][j] for the pruned subtree's CLV S over the prune
+ *     branch, into stash slot 1 (with S's scaler counts): the part of the edge log-likelihood
+ *     (core_likelihood.c:1388-1490) that is the same for every candidate.
+ *   SCORE: X = (M a)(M b), the CLV the new inner node would get between the two halves of the candidate branch
+ *     (a: the CLV pointing away from the pruning point, b: the one pointing towards it), is never stored: the site
+ *     likelihood sum_k sum_i X[k][i] U[k][i] goes through log, scaler term and pattern weight, the warp adds its
+ *     32 sites and accumulates into score_out[candidate][warp].  X is not rescaled (its children's counts only
+ *     enter the log term; 2^-768 is still a normal double), which changes nothing mathematically. */
+template <bool FULL>
+__device__ __forceinline__ void lean_op_special(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
+                                                double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+{
+  const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
+  unsigned int n1, n2;
+  lean_prefetch<FULL>(a, L, rec + 32, st ^ 1u, n1, n2);
+  const bool setup = w0.x == LSPECIAL_SETUP;
+  uint4 sc;
+  lean_children_generic<FULL>(a, L, w0, w1, st, L.sc_lane(), setup, acc, fsc, t1, t2, sc);
+  const unsigned int k = L.k();
+  const unsigned int ul = L.stash_lane() + L4_STASH_B; /* stash slot 1 */
+  if (setup)
+  {
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+    {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) acc[r][i] *= a.wpi[k * 4 + i];
+      sts_d2(ul + r * 1024, acc[r][0], acc[r][1]);
+      sts_d2(ul + r * 1024 + 512, acc[r][2], acc[r][3]);
+    }
+    if (L.sc_lane()) sts_u4(L.sst_lane() + 128, sc);
+  }
+  else
+  {
+    double lh[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+    {
+      const double2 x = lds_d2(ul + r * 1024), y = lds_d2(ul + r * 1024 + 512);
+      lh[r] = acc[r][0] * x.x + acc[r][1] * x.y + acc[r][2] * y.x + acc[r][3] * y.y;
+    }
+    /* sum over the 4 categories (the 4 lanes of a site group), then lane k finishes site s0 + k */
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+    {
+      lh[r] += __shfl_xor_sync(0xffffffffu, lh[r], 1);
+      lh[r] += __shfl_xor_sync(0xffffffffu, lh[r], 2);
+    }
+    const uint4 su = lds_u4(L.sst_lane() + 128);
+    /* the children's counts live in the group's first lane */
+    const int lead = (int)(L.lane & ~3u);
+    const unsigned int cx = __shfl_sync(0xffffffffu, sc.x, lead), cy = __shfl_sync(0xffffffffu, sc.y, lead);
+    const unsigned int cz = __shfl_sync(0xffffffffu, sc.z, lead), cw = __shfl_sync(0xffffffffu, sc.w, lead);
+    const double mine = k == 0 ? lh[0] : (k == 1 ? lh[1] : (k == 2 ? lh[2] : lh[3]));
+    const unsigned int cnt = k == 0 ? cx + su.x : (k == 1 ? cy + su.y : (k == 2 ? cz + su.z : cw + su.w));
+    double v = 0.0;
+    if (FULL || ((L.actmask >> k) & 1u)) v = (log(mine) + (double)cnt * LN_SCALE_THRESHOLD) * (double)a.weights[L.s0 + k];
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    if (L.lane == 0) a.score_out[(size_t)w0.w * a.score_stride + (blockIdx.x * L4_WARPS + (threadIdx.x >> 5))] += v;
+  }
+  fsc = make_uint4(0, 0, 0, 0);
+  t1 = n1;
+  t2 = n2;
+}
+
 /* One chunk (32 consecutive sites) through the staged operations [0, nseg); the record after the last one is
  * all zero (a harmless prefetch target).  wsm: this warp's shared-memory block (shared-window address), s0:
  * first of the lane's 4 consecutive sites.  FULL: all 32 sites exist — only then the specialised bodies run. */
-template <bool FULL>
+template <bool FULL, bool SCORING>
 __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops, unsigned int nseg, unsigned int s0,
                                            int lane, unsigned int wsm)
 {
@@ -578,12 +664,9 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
   {
     const unsigned int st = ((rec - sops) >> 5) & 1u;
     __syncwarp(); /* every lane is done with stage st^1 (previous operation): the bodies refill it for the next one */
-    unsigned int type = 0;
-    if (FULL)
-    {
-      type = LOPB_TYPE(lds_u1(rec + 28) >> 24);
-      if (__any_sync(0xffffffffu, ((t1 | t2) & 0x80808080u) != 0u)) type = 0; /* ambiguity codes: generic body */
-    }
+    unsigned int type = LOPB_TYPE(lds_u1(rec + 28) >> 24);
+    if (!(SCORING && type == LTYPE_SPECIAL) && (!FULL || __any_sync(0xffffffffu, ((t1 | t2) & 0x80808080u) != 0u)))
+      type = 0; /* partial chunk, or ambiguity codes: generic body */
     switch (type)
     {
       case LTYPE_TIP_TIP: lean_op_hot<SRC_TIP, SRC_TIP>(a, L, rec, st, acc, fsc, t1, t2); break;
@@ -592,6 +675,9 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
       case LTYPE_GLOBAL_FWD: lean_op_hot<SRC_GLOBAL, SRC_FWD>(a, L, rec, st, acc, fsc, t1, t2); break;
       case LTYPE_TIP_GLOBAL: lean_op_hot<SRC_TIP, SRC_GLOBAL>(a, L, rec, st, acc, fsc, t1, t2); break;
       case LTYPE_GLOBAL_GLOBAL: lean_op_hot<SRC_GLOBAL, SRC_GLOBAL>(a, L, rec, st, acc, fsc, t1, t2); break;
+      case LTYPE_SPECIAL:
+        if (SCORING) lean_op_special<FULL>(a, L, rec, st, acc, fsc, t1, t2); /* only the scoring kernel carries this body */
+        break;
       default: lean_op_generic<FULL>(a, L, rec, st, acc, fsc, t1, t2); break;
     }
   }
@@ -601,14 +687,14 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
   __syncwarp();
 }
 
-template <int TAG>
+template <int TAG, bool SCORING>
 __device__ __noinline__ void lean_chunk_tail(const LeanArgs & a, unsigned int sops, unsigned int nseg, unsigned int s0,
                                              int lane, unsigned int wsm)
 {
-  lean_chunk<false>(a, sops, nseg, s0, lane, wsm);
+  lean_chunk<false, SCORING>(a, sops, nseg, s0, lane, wsm);
 }
 
-template <int TAG>
+template <int TAG, bool SCORING>
 __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
 {
   extern __shared__ __align__(128) unsigned char l4_smem[];
@@ -636,14 +722,16 @@ __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
     {
       const unsigned int s0 = (unsigned int)(chunk * 32) + (unsigned int)(lane >> 2) * 4;
       if ((chunk + 1) * 32 <= a.sites)
-        lean_chunk<true>(a, sops, nseg, s0, lane, wsm);
+        lean_chunk<true, SCORING>(a, sops, nseg, s0, lane, wsm);
       else
-        lean_chunk_tail<TAG>(a, sops, nseg, s0, lane, wsm);
+        lean_chunk_tail<TAG, SCORING>(a, sops, nseg, s0, lane, wsm);
     }
   }
 }
 
-__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_kernel(LeanArgs a) { trav_dna4_body<0>(a); }
+__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_kernel(LeanArgs a) { trav_dna4_body<0, false>(a); }
+/* the same kernel with the SETUP / SCORE bodies of the batched regraft scoring (lean_op_special) */
+__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_score_kernel(LeanArgs a) { trav_dna4_body<2, true>(a); }
 
 /* many partitions in one launch (blockIdx.y = partition; batch mode, internal.h) */
 __global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_batch_kernel(const LeanArgs * __restrict__ arr)
@@ -653,7 +741,7 @@ __global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_batch_kernel(const
     reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
   __syncthreads();
   const LeanArgs a = sa;
-  trav_dna4_body<1>(a);
+  trav_dna4_body<1, false>(a);
 }
 
 /* ---- tip column codes ---------------------------------------------------------------------------- */
@@ -696,6 +784,9 @@ int g_opt_trav_debug = 0; /* LeanArgs::dbg */
 
 static size_t lean_smem_bytes(unsigned int seg) { return (size_t)(seg + 4) * 32 + (size_t)L4_WARPS * L4_WARP_SM; }
 
+static void lean_fill_args(PartCtx * c, LeanArgs & a, const LeanOp * d_ops, unsigned int count, unsigned int seg);
+static bool lean_set_smem_attr();
+
 bool lean_supported(const PartCtx * c)
 {
   const pll_partition_t * p = &c->pub;
@@ -716,35 +807,13 @@ bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int cou
     pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Operation list cannot be packed (matrix index >= 2^24).");
     return false;
   }
-  static bool attr_set = false;
-  if (!attr_set)
-  {
-    const int maxb = (int)lean_smem_bytes(L4_SEG_MAX);
-    if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
-                         "trav_dna4_kernel smem") ||
-        !pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
-                         "trav_dna4_batch_kernel smem"))
-      return false;
-    attr_set = true;
-  }
+  if (!lean_set_smem_attr()) return false;
   const bool collect = batch_collects(BK_TRAV_DNA4);
   const LeanOp * d_ops = collect ? (const LeanOp *)batch_pool_add(lean.data(), sizeof(LeanOp) * count)
                                  : (const LeanOp *)dev_stage_small(c, lean.data(), sizeof(LeanOp) * count);
   if (!d_ops) return false;
   LeanArgs a;
-  a.ops = d_ops;
-  a.nops = count;
-  a.sites = c->sites_alloc;
-  a.seg = seg;
-  a.tip_stride = (unsigned int)c->tip_stride;
-  a.clv = reinterpret_cast<char *>(c->d_clv);
-  a.scaler = reinterpret_cast<char *>(c->d_scaler);
-  a.pmat_il = c->d_pmat_il;
-  a.pmat_cols = c->d_pmat_cols;
-  a.tipcols = c->d_tipcols;
-  a.dbg = (unsigned int)g_opt_trav_debug;
-  a.clv_stride_b = (unsigned int)(c->clv_stride * sizeof(double));
-  a.scaler_stride_b = (unsigned int)(c->scaler_stride * sizeof(unsigned int));
+  lean_fill_args(c, a, d_ops, count, seg);
 
   const unsigned long long nchunks = ((unsigned long long)a.sites + 31) / 32;
   unsigned long long blocks = (nchunks + L4_WARPS - 1) / L4_WARPS;
@@ -761,6 +830,136 @@ bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int cou
   trav_dna4_kernel<<<(unsigned int)blocks, L4_WARPS * 32, lean_smem_bytes(seg), xstream(c)>>>(a);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_kernel launch");
+}
+
+/* ---- batched regraft scoring (algo_search.cpp) ------------------------------------------------------ */
+
+/* score[c] = sum over the launch's warps of score_out[c][warp], in a fixed order (deterministic) */
+__global__ void __launch_bounds__(256) spr_score_reduce_kernel(const double * __restrict__ part, unsigned int stride,
+                                                              double * __restrict__ out)
+{
+  __shared__ double s_red[256];
+  const double * row = part + (size_t)blockIdx.x * stride;
+  double x = 0.0;
+  for (unsigned int i = threadIdx.x; i < stride; i += 256) x += row[i];
+  s_red[threadIdx.x] = x;
+  __syncthreads();
+  for (unsigned int h = 128; h > 0; h >>= 1)
+  {
+    if (threadIdx.x < h) s_red[threadIdx.x] += s_red[threadIdx.x + h];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[blockIdx.x] = s_red[0];
+}
+
+static void lean_fill_args(PartCtx * c, LeanArgs & a, const LeanOp * d_ops, unsigned int count, unsigned int seg)
+{
+  memset(&a, 0, sizeof(a));
+  a.ops = d_ops;
+  a.nops = count;
+  a.sites = c->sites_alloc;
+  a.seg = seg;
+  a.tip_stride = (unsigned int)c->tip_stride;
+  a.clv = reinterpret_cast<char *>(c->d_clv);
+  a.scaler = reinterpret_cast<char *>(c->d_scaler);
+  a.pmat_il = c->d_pmat_il;
+  a.pmat_cols = c->d_pmat_cols;
+  a.tipcols = c->d_tipcols;
+  a.dbg = (unsigned int)g_opt_trav_debug;
+  a.clv_stride_b = (unsigned int)(c->clv_stride * sizeof(double));
+  a.scaler_stride_b = (unsigned int)(c->scaler_stride * sizeof(unsigned int));
+}
+
+static bool lean_set_smem_attr()
+{
+  static bool attr_set = false;
+  if (attr_set) return true;
+  const int maxb = (int)lean_smem_bytes(L4_SEG_MAX);
+  if (!pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
+                       "trav_dna4_kernel smem") ||
+      !pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
+                       "trav_dna4_batch_kernel smem") ||
+      !pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
+                       "trav_dna4_score_kernel smem"))
+    return false;
+  attr_set = true;
+  return true;
+}
+
+/* One launch over a list that mixes ordinary operations (kind 0; they may write scratch CLV rows: clv index
+ * nodes + r, scaler index scale_buffers + r), one SETUP (kind LSPECIAL_SETUP, first) and SCORE operations (kind
+ * LSPECIAL_SCORE, cand[i] = candidate number).  Special operations name their operands like ordinary ones
+ * (SETUP: child 2 = the pruned subtree over the prune branch; SCORE: the two CLVs either side of the candidate
+ * branch, both over the candidate's half-length matrix) and a parent row nobody reads.  host_scores[ncand] comes
+ * back after a stream synchronisation.  Preconditions (checked by the caller): lean_supported, no invariant
+ * sites, no ascertainment bias. */
+bool launch_trav_dna4_score(PartCtx * c, const pll_operation_t * ops, const unsigned char * kind,
+                            const unsigned int * cand, unsigned int count, unsigned int ncand,
+                            const unsigned int * params_indices, double * host_scores)
+{
+  pll_partition_t * p = &c->pub;
+  const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
+  if (!dev_sync_inputs(c)) return false;
+  static thread_local std::vector<LeanOp> lean;
+  const unsigned int seg = std::min<unsigned int>(L4_SEG_MAX, count);
+  /* stash slot 1 holds the SETUP result for the whole list (one slot is left for ordinary values) and does not
+   * survive a segment boundary: the list must fit one segment */
+  if (count > L4_SEG_MAX || ncand > PLLB200_SCORE_MAX ||
+      !trav_lean_resolve(ops, count, pattern_tip ? p->tips : 0, c->clv_first, seg, 1, true, lean, nullptr))
+  {
+    pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Regraft scoring list cannot be packed.");
+    return false;
+  }
+  for (unsigned int i = 0; i < count; ++i)
+    if (kind[i])
+    {
+      LeanOp & d = lean[i];
+      unsigned int fa = d.m1f >> 24, fb = d.m2f >> 24;
+      fa &= ~(unsigned int)(LOPA_PS | LOPA_STASH_W);
+      fb = (fb & 0x0fu) | ((unsigned int)LTYPE_SPECIAL << 5);
+      d.m1f = (d.m1f & LOP_MATRIX_MASK) | (fa << 24);
+      d.m2f = (d.m2f & LOP_MATRIX_MASK) | (fb << 24);
+      d.p = kind[i];
+      d.ps = cand[i];
+    }
+  if (!lean_set_smem_attr()) return false;
+  const LeanOp * d_ops = (const LeanOp *)dev_stage(c, lean.data(), sizeof(LeanOp) * count);
+  if (!d_ops) return false;
+  LeanArgs a;
+  lean_fill_args(c, a, d_ops, count, seg);
+  const unsigned long long nchunks = ((unsigned long long)a.sites + 31) / 32;
+  unsigned long long blocks = std::min<unsigned long long>((nchunks + L4_WARPS - 1) / L4_WARPS, (unsigned long long)c->sm_count * 2);
+  if (blocks < 1) blocks = 1;
+  const unsigned int stride = (unsigned int)blocks * L4_WARPS;
+  const size_t need = (size_t)ncand * stride + ncand;
+  if (c->score_cap < need)
+  {
+    CUDA_TRY(cudaStreamSynchronize(c->stream), false);
+    cudaFree(c->d_score);
+    c->d_score = nullptr;
+    c->score_cap = 0;
+    CUDA_TRY(cudaMalloc(&c->d_score, need * 2 * sizeof(double)), false);
+    c->score_cap = need * 2;
+  }
+  if (!c->h_score) CUDA_TRY(cudaHostAlloc(&c->h_score, PLLB200_SCORE_MAX * sizeof(double), cudaHostAllocDefault), false);
+  CUDA_TRY(cudaMemsetAsync(c->d_score, 0, (size_t)ncand * stride * sizeof(double), c->stream), false);
+  a.score_out = c->d_score;
+  a.score_stride = stride;
+  a.weights = c->d_weights;
+  for (unsigned int k = 0; k < 4; ++k)
+    for (unsigned int i = 0; i < 4; ++i) a.wpi[k * 4 + i] = p->rate_weights[k] * p->frequencies[params_indices[k]][i];
+  trav_dna4_score_kernel<<<(unsigned int)blocks, L4_WARPS * 32, lean_smem_bytes(seg), c->stream>>>(a);
+  ++g_kernel_launches;
+  if (!pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_score_kernel launch")) return false;
+  double * d_out = c->d_score + (size_t)ncand * stride;
+  spr_score_reduce_kernel<<<ncand, 256, 0, c->stream>>>(c->d_score, stride, d_out);
+  ++g_kernel_launches;
+  if (!pllb200_cuda_ok(cudaGetLastError(), "spr_score_reduce_kernel launch")) return false;
+  CUDA_TRY(cudaMemcpyAsync(c->h_score, d_out, sizeof(double) * ncand, cudaMemcpyDeviceToHost, c->stream), false);
+  g_d2h_bytes += sizeof(double) * ncand;
+  if (!dev_flush(c)) return false;
+  memcpy(host_scores, c->h_score, sizeof(double) * ncand);
+  return true;
 }
 
 bool flush_trav_dna4_lean(PartCtx * lead, const void * d_args, const BatchKind & k)

@@ -49,7 +49,9 @@ enum { SSRC_NONE = 0, SSRC_GLOBAL = 1, SSRC_SAME = 2 }; /* SAME: from where the 
 /* specialised body of the kernel (0 = generic).  Set when the parent has a scaler row and every child's scaler
  * counts come from where its CLV comes from (tip: none, forwarded / stash: same, global: global) */
 #define LOPB_TYPE(f) (((f) >> 5) & 7u)
-enum { LTYPE_GENERIC = 0, LTYPE_TIP_TIP, LTYPE_TIP_FWD, LTYPE_STASH_FWD, LTYPE_GLOBAL_FWD, LTYPE_TIP_GLOBAL, LTYPE_GLOBAL_GLOBAL };
+enum { LTYPE_GENERIC = 0, LTYPE_TIP_TIP, LTYPE_TIP_FWD, LTYPE_STASH_FWD, LTYPE_GLOBAL_FWD, LTYPE_TIP_GLOBAL, LTYPE_GLOBAL_GLOBAL,
+       LTYPE_SPECIAL /* regraft scoring: LeanOp::p = LSPECIAL_*, LeanOp::ps = candidate number */ };
+enum { LSPECIAL_SETUP = 1, LSPECIAL_SCORE = 2 };
 
 struct LeanStats
 {

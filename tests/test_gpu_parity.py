@@ -526,24 +526,72 @@ def test_model_parameter_optimisation_matches_reference(name):
 
 
 # ---- SPR round over device-resident CLVs (BASELINE configs[4]) ----
+@pytest.mark.parametrize("batch", [1, 0], ids=["batched_scoring", "sequential_scoring"])
 @pytest.mark.parametrize("name", sorted(OPT_GOLD["spr"].keys()))
-def test_spr_round_ends_on_the_reference_topology(name):
+def test_spr_round_ends_on_the_reference_topology(name, batch):
     """pllmod_algo_spr_round: identical final topology (every bipartition; RF distance 0), logL within the
-    reference's own 1e-6 absolute assert (algo_search.c:1453), branch lengths within the NR tolerance, and
-    the same number of CLV operations (= the same candidate moves were evaluated in the same order)."""
+    reference's own 1e-6 absolute assert (algo_search.c:1453), branch lengths within the NR tolerance, identical
+    cutoff statistics (= the same candidate moves were visited in the same order) — with the candidates of a
+    pruned subtree scored in one launch (spr_batch 1, the default; eligible: fast mode, one DNA Gamma-4 partition)
+    and one after the other as the reference does (spr_batch 0), where the number of CLV operations must also
+    be the reference's."""
     case = OPT_GOLD["spr"][name]
-    with Harness("b200", **case["args"]) as h:
-        start = h.loglh()
-        assert rel(start, case["start_loglh"]) < 1e-8
-        lh, co = h.spr_round(**case["spr"])
-        hs, ln = h.topology_signature()
-        ops = h.ops_counter()
+    pkg = load_product_package()
+    pkg.set_option("spr_batch", batch)
+    try:
+        with Harness("b200", **case["args"]) as h:
+            start = h.loglh()
+            assert rel(start, case["start_loglh"]) < 1e-8
+            pkg.reset_stats()
+            lh, co = h.spr_round(**case["spr"])
+            launches = pkg.stats()["kernel_launches"]
+            hs, ln = h.topology_signature()
+            ops = h.ops_counter()
+    finally:
+        pkg.set_option("spr_batch", 1)
     assert lh != 0.0
     assert [str(int(x)) for x in hs] == case["splits"], "topology differs from the reference"
     assert abs(lh - case["loglh"]) <= 1e-6 * max(1.0, abs(case["loglh"]) * 1e-3), (lh, case["loglh"])
     np.testing.assert_allclose(ln, case["brlens"], rtol=1e-4, atol=1e-6)
-    assert ops == case["ops"]
     np.testing.assert_allclose(co, case["cutoff"], rtol=1e-6)
+    eligible = (not case["spr"].get("thorough")) and case["args"].get("states", 4) == 4 \
+        and not isinstance(case["args"]["sites"], list)
+    if batch and eligible:
+        assert ops < case["ops"], "batched scoring did not run"
+        test_spr_round_ends_on_the_reference_topology.launches[name] = launches
+    else:
+        assert ops == case["ops"]
+        if eligible and name in test_spr_round_ends_on_the_reference_topology.launches:
+            # one scoring launch per pruned subtree instead of ~5 launches per candidate (the final all-branch
+            # optimisation of the kept topologies, the larger part on these small trees, is the same in both)
+            assert test_spr_round_ends_on_the_reference_topology.launches[name] < launches
+
+
+test_spr_round_ends_on_the_reference_topology.launches = {}
+
+
+def test_spr_round_batched_scoring_equals_sequential_on_a_larger_tree():
+    """150 taxa x 3000 sites, radius 1..5 with the cutoff rule on: the batched candidate scoring must lead the
+    round through the same moves as the sequential one (same cutoff statistics, same final topology and logL)."""
+    pkg = load_product_package()
+    out = {}
+    try:
+        for batch in (1, 0):
+            pkg.set_option("spr_batch", batch)
+            with Harness("b200", tips=150, sites=3000, seed=23) as h:
+                h.loglh(0)
+                pkg.reset_stats()
+                lh, co = h.spr_round(thorough=False, radius_min=1, radius_max=5, ntopol_keep=10, smoothings=16,
+                                     epsilon=1.0, bl_min=1e-6)
+                hs, ln = h.topology_signature()
+                out[batch] = (lh, co, [int(x) for x in hs], ln, pkg.stats()["kernel_launches"])
+    finally:
+        pkg.set_option("spr_batch", 1)
+    assert out[1][2] == out[0][2]
+    assert rel(out[1][0], out[0][0]) < 1e-10, (out[1][0], out[0][0])
+    np.testing.assert_allclose(out[1][1], out[0][1], rtol=1e-9)
+    np.testing.assert_allclose(out[1][3], out[0][3], rtol=1e-6, atol=1e-8)
+    assert out[1][4] < out[0][4], (out[1][4], out[0][4])
 
 
 # ---- treeinfo-level model optimisers, all partitions in lock step (SURVEY.md §8f rank 2) ----
