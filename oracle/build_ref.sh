@@ -41,6 +41,6 @@ gcc -shared -Wl,-Bsymbolic -o "$O/libpll_ref.so" l_*.o m_*.o -lm
 # the same-source harness (oracle/harness.c) compiled against the reference headers + library
 if [ -f "$HERE/harness.c" ]; then
   gcc -O2 -fPIC -shared -Wl,-Bsymbolic -DHARNESS_REFERENCE -I$S -I$M -I$M/tree -I$M/optimize -I$M/algorithm -I$M/util -I$M/msa -I$M/binary -w \
-      "$HERE/harness.c" -o "$O/libharness_ref.so" -L"$O" -l:libpll_ref.so -Wl,-rpath,'$ORIGIN' -lm
+      "$HERE/harness.c" -o "$O/libharness_ref.so" -L"$O" -l:libpll_ref.so -Wl,-rpath,'$ORIGIN' -lm -lpthread
 fi
 echo "build_ref: ok -> $O/libpll_ref.so"

@@ -107,6 +107,8 @@ SPR_CASES = [
     ("aa16_fast", dict(tips=16, sites=150, states=20, seed=3), dict(thorough=False, radius_max=4)),
     ("multi_unlinked_thorough", dict(tips=14, sites=[200, 150], states=[4, 4], alpha=[0.5, 1.0], linkage=2, seed=9),
      dict(thorough=True, radius_max=3, ntopol_keep=3)),
+    # a tree of BASELINE configs[4]'s kind at a size the reference finishes in seconds
+    ("dna200_fast_2k", dict(tips=200, sites=2000, seed=31), dict(thorough=False, radius_max=5)),
 ]
 
 
@@ -125,6 +127,28 @@ ALGO_OPT_CASES = [
 ]
 
 
+def spr_case(PH, name, kw, skw):
+    with PH.Harness("ref", **kw) as h:
+        start = h.loglh()
+        lh, co = h.spr_round(**skw)
+        hs, ln = h.topology_signature()
+        print(name, start, lh, h.ops_counter())
+        return dict(args=kw, spr=skw, start_loglh=start, loglh=lh, cutoff=co.tolist(),
+                    splits=[str(int(x)) for x in hs], brlens=ln.tolist(), ops=h.ops_counter())
+
+
+def add_missing_spr():
+    """--spr-missing: run only the SPR cases that tests/golden/ref_opt.json does not hold yet and merge them in."""
+    import pllharness as PH
+    path = os.path.join(GOLD, "ref_opt.json")
+    out = json.load(open(path))
+    for name, kw, skw in SPR_CASES:
+        if name not in out["spr"]:
+            out["spr"][name] = spr_case(PH, name, kw, skw)
+    with open(path, "w") as f:
+        json.dump(out, f, indent=1)
+
+
 def dump_opt():
     import pllharness as PH
     out = {"brent": [], "lbfgsb": [], "model": {}, "spr": {}, "algo_opt": {}}
@@ -140,13 +164,7 @@ def dump_opt():
                                          models=models, treeinfo=tp, brlens=h.branch_lengths().tolist())
             print(name, start, score, after)
     for name, kw, skw in SPR_CASES:
-        with PH.Harness("ref", **kw) as h:
-            start = h.loglh()
-            lh, co = h.spr_round(**skw)
-            hs, ln = h.topology_signature()
-            out["spr"][name] = dict(args=kw, spr=skw, start_loglh=start, loglh=lh, cutoff=co.tolist(),
-                                    splits=[str(int(x)) for x in hs], brlens=ln.tolist(), ops=h.ops_counter())
-            print(name, start, lh, h.ops_counter())
+        out["spr"][name] = spr_case(PH, name, kw, skw)
     for fn, lo, g, hi, tol in BRENT_CASES:
         r = PH.test_brent("ref", fn, lo, g, hi, tol)
         out["brent"].append(dict(args=[fn, lo, g, hi, tol], x=float(r["x"]), fx=float(r["fx"]), evals=r["evals"]))
@@ -171,6 +189,8 @@ def dump_opt():
 
 
 def main():
+    if "--spr-missing" in sys.argv:
+        return add_missing_spr()
     if "--opt-only" in sys.argv:
         return dump_opt()
     os.makedirs(GOLD, exist_ok=True)

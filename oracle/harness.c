@@ -1167,3 +1167,94 @@ unsigned int h_ancestral(void * hv, double * out, double * labels_sum)
   pllmod_treeinfo_destroy_ancestral(a);
   return n;
 }
+
+/* ---- a13 entry points that the other drivers do not reach (pll_optimize.c:1115,1146,1182) ---------- */
+
+/* pllmod_opt_optimize_branch_lengths_iterative on partition 0 (all branches, legacy driver) */
+double h_optimize_branch_lengths_iterative(void * hv, int smoothings, double tolerance)
+{
+  harness_t * h = (harness_t *)hv;
+  return pllmod_opt_optimize_branch_lengths_iterative(h->parts[0], h->ti->root, h->param_idx[0], 0, 0, tolerance,
+                                                      smoothings, 1);
+}
+
+/* pllmod_opt_compute_edge_loglikelihood_multi over all partitions at the edge of subnode node_index;
+ * persite (may be NULL): sum of sites of all partitions doubles */
+double h_edge_loglh_multi(void * hv, unsigned int node_index, double * persite)
+{
+  harness_t * h = (harness_t *)hv;
+  pllmod_treeinfo_t * ti = h->ti;
+  pll_unode_t * n = ti->subnodes[node_index];
+  return pllmod_opt_compute_edge_loglikelihood_multi(ti->partitions, ti->partition_count, n->clv_index,
+                                                     n->scaler_index, n->back->clv_index, n->back->scaler_index,
+                                                     n->pmatrix_index, ti->param_indices, persite,
+                                                     ti->parallel_context, ti->parallel_reduce_cb);
+}
+
+/* pllmod_opt_derivative_func: the Newton callback of the single-partition driver, fed by hand */
+int h_derivative_func(void * hv, unsigned int p, unsigned int node_index, const double * brlens, int n,
+                      double * df, double * ddf)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_unode_t * e = h->ti->subnodes[node_index];
+  if (!pll_update_sumtable(h->parts[p], e->clv_index, e->back->clv_index, e->scaler_index,
+                           e->back->scaler_index, h->param_idx[p], h->sumtables[p]))
+    return 0;
+  pll_optimize_options_t o;
+  memset(&o, 0, sizeof(o));
+  o.lk_params.partition = h->parts[p];
+  o.lk_params.rooted = 0;
+  o.lk_params.params_indices = h->param_idx[p];
+  o.lk_params.where.unrooted_t.parent_clv_index = e->clv_index;
+  o.lk_params.where.unrooted_t.parent_scaler_index = e->scaler_index;
+  o.lk_params.where.unrooted_t.child_clv_index = e->back->clv_index;
+  o.lk_params.where.unrooted_t.child_scaler_index = e->back->scaler_index;
+  o.lk_params.where.unrooted_t.edge_pmatrix_index = e->pmatrix_index;
+  o.sumtable = h->sumtables[p];
+  for (int i = 0; i < n; ++i) pllmod_opt_derivative_func(&o, brlens[i], &df[i], &ddf[i]);
+  return 1;
+}
+
+/* ---- thread safety across partitions (SURVEY.md 8b "Threading"): every handle is driven from its own
+ *      pthread at the same time — full logL, one Newton-Raphson smoothing pass, logL again.
+ *      out[3 * i + {0,1,2}] per handle. ---- */
+#include <pthread.h>
+typedef struct
+{
+  harness_t * h;
+  double * out;
+} thread_job_t;
+
+static void * thread_job(void * arg)
+{
+  thread_job_t * j = (thread_job_t *)arg;
+  pllmod_treeinfo_t * ti = j->h->ti;
+  j->out[0] = pllmod_treeinfo_compute_loglh(ti, 0);
+  j->out[1] = pllmod_opt_optimize_branch_lengths_local_multi(
+      ti->partitions, ti->partition_count, ti->root, ti->param_indices, ti->deriv_precomp, ti->branch_lengths,
+      ti->brlen_scalers, 0, 0, 0.1, 2, -1, 1, PLLMOD_OPT_BLO_NEWTON_FAST, ti->brlen_linkage, ti->parallel_context,
+      ti->parallel_reduce_cb);
+  j->out[2] = pllmod_treeinfo_compute_loglh(ti, 0);
+  return NULL;
+}
+
+int h_run_concurrently(void ** handles, int n, int threaded, double * out)
+{
+  pthread_t th[16];
+  thread_job_t jobs[16];
+  if (n > 16) return 0;
+  for (int i = 0; i < n; ++i)
+  {
+    jobs[i].h = (harness_t *)handles[i];
+    jobs[i].out = out + 3 * i;
+  }
+  if (!threaded)
+  {
+    for (int i = 0; i < n; ++i) thread_job(&jobs[i]);
+    return 1;
+  }
+  for (int i = 0; i < n; ++i)
+    if (pthread_create(&th[i], NULL, thread_job, &jobs[i])) return 0;
+  for (int i = 0; i < n; ++i) pthread_join(th[i], NULL);
+  return 1;
+}

@@ -92,7 +92,7 @@ def build_oracle():
         so = os.path.join(LIBDIR, "libharness_b200.so")
         if not _newer(so, [harness, LIB, os.path.join(ROOT, "include", "pllb200.h")]):
             _run(["gcc", "-O2", "-fPIC", "-shared", "-I" + os.path.join(ROOT, "include"), harness,
-                  "-o", so, "-L" + LIBDIR, "-l:libpll_b200.so", "-Wl,-rpath,$ORIGIN", "-lm"])
+                  "-o", so, "-L" + LIBDIR, "-l:libpll_b200.so", "-Wl,-rpath,$ORIGIN", "-lm", "-lpthread"])
         out["harness_b200"] = so
     if os.path.isdir("/root/reference/libs/libpll/src"):
         ref_so = os.path.join(ORACLE, "_ref", "libpll_ref.so")

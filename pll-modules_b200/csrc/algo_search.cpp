@@ -264,7 +264,8 @@ struct PhaseClock
   {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
-} g_phase;
+};
+thread_local PhaseClock g_phase;
 
 double optimize_bl_all(pllmod_treeinfo_t * ti, const SearchParams & prm, double lh_epsilon,
                        double smooth_factor)

@@ -17,10 +17,10 @@
 
 #include <algorithm>
 
-unsigned long long g_kernel_launches = 0;
-unsigned long long g_newton_iterations = 0;
-unsigned long long g_h2d_bytes = 0;
-unsigned long long g_d2h_bytes = 0;
+std::atomic<unsigned long long> g_kernel_launches{0};
+std::atomic<unsigned long long> g_newton_iterations{0};
+std::atomic<unsigned long long> g_h2d_bytes{0};
+std::atomic<unsigned long long> g_d2h_bytes{0};
 int g_opt_trav_ctas_per_sm = 0; /* 0 = occupancy query */
 int g_opt_trav_reorder = 1;
 int g_opt_fuse_root = 1;
@@ -64,7 +64,13 @@ extern "C" void pllb200_get_stats(pllb200_stats_t * out)
   out->newton_iterations = g_newton_iterations;
 }
 
-extern "C" void pllb200_reset_stats(void) { g_kernel_launches = g_h2d_bytes = g_d2h_bytes = g_newton_iterations = 0; }
+extern "C" void pllb200_reset_stats(void)
+{
+  g_kernel_launches = 0;
+  g_h2d_bytes = 0;
+  g_d2h_bytes = 0;
+  g_newton_iterations = 0;
+}
 
 extern "C" int pllb200_set_option(const char * name, int value)
 {
@@ -145,6 +151,7 @@ bool dev_ctx_init(PartCtx * c)
   c->scratch_rows = lean_shape && g_opt_scratch_rows > 0 ? (unsigned int)g_opt_scratch_rows : 0;
   c->scratch_mats = c->scratch_rows ? 512 : 0;
   c->d_score = nullptr; c->score_cap = 0; c->h_score = nullptr;
+  c->deriv_last_table = nullptr; c->deriv_reverse = 0;
   const unsigned int nclv = p->nodes - c->clv_first + c->scratch_rows;
   if (nclv)
   {

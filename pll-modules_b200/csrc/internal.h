@@ -12,6 +12,7 @@
 
 #include <cuda_runtime.h>
 
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <unordered_map>
@@ -119,6 +120,10 @@ struct PartCtx
   int next_slot;
   std::vector<PendingResult> pending;
 
+  /* derivative passes: table of the last call and its direction (k_derivatives.cu) */
+  const double * deriv_last_table;
+  int deriv_reverse;
+
   /* sumtable shadows keyed by the caller's host pointer */
   std::unordered_map<const void *, double *> sumtables;
   /* last use of every shadow: at most PLLB200_MAX_SUMTABLES are kept, least recently used first out */
@@ -156,10 +161,11 @@ bool pllb200_cuda_ok(cudaError_t e, const char * what);
   } while (0)
 
 /* global counters (device_ctx.cu) */
-extern unsigned long long g_kernel_launches;
-extern unsigned long long g_newton_iterations;
-extern unsigned long long g_h2d_bytes;
-extern unsigned long long g_d2h_bytes;
+/* statistics only, but partitions may be driven from several threads: atomic */
+extern std::atomic<unsigned long long> g_kernel_launches;
+extern std::atomic<unsigned long long> g_newton_iterations;
+extern std::atomic<unsigned long long> g_h2d_bytes;
+extern std::atomic<unsigned long long> g_d2h_bytes;
 extern int g_opt_trav_ctas_per_sm;
 extern int g_opt_trav_reorder;
 extern int g_opt_fuse_root;

@@ -247,8 +247,13 @@ struct DiagDna
   double d[8][4][3];
 };
 
+/* 132 B per site and pass: a pure stream.  A thread keeps DV_U independent 256-bit loads (and their pattern
+ * weights) in flight per trip — with one load per trip the kernel was latency-bound at 1.6 TB/s (round 1) —, the
+ * grid is one resident wave, and every other call on the same table walks it backwards (`reverse`), so that what
+ * the previous call touched last is still in the 126 MB L2 (the Newton kernel's trick, k_newton.cu). */
+#define DV_U 4
 template <int K>
-__global__ void __launch_bounds__(DV_THREADS) deriv_dna_kernel(DerivArgs a, DiagDna dg)
+__global__ void __launch_bounds__(DV_THREADS, 3) deriv_dna_kernel(DerivArgs a, DiagDna dg, int reverse)
 {
   const int lane = threadIdx.x & 31;
   const int k = lane % K;
@@ -265,25 +270,41 @@ __global__ void __launch_bounds__(DV_THREADS) deriv_dna_kernel(DerivArgs a, Diag
   const unsigned long long E = (unsigned long long)a.sites * K;
   const unsigned long long Eround = (E + 31) / 32 * 32;
   const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long trips = (Eround + stride - 1) / stride; /* per thread, the last one may be empty */
   double acc1 = 0.0, acc2 = 0.0;
-  for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < Eround;
-       e += stride)
+  for (unsigned long long t0 = 0; t0 < trips; t0 += DV_U)
   {
-    const bool act = e < E;
-    const unsigned long long site = e / K;
-    double L0 = 0.0, L1 = 0.0, L2 = 0.0;
-    if (act)
+    d4 s[DV_U];
+    unsigned int wgt[DV_U];
+    unsigned long long ee[DV_U];
+#pragma unroll
+    for (int u = 0; u < DV_U; ++u)
     {
-      const d4 s = ldg256(a.sum + e * 4);
-      L0 = s.x * d0[0] + s.y * d0[1] + s.z * d0[2] + s.w * d0[3];
-      L1 = s.x * d1[0] + s.y * d1[1] + s.z * d1[2] + s.w * d1[3];
-      L2 = s.x * d2[0] + s.y * d2[1] + s.z * d2[2] + s.w * d2[3];
+      const unsigned long long t = t0 + u < trips ? (reverse ? trips - 1 - (t0 + u) : t0 + u) : trips;
+      ee[u] = tid + t * stride; /* >= Eround for the whole warp when there is nothing to do */
+      s[u] = d4{0.0, 0.0, 0.0, 0.0};
+      wgt[u] = 0;
+      if (ee[u] < E)
+      {
+        s[u] = ldg256(a.sum + ee[u] * 4);
+        if (k == 0) wgt[u] = __ldg(a.weights + ee[u] / K);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < DV_U; ++u)
+    {
+      if (ee[u] >= Eround) continue; /* warp-uniform: Eround, stride and the warp's first tid are multiples of 32 */
+      const bool act = ee[u] < E;
+      double L0 = s[u].x * d0[0] + s[u].y * d0[1] + s[u].z * d0[2] + s[u].w * d0[3];
+      double L1 = s[u].x * d1[0] + s[u].y * d1[1] + s[u].z * d1[2] + s[u].w * d1[3];
+      double L2 = s[u].x * d2[0] + s[u].y * d2[1] + s[u].z * d2[2] + s[u].w * d2[3];
       if (pinv > 0.0)
       {
         double inv_lk = 0.0;
-        if (a.invariant)
+        if (act && a.invariant)
         {
-          const int inv = a.invariant[site];
+          const int inv = a.invariant[ee[u] / K];
           if (inv >= 0) inv_lk = fr[inv] * pinv;
         }
         L0 = L0 * (1.0 - pinv) + inv_lk;
@@ -293,21 +314,21 @@ __global__ void __launch_bounds__(DV_THREADS) deriv_dna_kernel(DerivArgs a, Diag
       L0 *= wk;
       L1 *= wk;
       L2 *= wk;
-    }
 #pragma unroll
-    for (int off = 1; off < K; off <<= 1)
-    {
-      L0 += __shfl_xor_sync(0xffffffffu, L0, off);
-      L1 += __shfl_xor_sync(0xffffffffu, L1, off);
-      L2 += __shfl_xor_sync(0xffffffffu, L2, off);
-    }
-    if (act && k == 0)
-    {
-      const double wgt = (double)a.weights[site];
-      const double r1 = -L1 / L0;
-      const double r2 = r1 * r1 - L2 / L0;
-      acc1 += wgt * r1;
-      acc2 += wgt * r2;
+      for (int off = 1; off < K; off <<= 1)
+      {
+        L0 += __shfl_xor_sync(0xffffffffu, L0, off);
+        L1 += __shfl_xor_sync(0xffffffffu, L1, off);
+        L2 += __shfl_xor_sync(0xffffffffu, L2, off);
+      }
+      if (act && k == 0)
+      {
+        const double w = (double)wgt[u];
+        const double r1 = -L1 / L0;
+        const double r2 = r1 * r1 - L2 / L0;
+        acc1 += w * r1;
+        acc2 += w * r2;
+      }
     }
   }
   double v[2] = {acc1, acc2};
@@ -641,15 +662,18 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
   {
     const unsigned long long E = (unsigned long long)a.sites * K;
     unsigned long long blocks = (E + DV_THREADS - 1) / DV_THREADS;
-    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 3; /* one resident wave at 3 CTAs per SM */
     if (blocks > cap) blocks = cap;
     if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+    /* repeated passes over one table (Newton-Raphson through the C API): alternate the direction */
+    const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
+    c->deriv_last_table = d_sumtable;
     switch (K)
     {
-      case 1: deriv_dna_kernel<1><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
-      case 2: deriv_dna_kernel<2><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
-      case 4: deriv_dna_kernel<4><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
-      default: deriv_dna_kernel<8><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg); break;
+      case 1: deriv_dna_kernel<1><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse); break;
+      case 2: deriv_dna_kernel<2><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse); break;
+      case 4: deriv_dna_kernel<4><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse); break;
+      default: deriv_dna_kernel<8><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse); break;
     }
   }
   else

@@ -67,10 +67,11 @@ __device__ __forceinline__ double site_finish(double terma, double terminv, unsi
 }
 
 #define LK_THREADS 256
+#define LK_U 2 /* elements per thread and trip */
 
 /* ---- 4-state path: ROOT=false edge (ii or ti), ROOT=true root ----------------------------- */
 template <int K, bool ROOT>
-__global__ void __launch_bounds__(LK_THREADS) logl_dna_kernel(LoglArgs a)
+__global__ void __launch_bounds__(LK_THREADS, 3) logl_dna_kernel(LoglArgs a)
 {
   __shared__ double s_mat[16 * K];
   __shared__ double s_freq[4 * K];
@@ -90,89 +91,121 @@ __global__ void __launch_bounds__(LK_THREADS) logl_dna_kernel(LoglArgs a)
   const unsigned long long Eround = (E + 31) / 32 * 32;
   double acc = 0.0;
 
-  for (unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; e < Eround;
-       e += stride)
+  /* 268 B (ii) / 137 B (ti) per site: a stream.  LK_U elements per thread and trip, every load of a trip (both
+   * CLV elements, scaler counts, pattern weight, tip code) issued before the first use — one element per trip
+   * left the kernel latency-bound at 2.1 TB/s (round 1); the grid is one resident wave. */
+  const unsigned long long tid = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const unsigned long long trips = (Eround + stride - 1) / stride;
+  for (unsigned long long t0 = 0; t0 < trips; t0 += LK_U)
   {
-    const bool act = e < E;
-    const unsigned long long site = e / K;
-    double term = 0.0, tinv = 0.0;
-    unsigned int sc = 0;
-    if (act)
+    d4 pv[LK_U], cv[LK_U];
+    unsigned int scv[LK_U], wv[LK_U], codev[LK_U];
+    unsigned long long ee[LK_U];
+#pragma unroll
+    for (int u = 0; u < LK_U; ++u)
     {
-      const d4 p = ldg256(a.pclv + e * 4);
-      double t0, t1, t2, t3;
-      if (ROOT)
+      ee[u] = tid + (t0 + u < trips ? t0 + u : trips) * stride;
+      pv[u] = cv[u] = d4{0.0, 0.0, 0.0, 0.0};
+      scv[u] = wv[u] = codev[u] = 0;
+      if (ee[u] < E)
       {
-        t0 = t1 = t2 = t3 = 1.0;
-      }
-      else if (a.ctip)
-      {
-        const unsigned int code = a.ctip[site];
-        const double * m = s_mat + k * 16;
-        t0 = ((code & 1) ? m[0] : 0.0) + ((code & 2) ? m[1] : 0.0) + ((code & 4) ? m[2] : 0.0) + ((code & 8) ? m[3] : 0.0);
-        t1 = ((code & 1) ? m[4] : 0.0) + ((code & 2) ? m[5] : 0.0) + ((code & 4) ? m[6] : 0.0) + ((code & 8) ? m[7] : 0.0);
-        t2 = ((code & 1) ? m[8] : 0.0) + ((code & 2) ? m[9] : 0.0) + ((code & 4) ? m[10] : 0.0) + ((code & 8) ? m[11] : 0.0);
-        t3 = ((code & 1) ? m[12] : 0.0) + ((code & 2) ? m[13] : 0.0) + ((code & 4) ? m[14] : 0.0) + ((code & 8) ? m[15] : 0.0);
-      }
-      else
-      {
-        const d4 c = ldg256(a.cclv + e * 4);
-        const double * m = s_mat + k * 16;
-        t0 = m[0] * c.x + m[1] * c.y + m[2] * c.z + m[3] * c.w;
-        t1 = m[4] * c.x + m[5] * c.y + m[6] * c.z + m[7] * c.w;
-        t2 = m[8] * c.x + m[9] * c.y + m[10] * c.z + m[11] * c.w;
-        t3 = m[12] * c.x + m[13] * c.y + m[14] * c.z + m[15] * c.w;
-      }
-      term = p.x * f0 * t0 + p.y * f1 * t1 + p.z * f2 * t2 + p.w * f3 * t3;
-      if (a.rate_scalers)
-      {
-        if (a.pscaler) sc += a.pscaler[e];
-        if (a.cscaler) sc += a.cscaler[e];
-      }
-      else if (k == 0)
-      {
-        if (a.pscaler) sc += a.pscaler[site];
-        if (a.cscaler) sc += a.cscaler[site];
+        const unsigned long long site = ee[u] / K;
+        pv[u] = ldg256(a.pclv + ee[u] * 4);
+        if (!ROOT)
+        {
+          if (a.ctip)
+            codev[u] = a.ctip[site];
+          else
+            cv[u] = ldg256(a.cclv + ee[u] * 4);
+        }
+        if (a.rate_scalers)
+        {
+          if (a.pscaler) scv[u] += a.pscaler[ee[u]];
+          if (a.cscaler) scv[u] += a.cscaler[ee[u]];
+        }
+        else if (k == 0)
+        {
+          if (a.pscaler) scv[u] += a.pscaler[site];
+          if (a.cscaler) scv[u] += a.cscaler[site];
+        }
+        if (k == 0) wv[u] = __ldg(a.weights + site);
       }
     }
-    unsigned int site_sc = sc;
-    if (a.rate_scalers)
+#pragma unroll
+    for (int u = 0; u < LK_U; ++u)
     {
-      unsigned int mn = sc;
+      if (ee[u] >= Eround) continue; /* warp-uniform */
+      const bool act = ee[u] < E;
+      const unsigned long long site = ee[u] / K;
+      double term = 0.0, tinv = 0.0;
+      const unsigned int sc = scv[u];
+      if (act)
+      {
+        const d4 p = pv[u];
+        double t0_, t1, t2, t3;
+        if (ROOT)
+        {
+          t0_ = t1 = t2 = t3 = 1.0;
+        }
+        else if (a.ctip)
+        {
+          const unsigned int code = codev[u];
+          const double * m = s_mat + k * 16;
+          t0_ = ((code & 1) ? m[0] : 0.0) + ((code & 2) ? m[1] : 0.0) + ((code & 4) ? m[2] : 0.0) + ((code & 8) ? m[3] : 0.0);
+          t1 = ((code & 1) ? m[4] : 0.0) + ((code & 2) ? m[5] : 0.0) + ((code & 4) ? m[6] : 0.0) + ((code & 8) ? m[7] : 0.0);
+          t2 = ((code & 1) ? m[8] : 0.0) + ((code & 2) ? m[9] : 0.0) + ((code & 4) ? m[10] : 0.0) + ((code & 8) ? m[11] : 0.0);
+          t3 = ((code & 1) ? m[12] : 0.0) + ((code & 2) ? m[13] : 0.0) + ((code & 4) ? m[14] : 0.0) + ((code & 8) ? m[15] : 0.0);
+        }
+        else
+        {
+          const d4 c = cv[u];
+          const double * m = s_mat + k * 16;
+          t0_ = m[0] * c.x + m[1] * c.y + m[2] * c.z + m[3] * c.w;
+          t1 = m[4] * c.x + m[5] * c.y + m[6] * c.z + m[7] * c.w;
+          t2 = m[8] * c.x + m[9] * c.y + m[10] * c.z + m[11] * c.w;
+          t3 = m[12] * c.x + m[13] * c.y + m[14] * c.z + m[15] * c.w;
+        }
+        term = p.x * f0 * t0_ + p.y * f1 * t1 + p.z * f2 * t2 + p.w * f3 * t3;
+      }
+      unsigned int site_sc = sc;
+      if (a.rate_scalers)
+      {
+        unsigned int mn = sc;
+#pragma unroll
+        for (int off = 1; off < K; off <<= 1)
+        {
+          const unsigned int o = __shfl_xor_sync(0xffffffffu, mn, off);
+          mn = o < mn ? o : mn;
+        }
+        unsigned int diff = sc - mn;
+        if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
+        for (unsigned int q = 0; q < diff; ++q) term *= SCALE_THRESHOLD_D;
+        site_sc = mn;
+      }
+      if (pinv > 0.0)
+      {
+        term = wk * term * (1.0 - pinv);
+        if (act && a.invariant)
+        {
+          const int inv = a.invariant[site];
+          if (inv >= 0) tinv = wk * s_freq[k * 4 + inv] * pinv;
+        }
+      }
+      else
+        term = term * wk;
 #pragma unroll
       for (int off = 1; off < K; off <<= 1)
       {
-        const unsigned int o = __shfl_xor_sync(0xffffffffu, mn, off);
-        mn = o < mn ? o : mn;
+        term += __shfl_xor_sync(0xffffffffu, term, off);
+        tinv += __shfl_xor_sync(0xffffffffu, tinv, off);
       }
-      unsigned int diff = sc - mn;
-      if (diff > PLL_SCALE_RATE_MAXDIFF) diff = PLL_SCALE_RATE_MAXDIFF;
-      for (unsigned int q = 0; q < diff; ++q) term *= SCALE_THRESHOLD_D;
-      site_sc = mn;
-    }
-    if (pinv > 0.0)
-    {
-      term = wk * term * (1.0 - pinv);
-      if (act && a.invariant)
+      if (act && k == 0)
       {
-        const int inv = a.invariant[site];
-        if (inv >= 0) tinv = wk * s_freq[k * 4 + inv] * pinv;
+        double lk = site_finish(term, tinv, site_sc, ROOT);
+        lk *= (double)wv[u];
+        if (a.persite) a.persite[site] = lk;
+        acc += lk;
       }
-    }
-    else
-      term = term * wk;
-#pragma unroll
-    for (int off = 1; off < K; off <<= 1)
-    {
-      term += __shfl_xor_sync(0xffffffffu, term, off);
-      tinv += __shfl_xor_sync(0xffffffffu, tinv, off);
-    }
-    if (act && k == 0)
-    {
-      double lk = site_finish(term, tinv, site_sc, ROOT);
-      lk *= (double)a.weights[site];
-      if (a.persite) a.persite[site] = lk;
-      acc += lk;
     }
   }
   double v[1] = {acc};
@@ -564,7 +597,7 @@ static bool dispatch_logl(PartCtx * c, const LoglArgs & a)
   {
     const unsigned long long E = (unsigned long long)a.sites * K;
     unsigned long long blocks = (E + LK_THREADS - 1) / LK_THREADS;
-    const unsigned long long cap = (unsigned long long)c->sm_count * 8;
+    const unsigned long long cap = (unsigned long long)c->sm_count * 3; /* one resident wave at 3 CTAs per SM */
     if (blocks > cap) blocks = cap;
     if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
     if (blocks < 1) blocks = 1;

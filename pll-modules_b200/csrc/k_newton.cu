@@ -155,11 +155,15 @@ __device__ __forceinline__ void newton_publish(const NewtonArgs & a, double x, d
 }
 
 
-/* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates) */
+/* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates);
+ * 4: 20 states, K = 4, unpadded (protein Gamma-4: warp-contiguous 1 KB loads, factors in registers) */
+#define NW_AA_TILE 160 /* 32-byte items (4 states of one rate) per warp and trip = 8 sites x 4 rates x 5 chunks */
 template <int MODE>
-__global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(NewtonArgs a)
+__global__ void __launch_bounds__(NW_THREADS, MODE == 4 ? 1 : (MODE == 2 ? 2 : 3)) newton_kernel(NewtonArgs a)
 {
-  constexpr bool DNA = MODE != 0;
+  constexpr bool DNA = MODE == 1 || MODE == 2;
+  /* MODE 4: per-item partial sums of a warp's tile, [item][L0 L1 L2] */
+  __shared__ double s_tr[MODE == 4 ? (NW_THREADS / 32) * NW_AA_TILE * 3 : 1];
   cg::grid_group grid = cg::this_grid();
   __shared__ double s_diag[NW_MAX_DIAG * 3];
   __shared__ double s_red[2][NW_THREADS / 32];
@@ -228,7 +232,94 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
     /* odd passes walk the table backwards: what the previous pass (or the sumtable kernel, which
      * writes ascending) touched last is still in the 126 MB L2 */
     const bool fwd = (iter & 1u) == 0;
-    if (MODE == 2)
+    if (MODE == 4)
+    {
+      /* 20 states x 4 rates, 640 B per site.  The table is a flat array of 32-byte items (4 states of one rate);
+       * a warp takes tiles of 160 items (8 sites) with five fully coalesced 1 KB loads, lane l owning items
+       * l, l+32, ..., l+128 of every tile — i.e. always the same five (rate, state chunk) pairs, whose 12 factors
+       * each (w_k (1 - pinv_k) folded in) sit in registers for the whole pass.  [Round 1: one 160-byte element per
+       * thread = 32 lines per warp load and a shared-memory read per FMA: L1TEX-bound at 3.2 TB/s.]  Item sums go
+       * through a per-warp shared-memory tile; 24 lanes add the 20 items of (site, L0|L1|L2), every third lane
+       * finishes a site. */
+      double fc[5][4][3];
+#pragma unroll
+      for (int u = 0; u < 5; ++u)
+      {
+        const unsigned int pi = (unsigned int)(u * 32 + lane) % 20u;
+        const unsigned int kk = pi / 5u, cc = pi % 5u;
+        const double wf = a.w[kk] * (1.0 - a.pinv[kk]);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+        {
+          const double * g = s_diag + (size_t)(kk * 20u + cc * 4u + j) * 3;
+          fc[u][j][0] = wf * g[0];
+          fc[u][j][1] = wf * g[1];
+          fc[u][j][2] = wf * g[2];
+        }
+      }
+      double * tr = s_tr + (size_t)warp * NW_AA_TILE * 3;
+      const unsigned long long ntiles = ((unsigned long long)a.sites + 7) / 8;
+      const unsigned long long items = (unsigned long long)a.sites * 20;
+      const unsigned long long gw = (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp;
+      const unsigned long long nw = (unsigned long long)gridDim.x * (NW_THREADS / 32);
+      const unsigned long long mytiles = gw < ntiles ? (ntiles - gw + nw - 1) / nw : 0;
+      const unsigned int fs = (unsigned int)lane / 3u, fcmp = (unsigned int)lane % 3u; /* lanes 0..23: (site, component) */
+      for (unsigned long long ti = 0; ti < mytiles; ++ti)
+      {
+        const unsigned long long tile = gw + (fwd ? ti : mytiles - 1 - ti) * nw;
+        const unsigned long long i0 = tile * NW_AA_TILE;
+        d4 v[5];
+#pragma unroll
+        for (int u = 0; u < 5; ++u)
+        {
+          const unsigned long long it = i0 + (unsigned int)(u * 32 + lane);
+          v[u] = d4{0.0, 0.0, 0.0, 0.0};
+          if (it < items) v[u] = ldg256(a.sum + it * 4);
+        }
+        const unsigned long long site = tile * 8 + fs;
+        unsigned int wgt = 0;
+        int inv = -1;
+        if (lane < 24 && fcmp == 0 && site < a.sites)
+        {
+          wgt = __ldg(a.weights + site);
+          if (any_pinv && a.invariant) inv = a.invariant[site];
+        }
+#pragma unroll
+        for (int u = 0; u < 5; ++u)
+        {
+          double * o = tr + (size_t)(u * 32 + lane) * 3;
+          o[0] = v[u].x * fc[u][0][0] + v[u].y * fc[u][1][0] + v[u].z * fc[u][2][0] + v[u].w * fc[u][3][0];
+          o[1] = v[u].x * fc[u][0][1] + v[u].y * fc[u][1][1] + v[u].z * fc[u][2][1] + v[u].w * fc[u][3][1];
+          o[2] = v[u].x * fc[u][0][2] + v[u].y * fc[u][1][2] + v[u].z * fc[u][2][2] + v[u].w * fc[u][3][2];
+        }
+        __syncwarp();
+        double L = 0.0;
+        if (lane < 24)
+        {
+          const double * q = tr + (size_t)fs * 60 + fcmp;
+#pragma unroll
+          for (int i = 0; i < 20; ++i) L += q[3 * i];
+        }
+        const double L1 = __shfl_down_sync(0xffffffffu, L, 1), L2 = __shfl_down_sync(0xffffffffu, L, 2);
+        if (lane < 24 && fcmp == 0 && site < a.sites)
+        {
+          double L0 = L;
+          if (inv >= 0)
+          {
+#pragma unroll
+            for (unsigned int kk = 0; kk < 4; ++kk)
+              L0 += a.w[kk] * a.pinv[kk] *
+                    a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * 20 * 20 + 20 + (unsigned int)inv];
+          }
+          const double r = 1.0 / L0;
+          const double r1 = -L1 * r;
+          acc1 += (double)wgt * r1;
+          acc2 += (double)wgt * (r1 * r1 - L2 * r);
+        }
+        __syncwarp(); /* the tile buffer is rewritten by the next trip */
+      }
+    }
+    else if (MODE == 2)
     {
       /* K = 4: a thread's 4 elements belong to 4 different sites and one rate.  Register slot j holds
        * trip it0 + (j ^ perm), perm = bit-reversed rate index, so that two exchange rounds with FIXED
@@ -1172,10 +1263,12 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   a.revert_on_limit = revert_on_limit;
 
   /* cooperative grid: never more CTAs than can be co-resident, never more than there is work */
-  static int per_sm[4] = {0, 0, 0, 0};
+  static int per_sm[5] = {0, 0, 0, 0, 0};
   int mode = s == 4 ? (K == 4 ? 2 : 1) : 0;
   if (mode == 2 && g_opt_fused_newton == 1) mode = 3; /* fused_newton=2 keeps the register version */
-  const void * fn = mode == 3   ? (const void *)newton_dna4_tma_kernel
+  if (s == 20 && p->states_padded == 20 && K == 4 && g_opt_fused_newton != 3) mode = 4; /* fused_newton=3: generic kernel */
+  const void * fn = mode == 4   ? (const void *)newton_kernel<4>
+                    : mode == 3 ? (const void *)newton_dna4_tma_kernel
                     : mode == 2 ? (const void *)newton_kernel<2>
                     : mode == 1 ? (const void *)newton_kernel<1>
                                 : (const void *)newton_kernel<0>;
@@ -1190,6 +1283,7 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   }
   const unsigned long long E = (unsigned long long)a.sites * K;
   unsigned long long blocks = mode == 3 ? (E + NT_TILE - 1) / NT_TILE : (E + NW_THREADS - 1) / NW_THREADS;
+  if (mode == 4) blocks = (((unsigned long long)a.sites + 7) / 8 + NW_THREADS / 32 - 1) / (NW_THREADS / 32); /* a warp per 8-site tile */
   unsigned long long cap = (unsigned long long)c->sm_count * std::min(per_sm[mode], 4);
   if (cap > PLLB200_MAX_RED_BLOCKS * 3 / 4) cap = PLLB200_MAX_RED_BLOCKS * 3 / 4; /* partials: 2 buffers x 2 values */
   if (blocks > cap) blocks = cap;

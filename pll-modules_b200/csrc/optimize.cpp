@@ -227,7 +227,7 @@ struct BloTrace
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
   }
 };
-static BloTrace g_blo_trace;
+static thread_local BloTrace g_blo_trace;
 
 /* re-orient one inner CLV: parent <- (right_child->back, left_child->back)  (pll_optimize.c:748-775) */
 static void reorient_clv(pll_partition_t ** partitions, size_t partition_count, pll_unode_t * parent,

@@ -100,6 +100,12 @@ def _lib(kind):
         lib.h_optimize_branch_lengths_single.restype = C.c_double
         lib.h_optimize_branch_lengths_single.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_double]
         lib.h_set_alpha.argtypes = [C.c_void_p, C.c_uint, C.c_double]
+        lib.h_optimize_branch_lengths_iterative.restype = C.c_double
+        lib.h_optimize_branch_lengths_iterative.argtypes = [C.c_void_p, C.c_int, C.c_double]
+        lib.h_edge_loglh_multi.restype = C.c_double
+        lib.h_edge_loglh_multi.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
+        lib.h_derivative_func.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]
+        lib.h_run_concurrently.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_void_p]
         lib.h_gamma_cats.argtypes = [C.c_double, C.c_uint, C.c_int, C.c_void_p]
         lib.h_perturb_edge.argtypes = [C.c_void_p, C.c_uint, C.c_double]
         lib.h_errmsg.restype = C.c_char_p
@@ -432,6 +438,20 @@ class Harness:
         self._cb = REDUCE_CB(fn)
         self.lib.h_set_reduce_cb(self.h, C.c_void_p(part), self._cb)
 
+    def optimize_branch_lengths_iterative(self, smoothings=2, tolerance=1e-3):
+        return self.lib.h_optimize_branch_lengths_iterative(self.h, smoothings, tolerance)
+
+    def edge_loglh_multi(self, node_index, persite=False):
+        buf = np.zeros(sum(self.sites)) if persite else None
+        ll = self.lib.h_edge_loglh_multi(self.h, node_index, buf.ctypes.data if persite else None)
+        return (ll, buf) if persite else ll
+
+    def derivative_func(self, node_index, brlens, p=0):
+        b = np.ascontiguousarray(brlens, dtype=np.float64)
+        df, ddf = np.zeros(len(b)), np.zeros(len(b))
+        assert self.lib.h_derivative_func(self.h, p, node_index, b.ctypes.data, len(b), df.ctypes.data, ddf.ctypes.data)
+        return df, ddf
+
     def op_type_counts(self, p=0):
         out = np.zeros(3, dtype=np.uint32)
         self.lib.h_op_type_counts(self.h, p, self.tips - 2, out.ctypes.data)
@@ -439,6 +459,15 @@ class Harness:
 
     def ops_counter(self):
         return self.lib.h_ops_counter(self.h)
+
+
+def run_concurrently(harnesses, threaded=True):
+    """Every harness (same kind) from its own pthread at once: [logL, -logL after one BLO call, logL] each."""
+    lib = harnesses[0].lib
+    arr = (C.c_void_p * len(harnesses))(*[h.h for h in harnesses])
+    out = np.zeros(3 * len(harnesses))
+    assert lib.h_run_concurrently(arr, len(harnesses), 1 if threaded else 0, out.ctypes.data)
+    return out.reshape(len(harnesses), 3)
 
 
 def gamma_cats(kind, alpha, cats, mode=0):

@@ -11,8 +11,8 @@ import os
 import numpy as np
 import pytest
 
-from pllharness import (ATTR_PATTERN_TIP, ATTR_RATE_SCALERS, BLO_NEWTON_FAST, BLO_NEWTON_OLDFAST,
-                        BLO_NEWTON_SAFE, Harness, have_reference, load_product_package)
+from pllharness import (ATTR_PATTERN_TIP, ATTR_RATE_SCALERS, BLO_NEWTON_FAST, BLO_NEWTON_OLDFAST, BLO_NEWTON_OLDSAFE,
+                        BLO_NEWTON_SAFE, Harness, have_reference, load_product_package, run_concurrently)
 
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -261,7 +261,7 @@ def test_sumtable_and_derivatives_every_edge(kw):
 
 
 @needs_ref
-@pytest.mark.parametrize("method", [BLO_NEWTON_FAST, BLO_NEWTON_SAFE, BLO_NEWTON_OLDFAST])
+@pytest.mark.parametrize("method", [BLO_NEWTON_FAST, BLO_NEWTON_SAFE, BLO_NEWTON_OLDFAST, BLO_NEWTON_OLDSAFE])
 def test_branch_length_optimisation_matches(method):
     kw = dict(tips=24, sites=3000)
     ref, dev = pair(**kw)
@@ -286,6 +286,87 @@ def test_single_partition_legacy_blo_and_radius():
             b = dev.optimize_branch_lengths_single(radius=radius, smoothings=1, tolerance=0.1)
             assert rel(b, a) < 1e-8, (radius, b, a)
             np.testing.assert_allclose(dev.branch_lengths(), ref.branch_lengths(), atol=1e-5, rtol=1e-6)
+
+
+@needs_ref
+@pytest.mark.parametrize("kw", [
+    dict(tips=30, sites=1003, states=20),                 # ragged: 1003 sites = 125 tiles of 8 + 3
+    dict(tips=16, sites=5, states=20),                    # less than one tile
+    dict(tips=24, sites=800, states=20, pinv=0.15),       # invariant-site term in the finishing lane
+    dict(tips=60, sites=20000, states=20),                # several tiles per warp, both walking directions
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_protein_newton_kernel_matches_generic_kernel_and_reference(kw):
+    """newton_kernel<4> (20 states, Gamma-4: warp-contiguous loads, factors in registers) against the generic
+    one-element-per-thread kernel (fused_newton 3) and the reference: -logL after smoothing and every branch length."""
+    pkg = load_product_package()
+    out = {}
+    try:
+        for mode in (1, 3):
+            pkg.set_option("fused_newton", mode)
+            with Harness("b200", **kw) as d:
+                d.loglh()
+                nll = d.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.01)
+                out[mode] = (nll, d.branch_lengths().copy())
+    finally:
+        pkg.set_option("fused_newton", 1)
+    assert rel(out[1][0], out[3][0]) < 1e-12, (out[1][0], out[3][0])
+    np.testing.assert_allclose(out[1][1], out[3][1], rtol=1e-9, atol=1e-12)
+    with Harness("ref", **kw) as r:
+        r.loglh()
+        a = r.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.01)
+        assert rel(out[1][0], a) < 1e-8, (out[1][0], a)
+        np.testing.assert_allclose(out[1][1], r.branch_lengths(), atol=1e-5, rtol=1e-6)
+
+
+@needs_ref
+def test_remaining_a13_entry_points_match_reference():
+    """pllmod_opt_optimize_branch_lengths_iterative, pllmod_opt_compute_edge_loglikelihood_multi and
+    pllmod_opt_derivative_func (pll_optimize.c:1115,1182,1146) through the same-source harness."""
+    kw = dict(tips=18, sites=[1500, 700], states=[4, 20], alpha=[0.6, 1.1])
+    ref, dev = pair(**kw)
+    with ref, dev:
+        ref.loglh(), dev.loglh()
+        for node in (ref.root(), kw["tips"] + 5):
+            ref.set_root(node), dev.set_root(node)
+            assert rel(dev.loglh(1), ref.loglh(1)) < 1e-8
+            a, b = ref.edge_loglh_multi(node), dev.edge_loglh_multi(node)
+            assert rel(b, a) < 1e-8, (node, b, a)
+            assert rel(b, dev.loglh(1)) < 1e-12          # the multi-partition edge logL IS the tree logL
+            for p in (0, 1):
+                df, ddf = dev.derivative_func(node, [0.003, 0.05, 0.4, 2.0], p=p)
+                rf, rdf = ref.derivative_func(node, [0.003, 0.05, 0.4, 2.0], p=p)
+                assert_deriv_close(df, rf)
+                assert_deriv_close(ddf, rdf)
+                d2, dd2 = dev.derivatives(node, [0.003, 0.05, 0.4, 2.0], p=p)   # same numbers as the direct call
+                assert np.array_equal(df, d2) and np.array_equal(ddf, dd2)
+    kw = dict(tips=22, sites=2500)
+    ref, dev = pair(**kw)
+    with ref, dev:
+        ref.loglh(), dev.loglh()
+        a = ref.optimize_branch_lengths_iterative(smoothings=2, tolerance=1e-3)
+        b = dev.optimize_branch_lengths_iterative(smoothings=2, tolerance=1e-3)
+        assert rel(b, a) < 1e-8, (b, a)
+        np.testing.assert_allclose(dev.branch_lengths(), ref.branch_lengths(), atol=1e-5, rtol=1e-6)
+
+
+def test_partitions_driven_from_two_threads_equal_the_serial_run():
+    """SURVEY.md 8b threading contract: distinct partitions (each with its own tree and treeinfo) driven from distinct
+    host threads at the same time give exactly the serial results (full logL, Newton-Raphson smoothing, logL)."""
+    shapes = [dict(tips=40, sites=20000), dict(tips=25, sites=4000, states=20), dict(tips=60, sites=9000, seed=5),
+              dict(tips=30, sites=[3000, 2000], states=[4, 4], alpha=[0.5, 1.2])]
+    hs = [Harness("b200", **kw) for kw in shapes]
+    try:
+        serial = run_concurrently(hs, threaded=False)
+    finally:
+        [h.close() for h in hs]
+    for rep in range(2):
+        hs = [Harness("b200", **kw) for kw in shapes]
+        try:
+            threaded = run_concurrently(hs, threaded=True)
+        finally:
+            [h.close() for h in hs]
+        assert np.all(np.isfinite(threaded)) and np.all(threaded[:, 0] < 0)
+        assert np.array_equal(threaded, serial), (rep, threaded, serial)
 
 
 @needs_ref
@@ -494,6 +575,88 @@ def test_baseline_c3_full_size_properties():
         with Harness("ref", rank=3, nranks=50, **kw) as r, Harness("b200", rank=3, nranks=50, **kw) as d:
             assert r.sites == d.sites == [4000]
             assert rel(d.loglh(), r.loglh()) < 1e-8
+
+
+C4_SHAPE = dict(tips=200, sites=[20000] * 100, states=[4 if p % 2 == 0 else 20 for p in range(100)],
+                alpha=[0.3 + 0.01 * p for p in range(100)])
+
+
+@needs_ref
+@pytest.mark.parametrize("shard", [0, 5])
+def test_baseline_c4_real_shape_per_partition_logl_matches_reference(shard):
+    """BASELINE.json configs[3] at its real shape: 100 partitions x 20 k sites, 200 taxa, DNA and protein alternating,
+    per-partition Gamma shapes, batch mode on — one GPU's 1/8 site share (2500 sites of every partition: exactly what a
+    GPU holds in the 8-GPU configuration; the whole config is 152 GB of CLVs) against the reference on the same share:
+    every partition's logL to 1e-8, and root-edge derivatives of four partitions."""
+    with Harness("ref", rank=shard, nranks=8, **C4_SHAPE) as r, Harness("b200", rank=shard, nranks=8, **C4_SHAPE) as d:
+        assert r.sites == d.sites == [2500] * 100
+        lr, ld = r.loglh(), d.loglh()
+        np.testing.assert_allclose(d.partition_loglh(), r.partition_loglh(), rtol=1e-8, atol=0)
+        assert rel(ld, lr) < 1e-8
+        # derivatives of the root edge, partition by partition (a smoothing pass of the reference takes 100 s here)
+        for p in (0, 1, 98, 99):
+            df, ddf = d.derivatives(d.root(), [0.02, 0.3], p=p)
+            rf, rdf = r.derivatives(r.root(), [0.02, 0.3], p=p)
+            assert_deriv_close(df, rf)
+            assert_deriv_close(ddf, rdf)
+
+
+def test_baseline_c4_real_shape_shards_add_up():
+    """The eight site shares of the real C4 shape, evaluated one after the other on this GPU, add up per partition
+    to the same numbers whichever way the 20 k sites are cut (8 x 2500 against 4 x 5000)."""
+    def total(nranks):
+        acc = np.zeros(100)
+        for rk in range(nranks):
+            with Harness("b200", rank=rk, nranks=nranks, **C4_SHAPE) as d:
+                d.loglh()
+                acc += d.partition_loglh()
+        return acc
+    np.testing.assert_allclose(total(8), total(4), rtol=1e-10, atol=0)
+
+
+@needs_ref
+def test_baseline_c5_slice_matches_reference():
+    """BASELINE.json configs[4] (DNA, 2000 taxa x 500 k sites): one 12.5 k-site slice of that alignment against the
+    reference — full logL, partial traversals after re-rooting as the SPR search does, one edge's derivatives."""
+    kw = dict(tips=2000, sites=500000)
+    with Harness("ref", rank=11, nranks=40, **kw) as r, Harness("b200", rank=11, nranks=40, **kw) as d:
+        assert r.sites == d.sites == [12500]
+        assert rel(d.loglh(), r.loglh()) < 1e-8
+        rng = np.random.RandomState(9)
+        for nd in rng.randint(kw["tips"], 4 * kw["tips"] - 6, size=6):
+            x = 0.05 + 0.1 * rng.rand()
+            r.perturb_edge(int(nd), x), d.perturb_edge(int(nd), x)
+            r.set_root(int(nd)), d.set_root(int(nd))
+            assert rel(d.loglh(1), r.loglh(1)) < 1e-8
+        root = d.root()
+        df, ddf = d.derivatives(root, [0.01, 0.1, 1.0])
+        rf, rdf = r.derivatives(r.root(), [0.01, 0.1, 1.0])
+        assert_deriv_close(df, rf)
+        assert_deriv_close(ddf, rdf)
+
+
+@needs_ref
+@pytest.mark.parametrize("kw", [
+    dict(tips=12, sites=150, states=61, rate_cats=4),                  # codon-sized alphabet (row N1): generic kernels
+    dict(tips=20, sites=64, states=61, rate_cats=2, brlen_scale=12.0),  # deep: scaling on the generic path
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_codon_sized_alphabet_matches_reference(kw):
+    """61 states (the codon alphabet size): CLVs, scalers, logL, derivatives and one smoothing pass against the
+    reference's generic kernels (core_partials.c:612-764)."""
+    ref, dev = pair(**kw)
+    with ref, dev:
+        assert rel(dev.loglh(), ref.loglh()) < 1e-8
+        tips = kw["tips"]
+        for i in range(tips - 2):
+            assert np.array_equal(dev.scaler(i), ref.scaler(i))
+            np.testing.assert_allclose(dev.clv(tips + i), ref.clv(tips + i), rtol=1e-10, atol=0)
+        df, ddf = dev.derivatives(dev.root(), [0.01, 0.1, 1.0])
+        rf, rdf = ref.derivatives(ref.root(), [0.01, 0.1, 1.0])
+        assert_deriv_close(df, rf)
+        assert_deriv_close(ddf, rdf)
+        a = ref.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=1, lh_epsilon=1.0)
+        b = dev.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=1, lh_epsilon=1.0)
+        assert rel(b, a) < 1e-8, (b, a)
 
 
 # ---- model-parameter optimisers over device-resident state (SURVEY.md §8a rows a13/a14) ----
