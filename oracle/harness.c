@@ -1178,6 +1178,14 @@ double h_optimize_branch_lengths_iterative(void * hv, int smoothings, double tol
                                                       smoothings, 1);
 }
 
+/* exported by the reference (pll_optimize.c:1182, PLL_EXPORT) but missing from its header pll_optimize.h */
+double pllmod_opt_compute_edge_loglikelihood_multi(pll_partition_t ** partitions, size_t partition_count,
+                                                   unsigned int parent_clv_index, int parent_scaler_index,
+                                                   unsigned int child_clv_index, int child_scaler_index,
+                                                   unsigned int matrix_index, unsigned int ** const params_indices,
+                                                   double * persite_lnl, void * parallel_context,
+                                                   void (*parallel_reduce_cb)(void *, double *, size_t, int));
+
 /* pllmod_opt_compute_edge_loglikelihood_multi over all partitions at the edge of subnode node_index;
  * persite (may be NULL): sum of sites of all partitions doubles */
 double h_edge_loglh_multi(void * hv, unsigned int node_index, double * persite)

@@ -20,6 +20,7 @@
 #include "internal.h"
 #include "devutil.cuh"
 #include "reduce.cuh"
+#include "aa4_pass.cuh"
 
 #include <cmath>
 #include <utility>
@@ -331,6 +332,35 @@ __global__ void __launch_bounds__(DV_THREADS, 3) deriv_dna_kernel(DerivArgs a, D
       }
     }
   }
+  double v[2] = {acc1, acc2};
+  grid_reduce_finish<2>(v, a.red);
+}
+
+/* 20 states, 4 categories, unpadded: the tile pass of aa4_pass.cuh (644 B per site); a.diag is the staged
+ * [k][j][3] table of the generic path */
+#define DVA_THREADS 256
+__global__ void __launch_bounds__(DVA_THREADS, 1) deriv_aa4_kernel(DerivArgs a, int reverse)
+{
+  __shared__ double s_tr[(DVA_THREADS / 32) * AA4_TILE * 3];
+  __shared__ double s_aux[24];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  bool any_pinv = false;
+  for (unsigned int kk = 0; kk < 4; ++kk) any_pinv |= a.pinv[kk] > 0.0;
+  if (threadIdx.x < 4) s_aux[threadIdx.x] = a.w[threadIdx.x] * (1.0 - a.pinv[threadIdx.x]);
+  if (threadIdx.x < 20)
+  {
+    double t = 0.0;
+    for (unsigned int kk = 0; kk < 4; ++kk)
+      t += a.w[kk] * a.pinv[kk] * a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * 20 * 20 + 20 + threadIdx.x];
+    s_aux[4 + threadIdx.x] = t;
+  }
+  __syncthreads();
+  double fc[5][4][3];
+  aa4_load_factors(a.diag, s_aux, lane, fc);
+  double acc1 = 0.0, acc2 = 0.0;
+  aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, fc,
+           s_tr + (size_t)warp * AA4_TILE * 3, (unsigned long long)blockIdx.x * (DVA_THREADS / 32) + warp,
+           (unsigned long long)gridDim.x * (DVA_THREADS / 32), reverse == 0, lane, acc1, acc2);
   double v[2] = {acc1, acc2};
   grid_reduce_finish<2>(v, a.red);
 }
@@ -675,6 +705,16 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
       case 4: deriv_dna_kernel<4><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse); break;
       default: deriv_dna_kernel<8><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse); break;
     }
+  }
+  else if (s == 20 && sp == 20 && K == 4 && g_opt_fused_newton != 3)
+  {
+    a.diag = (const double *)dev_stage(c, diag.data(), sizeof(double) * diag.size());
+    if (!a.diag) return false;
+    unsigned long long blocks = (((unsigned long long)a.sites + 7) / 8 + DVA_THREADS / 32 - 1) / (DVA_THREADS / 32);
+    if (blocks > (unsigned long long)c->sm_count) blocks = c->sm_count;
+    const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
+    c->deriv_last_table = d_sumtable;
+    deriv_aa4_kernel<<<(unsigned)blocks, DVA_THREADS, 0, c->stream>>>(a, reverse);
   }
   else
   {

@@ -21,6 +21,7 @@
  */
 #include "internal.h"
 #include "devutil.cuh"
+#include "aa4_pass.cuh"
 
 #include <algorithm>
 #include <cooperative_groups.h>
@@ -157,13 +158,13 @@ __device__ __forceinline__ void newton_publish(const NewtonArgs & a, double x, d
 
 /* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates);
  * 4: 20 states, K = 4, unpadded (protein Gamma-4: warp-contiguous 1 KB loads, factors in registers) */
-#define NW_AA_TILE 160 /* 32-byte items (4 states of one rate) per warp and trip = 8 sites x 4 rates x 5 chunks */
 template <int MODE>
 __global__ void __launch_bounds__(NW_THREADS, MODE == 4 ? 1 : (MODE == 2 ? 2 : 3)) newton_kernel(NewtonArgs a)
 {
   constexpr bool DNA = MODE == 1 || MODE == 2;
   /* MODE 4: per-item partial sums of a warp's tile, [item][L0 L1 L2] */
-  __shared__ double s_tr[MODE == 4 ? (NW_THREADS / 32) * NW_AA_TILE * 3 : 1];
+  __shared__ double s_tr[MODE == 4 ? (NW_THREADS / 32) * AA4_TILE * 3 : 1];
+  __shared__ double s_aux[24]; /* MODE 4: w_k (1 - pinv_k) | invariant-site term per state */
   cg::grid_group grid = cg::this_grid();
   __shared__ double s_diag[NW_MAX_DIAG * 3];
   __shared__ double s_red[2][NW_THREADS / 32];
@@ -234,90 +235,22 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 4 ? 1 : (MODE == 2 ? 2 : 3
     const bool fwd = (iter & 1u) == 0;
     if (MODE == 4)
     {
-      /* 20 states x 4 rates, 640 B per site.  The table is a flat array of 32-byte items (4 states of one rate);
-       * a warp takes tiles of 160 items (8 sites) with five fully coalesced 1 KB loads, lane l owning items
-       * l, l+32, ..., l+128 of every tile — i.e. always the same five (rate, state chunk) pairs, whose 12 factors
-       * each (w_k (1 - pinv_k) folded in) sit in registers for the whole pass.  [Round 1: one 160-byte element per
-       * thread = 32 lines per warp load and a shared-memory read per FMA: L1TEX-bound at 3.2 TB/s.]  Item sums go
-       * through a per-warp shared-memory tile; 24 lanes add the 20 items of (site, L0|L1|L2), every third lane
-       * finishes a site. */
+      /* 20 states x 4 rates: warp-contiguous loads, factors in registers (aa4_pass.cuh) */
       double fc[5][4][3];
-#pragma unroll
-      for (int u = 0; u < 5; ++u)
+      if (threadIdx.x < 4) s_aux[threadIdx.x] = a.w[threadIdx.x] * (1.0 - a.pinv[threadIdx.x]);
+      if (threadIdx.x < 20)
       {
-        const unsigned int pi = (unsigned int)(u * 32 + lane) % 20u;
-        const unsigned int kk = pi / 5u, cc = pi % 5u;
-        const double wf = a.w[kk] * (1.0 - a.pinv[kk]);
-#pragma unroll
-        for (int j = 0; j < 4; ++j)
-        {
-          const double * g = s_diag + (size_t)(kk * 20u + cc * 4u + j) * 3;
-          fc[u][j][0] = wf * g[0];
-          fc[u][j][1] = wf * g[1];
-          fc[u][j][2] = wf * g[2];
-        }
+        double t = 0.0;
+        for (unsigned int kk = 0; kk < 4; ++kk)
+          t += a.w[kk] * a.pinv[kk] *
+               a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * 20 * 20 + 20 + threadIdx.x];
+        s_aux[4 + threadIdx.x] = t;
       }
-      double * tr = s_tr + (size_t)warp * NW_AA_TILE * 3;
-      const unsigned long long ntiles = ((unsigned long long)a.sites + 7) / 8;
-      const unsigned long long items = (unsigned long long)a.sites * 20;
-      const unsigned long long gw = (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp;
-      const unsigned long long nw = (unsigned long long)gridDim.x * (NW_THREADS / 32);
-      const unsigned long long mytiles = gw < ntiles ? (ntiles - gw + nw - 1) / nw : 0;
-      const unsigned int fs = (unsigned int)lane / 3u, fcmp = (unsigned int)lane % 3u; /* lanes 0..23: (site, component) */
-      for (unsigned long long ti = 0; ti < mytiles; ++ti)
-      {
-        const unsigned long long tile = gw + (fwd ? ti : mytiles - 1 - ti) * nw;
-        const unsigned long long i0 = tile * NW_AA_TILE;
-        d4 v[5];
-#pragma unroll
-        for (int u = 0; u < 5; ++u)
-        {
-          const unsigned long long it = i0 + (unsigned int)(u * 32 + lane);
-          v[u] = d4{0.0, 0.0, 0.0, 0.0};
-          if (it < items) v[u] = ldg256(a.sum + it * 4);
-        }
-        const unsigned long long site = tile * 8 + fs;
-        unsigned int wgt = 0;
-        int inv = -1;
-        if (lane < 24 && fcmp == 0 && site < a.sites)
-        {
-          wgt = __ldg(a.weights + site);
-          if (any_pinv && a.invariant) inv = a.invariant[site];
-        }
-#pragma unroll
-        for (int u = 0; u < 5; ++u)
-        {
-          double * o = tr + (size_t)(u * 32 + lane) * 3;
-          o[0] = v[u].x * fc[u][0][0] + v[u].y * fc[u][1][0] + v[u].z * fc[u][2][0] + v[u].w * fc[u][3][0];
-          o[1] = v[u].x * fc[u][0][1] + v[u].y * fc[u][1][1] + v[u].z * fc[u][2][1] + v[u].w * fc[u][3][1];
-          o[2] = v[u].x * fc[u][0][2] + v[u].y * fc[u][1][2] + v[u].z * fc[u][2][2] + v[u].w * fc[u][3][2];
-        }
-        __syncwarp();
-        double L = 0.0;
-        if (lane < 24)
-        {
-          const double * q = tr + (size_t)fs * 60 + fcmp;
-#pragma unroll
-          for (int i = 0; i < 20; ++i) L += q[3 * i];
-        }
-        const double L1 = __shfl_down_sync(0xffffffffu, L, 1), L2 = __shfl_down_sync(0xffffffffu, L, 2);
-        if (lane < 24 && fcmp == 0 && site < a.sites)
-        {
-          double L0 = L;
-          if (inv >= 0)
-          {
-#pragma unroll
-            for (unsigned int kk = 0; kk < 4; ++kk)
-              L0 += a.w[kk] * a.pinv[kk] *
-                    a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * 20 * 20 + 20 + (unsigned int)inv];
-          }
-          const double r = 1.0 / L0;
-          const double r1 = -L1 * r;
-          acc1 += (double)wgt * r1;
-          acc2 += (double)wgt * (r1 * r1 - L2 * r);
-        }
-        __syncwarp(); /* the tile buffer is rewritten by the next trip */
-      }
+      __syncthreads();
+      aa4_load_factors(s_diag, s_aux, lane, fc);
+      aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, fc,
+               s_tr + (size_t)warp * AA4_TILE * 3, (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp,
+               (unsigned long long)gridDim.x * (NW_THREADS / 32), fwd, lane, acc1, acc2);
     }
     else if (MODE == 2)
     {
