@@ -83,6 +83,8 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_stash")) slot = &g_opt_trav_stash;
   else if (!strcmp(name, "trav_short")) slot = &g_opt_trav_short;
   else if (!strcmp(name, "scratch_rows")) slot = &g_opt_scratch_rows;
+  else if (!strcmp(name, "generic_dmma")) slot = &g_opt_generic_dmma;
+  else if (!strcmp(name, "fast_evals")) slot = &g_opt_fast_evals;
   else if (!strcmp(name, "spr_batch")) slot = &g_opt_spr_batch;
   else if (!strcmp(name, "trav_debug")) slot = &g_opt_trav_debug;
   else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;

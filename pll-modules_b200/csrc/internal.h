@@ -276,6 +276,8 @@ bool flush_trav_dna4_lean(PartCtx * lead, const void * d_args, const BatchKind &
 bool launch_tipcols_encode(PartCtx * c, unsigned int tip);
 bool launch_trav_dna4_score(PartCtx * c, const pll_operation_t * ops, const unsigned char * kind, const unsigned int * cand,
                             unsigned int count, unsigned int ncand, const unsigned int * params_indices, double * host_scores);
+extern int g_opt_generic_dmma;
+extern int g_opt_fast_evals; /* DNA Gamma-4 logL / derivative kernels on the 32-site tile mapping */
 extern int g_opt_scratch_rows;
 extern int g_opt_spr_batch;
 extern int g_opt_trav_stash;

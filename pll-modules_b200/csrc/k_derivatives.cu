@@ -336,12 +336,93 @@ __global__ void __launch_bounds__(DV_THREADS, 3) deriv_dna_kernel(DerivArgs a, D
   grid_reduce_finish<2>(v, a.red);
 }
 
+/* 4 categories without invariant sites (the hot shape): the tile mapping of logl_dna4_fast_kernel
+ * (k_likelihood.cu).  A warp takes 2 tiles of 32 sites per trip = 8 independent 256-bit loads per thread; a
+ * thread's 4 elements of a tile belong to 4 different sites, and two exchange rounds leave the three sums over the
+ * rates of a DIFFERENT site in each lane, so that the two divisions of a site run on all 32 lanes instead of on a
+ * quarter of them (deriv_dna_kernel<4>: 63 us per 1 M sites with DRAM at 26 %, issue slots full of divergent
+ * DDIV sequences).  Same arithmetic per site as deriv_dna_kernel<4>. */
+#define DVF_U 2
+__global__ void __launch_bounds__(DV_THREADS, 2) deriv_dna4_fast_kernel(DerivArgs a, DiagDna dg, int reverse)
+{
+  const unsigned int lane = threadIdx.x & 31u, k = lane & 3u;
+  const unsigned int perm = ((k & 1u) << 1) | (k >> 1);
+  const double wk = a.w[k];
+  double d0[4], d1[4], d2[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j)
+  {
+    d0[j] = dg.d[k][j][0];
+    d1[j] = dg.d[k][j][1];
+    d2[j] = dg.d[k][j][2];
+  }
+  const unsigned long long tiles = ((unsigned long long)a.sites + 31) / 32;
+  const unsigned long long groups = (tiles + DVF_U - 1) / DVF_U;
+  const unsigned long long nwarps = (unsigned long long)gridDim.x * (DV_THREADS / 32);
+  double acc1 = 0.0, acc2 = 0.0;
+  for (unsigned long long g0 = (unsigned long long)blockIdx.x * (DV_THREADS / 32) + (threadIdx.x >> 5); g0 < groups;
+       g0 += nwarps)
+  {
+    const unsigned long long g = reverse ? groups - 1 - g0 : g0;
+    d4 v[DVF_U][4];
+    unsigned int wgt[DVF_U];
+    bool actf[DVF_U];
+#pragma unroll
+    for (int u = 0; u < DVF_U; ++u)
+    {
+      const unsigned long long tile = g * DVF_U + u;
+      const unsigned long long site0 = tile * 32 + (lane >> 2);
+      const double * sp = a.sum + (tile * 128 + lane) * 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+      {
+        const unsigned int r = (unsigned int)j ^ perm;
+        v[u][j] = d4{0.0, 0.0, 0.0, 0.0};
+        if (site0 + 8 * r < a.sites) v[u][j] = ldg256(sp + r * 128);
+      }
+      actf[u] = site0 + 8 * perm < a.sites;
+      wgt[u] = actf[u] ? __ldg(a.weights + site0 + 8 * perm) : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < DVF_U; ++u)
+    {
+      double L0[4], L1[4], L2[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+      {
+        const d4 s = v[u][j];
+        L0[j] = (s.x * d0[0] + s.y * d0[1] + s.z * d0[2] + s.w * d0[3]) * wk;
+        L1[j] = (s.x * d1[0] + s.y * d1[1] + s.z * d1[2] + s.w * d1[3]) * wk;
+        L2[j] = (s.x * d2[0] + s.y * d2[1] + s.z * d2[2] + s.w * d2[3]) * wk;
+      }
+      L0[0] += __shfl_xor_sync(0xffffffffu, L0[2], 1);
+      L0[1] += __shfl_xor_sync(0xffffffffu, L0[3], 1);
+      L1[0] += __shfl_xor_sync(0xffffffffu, L1[2], 1);
+      L1[1] += __shfl_xor_sync(0xffffffffu, L1[3], 1);
+      L2[0] += __shfl_xor_sync(0xffffffffu, L2[2], 1);
+      L2[1] += __shfl_xor_sync(0xffffffffu, L2[3], 1);
+      L0[0] += __shfl_xor_sync(0xffffffffu, L0[1], 2);
+      L1[0] += __shfl_xor_sync(0xffffffffu, L1[1], 2);
+      L2[0] += __shfl_xor_sync(0xffffffffu, L2[1], 2);
+      if (actf[u])
+      {
+        const double w = (double)wgt[u];
+        const double r1 = -L1[0] / L0[0];
+        const double r2 = r1 * r1 - L2[0] / L0[0];
+        acc1 += w * r1;
+        acc2 += w * r2;
+      }
+    }
+  }
+  double vv[2] = {acc1, acc2};
+  grid_reduce_finish<2>(vv, a.red);
+}
+
 /* 20 states, 4 categories, unpadded: the tile pass of aa4_pass.cuh (644 B per site); a.diag is the staged
  * [k][j][3] table of the generic path */
 #define DVA_THREADS 256
-__global__ void __launch_bounds__(DVA_THREADS, 1) deriv_aa4_kernel(DerivArgs a, int reverse)
+__global__ void __launch_bounds__(DVA_THREADS, 2) deriv_aa4_kernel(DerivArgs a, int reverse)
 {
-  __shared__ double s_tr[(DVA_THREADS / 32) * AA4_TILE * 3];
   __shared__ double s_aux[24];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   bool any_pinv = false;
@@ -355,11 +436,11 @@ __global__ void __launch_bounds__(DVA_THREADS, 1) deriv_aa4_kernel(DerivArgs a, 
     s_aux[4 + threadIdx.x] = t;
   }
   __syncthreads();
-  double fc[5][4][3];
+  double fc[4][3];
   aa4_load_factors(a.diag, s_aux, lane, fc);
   double acc1 = 0.0, acc2 = 0.0;
   aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, fc,
-           s_tr + (size_t)warp * AA4_TILE * 3, (unsigned long long)blockIdx.x * (DVA_THREADS / 32) + warp,
+           (unsigned long long)blockIdx.x * (DVA_THREADS / 32) + warp,
            (unsigned long long)gridDim.x * (DVA_THREADS / 32), reverse == 0, lane, acc1, acc2);
   double v[2] = {acc1, acc2};
   grid_reduce_finish<2>(v, a.red);
@@ -698,6 +779,16 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     /* repeated passes over one table (Newton-Raphson through the C API): alternate the direction */
     const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
     c->deriv_last_table = d_sumtable;
+    if (K == 4 && !any_pinv && g_opt_fast_evals)
+    {
+      const unsigned long long groups = (((unsigned long long)a.sites + 31) / 32 + DVF_U - 1) / DVF_U;
+      blocks = (groups + DV_THREADS / 32 - 1) / (DV_THREADS / 32);
+      if (blocks > (unsigned long long)c->sm_count * 2) blocks = (unsigned long long)c->sm_count * 2;
+      if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+      if (blocks < 1) blocks = 1;
+      deriv_dna4_fast_kernel<<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse);
+    }
+    else
     switch (K)
     {
       case 1: deriv_dna_kernel<1><<<(unsigned)blocks, DV_THREADS, 0, c->stream>>>(a, dg, reverse); break;
@@ -711,7 +802,7 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     a.diag = (const double *)dev_stage(c, diag.data(), sizeof(double) * diag.size());
     if (!a.diag) return false;
     unsigned long long blocks = (((unsigned long long)a.sites + 7) / 8 + DVA_THREADS / 32 - 1) / (DVA_THREADS / 32);
-    if (blocks > (unsigned long long)c->sm_count) blocks = c->sm_count;
+    if (blocks > (unsigned long long)c->sm_count * 2) blocks = (unsigned long long)c->sm_count * 2;
     const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
     c->deriv_last_table = d_sumtable;
     deriv_aa4_kernel<<<(unsigned)blocks, DVA_THREADS, 0, c->stream>>>(a, reverse);

@@ -212,6 +212,109 @@ __global__ void __launch_bounds__(LK_THREADS, 3) logl_dna_kernel(LoglArgs a)
   grid_reduce_finish<1>(v, a.red);
 }
 
+/* ---- 4 states, 4 categories, per-site scalers, no invariant sites: the hot shape (BASELINE C2/C4/C5) --------
+ * The kernel above spends 290 warp instructions per 32 elements, most of them on its generality and on a
+ * log() that runs with a quarter of the lanes (profiles/r02_evals_ncu_summary.txt: 93 us per 1 M sites, DRAM at
+ * 18 %).  Here a warp takes a tile of 32 sites = 128 elements as 4 rows of 32: a thread's 4 elements belong to 4
+ * different sites and one rate.  All 8 256-bit loads of a trip are in flight before the first use; register slot j
+ * holds row j ^ perm (perm = bit-reversed rate index), so that two exchange rounds with fixed send/keep slots leave
+ * in slot 0 the sum over the rates of a DIFFERENT site in each lane (the trick of the Newton kernel, k_newton.cu):
+ * 3 shuffles of doubles per 4 elements instead of 8, and the logarithm, scaler term, weight and per-site store run
+ * on all 32 lanes.  Same arithmetic per element and same order over the rates as logl_dna_kernel<4>: per-site
+ * values are bit-identical, only the order of the final sum differs. */
+int g_opt_fast_evals = 1;
+#define LKF_THREADS 256
+template <bool CTIP>
+__global__ void __launch_bounds__(LKF_THREADS, 2) logl_dna4_fast_kernel(LoglArgs a)
+{
+  __shared__ __align__(16) double s_mat[4 * 18];
+  __shared__ __align__(16) double s_freq[16];
+  for (int i = threadIdx.x; i < 64; i += blockDim.x) s_mat[(i >> 4) * 18 + (i & 15)] = a.pmat[i];
+  for (int i = threadIdx.x; i < 16; i += blockDim.x)
+    s_freq[i] = a.eigen[(unsigned long long)a.freq_idx[i / 4] * a.eigen_stride + 2 * 4 * 4 + 4 + (i & 3)];
+  __syncthreads();
+  const unsigned int lane = threadIdx.x & 31u, k = lane & 3u;
+  const unsigned int perm = ((k & 1u) << 1) | (k >> 1);
+  const double wk = a.w[k];
+  /* matrix and frequencies are re-read from shared memory per element (rows of different rates in different
+   * banks): the 128 registers hold the 8 loads of a trip */
+  const double * m = s_mat + k * 18;
+  const double * f = s_freq + k * 4;
+  const unsigned long long tiles = ((unsigned long long)a.sites + 31) / 32;
+  const unsigned long long nwarps = (unsigned long long)gridDim.x * (LKF_THREADS / 32);
+  double acc = 0.0;
+  for (unsigned long long tile = (unsigned long long)blockIdx.x * (LKF_THREADS / 32) + (threadIdx.x >> 5); tile < tiles;
+       tile += nwarps)
+  {
+    const unsigned long long site0 = tile * 32 + (lane >> 2); /* + 8 * row */
+    const double * pp = a.pclv + (tile * 128 + lane) * 4;
+    const double * cp = CTIP ? nullptr : a.cclv + (tile * 128 + lane) * 4;
+    d4 pv[4], cv[4];
+    unsigned int code[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+    {
+      const unsigned int r = (unsigned int)j ^ perm;
+      pv[j] = cv[j] = d4{0.0, 0.0, 0.0, 0.0};
+      code[j] = 0;
+      if (site0 + 8 * r < a.sites)
+      {
+        pv[j] = ldg256(pp + r * 128);
+        if (CTIP)
+          code[j] = a.ctip[site0 + 8 * r];
+        else
+          cv[j] = ldg256(cp + r * 128);
+      }
+    }
+    /* the site this lane finishes: row perm */
+    const unsigned long long sitef = site0 + 8 * perm;
+    const bool actf = sitef < a.sites;
+    unsigned int sc = 0, wgt = 0;
+    if (actf)
+    {
+      wgt = __ldg(a.weights + sitef);
+      if (a.pscaler) sc += a.pscaler[sitef];
+      if (a.cscaler) sc += a.cscaler[sitef];
+    }
+    double term[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+    {
+      double t0, t1, t2, t3;
+      if (CTIP)
+      {
+        const unsigned int cd = code[j];
+        t0 = ((cd & 1) ? m[0] : 0.0) + ((cd & 2) ? m[1] : 0.0) + ((cd & 4) ? m[2] : 0.0) + ((cd & 8) ? m[3] : 0.0);
+        t1 = ((cd & 1) ? m[4] : 0.0) + ((cd & 2) ? m[5] : 0.0) + ((cd & 4) ? m[6] : 0.0) + ((cd & 8) ? m[7] : 0.0);
+        t2 = ((cd & 1) ? m[8] : 0.0) + ((cd & 2) ? m[9] : 0.0) + ((cd & 4) ? m[10] : 0.0) + ((cd & 8) ? m[11] : 0.0);
+        t3 = ((cd & 1) ? m[12] : 0.0) + ((cd & 2) ? m[13] : 0.0) + ((cd & 4) ? m[14] : 0.0) + ((cd & 8) ? m[15] : 0.0);
+      }
+      else
+      {
+        const d4 c = cv[j];
+        t0 = m[0] * c.x + m[1] * c.y + m[2] * c.z + m[3] * c.w;
+        t1 = m[4] * c.x + m[5] * c.y + m[6] * c.z + m[7] * c.w;
+        t2 = m[8] * c.x + m[9] * c.y + m[10] * c.z + m[11] * c.w;
+        t3 = m[12] * c.x + m[13] * c.y + m[14] * c.z + m[15] * c.w;
+      }
+      const d4 p = pv[j];
+      term[j] = (p.x * f[0] * t0 + p.y * f[1] * t1 + p.z * f[2] * t2 + p.w * f[3] * t3) * wk;
+    }
+    term[0] += __shfl_xor_sync(0xffffffffu, term[2], 1);
+    term[1] += __shfl_xor_sync(0xffffffffu, term[3], 1);
+    term[0] += __shfl_xor_sync(0xffffffffu, term[1], 2);
+    if (actf)
+    {
+      double lk = site_finish(term[0], 0.0, sc, false);
+      lk *= (double)wgt;
+      if (a.persite) a.persite[sitef] = lk;
+      acc += lk;
+    }
+  }
+  double v[1] = {acc};
+  grid_reduce_finish<1>(v, a.red);
+}
+
 /* ---- 20-state path (protein) ------------------------------------------------------------------
  * thread = (site, category) like the 4-state kernel; the child's 20 values (or the tip mask as 0/1) and
  * the parent's sit in registers (5 + 5 256-bit loads), the K P-matrices in shared memory with a row
@@ -593,7 +696,21 @@ template <bool ROOT>
 static bool dispatch_logl(PartCtx * c, const LoglArgs & a)
 {
   const unsigned int K = a.K;
-  if (a.states == 4 && (K == 1 || K == 2 || K == 4 || K == 8))
+  bool no_pinv = true;
+  for (unsigned int k = 0; k < K && k < LK_MAXK; ++k) no_pinv &= !(a.pinv[k] > 0.0);
+  if (!ROOT && g_opt_fast_evals && a.states == 4 && K == 4 && !a.rate_scalers && no_pinv && (a.ctip || a.cclv))
+  {
+    unsigned long long blocks = (((unsigned long long)a.sites + 31) / 32 + LKF_THREADS / 32 - 1) / (LKF_THREADS / 32);
+    const unsigned long long cap = (unsigned long long)c->sm_count * 2; /* one resident wave */
+    if (blocks > cap) blocks = cap;
+    if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
+    if (blocks < 1) blocks = 1;
+    if (a.ctip)
+      logl_dna4_fast_kernel<true><<<(unsigned)blocks, LKF_THREADS, 0, c->stream>>>(a);
+    else
+      logl_dna4_fast_kernel<false><<<(unsigned)blocks, LKF_THREADS, 0, c->stream>>>(a);
+  }
+  else if (a.states == 4 && (K == 1 || K == 2 || K == 4 || K == 8))
   {
     const unsigned long long E = (unsigned long long)a.sites * K;
     unsigned long long blocks = (E + LK_THREADS - 1) / LK_THREADS;

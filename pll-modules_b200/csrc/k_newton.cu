@@ -157,13 +157,11 @@ __device__ __forceinline__ void newton_publish(const NewtonArgs & a, double x, d
 
 
 /* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates);
- * 4: 20 states, K = 4, unpadded (protein Gamma-4: warp-contiguous 1 KB loads, factors in registers) */
+ * 4: 20 states, K = 4, unpadded (protein Gamma-4: a lane per (rate, state chunk), 640-byte warp loads) */
 template <int MODE>
-__global__ void __launch_bounds__(NW_THREADS, MODE == 4 ? 1 : (MODE == 2 ? 2 : 3)) newton_kernel(NewtonArgs a)
+__global__ void __launch_bounds__(NW_THREADS, (MODE == 4 || MODE == 2) ? 2 : 3) newton_kernel(NewtonArgs a)
 {
   constexpr bool DNA = MODE == 1 || MODE == 2;
-  /* MODE 4: per-item partial sums of a warp's tile, [item][L0 L1 L2] */
-  __shared__ double s_tr[MODE == 4 ? (NW_THREADS / 32) * AA4_TILE * 3 : 1];
   __shared__ double s_aux[24]; /* MODE 4: w_k (1 - pinv_k) | invariant-site term per state */
   cg::grid_group grid = cg::this_grid();
   __shared__ double s_diag[NW_MAX_DIAG * 3];
@@ -235,8 +233,8 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 4 ? 1 : (MODE == 2 ? 2 : 3
     const bool fwd = (iter & 1u) == 0;
     if (MODE == 4)
     {
-      /* 20 states x 4 rates: warp-contiguous loads, factors in registers (aa4_pass.cuh) */
-      double fc[5][4][3];
+      /* 20 states x 4 rates: lane = (rate, state chunk), factors in registers (aa4_pass.cuh) */
+      double fc[4][3];
       if (threadIdx.x < 4) s_aux[threadIdx.x] = a.w[threadIdx.x] * (1.0 - a.pinv[threadIdx.x]);
       if (threadIdx.x < 20)
       {
@@ -249,7 +247,7 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 4 ? 1 : (MODE == 2 ? 2 : 3
       __syncthreads();
       aa4_load_factors(s_diag, s_aux, lane, fc);
       aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, fc,
-               s_tr + (size_t)warp * AA4_TILE * 3, (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp,
+               (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp,
                (unsigned long long)gridDim.x * (NW_THREADS / 32), fwd, lane, acc1, acc2);
     }
     else if (MODE == 2)

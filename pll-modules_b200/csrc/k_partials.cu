@@ -56,6 +56,8 @@ struct GenOpArgs
   int is4; /* 4-state partitions store the raw mask as the tip code */
 };
 
+int g_opt_generic_dmma = 1; /* 17..64 states (not 20): per-operation DMMA kernel instead of the scalar one */
+
 #define GEN_THREADS 128
 #define GEN_MAXS 64
 
@@ -130,6 +132,140 @@ __global__ void __launch_bounds__(GEN_THREADS) partial_generic_kernel(GenOpArgs 
   }
   double * dst = a.parent + e * sp;
   for (unsigned int i = 0; i < s; ++i) dst[i] = flag ? out[i] * SCALE_FACTOR_D : out[i];
+}
+
+/* ------------------------------------------------------------------------------------------ */
+/* 17..64 states except 20 (codon models: 61): one operation per launch on the FP64 tensor cores */
+/* ------------------------------------------------------------------------------------------ */
+/* X[site][i] = sum_j C[site][j] P[i][j] per rate category is a dense [sites x s] x [s x s] product
+ * (core_partials.c:612-764 computes it with s^2 scalar FMAs per site and category): DMMA tiles
+ * mma.sync.m8n8k4.f64 with M = 8 sites, N = 8 parent states (ceil(s/8) tiles), K = 4 child states (sp/4 steps).
+ * A fragment (lane = 4 row + col): the child CLV element [site0 + row][4 ks + col], one 8-byte load per k-step
+ * (a quad of lanes reads 32 contiguous bytes); B fragment: P[8 nt + row][4 ks + col] from shared memory (row pitch
+ * 68 doubles: the 16 lanes of a half warp hit 16 different bank pairs); D fragment: parent states 8 nt + 2 col, +1
+ * of site row.  A CTA stages both matrices of ONE category (70 KB) and runs its 64 tiles of 8 sites through
+ * them, category after category; a warp always owns the same tiles, so the per-site maximum over the categories
+ * accumulates in shared memory without atomics, and the rare rescaling (all K s entries of a site < 2^-256:
+ * core_partials.c:729-763) is a second pass of the warp over what it stored.  Tip children (tip patterns) are
+ * sums of matrix columns over the set bits of the code's state mask.  Per-rate scalers: generic kernel. */
+#define PD_WARPS 8
+#define PD_PITCH 68
+#define PD_TILES 64 /* tiles of 8 sites per CTA */
+#define PD_SMEM (2 * 64 * PD_PITCH * sizeof(double) + PD_TILES * 8 * sizeof(int))
+
+__device__ __forceinline__ void pd_dmma(double & c0, double & c1, double a, double b)
+{
+  asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+__global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a)
+{
+  extern __shared__ __align__(16) double pd_sm[];
+  double * sM[2] = {pd_sm, pd_sm + 64 * PD_PITCH};
+  int * s_max = reinterpret_cast<int *>(pd_sm + 2 * 64 * PD_PITCH);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int row = lane >> 2, col = lane & 3;
+  const unsigned int s = a.states, sp = a.sp, K = a.K;
+  const unsigned int NT = (s + 7) / 8, KS = sp / 4;
+  const unsigned long long tile0 = (unsigned long long)blockIdx.x * PD_TILES;
+  const bool tip[2] = {a.ltip != nullptr, a.rtip != nullptr};
+  const bool tiptip = tip[0] && tip[1];
+  for (int i = threadIdx.x; i < PD_TILES * 8; i += blockDim.x) s_max[i] = -2147483647 - 1;
+
+  for (unsigned int k = 0; k < K; ++k)
+  {
+    __syncthreads(); /* everybody is done with the previous category's matrices */
+    for (unsigned int idx = threadIdx.x; idx < 2 * 64 * 64; idx += blockDim.x)
+    {
+      const unsigned int q = idx >> 12, i = (idx >> 6) & 63u, j = idx & 63u;
+      const double * m = q ? a.rmat : a.lmat;
+      sM[q][i * PD_PITCH + j] = (i < s && j < s) ? __ldg(m + ((size_t)k * s + i) * sp + j) : 0.0;
+    }
+    __syncthreads();
+    for (unsigned int t = warp; t < PD_TILES; t += PD_WARPS)
+    {
+      const unsigned long long site = (tile0 + t) * 8 + row;
+      if ((tile0 + t) * 8 >= a.sites) break; /* warp-uniform */
+      const bool act = site < a.sites;
+      double D[2][8][2];
+#pragma unroll
+      for (int q = 0; q < 2; ++q)
+      {
+        const double * M = sM[q];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) D[q][nt][0] = D[q][nt][1] = 0.0;
+        if (tip[q])
+        {
+          unsigned long long mask = 0;
+          if (act) mask = a.tipmap[(q ? a.rtip : a.ltip)[site]];
+          while (mask)
+          {
+            const unsigned int j = (unsigned int)__ffsll((long long)mask) - 1u;
+            mask &= mask - 1;
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt)
+              if ((unsigned int)nt < NT)
+              {
+                D[q][nt][0] += M[(nt * 8 + 2 * col) * PD_PITCH + j];
+                D[q][nt][1] += M[(nt * 8 + 2 * col + 1) * PD_PITCH + j];
+              }
+          }
+        }
+        else
+        {
+          const double * cv = (q ? a.right : a.left) + ((size_t)site * K + k) * sp + col;
+          for (unsigned int ks = 0; ks < KS; ++ks)
+          {
+            const double av = (act && 4 * ks + col < s) ? cv[4 * ks] : 0.0; /* padding is never read (may hold anything) */
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt)
+              if ((unsigned int)nt < NT) pd_dmma(D[q][nt][0], D[q][nt][1], av, M[(nt * 8 + row) * PD_PITCH + 4 * ks + col]);
+          }
+        }
+      }
+      int m = -2147483647 - 1;
+      double * dst = a.parent + ((size_t)site * K + k) * sp;
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt)
+        if ((unsigned int)nt < NT)
+        {
+          const double o0 = D[0][nt][0] * D[1][nt][0], o1 = D[0][nt][1] * D[1][nt][1];
+          const unsigned int i0 = nt * 8 + 2 * col;
+          if (i0 < s) m = max(m, __double2hiint(o0));
+          if (i0 + 1 < s) m = max(m, __double2hiint(o1));
+          if (act && i0 < sp) *reinterpret_cast<double2 *>(dst + i0) = make_double2(o0, o1); /* sp is a multiple of 4 */
+        }
+      m = max(m, __shfl_xor_sync(0xffffffffu, m, 1));
+      m = max(m, __shfl_xor_sync(0xffffffffu, m, 2));
+      if (col == 0) s_max[t * 8 + row] = max(s_max[t * 8 + row], m);
+    }
+  }
+  if (!a.pscaler) return;
+  __syncwarp();
+  /* scaler counts and the rare rescaling pass: the warp's own tiles */
+  for (unsigned int t = warp; t < PD_TILES; t += PD_WARPS)
+  {
+    const unsigned long long site = (tile0 + t) * 8 + row;
+    if ((tile0 + t) * 8 >= a.sites) break;
+    const bool act = site < a.sites;
+    const bool scale = act && !tiptip && s_max[t * 8 + row] < 0x2FF00000;
+    if (act && col == 0)
+    {
+      unsigned int v = scale ? 1u : 0u;
+      if (a.lscaler) v += a.lscaler[site];
+      if (a.rscaler) v += a.rscaler[site];
+      a.pscaler[site] = v;
+    }
+    if (__any_sync(0xffffffffu, scale))
+    {
+      __syncwarp(); /* the stores of the other lanes of this warp */
+      if (scale)
+      {
+        double * rowp = a.parent + (size_t)site * K * sp;
+        for (unsigned int e = col; e < K * sp; e += 4) rowp[e] *= SCALE_FACTOR_D;
+      }
+    }
+  }
 }
 
 /* ------------------------------------------------------------------------------------------ */
@@ -271,6 +407,23 @@ bool launch_partials(PartCtx * c, const pll_operation_t * ops_in, unsigned int c
     a.K = K;
     a.rate_scalers = rate_scalers;
     a.is4 = p->states == 4;
+    if (g_opt_generic_dmma && p->states > 16 && p->states <= 64 && p->states_padded <= 64 && !rate_scalers &&
+        (!pattern_tip || c->d_tipmap))
+    {
+      static bool attr_set = false;
+      if (!attr_set)
+      {
+        if (!pllb200_cuda_ok(cudaFuncSetAttribute(partial_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PD_SMEM),
+                             "partial_dmma_kernel smem"))
+          return false;
+        attr_set = true;
+      }
+      const unsigned int tiles = (c->sites_alloc + 7) / 8;
+      partial_dmma_kernel<<<(tiles + PD_TILES - 1) / PD_TILES, PD_WARPS * 32, PD_SMEM, c->stream>>>(a);
+      ++g_kernel_launches;
+      if (!pllb200_cuda_ok(cudaGetLastError(), "partial_dmma_kernel launch")) return false;
+      continue;
+    }
     const unsigned int spb = GEN_THREADS / K;
     const unsigned int blocks = (c->sites_alloc + spb - 1) / spb;
     partial_generic_kernel<<<blocks, GEN_THREADS, 0, c->stream>>>(a);

@@ -173,6 +173,20 @@ __global__ void pmatrix_batch_kernel(const PmatBatchPart * __restrict__ parts)
 static bool tiptab_usable(const PartCtx * c) { return c->d_tiptab && c->d_tipmap && c->pub.maxstates <= PM_TIP_CODES; }
 
 /* one matrix whose branch length is already on the device (written by the queued Newton kernel) */
+/* more than 48 KB of dynamic shared memory (more than 54 states) needs an opt-in per kernel */
+static bool pmat_smem_optin(size_t smem)
+{
+  static size_t granted = 48 * 1024;
+  if (smem <= granted) return true;
+  if (!pllb200_cuda_ok(cudaFuncSetAttribute(pmatrix_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                       "pmatrix_kernel shared memory") ||
+      !pllb200_cuda_ok(cudaFuncSetAttribute(pmatrix_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                       "pmatrix_batch_kernel shared memory"))
+    return false;
+  granted = smem;
+  return true;
+}
+
 bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,
                            const double * d_length)
 {
@@ -206,6 +220,7 @@ bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, uns
   unsigned int threads = ((s * sp + 31) / 32) * 32;
   if (threads > 512) threads = 512;
   const size_t smem = sizeof(double) * (sp + 2 * s * sp);
+  if (!pmat_smem_optin(smem)) return false;
   pmatrix_kernel<<<K, threads, smem, c->stream>>>(c->d_pmat, c->d_pmat_il, c->d_eigen, c->eigen_stride, d_idx,
                                                   d_length, s, sp, K, a);
   ++g_kernel_launches;
@@ -292,6 +307,7 @@ bool launch_pmatrix(PartCtx * c, const unsigned int * params_indices,
   unsigned int threads = ((s * sp + 31) / 32) * 32;
   if (threads > 512) threads = 512;
   const size_t smem = sizeof(double) * (sp + 2 * s * sp);
+  if (!pmat_smem_optin(smem)) return false;
   if (batch_collects(BK_PMAT))
   {
     PmatBatchPart b;

@@ -638,7 +638,7 @@ def test_baseline_c5_slice_matches_reference():
 @needs_ref
 @pytest.mark.parametrize("kw", [
     dict(tips=12, sites=150, states=61, rate_cats=4),                  # codon-sized alphabet (row N1): generic kernels
-    dict(tips=20, sites=64, states=61, rate_cats=2, brlen_scale=12.0),  # deep: scaling on the generic path
+    dict(tips=110, sites=64, states=61, rate_cats=2, brlen_scale=12.0), # deep: scaling on the generic path
 ], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
 def test_codon_sized_alphabet_matches_reference(kw):
     """61 states (the codon alphabet size): CLVs, scalers, logL, derivatives and one smoothing pass against the
@@ -657,6 +657,76 @@ def test_codon_sized_alphabet_matches_reference(kw):
         a = ref.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=1, lh_epsilon=1.0)
         b = dev.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=1, lh_epsilon=1.0)
         assert rel(b, a) < 1e-8, (b, a)
+
+
+@pytest.mark.parametrize("kw", [
+    dict(tips=14, sites=333, states=61),                                   # codon size, tip patterns
+    dict(tips=10, sites=100, states=64, rate_cats=2),                      # full tiles
+    dict(tips=12, sites=77, states=17, rate_cats=1),                       # 3 n-tiles, ragged
+    dict(tips=16, sites=250, states=25, attributes=0),                     # tip CLVs: every child through the tensor pipe
+    dict(tips=150, sites=130, states=32, brlen_scale=14.0),                # deep: the rescaling pass
+    dict(tips=120, sites=9, states=61, brlen_scale=10.0, attributes=0),    # one tile + one site, rescaling
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_generic_dmma_kernel_equals_the_scalar_generic_kernel(kw):
+    """partial_dmma_kernel (17..64 states on the FP64 tensor cores, one launch per operation) against
+    partial_generic_kernel (scalar): same scaler counts, CLVs to rounding (the DMMA adds in another order)."""
+    pkg = load_product_package()
+    tips = kw["tips"]
+    out = {}
+    try:
+        for mode in (1, 0):
+            pkg.set_option("generic_dmma", mode)
+            with Harness("b200", **kw) as h:
+                ll = h.loglh(0)
+                out[mode] = (ll, [h.clv(tips + i).copy() for i in range(tips - 2)],
+                             [h.scaler(i).copy() for i in range(tips - 2)])
+    finally:
+        pkg.set_option("generic_dmma", 1)
+    assert rel(out[1][0], out[0][0]) < 1e-12, (out[1][0], out[0][0])
+    for i in range(tips - 2):
+        assert np.array_equal(out[1][2][i], out[0][2][i]), ("scaler", i)
+        np.testing.assert_allclose(out[1][1][i], out[0][1][i], rtol=1e-11, atol=0)
+    if kw.get("brlen_scale", 1.0) > 1.0:
+        assert any(int(s.sum()) > 0 for s in out[1][2])
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kw", [
+    dict(tips=16, sites=10000),                                   # inner-inner and tip-inner edges, full tiles
+    dict(tips=9, sites=37),                                       # one tile + 5 sites
+    dict(tips=5, sites=1),
+    dict(tips=100, sites=2003, brlen_scale=10.0),                 # scaler counts in the site term
+    dict(tips=30, sites=513, attributes=0),                       # tip CLVs
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_dna_gamma4_tile_kernels_equal_the_general_kernels(kw):
+    """logl_dna4_fast_kernel / deriv_dna4_fast_kernel (32-site tiles, a lane finishes a site) against
+    logl_dna_kernel<4> / deriv_dna_kernel<4>: per-site log-likelihoods bit for bit, sums to rounding, on tip edges
+    and inner edges."""
+    pkg = load_product_package()
+    tips = kw["tips"]
+    brl = [1e-4, 0.01, 0.3, 5.0]
+    out = {}
+    try:
+        for mode in (1, 0):
+            pkg.set_option("fast_evals", mode)
+            with Harness("b200", **kw) as h:
+                res = []
+                nsub = tips + 3 * (tips - 2)
+                nodes = [0, tips - 1] + list(range(tips, nsub, max(1, (nsub - tips) // 5)))
+                for node in nodes:
+                    h.set_root(int(node))
+                    ll = h.loglh()
+                    ll2, per = h.edge_loglh_multi(h.root(), persite=True)
+                    df, ddf = h.derivatives(h.root(), brl)
+                    res.append((ll, ll2, per.copy(), df.copy(), ddf.copy()))
+                out[mode] = res
+    finally:
+        pkg.set_option("fast_evals", 1)
+    for a, b in zip(out[1], out[0]):
+        assert np.array_equal(a[2], b[2])
+        assert rel(a[0], b[0]) < 1e-13 and rel(a[1], b[1]) < 1e-13
+        np.testing.assert_allclose(a[3], b[3], rtol=1e-10, atol=1e-9)
+        np.testing.assert_allclose(a[4], b[4], rtol=1e-10, atol=1e-9)
 
 
 # ---- model-parameter optimisers over device-resident state (SURVEY.md §8a rows a13/a14) ----
