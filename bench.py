@@ -369,32 +369,44 @@ def main():
     extra = {}
     # ---- logL and derivative evaluations/s at fixed S (second half of BASELINE's metric) -----------
     root = h.root()
-    nrep = max(3, a.steps)
+    nrep = max(20, a.steps)
+    h.edge_loglh(root)
     barrier()
-    t0 = time.perf_counter()
-    for _ in range(nrep):
-        h.edge_loglh(root)
+    logl_s = h.time_edge_loglh(root, nrep)            # C loop: launch + kernel + host wait per call
     barrier()
-    logl_s = (time.perf_counter() - t0) / nrep
     h.derivatives(root, [0.1])
     barrier()
     t0 = time.perf_counter()
     h.derivatives(root, [0.1])
     barrier()
     t1 = time.perf_counter() - t0
-    nder = 8
-    t0 = time.perf_counter()
-    h.derivatives(root, list(np.linspace(0.01, 0.5, 1 + nder)))
+    deriv_s = max(1e-9, h.time_derivatives(root, nrep))
     barrier()
-    tn = time.perf_counter() - t0
-    deriv_s = max(1e-9, (tn - t1) / nder)
+    # the kernels alone, by CUDA events the library records around them on its stream
+    pkg.set_option("eval_timing", 1)
+    lk_us, dv_us = [], []
+    for i in range(nrep):
+        h.edge_loglh(root)
+        lk_us.append(pkg.last_eval_kernel_us())
+    for i in range(nrep):
+        h.derivatives(root, [0.01 + 0.02 * i])
+        dv_us.append(pkg.last_eval_kernel_us())
+    pkg.set_option("eval_timing", 0)
+    lk_us, dv_us = sorted(lk_us), sorted(dv_us)
     root_is_ti = h.node_info(root)["tip"] or h.node_info(h.node_info(root)["back"])["tip"]
     extra["logl_evals_per_s"] = world / logl_s if world == 1 else 1.0 / logl_s
     extra["logl_GBps_algorithmic"] = (137 if root_is_ti else 268) * S / logl_s / 1e9
     extra["deriv_evals_per_s"] = 1.0 / deriv_s
     extra["deriv_GBps_algorithmic"] = 132 * S / deriv_s / 1e9
     extra["sumtable_builds_per_s"] = 1.0 / max(1e-9, t1 - deriv_s)
-    extra["evals_note"] = ("host wall clock through the C ABI incl. launch + sync, %d sites per GPU, root edge is %s"
+    per_site_logl = 137 if root_is_ti else 268
+    extra["logl_kernel_us"] = lk_us[len(lk_us) // 2]
+    extra["logl_kernel_GBps"] = per_site_logl * S / (lk_us[len(lk_us) // 2] * 1e-6) / 1e9
+    extra["deriv_kernel_us"] = dv_us[len(dv_us) // 2]
+    extra["deriv_kernel_GBps"] = 132 * S / (dv_us[len(dv_us) // 2] * 1e-6) / 1e9
+    extra["eval_kernel_note"] = ("median of %d launches, CUDA events around the kernel on its stream; the derivative pass re-reads "
+                                 "a %.0f MB table, part of which the previous pass left in the 126 MB L2" % (nrep, 128e-6 * S))
+    extra["evals_note"] = ("host wall clock of a C loop over the C ABI incl. launch + host wait per call, %d sites per GPU, root edge is %s"
                            % (S, "tip-inner" if root_is_ti else "inner-inner"))
     if a.blo:
         h.set_branch_lengths(brl)

@@ -1039,6 +1039,10 @@ void pllb200_get_stats(pllb200_stats_t * out);
 void pllb200_reset_stats(void);
 /* name in {"trav_ctas_per_sm","trav_reorder","fuse_root","trav_variant","trav_forward","fused_newton","queued_newton"}; returns previous value, -1 if unknown */
 int pllb200_set_option(const char * name, int value);
+/* Measurement aid (no reference counterpart): with option "eval_timing" = 1 the logL / derivative launchers bracket
+ * their kernel with CUDA events on its stream; this returns the device time of the most recent one in microseconds
+ * (-1 if none).  bench.py reports it next to the host wall-clock rate of the same calls. */
+double pllb200_last_eval_kernel_us(void);
 
 #ifdef __cplusplus
 }

@@ -505,6 +505,42 @@ int h_derivatives(void * hv, unsigned int p, unsigned int node_index, const doub
   return 1;
 }
 
+/* seconds per call of pll_compute_edge_loglikelihood / pll_compute_likelihood_derivatives in a C loop (no
+ * interpreter between the calls); the derivative loop varies the branch length like a Newton iteration does */
+double h_time_edge_loglh(void * hv, unsigned int p, unsigned int node_index, int reps)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_unode_t * n = h->ti->subnodes[node_index];
+  struct timespec t0, t1;
+  volatile double sink = 0.0;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  for (int r = 0; r < reps; ++r)
+    sink += pll_compute_edge_loglikelihood(h->parts[p], n->clv_index, n->scaler_index, n->back->clv_index,
+                                           n->back->scaler_index, n->pmatrix_index, h->param_idx[p], NULL);
+  clock_gettime(CLOCK_MONOTONIC, &t1);
+  (void)sink;
+  return ((double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec)) / (reps > 0 ? reps : 1);
+}
+
+double h_time_derivatives(void * hv, unsigned int p, unsigned int node_index, int reps)
+{
+  harness_t * h = (harness_t *)hv;
+  pll_unode_t * e = h->ti->subnodes[node_index];
+  if (!pll_update_sumtable(h->parts[p], e->clv_index, e->back->clv_index, e->scaler_index,
+                           e->back->scaler_index, h->param_idx[p], h->sumtables[p]))
+    return -1.0;
+  struct timespec t0, t1;
+  double df, ddf;
+  clock_gettime(CLOCK_MONOTONIC, &t0);
+  for (int r = 0; r < reps; ++r)
+    if (!pll_compute_likelihood_derivatives(h->parts[p], e->scaler_index, e->back->scaler_index,
+                                            0.01 + 0.49 * (double)r / (double)(reps > 1 ? reps - 1 : 1),
+                                            h->param_idx[p], h->sumtables[p], &df, &ddf))
+      return -1.0;
+  clock_gettime(CLOCK_MONOTONIC, &t1);
+  return ((double)(t1.tv_sec - t0.tv_sec) + 1e-9 * (double)(t1.tv_nsec - t0.tv_nsec)) / (reps > 0 ? reps : 1);
+}
+
 /* out: sites*rate_cats*states (unpadded) */
 int h_get_sumtable(void * hv, unsigned int p, double * out)
 {

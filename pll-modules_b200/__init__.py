@@ -67,6 +67,13 @@ def set_option(name, value):
     return load().pllb200_set_option(name.encode(), int(value))
 
 
+def last_eval_kernel_us():
+    """Device time of the most recent logL / derivative kernel (option "eval_timing" must be 1), microseconds."""
+    lib = load()
+    lib.pllb200_last_eval_kernel_us.restype = ctypes.c_double
+    return lib.pllb200_last_eval_kernel_us()
+
+
 def exchange_create(partition_ptr):
     """CUDA IPC handle (64 bytes) of this rank's exchange buffer for the multi-GPU Newton kernel."""
     buf = ctypes.create_string_buffer(64)

@@ -27,6 +27,33 @@ int g_opt_fuse_root = 1;
 /* scratch CLV / scaler rows behind the arenas of Gamma-4 DNA partitions: the batched regraft scoring of
  * pllmod_algo_spr_round keeps one outward-pointing CLV per search depth there (radius_max + 2 rows) */
 int g_opt_scratch_rows = 12;
+/* measurement aid (bench.py): device time of the last logL / derivative kernel, by events on its stream */
+int g_opt_eval_timing = 0;
+static cudaEvent_t g_et0, g_et1;
+static bool g_et_ready = false, g_et_pending = false;
+void eval_timing_begin(cudaStream_t s)
+{
+  if (!g_opt_eval_timing) return;
+  if (!g_et_ready)
+  {
+    if (cudaEventCreate(&g_et0) != cudaSuccess || cudaEventCreate(&g_et1) != cudaSuccess) return;
+    g_et_ready = true;
+  }
+  cudaEventRecord(g_et0, s);
+}
+void eval_timing_end(cudaStream_t s)
+{
+  if (!g_opt_eval_timing || !g_et_ready) return;
+  cudaEventRecord(g_et1, s);
+  g_et_pending = true;
+}
+extern "C" double pllb200_last_eval_kernel_us(void)
+{
+  if (!g_et_pending) return -1.0;
+  float ms = 0.f;
+  if (cudaEventSynchronize(g_et1) != cudaSuccess || cudaEventElapsedTime(&ms, g_et0, g_et1) != cudaSuccess) return -1.0;
+  return 1000.0 * (double)ms;
+}
 int g_opt_spr_batch = 1; /* pllmod_algo_spr_round, fast mode: score all candidates of a pruned subtree in one launch */
 
 static __thread int t_device = -1;
@@ -85,6 +112,7 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "scratch_rows")) slot = &g_opt_scratch_rows;
   else if (!strcmp(name, "generic_dmma")) slot = &g_opt_generic_dmma;
   else if (!strcmp(name, "fast_evals")) slot = &g_opt_fast_evals;
+  else if (!strcmp(name, "eval_timing")) slot = &g_opt_eval_timing;
   else if (!strcmp(name, "spr_batch")) slot = &g_opt_spr_batch;
   else if (!strcmp(name, "trav_debug")) slot = &g_opt_trav_debug;
   else if (!strcmp(name, "fused_newton")) slot = &g_opt_fused_newton;

@@ -277,6 +277,9 @@ bool launch_tipcols_encode(PartCtx * c, unsigned int tip);
 bool launch_trav_dna4_score(PartCtx * c, const pll_operation_t * ops, const unsigned char * kind, const unsigned int * cand,
                             unsigned int count, unsigned int ncand, const unsigned int * params_indices, double * host_scores);
 extern int g_opt_generic_dmma;
+extern int g_opt_eval_timing;
+void eval_timing_begin(cudaStream_t s);
+void eval_timing_end(cudaStream_t s);
 extern int g_opt_fast_evals; /* DNA Gamma-4 logL / derivative kernels on the 32-site tile mapping */
 extern int g_opt_scratch_rows;
 extern int g_opt_spr_batch;
@@ -300,7 +303,7 @@ bool newton_fused_supported(const PartCtx * c);
 bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
                    double xmin, double x0, double xmax, double tol, unsigned int max_iters,
                    double scale, int slot, double * brlen_io = nullptr, int x0_from_device = 0,
-                   int revert_on_limit = 0);
+                   int revert_on_limit = 0, int eval_only = 0);
 bool launch_newton_multi(PartCtx ** cs, unsigned int count, unsigned int * const * params_indices,
                          double * const * d_sumtables, const double * scales, double xmin, double x0,
                          double xmax, double tol, unsigned int max_iters, int slot);

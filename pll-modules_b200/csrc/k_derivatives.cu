@@ -418,12 +418,13 @@ __global__ void __launch_bounds__(DV_THREADS, 2) deriv_dna4_fast_kernel(DerivArg
   grid_reduce_finish<2>(vv, a.red);
 }
 
-/* 20 states, 4 categories, unpadded: the tile pass of aa4_pass.cuh (644 B per site); a.diag is the staged
+/* 20 states, 4 categories, unpadded: the tensor-core pass of aa4_pass.cuh (644 B per site); a.diag is the staged
  * [k][j][3] table of the generic path */
 #define DVA_THREADS 256
-__global__ void __launch_bounds__(DVA_THREADS, 2) deriv_aa4_kernel(DerivArgs a, int reverse)
+__global__ void __launch_bounds__(DVA_THREADS, 3) deriv_aa4_kernel(DerivArgs a, int reverse)
 {
   __shared__ double s_aux[24];
+  __shared__ double s_bt[AA4_BT];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   bool any_pinv = false;
   for (unsigned int kk = 0; kk < 4; ++kk) any_pinv |= a.pinv[kk] > 0.0;
@@ -436,10 +437,10 @@ __global__ void __launch_bounds__(DVA_THREADS, 2) deriv_aa4_kernel(DerivArgs a, 
     s_aux[4 + threadIdx.x] = t;
   }
   __syncthreads();
-  double fc[4][3];
-  aa4_load_factors(a.diag, s_aux, lane, fc);
+  aa4_build_b(a.diag, s_aux, s_bt);
+  __syncthreads();
   double acc1 = 0.0, acc2 = 0.0;
-  aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, fc,
+  aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, s_bt,
            (unsigned long long)blockIdx.x * (DVA_THREADS / 32) + warp,
            (unsigned long long)gridDim.x * (DVA_THREADS / 32), reverse == 0, lane, acc1, acc2);
   double v[2] = {acc1, acc2};
@@ -695,6 +696,20 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Invalid scaler index in derivative call.");
     return false;
   }
+  /* 4 states x 4 rates without ascertainment correction: one pass of the Newton kernel's TMA ring (k_newton.cu) —
+   * the table streams through shared memory with two stages in flight per CTA instead of through registers */
+  if (s == 4 && p->sites >= 4096 && K == 4 && !asc_type && g_opt_fast_evals == 1 && g_opt_fused_newton == 1 &&
+      newton_fused_supported(c))
+  {
+    eval_timing_begin(c->stream);
+    const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
+    c->deriv_last_table = d_sumtable;
+    if (!launch_newton(c, params_indices, d_sumtable, branch_length, branch_length, branch_length, 0.0, 1, 1.0, slot,
+                       nullptr, 0, 0, reverse ? 2 : 1))
+      return false;
+    eval_timing_end(c->stream);
+    return true;
+  }
   if (!dev_sync_inputs(c) || !dev_sync_eigen(c, params_indices)) return false;
   DerivArgs a;
   memset(&a, 0, sizeof(a));
@@ -769,6 +784,7 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
       }
     }
   }
+  eval_timing_begin(c->stream);
   if (dna)
   {
     const unsigned long long E = (unsigned long long)a.sites * K;
@@ -802,7 +818,7 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     a.diag = (const double *)dev_stage(c, diag.data(), sizeof(double) * diag.size());
     if (!a.diag) return false;
     unsigned long long blocks = (((unsigned long long)a.sites + 7) / 8 + DVA_THREADS / 32 - 1) / (DVA_THREADS / 32);
-    if (blocks > (unsigned long long)c->sm_count * 2) blocks = (unsigned long long)c->sm_count * 2;
+    if (blocks > (unsigned long long)c->sm_count * 3) blocks = (unsigned long long)c->sm_count * 3;
     const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
     c->deriv_last_table = d_sumtable;
     deriv_aa4_kernel<<<(unsigned)blocks, DVA_THREADS, 0, c->stream>>>(a, reverse);
@@ -818,6 +834,7 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
     deriv_generic_kernel<<<(unsigned)blocks, DVG_THREADS, 0, c->stream>>>(a);
   }
+  eval_timing_end(c->stream);
   ++g_kernel_launches;
   if (!pllb200_cuda_ok(cudaGetLastError(), "derivative kernel launch")) return false;
   if (asc_terms)

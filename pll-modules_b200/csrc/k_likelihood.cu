@@ -315,6 +315,178 @@ __global__ void __launch_bounds__(LKF_THREADS, 2) logl_dna4_fast_kernel(LoglArgs
   grid_reduce_finish<1>(v, a.red);
 }
 
+/* ---- the same shape with the CLVs streamed through a TMA ring ------------------------------------------------
+ * The register kernel above is latency-bound (ncu, 1 M sites: 16 warps per SM issue their loads, wait, compute
+ * ~440 instructions per trip and only then ask for more: 3.2 TB/s).  Here one producer thread keeps whole stages in
+ * flight by cp.async.bulk — per 128 sites both CLV tiles (2 x 16 KB, or the tip codes), the scaler counts and the
+ * pattern weights, completion on one mbarrier per stage — while 8 consumer warps lift a stage into registers, hand
+ * it back and compute: the pattern of newton_dna4_tma_kernel (k_newton.cu).  Thread t owns elements t and 256 + t
+ * of a tile = one rate of two sites; slot j holds row j ^ (k & 1), so that one fixed-slot exchange and one
+ * butterfly leave the sum over the rates in the lanes with k < 2, one site each.  Per-site arithmetic and the
+ * order over the rates are those of logl_dna_kernel<4>. */
+#define LT_SITES 128
+#define LT_TILE (LT_SITES * 4)
+#define LT_CONSUMERS 256
+#define LT_THREADS (LT_CONSUMERS + 32)
+
+template <bool CTIP>
+struct LoglTmaSmem
+{
+  static constexpr int STAGES = CTIP ? 5 : 3;
+  double p[STAGES][LT_TILE * 4];
+  double c[CTIP ? 1 : STAGES][CTIP ? 4 : LT_TILE * 4];
+  unsigned int psc[STAGES][LT_SITES];
+  unsigned int csc[STAGES][LT_SITES];
+  unsigned int wts[STAGES][LT_SITES];
+  unsigned char code[STAGES][LT_SITES];
+  unsigned long long full[STAGES];
+  unsigned long long empty[STAGES];
+  double mat[4 * 18];
+  double freq[16];
+};
+
+__device__ __forceinline__ void lt_mbar_arrive(unsigned long long * bar)
+{
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+/* 32 bytes of a staged element without bank conflicts: lanes 4-7 of every 8 read the upper half first */
+__device__ __forceinline__ d4 lt_lift(const double * src, unsigned int swz)
+{
+  const double2 h0 = *reinterpret_cast<const double2 *>(src + 2 * swz);
+  const double2 h1 = *reinterpret_cast<const double2 *>(src + 2 * (swz ^ 1u));
+  const double2 lo = swz ? h1 : h0, hi = swz ? h0 : h1;
+  return d4{lo.x, lo.y, hi.x, hi.y};
+}
+
+template <bool CTIP>
+__global__ void __launch_bounds__(LT_THREADS, 2) logl_dna4_tma_kernel(LoglArgs a)
+{
+  using Smem = LoglTmaSmem<CTIP>;
+  constexpr int STAGES = Smem::STAGES;
+  extern __shared__ __align__(128) unsigned char lt_smem_raw[];
+  Smem & sm = *reinterpret_cast<Smem *>(lt_smem_raw);
+  const unsigned int tid = threadIdx.x, lane = tid & 31u;
+  const bool producer = tid >= LT_CONSUMERS;
+  if (tid == 0)
+  {
+    for (int st = 0; st < STAGES; ++st)
+    {
+      mbar_init(&sm.full[st], 1);
+      mbar_init(&sm.empty[st], LT_CONSUMERS / 32);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (unsigned int i = tid; i < 64; i += blockDim.x) sm.mat[(i >> 4) * 18 + (i & 15)] = a.pmat[i];
+  for (unsigned int i = tid; i < 16; i += blockDim.x)
+    sm.freq[i] = a.eigen[(unsigned long long)a.freq_idx[i / 4] * a.eigen_stride + 2 * 4 * 4 + 4 + (i & 3)];
+  __syncthreads();
+
+  const unsigned long long tiles = ((unsigned long long)a.sites + LT_SITES - 1) / LT_SITES;
+  const unsigned int G = gridDim.x, b = blockIdx.x;
+  const unsigned int nt = b < tiles ? (unsigned int)((tiles - b + G - 1) / G) : 0u;
+  double acc = 0.0;
+
+  if (producer)
+  {
+    if (lane == 0)
+      for (unsigned int i = 0; i < nt; ++i)
+      {
+        const unsigned int slot = i % STAGES, fill = i / STAGES;
+        if (fill) mbar_wait(&sm.empty[slot], (fill - 1u) & 1u); /* previous contents are in registers */
+        const unsigned long long site0 = ((unsigned long long)b + (unsigned long long)i * G) * LT_SITES;
+        const unsigned int ns = (unsigned int)((a.sites - site0) < LT_SITES ? (a.sites - site0) : LT_SITES);
+        const unsigned int b4 = ((ns + 3u) & ~3u) * 4u;  /* rows are padded to 256 bytes: rounding up stays inside */
+        const unsigned int b1 = (ns + 15u) & ~15u;
+        unsigned int bytes = ns * 128u + b4;
+        if (CTIP) bytes += b1; else bytes += ns * 128u;
+        if (a.pscaler) bytes += b4;
+        if (a.cscaler) bytes += b4;
+        mbar_expect_tx(&sm.full[slot], bytes);
+        tma_load_1d(sm.p[slot], a.pclv + site0 * 16, ns * 128u, &sm.full[slot]);
+        if (CTIP)
+          tma_load_1d(sm.code[slot], a.ctip + site0, b1, &sm.full[slot]);
+        else
+          tma_load_1d(sm.c[slot], a.cclv + site0 * 16, ns * 128u, &sm.full[slot]);
+        tma_load_1d(sm.wts[slot], a.weights + site0, b4, &sm.full[slot]);
+        if (a.pscaler) tma_load_1d(sm.psc[slot], a.pscaler + site0, b4, &sm.full[slot]);
+        if (a.cscaler) tma_load_1d(sm.csc[slot], a.cscaler + site0, b4, &sm.full[slot]);
+      }
+  }
+  else
+  {
+    const unsigned int k = tid & 3u, row0 = k & 1u;
+    const unsigned int swz = (tid >> 2) & 1u;
+    const double wk = a.w[k];
+    const double * m = sm.mat + k * 18;
+    const double * f = sm.freq + k * 4;
+    const bool finisher_lane = (k & 2u) == 0u;
+    for (unsigned int i = 0; i < nt; ++i)
+    {
+      const unsigned int slot = i % STAGES;
+      const unsigned long long site0 = ((unsigned long long)b + (unsigned long long)i * G) * LT_SITES;
+      const unsigned int ns = (unsigned int)((a.sites - site0) < LT_SITES ? (a.sites - site0) : LT_SITES);
+      mbar_wait(&sm.full[slot], (i / STAGES) & 1u);
+      d4 pv[2], cv[2];
+      unsigned int code[2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+      {
+        const unsigned int el = (((unsigned int)j ^ row0) << 8) + tid;
+        pv[j] = lt_lift(sm.p[slot] + (size_t)el * 4, swz);
+        if (CTIP)
+          code[j] = sm.code[slot][el >> 2];
+        else
+          cv[j] = lt_lift(sm.c[slot] + (size_t)el * 4, swz);
+      }
+      const unsigned int sl = (row0 << 6) + (tid >> 2); /* tile-local site this lane finishes */
+      const bool actf = finisher_lane && sl < ns;
+      unsigned int wgt = sm.wts[slot][sl], sc = 0;
+      if (a.pscaler) sc += sm.psc[slot][sl];
+      if (a.cscaler) sc += sm.csc[slot][sl];
+      __syncwarp();
+      if (lane == 0) lt_mbar_arrive(&sm.empty[slot]); /* this warp no longer needs the stage */
+      double term[2];
+#pragma unroll
+      for (int j = 0; j < 2; ++j)
+      {
+        const unsigned int el = (((unsigned int)j ^ row0) << 8) + tid;
+        double t0, t1, t2, t3;
+        if (CTIP)
+        {
+          const unsigned int cd = code[j];
+          t0 = ((cd & 1) ? m[0] : 0.0) + ((cd & 2) ? m[1] : 0.0) + ((cd & 4) ? m[2] : 0.0) + ((cd & 8) ? m[3] : 0.0);
+          t1 = ((cd & 1) ? m[4] : 0.0) + ((cd & 2) ? m[5] : 0.0) + ((cd & 4) ? m[6] : 0.0) + ((cd & 8) ? m[7] : 0.0);
+          t2 = ((cd & 1) ? m[8] : 0.0) + ((cd & 2) ? m[9] : 0.0) + ((cd & 4) ? m[10] : 0.0) + ((cd & 8) ? m[11] : 0.0);
+          t3 = ((cd & 1) ? m[12] : 0.0) + ((cd & 2) ? m[13] : 0.0) + ((cd & 4) ? m[14] : 0.0) + ((cd & 8) ? m[15] : 0.0);
+        }
+        else
+        {
+          const d4 c = cv[j];
+          t0 = m[0] * c.x + m[1] * c.y + m[2] * c.z + m[3] * c.w;
+          t1 = m[4] * c.x + m[5] * c.y + m[6] * c.z + m[7] * c.w;
+          t2 = m[8] * c.x + m[9] * c.y + m[10] * c.z + m[11] * c.w;
+          t3 = m[12] * c.x + m[13] * c.y + m[14] * c.z + m[15] * c.w;
+        }
+        const d4 p = pv[j];
+        term[j] = (p.x * f[0] * t0 + p.y * f[1] * t1 + p.z * f[2] * t2 + p.w * f[3] * t3) * wk;
+        if ((el >> 2) >= ns) term[j] = 0.0; /* last, partial tile: what lies behind it in the stage is stale */
+      }
+      term[0] += __shfl_xor_sync(0xffffffffu, term[1], 1);
+      term[0] += __shfl_xor_sync(0xffffffffu, term[0], 2);
+      if (actf)
+      {
+        double lk = site_finish(term[0], 0.0, sc, false);
+        lk *= (double)wgt;
+        if (a.persite) a.persite[site0 + sl] = lk;
+        acc += lk;
+      }
+    }
+  }
+  double v[1] = {acc};
+  grid_reduce_finish<1>(v, a.red);
+}
+
 /* ---- 20-state path (protein) ------------------------------------------------------------------
  * thread = (site, category) like the 4-state kernel; the child's 20 values (or the tip mask as 0/1) and
  * the parent's sit in registers (5 + 5 256-bit loads), the K P-matrices in shared memory with a row
@@ -696,6 +868,7 @@ template <bool ROOT>
 static bool dispatch_logl(PartCtx * c, const LoglArgs & a)
 {
   const unsigned int K = a.K;
+  eval_timing_begin(c->stream);
   bool no_pinv = true;
   for (unsigned int k = 0; k < K && k < LK_MAXK; ++k) no_pinv &= !(a.pinv[k] > 0.0);
   if (!ROOT && g_opt_fast_evals && a.states == 4 && K == 4 && !a.rate_scalers && no_pinv && (a.ctip || a.cclv))
@@ -705,7 +878,28 @@ static bool dispatch_logl(PartCtx * c, const LoglArgs & a)
     if (blocks > cap) blocks = cap;
     if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
     if (blocks < 1) blocks = 1;
-    if (a.ctip)
+    if (g_opt_fast_evals == 1 && a.sites >= 4096)
+    {
+      /* streamed through shared memory by TMA */
+      static bool optin = false;
+      if (!optin)
+      {
+        if (!pllb200_cuda_ok(cudaFuncSetAttribute(logl_dna4_tma_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  (int)sizeof(LoglTmaSmem<true>) + 128), "logl TMA kernel shared memory") ||
+            !pllb200_cuda_ok(cudaFuncSetAttribute(logl_dna4_tma_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                  (int)sizeof(LoglTmaSmem<false>) + 128), "logl TMA kernel shared memory"))
+          return false;
+        optin = true;
+      }
+      unsigned long long tb = ((unsigned long long)a.sites + LT_SITES - 1) / LT_SITES;
+      if (tb > cap) tb = cap;
+      if (tb > PLLB200_MAX_RED_BLOCKS) tb = PLLB200_MAX_RED_BLOCKS;
+      if (a.ctip)
+        logl_dna4_tma_kernel<true><<<(unsigned)tb, LT_THREADS, sizeof(LoglTmaSmem<true>) + 128, c->stream>>>(a);
+      else
+        logl_dna4_tma_kernel<false><<<(unsigned)tb, LT_THREADS, sizeof(LoglTmaSmem<false>) + 128, c->stream>>>(a);
+    }
+    else if (a.ctip)
       logl_dna4_fast_kernel<true><<<(unsigned)blocks, LKF_THREADS, 0, c->stream>>>(a);
     else
       logl_dna4_fast_kernel<false><<<(unsigned)blocks, LKF_THREADS, 0, c->stream>>>(a);
@@ -756,6 +950,7 @@ static bool dispatch_logl(PartCtx * c, const LoglArgs & a)
     if (blocks > PLLB200_MAX_RED_BLOCKS) blocks = PLLB200_MAX_RED_BLOCKS;
     logl_generic_kernel<<<(unsigned)blocks, LKG_THREADS, 0, c->stream>>>(a, ROOT ? 1 : 0);
   }
+  eval_timing_end(c->stream);
   ++g_kernel_launches;
   return pllb200_cuda_ok(cudaGetLastError(), "logl kernel launch");
 }

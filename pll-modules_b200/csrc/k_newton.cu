@@ -22,6 +22,7 @@
 #include "internal.h"
 #include "devutil.cuh"
 #include "aa4_pass.cuh"
+#include "reduce.cuh"
 
 #include <algorithm>
 #include <cooperative_groups.h>
@@ -59,6 +60,10 @@ struct NewtonArgs
    * branch in device memory; the start value comes from there when the branch was already visited */
   double * brlen_io;
   int x0_from_device, revert_on_limit;
+  /* newton_dna4_tma_kernel only: 1 / 2 = one pass at x0 (backwards / forwards over the table), result {d_f, dd_f}:
+   * pll_compute_likelihood_derivatives on the TMA ring (k_derivatives.cu) */
+  int eval_only;
+  unsigned int * ticket; /* eval_only: last-CTA reduction (reduce.cuh) instead of a grid barrier */
   /* multi-GPU (site-sharded ranks, one process per GPU): every pass ends with an all-gather of the local
    * (d_f, dd_f) over NVLink peer memory instead of a host callback.  inbox[r] is rank r's exchange
    * buffer (own: local pointer, others: CUDA IPC mappings): [2 parities][8 ranks]{f, df, seq, -} then the
@@ -157,12 +162,13 @@ __device__ __forceinline__ void newton_publish(const NewtonArgs & a, double x, d
 
 
 /* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates);
- * 4: 20 states, K = 4, unpadded (protein Gamma-4: a lane per (rate, state chunk), 640-byte warp loads) */
+ * 4: 20 states, K = 4, unpadded (protein Gamma-4: the pass is a [sites x 80] x [80 x 3] product on the FP64 tensor cores) */
 template <int MODE>
-__global__ void __launch_bounds__(NW_THREADS, (MODE == 4 || MODE == 2) ? 2 : 3) newton_kernel(NewtonArgs a)
+__global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(NewtonArgs a)
 {
   constexpr bool DNA = MODE == 1 || MODE == 2;
   __shared__ double s_aux[24]; /* MODE 4: w_k (1 - pinv_k) | invariant-site term per state */
+  __shared__ double s_bt[MODE == 4 ? AA4_BT : 1]; /* MODE 4: B fragments of the pass */
   cg::grid_group grid = cg::this_grid();
   __shared__ double s_diag[NW_MAX_DIAG * 3];
   __shared__ double s_red[2][NW_THREADS / 32];
@@ -233,8 +239,7 @@ __global__ void __launch_bounds__(NW_THREADS, (MODE == 4 || MODE == 2) ? 2 : 3) 
     const bool fwd = (iter & 1u) == 0;
     if (MODE == 4)
     {
-      /* 20 states x 4 rates: lane = (rate, state chunk), factors in registers (aa4_pass.cuh) */
-      double fc[4][3];
+      /* 20 states x 4 rates: the pass runs on the FP64 tensor cores (aa4_pass.cuh) */
       if (threadIdx.x < 4) s_aux[threadIdx.x] = a.w[threadIdx.x] * (1.0 - a.pinv[threadIdx.x]);
       if (threadIdx.x < 20)
       {
@@ -245,8 +250,9 @@ __global__ void __launch_bounds__(NW_THREADS, (MODE == 4 || MODE == 2) ? 2 : 3) 
         s_aux[4 + threadIdx.x] = t;
       }
       __syncthreads();
-      aa4_load_factors(s_diag, s_aux, lane, fc);
-      aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, fc,
+      aa4_build_b(s_diag, s_aux, s_bt);
+      __syncthreads();
+      aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, s_bt,
                (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp,
                (unsigned long long)gridDim.x * (NW_THREADS / 32), fwd, lane, acc1, acc2);
     }
@@ -538,6 +544,7 @@ __device__ __forceinline__ void mbar_arrive(unsigned long long * bar)
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
+template <bool EVAL> /* EVAL: one pass, no grid barrier: an ordinary (non-cooperative) launch */
 __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonArgs a)
 {
   cg::grid_group grid = cg::this_grid();
@@ -590,7 +597,7 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
       status = NW_LIMIT;
       break;
     }
-    const bool fwd = (iter & 1u) == 0;
+    const bool fwd = a.eval_only ? a.eval_only == 2 : (iter & 1u) == 0;
     double acc1 = 0.0, acc2 = 0.0;
 
     if (producer)
@@ -613,7 +620,8 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
         /* the table does not change between passes: start the next pass (opposite direction) now, so
          * that its first tiles land while the grid reduces; if there is no next pass they are drained
          * before the kernel ends */
-        for (unsigned int i = 0; i < NT_STAGES && i < nt; ++i) issue(used + nt + i, i, !fwd);
+        if (!a.eval_only)
+          for (unsigned int i = 0; i < NT_STAGES && i < nt; ++i) issue(used + nt + i, i, !fwd);
       }
     }
     else if (tid < 16)
@@ -709,20 +717,37 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
         }
       }
       /* warp partial */
+      if (!EVAL)
+      {
 #pragma unroll
-      for (int off = 16; off > 0; off >>= 1)
-      {
-        acc1 += __shfl_down_sync(0xffffffffu, acc1, off);
-        acc2 += __shfl_down_sync(0xffffffffu, acc2, off);
-      }
-      if (lane == 0)
-      {
-        sm.red[0][warp] = acc1;
-        sm.red[1][warp] = acc2;
+        for (int off = 16; off > 0; off >>= 1)
+        {
+          acc1 += __shfl_down_sync(0xffffffffu, acc1, off);
+          acc2 += __shfl_down_sync(0xffffffffu, acc2, off);
+        }
+        if (lane == 0)
+        {
+          sm.red[0][warp] = acc1;
+          sm.red[1][warp] = acc2;
+        }
       }
     }
+    if (EVAL)
+    {
+      /* d_f = sum, dd_f = sum (scale 1): block -> grid by ticket, the last CTA publishes result and tag */
+      double v[2] = {acc1, acc2};
+      ReduceOut r;
+      r.partials = a.partials;
+      r.ticket = a.ticket;
+      r.result_dev = a.result_dev;
+      r.result_host = a.result_host;
+      r.tag_host = a.tag_host;
+      r.tag = a.tag;
+      grid_reduce_finish<2>(v, r);
+      return;
+    }
     used += nt;
-    prefetched = nt < NT_STAGES ? nt : NT_STAGES;
+    prefetched = a.eval_only ? 0u : (nt < NT_STAGES ? nt : NT_STAGES);
     __syncthreads();
 
     /* CTA partial -> grid total (deterministic: fixed order in every CTA) */
@@ -1171,7 +1196,7 @@ static bool fill_newton_model(PartCtx * c, const unsigned int * params_indices, 
 
 bool launch_newton(PartCtx * c, const unsigned int * params_indices, const double * d_sumtable,
                    double xmin, double x0, double xmax, double tol, unsigned int max_iters,
-                   double scale, int slot, double * brlen_io, int x0_from_device, int revert_on_limit)
+                   double scale, int slot, double * brlen_io, int x0_from_device, int revert_on_limit, int eval_only)
 {
   pll_partition_t * p = &c->pub;
   const unsigned int K = p->rate_cats, s = p->states;
@@ -1192,36 +1217,43 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   a.brlen_io = brlen_io;
   a.x0_from_device = x0_from_device;
   a.revert_on_limit = revert_on_limit;
+  a.eval_only = eval_only;
+  a.ticket = c->d_ticket;
+  if (eval_only) a.nranks = 1; /* the caller's reduction callback adds the ranks' derivatives */
 
   /* cooperative grid: never more CTAs than can be co-resident, never more than there is work */
-  static int per_sm[5] = {0, 0, 0, 0, 0};
+  static int per_sm[8] = {0, 0, 0, 0, 0, 0, 0, 0};
   int mode = s == 4 ? (K == 4 ? 2 : 1) : 0;
   if (mode == 2 && g_opt_fused_newton == 1) mode = 3; /* fused_newton=2 keeps the register version */
   if (s == 20 && p->states_padded == 20 && K == 4 && g_opt_fused_newton != 3) mode = 4; /* fused_newton=3: generic kernel */
+  if (eval_only && mode != 3)
+    return pllb200_cuda_ok(cudaErrorInvalidValue, "derivative pass on the TMA ring: wrong shape");
   const void * fn = mode == 4   ? (const void *)newton_kernel<4>
-                    : mode == 3 ? (const void *)newton_dna4_tma_kernel
+                    : mode == 3 ? (eval_only ? (const void *)newton_dna4_tma_kernel<true> : (const void *)newton_dna4_tma_kernel<false>)
                     : mode == 2 ? (const void *)newton_kernel<2>
                     : mode == 1 ? (const void *)newton_kernel<1>
                                 : (const void *)newton_kernel<0>;
   const size_t dyn = mode == 3 ? sizeof(NewtonTmaSmem) + 128 : 0;
-  if (!per_sm[mode])
+  const unsigned int threads = mode == 3 ? NT_THREADS : NW_THREADS;
+  const int pi = eval_only ? 6 : mode;
+  if (!per_sm[pi])
   {
     if (dyn && cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn) != cudaSuccess)
       return pllb200_cuda_ok(cudaGetLastError(), "newton kernel shared memory");
     int nb = 0;
-    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, mode == 3 ? NT_THREADS : NW_THREADS, dyn);
-    per_sm[mode] = (e == cudaSuccess && nb > 0) ? nb : 1;
+    const cudaError_t e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, (int)threads, dyn);
+    per_sm[pi] = (e == cudaSuccess && nb > 0) ? nb : 1;
   }
   const unsigned long long E = (unsigned long long)a.sites * K;
   unsigned long long blocks = mode == 3 ? (E + NT_TILE - 1) / NT_TILE : (E + NW_THREADS - 1) / NW_THREADS;
   if (mode == 4) blocks = (((unsigned long long)a.sites + 7) / 8 + NW_THREADS / 32 - 1) / (NW_THREADS / 32); /* a warp per 8-site tile */
-  unsigned long long cap = (unsigned long long)c->sm_count * std::min(per_sm[mode], 4);
+  unsigned long long cap = (unsigned long long)c->sm_count * std::min(per_sm[pi], 4);
   if (cap > PLLB200_MAX_RED_BLOCKS * 3 / 4) cap = PLLB200_MAX_RED_BLOCKS * 3 / 4; /* partials: 2 buffers x 2 values */
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   void * kargs[] = {&a};
-  const cudaError_t e = cudaLaunchCooperativeKernel(fn, dim3((unsigned)blocks), dim3(mode == 3 ? NT_THREADS : NW_THREADS), kargs, dyn,
-                                                      c->stream);
+  const cudaError_t e = eval_only ? cudaLaunchKernel(fn, dim3((unsigned)blocks), dim3(threads), kargs, dyn, c->stream)
+                                  : cudaLaunchCooperativeKernel(fn, dim3((unsigned)blocks), dim3(threads), kargs, dyn, c->stream);
   ++g_kernel_launches;
   return pllb200_cuda_ok(e, "newton kernel launch");
 }

@@ -87,6 +87,10 @@ def _lib(kind):
         lib.h_time_update_partials.restype = C.c_double
         lib.h_time_update_partials.argtypes = [C.c_void_p, C.c_int]
         lib.h_queue_update_partials.argtypes = [C.c_void_p]
+        lib.h_time_edge_loglh.restype = C.c_double
+        lib.h_time_edge_loglh.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_int]
+        lib.h_time_derivatives.restype = C.c_double
+        lib.h_time_derivatives.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_int]
         lib.h_update_partials_only.argtypes = [C.c_void_p, C.c_int]
         lib.h_edge_loglh.restype = C.c_double
         lib.h_edge_loglh.argtypes = [C.c_void_p, C.c_uint, C.c_uint]
@@ -409,6 +413,12 @@ class Harness:
 
     def time_update_partials(self, reps=1):
         return self.lib.h_time_update_partials(self.h, reps)
+
+    def time_edge_loglh(self, node_index, reps=10, p=0):
+        return self.lib.h_time_edge_loglh(self.h, p, node_index, reps)
+
+    def time_derivatives(self, node_index, reps=10, p=0):
+        return self.lib.h_time_derivatives(self.h, p, node_index, reps)
 
     def queue_update_partials(self):
         self.lib.h_queue_update_partials(self.h)

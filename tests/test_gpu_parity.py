@@ -296,8 +296,9 @@ def test_single_partition_legacy_blo_and_radius():
     dict(tips=60, sites=20000, states=20),                # several tiles per warp, both walking directions
 ], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
 def test_protein_newton_kernel_matches_generic_kernel_and_reference(kw):
-    """newton_kernel<4> (20 states, Gamma-4: warp-contiguous loads, factors in registers) against the generic
-    one-element-per-thread kernel (fused_newton 3) and the reference: -logL after smoothing and every branch length."""
+    """20 states, Gamma-4: newton_kernel<4> / deriv_aa4_kernel (the pass as a [sites x 80] x [80 x 3] product on the
+    FP64 tensor cores, aa4_pass.cuh) against the generic one-element-per-thread kernels (fused_newton 3) and the
+    reference: -logL after smoothing, every branch length, and the stand-alone derivative pass."""
     pkg = load_product_package()
     out = {}
     try:
@@ -305,12 +306,17 @@ def test_protein_newton_kernel_matches_generic_kernel_and_reference(kw):
             pkg.set_option("fused_newton", mode)
             with Harness("b200", **kw) as d:
                 d.loglh()
+                dd = d.derivatives(d.root(), [0.004, 0.07, 0.9])
                 nll = d.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.01)
-                out[mode] = (nll, d.branch_lengths().copy())
+                out[mode] = (nll, d.branch_lengths().copy(), dd)
     finally:
         pkg.set_option("fused_newton", 1)
-    assert rel(out[1][0], out[3][0]) < 1e-12, (out[1][0], out[3][0])
-    np.testing.assert_allclose(out[1][1], out[3][1], rtol=1e-7, atol=1e-10)   # summation order differs; NR stops at 1e-5
+    for mode in (1,):
+        assert rel(out[mode][0], out[3][0]) < 1e-12, (mode, out[mode][0], out[3][0])
+        # summation order differs; NR stops at 1e-5
+        np.testing.assert_allclose(out[mode][1], out[3][1], rtol=1e-7, atol=1e-10)
+        np.testing.assert_allclose(out[mode][2][0], out[3][2][0], rtol=1e-10, atol=1e-9)
+        np.testing.assert_allclose(out[mode][2][1], out[3][2][1], rtol=1e-10, atol=1e-9)
     with Harness("ref", **kw) as r:
         r.loglh()
         a = r.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.01)
