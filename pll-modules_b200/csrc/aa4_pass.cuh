@@ -6,14 +6,18 @@
  * (L, L', L'')[site] = sum_{e < 80} sum[site][e] * F[e][c],  F[e] = w_k (1 - pinv_k) (1, l, l^2) exp(l t)
  * is a [sites x 80] x [80 x 3] product: it runs on the FP64 tensor cores as mma.sync.m8n8k4 tiles with M = 8 sites,
  * N = 8 columns (3 used), K = 4 table entries per step, 20 steps per tile.
- *   A fragment (lane = 4 row + col): sum[site0 + row][4 ks + col] — one 8-byte load per lane and step, a quad of
- *     lanes reads one 32-byte sector, all 20 loads of a tile are issued before the first mma;
- *   B fragment: F[4 ks + col][n = lane / 4] (zero for n >= 3) from a 5 KB shared table [ks][lane] rebuilt once per
- *     pass (conflict-free 8-byte reads);
+ *   A fragment (lane = 4 row + col): the K dimension may be permuted freely as long as B follows, so lane (row, col)
+ *     loads five 256-bit pieces sum[site0 + row][16 g + 4 col .. + 3], g = 0..4 — a quad of lanes reads one whole
+ *     128-byte line of its site, a warp load touches 8 full lines — and k-step (g, j) takes component j of piece g:
+ *     table entry e = 16 g + 4 col + j.  (With one 8-byte load per k-step, 20 per lane, the pass was bound by L1
+ *     tag lookups: 240 us per Newton launch under ncu against 203 for the FMA version; profiles/README.md.)
+ *   B fragment: F[16 g + 4 col + j][n = lane / 4] (zero for n >= 3) from a 5 KB shared table [ks = 4 g + j][lane]
+ *     rebuilt once per pass (conflict-free 8-byte reads);
  *   D fragment: lane 4 row holds (L, L'), lane 4 row + 1 holds (L'', 0): one shuffle, then every fourth lane
  *     finishes its site (one reciprocal, pattern weight, invariant-site term).
- * 20 loads + 20 shared reads + 20 mma per 8 sites instead of 96 FMA + 27 shuffles + selects (~700 instructions,
- * issue-bound at 60 us per 128 MB pass: profiles/r02c_newton_aa_ncu_summary.txt).
+ * 5 loads + 20 shared reads + 20 mma per 8 sites instead of 96 FMA + 27 shuffles + selects (~700 instructions:
+ * profiles/r02c_newton_aa_ncu_summary.csv).  In a smoothing pass all three variants take the same ~28 us per pass:
+ * the 128 MB table is just larger than the 126 MB L2 and the pass runs at what DRAM + L2 deliver (4.6 TB/s).
  *
  * [History.  Round 2 b: a lane per (rate, state chunk), 8 sites per trip in registers / through a TMA ring:
  *  350 instructions per 4 sites, issue-bound.  Round 2 a: 160-item tiles with 60 factors per lane: 218 registers,
@@ -38,7 +42,7 @@ __device__ __forceinline__ void aa4_build_b(const double * diag, const double * 
 {
   for (unsigned int i = threadIdx.x; i < AA4_BT; i += blockDim.x)
   {
-    const unsigned int ks = i >> 5, l = i & 31u, n = l >> 2, e = 4u * ks + (l & 3u);
+    const unsigned int ks = i >> 5, l = i & 31u, n = l >> 2, e = 16u * (ks >> 2) + 4u * (l & 3u) + (ks & 3u);
     bt[i] = n < 3u ? wf[e / 20u] * diag[e * 3u + n] : 0.0;
   }
 }
@@ -59,10 +63,14 @@ __device__ __forceinline__ void aa4_pass(const double * __restrict__ sum, const 
     const unsigned long long tile = gw + (fwd ? ti : mytiles - 1 - ti) * nw;
     const unsigned long long site = tile * AA4_SITES + ((unsigned int)lane >> 2);
     const bool act = site < sites;
-    const double * src = sum + site * 80 + ((unsigned int)lane & 3u);
-    double av[20];
+    const double * src = sum + site * 80 + 4u * ((unsigned int)lane & 3u);
+    d4 xv[5];
 #pragma unroll
-    for (int ks = 0; ks < 20; ++ks) av[ks] = act ? __ldg(src + 4 * ks) : 0.0;
+    for (int g = 0; g < 5; ++g)
+    {
+      xv[g] = d4{0.0, 0.0, 0.0, 0.0};
+      if (act) xv[g] = ldg256(src + 16 * g);
+    }
     const bool finisher = ((unsigned int)lane & 3u) == 0u && act;
     unsigned int wgt = 0;
     int inv = -1;
@@ -73,7 +81,13 @@ __device__ __forceinline__ void aa4_pass(const double * __restrict__ sum, const 
     }
     double d0 = 0.0, d1 = 0.0;
 #pragma unroll
-    for (int ks = 0; ks < 20; ++ks) aa4_dmma(d0, d1, av[ks], btl[ks * 32]);
+    for (int g = 0; g < 5; ++g)
+    {
+      aa4_dmma(d0, d1, xv[g].x, btl[(4 * g + 0) * 32]);
+      aa4_dmma(d0, d1, xv[g].y, btl[(4 * g + 1) * 32]);
+      aa4_dmma(d0, d1, xv[g].z, btl[(4 * g + 2) * 32]);
+      aa4_dmma(d0, d1, xv[g].w, btl[(4 * g + 3) * 32]);
+    }
     const double L2 = __shfl_down_sync(0xffffffffu, d0, 1);
     if (finisher)
     {

@@ -411,6 +411,7 @@ bool dev_sync_inputs(PartCtx * c)
     CUDA_TRY(cudaMemcpyAsync(c->d_tipmap, st, 256 * sizeof(unsigned long long),
                              cudaMemcpyDeviceToDevice, xstream(c)), false);
     c->tipmap_dirty = false;
+    ++c->tipmap_gen;
     if (c->d_tiptab) c->tiptab_stale = true; /* tables of already computed matrices lack the new codes */
   }
   if (c->weights_dirty)

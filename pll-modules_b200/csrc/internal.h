@@ -81,6 +81,7 @@ struct PartCtx
   unsigned long long xred_seq;
   double * d_sumfrag;         /* lazily allocated: 20-state sumtable matrices as DMMA fragment images */
   std::vector<unsigned long long> sumfrag_key;
+  unsigned long long tipmap_gen = 0; /* bumped whenever the tip map is uploaded again */
   /* batched regraft scoring (k_traversal_dna4.cu): per-warp partial sums + results, pinned landing buffer */
   double * d_score;
   size_t score_cap;

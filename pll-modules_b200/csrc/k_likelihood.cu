@@ -214,7 +214,7 @@ __global__ void __launch_bounds__(LK_THREADS, 3) logl_dna_kernel(LoglArgs a)
 
 /* ---- 4 states, 4 categories, per-site scalers, no invariant sites: the hot shape (BASELINE C2/C4/C5) --------
  * The kernel above spends 290 warp instructions per 32 elements, most of them on its generality and on a
- * log() that runs with a quarter of the lanes (profiles/r02_evals_ncu_summary.txt: 93 us per 1 M sites, DRAM at
+ * log() that runs with a quarter of the lanes (profiles/r02_evals_ncu_summary.csv: 93 us per 1 M sites, DRAM at
  * 18 %).  Here a warp takes a tile of 32 sites = 128 elements as 4 rows of 32: a thread's 4 elements belong to 4
  * different sites and one rate.  All 8 256-bit loads of a trip are in flight before the first use; register slot j
  * holds row j ^ perm (perm = bit-reversed rate index), so that two exchange rounds with fixed send/keep slots leave
@@ -343,6 +343,7 @@ struct LoglTmaSmem
   unsigned long long empty[STAGES];
   double mat[4 * 18];
   double freq[16];
+  double tab[CTIP ? 16 * 16 : 1]; /* tip child: [code][rate][row] = sum of the matrix columns in the code's mask */
 };
 
 __device__ __forceinline__ void lt_mbar_arrive(unsigned long long * bar)
@@ -380,6 +381,13 @@ __global__ void __launch_bounds__(LT_THREADS, 2) logl_dna4_tma_kernel(LoglArgs a
   for (unsigned int i = tid; i < 64; i += blockDim.x) sm.mat[(i >> 4) * 18 + (i & 15)] = a.pmat[i];
   for (unsigned int i = tid; i < 16; i += blockDim.x)
     sm.freq[i] = a.eigen[(unsigned long long)a.freq_idx[i / 4] * a.eigen_stride + 2 * 4 * 4 + 4 + (i & 3)];
+  if (CTIP && tid < 256)
+  {
+    /* added in state order like the masked sums of the general kernel (absent states add 0.0: same bits) */
+    const unsigned int cd = tid >> 4;
+    const double * mr = a.pmat + ((tid >> 2) & 3u) * 16 + (tid & 3u) * 4;
+    sm.tab[tid] = ((cd & 1) ? mr[0] : 0.0) + ((cd & 2) ? mr[1] : 0.0) + ((cd & 4) ? mr[2] : 0.0) + ((cd & 8) ? mr[3] : 0.0);
+  }
   __syncthreads();
 
   const unsigned long long tiles = ((unsigned long long)a.sites + LT_SITES - 1) / LT_SITES;
@@ -454,11 +462,12 @@ __global__ void __launch_bounds__(LT_THREADS, 2) logl_dna4_tma_kernel(LoglArgs a
         double t0, t1, t2, t3;
         if (CTIP)
         {
-          const unsigned int cd = code[j];
-          t0 = ((cd & 1) ? m[0] : 0.0) + ((cd & 2) ? m[1] : 0.0) + ((cd & 4) ? m[2] : 0.0) + ((cd & 8) ? m[3] : 0.0);
-          t1 = ((cd & 1) ? m[4] : 0.0) + ((cd & 2) ? m[5] : 0.0) + ((cd & 4) ? m[6] : 0.0) + ((cd & 8) ? m[7] : 0.0);
-          t2 = ((cd & 1) ? m[8] : 0.0) + ((cd & 2) ? m[9] : 0.0) + ((cd & 4) ? m[10] : 0.0) + ((cd & 8) ? m[11] : 0.0);
-          t3 = ((cd & 1) ? m[12] : 0.0) + ((cd & 2) ? m[13] : 0.0) + ((cd & 4) ? m[14] : 0.0) + ((cd & 8) ? m[15] : 0.0);
+          const double * tr = sm.tab + ((code[j] & 15u) << 4) + (k << 2);
+          const double2 ta = *reinterpret_cast<const double2 *>(tr), tb = *reinterpret_cast<const double2 *>(tr + 2);
+          t0 = ta.x;
+          t1 = ta.y;
+          t2 = tb.x;
+          t3 = tb.y;
         }
         else
         {

@@ -1182,11 +1182,24 @@ bool flush_trav_aa4(PartCtx * lead, const void * d_args, const BatchKind & k)
  * R[j][i] = V[j][i]  (rebuilt only when the eigen data of a category changes), the parent buffer is the
  * sumtable, and there is no scaling.  The generic kernel took 1.56 ms for 200 k sites (1.2 TB/s). */
 __global__ void sumfrag_kernel(double * __restrict__ frag, const double * __restrict__ eigen,
-                               unsigned long long eigen_stride, unsigned int K, PmatIdx idx)
+                               unsigned long long eigen_stride, unsigned int K, PmatIdx idx,
+                               const unsigned long long * __restrict__ tipmap)
 {
   const unsigned int k = blockIdx.x;
   const double * blk = eigen + (unsigned long long)idx.v[k] * eigen_stride;
   const double * ev = blk, * iev = blk + 400, * fr = blk + 800 + 20;
+  /* third block: what a tip code contributes through L, [code 24][k][20] like the P-matrix tip tables of
+   * k_pmatrix.cu (states added in order, like the masked sums of core_derivatives.c:300-340) */
+  if (tipmap)
+    for (unsigned int t = threadIdx.x; t < 480; t += blockDim.x)
+    {
+      const unsigned int code = t / 20, o = t % 20;
+      const unsigned long long mask = tipmap[code];
+      double v = 0.0;
+      for (unsigned int n = 0; n < 20; ++n)
+        if ((mask >> n) & 1ull) v += fr[n] * iev[n * 20 + o];
+      frag[(size_t)2 * K * AA_FRAG + ((size_t)code * K + k) * 20 + o] = v;
+    }
   for (unsigned int t = threadIdx.x; t < 400; t += blockDim.x)
   {
     const unsigned int o = t / 20, n = t % 20; /* output state j, summed state i */
@@ -1202,7 +1215,7 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
 {
   pll_partition_t * p = &c->pub;
   const unsigned int K = p->rate_cats;
-  const size_t frag_doubles = (size_t)2 * K * AA_FRAG;
+  const size_t frag_doubles = (size_t)3 * K * AA_FRAG; /* L, R, tip table of L */
   if (!c->d_sumfrag)
   {
     if (!pllb200_cuda_ok(cudaMalloc(&c->d_sumfrag, frag_doubles * sizeof(double)), "sumtable fragments")) return false;
@@ -1210,14 +1223,20 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
       return false;
     c->sumfrag_key.clear();
   }
-  std::vector<unsigned long long> key(K);
+  /* Gamma-4 edges run on the forwarding kernel (one operation: 82 us against 108 us at C3); its tip children are
+   * table lookups, so the table of L rides along */
+  const bool tip_lookup = c->d_tipmap && p->tipmap && p->maxstates <= 24;
+  const bool aa4 = K == 4 && g_opt_aa_variant == 0 && !batch_collects(BK_TRAV_AA) && (!first_is_tip || tip_lookup);
+  std::vector<unsigned long long> key(K + 1);
   for (unsigned int k = 0; k < K; ++k)
     key[k] = ((unsigned long long)params_indices[k] << 32) | c->eigen_version[params_indices[k]];
+  key[K] = tip_lookup ? c->tipmap_gen + 1 : 0;
   if (key != c->sumfrag_key)
   {
     PmatIdx idx;
     for (unsigned int k = 0; k < K; ++k) idx.v[k] = params_indices[k];
-    sumfrag_kernel<<<K, 128, 0, xstream(c)>>>(c->d_sumfrag, c->d_eigen, c->eigen_stride, K, idx);
+    sumfrag_kernel<<<K, 128, 0, xstream(c)>>>(c->d_sumfrag, c->d_eigen, c->eigen_stride, K, idx,
+                                              tip_lookup ? c->d_tipmap : nullptr);
     ++g_kernel_launches;
     if (!pllb200_cuda_ok(cudaGetLastError(), "sumfrag_kernel launch")) return false;
     c->sumfrag_key = key;
@@ -1250,5 +1269,10 @@ bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsi
   a.tipchars = c->d_tipchars;
   a.tipmap = c->d_tipmap;
   a.l1_prefetch = 0;
+  if (aa4)
+  {
+    a.tiptab = c->d_sumfrag + (size_t)2 * K * AA_FRAG;
+    return launch_aa4_variant<AA4_T, AA4_W, AA4_MINB, AA4_TS>(c, a);
+  }
   return launch_aa_variant<2, 4, 3>(c, a);
 }
