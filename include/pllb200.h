@@ -1037,7 +1037,11 @@ typedef struct
 } pllb200_stats_t;
 void pllb200_get_stats(pllb200_stats_t * out);
 void pllb200_reset_stats(void);
-/* name in {"trav_ctas_per_sm","trav_reorder","fuse_root","trav_variant","trav_forward","fused_newton","queued_newton"}; returns previous value, -1 if unknown */
+/* Experiment knobs (never needed by a caller; DESIGN.md section 7 lists them): "trav_variant", "trav_stash", "trav_short",
+ * "trav_forward", "trav_reorder", "trav_ctas_per_sm", "fuse_root", "fused_newton" (0 per-iteration path, 1 TMA ring /
+ * tensor-core pass, 2 register version, 3 generic kernel), "queued_newton", "spr_batch", "scratch_rows",
+ * "generic_dmma" (17..64 states on the FP64 tensor cores), "fast_evals" (0 general logL / derivative kernels,
+ * 1 TMA ring, 2 register tile kernels), "eval_timing".  Returns the previous value, -1 if the name is unknown. */
 int pllb200_set_option(const char * name, int value);
 /* Measurement aid (no reference counterpart): with option "eval_timing" = 1 the logL / derivative launchers bracket
  * their kernel with CUDA events on its stream; this returns the device time of the most recent one in microseconds
