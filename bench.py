@@ -511,7 +511,7 @@ def main():
             sys.path.insert(0, os.path.join(ROOT, "scripts"))
             import secondary
             sec = {}
-            for name, fn in (("C3", secondary.c3), ("C4", secondary.c4), ("C5", secondary.c5)):
+            for name, fn in (("C3", secondary.c3), ("C4", secondary.c4), ("C5", secondary.c5), ("N1", secondary.n1)):
                 t0 = time.perf_counter()
                 try:
                     sec[name] = fn()

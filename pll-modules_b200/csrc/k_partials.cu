@@ -140,10 +140,10 @@ __global__ void __launch_bounds__(GEN_THREADS) partial_generic_kernel(GenOpArgs 
 /* X[site][i] = sum_j C[site][j] P[i][j] per rate category is a dense [sites x s] x [s x s] product
  * (core_partials.c:612-764 computes it with s^2 scalar FMAs per site and category): DMMA tiles
  * mma.sync.m8n8k4.f64 with M = 8 sites, N = 8 parent states (ceil(s/8) tiles), K = 4 child states (sp/4 steps).
- * A fragment (lane = 4 row + col): the child CLV element [site0 + row][4 ks + col], one 8-byte load per k-step
- * (a quad of lanes reads 32 contiguous bytes); B fragment: P[8 nt + row][4 ks + col] from shared memory (row pitch
- * 68 doubles: the 16 lanes of a half warp hit 16 different bank pairs); D fragment: parent states 8 nt + 2 col, +1
- * of site row.  A CTA stages both matrices of ONE category (70 KB) and runs its 64 tiles of 8 sites through
+ * A fragment (lane = 4 row + col): 256-bit pieces child[site0 + row][16 g + 4 col .. + 3], all requested before the
+ * first mma; k-step 4 g + j takes component j (the K dimension is permuted, the staged matrix columns follow:
+ * pd_col); B fragment from shared memory (row pitch 68 doubles: the 16 lanes of a half warp hit 16 different bank
+ * pairs); D fragment: parent states 8 nt + 2 col, +1 of site row.  A CTA stages both matrices of ONE category (70 KB) and runs its 64 tiles of 8 sites through
  * them, category after category; a warp always owns the same tiles, so the per-site maximum over the categories
  * accumulates in shared memory without atomics, and the rare rescaling (all K s entries of a site < 2^-256:
  * core_partials.c:729-763) is a second pass of the warp over what it stored.  Tip children (tip patterns) are
@@ -151,25 +151,30 @@ __global__ void __launch_bounds__(GEN_THREADS) partial_generic_kernel(GenOpArgs 
 #define PD_WARPS 8
 #define PD_PITCH 68
 #define PD_TILES 64 /* tiles of 8 sites per CTA */
-#define PD_SMEM (2 * 64 * PD_PITCH * sizeof(double) + PD_TILES * 8 * sizeof(int))
+#define PD_SMEM (2 * 64 * PD_PITCH * sizeof(double) + PD_TILES * 8 * sizeof(int) + 2 * 64 * sizeof(double))
 
 __device__ __forceinline__ void pd_dmma(double & c0, double & c1, double a, double b)
 {
   asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-__global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a)
+/* position of matrix column j in the staged image */
+__device__ __forceinline__ unsigned int pd_col(unsigned int j) { return (j & ~15u) | ((j & 3u) << 2) | ((j >> 2) & 3u); }
+
+__global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a, unsigned int tiles_per_cta)
 {
   extern __shared__ __align__(16) double pd_sm[];
   double * sM[2] = {pd_sm, pd_sm + 64 * PD_PITCH};
   int * s_max = reinterpret_cast<int *>(pd_sm + 2 * 64 * PD_PITCH);
+  double * s_rs = reinterpret_cast<double *>(s_max + PD_TILES * 8); /* [2][64] row sums: a fully ambiguous tip */
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int row = lane >> 2, col = lane & 3;
   const unsigned int s = a.states, sp = a.sp, K = a.K;
-  const unsigned int NT = (s + 7) / 8, KS = sp / 4;
-  const unsigned long long tile0 = (unsigned long long)blockIdx.x * PD_TILES;
+  const unsigned int NT = (s + 7) / 8;
+  const unsigned long long tile0 = (unsigned long long)blockIdx.x * tiles_per_cta;
   const bool tip[2] = {a.ltip != nullptr, a.rtip != nullptr};
   const bool tiptip = tip[0] && tip[1];
+  const unsigned long long full_mask = s >= 64 ? ~0ull : (1ull << s) - 1ull;
   for (int i = threadIdx.x; i < PD_TILES * 8; i += blockDim.x) s_max[i] = -2147483647 - 1;
 
   for (unsigned int k = 0; k < K; ++k)
@@ -179,10 +184,21 @@ __global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a
     {
       const unsigned int q = idx >> 12, i = (idx >> 6) & 63u, j = idx & 63u;
       const double * m = q ? a.rmat : a.lmat;
-      sM[q][i * PD_PITCH + j] = (i < s && j < s) ? __ldg(m + ((size_t)k * s + i) * sp + j) : 0.0;
+      /* columns are stored with the 4 x 4 blocks of every 16 transposed (see the A fragment below) */
+      sM[q][i * PD_PITCH + pd_col(j)] = (i < s && j < s) ? __ldg(m + ((size_t)k * s + i) * sp + j) : 0.0;
     }
     __syncthreads();
-    for (unsigned int t = warp; t < PD_TILES; t += PD_WARPS)
+    if ((tip[0] || tip[1]) && threadIdx.x < 128)
+    {
+      /* gaps / unknown characters carry every state: their masked sum is the row sum, added in state order like
+       * the loop below — one lookup instead of s iterations for the whole warp */
+      const double * Mr = sM[threadIdx.x >> 6] + (threadIdx.x & 63) * PD_PITCH;
+      double v = 0.0;
+      for (unsigned int j = 0; j < s; ++j) v += Mr[pd_col(j)];
+      s_rs[threadIdx.x] = v;
+    }
+    if (tip[0] || tip[1]) __syncthreads();
+    for (unsigned int t = warp; t < tiles_per_cta; t += PD_WARPS)
     {
       const unsigned long long site = (tile0 + t) * 8 + row;
       if ((tile0 + t) * 8 >= a.sites) break; /* warp-uniform */
@@ -198,6 +214,17 @@ __global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a
         {
           unsigned long long mask = 0;
           if (act) mask = a.tipmap[(q ? a.rtip : a.ltip)[site]];
+          if (mask == full_mask)
+          {
+#pragma unroll
+            for (int nt = 0; nt < 8; ++nt)
+              if ((unsigned int)nt < NT)
+              {
+                D[q][nt][0] = s_rs[q * 64 + nt * 8 + 2 * col];
+                D[q][nt][1] = s_rs[q * 64 + nt * 8 + 2 * col + 1];
+              }
+            mask = 0;
+          }
           while (mask)
           {
             const unsigned int j = (unsigned int)__ffsll((long long)mask) - 1u;
@@ -206,20 +233,38 @@ __global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a
             for (int nt = 0; nt < 8; ++nt)
               if ((unsigned int)nt < NT)
               {
-                D[q][nt][0] += M[(nt * 8 + 2 * col) * PD_PITCH + j];
-                D[q][nt][1] += M[(nt * 8 + 2 * col + 1) * PD_PITCH + j];
+                D[q][nt][0] += M[(nt * 8 + 2 * col) * PD_PITCH + pd_col(j)];
+                D[q][nt][1] += M[(nt * 8 + 2 * col + 1) * PD_PITCH + pd_col(j)];
               }
           }
         }
         else
         {
-          const double * cv = (q ? a.right : a.left) + ((size_t)site * K + k) * sp + col;
-          for (unsigned int ks = 0; ks < KS; ++ks)
-          {
-            const double av = (act && 4 * ks + col < s) ? cv[4 * ks] : 0.0; /* padding is never read (may hold anything) */
+          /* the K dimension of an MMA may be permuted as long as B follows: lane (row, col) loads 256-bit pieces
+           * child[16 g + 4 col .. + 3] (a quad of lanes = one 128-byte line of its site), k-step 4 g + j takes
+           * component j: child state e = 16 g + 4 col + j, whose matrix column sits at 16 g + 4 j + col */
+          const double * cv = (q ? a.right : a.left) + ((size_t)site * K + k) * sp + 4 * col;
+          d4 piece[4];
 #pragma unroll
-            for (int nt = 0; nt < 8; ++nt)
-              if ((unsigned int)nt < NT) pd_dmma(D[q][nt][0], D[q][nt][1], av, M[(nt * 8 + row) * PD_PITCH + 4 * ks + col]);
+          for (int g = 0; g < 4; ++g)
+          {
+            piece[g] = d4{0.0, 0.0, 0.0, 0.0};
+            if (act && 16u * g + 4u * col < sp) piece[g] = ldg256(cv + 16 * g);
+          }
+#pragma unroll
+          for (int g = 0; g < 4; ++g)
+          {
+            if (16u * g >= sp) break; /* warp-uniform */
+            const unsigned int e0 = 16u * g + 4u * col;
+            /* padding is never used (it may hold anything) */
+            const double av[4] = {e0 < s ? piece[g].x : 0.0, e0 + 1 < s ? piece[g].y : 0.0, e0 + 2 < s ? piece[g].z : 0.0,
+                                  e0 + 3 < s ? piece[g].w : 0.0};
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+              for (int nt = 0; nt < 8; ++nt)
+                if ((unsigned int)nt < NT)
+                  pd_dmma(D[q][nt][0], D[q][nt][1], av[j], M[(nt * 8 + row) * PD_PITCH + 16 * g + 4 * j + col]);
           }
         }
       }
@@ -243,7 +288,7 @@ __global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a
   if (!a.pscaler) return;
   __syncwarp();
   /* scaler counts and the rare rescaling pass: the warp's own tiles */
-  for (unsigned int t = warp; t < PD_TILES; t += PD_WARPS)
+  for (unsigned int t = warp; t < tiles_per_cta; t += PD_WARPS)
   {
     const unsigned long long site = (tile0 + t) * 8 + row;
     if ((tile0 + t) * 8 >= a.sites) break;
@@ -418,8 +463,13 @@ bool launch_partials(PartCtx * c, const pll_operation_t * ops_in, unsigned int c
           return false;
         attr_set = true;
       }
+      /* tiles of 8 sites per CTA: a multiple of the warp count, sized so that the grid is about one resident wave
+       * (2 CTAs per SM); a CTA re-stages the matrices of every category, so more than that only costs L2 reads */
       const unsigned int tiles = (c->sites_alloc + 7) / 8;
-      partial_dmma_kernel<<<(tiles + PD_TILES - 1) / PD_TILES, PD_WARPS * 32, PD_SMEM, c->stream>>>(a);
+      unsigned int tpc = (tiles + 2 * c->sm_count - 1) / (2 * c->sm_count);
+      tpc = (tpc + PD_WARPS - 1) / PD_WARPS * PD_WARPS;
+      if (tpc > PD_TILES) tpc = PD_TILES;
+      partial_dmma_kernel<<<(tiles + tpc - 1) / tpc, PD_WARPS * 32, PD_SMEM, c->stream>>>(a, tpc);
       ++g_kernel_launches;
       if (!pllb200_cuda_ok(cudaGetLastError(), "partial_dmma_kernel launch")) return false;
       continue;

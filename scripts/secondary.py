@@ -56,6 +56,26 @@ def c3(sites=200000, tips=500):
             "blo_one_smoothing_s": tb, "blo_branches": 2 * tips - 3, "blo_neg_loglh": nll}
 
 
+def n1(sites=20000, tips=100, states=61):
+    """Codon-sized alphabet (61 states, Gamma-4): full traversal on partial_dmma_kernel (one launch per operation)."""
+    with Harness("b200", tips=tips, sites=sites, states=states) as h:
+        ll = h.loglh(0)
+        tk = h.time_update_partials(3)
+        t = timed(lambda: h.loglh(0), 3)
+        c = h.op_type_counts()
+    sp = (states + 3) // 4 * 4
+    nt = (states + 7) // 8
+    # executed DMMA work: an inner child is ceil(s/8) n-tiles x sp/4 k-steps of m8n8k4 (512 flop) per 8 sites and category
+    inner_children = 2 * c["ii"] + c["ti"]
+    dmma_flops = inner_children * (sites / 8.0) * 4 * nt * (sp // 4) * 512
+    clv_bytes = 8.0 * sites * 4 * sp
+    return {"workload": "%d states, Gamma-4, %d taxa x %d sites (row N1: codon-sized alphabet)" % (states, tips, sites),
+            "loglh": ll, "traversal_ms": tk * 1e3, "full_loglh_ms": t * 1e3, "site_updates_per_s": (tips - 2) * sites / tk,
+            "dense_equiv_TFLOPs_fp64": (tips - 2) * sites * 4 * (4.0 * states * states + states) / tk / 1e12,
+            "dmma_frac": dmma_flops / tk / DMMA_PEAK, "dmma_peak_TFLOPs": DMMA_PEAK / 1e12,
+            "clv_GBps": (inner_children + tips - 2) * clv_bytes / tk / 1e9}
+
+
 def c4(sites=2500, tips=200, nparts=100):
     pkg = load_product_package()
     states = [4 if p % 2 == 0 else 20 for p in range(nparts)]
@@ -123,4 +143,4 @@ if __name__ == "__main__":
         if name == "c5full":
             print(json.dumps({"c5full": c5(spr_tips=2000, spr_sites=500000)}), flush=True)
         else:
-            print(json.dumps({name: {"c3": c3, "c4": c4, "c5": c5}[name]()}), flush=True)
+            print(json.dumps({name: {"c3": c3, "c4": c4, "c5": c5, "n1": n1}[name]()}), flush=True)
