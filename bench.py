@@ -211,7 +211,8 @@ def attach_reduce(h, pkg, a, rank, world):
 
 def multi_gpu_check(pkg, a, rank, world, barrier):
     """A 64-taxon x (world * 40k)-site alignment sharded over the ranks against the same alignment on rank 0
-    alone: logL, and -logL after one Newton-Raphson smoothing pass (exercises the in-kernel exchange)."""
+    alone: logL, -logL after one Newton-Raphson smoothing pass (exercises the in-kernel exchange), and one SPR round."""
+    import numpy as np
     from pllharness import Harness
     tips, S = 64, 40000 * world
     with Harness("b200", tips=tips, sites=S, rank=rank, nranks=world) as hs:
@@ -219,16 +220,34 @@ def multi_gpu_check(pkg, a, rank, world, barrier):
         ll_s = hs.loglh(0)
         blo_s = hs.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)
         barrier()
+    # one SPR round (batched regraft scoring: the per-candidate scores are summed over the ranks before the
+    # reference's cutoff logic is replayed) on a smaller alignment
+    stips, sS = 40, 6000 * world
+    spr_kw = dict(thorough=False, radius_min=1, radius_max=4, ntopol_keep=5, smoothings=4, epsilon=0.1, bl_min=1e-6)
+    with Harness("b200", tips=stips, sites=sS, rank=rank, nranks=world) as hs:
+        attach_reduce(hs, pkg, a, rank, world)
+        hs.loglh(0)
+        spr_s, _ = hs.spr_round(**spr_kw)
+        topo_s = hs.topology_signature()[0]
+        barrier()
     out = None
     if rank == 0:
         with Harness("b200", tips=tips, sites=S) as h1:
             ll_1 = h1.loglh(0)
             blo_1 = h1.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)
+        with Harness("b200", tips=stips, sites=sS) as h1:
+            h1.loglh(0)
+            spr_1, _ = h1.spr_round(**spr_kw)
+            topo_1 = h1.topology_signature()[0]
         out = {"shape": "%d taxa x %d sites over %d ranks vs one GPU" % (tips, S, world),
                "logl_sharded": ll_s, "logl_one_gpu": ll_1, "logl_rel_err": abs(ll_s - ll_1) / abs(ll_1),
                "blo_sharded": blo_s, "blo_one_gpu": blo_1, "blo_rel_err": abs(blo_s - blo_1) / abs(blo_1),
                "tolerance": 1e-10, "reduce": a.reduce}
-        out["ok"] = bool(out["logl_rel_err"] <= 1e-10 and out["blo_rel_err"] <= 1e-10)
+        out["spr_round"] = {"shape": "%d taxa x %d sites, radius 1..4, ntopol_keep 5" % (stips, sS), "loglh_sharded": spr_s,
+                            "loglh_one_gpu": spr_1, "rel_err": abs(spr_s - spr_1) / abs(spr_1),
+                            "same_topology": bool(np.array_equal(np.asarray(topo_s), np.asarray(topo_1)))}
+        out["ok"] = bool(out["logl_rel_err"] <= 1e-10 and out["blo_rel_err"] <= 1e-10 and
+                         out["spr_round"]["rel_err"] <= 1e-9 and out["spr_round"]["same_topology"])
     barrier()
     return out
 
