@@ -101,4 +101,76 @@ __device__ __forceinline__ void aa4_pass(const double * __restrict__ sum, const 
   }
 }
 
+/* ---- the same pass for any table row of E = K * states_padded doubles with E % 16 == 0 (17..64 states) ---------
+ * bt: E / 4 * 32 doubles.  diag: [k][j < s][3]; wf[k] = w_k (1 - pinv_k).  Padding entries of a table row are zero
+ * (both sumtable kernels write them) and get factor zero. */
+__device__ __forceinline__ void dmma_build_b(const double * diag, const double * wf, double * bt, unsigned int s,
+                                             unsigned int sp, unsigned int E)
+{
+  for (unsigned int i = threadIdx.x; i < E * 8u; i += blockDim.x)
+  {
+    const unsigned int ks = i >> 5, l = i & 31u, n = l >> 2, e = 16u * (ks >> 2) + 4u * (l & 3u) + (ks & 3u);
+    const unsigned int k = e / sp, j = e % sp;
+    bt[i] = (n < 3u && j < s) ? wf[k] * diag[(k * s + j) * 3u + n] : 0.0;
+  }
+}
+
+/* inv_lk: null, or per state the invariant-site term */
+__device__ __forceinline__ void dmma_pass(const double * __restrict__ sum, const unsigned int * __restrict__ weights,
+                                          const int * __restrict__ invariant, const double * inv_lk,
+                                          unsigned int sites, const double * bt, unsigned int E, unsigned long long gw,
+                                          unsigned long long nw, bool fwd, int lane, double & acc1, double & acc2)
+{
+  const unsigned long long ntiles = ((unsigned long long)sites + 7) / 8;
+  const unsigned long long mytiles = gw < ntiles ? (ntiles - gw + nw - 1) / nw : 0;
+  const unsigned int pieces = E / 16u;
+  const double * btl = bt + lane;
+  for (unsigned long long ti = 0; ti < mytiles; ++ti)
+  {
+    const unsigned long long tile = gw + (fwd ? ti : mytiles - 1 - ti) * nw;
+    const unsigned long long site = tile * 8 + ((unsigned int)lane >> 2);
+    const bool act = site < sites;
+    const double * src = sum + site * E + 4u * ((unsigned int)lane & 3u);
+    const bool finisher = ((unsigned int)lane & 3u) == 0u && act;
+    unsigned int wgt = 0;
+    int inv = -1;
+    if (finisher)
+    {
+      wgt = __ldg(weights + site);
+      if (inv_lk && invariant) inv = invariant[site];
+    }
+    double d0 = 0.0, d1 = 0.0;
+    for (unsigned int g0 = 0; g0 < pieces; g0 += 8) /* 8 pieces = 64 registers in flight per lane */
+    {
+      d4 xv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+      {
+        xv[u] = d4{0.0, 0.0, 0.0, 0.0};
+        if (act && g0 + u < pieces) xv[u] = ldg256(src + 16 * (g0 + u));
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+      {
+        if (g0 + u >= pieces) break; /* warp-uniform */
+        const double * b = btl + (size_t)(4 * (g0 + u)) * 32;
+        aa4_dmma(d0, d1, xv[u].x, b[0]);
+        aa4_dmma(d0, d1, xv[u].y, b[32]);
+        aa4_dmma(d0, d1, xv[u].z, b[64]);
+        aa4_dmma(d0, d1, xv[u].w, b[96]);
+      }
+    }
+    const double L2 = __shfl_down_sync(0xffffffffu, d0, 1);
+    if (finisher)
+    {
+      double L0 = d0;
+      if (inv >= 0) L0 += inv_lk[inv];
+      const double r = 1.0 / L0;
+      const double r1 = -d1 * r;
+      acc1 += (double)wgt * r1;
+      acc2 += (double)wgt * (r1 * r1 - L2 * r);
+    }
+  }
+}
+
 #endif

@@ -291,7 +291,7 @@ void dev_ctx_destroy(PartCtx * c)
   cudaFree(c->d_pmat_cols); cudaFree(c->d_tipcols); cudaFree(c->d_score);
   if (c->h_score) cudaFreeHost(c->h_score);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
-  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag);
+  cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag); cudaFree(c->d_sumgen);
   cudaFree(c->d_multi);
   if (c->ev_batch) cudaEventDestroy(c->ev_batch);
   for (int r = 0; r < 8; ++r)

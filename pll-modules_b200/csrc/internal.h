@@ -81,6 +81,8 @@ struct PartCtx
   unsigned long long xred_seq;
   double * d_sumfrag;         /* lazily allocated: 20-state sumtable matrices as DMMA fragment images */
   std::vector<unsigned long long> sumfrag_key;
+  double * d_sumgen = nullptr; /* lazily allocated: 17..64-state sumtable matrices [L | R][K][s][sp] */
+  std::vector<unsigned long long> sumgen_key;
   unsigned long long tipmap_gen = 0; /* bumped whenever the tip map is uploaded again */
   /* batched regraft scoring (k_traversal_dna4.cu): per-warp partial sums + results, pinned landing buffer */
   double * d_score;
@@ -308,6 +310,9 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
 bool launch_newton_multi(PartCtx ** cs, unsigned int count, unsigned int * const * params_indices,
                          double * const * d_sumtables, const double * scales, double xmin, double x0,
                          double xmax, double tol, unsigned int max_iters, int slot);
+bool generic_dmma_usable(const PartCtx * c);
+bool launch_sumtable_dmma(PartCtx * c, bool first_is_tip, unsigned int first, unsigned int second,
+                          const unsigned int * params_indices, double * d_sumtable);
 bool launch_sumtable_aa(PartCtx * c, bool first_is_tip, unsigned int first, unsigned int second,
                         const unsigned int * params_indices, double * d_sumtable);
 bool launch_pmatrix_devlen(PartCtx * c, const unsigned int * params_indices, unsigned int matrix_index,

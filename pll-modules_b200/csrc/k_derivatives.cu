@@ -614,6 +614,11 @@ bool launch_sumtable(PartCtx * c, unsigned int parent_clv, unsigned int child_cl
     const unsigned int first = ctip ? child_clv : parent_clv, second = ctip ? parent_clv : child_clv;
     return launch_sumtable_aa(c, ptip || ctip, first, second, params_indices, d_sumtable);
   }
+  if (generic_dmma_usable(c) && (!(ptip || ctip) || c->d_tipmap))
+  {
+    const unsigned int first = ctip ? child_clv : parent_clv, second = ctip ? parent_clv : child_clv;
+    return launch_sumtable_dmma(c, ptip || ctip, first, second, params_indices, d_sumtable);
+  }
   SumArgs a;
   memset(&a, 0, sizeof(a));
   if (ptip || ctip)

@@ -33,6 +33,7 @@ namespace cg = cooperative_groups;
 #define NW_MAXK 32
 #define NW_MAXRANKS 8
 #define NW_MAX_DIAG 512 /* K * states */
+#define NW_DMMA_MAXE 256 /* MODE 5: K * states_padded */
 
 /* status codes returned in result[1] */
 #define NW_OK 0.0
@@ -164,11 +165,11 @@ __device__ __forceinline__ void newton_publish(const NewtonArgs & a, double x, d
 /* MODE 0: any state count;  1: 4 states, any K;  2: 4 states, K = 4 (reduce-scatter over the rates);
  * 4: 20 states, K = 4, unpadded (protein Gamma-4: the pass is a [sites x 80] x [80 x 3] product on the FP64 tensor cores) */
 template <int MODE>
-__global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(NewtonArgs a)
+__global__ void __launch_bounds__(NW_THREADS, (MODE == 2 || MODE == 5) ? 2 : 3) newton_kernel(NewtonArgs a)
 {
   constexpr bool DNA = MODE == 1 || MODE == 2;
-  __shared__ double s_aux[24]; /* MODE 4: w_k (1 - pinv_k) | invariant-site term per state */
-  __shared__ double s_bt[MODE == 4 ? AA4_BT : 1]; /* MODE 4: B fragments of the pass */
+  __shared__ double s_aux[MODE == 5 ? 80 : 24]; /* MODE 4 / 5: w_k (1 - pinv_k) | invariant-site term per state */
+  __shared__ double s_bt[MODE == 4 ? AA4_BT : (MODE == 5 ? NW_DMMA_MAXE * 8 : 1)]; /* B fragments of the tensor-core pass */
   cg::grid_group grid = cg::this_grid();
   __shared__ double s_diag[NW_MAX_DIAG * 3];
   __shared__ double s_red[2][NW_THREADS / 32];
@@ -255,6 +256,24 @@ __global__ void __launch_bounds__(NW_THREADS, MODE == 2 ? 2 : 3) newton_kernel(N
       aa4_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 4 : nullptr, a.sites, s_bt,
                (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp,
                (unsigned long long)gridDim.x * (NW_THREADS / 32), fwd, lane, acc1, acc2);
+    }
+    else if (MODE == 5)
+    {
+      /* 17..64 states, K * states_padded a multiple of 16 and <= NW_DMMA_MAXE: the generic tensor-core pass */
+      if (threadIdx.x < K) s_aux[threadIdx.x] = a.w[threadIdx.x] * (1.0 - a.pinv[threadIdx.x]);
+      if (threadIdx.x < s)
+      {
+        double t = 0.0;
+        for (unsigned int kk = 0; kk < K; ++kk)
+          t += a.w[kk] * a.pinv[kk] * a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * s * sp + sp + threadIdx.x];
+        s_aux[16 + threadIdx.x] = t;
+      }
+      __syncthreads();
+      dmma_build_b(s_diag, s_aux, s_bt, s, sp, K * sp);
+      __syncthreads();
+      dmma_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 16 : nullptr, a.sites, s_bt, K * sp,
+                (unsigned long long)blockIdx.x * (NW_THREADS / 32) + warp,
+                (unsigned long long)gridDim.x * (NW_THREADS / 32), fwd, lane, acc1, acc2);
     }
     else if (MODE == 2)
     {
@@ -1226,9 +1245,13 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   int mode = s == 4 ? (K == 4 ? 2 : 1) : 0;
   if (mode == 2 && g_opt_fused_newton == 1) mode = 3; /* fused_newton=2 keeps the register version */
   if (s == 20 && p->states_padded == 20 && K == 4 && g_opt_fused_newton != 3) mode = 4; /* fused_newton=3: generic kernel */
+  if (mode == 0 && g_opt_fused_newton == 1 && g_opt_generic_dmma && s > 16 && s <= 64 && K <= 16 &&
+      (K * p->states_padded) % 16 == 0 && K * p->states_padded <= NW_DMMA_MAXE)
+    mode = 5;
   if (eval_only && mode != 3)
     return pllb200_cuda_ok(cudaErrorInvalidValue, "derivative pass on the TMA ring: wrong shape");
-  const void * fn = mode == 4   ? (const void *)newton_kernel<4>
+  const void * fn = mode == 5   ? (const void *)newton_kernel<5>
+                    : mode == 4 ? (const void *)newton_kernel<4>
                     : mode == 3 ? (eval_only ? (const void *)newton_dna4_tma_kernel<true> : (const void *)newton_dna4_tma_kernel<false>)
                     : mode == 2 ? (const void *)newton_kernel<2>
                     : mode == 1 ? (const void *)newton_kernel<1>
@@ -1246,7 +1269,7 @@ bool launch_newton(PartCtx * c, const unsigned int * params_indices, const doubl
   }
   const unsigned long long E = (unsigned long long)a.sites * K;
   unsigned long long blocks = mode == 3 ? (E + NT_TILE - 1) / NT_TILE : (E + NW_THREADS - 1) / NW_THREADS;
-  if (mode == 4) blocks = (((unsigned long long)a.sites + 7) / 8 + NW_THREADS / 32 - 1) / (NW_THREADS / 32); /* a warp per 8-site tile */
+  if (mode == 4 || mode == 5) blocks = (((unsigned long long)a.sites + 7) / 8 + NW_THREADS / 32 - 1) / (NW_THREADS / 32); /* a warp per 8-site tile */
   unsigned long long cap = (unsigned long long)c->sm_count * std::min(per_sm[pi], 4);
   if (cap > PLLB200_MAX_RED_BLOCKS * 3 / 4) cap = PLLB200_MAX_RED_BLOCKS * 3 / 4; /* partials: 2 buffers x 2 values */
   if (blocks > cap) blocks = cap;

@@ -313,6 +313,102 @@ __global__ void __launch_bounds__(PD_WARPS * 32) partial_dmma_kernel(GenOpArgs a
   }
 }
 
+/* ---- host side of the 17..64-state tensor-core kernel ------------------------------------------------ */
+bool generic_dmma_usable(const PartCtx * c)
+{
+  const pll_partition_t * p = &c->pub;
+  return g_opt_generic_dmma && p->states > 16 && p->states <= 64 && p->states_padded <= 64 &&
+         !(p->attributes & PLL_ATTRIB_RATE_SCALERS);
+}
+
+static bool launch_partial_dmma(PartCtx * c, const GenOpArgs & a, cudaStream_t stream)
+{
+  static bool attr_set = false;
+  if (!attr_set)
+  {
+    if (!pllb200_cuda_ok(cudaFuncSetAttribute(partial_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PD_SMEM),
+                         "partial_dmma_kernel smem"))
+      return false;
+    attr_set = true;
+  }
+  /* tiles of 8 sites per CTA: a multiple of the warp count, sized so that the grid is about one resident wave
+   * (2 CTAs per SM); a CTA re-stages the matrices of every category, so more than that only costs L2 reads */
+  const unsigned int tiles = (a.sites + 7) / 8;
+  unsigned int tpc = (tiles + 2 * c->sm_count - 1) / (2 * c->sm_count);
+  tpc = (tpc + PD_WARPS - 1) / PD_WARPS * PD_WARPS;
+  if (tpc > PD_TILES) tpc = PD_TILES;
+  if (tpc < PD_WARPS) tpc = PD_WARPS;
+  partial_dmma_kernel<<<(tiles + tpc - 1) / tpc, PD_WARPS * 32, PD_SMEM, stream>>>(a, tpc);
+  ++g_kernel_launches;
+  return pllb200_cuda_ok(cudaGetLastError(), "partial_dmma_kernel launch");
+}
+
+/* The sumtable of an edge (A.6 of SURVEY.md, core_derivatives.c:116-640) IS a partial-likelihood operation whose
+ * "P-matrices" are the eigenvector images  L[j][i] = pi_i Vinv[i][j]  and  R[j][i] = V[j][i], whose parent buffer is
+ * the sumtable, and which never scales (the trick of launch_sumtable_aa, k_traversal_aa.cu).  The scalar kernel
+ * took 2.2 ms per edge at 61 states x 20 k sites = 81 % of a smoothing pass
+ * (profiles/r02h_launches_blo_codon_100x20k.txt). */
+struct SumGenIdx
+{
+  unsigned int v[32];
+};
+
+__global__ void sumgen_kernel(double * __restrict__ out, const double * __restrict__ eigen, unsigned long long eigen_stride,
+                              unsigned int K, unsigned int s, unsigned int sp, SumGenIdx idx)
+{
+  const unsigned int k = blockIdx.x;
+  const double * blk = eigen + (unsigned long long)idx.v[k] * eigen_stride;
+  const double * ev = blk, * iev = blk + s * sp, * fr = blk + 2 * s * sp + sp;
+  double * L = out + (size_t)k * s * sp, * R = out + ((size_t)K + k) * s * sp;
+  for (unsigned int t = threadIdx.x; t < s * sp; t += blockDim.x)
+  {
+    const unsigned int j = t / sp, i = t % sp;
+    L[t] = i < s ? fr[i] * iev[i * sp + j] : 0.0;
+    R[t] = i < s ? ev[j * sp + i] : 0.0;
+  }
+}
+
+bool launch_sumtable_dmma(PartCtx * c, bool first_is_tip, unsigned int first, unsigned int second,
+                          const unsigned int * params_indices, double * d_sumtable)
+{
+  pll_partition_t * p = &c->pub;
+  const unsigned int K = p->rate_cats, s = p->states, sp = p->states_padded;
+  if (K > 32) return false;
+  const size_t doubles = (size_t)2 * K * s * sp;
+  if (!c->d_sumgen &&
+      !pllb200_cuda_ok(cudaMalloc(&c->d_sumgen, doubles * sizeof(double)), "sumtable eigenvector images"))
+    return false;
+  std::vector<unsigned long long> key(K);
+  for (unsigned int k = 0; k < K; ++k)
+    key[k] = ((unsigned long long)params_indices[k] << 32) | c->eigen_version[params_indices[k]];
+  if (key != c->sumgen_key)
+  {
+    SumGenIdx idx;
+    memset(&idx, 0, sizeof(idx));
+    for (unsigned int k = 0; k < K; ++k) idx.v[k] = params_indices[k];
+    sumgen_kernel<<<K, 256, 0, xstream(c)>>>(c->d_sumgen, c->d_eigen, c->eigen_stride, K, s, sp, idx);
+    ++g_kernel_launches;
+    if (!pllb200_cuda_ok(cudaGetLastError(), "sumgen_kernel launch")) return false;
+    c->sumgen_key = key;
+  }
+  GenOpArgs a;
+  memset(&a, 0, sizeof(a));
+  a.parent = d_sumtable;
+  if (first_is_tip)
+    a.ltip = c->d_tipchars + (size_t)first * c->tip_stride;
+  else
+    a.left = clv_dev(c, first);
+  a.right = clv_dev(c, second);
+  a.lmat = c->d_sumgen;
+  a.rmat = c->d_sumgen + (size_t)K * s * sp;
+  a.tipmap = c->d_tipmap;
+  a.sites = c->sites_alloc;
+  a.states = s;
+  a.sp = sp;
+  a.K = K;
+  return launch_partial_dmma(c, a, xstream(c));
+}
+
 /* ------------------------------------------------------------------------------------------ */
 /* host: validation, L2-friendly scheduling, dispatch                                          */
 /* ------------------------------------------------------------------------------------------ */
@@ -452,26 +548,9 @@ bool launch_partials(PartCtx * c, const pll_operation_t * ops_in, unsigned int c
     a.K = K;
     a.rate_scalers = rate_scalers;
     a.is4 = p->states == 4;
-    if (g_opt_generic_dmma && p->states > 16 && p->states <= 64 && p->states_padded <= 64 && !rate_scalers &&
-        (!pattern_tip || c->d_tipmap))
+    if (generic_dmma_usable(c) && (!pattern_tip || c->d_tipmap))
     {
-      static bool attr_set = false;
-      if (!attr_set)
-      {
-        if (!pllb200_cuda_ok(cudaFuncSetAttribute(partial_dmma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PD_SMEM),
-                             "partial_dmma_kernel smem"))
-          return false;
-        attr_set = true;
-      }
-      /* tiles of 8 sites per CTA: a multiple of the warp count, sized so that the grid is about one resident wave
-       * (2 CTAs per SM); a CTA re-stages the matrices of every category, so more than that only costs L2 reads */
-      const unsigned int tiles = (c->sites_alloc + 7) / 8;
-      unsigned int tpc = (tiles + 2 * c->sm_count - 1) / (2 * c->sm_count);
-      tpc = (tpc + PD_WARPS - 1) / PD_WARPS * PD_WARPS;
-      if (tpc > PD_TILES) tpc = PD_TILES;
-      partial_dmma_kernel<<<(tiles + tpc - 1) / tpc, PD_WARPS * 32, PD_SMEM, c->stream>>>(a, tpc);
-      ++g_kernel_launches;
-      if (!pllb200_cuda_ok(cudaGetLastError(), "partial_dmma_kernel launch")) return false;
+      if (!launch_partial_dmma(c, a, c->stream)) return false;
       continue;
     }
     const unsigned int spb = GEN_THREADS / K;

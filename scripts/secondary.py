@@ -63,6 +63,10 @@ def n1(sites=20000, tips=100, states=61):
         tk = h.time_update_partials(3)
         t = timed(lambda: h.loglh(0), 3)
         c = h.op_type_counts()
+        h.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)   # allocates the sumtable
+        tb0 = time.perf_counter()
+        nll = h.optimize_branch_lengths(method=0, radius=-1, max_iters=1, lh_epsilon=1.0)
+        tb = time.perf_counter() - tb0
     sp = (states + 3) // 4 * 4
     nt = (states + 7) // 8
     # executed DMMA work: an inner child is ceil(s/8) n-tiles x sp/4 k-steps of m8n8k4 (512 flop) per 8 sites and category
@@ -73,7 +77,8 @@ def n1(sites=20000, tips=100, states=61):
             "loglh": ll, "traversal_ms": tk * 1e3, "full_loglh_ms": t * 1e3, "site_updates_per_s": (tips - 2) * sites / tk,
             "dense_equiv_TFLOPs_fp64": (tips - 2) * sites * 4 * (4.0 * states * states + states) / tk / 1e12,
             "dmma_frac": dmma_flops / tk / DMMA_PEAK, "dmma_peak_TFLOPs": DMMA_PEAK / 1e12,
-            "clv_GBps": (inner_children + tips - 2) * clv_bytes / tk / 1e9}
+            "clv_GBps": (inner_children + tips - 2) * clv_bytes / tk / 1e9,
+            "blo_one_smoothing_s": tb, "blo_branches": 2 * tips - 3, "blo_neg_loglh": nll}
 
 
 def c4(sites=2500, tips=200, nparts=100):

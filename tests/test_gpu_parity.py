@@ -235,6 +235,8 @@ def test_protein_forwarding_kernel_equals_the_per_operation_kernel(kw):
     dict(tips=40, sites=1500, pinv=0.25),
     dict(tips=12, sites=300, states=20),
     dict(tips=60, sites=1000, brlen_scale=10.0, attributes=ATTR_PATTERN_TIP | ATTR_RATE_SCALERS),
+    dict(tips=12, sites=203, states=61, rate_cats=2),             # sumtable as a tensor-core operation (tip + inner edges)
+    dict(tips=10, sites=90, states=25, attributes=0),             # the same with tip CLVs, padded 25 -> 28
 ], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
 def test_sumtable_and_derivatives_every_edge(kw):
     """Re-root on several edges (tip edges and inner edges), compare sumtable + d/dd at 6 lengths."""
@@ -733,6 +735,31 @@ def test_dna_gamma4_tile_kernels_equal_the_general_kernels(kw):
         assert rel(a[0], b[0]) < 1e-13 and rel(a[1], b[1]) < 1e-13
         np.testing.assert_allclose(a[3], b[3], rtol=1e-10, atol=1e-9)
         np.testing.assert_allclose(a[4], b[4], rtol=1e-10, atol=1e-9)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kw", [
+    dict(tips=14, sites=1003, states=61),                  # E = 4 x 64 = 256: two groups of 8 pieces per tile
+    dict(tips=10, sites=333, states=32, rate_cats=2),      # E = 64
+    dict(tips=12, sites=500, states=61, pinv=0.1),         # invariant-site term in the finishing lane
+], ids=lambda kw: "-".join("%s%s" % (k[:3], v) for k, v in kw.items()))
+def test_generic_tensor_core_newton_pass_equals_the_scalar_kernel(kw):
+    """newton_kernel<5> (17..64 states: the derivative pass as a [sites x E] x [E x 3] product on the FP64 tensor
+    cores, dmma_pass in aa4_pass.cuh) against newton_kernel<0> (fused_newton 2): -logL after two smoothing passes and
+    every branch length."""
+    pkg = load_product_package()
+    out = {}
+    try:
+        for mode in (1, 2):
+            pkg.set_option("fused_newton", mode)
+            with Harness("b200", **kw) as d:
+                d.loglh()
+                nll = d.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.01)
+                out[mode] = (nll, d.branch_lengths().copy())
+    finally:
+        pkg.set_option("fused_newton", 1)
+    assert rel(out[1][0], out[2][0]) < 1e-12, (out[1][0], out[2][0])
+    np.testing.assert_allclose(out[1][1], out[2][1], rtol=1e-7, atol=1e-10)
 
 
 # ---- model-parameter optimisers over device-resident state (SURVEY.md §8a rows a13/a14) ----
