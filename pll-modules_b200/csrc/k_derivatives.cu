@@ -447,6 +447,35 @@ __global__ void __launch_bounds__(DVA_THREADS, 3) deriv_aa4_kernel(DerivArgs a, 
   grid_reduce_finish<2>(v, a.red);
 }
 
+/* 17..64 states, K * states_padded a multiple of 16 and <= DVD_MAXE: dmma_pass of aa4_pass.cuh */
+#define DVD_MAXE 256
+__global__ void __launch_bounds__(DVA_THREADS, 2) deriv_dmma_kernel(DerivArgs a, int reverse)
+{
+  __shared__ double s_aux[80];
+  __shared__ double s_bt[DVD_MAXE * 8];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const unsigned int K = a.K, s = a.states, sp = a.sp;
+  bool any_pinv = false;
+  for (unsigned int kk = 0; kk < K; ++kk) any_pinv |= a.pinv[kk] > 0.0;
+  if (threadIdx.x < K) s_aux[threadIdx.x] = a.w[threadIdx.x] * (1.0 - a.pinv[threadIdx.x]);
+  if (threadIdx.x < s)
+  {
+    double t = 0.0;
+    for (unsigned int kk = 0; kk < K; ++kk)
+      t += a.w[kk] * a.pinv[kk] * a.eigen[(unsigned long long)a.model_idx[kk] * a.eigen_stride + 2 * s * sp + sp + threadIdx.x];
+    s_aux[16 + threadIdx.x] = t;
+  }
+  __syncthreads();
+  dmma_build_b(a.diag, s_aux, s_bt, s, sp, K * sp);
+  __syncthreads();
+  double acc1 = 0.0, acc2 = 0.0;
+  dmma_pass(a.sum, a.weights, a.invariant, (any_pinv && a.invariant) ? s_aux + 16 : nullptr, a.sites, s_bt, K * sp,
+            (unsigned long long)blockIdx.x * (DVA_THREADS / 32) + warp,
+            (unsigned long long)gridDim.x * (DVA_THREADS / 32), reverse == 0, lane, acc1, acc2);
+  double v[2] = {acc1, acc2};
+  grid_reduce_finish<2>(v, a.red);
+}
+
 __global__ void __launch_bounds__(DVG_THREADS) deriv_generic_kernel(DerivArgs a)
 {
   __shared__ double s_l[3][DVG_THREADS];
@@ -827,6 +856,17 @@ bool launch_derivatives(PartCtx * c, int parent_scaler, int child_scaler, double
     const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
     c->deriv_last_table = d_sumtable;
     deriv_aa4_kernel<<<(unsigned)blocks, DVA_THREADS, 0, c->stream>>>(a, reverse);
+  }
+  else if (generic_dmma_usable(c) && g_opt_fused_newton == 1 && K <= 16 && (K * sp) % 16 == 0 && K * sp <= DVD_MAXE)
+  {
+    a.diag = (const double *)dev_stage(c, diag.data(), sizeof(double) * diag.size());
+    if (!a.diag) return false;
+    unsigned long long blocks = (((unsigned long long)a.sites + 7) / 8 + DVA_THREADS / 32 - 1) / (DVA_THREADS / 32);
+    if (blocks > (unsigned long long)c->sm_count * 2) blocks = (unsigned long long)c->sm_count * 2;
+    if (blocks < 1) blocks = 1;
+    const int reverse = (c->deriv_last_table == d_sumtable) ? (c->deriv_reverse ^= 1) : (c->deriv_reverse = 0);
+    c->deriv_last_table = d_sumtable;
+    deriv_dmma_kernel<<<(unsigned)blocks, DVA_THREADS, 0, c->stream>>>(a, reverse);
   }
   else
   {

@@ -754,12 +754,15 @@ def test_generic_tensor_core_newton_pass_equals_the_scalar_kernel(kw):
             pkg.set_option("fused_newton", mode)
             with Harness("b200", **kw) as d:
                 d.loglh()
+                dd = d.derivatives(d.root(), [0.003, 0.08, 1.1])   # deriv_dmma_kernel / deriv_generic_kernel
                 nll = d.optimize_branch_lengths(method=BLO_NEWTON_FAST, radius=-1, max_iters=2, lh_epsilon=0.01)
-                out[mode] = (nll, d.branch_lengths().copy())
+                out[mode] = (nll, d.branch_lengths().copy(), dd)
     finally:
         pkg.set_option("fused_newton", 1)
     assert rel(out[1][0], out[2][0]) < 1e-12, (out[1][0], out[2][0])
     np.testing.assert_allclose(out[1][1], out[2][1], rtol=1e-7, atol=1e-10)
+    np.testing.assert_allclose(out[1][2][0], out[2][2][0], rtol=1e-10, atol=1e-9)
+    np.testing.assert_allclose(out[1][2][1], out[2][2][1], rtol=1e-10, atol=1e-9)
 
 
 # ---- model-parameter optimisers over device-resident state ----
