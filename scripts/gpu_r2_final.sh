@@ -17,4 +17,7 @@ timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --lo
 E="python bench.py --tips 65 --sites 1000000 --steps 3 --warmup 3 --no-cpu-baseline --no-secondary"
 $E > $O/plain_evals.log 2>&1 && \
 timeout 300 ncu --set full --clock-control none --import-source on -k regex:"logl_dna4_tma" -s 4 -c 2 -o $O/logl_tma_full $E > $O/ncu_evals.log 2>&1
+C="python scripts/bench_blo.py 100 20000 61"
+$C > $O/plain_blo_codon.log 2>&1 && \
+timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file $O/launches_blo_codon_100x20k.csv $C > $O/ncu_blo_codon.log 2>&1
 ls -la $O
