@@ -147,6 +147,42 @@ __device__ __forceinline__ bool newton_allgather(const Args & a, unsigned long l
   return true;
 }
 
+/* After the grid barrier every CTA forms the same ordered sum of all CTAs' partials.  The CTA's first 256 threads
+ * take one or two partials each — one L2 round trip — instead of one warp walking G / 32 dependent loads (296
+ * CTAs: ten serial L2 latencies, 3.6 us of every pass).  red: [2][NW_THREADS / 32] shared doubles (the warp
+ * partials of the pass, already consumed).  Returns the totals in thread 0 only. */
+__device__ __forceinline__ void newton_sum_partials(const double * buf, unsigned int G, double (*red)[NW_THREADS / 32],
+                                                    double & t1, double & t2)
+{
+  const unsigned int tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+  double a1 = 0.0, a2 = 0.0;
+  if (tid < NW_THREADS)
+    for (unsigned int q = tid; q < G; q += NW_THREADS)
+    {
+      a1 += __ldcg(buf + q);
+      a2 += __ldcg(buf + G + q);
+    }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1)
+  {
+    a1 += __shfl_down_sync(0xffffffffu, a1, off);
+    a2 += __shfl_down_sync(0xffffffffu, a2, off);
+  }
+  if (tid < NW_THREADS && lane == 0)
+  {
+    red[0][warp] = a1;
+    red[1][warp] = a2;
+  }
+  __syncthreads();
+  t1 = t2 = 0.0;
+  if (tid == 0)
+    for (int wi = 0; wi < NW_THREADS / 32; ++wi)
+    {
+      t1 += red[0][wi];
+      t2 += red[1][wi];
+    }
+}
+
 /* what the host does with a result (pll_optimize.c:1524-1560), for the queued mode: an unconverged or
  * failed branch keeps its old length, and so does a change below 1e-10 */
 __device__ __forceinline__ void newton_publish(const NewtonArgs & a, double x, double xorig, double status,
@@ -462,21 +498,10 @@ __global__ void __launch_bounds__(NW_THREADS, (MODE == 2 || MODE == 5) ? 2 : 3) 
     }
     grid.sync();
     /* every CTA: the same ordered sum of all partials */
-    if (warp == 0)
     {
-      double t1 = 0.0, t2 = 0.0;
-      for (unsigned int b = lane; b < gridDim.x; b += 32)
-      {
-        t1 += __ldcg(buf + b);
-        t2 += __ldcg(buf + gridDim.x + b);
-      }
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1)
-      {
-        t1 += __shfl_down_sync(0xffffffffu, t1, off);
-        t2 += __shfl_down_sync(0xffffffffu, t2, off);
-      }
-      if (lane == 0)
+      double t1, t2;
+      newton_sum_partials(buf, gridDim.x, s_red, t1, t2);
+      if (threadIdx.x == 0)
       {
         if (a.nranks > 1 && !newton_allgather(a, pass0 + iter, t1, t2)) t1 = t2 = nan("");
         s_tot[0] = t1;
@@ -783,21 +808,10 @@ __global__ void __launch_bounds__(NT_THREADS, 2) newton_dna4_tma_kernel(NewtonAr
       buf[G + b] = p2;
     }
     grid.sync();
-    if (warp == 0)
     {
-      double t1 = 0.0, t2 = 0.0;
-      for (unsigned int q = lane; q < G; q += 32)
-      {
-        t1 += __ldcg(buf + q);
-        t2 += __ldcg(buf + G + q);
-      }
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1)
-      {
-        t1 += __shfl_down_sync(0xffffffffu, t1, off);
-        t2 += __shfl_down_sync(0xffffffffu, t2, off);
-      }
-      if (lane == 0)
+      double t1, t2;
+      newton_sum_partials(buf, G, sm.red, t1, t2);
+      if (tid == 0)
       {
         if (a.nranks > 1 && !newton_allgather(a, pass0 + iter, t1, t2)) t1 = t2 = nan("");
         sm.tot[0] = t1;
@@ -1084,21 +1098,10 @@ __global__ void __launch_bounds__(NW_THREADS, 3) newton_multi_kernel(NewtonMulti
       buf[gridDim.x + blockIdx.x] = p2;
     }
     grid.sync();
-    if (warp == 0)
     {
-      double t1 = 0.0, t2 = 0.0;
-      for (unsigned int b = lane; b < gridDim.x; b += 32)
-      {
-        t1 += __ldcg(buf + b);
-        t2 += __ldcg(buf + gridDim.x + b);
-      }
-#pragma unroll
-      for (int off = 16; off > 0; off >>= 1)
-      {
-        t1 += __shfl_down_sync(0xffffffffu, t1, off);
-        t2 += __shfl_down_sync(0xffffffffu, t2, off);
-      }
-      if (lane == 0)
+      double t1, t2;
+      newton_sum_partials(buf, gridDim.x, s_red, t1, t2);
+      if (threadIdx.x == 0)
       {
         if (m.nranks > 1 && !newton_allgather(m, pass0 + iter, t1, t2)) t1 = t2 = nan("");
         s_tot[0] = t1;
