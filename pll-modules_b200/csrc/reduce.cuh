@@ -2,7 +2,7 @@
  * reduce.cuh — deterministic grid reduction used by the logL and derivative kernels.
  *
  * warp shuffle -> block (shared memory) -> one partial per CTA in HBM -> the CTA that takes the
- * last ticket sums the partials in index order and writes the result both to the device result
+ * last ticket sums the partials in a fixed tree order and writes the result both to the device result
  * slot (for a following NCCL all-reduce) and to mapped pinned host memory (so the host needs no
  * extra copy after the stream sync).  For a fixed grid size the summation order is fixed, so
  * repeated evaluations are bit-identical (the reference sums sequentially over sites,
@@ -68,14 +68,25 @@ __device__ __forceinline__ void grid_reduce_finish(double (&v)[N], const ReduceO
   __syncthreads();
   if (!s_last) return;
   __threadfence();
+  /* the last CTA: every thread takes partials b = tid, tid + blockDim, ... (one L2 round trip for up to blockDim
+   * CTAs; a single warp walking gridDim / 32 dependent loads cost ~3.6 us at 296 CTAs), then the block tree above */
+#pragma unroll
+  for (int n = 0; n < N; ++n)
+  {
+    double x = 0.0;
+    for (unsigned int b = threadIdx.x; b < gridDim.x; b += blockDim.x)
+      x += __ldcg(r.partials + (size_t)n * gridDim.x + b);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
+    if (lane == 0) s_red[n][warp] = x;
+  }
+  __syncthreads();
   if (warp == 0)
   {
 #pragma unroll
     for (int n = 0; n < N; ++n)
     {
-      double x = 0.0;
-      for (unsigned int b = lane; b < gridDim.x; b += 32)
-        x += __ldcg(r.partials + (size_t)n * gridDim.x + b);
+      double x = lane < nwarps ? s_red[n][lane] : 0.0;
 #pragma unroll
       for (int off = 16; off > 0; off >>= 1) x += __shfl_down_sync(0xffffffffu, x, off);
       if (lane == 0)
