@@ -313,7 +313,7 @@ def main():
         raise SystemExit("bench.py needs a CUDA device: libpll_b200 has no CPU fallback")
     torch.cuda.set_device(local_rank)
     pkg.load().pllb200_set_device(local_rank)
-    for opt in ("trav_variant", "trav_reorder", "trav_ctas_per_sm", "trav_forward", "trav_stash", "trav_debug", "trav_prefetch", "fused_newton", "queued_newton"):      # tuning knobs (experiments)
+    for opt in ("trav_variant", "trav_reorder", "trav_ctas_per_sm", "trav_forward", "trav_stash", "trav_debug", "trav_prefetch", "trav_split", "trav_split_rounds", "fused_newton", "queued_newton"):      # tuning knobs (experiments)
         if os.environ.get("PLLB200_" + opt.upper()):
             pkg.set_option(opt, int(os.environ["PLLB200_" + opt.upper()]))
     if world > 1:

@@ -109,6 +109,8 @@ extern "C" int pllb200_set_option(const char * name, int value)
   else if (!strcmp(name, "trav_forward")) slot = &g_opt_trav_forward;
   else if (!strcmp(name, "trav_stash")) slot = &g_opt_trav_stash;
   else if (!strcmp(name, "trav_short")) slot = &g_opt_trav_short;
+  else if (!strcmp(name, "trav_split")) slot = &g_opt_trav_split;
+  else if (!strcmp(name, "trav_split_rounds")) slot = &g_opt_trav_split_rounds;
   else if (!strcmp(name, "scratch_rows")) slot = &g_opt_scratch_rows;
   else if (!strcmp(name, "generic_dmma")) slot = &g_opt_generic_dmma;
   else if (!strcmp(name, "fast_evals")) slot = &g_opt_fast_evals;

@@ -174,6 +174,8 @@ extern int g_opt_trav_reorder;
 extern int g_opt_fuse_root;
 extern int g_opt_trav_variant;
 extern int g_opt_trav_short;
+extern int g_opt_trav_split;
+extern int g_opt_trav_split_rounds;
 extern int g_opt_trav_forward;
 extern int g_opt_trav_prefetch;
 extern int g_opt_fused_newton;

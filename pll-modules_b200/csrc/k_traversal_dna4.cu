@@ -52,7 +52,7 @@ struct LeanArgs
   const unsigned int * weights;
   unsigned int score_stride;
   double wpi[16];            /* [category][state]: rate weight x frequency */
-  unsigned int dbg; /* timing ablations only (option trav_debug): 1 no tip loads, 2 no CLV stores, 4 no scaler stores */
+  unsigned int dbg; /* timing ablations only (option trav_debug): 1 no tip loads, 2 no CLV stores, 4 no scaler stores, 8 plain chunk stride in the last round */
 };
 
 #define L4_WARPS 8
@@ -703,9 +703,8 @@ __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
   const unsigned int sm0 = smem_u32(l4_smem);
   const unsigned int sops = sm0;
   const unsigned int wsm = sm0 + (a.seg + 4) * 32 + warp * L4_WARP_SM; /* + the zero record, 128-byte aligned */
-  const unsigned long long nchunks = ((unsigned long long)a.sites + 31) / 32;
-  const unsigned long long gwarp = (unsigned long long)blockIdx.x * L4_WARPS + warp;
-  const unsigned long long nwarps = (unsigned long long)gridDim.x * L4_WARPS;
+  const unsigned int nchunks = (unsigned int)(((unsigned long long)a.sites + 31) / 32);
+  const unsigned int nwarps = gridDim.x * L4_WARPS;
 
 
   for (unsigned int seg = 0; seg < a.nops; seg += a.seg)
@@ -718,10 +717,18 @@ __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
       if (threadIdx.x < 8) sts_u4(sops + (nseg * 2 + threadIdx.x) * 16, make_uint4(0, 0, 0, 0)); /* prefetch targets behind the last operation */
     }
     __syncthreads();
-    for (unsigned long long chunk = gwarp; chunk < nchunks; chunk += nwarps)
+    /* full rounds: a CTA takes L4_WARPS consecutive chunks; the last, partial round is dealt out warp-major over the
+     * CTAs (warp 0 of every CTA, then warp 1 ...) so that every SM keeps the same number of warps busy: with the
+     * plain stride the first CTAs ran a whole extra round at full occupancy while the other SMs idled (125 k sites
+     * per GPU = 1.65 rounds cost 2.0) */
+    const unsigned int full_end = (a.dbg & 8u) ? nchunks : nchunks - nchunks % nwarps;
+    for (unsigned int round0 = 0; round0 < nchunks; round0 += nwarps)
     {
-      const unsigned int s0 = (unsigned int)(chunk * 32) + (unsigned int)(lane >> 2) * 4;
-      if ((chunk + 1) * 32 <= a.sites)
+      const unsigned int chunk =
+        round0 + (round0 < full_end ? blockIdx.x * L4_WARPS + warp : warp * gridDim.x + blockIdx.x);
+      if (chunk >= nchunks) break;
+      const unsigned int s0 = chunk * 32u + (unsigned int)(lane >> 2) * 4;
+      if ((unsigned long long)(chunk + 1) * 32 <= a.sites)
         lean_chunk<true, SCORING>(a, sops, nseg, s0, lane, wsm);
       else
         lean_chunk_tail<TAG, SCORING>(a, sops, nseg, s0, lane, wsm);
@@ -795,11 +802,95 @@ bool lean_supported(const PartCtx * c)
          c->clv_stride * sizeof(double) < (1ull << 32) && c->scaler_stride * sizeof(unsigned int) < (1ull << 32);
 }
 
+/* A full traversal as independent sub-lists (trav_split_ops): a warp's walk over a whole list is one dependent chain
+ * of `count` operations (~1 us each), so a launch cannot finish faster than (rounds of chunks per warp) x that chain,
+ * however few warps the last round keeps busy: an 8-GPU shard of C2 (125 k sites = 1.65 rounds) paid 2.3 rounds.
+ * Here every CTA of launch 1 takes ONE sub-list (blockIdx.y; subtrees of at most `target` operations, nothing
+ * shared between them) for 8 chunks and the block scheduler deals CTAs out as others finish; launch 2 runs the few
+ * operations above the subtrees.  Reuses the batch kernel (one LeanArgs per blockIdx.y). */
+/* measured on one B200 (profiles/r02q_split_*.txt), kernel time of a full C2 traversal, single list -> split at 128:
+ * 125 k sites 4.57 -> 3.40 ms, 250 k 7.72 -> 6.71, 500 k 13.5 -> 13.0, 1 M 25.9 -> 26.0 (no gain: 13 rounds hide the chain) */
+int g_opt_trav_split = 128;      /* sub-list length; 0 = never split */
+int g_opt_trav_split_rounds = 8; /* split only when a resident warp would take fewer chunks than this */
+
+static bool launch_trav_dna4_split(PartCtx * c, const pll_operation_t * ops, unsigned int count, bool * done)
+{
+  pll_partition_t * p = &c->pub;
+  const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
+  static thread_local std::vector<pll_operation_t> ordered;
+  static thread_local std::vector<unsigned int> bounds;
+  static thread_local std::vector<LeanOp> lean, part;
+  static thread_local std::vector<LeanArgs> args;
+  *done = false;
+  const unsigned int target = std::min<unsigned int>((unsigned int)g_opt_trav_split, L4_SEG_MAX);
+  if (!trav_split_ops(ops, count, p->nodes, target, ordered, bounds)) return true;
+  const unsigned int nlists = (unsigned int)bounds.size() - 1; /* the last one is the top */
+  if (nlists < 2 || nlists - 1 > 65535u) return true;
+  lean.resize(count);
+  for (unsigned int l = 0; l < nlists; ++l)
+  {
+    const unsigned int b = bounds[l], n = bounds[l + 1] - b;
+    if (!trav_lean_resolve(ordered.data() + b, n, pattern_tip ? p->tips : 0, c->clv_first, std::min<unsigned int>(L4_SEG_MAX, n),
+                           g_opt_trav_stash, g_opt_trav_forward != 0, part, nullptr))
+    {
+      pllb200_set_error(PLL_ERROR_PARAM_INVALID, "Operation list cannot be packed (matrix index >= 2^24).");
+      return false;
+    }
+    std::copy(part.begin(), part.end(), lean.begin() + b);
+  }
+  if (!lean_set_smem_attr()) return false;
+  const LeanOp * d_ops = (const LeanOp *)dev_stage_small(c, lean.data(), sizeof(LeanOp) * count);
+  if (!d_ops) return false;
+  args.resize(nlists - 1);
+  unsigned int maxseg = 1;
+  for (unsigned int l = 0; l + 1 < nlists; ++l)
+  {
+    const unsigned int n = bounds[l + 1] - bounds[l];
+    const unsigned int seg = (n + 3u) & ~3u; /* keeps the per-warp blocks behind the records 128-byte aligned */
+    lean_fill_args(c, args[l], d_ops + bounds[l], n, seg);
+    maxseg = std::max(maxseg, seg);
+  }
+  /* read by every CTA: device memory, never the mapped host ring */
+  const LeanArgs * d_args = (const LeanArgs *)dev_stage(c, args.data(), sizeof(LeanArgs) * args.size());
+  if (!d_args) return false;
+  const unsigned long long nchunks = ((unsigned long long)c->sites_alloc + 31) / 32;
+  const unsigned long long bx = (nchunks + L4_WARPS - 1) / L4_WARPS;
+  if (bx > 0x7fffffffull) return true;
+  trav_dna4_batch_kernel<<<dim3((unsigned int)bx, nlists - 1), L4_WARPS * 32, lean_smem_bytes(maxseg), xstream(c)>>>(d_args);
+  ++g_kernel_launches;
+  if (!pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_batch_kernel (split) launch")) return false;
+  /* the top */
+  {
+    const unsigned int b = bounds[nlists - 1], n = count - b;
+    LeanArgs a;
+    const unsigned int seg = std::min<unsigned int>(L4_SEG_MAX, n);
+    lean_fill_args(c, a, d_ops + b, n, seg);
+    unsigned long long blocks = std::min<unsigned long long>(bx, (unsigned long long)c->sm_count * 2);
+    trav_dna4_kernel<<<(unsigned int)blocks, L4_WARPS * 32, lean_smem_bytes(seg), xstream(c)>>>(a);
+    ++g_kernel_launches;
+    if (!pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_kernel (top) launch")) return false;
+  }
+  *done = true;
+  return true;
+}
+
 bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int count)
 {
   pll_partition_t * p = &c->pub;
   const bool pattern_tip = (p->attributes & PLL_ATTRIB_PATTERN_TIP) != 0;
   static thread_local std::vector<LeanOp> lean;
+  const bool collect = batch_collects(BK_TRAV_DNA4);
+  if (!collect && g_opt_trav_split > 1 && count > 2u * (unsigned int)g_opt_trav_split)
+  {
+    const unsigned long long nwarps = (unsigned long long)c->sm_count * 2 * L4_WARPS;
+    const unsigned long long nchunks = ((unsigned long long)c->sites_alloc + 31) / 32;
+    if (nchunks < (unsigned long long)g_opt_trav_split_rounds * nwarps)
+    {
+      bool done = false;
+      if (!launch_trav_dna4_split(c, ops, count, &done)) return false;
+      if (done) return true;
+    }
+  }
   const unsigned int seg = std::min<unsigned int>(L4_SEG_MAX, count);
   if (!trav_lean_resolve(ops, count, pattern_tip ? p->tips : 0, c->clv_first, seg, g_opt_trav_stash,
                          g_opt_trav_forward != 0, lean, nullptr))
@@ -808,7 +899,6 @@ bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int cou
     return false;
   }
   if (!lean_set_smem_attr()) return false;
-  const bool collect = batch_collects(BK_TRAV_DNA4);
   const LeanOp * d_ops = collect ? (const LeanOp *)batch_pool_add(lean.data(), sizeof(LeanOp) * count)
                                  : (const LeanOp *)dev_stage_small(c, lean.data(), sizeof(LeanOp) * count);
   if (!d_ops) return false;

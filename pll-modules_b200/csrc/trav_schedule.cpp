@@ -29,12 +29,10 @@ void producer_reset(Scratch & s)
 }
 } // namespace
 
-bool trav_order_ops(const pll_operation_t * ops, unsigned int count, unsigned int nodes, bool by_need,
-                    std::vector<pll_operation_t> & out)
+/* Reads `ops` as an expression forest: producer (node -> op), consumer, subtree size and Sethi-Ullman label of
+ * every op.  False (producer[] reset) when the list is not such a forest.  On success the caller resets producer[]. */
+static bool forest_build(const pll_operation_t * ops, unsigned int count, unsigned int nodes, Scratch & s)
 {
-  out.clear();
-  if (count < 3) return false;
-  Scratch & s = t_s;
   if (s.producer.size() < nodes) s.producer.resize(nodes, -1);
   bool ok = true;
   for (unsigned int i = 0; i < count && ok; ++i)
@@ -82,45 +80,121 @@ bool trav_order_ops(const pll_operation_t * ops, unsigned int count, unsigned in
       s.need[i] = s.need[pc[0] >= 0 ? pc[0] : pc[1]];
     if (s.consumer[i] >= 0) s.size[s.consumer[i]] += s.size[i];
   }
-  out.reserve(count);
+  return true;
+}
+
+/* Appends the subtree of op `root` to `out`, depth-first, the child that needs more live values first (ties and
+ * !by_need: heavier subtree first).  With `cut_below` > 0 children whose subtree has at most that many ops are
+ * not entered (they belong to another list). */
+static void forest_emit(const pll_operation_t * ops, unsigned int nodes, bool by_need, Scratch & s, int root,
+                        int cut_below, std::vector<pll_operation_t> & out)
+{
   s.stack.clear();
-  for (unsigned int root = 0; root < count; ++root)
+  s.stack.push_back({root, 0});
+  while (!s.stack.empty())
   {
-    if (s.consumer[root] >= 0) continue;
-    s.stack.push_back({(int)root, 0});
-    while (!s.stack.empty())
+    auto & top = s.stack.back();
+    const int i = top.first;
+    if (top.second == 1)
     {
-      auto & top = s.stack.back();
-      const int i = top.first;
-      if (top.second == 1)
-      {
-        out.push_back(ops[i]);
-        s.stack.pop_back();
-        continue;
-      }
-      top.second = 1;
-      int ch[2] = {-1, -1};
-      const unsigned int cc[2] = {ops[i].child1_clv_index, ops[i].child2_clv_index};
-      for (int q = 0; q < 2; ++q)
-        if (cc[q] < nodes && s.producer[cc[q]] >= 0) ch[q] = s.producer[cc[q]];
-      int first = ch[0], second = ch[1];
-      if (first < 0)
-        std::swap(first, second);
-      else if (second >= 0)
-      {
-        const bool second_first = by_need && s.need[second] != s.need[first] ? s.need[second] > s.need[first]
-                                                                              : s.size[second] > s.size[first];
-        if (second_first) std::swap(first, second);
-      }
-      /* `first` is visited first => pushed last */
-      if (second >= 0) s.stack.push_back({second, 0});
-      if (first >= 0) s.stack.push_back({first, 0});
+      out.push_back(ops[i]);
+      s.stack.pop_back();
+      continue;
     }
+    top.second = 1;
+    int ch[2] = {-1, -1};
+    const unsigned int cc[2] = {ops[i].child1_clv_index, ops[i].child2_clv_index};
+    for (int q = 0; q < 2; ++q)
+      if (cc[q] < nodes && s.producer[cc[q]] >= 0 && s.size[s.producer[cc[q]]] > cut_below) ch[q] = s.producer[cc[q]];
+    int first = ch[0], second = ch[1];
+    if (first < 0)
+      std::swap(first, second);
+    else if (second >= 0)
+    {
+      const bool second_first = by_need && s.need[second] != s.need[first] ? s.need[second] > s.need[first]
+                                                                            : s.size[second] > s.size[first];
+      if (second_first) std::swap(first, second);
+    }
+    /* `first` is visited first => pushed last */
+    if (second >= 0) s.stack.push_back({second, 0});
+    if (first >= 0) s.stack.push_back({first, 0});
   }
+}
+
+bool trav_order_ops(const pll_operation_t * ops, unsigned int count, unsigned int nodes, bool by_need,
+                    std::vector<pll_operation_t> & out)
+{
+  out.clear();
+  if (count < 3) return false;
+  Scratch & s = t_s;
+  if (!forest_build(ops, count, nodes, s)) return false;
+  out.reserve(count);
+  for (unsigned int root = 0; root < count; ++root)
+    if (s.consumer[root] < 0) forest_emit(ops, nodes, by_need, s, (int)root, 0, out);
   producer_reset(s);
   if (out.size() != count)
   {
     out.clear();
+    return false;
+  }
+  return true;
+}
+
+bool trav_split_ops(const pll_operation_t * ops, unsigned int count, unsigned int nodes, unsigned int target,
+                    std::vector<pll_operation_t> & out, std::vector<unsigned int> & bounds)
+{
+  out.clear();
+  bounds.clear();
+  if (target < 2 || count <= target) return false;
+  Scratch & s = t_s;
+  if (!forest_build(ops, count, nodes, s)) return false;
+  /* maximal subtrees of at most `target` ops, largest first, first fit into lists of at most `target` ops */
+  std::vector<std::pair<int, int>> roots; /* (size, op) */
+  unsigned int ntop = 0;
+  for (unsigned int i = 0; i < count; ++i)
+  {
+    if (s.size[i] > (int)target)
+      ++ntop;
+    else if (s.consumer[i] < 0 || s.size[s.consumer[i]] > (int)target)
+      roots.push_back({s.size[i], (int)i});
+  }
+  if (ntop == 0)
+  {
+    producer_reset(s);
+    return false;
+  }
+  std::sort(roots.begin(), roots.end(), [](const std::pair<int, int> & a, const std::pair<int, int> & b) {
+    return a.first != b.first ? a.first > b.first : a.second < b.second;
+  });
+  std::vector<unsigned int> fill;
+  std::vector<std::vector<int>> bins;
+  for (const auto & r : roots)
+  {
+    size_t b = 0;
+    while (b < bins.size() && fill[b] + (unsigned int)r.first > target) ++b;
+    if (b == bins.size())
+    {
+      bins.emplace_back();
+      fill.push_back(0);
+    }
+    bins[b].push_back(r.second);
+    fill[b] += (unsigned int)r.first;
+  }
+  out.reserve(count);
+  bounds.push_back(0);
+  for (const auto & bin : bins)
+  {
+    for (int r : bin) forest_emit(ops, nodes, true, s, r, 0, out);
+    bounds.push_back((unsigned int)out.size());
+  }
+  for (unsigned int root = 0; root < count; ++root)
+    if (s.consumer[root] < 0 && s.size[root] > (int)target) forest_emit(ops, nodes, true, s, (int)root, (int)target, out);
+  bounds.push_back((unsigned int)out.size());
+  producer_reset(s);
+  if (out.size() != count)
+  {
+    out.clear();
+    bounds.clear();
     return false;
   }
   return true;
@@ -332,4 +406,17 @@ extern "C" int pllb200_debug_schedule(const pll_operation_t * ops, unsigned int 
   if (stats_out) memcpy(stats_out, &st, sizeof(st));
   if (ops_out) memcpy(ops_out, lean.data(), sizeof(LeanOp) * count);
   return 1;
+}
+
+/* CPU-testable entry of trav_split_ops: ops_out = the re-ordered pll_operation_t list, bounds_out[0..n] = list
+ * boundaries (the last list is the top).  Returns the number of lists, 0 when the list is not split. */
+extern "C" int pllb200_debug_split(const pll_operation_t * ops, unsigned int count, unsigned int nodes, unsigned int target,
+                                   pll_operation_t * ops_out, unsigned int * bounds_out, unsigned int max_bounds)
+{
+  std::vector<pll_operation_t> ordered;
+  std::vector<unsigned int> bounds;
+  if (!trav_split_ops(ops, count, nodes, target, ordered, bounds) || bounds.size() > max_bounds) return 0;
+  memcpy(ops_out, ordered.data(), sizeof(pll_operation_t) * count);
+  memcpy(bounds_out, bounds.data(), sizeof(unsigned int) * bounds.size());
+  return (int)bounds.size() - 1;
 }

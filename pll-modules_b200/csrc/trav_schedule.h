@@ -66,6 +66,14 @@ struct LeanStats
 bool trav_order_ops(const pll_operation_t * ops, unsigned int count, unsigned int nodes, bool by_need,
                     std::vector<pll_operation_t> & out);
 
+/* Cut a forest into INDEPENDENT lists: every maximal subtree of at most `target` operations goes whole into one
+ * of the first lists (first fit, largest first: lists of at most `target` operations that read nothing another of
+ * them writes), the operations above them form the last list (the "top"), which reads the subtree roots from
+ * global memory.  out = the lists back to back, each in Sethi-Ullman order; bounds = their boundaries (n + 1
+ * entries for n lists).  False when the list is not a forest or needs no cut (count <= target). */
+bool trav_split_ops(const pll_operation_t * ops, unsigned int count, unsigned int nodes, unsigned int target,
+                    std::vector<pll_operation_t> & out, std::vector<unsigned int> & bounds);
+
 /* Resolve `ops` (in execution order) into LeanOps.  `tips` = number of pattern tips (0 when tips own
  * CLVs), `seg_len` = operations staged per shared-memory segment (stash and forwarding do not cross a
  * segment), `slots` = stash slots (0..2).  Returns false when an index does not fit the packed format. */

@@ -149,6 +149,40 @@ def test_dna_stash_kernel_equals_the_round1_kernel_bit_for_bit(kw):
             assert np.array_equal(got[1][i], base[1][i]), (key, "clv", i)
 
 
+@pytest.mark.parametrize("kw,target", [
+    (dict(tips=300, sites=5000), 16),
+    (dict(tips=700, sites=2101), 64),                          # ragged last chunk, lists of several sizes
+    (dict(tips=1000, sites=1000), 128),
+    (dict(tips=200, sites=3000, brlen_scale=10.0), 8),         # scaling votes fire on both sides of a cut
+    (dict(tips=150, sites=777, seed=AMBIG | 5), 8),            # ambiguity codes: generic body
+], ids=lambda v: str(v) if isinstance(v, int) else "-".join("%s%s" % (k[:3], x) for k, x in v.items()))
+def test_dna_traversal_split_into_independent_sublists_is_bit_identical(kw, target):
+    """option trav_split: a full traversal as one launch over independent subtrees of at most `target` operations
+    (blockIdx.y = sub-list) + one launch for the operations above them writes exactly the CLVs, scaler counts and
+    logL of the single-list launch."""
+    pkg = load_product_package()
+    tips = kw["tips"]
+    out = {}
+    old_split, old_rounds = pkg.set_option("trav_split", 0), pkg.set_option("trav_split_rounds", 1 << 20)
+    try:
+        for split in (0, target):
+            pkg.set_option("trav_split", split)
+            pkg.reset_stats()
+            with Harness("b200", **kw) as h:
+                ll = h.loglh()
+                out[split] = (ll, [h.clv(tips + i).copy() for i in range(tips - 2)],
+                              [h.scaler(i).copy() for i in range(tips - 2)], pkg.stats()["kernel_launches"])
+    finally:
+        pkg.set_option("trav_split", old_split)
+        pkg.set_option("trav_split_rounds", old_rounds)
+    base, got = out[0], out[target]
+    assert got[3] == base[3] + 1, (got[3], base[3])          # the split really ran: one more launch
+    assert got[0] == base[0]
+    for i in range(tips - 2):
+        assert np.array_equal(got[2][i], base[2][i]), ("scaler", i)
+        assert np.array_equal(got[1][i], base[1][i]), ("clv", i)
+
+
 def test_dna_partial_traversals_are_bit_stable_when_a_warp_takes_several_chunks():
     """100 k sites = 3125 chunks for 2368 resident warps: warps of the persistent grid walk more than one chunk.
     A sequence of re-rootings + incremental evaluations (what an SPR round does) must give bit-identical logL on

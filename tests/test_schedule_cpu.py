@@ -155,3 +155,100 @@ def test_unordered_lists_keep_their_order_and_stay_correct():
     exp = expected(ops2, tips)
     for node in exp:
         assert got[node] == exp[node], node
+
+
+def split(ops, nodes, target):
+    lib = load_product_package().load()
+    lib.pllb200_debug_split.restype = C.c_int
+    lib.pllb200_debug_split.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_void_p, C.c_uint]
+    ops = np.ascontiguousarray(ops, dtype=np.int32)
+    out = np.zeros_like(ops)
+    bounds = np.zeros(len(ops) + 2, dtype=np.uint32)
+    n = lib.pllb200_debug_split(ops.ctypes.data, len(ops), nodes, target, out.ctypes.data, bounds.ctypes.data, len(bounds))
+    return out, bounds[:n + 1].tolist() if n else []
+
+
+@pytest.mark.parametrize("tips,seed,target", [(1000, 3, 128), (1000, 4, 64), (1000, 5, 256), (300, 6, 16), (2000, 7, 128),
+                                              (50, 8, 2)])
+def test_split_lists_are_independent_and_cover_the_forest(tips, seed, target):
+    """trav_split_ops: the first lists hold whole subtrees of at most `target` operations and may run in any order
+    (here: reversed) before the top list; every list is then resolved and replayed on its own, as the kernel does."""
+    ops, nodes = random_ops(tips, seed)
+    out, bounds = split(ops, nodes, target)
+    assert bounds and bounds[0] == 0 and bounds[-1] == len(ops)
+    assert sorted(out[:, 0].tolist()) == sorted(ops[:, 0].tolist())
+    lists = [out[bounds[i]:bounds[i + 1]] for i in range(len(bounds) - 1)]
+    assert all(0 < len(x) <= target for x in lists[:-1]), [len(x) for x in lists]
+    # no phase-1 list reads what another phase-1 list writes
+    for i, a in enumerate(lists[:-1]):
+        reads = set(a[:, 2].tolist()) | set(a[:, 5].tolist())
+        for j, b in enumerate(lists[:-1]):
+            if i != j:
+                assert not (reads & set(b[:, 0].tolist()))
+    # replay: phase-1 lists in reversed order, then the top, through one shared model of global memory
+    mem_order = list(reversed(lists[:-1])) + [lists[-1]]
+    flat = np.vstack(mem_order)
+    # a concatenation replayed with one segment per list = what the two launches do
+    got, exp = {}, expected(ops, tips)
+    mem, smem = {}, {}
+    for sub in mem_order:
+        lean, _ = schedule(sub, nodes, tips, 512, 2, reorder=0)
+        done = replay_shared(lean, tips, mem, smem)
+        got.update(done)
+    assert set(got) == set(exp) and len(flat) == len(ops)
+    for node in exp:
+        assert got[node] == exp[node], node
+    # the top list is small: the operations with more than `target` operations below them
+    if tips >= 1000:
+        assert len(lists[-1]) <= 6 * len(ops) // target, (len(lists[-1]), len(lists))
+
+
+def replay_shared(lean, tips, mem, smem):
+    """replay() of one list against a global-memory model shared with the lists that ran before."""
+    done = {}
+    stash = [None, None]
+    fw = None
+    for o in range(len(lean)):
+        p, c1, c2, ps, s1, s2, m1f, m2f = [int(v) for v in lean[o]]
+        fa, fb = m1f >> 24, m2f >> 24
+        m1, m2 = m1f & 0xFFFFFF, m2f & 0xFFFFFF
+        src = [fa & 3, (fa >> 3) & 3]
+        slot = [(fa >> 2) & 1, (fa >> 5) & 1]
+        ssrc = [fb & 3, (fb >> 2) & 3]
+        kids, scal = [], []
+        for q, (c, s) in enumerate(((c1, s1), (c2, s2))):
+            if src[q] == SRC_TIP:
+                kids.append(("tip", c))
+            elif src[q] == SRC_FWD:
+                assert fw is not None and fw[0] == c + tips
+                kids.append(("clv", fw[0]))
+            elif src[q] == SRC_STASH:
+                assert stash[slot[q]] is not None and stash[slot[q]][0] == c + tips
+                kids.append(("clv", stash[slot[q]][0]))
+            else:
+                kids.append(("clv", mem.get(c, ("ext", c + tips))))
+            if ssrc[q] == 0:
+                scal.append(None)
+            elif ssrc[q] == 1:
+                scal.append(smem.get(s, ("ext", s)))
+            else:
+                holder = fw if src[q] == SRC_FWD else stash[slot[q]]
+                assert holder is not None and holder[1] == s
+                scal.append(holder[0])
+        node = p + tips
+        has_ps = bool(fa & 0x40)
+        done[node] = (frozenset([(kids[0], m1, scal[0]), (kids[1], m2, scal[1])]), ps if has_ps else -1)
+        mem[p] = node
+        if has_ps:
+            smem[ps] = node
+        fw = (node, ps if has_ps else -2)
+        if fa & 0x80:
+            stash[(fb >> 4) & 1] = (node, ps if has_ps else -2)
+    return done
+
+
+def test_split_declines_short_lists_and_non_forests():
+    ops, nodes = random_ops(40, 9)
+    assert split(ops, nodes, 64)[1] == []          # nothing to cut
+    ops2 = np.vstack([ops, ops[:1]])               # a buffer written twice
+    assert split(ops2, nodes, 8)[1] == []
