@@ -243,7 +243,7 @@ bool dev_ctx_init(PartCtx * c)
     if (s == 4)
     {
       CUDA_TRY(cudaMalloc(&c->d_tipcols, (size_t)p->tips * c->tip_stride), false);
-      CUDA_TRY(cudaMemsetAsync(c->d_tipcols, 4, (size_t)p->tips * c->tip_stride, c->stream), false); /* code 15 = N */
+      CUDA_TRY(cudaMemsetAsync(c->d_tipcols, L4_TIPCOL_N, (size_t)p->tips * c->tip_stride, c->stream), false); /* code 15 = N */
     }
     CUDA_TRY(cudaMalloc(&c->d_tipmap, 256 * sizeof(unsigned long long)), false);
     CUDA_TRY(cudaMemsetAsync(c->d_tipmap, 0, 256 * sizeof(unsigned long long), c->stream), false);

@@ -278,6 +278,7 @@ bool launch_trav_dna(PartCtx * c, const pll_operation_t * ops, unsigned int coun
 bool lean_supported(const PartCtx * c);
 bool launch_trav_dna4(PartCtx * c, const pll_operation_t * ops, unsigned int count);
 bool flush_trav_dna4_lean(PartCtx * lead, const void * d_args, const BatchKind & k);
+#define L4_TIPCOL_N 32 /* column code of N in d_tipcols (tipcols_encode_kernel) */
 bool launch_tipcols_encode(PartCtx * c, unsigned int tip);
 bool launch_trav_dna4_score(PartCtx * c, const pll_operation_t * ops, const unsigned char * kind, const unsigned int * cand,
                             unsigned int count, unsigned int ncand, const unsigned int * params_indices, double * host_scores);

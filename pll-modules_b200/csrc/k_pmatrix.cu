@@ -63,7 +63,9 @@ __device__ __forceinline__ void pmatrix_dna_cols(const double * out, double * co
       v = out[i * sp + c];
     else
       v = ((out[i * sp] + out[i * sp + 1]) + out[i * sp + 2]) + out[i * sp + 3];
-    cols[(((size_t)m * 5 + c) * K + k) * 4 + i] = v;
+    /* odd columns keep rows 2-3 before rows 0-1 (shared-memory banks of the traversal kernel's lookups:
+     * tip_term, k_traversal_dna4.cu) */
+    cols[(((size_t)m * 5 + c) * K + k) * 4 + ((c & 1u) ? (i ^ 2u) : i)] = v;
   }
 }
 

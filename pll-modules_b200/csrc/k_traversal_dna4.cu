@@ -132,8 +132,14 @@ __device__ __forceinline__ void mbar_expect_u32(unsigned int bar, unsigned int b
 #define L4_THRESHOLD_HI 0x2FF00000
 __device__ __forceinline__ int hi_s(double x) { return __double2hiint(x); }
 
-/* term of a tip child for one element: column `b` of the staged table (b < 5), or — ambiguity codes other
- * than N, flagged 0x80 — the sum of the columns of the code's bits in state order */
+/* term of a tip child for one element.  `b` is the tip's column code (tipcols_encode_kernel): 16-byte offset of
+ * the code's column in the staged table, or — ambiguity codes other than N — 0x80 | code: the sum of the columns
+ * of the code's bits in state order.
+ * Bank conflicts: every column starts at the same bank, and a 16-byte shared-memory load is served a quarter warp
+ * (two site groups) at a time, so two groups with different codes collided on the banks of their category.  The
+ * odd columns (C, T) therefore hold their two halves in the opposite order (pmatrix_dna_cols) and the code's bit 0
+ * says so: rows 0-1 of an even column sit in banks 0-3 (+ 8 k), of an odd column in banks 4-7 — two groups only
+ * collide when their codes differ but have the same parity */
 template <bool SLOW>
 __device__ __forceinline__ void tip_term(unsigned int tab_k, unsigned int b, double (&t)[4])
 {
@@ -144,7 +150,7 @@ __device__ __forceinline__ void tip_term(unsigned int tab_k, unsigned int b, dou
     for (int j = 0; j < 4; ++j)
       if ((b >> j) & 1u)
       {
-        const double2 a = lds_d2(tab_k + j * 128), c = lds_d2(tab_k + j * 128 + 16);
+        const double2 a = lds_d2(tab_k + j * 128 + (j & 1) * 16), c = lds_d2(tab_k + j * 128 + 16 - (j & 1) * 16);
         t[0] += a.x;
         t[1] += a.y;
         t[2] += c.x;
@@ -152,7 +158,8 @@ __device__ __forceinline__ void tip_term(unsigned int tab_k, unsigned int b, dou
       }
     return;
   }
-  const double2 a = lds_d2(tab_k + b * 128), c = lds_d2(tab_k + b * 128 + 16);
+  const unsigned int p = tab_k + b * 16;
+  const double2 a = lds_d2(p), c = lds_d2(p ^ 16u); /* tab_k is a multiple of 32 */
   t[0] = a.x;
   t[1] = a.y;
   t[2] = c.x;
@@ -753,7 +760,8 @@ __global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_batch_kernel(const
 
 /* ---- tip column codes ---------------------------------------------------------------------------- */
 
-/* 4-bit DNA code -> column of the table: A C G T -> 0..3, N (all four) -> 4, anything else -> 0x80 | code */
+/* 4-bit DNA code -> 16-byte offset of its column in the table (column c at 128 c, odd columns with their halves
+ * exchanged: + 1): A C G T -> 0, 9, 16, 25, N (all four) -> 32, anything else -> 0x80 | code */
 __global__ void tipcols_encode_kernel(const unsigned char * __restrict__ src, unsigned char * __restrict__ dst, size_t n)
 {
   for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
@@ -763,10 +771,10 @@ __global__ void tipcols_encode_kernel(const unsigned char * __restrict__ src, un
     switch (c)
     {
       case 1: v = 0; break;
-      case 2: v = 1; break;
-      case 4: v = 2; break;
-      case 8: v = 3; break;
-      case 15: v = 4; break;
+      case 2: v = 9; break;
+      case 4: v = 16; break;
+      case 8: v = 25; break;
+      case 15: v = L4_TIPCOL_N; break;
       default: v = (unsigned char)(0x80u | c); break;
     }
     dst[i] = v;
