@@ -645,6 +645,14 @@ void h_op_type_counts(void * hv, unsigned int p, unsigned int nops, unsigned int
   }
 }
 
+/* the operation list of the last traversal (8 ints per operation, pll_operation_t order); returns what fits */
+unsigned int h_get_operations(void * hv, unsigned int nops, int * out)
+{
+  harness_t * h = (harness_t *)hv;
+  memcpy(out, h->ti->operations, (size_t)nops * sizeof(pll_operation_t));
+  return nops;
+}
+
 /* ---- scalar optimisers --------------------------------------------------- */
 
 /* analytic objectives so that Brent / L-BFGS-B / EM can be compared between the two libraries

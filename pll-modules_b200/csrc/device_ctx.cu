@@ -165,7 +165,7 @@ bool dev_ctx_init(PartCtx * c)
   c->eigen_stride = (size_t)2 * s * sp + 2 * sp;
 
   c->d_clv = nullptr; c->d_scaler = nullptr; c->d_pmat = nullptr; c->d_pmat_il = nullptr; c->d_tiptab = nullptr; c->tiptab_stale = false;
-  c->d_pmat_cols = nullptr; c->d_tipcols = nullptr;
+  c->d_pmat_cols = nullptr; c->d_tipcols = nullptr; c->d_split_tickets = nullptr;
   c->d_tipchars = nullptr; c->d_weights = nullptr; c->d_invariant = nullptr; c->d_eigen = nullptr;
   c->d_tipmap = nullptr; c->d_persite = nullptr; c->d_ancestral = nullptr; c->d_brlen = nullptr; c->d_sumfrag = nullptr;
   c->d_multi = nullptr; c->multi_cap = 0; c->ev_batch = nullptr;
@@ -221,6 +221,9 @@ bool dev_ctx_init(PartCtx * c)
       const size_t cbytes = (size_t)(p->prob_matrices + c->scratch_mats) * 5 * K * 4 * sizeof(double);
       CUDA_TRY(cudaMalloc(&c->d_pmat_cols, cbytes), false);
       CUDA_TRY(cudaMemsetAsync(c->d_pmat_cols, 0, cbytes, c->stream), false);
+      const size_t tbytes = ((size_t)c->sites_alloc / 256 + 1) * sizeof(unsigned int);
+      CUDA_TRY(cudaMalloc(&c->d_split_tickets, tbytes), false);
+      CUDA_TRY(cudaMemsetAsync(c->d_split_tickets, 0, tbytes, c->stream), false);
     }
     else if (s == 20)
     {
@@ -290,7 +293,7 @@ void dev_ctx_destroy(PartCtx * c)
   for (auto & kv : c->sumtables) cudaFree(kv.second);
   c->sumtables.clear();
   cudaFree(c->d_clv); cudaFree(c->d_scaler); cudaFree(c->d_pmat); cudaFree(c->d_pmat_il); cudaFree(c->d_tiptab);
-  cudaFree(c->d_pmat_cols); cudaFree(c->d_tipcols); cudaFree(c->d_score);
+  cudaFree(c->d_pmat_cols); cudaFree(c->d_tipcols); cudaFree(c->d_split_tickets); cudaFree(c->d_score);
   if (c->h_score) cudaFreeHost(c->h_score);
   cudaFree(c->d_tipchars); cudaFree(c->d_weights); cudaFree(c->d_invariant); cudaFree(c->d_eigen);
   cudaFree(c->d_tipmap); cudaFree(c->d_persite); cudaFree(c->d_ancestral); cudaFree(c->d_brlen); cudaFree(c->d_sumfrag); cudaFree(c->d_sumgen);

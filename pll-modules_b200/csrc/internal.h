@@ -60,6 +60,7 @@ struct PartCtx
   /* 4 states: per matrix the five column sums a DNA tip code selects, [m][A C G T N][cat k][row i] — what a tip
    * child contributes to a parent, read by table lookup in k_traversal_dna4.cu */
   double * d_pmat_cols;
+  unsigned int * d_split_tickets; /* one counter per group of 8 chunks (trav_dna4_split_kernel), zero between launches */
   unsigned char * d_tipcols;  /* twin of d_tipchars (4 states + tip patterns): column number of every code */
   /* 20 states + tip patterns: per matrix the products P x (tip state vector) of every tip code,
    * [prob_matrices][code 24][k][20] — the same K*480 doubles per matrix as the fragment image, so a tip

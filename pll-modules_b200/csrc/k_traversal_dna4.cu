@@ -33,6 +33,7 @@
 #include "trav_schedule.h"
 
 #include <algorithm>
+#include <atomic>
 
 struct LeanArgs
 {
@@ -701,8 +702,10 @@ __device__ __noinline__ void lean_chunk_tail(const LeanArgs & a, unsigned int so
   lean_chunk<false, SCORING>(a, sops, nseg, s0, lane, wsm);
 }
 
+/* bid / nblk: this CTA's number among the CTAs that share the chunks of one list (blockIdx.x / gridDim.x everywhere
+ * but in the sub-list kernel below) */
 template <int TAG, bool SCORING>
-__device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
+__device__ __forceinline__ void trav_dna4_body(const LeanArgs & a, const unsigned int bid, const unsigned int nblk)
 {
   extern __shared__ __align__(128) unsigned char l4_smem[];
   const int lane = threadIdx.x & 31;
@@ -711,7 +714,7 @@ __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
   const unsigned int sops = sm0;
   const unsigned int wsm = sm0 + (a.seg + 4) * 32 + warp * L4_WARP_SM; /* + the zero record, 128-byte aligned */
   const unsigned int nchunks = (unsigned int)(((unsigned long long)a.sites + 31) / 32);
-  const unsigned int nwarps = gridDim.x * L4_WARPS;
+  const unsigned int nwarps = nblk * L4_WARPS;
 
 
   for (unsigned int seg = 0; seg < a.nops; seg += a.seg)
@@ -732,7 +735,7 @@ __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
     for (unsigned int round0 = 0; round0 < nchunks; round0 += nwarps)
     {
       const unsigned int chunk =
-        round0 + (round0 < full_end ? blockIdx.x * L4_WARPS + warp : warp * gridDim.x + blockIdx.x);
+        round0 + (round0 < full_end ? bid * L4_WARPS + warp : warp * nblk + bid);
       if (chunk >= nchunks) break;
       const unsigned int s0 = chunk * 32u + (unsigned int)(lane >> 2) * 4;
       if ((unsigned long long)(chunk + 1) * 32 <= a.sites)
@@ -743,9 +746,9 @@ __device__ __forceinline__ void trav_dna4_body(const LeanArgs & a)
   }
 }
 
-__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_kernel(LeanArgs a) { trav_dna4_body<0, false>(a); }
+__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_kernel(LeanArgs a) { trav_dna4_body<0, false>(a, blockIdx.x, gridDim.x); }
 /* the same kernel with the SETUP / SCORE bodies of the batched regraft scoring (lean_op_special) */
-__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_score_kernel(LeanArgs a) { trav_dna4_body<2, true>(a); }
+__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_score_kernel(LeanArgs a) { trav_dna4_body<2, true>(a, blockIdx.x, gridDim.x); }
 
 /* many partitions in one launch (blockIdx.y = partition; batch mode, internal.h) */
 __global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_batch_kernel(const LeanArgs * __restrict__ arr)
@@ -755,7 +758,45 @@ __global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_batch_kernel(const
     reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + blockIdx.y)[i];
   __syncthreads();
   const LeanArgs a = sa;
-  trav_dna4_body<1, false>(a);
+  trav_dna4_body<1, false>(a, blockIdx.x, gridDim.x);
+}
+
+/* One full traversal as independent sub-lists + the operations above them, in ONE launch (launch_trav_dna4_split):
+ * blockIdx.x = sub-list (arr[0 .. nsub-1]), blockIdx.y = group of L4_WARPS chunks.  A CTA walks its sub-list for its
+ * group and takes a ticket of the group; the CTA that takes the last one finds every subtree root of the group in
+ * global memory and walks the top list (arr[nsub]) for it right away, while other CTAs still work on sub-lists of other
+ * groups — the short, latency-bound top chains hide between them instead of forming a sparse second launch.
+ * tickets[gridDim.y] are zero at launch and zero again at exit. */
+__global__ void __launch_bounds__(L4_WARPS * 32, 2) trav_dna4_split_kernel(const LeanArgs * __restrict__ arr, unsigned int nsub,
+                                                                          unsigned int * __restrict__ tickets)
+{
+  __shared__ LeanArgs sa;
+  __shared__ unsigned int s_last;
+  unsigned int which = blockIdx.x;
+  for (int phase = 0; phase < 2; ++phase)
+  {
+    __syncthreads();
+    for (unsigned int i = threadIdx.x; i < sizeof(LeanArgs) / 4; i += blockDim.x)
+      reinterpret_cast<unsigned int *>(&sa)[i] = reinterpret_cast<const unsigned int *>(arr + which)[i];
+    __syncthreads();
+    {
+      const LeanArgs a = sa;
+      trav_dna4_body<3, false>(a, blockIdx.y, gridDim.y);
+    }
+    if (phase) break;
+    __threadfence(); /* this thread's CLV and scaler stores are visible device-wide before the ticket is */
+    __syncthreads();
+    if (threadIdx.x == 0)
+    {
+      const unsigned int t = atomicAdd(tickets + blockIdx.y, 1u);
+      s_last = t + 1 == nsub;
+      if (s_last) tickets[blockIdx.y] = 0;
+    }
+    __syncthreads();
+    if (!s_last) break;
+    __threadfence(); /* ... and the other CTAs' stores before this CTA's loads */
+    which = nsub;
+  }
 }
 
 /* ---- tip column codes ---------------------------------------------------------------------------- */
@@ -813,13 +854,18 @@ bool lean_supported(const PartCtx * c)
 /* A full traversal as independent sub-lists (trav_split_ops): a warp's walk over a whole list is one dependent chain
  * of `count` operations (~1 us each), so a launch cannot finish faster than (rounds of chunks per warp) x that chain,
  * however few warps the last round keeps busy: an 8-GPU shard of C2 (125 k sites = 1.65 rounds) paid 2.3 rounds.
- * Here every CTA of launch 1 takes ONE sub-list (blockIdx.y; subtrees of at most `target` operations, nothing
- * shared between them) for 8 chunks and the block scheduler deals CTAs out as others finish; launch 2 runs the few
- * operations above the subtrees.  Reuses the batch kernel (one LeanArgs per blockIdx.y). */
-/* measured on one B200 (profiles/r02q_split_*.txt), kernel time of a full C2 traversal, single list -> split at 128:
- * 125 k sites 4.57 -> 3.40 ms, 250 k 7.72 -> 6.71, 500 k 13.5 -> 13.0, 1 M 25.9 -> 26.0 (no gain: 13 rounds hide the chain) */
+ * Here a CTA takes ONE sub-list (subtrees of at most `target` operations, nothing shared between sub-lists) for 8
+ * chunks, the block scheduler deals CTAs out as others finish, and the CTA that completes a group of chunks walks the
+ * operations above the subtrees for it (trav_dna4_split_kernel). */
+/* measured on one B200 (profiles/r02q_split_sweep.txt, r02v_split_fused.txt), kernel time of a full C2 traversal, single
+ * list -> sub-lists of 128: 125 k sites 4.49 -> 3.44 ms, 250 k 7.57 -> 6.77, 500 k 12.8 -> 13.05 and 1 M 25.4 -> 26.6
+ * (worse: many rounds hide the chain, and the top's operations read their children from DRAM) */
 int g_opt_trav_split = 128;      /* sub-list length; 0 = never split */
-int g_opt_trav_split_rounds = 8; /* split only when a resident warp would take fewer chunks than this */
+int g_opt_trav_split_rounds = 4; /* split only when a resident warp would take fewer chunks than this (~300 k sites) */
+
+static std::atomic<unsigned long long> g_split_launches{0};
+/* tests: how many traversals ran as sub-lists so far */
+extern "C" unsigned long long pllb200_debug_split_launches(void) { return g_split_launches.load(); }
 
 static bool launch_trav_dna4_split(PartCtx * c, const pll_operation_t * ops, unsigned int count, bool * done)
 {
@@ -833,7 +879,7 @@ static bool launch_trav_dna4_split(PartCtx * c, const pll_operation_t * ops, uns
   const unsigned int target = std::min<unsigned int>((unsigned int)g_opt_trav_split, L4_SEG_MAX);
   if (!trav_split_ops(ops, count, p->nodes, target, ordered, bounds)) return true;
   const unsigned int nlists = (unsigned int)bounds.size() - 1; /* the last one is the top */
-  if (nlists < 2 || nlists - 1 > 65535u) return true;
+  if (nlists < 2 || !c->d_split_tickets) return true;
   lean.resize(count);
   for (unsigned int l = 0; l < nlists; ++l)
   {
@@ -849,35 +895,28 @@ static bool launch_trav_dna4_split(PartCtx * c, const pll_operation_t * ops, uns
   if (!lean_set_smem_attr()) return false;
   const LeanOp * d_ops = (const LeanOp *)dev_stage_small(c, lean.data(), sizeof(LeanOp) * count);
   if (!d_ops) return false;
-  args.resize(nlists - 1);
+  const unsigned long long nchunks = ((unsigned long long)c->sites_alloc + 31) / 32;
+  const unsigned long long groups = (nchunks + L4_WARPS - 1) / L4_WARPS;
+  if (groups > 65535ull) return true; /* gridDim.y */
+  args.resize(nlists);
   unsigned int maxseg = 1;
-  for (unsigned int l = 0; l + 1 < nlists; ++l)
+  for (unsigned int l = 0; l < nlists; ++l)
   {
     const unsigned int n = bounds[l + 1] - bounds[l];
-    const unsigned int seg = (n + 3u) & ~3u; /* keeps the per-warp blocks behind the records 128-byte aligned */
+    const unsigned int seg = std::min<unsigned int>(L4_SEG_MAX, (n + 3u) & ~3u); /* keeps the per-warp blocks behind the records 128-byte aligned */
     lean_fill_args(c, args[l], d_ops + bounds[l], n, seg);
     maxseg = std::max(maxseg, seg);
   }
   /* read by every CTA: device memory, never the mapped host ring */
   const LeanArgs * d_args = (const LeanArgs *)dev_stage(c, args.data(), sizeof(LeanArgs) * args.size());
   if (!d_args) return false;
-  const unsigned long long nchunks = ((unsigned long long)c->sites_alloc + 31) / 32;
-  const unsigned long long bx = (nchunks + L4_WARPS - 1) / L4_WARPS;
-  if (bx > 0x7fffffffull) return true;
-  trav_dna4_batch_kernel<<<dim3((unsigned int)bx, nlists - 1), L4_WARPS * 32, lean_smem_bytes(maxseg), xstream(c)>>>(d_args);
+  if (!pllb200_cuda_ok(cudaMemsetAsync(c->d_split_tickets, 0, sizeof(unsigned int) * groups, xstream(c)), "split tickets"))
+    return false;
+  trav_dna4_split_kernel<<<dim3(nlists - 1, (unsigned int)groups), L4_WARPS * 32, lean_smem_bytes(maxseg), xstream(c)>>>(
+      d_args, nlists - 1, c->d_split_tickets);
   ++g_kernel_launches;
-  if (!pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_batch_kernel (split) launch")) return false;
-  /* the top */
-  {
-    const unsigned int b = bounds[nlists - 1], n = count - b;
-    LeanArgs a;
-    const unsigned int seg = std::min<unsigned int>(L4_SEG_MAX, n);
-    lean_fill_args(c, a, d_ops + b, n, seg);
-    unsigned long long blocks = std::min<unsigned long long>(bx, (unsigned long long)c->sm_count * 2);
-    trav_dna4_kernel<<<(unsigned int)blocks, L4_WARPS * 32, lean_smem_bytes(seg), xstream(c)>>>(a);
-    ++g_kernel_launches;
-    if (!pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_kernel (top) launch")) return false;
-  }
+  ++g_split_launches;
+  if (!pllb200_cuda_ok(cudaGetLastError(), "trav_dna4_split_kernel launch")) return false;
   *done = true;
   return true;
 }
@@ -978,7 +1017,9 @@ static bool lean_set_smem_attr()
       !pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
                        "trav_dna4_batch_kernel smem") ||
       !pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_score_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
-                       "trav_dna4_score_kernel smem"))
+                       "trav_dna4_score_kernel smem") ||
+      !pllb200_cuda_ok(cudaFuncSetAttribute(trav_dna4_split_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, maxb),
+                       "trav_dna4_split_kernel smem"))
     return false;
   attr_set = true;
   return true;

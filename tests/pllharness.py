@@ -119,6 +119,7 @@ def _lib(kind):
         lib.h_treeinfo.argtypes = [C.c_void_p]
         lib.h_set_reduce_cb.argtypes = [C.c_void_p, C.c_void_p, REDUCE_CB]
         lib.h_op_type_counts.argtypes = [C.c_void_p, C.c_uint, C.c_uint, C.c_void_p]
+        lib.h_get_operations.argtypes = [C.c_void_p, C.c_uint, C.c_void_p]
         lib.h_ops_counter.restype = C.c_uint
         lib.h_ops_counter.argtypes = [C.c_void_p]
         lib.h_test_brent.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, C.c_void_p]
@@ -466,6 +467,12 @@ class Harness:
         out = np.zeros(3, dtype=np.uint32)
         self.lib.h_op_type_counts(self.h, p, self.tips - 2, out.ctypes.data)
         return dict(tt=int(out[0]), ti=int(out[1]), ii=int(out[2]))
+
+    def operations(self, nops):
+        """pll_operation_t rows of the last traversal (after loglh(0): tips - 2 of them)."""
+        out = np.zeros((nops, 8), dtype=np.int32)
+        self.lib.h_get_operations(self.h, nops, out.ctypes.data)
+        return out
 
     def ops_counter(self):
         return self.lib.h_ops_counter(self.h)

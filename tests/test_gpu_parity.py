@@ -5,6 +5,7 @@
 Tolerances (BASELINE.json north_star): logL 1e-8 relative, derivatives 1e-6 relative (absolute floor
 1e-9 where |value| < 1e-3), scaler counts exact away from the 2^-256 threshold.
 """
+import ctypes as C
 import json
 import os
 
@@ -157,26 +158,28 @@ def test_dna_stash_kernel_equals_the_round1_kernel_bit_for_bit(kw):
     (dict(tips=150, sites=777, seed=AMBIG | 5), 8),            # ambiguity codes: generic body
 ], ids=lambda v: str(v) if isinstance(v, int) else "-".join("%s%s" % (k[:3], x) for k, x in v.items()))
 def test_dna_traversal_split_into_independent_sublists_is_bit_identical(kw, target):
-    """option trav_split: a full traversal as one launch over independent subtrees of at most `target` operations
-    (blockIdx.y = sub-list) + one launch for the operations above them writes exactly the CLVs, scaler counts and
-    logL of the single-list launch."""
+    """option trav_split: a full traversal as independent subtrees of at most `target` operations (blockIdx.x =
+    sub-list) whose last finisher per group of chunks walks the operations above them, in one launch, writes exactly
+    the CLVs, scaler counts and logL of the single-list launch."""
     pkg = load_product_package()
+    lib = pkg.load()
     tips = kw["tips"]
     out = {}
     old_split, old_rounds = pkg.set_option("trav_split", 0), pkg.set_option("trav_split_rounds", 1 << 20)
     try:
         for split in (0, target):
             pkg.set_option("trav_split", split)
-            pkg.reset_stats()
+            lib.pllb200_debug_split_launches.restype = C.c_ulonglong
+            before = lib.pllb200_debug_split_launches()
             with Harness("b200", **kw) as h:
                 ll = h.loglh()
                 out[split] = (ll, [h.clv(tips + i).copy() for i in range(tips - 2)],
-                              [h.scaler(i).copy() for i in range(tips - 2)], pkg.stats()["kernel_launches"])
+                              [h.scaler(i).copy() for i in range(tips - 2)], lib.pllb200_debug_split_launches() - before)
     finally:
         pkg.set_option("trav_split", old_split)
         pkg.set_option("trav_split_rounds", old_rounds)
     base, got = out[0], out[target]
-    assert got[3] == base[3] + 1, (got[3], base[3])          # the split really ran: one more launch
+    assert got[3] == 1 and base[3] == 0, (got[3], base[3])   # the split really ran
     assert got[0] == base[0]
     for i in range(tips - 2):
         assert np.array_equal(got[2][i], base[2][i]), ("scaler", i)
