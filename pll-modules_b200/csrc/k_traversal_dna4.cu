@@ -666,13 +666,19 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
   __syncwarp();
   lean_prefetch<FULL>(a, L, sops, 0, t1, t2);
 
-  /* the loop variable is the record's shared-memory address (records are 32 bytes: bit 5 = stage) */
-  const unsigned int rec_end = sops + nseg * 32;
-  for (unsigned int rec = sops; rec != rec_end; rec += 32)
+  /* The loop variable is the record's shared-memory address (records are 32 bytes: bit 5 = stage).  There is no
+   * trip count: the record behind the last operation is all zero (no real operation has parent row = child rows =
+   * 0) and decodes to the generic type, whose branch leaves the loop.  [With `rec != rec_end` ptxas evaluated the
+   * test at the top of an iteration and kept the predicate in LOCAL memory across the body — every predicate
+   * register is in use —, and its reload behind the body's stores took 19 % of the kernel's stall samples
+   * (profiles/r02u_trav_dna4_stalls_by_sass.txt); a test pinned behind the body reloaded `nseg` instead.] */
+  (void)nseg;
+  for (unsigned int rec = sops;; rec += 32)
   {
     const unsigned int st = ((rec - sops) >> 5) & 1u;
     __syncwarp(); /* every lane is done with stage st^1 (previous operation): the bodies refill it for the next one */
-    unsigned int type = LOPB_TYPE(lds_u1(rec + 28) >> 24);
+    const unsigned int m2f = lds_u1(rec + 28);
+    unsigned int type = LOPB_TYPE(m2f >> 24);
     if (!(SCORING && type == LTYPE_SPECIAL) && (!FULL || __any_sync(0xffffffffu, ((t1 | t2) & 0x80808080u) != 0u)))
       type = 0; /* partial chunk, or ambiguity codes: generic body */
     switch (type)
@@ -686,9 +692,17 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
       case LTYPE_SPECIAL:
         if (SCORING) lean_op_special<FULL>(a, L, rec, st, acc, fsc, t1, t2); /* only the scoring kernel carries this body */
         break;
-      default: lean_op_generic<FULL>(a, L, rec, st, acc, fsc, t1, t2); break;
+      default:
+        if (m2f == 0u)
+        {
+          const uint4 z = lds_u4(rec);
+          if ((z.x | z.y | z.z) == 0u) goto list_done;
+        }
+        lean_op_generic<FULL>(a, L, rec, st, acc, fsc, t1, t2);
+        break;
     }
   }
+list_done:
   /* the last operation prefetched the zero record behind the segment: that copy must have landed before the
    * next chunk's first copies go into the same stage (copies of different groups may land in any order) */
   cp_async_wait0();

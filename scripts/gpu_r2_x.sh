@@ -1,0 +1,6 @@
+#!/bin/bash
+O=gpurun_out/r02x; mkdir -p $O
+cp pll-modules_b200/lib/libpll_b200.sent pll-modules_b200/lib/libpll_b200.so
+timeout 900 python -m pytest tests/test_gpu_parity.py -x -q -m gpu -k "golden or clvs_scalers or stash_kernel or split_into or bit_stable or ambiguity or c2_full or spr_round or c5_slice or partial_trav or multi_partition or c4" > $O/pytest.log 2>&1; tail -3 $O/pytest.log
+bash scripts/gpu_r2_s.sh base sent
+cp pll-modules_b200/lib/libpll_b200.sent pll-modules_b200/lib/libpll_b200.so
