@@ -57,6 +57,11 @@ struct LeanArgs
 };
 
 #define L4_WARPS 8
+#ifndef L4_TIP_AHEAD
+/* tip codes are requested this many operations before their use (1 or 2).  2 was measured: the two extra live
+ * registers make ptxas park an in-flight load result in local memory (STL waits for the load): 32.1 vs 24.9 ms at C2 */
+#define L4_TIP_AHEAD 1
+#endif
 #define L4_SEG_MAX 512
 #define L4_STASH_B 4096u
 #define L4_WARP_SM (2 * L4_STASH_B + 2 * 128 + 2 * 2 * 640 + 16 + 112) /* stash | scaler stash | matrices | barriers | pad -> 11136 */
@@ -260,10 +265,10 @@ __device__ __forceinline__ uint4 lean_load_scalers(const LeanArgs & a, const Lan
  * it can be scheduled into the arithmetic of the current operation.  [A per-warp TMA bulk copy cost ~80 issue
  * slots per operation: address set-up plus the elect / R2UR sequence around each UBLKCP.] */
 template <bool FULL>
-__device__ __forceinline__ void lean_prefetch(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
-                                              unsigned int & n1, unsigned int & n2)
+__device__ __forceinline__ void lean_prefetch(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int rec_tip,
+                                              unsigned int st, unsigned int & n1, unsigned int & n2)
 {
-  const uint4 x0 = lds_u4(rec), x1 = lds_u4(rec + 16);
+  const uint4 x1 = lds_u4(rec + 16);
   const unsigned int fn = x1.z >> 24;
   const bool t1 = LOPA_SRC1(fn) == SRC_TIP, t2 = LOPA_SRC2(fn) == SRC_TIP;
   const char * cols = reinterpret_cast<const char *>(a.pmat_cols) + L.lane * 16;
@@ -276,11 +281,35 @@ __device__ __forceinline__ void lean_prefetch(const LeanArgs & a, const LaneCtx 
   if (t1 && L.lane < 8) cp_async16(dst + 512, g1 + 512);
   if (t2 && L.lane < 8) cp_async16(dst + 640 + 512, g2 + 512);
   cp_async_commit();
+  /* tip codes: of the operation at rec_tip (L4_TIP_AHEAD operations ahead) */
+  const uint4 y0 = lds_u4(rec_tip);
+  const unsigned int ft = L4_TIP_AHEAD == 1 ? fn : lds_u1(rec_tip + 24) >> 24;
   n1 = 0;
   n2 = 0;
-  if (t1) n1 = lean_load_tips<FULL>(a, L, x0.y);
-  if (t2) n2 = lean_load_tips<FULL>(a, L, x0.z);
+  if (LOPA_SRC1(ft) == SRC_TIP) n1 = lean_load_tips<FULL>(a, L, y0.y);
+  if (LOPA_SRC2(ft) == SRC_TIP) n2 = lean_load_tips<FULL>(a, L, y0.z);
 }
+
+/* tip column codes in flight: of the current operation (t) and, with L4_TIP_AHEAD == 2, of the next one (u) */
+struct TipQ
+{
+  unsigned int t1, t2, u1, u2;
+  __device__ __forceinline__ void advance(unsigned int n1, unsigned int n2)
+  {
+    if (L4_TIP_AHEAD == 1)
+    {
+      t1 = n1;
+      t2 = n2;
+    }
+    else
+    {
+      t1 = u1;
+      t2 = u2;
+      u1 = n1;
+      u2 = n2;
+    }
+  }
+};
 
 /* underflow scaling vote (core_partials.c:729-763; never for tip-tip: :185-186), scaler counts, global store,
  * stash.  sc: sum of the children's counts (sc lanes).  w0 = {p, c1, c2, ps}. */
@@ -402,12 +431,13 @@ __device__ __forceinline__ void lean_tip_multiply(unsigned int tab, unsigned int
  * full chunk; no ambiguity code other than N in the tip codes (checked here: `slow` runs the generic body). */
 template <int SRC1, int SRC2>
 __device__ __forceinline__ void lean_op_hot(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
-                                            double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+                                            double (&acc)[4][4], uint4 & fsc, TipQ & q)
 {
   const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
   const unsigned int fa = w1.z >> 24, fb = w1.w >> 24;
   unsigned int n1, n2;
-  lean_prefetch<true>(a, L, rec + 32, st ^ 1u, n1, n2);
+  lean_prefetch<true>(a, L, rec + 32, rec + 32 * L4_TIP_AHEAD, st ^ 1u, n1, n2);
+  const unsigned int t1 = q.t1, t2 = q.t2;
 
   uint4 q1 = make_uint4(0, 0, 0, 0), q2 = make_uint4(0, 0, 0, 0);
   if (L.sc_lane())
@@ -466,8 +496,7 @@ __device__ __forceinline__ void lean_op_hot(const LeanArgs & a, const LaneCtx & 
 
   const uint4 sc = make_uint4(q1.x + q2.x, q1.y + q2.y, q1.z + q2.z, q1.w + q2.w);
   lean_finish<true, SRC1 == SRC_TIP && SRC2 == SRC_TIP>(a, L, w0, fa | LOPA_PS, fb, acc, sc, fsc);
-  t1 = n1;
-  t2 = n2;
+  q.advance(n1, n2);
 }
 
 /* both child terms of an operation whose sources are read at run time: acc <- (M2 x child2) * (M1 x child1),
@@ -552,20 +581,20 @@ __device__ __forceinline__ void lean_children_generic(const LeanArgs & a, const 
 /* any operation: sources, scaler sources and flags read at run time */
 template <bool FULL>
 __device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
-                                                double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+                                                double (&acc)[4][4], uint4 & fsc, TipQ & q)
 {
   const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
   const unsigned int fa = w1.z >> 24, fb = w1.w >> 24;
   unsigned int n1, n2;
-  lean_prefetch<FULL>(a, L, rec + 32, st ^ 1u, n1, n2);
+  lean_prefetch<FULL>(a, L, rec + 32, rec + 32 * L4_TIP_AHEAD, st ^ 1u, n1, n2);
+  const unsigned int t1 = q.t1, t2 = q.t2;
   uint4 sc;
   lean_children_generic<FULL>(a, L, w0, w1, st, (fa & LOPA_PS) && L.sc_lane(), false, acc, fsc, t1, t2, sc);
   if (LOPA_SRC1(fa) == SRC_TIP && LOPA_SRC2(fa) == SRC_TIP)
     lean_finish<FULL, true>(a, L, w0, fa, fb, acc, sc, fsc);
   else
     lean_finish<FULL, false>(a, L, w0, fa, fb, acc, sc, fsc);
-  t1 = n1;
-  t2 = n2;
+  q.advance(n1, n2);
 }
 
 /* The two operations of a batched regraft scoring list (algo_search.cpp, pllmod_algo_spr_round: every candidate
@@ -580,11 +609,12 @@ __device__ __forceinline__ void lean_op_generic(const LeanArgs & a, const LaneCt
  *     enter the log term; 2^-768 is still a normal double), which changes nothing mathematically. */
 template <bool FULL>
 __device__ __forceinline__ void lean_op_special(const LeanArgs & a, const LaneCtx & L, unsigned int rec, unsigned int st,
-                                                double (&acc)[4][4], uint4 & fsc, unsigned int & t1, unsigned int & t2)
+                                                double (&acc)[4][4], uint4 & fsc, TipQ & q)
 {
   const uint4 w0 = lds_u4(rec), w1 = lds_u4(rec + 16);
   unsigned int n1, n2;
-  lean_prefetch<FULL>(a, L, rec + 32, st ^ 1u, n1, n2);
+  lean_prefetch<FULL>(a, L, rec + 32, rec + 32 * L4_TIP_AHEAD, st ^ 1u, n1, n2);
+  const unsigned int t1 = q.t1, t2 = q.t2;
   const bool setup = w0.x == LSPECIAL_SETUP;
   uint4 sc;
   lean_children_generic<FULL>(a, L, w0, w1, st, L.sc_lane(), setup, acc, fsc, t1, t2, sc);
@@ -632,8 +662,7 @@ __device__ __forceinline__ void lean_op_special(const LeanArgs & a, const LaneCt
     if (L.lane == 0) a.score_out[(size_t)w0.w * a.score_stride + (blockIdx.x * L4_WARPS + (threadIdx.x >> 5))] += v;
   }
   fsc = make_uint4(0, 0, 0, 0);
-  t1 = n1;
-  t2 = n2;
+  q.advance(n1, n2);
 }
 
 /* One chunk (32 consecutive sites) through the staged operations [0, nseg); the record after the last one is
@@ -661,10 +690,18 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
 #pragma unroll
   for (int r = 0; r < 4; ++r) acc[r][0] = acc[r][1] = acc[r][2] = acc[r][3] = 0.0;
   uint4 fsc = make_uint4(0, 0, 0, 0); /* ... and its scaler counts (sc lanes) */
-  unsigned int t1, t2;                /* packed tip column codes of the CURRENT operation */
+  TipQ q;                             /* packed tip column codes of the CURRENT operation (and the next) */
 
   __syncwarp();
-  lean_prefetch<FULL>(a, L, sops, 0, t1, t2);
+  lean_prefetch<FULL>(a, L, sops, sops, 0, q.t1, q.t2);
+  q.u1 = q.u2 = 0;
+  if (L4_TIP_AHEAD == 2)
+  {
+    const uint4 y0 = lds_u4(sops + 32);
+    const unsigned int ft = lds_u1(sops + 32 + 24) >> 24;
+    if (LOPA_SRC1(ft) == SRC_TIP) q.u1 = lean_load_tips<FULL>(a, L, y0.y);
+    if (LOPA_SRC2(ft) == SRC_TIP) q.u2 = lean_load_tips<FULL>(a, L, y0.z);
+  }
 
   /* The loop variable is the record's shared-memory address (records are 32 bytes: bit 5 = stage).  There is no
    * trip count: the record behind the last operation is all zero (no real operation has parent row = child rows =
@@ -679,18 +716,18 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
     __syncwarp(); /* every lane is done with stage st^1 (previous operation): the bodies refill it for the next one */
     const unsigned int m2f = lds_u1(rec + 28);
     unsigned int type = LOPB_TYPE(m2f >> 24);
-    if (!(SCORING && type == LTYPE_SPECIAL) && (!FULL || __any_sync(0xffffffffu, ((t1 | t2) & 0x80808080u) != 0u)))
+    if (!(SCORING && type == LTYPE_SPECIAL) && (!FULL || __any_sync(0xffffffffu, ((q.t1 | q.t2) & 0x80808080u) != 0u)))
       type = 0; /* partial chunk, or ambiguity codes: generic body */
     switch (type)
     {
-      case LTYPE_TIP_TIP: lean_op_hot<SRC_TIP, SRC_TIP>(a, L, rec, st, acc, fsc, t1, t2); break;
-      case LTYPE_TIP_FWD: lean_op_hot<SRC_TIP, SRC_FWD>(a, L, rec, st, acc, fsc, t1, t2); break;
-      case LTYPE_STASH_FWD: lean_op_hot<SRC_STASH, SRC_FWD>(a, L, rec, st, acc, fsc, t1, t2); break;
-      case LTYPE_GLOBAL_FWD: lean_op_hot<SRC_GLOBAL, SRC_FWD>(a, L, rec, st, acc, fsc, t1, t2); break;
-      case LTYPE_TIP_GLOBAL: lean_op_hot<SRC_TIP, SRC_GLOBAL>(a, L, rec, st, acc, fsc, t1, t2); break;
-      case LTYPE_GLOBAL_GLOBAL: lean_op_hot<SRC_GLOBAL, SRC_GLOBAL>(a, L, rec, st, acc, fsc, t1, t2); break;
+      case LTYPE_TIP_TIP: lean_op_hot<SRC_TIP, SRC_TIP>(a, L, rec, st, acc, fsc, q); break;
+      case LTYPE_TIP_FWD: lean_op_hot<SRC_TIP, SRC_FWD>(a, L, rec, st, acc, fsc, q); break;
+      case LTYPE_STASH_FWD: lean_op_hot<SRC_STASH, SRC_FWD>(a, L, rec, st, acc, fsc, q); break;
+      case LTYPE_GLOBAL_FWD: lean_op_hot<SRC_GLOBAL, SRC_FWD>(a, L, rec, st, acc, fsc, q); break;
+      case LTYPE_TIP_GLOBAL: lean_op_hot<SRC_TIP, SRC_GLOBAL>(a, L, rec, st, acc, fsc, q); break;
+      case LTYPE_GLOBAL_GLOBAL: lean_op_hot<SRC_GLOBAL, SRC_GLOBAL>(a, L, rec, st, acc, fsc, q); break;
       case LTYPE_SPECIAL:
-        if (SCORING) lean_op_special<FULL>(a, L, rec, st, acc, fsc, t1, t2); /* only the scoring kernel carries this body */
+        if (SCORING) lean_op_special<FULL>(a, L, rec, st, acc, fsc, q); /* only the scoring kernel carries this body */
         break;
       default:
         if (m2f == 0u)
@@ -698,7 +735,7 @@ __device__ __forceinline__ void lean_chunk(const LeanArgs & a, unsigned int sops
           const uint4 z = lds_u4(rec);
           if ((z.x | z.y | z.z) == 0u) goto list_done;
         }
-        lean_op_generic<FULL>(a, L, rec, st, acc, fsc, t1, t2);
+        lean_op_generic<FULL>(a, L, rec, st, acc, fsc, q);
         break;
     }
   }
