@@ -448,8 +448,8 @@ def main():
     fused_min_bytes = (tips - 2) * S * 132 + tips * S
     achieved = fused_min_bytes / (kern_avg * 1e-3) / 1e9
     # dram__bytes_read.sum + dram__bytes_write.sum of the kernel in one `ncu --set full` capture at 200k sites
-    # (profiles/r02_trav_dna4_ncu_full_summary.csv): 0.75 GB read + 26.46 GB written; linear in sites
-    traffic = 27.208e9 * S / 200000.0 * (tips - 2) / 998.0
+    # (profiles/r02zz_trav_dna4_ncu_full_summary.csv): 0.745 GB read + 26.309 GB written; linear in sites
+    traffic = 27.054e9 * S / 200000.0 * (tips - 2) / 998.0
     # the kernel's DRAM traffic is writes, and a write-only stream does not reach the copy figure of
     # MEASURED_PEAKS.json: time one here (4 GiB fill, best of 5)
     write_peak = None
@@ -487,7 +487,7 @@ def main():
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic,
                          "traffic_note": "constant from one ncu --set full capture of this kernel at 200k sites "
-                                         "(profiles/r02_trav_dna4_ncu_full_summary.csv: dram read 0.75 GB + write 26.46 GB), "
+                                         "(profiles/r02zz_trav_dna4_ncu_full_summary.csv: dram read 0.745 GB + write 26.309 GB), "
                                          "scaled linearly in sites and operations; not measured by this run "
                                          "(a 1M-site launch cannot be replayed by ncu)",
                          "achieved_is": "fused-minimum bytes / kernel time: (taxa-2) x sites x 132 B written + taxa x sites "
