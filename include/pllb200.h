@@ -1038,7 +1038,9 @@ typedef struct
 void pllb200_get_stats(pllb200_stats_t * out);
 void pllb200_reset_stats(void);
 /* Experiment knobs (never needed by a caller; DESIGN.md section 7 lists them): "trav_variant", "trav_stash", "trav_short",
- * "trav_forward", "trav_reorder", "trav_ctas_per_sm", "fuse_root", "fused_newton" (0 per-iteration path, 1 TMA ring /
+ * "trav_forward", "trav_reorder", "trav_ctas_per_sm", "trav_split" / "trav_split_rounds" (sub-list length, 0 = one
+ * list; chunks per resident warp below which a full traversal runs as independent sub-lists), "fuse_root",
+ * "fused_newton" (0 per-iteration path, 1 TMA ring /
  * tensor-core pass, 2 register version, 3 generic kernel), "queued_newton", "spr_batch", "scratch_rows",
  * "generic_dmma" (17..64 states on the FP64 tensor cores), "fast_evals" (0 general logL / derivative kernels,
  * 1 TMA ring, 2 register tile kernels), "eval_timing".  Returns the previous value, -1 if the name is unknown. */
